@@ -558,3 +558,420 @@ def flatten(ts: TaskSpec) -> dict:
     M["_missing_meshes"] = list(mc.missing)
     M["opt_timestep"], M["opt_gravity"], M["opt_density"], M["opt_viscosity"] = dt, gravity, density, viscosity
     return M
+
+
+# ----------------------------------------------------------------------------
+def _mix_pair(g1: Geom, g2: Geom):
+    """MuJoCo contact-parameter mixing for equal priority [3P]: condim/friction/margin/gap = max,
+    solref/solimp = solmix-weighted mean."""
+    mix = g1.solmix / (g1.solmix + g2.solmix)
+    fr = np.maximum(g1.friction, g2.friction)
+    if g1.solref[0] > 0 and g2.solref[0] > 0:
+        solref = mix * g1.solref + (1 - mix) * g2.solref
+    else:
+        solref = np.minimum(g1.solref, g2.solref)
+    solimp = mix * g1.solimp + (1 - mix) * g2.solimp
+    return (max(g1.condim, g2.condim), fr, solref, solimp, max(g1.margin, g2.margin), max(g1.gap, g2.gap))
+
+
+def _rbound(g: Geom):
+    s = g.size
+    return {"plane": -1.0, "sphere": s[0], "capsule": s[0] + s[1], "ellipsoid": max(s),
+            "cylinder": np.hypot(s[0], s[1]), "box": np.linalg.norm(s)}[g.type]
+
+
+def finalize(M: dict, ts: TaskSpec) -> dict:
+    """Second half of the flattening: geoms, candidate pairs, sites, tendons,
+    actuators, sensors, fluid elements, qpos0-derived constants, task tables."""
+    fb_parent = M["body_parent"]
+    owner_of = M["_owner_of"]
+    order = {b.name: i for i, b in enumerate(ts.world.walk())}  # unfused (MuJoCo) body numbering
+    geoms = M.pop("_geoms")
+    ng = len(geoms)
+    for i, r in enumerate(geoms):
+        r["mjbody"] = order[r["spec_body"]]
+    M["ngeom"] = ng
+    M["geom_type"] = np.array([GEOM_TYPES[r["g"].type] for r in geoms], np.int32)
+    M["geom_bodyid"] = np.array([r["body"] for r in geoms], np.int32)
+    M["geom_pos"] = np.array([r["pos"] for r in geoms])
+    M["geom_quat"] = np.array([r["quat"] for r in geoms])
+    M["geom_size"] = np.array([r["g"].size for r in geoms])
+    M["geom_rbound"] = np.array([_rbound(r["g"]) for r in geoms])
+    M["_names_geom"] = [r["g"].name for r in geoms]
+
+    excl = set()
+    for a, b in ts.excludes:
+        excl.add((a, b))
+        excl.add((b, a))
+    pairs = []
+    for i in range(ng):
+        for j in range(i + 1, ng):
+            a, b = geoms[i], geoms[j]
+            ga, gb = a["g"], b["g"]
+            if not ((ga.contype & gb.conaffinity) or (gb.contype & ga.conaffinity)):
+                continue
+            w1, w2 = a["body"], b["body"]
+            if w1 == w2:
+                continue
+            wp1 = fb_parent[w1] if w1 > 0 else -1
+            wp2 = fb_parent[w2] if w2 > 0 else -1
+            if w1 != 0 and w2 != 0 and (w1 == wp2 or w2 == wp1):
+                continue
+            if (a["spec_body"], b["spec_body"]) in excl:
+                continue
+            key = (min(a["mjbody"], b["mjbody"]), max(a["mjbody"], b["mjbody"]))
+            first, second = (i, j) if a["mjbody"] <= b["mjbody"] else (j, i)
+            pairs.append((key, first, second))
+    pairs.sort(key=lambda p: (p[0], p[1], p[2]))
+    pg1, pg2, pcd, pfr, psr, psi, pmg, pgap = [], [], [], [], [], [], [], []
+    for _, i, j in pairs:
+        if M["geom_type"][i] > M["geom_type"][j]:
+            i, j = j, i
+        cd, fr, sr, si, mg, gp = _mix_pair(geoms[i]["g"], geoms[j]["g"])
+        pg1.append(i); pg2.append(j); pcd.append(cd); pfr.append(fr); psr.append(sr); psi.append(si)
+        pmg.append(mg); pgap.append(gp)
+    M["npair"] = len(pairs)
+    M["pair_geom1"], M["pair_geom2"] = np.array(pg1, np.int32), np.array(pg2, np.int32)
+    M["pair_condim"] = np.array(pcd, np.int32)
+    M["pair_friction"], M["pair_solref"], M["pair_solimp"] = np.array(pfr), np.array(psr), np.array(psi)
+    M["pair_margin"], M["pair_gap"] = np.array(pmg), np.array(pgap)
+
+    sites = M.pop("_sites")
+    M["nsite"] = len(sites)
+    M["site_bodyid"] = np.array([r["body"] for r in sites], np.int32)
+    M["site_pos"] = np.array([r["pos"] for r in sites])
+    M["site_quat"] = np.array([r["quat"] for r in sites])
+    M["site_type"] = np.array([GEOM_TYPES[r["s"].type] for r in sites], np.int32)
+    M["site_size"] = np.array([r["s"].size for r in sites])
+    M["_names_site"] = [r["s"].name for r in sites]
+    sid = {n: i for i, n in enumerate(M["_names_site"])}
+    jid = M.pop("_jid")
+
+    # fixed tendons
+    tadr, tnum, wdof, wqpos, wcoef, tid = [], [], [], [], [], {}
+    for t in ts.tendons:
+        tid[t.name] = len(tadr)
+        tadr.append(len(wdof)); tnum.append(len(t.joints))
+        for jn_, c in t.joints:
+            j = jid[jn_]
+            wdof.append(M["jnt_dofadr"][j]); wqpos.append(M["jnt_qposadr"][j]); wcoef.append(c)
+    M["ntendon"], M["nwrap"] = len(tadr), len(wdof)
+    M["tendon_adr"], M["tendon_num"] = np.array(tadr, np.int32), np.array(tnum, np.int32)
+    M["wrap_dofadr"], M["wrap_qposadr"], M["wrap_coef"] = np.array(wdof, np.int32), np.array(wqpos, np.int32), np.array(wcoef)
+
+    # actuators
+    acts = ts.actuators
+    nu = len(acts)
+    trn = {"joint": 0, "tendon": 1, "body": 2}
+    M["nu"] = nu
+    M["act_trntype"] = np.array([trn[a.trntype] for a in acts], np.int32)
+    tr = []
+    for a in acts:
+        if a.trntype == "joint":
+            tr.append(jid[a.target])
+        elif a.trntype == "tendon":
+            tr.append(tid[a.target])
+        else:
+            tr.append(owner_of[a.target][0])
+    M["act_trnid"] = np.array(tr, np.int32)
+    M["act_gainprm"] = np.array([a.gainprm for a in acts], np.float64)
+    M["act_biasprm"] = np.array([a.biasprm if a.biastype == "affine" else np.zeros(3) for a in acts]).reshape(nu, 3)
+    M["act_dyntype"] = np.array([1 if a.dyntype == "filter" else 0 for a in acts], np.int32)
+    M["act_dynprm"] = np.array([a.dynprm for a in acts], np.float64)
+    M["act_ctrllimited"] = np.array([int(a.ctrllimited) for a in acts], np.int32)
+    M["act_ctrlrange"] = np.array([a.ctrlrange for a in acts]).reshape(nu, 2)
+    M["act_forcelimited"] = np.array([int(a.forcelimited) for a in acts], np.int32)
+    M["act_forcerange"] = np.array([a.forcerange for a in acts]).reshape(nu, 2)
+    M["act_gear"] = np.array([a.gear for a in acts], np.float64)
+    adr, na = [], 0
+    for a in acts:
+        if a.dyntype == "filter":
+            adr.append(na); na += 1
+        else:
+            adr.append(-1)
+    M["na"] = na
+    M["act_actadr"] = np.array(adr, np.int32)
+    M["_names_act"] = [a.name for a in acts]
+
+    # sensors (site sensors only); sensordata layout in MJCF order
+    st = {"accelerometer": 0, "gyro": 1, "velocimeter": 2, "force": 3, "touch": 4}
+    sens = [s for s in ts.sensors if s.site in sid]
+    M["nsensor"] = len(sens)
+    M["sensor_type"] = np.array([st[s.type] for s in sens], np.int32)
+    M["sensor_site"] = np.array([sid[s.site] for s in sens], np.int32)
+    sadr, n = [], 0
+    for s in sens:
+        sadr.append(n); n += 1 if s.type == "touch" else 3
+    M["sensor_adr"], M["nsensordata"] = np.array(sadr, np.int32), n
+    M["_names_sensor"] = [s.name for s in sens]
+
+    # fluid elements
+    fbx = M.pop("_fluid_boxes")
+    use_fluid = M["opt_density"] > 0 or M["opt_viscosity"] > 0
+    if not use_fluid:
+        fbx = []
+    M["nfluidbox"] = len(fbx)
+    M["fbox_bodyid"] = np.array([r["body"] for r in fbx], np.int32)
+    M["fbox_pos"] = np.array([r["pos"] for r in fbx]).reshape(-1, 3)
+    M["fbox_quat"] = np.array([r["quat"] for r in fbx]).reshape(-1, 4)
+    M["fbox_size"] = np.array([r["box"] for r in fbx]).reshape(-1, 3)
+    fg = M.pop("_fluid_geoms")
+    M["nfluidgeom"] = len(fg)
+    M["fgeom_bodyid"] = np.array([r["body"] for r in fg], np.int32)
+    M["fgeom_pos"] = np.array([r["pos"] for r in fg]).reshape(-1, 3)
+    M["fgeom_quat"] = np.array([r["quat"] for r in fg]).reshape(-1, 4)
+    M["fgeom_size"] = np.array([r["g"].size for r in fg]).reshape(-1, 3)
+    M["fgeom_coef"] = np.array([_ellipsoid_fluid_coef(r["g"]) for r in fg]).reshape(-1, 12)
+    return M
+
+
+def _ellipsoid_fluid_coef(g: Geom):
+    """geom_fluid[12] = [interaction, blunt, slender, angular, kutta, magnus, virtual_mass[3],
+    virtual_inertia[3]] — added-mass coefficients of an ellipsoid in potential flow (Lamb) [3P]."""
+    from scipy.integrate import quad
+    a, b, c = g.size
+    def kappa(x, y, z):
+        f = lambda l: 1.0 / ((x * x + l) * np.sqrt((x * x + l) * (y * y + l) * (z * z + l)))
+        return x * y * z * quad(f, 0, np.inf, limit=400)[0]
+    k = np.array([kappa(a, b, c), kappa(b, c, a), kappa(c, a, b)])
+    vol = 4.0 / 3.0 * np.pi * a * b * c
+    vmass = vol * k / np.maximum(1e-12, 2 - k)
+    d = np.array([a, b, c])
+    vin = np.zeros(3)
+    for i in range(3):
+        j, l = (i + 1) % 3, (i + 2) % 3
+        num = (d[j] ** 2 - d[l] ** 2) ** 2 * abs(k[l] - k[j])
+        den = max(1e-12, abs(2 * (d[j] ** 2 - d[l] ** 2) + (d[j] ** 2 + d[l] ** 2) * (k[j] - k[l])))
+        vin[i] = vol * num / den / 5.0
+    return np.concatenate([[1.0], g.fluidcoef, vmass, vin])
+
+
+# ----------------------------------------------------------------------------
+def _kin0(M, qpos):
+    """Plain numpy forward kinematics (host-side, for compile-time constants only)."""
+    nb = M["nbody"]
+    xpos, xquat = np.zeros((nb, 3)), np.tile([1.0, 0, 0, 0], (nb, 1))
+    xanchor, xaxis = np.zeros((M["njnt"], 3)), np.zeros((M["njnt"], 3))
+    for b in range(1, nb):
+        p = M["body_parent"][b]
+        pos, quat = _compose(xpos[p], xquat[p], M["body_pos"][b], M["body_quat"][b])
+        for j in range(M["body_jntadr"][b], M["body_jntadr"][b] + M["body_jntnum"][b]):
+            a, t = M["jnt_qposadr"][j], M["jnt_type"][j]
+            if t == JNT_FREE:
+                pos, quat = qpos[a:a + 3].copy(), qpos[a + 3:a + 7] / np.linalg.norm(qpos[a + 3:a + 7])
+                xanchor[j], xaxis[j] = pos, quat_rot(quat, M["jnt_axis"][j])
+                continue
+            xanchor[j] = pos + quat_rot(quat, M["jnt_pos"][j])
+            xaxis[j] = quat_rot(quat, M["jnt_axis"][j])
+            if t == JNT_BALL:
+                ql = qpos[a:a + 4] / np.linalg.norm(qpos[a:a + 4])
+            else:
+                ang = qpos[a] - M["qpos0"][a]
+                ql = np.concatenate([[np.cos(ang / 2)], np.sin(ang / 2) * M["jnt_axis"][j]])
+            quat = quat_mul(quat, ql)
+            pos = xanchor[j] - quat_rot(quat, M["jnt_pos"][j])
+        xpos[b], xquat[b] = pos, quat
+    return xpos, xquat, xanchor, xaxis
+
+
+def _mass_matrix0(M, qpos):
+    """Dense M(q) = sum_b J_b^T diag(I_b, m_b) J_b + armature, and the per-body 6xnv Jacobians at the
+    body CoM ([rot; lin] rows)."""
+    nb, nv = M["nbody"], M["nv"]
+    xpos, xquat, xanchor, xaxis = _kin0(M, qpos)
+    xipos = np.array([xpos[b] + quat_rot(xquat[b], M["body_ipos"][b]) for b in range(nb)])
+    J = np.zeros((nb, 6, nv))
+    for b in range(1, nb):
+        c = b
+        while c > 0:
+            R = quat_to_mat(xquat[c])
+            for j in range(M["body_jntadr"][c], M["body_jntadr"][c] + M["body_jntnum"][c]):
+                d, t = M["jnt_dofadr"][j], M["jnt_type"][j]
+                if t == JNT_HINGE:
+                    J[b, :3, d] = xaxis[j]
+                    J[b, 3:, d] = np.cross(xaxis[j], xipos[b] - xanchor[j])
+                else:
+                    if t == JNT_FREE:
+                        J[b, 3:, d:d + 3] = np.eye(3)
+                        d += 3
+                    for k in range(3):
+                        J[b, :3, d + k] = R[:, k]
+                        J[b, 3:, d + k] = np.cross(R[:, k], xipos[b] - xanchor[j])
+            c = M["body_parent"][c]
+    H = np.diag(M["dof_armature"]).astype(np.float64)
+    for b in range(1, nb):
+        Ri = quat_to_mat(quat_mul(xquat[b], M["body_iquat"][b]))
+        Iw = Ri @ np.diag(M["body_inertia"][b]) @ Ri.T
+        H += J[b, :3].T @ Iw @ J[b, :3] + M["body_mass"][b] * J[b, 3:].T @ J[b, 3:]
+    return H, J
+
+
+def constants(M: dict, ts: TaskSpec) -> dict:
+    """qpos0-derived constants [3P mj_setConst]: dof_invweight0, body_invweight0, meaninertia,
+    `springdamper` -> stiffness/damping."""
+    nv, nb = M["nv"], M["nbody"]
+    H, J = _mass_matrix0(M, M["qpos0"])
+    Hinv = np.linalg.inv(H)
+    M["stat_meaninertia"] = float(np.trace(H) / nv)
+    dinv = np.diag(Hinv).copy()
+    dof_iw = np.zeros(nv)
+    for j in range(M["njnt"]):
+        d, t = M["jnt_dofadr"][j], M["jnt_type"][j]
+        if t == JNT_HINGE:
+            dof_iw[d] = dinv[d]
+        elif t == JNT_BALL:
+            dof_iw[d:d + 3] = dinv[d:d + 3].mean()
+        else:
+            dof_iw[d:d + 3] = dinv[d:d + 3].mean()
+            dof_iw[d + 3:d + 6] = dinv[d + 3:d + 6].mean()
+    M["dof_invweight0"] = dof_iw
+    biw = np.zeros((nb, 2))
+    for b in range(1, nb):
+        if M["body_mass"][b] <= 0 and M["body_dofnum"][b] == 0:
+            continue
+        A = J[b] @ Hinv @ J[b].T
+        biw[b, 0] = np.trace(A[3:, 3:]) / 3.0  # translational
+        biw[b, 1] = np.trace(A[:3, :3]) / 3.0  # rotational
+    M["body_invweight0"] = biw
+    # springdamper (haltere class, fruitfly.xml:90): stiffness/damping from the joint's effective inertia
+    stiff, damp = M["jnt_stiffness"].copy(), M["dof_damping"].copy()
+    names = M["_names_jnt"]
+    spec_j = {j.name: j for j in [jj for b in ts.world.walk() for jj in b.joints]}
+    for j, nm in enumerate(names):
+        sd = spec_j[nm].springdamper
+        if sd is not None and sd[0] > 0 and sd[1] > 0:
+            d = M["jnt_dofadr"][j]
+            inertia = 1.0 / max(MJ_MINVAL, dof_iw[d])
+            stiff[j] = inertia / max(MJ_MINVAL, sd[0] ** 2 * sd[1] ** 2)
+            damp[d] = 2.0 * inertia / max(MJ_MINVAL, sd[0])
+    M["jnt_stiffness"], M["dof_damping"] = stiff, damp
+    return M
+
+
+# ----------------------------------------------------------------------------
+_TASK_TYPE = {"walk_on_ball": 0, "walk_imitation": 1, "flight_imitation": 2}
+_APPENDAGES = ("claw_T1_left", "claw_T1_right", "claw_T2_left", "claw_T2_right", "claw_T3_left",
+               "claw_T3_right", "head")  # fruitfly.py:422-446
+_LEG_HINGES_PER_LEG = 11
+
+
+def task_tables(M: dict, ts: TaskSpec) -> dict:
+    """Index maps and constants of the task layer (action scatter, observation layout, reward/termination
+    thresholds).  Cites: fruitfly.py:283-318,480-526; tasks/base.py:154-168,237-261; walk_imitation.py:60-84;
+    walk_on_ball.py:47; flight_imitation.py:44-85; tasks/constants.py:16-27."""
+    from .model_fields import OBS_KEYS
+    w = ts.walker
+    jn, jq, jd = M["_names_jnt"], M["jnt_qposadr"], M["jnt_dofadr"]
+    jid = {n: i for i, n in enumerate(jn)}
+    sid = {n: i for i, n in enumerate(M["_names_site"])}
+    M["task_type"] = _TASK_TYPE[ts.task]
+    M["n_substeps"], M["future_steps"] = ts.n_substeps, ts.future_steps
+    M["control_dt"], M["time_limit"] = ts.control_dt, ts.time_limit
+    M["max_episode_steps"] = int(round(ts.time_limit / ts.control_dt)) + 1  # walk_imitation.py:60
+    M["action_dim"] = w.action_dim
+    ca = -np.ones(M["nu"], np.int32)
+    for k, idx in w.action_indices.items():
+        if w.ctrl_indices.get(k) and idx:
+            for c, a in zip(w.ctrl_indices[k], idx):
+                ca[c] = a
+    M["ctrl_action"] = ca
+    amin, amax = -np.ones(w.action_dim), np.ones(w.action_dim)
+    for c in range(M["nu"]):
+        if ca[c] >= 0:
+            amin[ca[c]], amax[ca[c]] = M["act_ctrlrange"][c]
+    M["action_min"], M["action_max"] = amin, amax
+    M["user_action"] = w.action_indices["user"][0] if w.action_indices["user"] else -1
+    root = M["_owner_of"]["walker/thorax"][0]
+    M["root_body"] = root
+    if "walker/" in jid:
+        M["root_qposadr"], M["root_dofadr"] = int(jq[jid["walker/"]]), int(jd[jid["walker/"]])
+    else:
+        M["root_qposadr"] = M["root_dofadr"] = -1
+    if "ghost/" in jid:
+        M["ghost_qposadr"], M["ghost_dofadr"] = int(jq[jid["ghost/"]]), int(jd[jid["ghost/"]])
+    else:
+        M["ghost_qposadr"] = M["ghost_dofadr"] = -1
+    M["ball_dofadr"] = int(jd[jid["ball"]]) if "ball" in jid else -1
+    M["thorax_site"] = sid["walker/thorax"]
+    oj = ["walker/" + n for n in w.observable_joints]
+    M["n_obs_joints"] = len(oj)
+    M["obs_joint_qposadr"] = np.array([jq[jid[n]] for n in oj], np.int32)
+    M["obs_joint_dofadr"] = np.array([jd[jid[n]] for n in oj], np.int32)
+    walking = ts.task != "flight_imitation"
+    app = [sid["walker/" + n] for n in _APPENDAGES] if walking else []
+    M["n_appendages"], M["appendage_site"] = len(app), np.array(app, np.int32)
+    # mocap joints/sites: the walking dataset's id2name lists are not shipped
+    # (config/train_config_fly.yaml:12); default = the 66 leg hinges in model order, 6 claw sites.
+    if ts.task == "walk_imitation":
+        mj = [i for i, n in enumerate(jn) if n.startswith("walker/") and _any_in(_LEG, n)]
+        ms = [sid["walker/" + n] for n in _APPENDAGES[:6]]
+    else:
+        mj, ms = [], []
+    M["n_mocap_joints"], M["mocap_joint"] = len(mj), np.array(mj, np.int32)
+    M["n_mocap_sites"], M["mocap_site"] = len(ms), np.array(ms, np.int32)
+    wj = [f"walker/wing_{ax}_{side}" for side in ("left", "right") for ax in ("yaw", "roll", "pitch")]
+    M["wing_joint"] = np.array([jid[n] for n in wj], np.int32)  # flight_imitation.py / base.py:315-320 order
+    M["wing_action"] = np.array(w.action_indices["wings"] if w.action_indices["wings"] else [-1] * 6, np.int32)
+    # reset pose: qpos0, wings at springref (fruitfly.py:335-340) == retract_wings values (task_utils.py:117-122)
+    qr = M["qpos0"].copy()
+    if walking:
+        for n in wj:
+            qr[jq[jid[n]]] = M["qpos_spring"][jq[jid[n]]]
+    M["qpos_reset"] = qr
+    # observation layout (alphabetical keys)
+    F = ts.future_steps + 1
+    dims = {"accelerometer": 3, "gyro": 3, "velocimeter": 3, "world_zaxis": 3, "joints_pos": len(oj),
+            "joints_vel": len(oj), "actuator_activation": M["na"]}
+    if walking:
+        dims.update(appendages_pos=21, force=18, touch=6)
+    if ts.task == "walk_on_ball":
+        dims["ball_qvel"] = 3
+    if ts.task in ("walk_imitation", "flight_imitation"):
+        dims.update(ref_displacement=3 * F, ref_root_quat=4 * F)
+    off, n = -np.ones(16, np.int32), 0
+    for i, k in enumerate(OBS_KEYS):
+        if k in dims:
+            off[i] = n
+            n += dims[k]
+    M["obs_offset"], M["obs_dim"] = off, n
+    M["_obs_dims"] = dims
+    M["terminal_linvel"], M["terminal_angvel"] = 50.0, 200.0  # tasks/constants.py:18-19
+    M["terminal_qacc"], M["terminal_height"] = 1e14, 0.2      # constants.py:25,27
+    M["terminal_com_dist"] = {"walk_imitation": 0.3, "flight_imitation": 2.0}.get(ts.task, 0.0)  # fly_envs.py:33,78
+    M["ghost_offset"] = np.zeros(3)
+    M["pad_first_obs"], M["inference_mode"] = 0, 0
+    # solver options: MuJoCo defaults [3P] + fruitfly.xml:4
+    M["opt_iterations"], M["opt_ls_iterations"] = 100, 50
+    M["opt_noslip_iterations"] = int(ts.option.get("noslip_iterations", 0))
+    M["opt_tolerance"], M["opt_ls_tolerance"], M["opt_noslip_tolerance"], M["opt_impratio"] = 1e-8, 0.01, 1e-6, 1.0
+    return M
+
+
+def compile_task(task: str, xml_path: str) -> dict:
+    ts = TaskSpec(task, xml_path)
+    M = flatten(ts)
+    M = finalize(M, ts)
+    M = constants(M, ts)
+    M = task_tables(M, ts)
+    M.pop("_owner_of")
+    return M
+
+
+def save_model(M: dict, path: str):
+    import json
+    arrs = {k: np.asarray(v) for k, v in M.items() if not k.startswith("_")}
+    meta = {k: v for k, v in M.items() if k.startswith("_")}
+    np.savez_compressed(path, _meta=np.frombuffer(json.dumps(meta).encode(), dtype=np.uint8), **arrs)
+
+
+def load_model(path: str) -> dict:
+    import json
+    z = np.load(path)
+    M = {}
+    for k in z.files:
+        if k == "_meta":
+            M.update(json.loads(bytes(z[k]).decode()))
+        else:
+            a = z[k]
+            M[k] = a.item() if a.ndim == 0 else a
+    return M
