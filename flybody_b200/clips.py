@@ -1,0 +1,129 @@
+"""Reference clips for the imitation tasks (host side).
+
+The 16 252-snippet walking dataset named by `vnl_ray/config/train_config_fly.yaml:12` is not shipped, and
+h5py is not installed, so clips are generated synthetically in the *format* the reference loaders produce
+(`vnl_ray/tasks/trajectory_loaders.py:163-215`): per clip
+    qpos       [T, 7 + n_j]   root pos, root quat, mocap joint angles (xy re-origined, loaders :130,206)
+    qvel       [T, 6 + n_j]   root linear (world) / angular (local) velocity, joint velocities
+    root2site  [T, n_s, 3]    egocentric end-effector vectors   (semantics of rewards.py:36-60)
+    joint_quat [T, n_j, 4]    egocentric joint orientation quats (quaternions.py:298-321)
+`pack_clips` lays a set of clips out as one float32 table + offsets for the device.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from .mjcf import quat_mul, quat_conj, quat_to_mat, quat_rot
+from .compile_fly import _kin0, JNT_HINGE
+
+
+def _quat_z2vec(v):
+    v = v / np.linalg.norm(v)
+    if v[0] == 0.0 and v[1] == 0.0:
+        return np.array([0.0, 1, 0, 0]) if v[2] < 0 else np.array([1.0, 0, 0, 0])
+    ax = np.array([-v[1], v[0], 0.0])
+    ax /= np.linalg.norm(ax)
+    ang = np.arccos(v[2])
+    return np.concatenate([[np.cos(ang / 2)], np.sin(ang / 2) * ax])
+
+
+def walker_features(M: dict, qpos: np.ndarray):
+    """root2site [n_s,3] and joint_quat [n_j,4] of the walker at `qpos` (rewards.get_walker_features)."""
+    xpos, xquat, xanchor, xaxis = _kin0(M, qpos)
+    ra = M["root_qposadr"]
+    p, q = qpos[ra:ra + 3], qpos[ra + 3:ra + 7] / np.linalg.norm(qpos[ra + 3:ra + 7])
+    Rt = quat_to_mat(q).T
+    r2s = []
+    for s in M["mocap_site"]:
+        b = M["site_bodyid"][s]
+        sp = xpos[b] + quat_rot(xquat[b], M["site_pos"][s])
+        r2s.append(Rt @ (sp - p))
+    jq = []
+    for j in M["mocap_joint"]:
+        ax = Rt @ xaxis[j]
+        ang = qpos[M["jnt_qposadr"][j]]
+        q2 = np.concatenate([[np.cos(ang / 2)], np.sin(ang / 2) * ax / np.linalg.norm(ax)])
+        jq.append(quat_mul(q2, _quat_z2vec(ax)))
+    return np.array(r2s).reshape(-1, 3), np.array(jq).reshape(-1, 4)
+
+
+def synth_walk_clip(M: dict, T: int = 600, seed: int = 0, speed=(1.0, 3.0), features: bool = True):
+    """One synthetic walking clip: smooth random-walk root path at 1-3 cm/s, z at the spawn height
+    (fruitfly.py:23), integrated yaw, tripod-gait leg sinusoids inside each joint's range."""
+    rng = np.random.RandomState(seed)
+    dt = float(M["control_dt"])
+    nj = int(M["n_mocap_joints"])
+    v = rng.uniform(*speed)
+    yaw_rate = np.cumsum(rng.normal(0, 0.02, T)) * 0.5
+    yaw_rate = np.clip(yaw_rate, -1.0, 1.0)
+    yaw = rng.uniform(-np.pi, np.pi) + np.cumsum(yaw_rate) * dt
+    pos = np.zeros((T, 3))
+    pos[:, 0] = np.cumsum(v * np.cos(yaw)) * dt
+    pos[:, 1] = np.cumsum(v * np.sin(yaw)) * dt
+    pos[:, :2] -= pos[0, :2]
+    pos[:, 2] = M["qpos0"][M["root_qposadr"] + 2]
+    quat = np.stack([np.cos(yaw / 2), 0 * yaw, 0 * yaw, np.sin(yaw / 2)], axis=1)
+    qpos = np.zeros((T, 7 + nj))
+    qpos[:, :3], qpos[:, 3:7] = pos, quat
+    names = M["_names_jnt"]
+    t = np.arange(T) * dt
+    freq = rng.uniform(8.0, 12.0)
+    for i, j in enumerate(M["mocap_joint"]):
+        lo, hi = M["jnt_range"][j]
+        n = names[j]
+        leg = ["T1_left", "T1_right", "T2_left", "T2_right", "T3_left", "T3_right"]
+        li = next((k for k, s in enumerate(leg) if s in n), 0)
+        phase = 0.0 if li in (0, 3, 4) else np.pi  # tripod groups
+        amp = 0.0
+        if "coxa_T" in n and "twist" not in n and "abduct" not in n:
+            amp = 0.12
+        elif "femur_T" in n and "twist" not in n:
+            amp = 0.15
+        elif "tibia" in n:
+            amp = 0.15
+        a = amp * np.sin(2 * np.pi * freq * t + phase + (0.5 if "tibia" in n else 0.0))
+        qpos[:, 7 + i] = np.clip(M["qpos0"][M["jnt_qposadr"][j]] + a, lo + 1e-3, hi - 1e-3)
+    qvel = np.zeros((T, 6 + nj))
+    qvel[:-1, :3] = np.diff(pos, axis=0) / dt
+    for k in range(T - 1):
+        dq = quat_mul(quat_conj(quat[k]), quat[k + 1])
+        s = np.linalg.norm(dq[1:])
+        ang = 2 * np.arctan2(s, dq[0])
+        qvel[k, 3:6] = (dq[1:] / s * ang / dt) if s > 1e-12 else 0.0
+    qvel[:-1, 6:] = np.diff(qpos[:, 7:], axis=0) / dt
+    qvel[-1] = qvel[-2]
+    clip = dict(qpos=qpos, qvel=qvel)
+    if features:
+        r2s, jq = np.zeros((T, int(M["n_mocap_sites"]), 3)), np.zeros((T, nj, 4))
+        full = M["qpos_reset"].copy()
+        for k in range(T):
+            full[M["root_qposadr"]:M["root_qposadr"] + 7] = qpos[k, :7]
+            for i, j in enumerate(M["mocap_joint"]):
+                full[M["jnt_qposadr"][j]] = qpos[k, 7 + i]
+            r2s[k], jq[k] = walker_features(M, full)
+        clip.update(root2site=r2s, joint_quat=jq)
+    return clip
+
+
+def clip_row_width(M: dict) -> int:
+    """Floats per packed clip row: qpos (7+n_j) | qvel (6+n_j) | root2site (3 n_s) | joint_quat (4 n_j)."""
+    nj, ns = int(M["n_mocap_joints"]), int(M["n_mocap_sites"])
+    return (7 + nj) + (6 + nj) + 3 * ns + 4 * nj
+
+
+def pack_clips(M: dict, clips: list):
+    """-> (table float32 [sum T, row_width], offsets int32 [n], lengths int32 [n])."""
+    W = clip_row_width(M)
+    nj, ns = int(M["n_mocap_joints"]), int(M["n_mocap_sites"])
+    rows, off, ln, n = [], [], [], 0
+    for c in clips:
+        T = c["qpos"].shape[0]
+        r = np.zeros((T, W), np.float32)
+        r[:, :7 + nj] = c["qpos"]
+        r[:, 7 + nj:13 + 2 * nj] = c["qvel"]
+        if ns:
+            r[:, 13 + 2 * nj:13 + 2 * nj + 3 * ns] = c["root2site"].reshape(T, -1)
+        if nj:
+            r[:, 13 + 2 * nj + 3 * ns:] = c["joint_quat"].reshape(T, -1)
+        rows.append(r); off.append(n); ln.append(T); n += T
+    return np.concatenate(rows), np.array(off, np.int32), np.array(ln, np.int32)

@@ -868,6 +868,14 @@ def task_tables(M: dict, ts: TaskSpec) -> dict:
     M["n_substeps"], M["future_steps"] = ts.n_substeps, ts.future_steps
     M["control_dt"], M["time_limit"] = ts.control_dt, ts.time_limit
     M["max_episode_steps"] = int(round(ts.time_limit / ts.control_dt)) + 1  # walk_imitation.py:60
+    # composer.Environment ends the episode when physics.time() >= time_limit; time is the float64 running sum of
+    # the physics timestep, so the first control step at which that holds is found by the same accumulation.
+    t, k = 0.0, 0
+    while t < ts.time_limit:
+        for _ in range(ts.n_substeps):
+            t += ts.physics_dt
+        k += 1
+    M["time_limit_steps"] = k
     M["action_dim"] = w.action_dim
     ca = -np.ones(M["nu"], np.int32)
     for k, idx in w.action_indices.items():

@@ -16,7 +16,7 @@ SCALAR_INT = [
     "opt_iterations", "opt_ls_iterations", "opt_noslip_iterations",
     # task block
     "task_type",            # 0 walk_on_ball, 1 walk_imitation, 2 flight_imitation
-    "n_substeps", "future_steps", "action_dim", "obs_dim", "max_episode_steps",
+    "n_substeps", "future_steps", "action_dim", "obs_dim", "max_episode_steps", "time_limit_steps",
     "root_body", "root_qposadr", "root_dofadr", "ghost_qposadr", "ghost_dofadr", "ball_dofadr",
     "thorax_site", "n_obs_joints", "n_appendages", "n_mocap_joints", "n_mocap_sites",
     "user_action", "pad_first_obs", "inference_mode",

@@ -1,0 +1,139 @@
+"""ctypes wrapper of the float64 CPU oracle (oracle/flyb_oracle.c).  TEST INFRASTRUCTURE ONLY:
+imported by tests/, __graft_entry__.smoke() and bench.py's CPU-baseline legs, never by flybody_b200/."""
+from __future__ import annotations
+
+import ctypes
+import os
+import subprocess
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = os.path.join(_HERE, "_build", "libflyb_oracle.so")
+
+
+def build(force: bool = False):
+    src = os.path.join(_HERE, "flyb_oracle.c")
+    if force or not os.path.exists(_LIB) or os.path.getmtime(_LIB) < os.path.getmtime(src):
+        subprocess.check_call(["make", "-s", "-C", _HERE])
+    return _LIB
+
+
+class Contact(ctypes.Structure):
+    _fields_ = [("pair", ctypes.c_int), ("geom1", ctypes.c_int), ("geom2", ctypes.c_int), ("dim", ctypes.c_int),
+                ("exclude", ctypes.c_int), ("efc_address", ctypes.c_int), ("dist", ctypes.c_double),
+                ("includemargin", ctypes.c_double), ("mu", ctypes.c_double), ("pos", ctypes.c_double * 3),
+                ("frame", ctypes.c_double * 9), ("friction", ctypes.c_double * 3), ("solref", ctypes.c_double * 2),
+                ("solimp", ctypes.c_double * 5)]
+
+
+class Clip(ctypes.Structure):
+    _fields_ = [("T", ctypes.c_int), ("qpos", ctypes.POINTER(ctypes.c_double)), ("qvel", ctypes.POINTER(ctypes.c_double)),
+                ("root2site", ctypes.POINTER(ctypes.c_double)), ("joint_quat", ctypes.POINTER(ctypes.c_double))]
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        from flybody_b200.model_pack import FlybModel
+        L = ctypes.CDLL(build())
+        L.flyo_create.restype = ctypes.c_void_p
+        L.flyo_create.argtypes = [ctypes.POINTER(FlybModel)]
+        for fn in ("flyo_destroy", "flyo_reset_data", "flyo_forward", "flyo_step"):
+            getattr(L, fn).argtypes = [ctypes.c_void_p]
+            getattr(L, fn).restype = None
+        L.flyo_set_option.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_double]
+        L.flyo_dptr.restype = ctypes.POINTER(ctypes.c_double)
+        L.flyo_dptr.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.POINTER(ctypes.c_int)]
+        L.flyo_iptr.restype = ctypes.POINTER(ctypes.c_int)
+        L.flyo_iptr.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.POINTER(ctypes.c_int)]
+        L.flyo_contacts.restype = ctypes.POINTER(Contact)
+        L.flyo_contacts.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_int)]
+        L.flyo_set_clip.argtypes = [ctypes.c_void_p, ctypes.POINTER(Clip)]
+        dp = ctypes.POINTER(ctypes.c_double)
+        L.flyo_env_reset.argtypes = [ctypes.c_void_p, dp]
+        L.flyo_env_reset.restype = ctypes.c_int
+        L.flyo_env_step.argtypes = [ctypes.c_void_p, dp, dp, dp, dp]
+        L.flyo_env_step.restype = ctypes.c_int
+        _lib = L
+    return _lib
+
+
+class OracleEnv:
+    """One float64 environment.  `d("qpos")` returns a live numpy view into the C arrays."""
+
+    def __init__(self, model: dict):
+        from flybody_b200.model_pack import pack_model
+        self.M = model
+        self._struct, self._keep = pack_model(model)
+        self._h = lib().flyo_create(ctypes.byref(self._struct))
+        self._clip = None
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().flyo_destroy(self._h)
+            self._h = None
+
+    def d(self, name: str) -> np.ndarray:
+        n = ctypes.c_int(0)
+        p = lib().flyo_dptr(self._h, name.encode(), ctypes.byref(n))
+        if not p:
+            raise KeyError(name)
+        return np.ctypeslib.as_array(p, shape=(n.value,))
+
+    def i(self, name: str) -> np.ndarray:
+        n = ctypes.c_int(0)
+        p = lib().flyo_iptr(self._h, name.encode(), ctypes.byref(n))
+        if not p:
+            raise KeyError(name)
+        return np.ctypeslib.as_array(p, shape=(max(n.value, 0),))
+
+    def option(self, name: str, value: float):
+        lib().flyo_set_option(self._h, name.encode(), float(value))
+
+    def reset_data(self):
+        lib().flyo_reset_data(self._h)
+
+    def forward(self):
+        lib().flyo_forward(self._h)
+
+    def step(self, n: int = 1):
+        for _ in range(n):
+            lib().flyo_step(self._h)
+
+    def contacts(self):
+        n = ctypes.c_int(0)
+        p = lib().flyo_contacts(self._h, ctypes.byref(n))
+        out = []
+        for k in range(n.value):
+            c = p[k]
+            out.append(dict(pair=c.pair, geom1=c.geom1, geom2=c.geom2, dim=c.dim, exclude=c.exclude,
+                            efc_address=c.efc_address, dist=c.dist, pos=np.array(c.pos), frame=np.array(c.frame),
+                            mu=c.mu, friction=np.array(c.friction)))
+        return out
+
+    # ---- task level
+    def set_clip(self, qpos, qvel, root2site=None, joint_quat=None):
+        arrs = [np.ascontiguousarray(a, dtype=np.float64) if a is not None else None
+                for a in (qpos, qvel, root2site, joint_quat)]
+        dp = ctypes.POINTER(ctypes.c_double)
+        c = Clip(T=arrs[0].shape[0], qpos=arrs[0].ctypes.data_as(dp), qvel=arrs[1].ctypes.data_as(dp),
+                 root2site=arrs[2].ctypes.data_as(dp) if arrs[2] is not None else None,
+                 joint_quat=arrs[3].ctypes.data_as(dp) if arrs[3] is not None else None)
+        self._clip = (c, arrs)
+        lib().flyo_set_clip(self._h, ctypes.byref(c))
+
+    def env_reset(self):
+        obs = np.zeros(self.M["obs_dim"])
+        st = lib().flyo_env_reset(self._h, obs.ctypes.data_as(ctypes.POINTER(ctypes.c_double)))
+        return st, obs
+
+    def env_step(self, action):
+        dp = ctypes.POINTER(ctypes.c_double)
+        a = np.ascontiguousarray(action, dtype=np.float64)
+        obs = np.zeros(self.M["obs_dim"])
+        r, g = ctypes.c_double(0), ctypes.c_double(0)
+        st = lib().flyo_env_step(self._h, a.ctypes.data_as(dp), obs.ctypes.data_as(dp), ctypes.byref(r), ctypes.byref(g))
+        return st, r.value, g.value, obs
