@@ -1,0 +1,496 @@
+/* fly_dyn.cuh - smooth dynamics of one environment, warp-cooperative.
+ *
+ * Stages m1-m4, m7-m10 of SURVEY.md section 8(a2): kinematics, subtree CoM / cinert / cdof, composite
+ * inertia -> tree-sparse mass matrix, L^T D L factorisation and solves on the tree sparsity, body
+ * velocities, passive forces (springs, dampers, inertia-box and ellipsoid fluid models), RNE bias,
+ * actuation.  The tree recursions run one depth level at a time with the bodies (or dofs, or matrix
+ * entries) of the level spread over the lanes; sums toward the root are gathers over precomputed
+ * child / descendant lists so that no atomics are needed and results are deterministic. */
+#ifndef FLY_DYN_CUH_
+#define FLY_DYN_CUH_
+#include "fly_ws.cuh"
+
+/* ---------------------------------------------------------------- m1 kinematics */
+template <class T>
+FLY_FN void fly_kinematics(const DModel<T>& m, const Ws<T>& w) {
+  FLY_LANE0 {
+    for (int k = 0; k < 3; k++) { w.xpos[k] = 0; w.xipos[k] = 0; }
+    w.xquat[0] = 1; w.xquat[1] = w.xquat[2] = w.xquat[3] = 0;
+    for (int k = 0; k < 9; k++) { w.xmat[k] = (k % 4 == 0) ? T(1) : T(0); w.ximat[k] = w.xmat[k]; }
+  }
+  FLY_SYNC();
+  for (int L = 1; L <= m.nlevel; L++) {
+    const int adr = m.lvl_adr[L], n = m.lvl_adr[L + 1] - adr;
+    FLY_FOR(k, n) {
+      const int b = m.lvl_body[adr + k], p = m.body_parent[b];
+      T pos[3], quat[4], t[3];
+      mat_vec(t, w.xmat + 9 * p, m.body_pos + 3 * b);
+      for (int c = 0; c < 3; c++) pos[c] = w.xpos[3 * p + c] + t[c];
+      quat_mul(quat, w.xquat + 4 * p, m.body_quat + 4 * b);
+      const int j0 = m.body_jntadr[b], j1 = j0 + m.body_jntnum[b];
+      for (int j = j0; j < j1; j++) {
+        const int qa = m.jnt_qposadr[j], type = m.jnt_type[j];
+        if (type == FLYB_JNT_FREE) {
+          quat_normalize(w.qpos + qa + 3);
+          for (int c = 0; c < 3; c++) { pos[c] = w.qpos[qa + c]; w.xanchor[3 * j + c] = pos[c]; }
+          for (int c = 0; c < 4; c++) quat[c] = w.qpos[qa + 3 + c];
+          rot_vec_quat(w.xaxis + 3 * j, m.jnt_axis + 3 * j, quat);
+          continue;
+        }
+        T anchor[3];
+        rot_vec_quat(t, m.jnt_pos + 3 * j, quat);
+        for (int c = 0; c < 3; c++) { anchor[c] = pos[c] + t[c]; w.xanchor[3 * j + c] = anchor[c]; }
+        rot_vec_quat(w.xaxis + 3 * j, m.jnt_axis + 3 * j, quat);
+        T ql[4], nq[4];
+        if (type == FLYB_JNT_BALL) {
+          quat_normalize(w.qpos + qa);
+          for (int c = 0; c < 4; c++) ql[c] = w.qpos[qa + c];
+        } else {
+          axis_angle_quat(ql, m.jnt_axis + 3 * j, w.qpos[qa] - m.qpos0[qa]);
+        }
+        quat_mul(nq, quat, ql);
+        for (int c = 0; c < 4; c++) quat[c] = nq[c];
+        rot_vec_quat(t, m.jnt_pos + 3 * j, quat);
+        for (int c = 0; c < 3; c++) pos[c] = anchor[c] - t[c];
+      }
+      quat_normalize(quat);
+      T mat[9], iq[4];
+      quat2mat(mat, quat);
+      for (int c = 0; c < 3; c++) w.xpos[3 * b + c] = pos[c];
+      for (int c = 0; c < 4; c++) w.xquat[4 * b + c] = quat[c];
+      for (int c = 0; c < 9; c++) w.xmat[9 * b + c] = mat[c];
+      mat_vec(t, mat, m.body_ipos + 3 * b);
+      for (int c = 0; c < 3; c++) w.xipos[3 * b + c] = pos[c] + t[c];
+      quat_mul(iq, quat, m.body_iquat + 4 * b);
+      quat2mat(w.ximat + 9 * b, iq);
+    }
+    FLY_SYNC();
+  }
+  FLY_FOR(g, m.ngeom) {
+    const int b = m.geom_bodyid[g];
+    T t[3];
+    mat_vec(t, w.xmat + 9 * b, m.geom_pos + 3 * g);
+    for (int c = 0; c < 3; c++) w.geom_xpos[3 * g + c] = w.xpos[3 * b + c] + t[c];
+  }
+  FLY_FOR(s, m.nsite) {
+    const int b = m.site_bodyid[s];
+    T t[3];
+    mat_vec(t, w.xmat + 9 * b, m.site_pos + 3 * s);
+    for (int c = 0; c < 3; c++) w.site_xpos[3 * s + c] = w.xpos[3 * b + c] + t[c];
+    mat_mul(w.site_xmat + 9 * s, w.xmat + 9 * b, m.site_mat + 9 * s);
+  }
+  FLY_SYNC();
+}
+
+/* world-frame rotation of a collision geom */
+template <class T>
+FLY_INL void fly_geom_xmat(const DModel<T>& m, const Ws<T>& w, int g, T* mat) {
+  mat_mul(mat, w.xmat + 9 * m.geom_bodyid[g], m.geom_mat + 9 * g);
+}
+
+/* acc[b] (K numbers per body) <- acc[b] + sum over children, for every non-world body, leaves first */
+template <class T>
+FLY_INL void fly_tree_upsweep(const DModel<T>& m, T* acc, int K) {
+  for (int L = m.nlevel - 1; L >= 1; L--) {
+    const int adr = m.lvl_adr[L], n = m.lvl_adr[L + 1] - adr;
+    FLY_FOR(it, n * K) {
+      const int b = m.lvl_body[adr + it / K], c = it % K;
+      const int c0 = m.child_adr[b], c1 = m.child_adr[b + 1];
+      if (c1 > c0) {
+        T s = acc[K * b + c];
+        for (int q = c0; q < c1; q++) s += acc[K * m.child[q] + c];
+        acc[K * b + c] = s;
+      }
+    }
+    FLY_SYNC();
+  }
+}
+
+/* ---------------------------------------------------------------- m2 comPos */
+template <class T>
+FLY_FN void fly_com_pos(const DModel<T>& m, const Ws<T>& w) {
+  FLY_FOR(it, 3 * m.nbody) w.scom[it] = m.body_mass[it / 3] * w.xipos[it];
+  FLY_SYNC();
+  fly_tree_upsweep(m, w.scom, 3);
+  FLY_FOR(it, 3 * m.nbody) {
+    const int b = it / 3;
+    const T sm = m.body_subtreemass[b];
+    w.scom[it] = sm < minval<T>() ? w.xipos[it] : w.scom[it] / sm;
+  }
+  FLY_SYNC();
+  FLY_FOR(bb, m.nbody - 1) {
+    const int b = bb + 1;
+    const T* R = w.ximat + 9 * b;
+    const T* I = m.body_inertia + 3 * b;
+    const T* c0 = w.scom + 3 * m.body_rootid[b];
+    T d[3], mass = m.body_mass[b];
+    T* ci = w.cinert + 10 * b;
+    for (int k = 0; k < 3; k++) d[k] = w.xipos[3 * b + k] - c0[k];
+    const T dd = dot3(d, d);
+    T W[6];
+    const int rr[6] = {0, 1, 2, 0, 0, 1}, cc[6] = {0, 1, 2, 1, 2, 2};
+    for (int e = 0; e < 6; e++) {
+      const int r = rr[e], c = cc[e];
+      W[e] = R[3 * r] * I[0] * R[3 * c] + R[3 * r + 1] * I[1] * R[3 * c + 1] + R[3 * r + 2] * I[2] * R[3 * c + 2]
+             + mass * ((r == c ? dd : T(0)) - d[r] * d[c]);
+    }
+    for (int e = 0; e < 6; e++) ci[e] = W[e];
+    ci[6] = mass * d[0]; ci[7] = mass * d[1]; ci[8] = mass * d[2]; ci[9] = mass;
+  }
+  FLY_FOR(j, m.njnt) {
+    const int b = m.jnt_bodyid[j];
+    int da = m.jnt_dofadr[j];
+    const T* c0 = w.scom + 3 * m.body_rootid[b];
+    T off[3];
+    for (int k = 0; k < 3; k++) off[k] = c0[k] - w.xanchor[3 * j + k];
+    const int type = m.jnt_type[j];
+    if (type == FLYB_JNT_HINGE) {
+      T* cd = w.cdof + 6 * da;
+      for (int k = 0; k < 3; k++) cd[k] = w.xaxis[3 * j + k];
+      cross3(cd + 3, w.xaxis + 3 * j, off);
+    } else {
+      if (type == FLYB_JNT_FREE) {
+        for (int k = 0; k < 3; k++) {
+          T* cd = w.cdof + 6 * (da + k);
+          for (int c = 0; c < 6; c++) cd[c] = 0;
+          cd[3 + k] = 1;
+        }
+        da += 3;
+      }
+      for (int k = 0; k < 3; k++) {
+        T ax[3] = {w.xmat[9 * b + k], w.xmat[9 * b + 3 + k], w.xmat[9 * b + 6 + k]};
+        T* cd = w.cdof + 6 * (da + k);
+        for (int c = 0; c < 3; c++) cd[c] = ax[c];
+        cross3(cd + 3, ax, off);
+      }
+    }
+  }
+  FLY_SYNC();
+}
+
+/* ---------------------------------------------------------------- m4 CRB -> tree-sparse M */
+template <class T>
+FLY_FN void fly_crb(const DModel<T>& m, const Ws<T>& w) {
+  FLY_FOR(it, 10 * m.nbody) w.crb[it] = it < 10 ? T(0) : w.cinert[it];
+  FLY_SYNC();
+  fly_tree_upsweep(m, w.crb, 10);
+  T* f = w.cdof_dot; /* scratch: cdof_dot is rebuilt later, in the velocity stage */
+  FLY_FOR(i, m.nv) inert_vec(f + 6 * i, w.crb + 10 * m.dof_bodyid[i], w.cdof + 6 * i);
+  FLY_SYNC();
+  FLY_FOR(e, m.nM) {
+    const int i = m.mrow[e], j = m.mcol[e], k = e - m.madr[i];
+    T s = 0;
+    if (k <= m.kdepth[i]) {
+      const T *a = w.cdof + 6 * j, *b = f + 6 * i;
+      s = a[0] * b[0] + a[1] * b[1] + a[2] * b[2] + a[3] * b[3] + a[4] * b[4] + a[5] * b[5];
+      if (k == 0) s += m.dof_armature[i];
+    }
+    w.qM[e] = s;
+  }
+  FLY_SYNC();
+}
+
+/* ---------------------------------------------------------------- tree-sparse L^T D L
+ * A (layout of qM: row i holds A(i, i), A(i, parent), A(i, grandparent) ...) is factorised in place:
+ * afterwards row i holds D_i followed by L(i, ancestor).  Gather form: an entry only reads finished rows
+ * of descendants, so each depth level is one parallel phase. */
+template <class T>
+FLY_FN void fly_factor(const DModel<T>& m, T* A) {
+  for (int L = m.ndlevel - 1; L >= 0; L--) {
+    const int adr = m.dlvl_adr[L], n = m.dlvl_adr[L + 1] - adr, nl = m.dlvl_nlight[L], W = L + 1;
+    FLY_FOR(it, nl * W) {
+      const int i = m.dlvl_dof[adr + it / W], k = it % W;
+      T s = A[m.madr[i] + k];
+      for (int q = m.desc_adr[i]; q < m.desc_adr[i + 1]; q++) {
+        const int pk = m.desc[q], c = pk & 255, a = pk >> 8;
+        s -= A[a] * A[m.madr[c]] * A[a + k];
+      }
+      A[m.madr[i] + k] = s;
+    }
+    for (int h = nl; h < n; h++) {  /* heavy dofs: descendants over lanes, one entry at a time */
+      const int i = m.dlvl_dof[adr + h], q0 = m.desc_adr[i], nd = m.desc_adr[i + 1] - q0;
+      for (int k = 0; k < W; k++) {
+        T s = 0;
+        FLY_FOR(q, nd) {
+          const int pk = m.desc[q0 + q], c = pk & 255, a = pk >> 8;
+          s += A[a] * A[m.madr[c]] * A[a + k];
+        }
+        s = warp_sum(s);
+        FLY_SYNC();
+        FLY_LANE0 A[m.madr[i] + k] -= s;
+      }
+    }
+    FLY_SYNC();
+    FLY_FOR(it, n * W) {
+      const int i = m.dlvl_dof[adr + it / W], k = it % W;
+      if (k > 0) A[m.madr[i] + k] /= A[m.madr[i]];
+    }
+    FLY_SYNC();
+  }
+}
+
+/* x <- (L^T D L)^-1 x */
+template <class T>
+FLY_FN void fly_solve(const DModel<T>& m, const T* LD, T* x) {
+  for (int L = m.ndlevel - 2; L >= 0; L--) {
+    const int adr = m.dlvl_adr[L], n = m.dlvl_adr[L + 1] - adr, nl = m.dlvl_nlight[L];
+    FLY_FOR(k, nl) {
+      const int j = m.dlvl_dof[adr + k];
+      T s = 0;
+      for (int q = m.desc_adr[j]; q < m.desc_adr[j + 1]; q++) {
+        const int pk = m.desc[q];
+        s += LD[pk >> 8] * x[pk & 255];
+      }
+      x[j] -= s;
+    }
+    for (int h = nl; h < n; h++) {
+      const int j = m.dlvl_dof[adr + h], q0 = m.desc_adr[j], nd = m.desc_adr[j + 1] - q0;
+      T s = 0;
+      FLY_FOR(q, nd) {
+        const int pk = m.desc[q0 + q];
+        s += LD[pk >> 8] * x[pk & 255];
+      }
+      s = warp_sum(s);
+      FLY_SYNC();
+      FLY_LANE0 x[j] -= s;
+    }
+    FLY_SYNC();
+  }
+  FLY_FOR(i, m.nv) x[i] /= LD[m.madr[i]];
+  FLY_SYNC();
+  for (int L = 1; L < m.ndlevel; L++) {
+    const int adr = m.dlvl_adr[L], n = m.dlvl_adr[L + 1] - adr;
+    FLY_FOR(k, n) {
+      const int i = m.dlvl_dof[adr + k], a = m.madr[i];
+      T s = 0;
+      for (int q = 1; q <= L; q++) s += LD[a + q] * x[m.mcol[a + q]];
+      x[i] -= s;
+    }
+    FLY_SYNC();
+  }
+}
+
+/* r <- M v (tree-sparse symmetric product) */
+template <class T>
+FLY_FN void fly_mul_m(const DModel<T>& m, const T* M, T* r, const T* v) {
+  FLY_FOR(i, m.nv) {
+    const int a = m.madr[i], nrow = m.madr[i + 1] - a;
+    T s = 0;
+    for (int q = 0; q < nrow; q++) s += M[a + q] * v[m.mcol[a + q]];
+    if (m.hsublast[i] - i <= FLY_HEAVY)
+      for (int q = m.desc_adr[i]; q < m.desc_adr[i + 1]; q++) {
+        const int pk = m.desc[q];
+        s += M[pk >> 8] * v[pk & 255];
+      }
+    r[i] = s;
+  }
+  FLY_SYNC();
+  for (int h = 0; h < m.nheavy; h++) {
+    const int i = m.heavy_dof[h], q0 = m.desc_adr[i], nd = m.desc_adr[i + 1] - q0;
+    T s = 0;
+    FLY_FOR(q, nd) {
+      const int pk = m.desc[q0 + q];
+      s += M[pk >> 8] * v[pk & 255];
+    }
+    s = warp_sum(s);
+    FLY_SYNC();
+    FLY_LANE0 r[i] += s;
+  }
+  FLY_SYNC();
+}
+
+/* ---------------------------------------------------------------- m7 comVel */
+template <class T>
+FLY_FN void fly_com_vel(const DModel<T>& m, const Ws<T>& w) {
+  FLY_LANE0 for (int c = 0; c < 6; c++) w.cvel[c] = 0;
+  FLY_SYNC();
+  for (int L = 1; L <= m.nlevel; L++) {
+    const int adr = m.lvl_adr[L], n = m.lvl_adr[L + 1] - adr;
+    FLY_FOR(k, n) {
+      const int b = m.lvl_body[adr + k];
+      T v[6];
+      for (int c = 0; c < 6; c++) v[c] = w.cvel[6 * m.body_parent[b] + c];
+      const int j0 = m.body_jntadr[b], j1 = j0 + m.body_jntnum[b];
+      for (int j = j0; j < j1; j++) {
+        int d = m.jnt_dofadr[j], nd = 1;
+        const int type = m.jnt_type[j];
+        if (type == FLYB_JNT_FREE) {
+          for (int c = 0; c < 18; c++) w.cdof_dot[6 * d + c] = 0;
+          for (int q = 0; q < 3; q++) for (int c = 0; c < 6; c++) v[c] += w.cdof[6 * (d + q) + c] * w.qvel[d + q];
+          d += 3; nd = 3;
+        } else if (type == FLYB_JNT_BALL) nd = 3;
+        for (int q = 0; q < nd; q++) cross_motion(w.cdof_dot + 6 * (d + q), v, w.cdof + 6 * (d + q));
+        for (int q = 0; q < nd; q++) for (int c = 0; c < 6; c++) v[c] += w.cdof[6 * (d + q) + c] * w.qvel[d + q];
+      }
+      for (int c = 0; c < 6; c++) w.cvel[6 * b + c] = v[c];
+    }
+    FLY_SYNC();
+  }
+}
+
+/* 6D velocity [ang; lin] of a frame (pos, mat) rigidly attached to body b, expressed in that frame */
+template <class T>
+FLY_INL void fly_local_velocity(const DModel<T>& m, const Ws<T>& w, T* lv, int b, const T* pos, const T* mat) {
+  const T* c0 = w.scom + 3 * m.body_rootid[b];
+  const T* cv = w.cvel + 6 * b;
+  T off[3] = {pos[0] - c0[0], pos[1] - c0[1], pos[2] - c0[2]}, t[3], lin[3];
+  cross3(t, cv, off);
+  for (int k = 0; k < 3; k++) lin[k] = cv[3 + k] + t[k];
+  matT_vec(lv, mat, cv);
+  matT_vec(lv + 3, mat, lin);
+}
+
+/* ---------------------------------------------------------------- m7 passive forces */
+template <class T> FLY_INL T pow4(T x) { T y = x * x; return y * y; }
+
+template <class T>
+FLY_FN void fly_passive(const DModel<T>& m, const Ws<T>& w) {
+  FLY_FOR(d, m.nv) {
+    T f = -m.dof_damping[d] * w.qvel[d];
+    const int j = m.dof_jntid[d];
+    if (m.jnt_type[j] == FLYB_JNT_HINGE) {
+      const int qa = m.jnt_qposadr[j];
+      f -= m.jnt_stiffness[j] * (w.qpos[qa] - m.qpos_spring[qa]);
+    }
+    w.qfrc_passive[d] = f;
+  }
+  FLY_SYNC();
+  if (m.flags & FLY_OPT_NOFLUID) return;
+  const T rho = m.density, beta = m.viscosity, PI = T(FLY_PI);
+  const int nbox = m.nfluidbox, nel = nbox + m.nfluidgeom;
+  /* phase 1: each fluid element -> world-frame spatial force [torque; force] about its tree's CoM */
+  FLY_FOR(i, nel) {
+    const bool isbox = i < nbox;
+    const int e = isbox ? i : i - nbox;
+    const int b = isbox ? m.fbox_bodyid[e] : m.fgeom_bodyid[e];
+    const T* lp = isbox ? m.fbox_pos + 3 * e : m.fgeom_pos + 3 * e;
+    const T* lm = isbox ? m.fbox_mat + 9 * e : m.fgeom_mat + 9 * e;
+    T pos[3], mat[9], t[3], lv[6], lf[6];
+    mat_vec(t, w.xmat + 9 * b, lp);
+    for (int k = 0; k < 3; k++) pos[k] = w.xpos[3 * b + k] + t[k];
+    mat_mul(mat, w.xmat + 9 * b, lm);
+    fly_local_velocity(m, w, lv, b, pos, mat);
+    for (int k = 0; k < 6; k++) lf[k] = 0;
+    if (isbox) {
+      const T* bx = m.fbox_size + 3 * e;
+      if (beta > 0) {
+        const T diam = (bx[0] + bx[1] + bx[2]) / T(3);
+        for (int k = 0; k < 3; k++) {
+          lf[k] = -PI * diam * diam * diam * beta * lv[k];
+          lf[3 + k] = -T(3) * PI * diam * beta * lv[3 + k];
+        }
+      }
+      if (rho > 0) {
+        lf[3] -= T(0.5) * rho * bx[1] * bx[2] * fabs_(lv[3]) * lv[3];
+        lf[4] -= T(0.5) * rho * bx[0] * bx[2] * fabs_(lv[4]) * lv[4];
+        lf[5] -= T(0.5) * rho * bx[0] * bx[1] * fabs_(lv[5]) * lv[5];
+        lf[0] -= rho * bx[0] * (pow4(bx[1]) + pow4(bx[2])) * fabs_(lv[0]) * lv[0] / T(64);
+        lf[1] -= rho * bx[1] * (pow4(bx[0]) + pow4(bx[2])) * fabs_(lv[1]) * lv[1] / T(64);
+        lf[2] -= rho * bx[2] * (pow4(bx[0]) + pow4(bx[1])) * fabs_(lv[2]) * lv[2] / T(64);
+      }
+    } else {
+      /* ellipsoid model (wing_*_fluid geoms, vnl_ray/tasks/base.py:309-313) */
+      const T* s = m.fgeom_size + 3 * e;
+      const T* c = m.fgeom_coef + 12 * e;
+      const T blunt = c[1], slender = c[2], angc = c[3], kutta = c[4], magnus = c[5];
+      const T *vm = c + 6, *vi = c + 9, *wv = lv, *v = lv + 3;
+      T p[3] = {rho * vm[0] * v[0], rho * vm[1] * v[1], rho * vm[2] * v[2]};
+      T Lm[3] = {rho * vi[0] * wv[0], rho * vi[1] * wv[1], rho * vi[2] * wv[2]}, a1[3], a2[3], a3[3];
+      cross3(a1, p, wv); cross3(a2, p, v); cross3(a3, Lm, wv);
+      for (int k = 0; k < 3; k++) { lf[3 + k] += a1[k]; lf[k] += a2[k] + a3[k]; }
+      const T vol = T(4.0 / 3.0) * PI * s[0] * s[1] * s[2];
+      const T dmax = fmax_(s[0], fmax_(s[1], s[2])), dmin = fmin_(s[0], fmin_(s[1], s[2]));
+      const T dmid = s[0] + s[1] + s[2] - dmax - dmin;
+      const T A_max = PI * dmax * dmid;
+      T mg[3];
+      cross3(mg, wv, v);
+      for (int k = 0; k < 3; k++) lf[3 + k] += magnus * rho * vol * mg[k];
+      const T bc = s[1] * s[2], ca = s[2] * s[0], ab = s[0] * s[1];
+      const T pd = pow4(bc) * v[0] * v[0] + pow4(ca) * v[1] * v[1] + pow4(ab) * v[2] * v[2];
+      const T pn = bc * bc * v[0] * v[0] + ca * ca * v[1] * v[1] + ab * ab * v[2] * v[2];
+      const T A_proj = PI * sqrt(pd / fmax_(minval<T>(), pn));
+      const T speed = norm3(v);
+      T nrm[3] = {bc * bc * v[0], ca * ca * v[1], ab * ab * v[2]};
+      const T cos_alpha = pn / fmax_(minval<T>(), speed * pd);
+      T circ[3], kf[3];
+      cross3(circ, nrm, v);
+      for (int k = 0; k < 3; k++) circ[k] *= kutta * rho * cos_alpha * A_proj;
+      cross3(kf, circ, v);
+      for (int k = 0; k < 3; k++) lf[3 + k] += kf[k];
+      const T eqD = T(2.0 / 3.0) * (s[0] + s[1] + s[2]);
+      const T I_max = T(8.0 / 15.0) * PI * dmid * pow4(dmax);
+      T mv[3];
+      for (int k = 0; k < 3; k++) {
+        const T o = fmax_(s[(k + 1) % 3], s[(k + 2) % 3]);
+        const T II = T(8.0 / 15.0) * PI * s[k] * pow4(o);
+        mv[k] = wv[k] * (angc * II + slender * (I_max - II));
+      }
+      const T drag_lin = beta * T(3) * PI * eqD + rho * speed * (A_proj * blunt + slender * (A_max - A_proj));
+      const T drag_ang = beta * PI * eqD * eqD * eqD + rho * norm3(mv);
+      for (int k = 0; k < 3; k++) { lf[3 + k] -= drag_lin * v[k]; lf[k] -= drag_ang * wv[k]; }
+      for (int k = 0; k < 6; k++) lf[k] *= c[0];
+    }
+    T f[3], tq[3], off[3], x[3];
+    mat_vec(tq, mat, lf); mat_vec(f, mat, lf + 3);
+    const T* c0 = w.scom + 3 * m.body_rootid[b];
+    for (int k = 0; k < 3; k++) off[k] = pos[k] - c0[k];
+    cross3(x, off, f);
+    for (int k = 0; k < 3; k++) { w.boxf[6 * i + k] = tq[k] + x[k]; w.boxf[6 * i + 3 + k] = f[k]; }
+  }
+  FLY_SYNC();
+  /* phase 2: sum per body, then toward the root; qfrc[d] = cdof[d] . F(subtree of d's body) */
+  FLY_FOR(it, 6 * m.nbody) {
+    const int b = it / 6, c = it % 6;
+    T s = 0;
+    for (int q = m.body_fbox_adr[b]; q < m.body_fbox_adr[b + 1]; q++) s += w.boxf[6 * m.body_fbox[q] + c];
+    for (int g = 0; g < m.nfluidgeom; g++) if (m.fgeom_bodyid[g] == b) s += w.boxf[6 * (nbox + g) + c];
+    w.bodyf[it] = s;
+  }
+  FLY_SYNC();
+  fly_tree_upsweep(m, w.bodyf, 6);
+  FLY_FOR(d, m.nv) {
+    const T *cd = w.cdof + 6 * d, *F = w.bodyf + 6 * m.dof_bodyid[d];
+    w.qfrc_passive[d] += cd[0] * F[0] + cd[1] * F[1] + cd[2] * F[2] + cd[3] * F[3] + cd[4] * F[4] + cd[5] * F[5];
+  }
+  FLY_SYNC();
+}
+
+/* ---------------------------------------------------------------- m8 / m12 recursive Newton-Euler
+ * flg_acc = 0: bias forces into `result`.  flg_acc = 1, post = 1: cacc / cfrc_int with contact forces (sensors). */
+template <class T>
+FLY_FN void fly_rne(const DModel<T>& m, const Ws<T>& w, T* result, int flg_acc, int post) {
+  FLY_LANE0 {
+    for (int c = 0; c < 3; c++) { w.cacc[c] = 0; w.cacc[3 + c] = -m.gravity[c]; }
+    for (int c = 0; c < 6; c++) w.cfrc_int[c] = 0;
+  }
+  FLY_SYNC();
+  for (int L = 1; L <= m.nlevel; L++) {
+    const int adr = m.lvl_adr[L], n = m.lvl_adr[L + 1] - adr;
+    FLY_FOR(k, n) {
+      const int b = m.lvl_body[adr + k];
+      T a[6];
+      for (int c = 0; c < 6; c++) a[c] = w.cacc[6 * m.body_parent[b] + c];
+      const int d0 = m.body_dofadr[b], d1 = d0 + m.body_dofnum[b];
+      for (int d = d0; d < d1; d++) {
+        const T qv = w.qvel[d], qa = flg_acc ? w.qacc[d] : T(0);
+        for (int c = 0; c < 6; c++) a[c] += w.cdof_dot[6 * d + c] * qv + w.cdof[6 * d + c] * qa;
+      }
+      for (int c = 0; c < 6; c++) w.cacc[6 * b + c] = a[c];
+      T Ia[6], Iv[6], x[6];
+      inert_vec(Ia, w.cinert + 10 * b, a);
+      inert_vec(Iv, w.cinert + 10 * b, w.cvel + 6 * b);
+      cross_force(x, w.cvel + 6 * b, Iv);
+      for (int c = 0; c < 6; c++) w.cfrc_int[6 * b + c] = Ia[c] + x[c] - (post ? w.cfrc_ext[6 * b + c] : T(0));
+    }
+    FLY_SYNC();
+  }
+  fly_tree_upsweep(m, w.cfrc_int, 6);
+  if (result) {
+    FLY_FOR(d, m.nv) {
+      const T *cd = w.cdof + 6 * d, *F = w.cfrc_int + 6 * m.dof_bodyid[d];
+      result[d] = cd[0] * F[0] + cd[1] * F[1] + cd[2] * F[2] + cd[3] * F[3] + cd[4] * F[4] + cd[5] * F[5];
+    }
+    FLY_SYNC();
+  }
+}
+#endif

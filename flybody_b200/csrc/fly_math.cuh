@@ -1,0 +1,170 @@
+/* fly_math.cuh - execution-model macros and small vector/quaternion helpers for the fly engine.
+ *
+ * One environment is stepped by ONE WARP.  All engine code is written against four primitives:
+ *   FLY_FOR(i, n)   work items 0..n-1 spread over the 32 lanes (items must be independent)
+ *   FLY_SYNC()      warp barrier + memory ordering between phases
+ *   FLY_LANE0       section executed by a single lane
+ *   warp_sum/max    butterfly all-reduce (identical bits on every lane, so control flow stays uniform)
+ * Under nvcc these map to lane-strided loops, __syncwarp and shuffles.  With FLY_EMU defined (tests/emu,
+ * built by g++ for the CPU unit tests) a "warp" is a single thread: FLY_FOR is a plain loop and the rest
+ * are no-ops, which is exactly equivalent as long as FLY_FOR bodies are independent. */
+#ifndef FLY_MATH_CUH_
+#define FLY_MATH_CUH_
+#include <math.h>
+#include <stdint.h>
+
+#if defined(__CUDACC__) && !defined(FLY_EMU)
+#define FLY_GPU 1
+#define FLY_FN __device__ __noinline__
+#define FLY_INL __device__ __forceinline__
+#define FLY_LANE() ((int)(threadIdx.x & 31))
+#define FLY_FOR(i, n) for (int i = FLY_LANE(); i < (n); i += 32)
+#define FLY_SYNC() __syncwarp()
+#define FLY_LANE0 if (FLY_LANE() == 0)
+#define FLY_LDG(p) __ldg(p)
+template <class T> FLY_INL T warp_sum(T v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+template <class T> FLY_INL T warp_max(T v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) { T u = __shfl_xor_sync(0xffffffffu, v, o); v = u > v ? u : v; }
+  return v;
+}
+FLY_INL int warp_sum_i(int v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+/* ordered stream compaction of the items i in [0,n) with pred(i): writes their indices to out[], in order */
+template <class P> FLY_INL int warp_compact(int n, P pred, unsigned short* out, int maxout) {
+  int cnt = 0;
+  const int lane = FLY_LANE();
+  for (int base = 0; base < n; base += 32) {
+    int i = base + lane;
+    bool p = i < n && pred(i);
+    unsigned mask = __ballot_sync(0xffffffffu, p);
+    int pos = cnt + __popc(mask & ((1u << lane) - 1u));
+    if (p && pos < maxout) out[pos] = (unsigned short)i;
+    cnt += __popc(mask);
+  }
+  __syncwarp();
+  return cnt;
+}
+#else
+#define FLY_FN static
+#define FLY_INL static inline
+#define FLY_LANE() 0
+#define FLY_FOR(i, n) for (int i = 0; i < (n); i++)
+#define FLY_SYNC()
+#define FLY_LANE0
+#define FLY_LDG(p) (*(p))
+template <class T> FLY_INL T warp_sum(T v) { return v; }
+template <class T> FLY_INL T warp_max(T v) { return v; }
+FLY_INL int warp_sum_i(int v) { return v; }
+template <class P> FLY_INL int warp_compact(int n, P pred, unsigned short* out, int maxout) {
+  int cnt = 0;
+  for (int i = 0; i < n; i++)
+    if (pred(i)) { if (cnt < maxout) out[cnt] = (unsigned short)i; cnt++; }
+  return cnt;
+}
+#endif
+
+#define FLY_MINVAL 1e-15
+#define FLY_PI 3.14159265358979323846
+
+template <class T> FLY_INL T fmin_(T a, T b) { return a < b ? a : b; }
+template <class T> FLY_INL T fmax_(T a, T b) { return a > b ? a : b; }
+template <class T> FLY_INL T fabs_(T a) { return a < 0 ? -a : a; }
+/* smallest positive value treated as zero; float cannot represent 1e-15 relative sizes so keep it tiny */
+template <class T> FLY_INL T minval() { return (T)FLY_MINVAL; }
+
+template <class T> FLY_INL void cross3(T* r, const T* a, const T* b) {
+  T x = a[1] * b[2] - a[2] * b[1], y = a[2] * b[0] - a[0] * b[2], z = a[0] * b[1] - a[1] * b[0];
+  r[0] = x; r[1] = y; r[2] = z;
+}
+template <class T> FLY_INL T dot3(const T* a, const T* b) { return a[0] * b[0] + a[1] * b[1] + a[2] * b[2]; }
+template <class T> FLY_INL T norm3(const T* a) { return sqrt(dot3(a, a)); }
+template <class T> FLY_INL T normalize3(T* a) {
+  T n = norm3(a);
+  if (n < minval<T>()) { a[0] = 1; a[1] = 0; a[2] = 0; return 0; }
+  T s = T(1) / n;
+  a[0] *= s; a[1] *= s; a[2] *= s;
+  return n;
+}
+template <class T> FLY_INL void quat_mul(T* r, const T* a, const T* b) {
+  T w = a[0] * b[0] - a[1] * b[1] - a[2] * b[2] - a[3] * b[3];
+  T x = a[0] * b[1] + a[1] * b[0] + a[2] * b[3] - a[3] * b[2];
+  T y = a[0] * b[2] - a[1] * b[3] + a[2] * b[0] + a[3] * b[1];
+  T z = a[0] * b[3] + a[1] * b[2] - a[2] * b[1] + a[3] * b[0];
+  r[0] = w; r[1] = x; r[2] = y; r[3] = z;
+}
+template <class T> FLY_INL void quat_normalize(T* q) {
+  T n = sqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
+  if (n < minval<T>()) { q[0] = 1; q[1] = q[2] = q[3] = 0; return; }
+  T s = T(1) / n;
+  q[0] *= s; q[1] *= s; q[2] *= s; q[3] *= s;
+}
+template <class T> FLY_INL void quat2mat(T* m, const T* q) {
+  T w = q[0], x = q[1], y = q[2], z = q[3];
+  m[0] = w * w + x * x - y * y - z * z; m[1] = 2 * (x * y - w * z); m[2] = 2 * (x * z + w * y);
+  m[3] = 2 * (x * y + w * z); m[4] = w * w - x * x + y * y - z * z; m[5] = 2 * (y * z - w * x);
+  m[6] = 2 * (x * z - w * y); m[7] = 2 * (y * z + w * x); m[8] = w * w - x * x - y * y + z * z;
+}
+template <class T> FLY_INL void mat_vec(T* r, const T* m, const T* v) {
+  T x = m[0] * v[0] + m[1] * v[1] + m[2] * v[2], y = m[3] * v[0] + m[4] * v[1] + m[5] * v[2],
+    z = m[6] * v[0] + m[7] * v[1] + m[8] * v[2];
+  r[0] = x; r[1] = y; r[2] = z;
+}
+template <class T> FLY_INL void matT_vec(T* r, const T* m, const T* v) {
+  T x = m[0] * v[0] + m[3] * v[1] + m[6] * v[2], y = m[1] * v[0] + m[4] * v[1] + m[7] * v[2],
+    z = m[2] * v[0] + m[5] * v[1] + m[8] * v[2];
+  r[0] = x; r[1] = y; r[2] = z;
+}
+template <class T> FLY_INL void mat_mul(T* r, const T* a, const T* b) { /* r = a b, 3x3 row-major */
+  for (int i = 0; i < 3; i++)
+    for (int j = 0; j < 3; j++) r[3 * i + j] = a[3 * i] * b[j] + a[3 * i + 1] * b[3 + j] + a[3 * i + 2] * b[6 + j];
+}
+template <class T> FLY_INL void rot_vec_quat(T* r, const T* v, const T* q) {
+  T m[9];
+  quat2mat(m, q);
+  mat_vec(r, m, v);
+}
+template <class T> FLY_INL void axis_angle_quat(T* q, const T* axis, T angle) {
+  T s = sin(T(0.5) * angle);
+  q[0] = cos(T(0.5) * angle); q[1] = axis[0] * s; q[2] = axis[1] * s; q[3] = axis[2] * s;
+}
+/* q <- q * exp(h w / 2), w in the local frame */
+template <class T> FLY_INL void quat_integrate(T* q, const T* w, T h) {
+  T ax[3] = {w[0], w[1], w[2]};
+  T n = normalize3(ax);
+  if (n * h == 0 || n < minval<T>()) return;
+  T dq[4], r[4];
+  axis_angle_quat(dq, ax, n * h);
+  quat_mul(r, q, dq);
+  q[0] = r[0]; q[1] = r[1]; q[2] = r[2]; q[3] = r[3];
+  quat_normalize(q);
+}
+/* spatial algebra on [angular; linear] 6-vectors about a common point */
+template <class T> FLY_INL void cross_motion(T* r, const T* v, const T* s) {
+  T a[3], b[3], c[3];
+  cross3(a, v, s); cross3(b, v, s + 3); cross3(c, v + 3, s);
+  r[0] = a[0]; r[1] = a[1]; r[2] = a[2]; r[3] = b[0] + c[0]; r[4] = b[1] + c[1]; r[5] = b[2] + c[2];
+}
+template <class T> FLY_INL void cross_force(T* r, const T* v, const T* f) {
+  T a[3], b[3], c[3];
+  cross3(a, v, f); cross3(b, v + 3, f + 3); cross3(c, v, f + 3);
+  r[0] = a[0] + b[0]; r[1] = a[1] + b[1]; r[2] = a[2] + b[2]; r[3] = c[0]; r[4] = c[1]; r[5] = c[2];
+}
+/* 10-number spatial inertia about a reference point: [Ixx Iyy Izz Ixy Ixz Iyz, m*c(3), m] */
+template <class T> FLY_INL void inert_vec(T* r, const T* I, const T* v) {
+  const T* h = I + 6;
+  T m = I[9], hv[3], wh[3];
+  cross3(hv, h, v + 3); cross3(wh, v, h);
+  r[0] = I[0] * v[0] + I[3] * v[1] + I[4] * v[2] + hv[0];
+  r[1] = I[3] * v[0] + I[1] * v[1] + I[5] * v[2] + hv[1];
+  r[2] = I[4] * v[0] + I[5] * v[1] + I[2] * v[2] + hv[2];
+  r[3] = m * v[3] + wh[0]; r[4] = m * v[4] + wh[1]; r[5] = m * v[5] + wh[2];
+}
+#endif
