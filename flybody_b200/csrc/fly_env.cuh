@@ -1,0 +1,350 @@
+/* fly_env.cuh - one control step (or reset) of one environment: composer.Environment.step semantics
+ *  with the task hooks of vnl_ray/tasks fused in. */
+#ifndef FLY_ENV_CUH_
+#define FLY_ENV_CUH_
+#include "fly_task.cuh"
+
+/* per-env persistent integers */
+enum { FLY_SI_STEP = 0, FLY_SI_EPISODE_STEPS, FLY_SI_RESET_NEXT, FLY_SI_CLIP, FLY_SI_EPISODE, FLY_SI_FORCED_CLIP,
+       FLY_SI_EPLEN, FLY_SI_COUNT = 8 };
+/* per-env trace integers (optional debug output) */
+enum { FLY_TR_NCON = 0, FLY_TR_NEFC, FLY_TR_NLIMIT, FLY_TR_NITER, FLY_TR_OVERFLOW, FLY_TR_NCAND, FLY_TR_PAIRS = 8,
+       FLY_TR_INTS = 8 + FLY_MAXCON };
+
+template <class T>
+struct FlyIO {
+  T* sreal;            /* [N, sreal_stride]: qpos | qvel | act | qacc_warmstart | episode return */
+  int* sint;           /* [N, FLY_SI_COUNT] */
+  int sreal_stride;
+  const float* action; /* [N, action_dim] */
+  float* obs;          /* [N, obs_dim] */
+  float* reward;       /* [N] */
+  float* discount;     /* [N] */
+  int* step_type;      /* [N] 0 FIRST, 1 MID, 2 LAST */
+  int* trace_int;      /* nullable [N, FLY_TR_INTS] */
+  T* trace_real;       /* nullable [N, trace_real_stride]: con_dist[MAXCON] | qacc[nv] | sensordata | efc_force[MAXEFC] */
+  int trace_real_stride;
+  float* stats;        /* nullable [N, 4] per-env episode stats written at episode end: return, length, fatal, count */
+  unsigned long long seed;
+  int env_offset;      /* global id of env 0 of this shard */
+  int force_reset;     /* 1: reset every env in mask regardless of reset_next */
+  const unsigned char* reset_mask; /* nullable */
+};
+
+FLY_INL unsigned long long fly_hash(unsigned long long x) {  /* splitmix64 finaliser */
+  x += 0x9E3779B97F4A7C15ull;
+  x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+  x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+  return x ^ (x >> 31);
+}
+
+template <class T> FLY_INL void quat_recip(T* r, const T* q) {  /* quaternions.py:88-102 */
+  const T n2 = q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3];
+  r[0] = q[0] / n2; r[1] = -q[1] / n2; r[2] = -q[2] / n2; r[3] = -q[3] / n2;
+}
+template <class T> FLY_INL void quat_rotate(T* r, const T* v, const T* q) {  /* quaternions.py:105-134 */
+  T qi[4], va[4] = {0, v[0], v[1], v[2]}, t[4], o[4];
+  quat_recip(qi, q);
+  quat_mul(t, va, qi); quat_mul(o, q, t);
+  r[0] = o[1]; r[1] = o[2]; r[2] = o[3];
+}
+template <class T> FLY_INL void quat_z2vec(T* q, const T* vin) {  /* quaternions.py:205-252 */
+  T v[3] = {vin[0], vin[1], vin[2]};
+  const bool edge = (v[0] == 0 && v[1] == 0);
+  if (edge) v[0] = 1;
+  const T n = norm3(v);
+  v[0] /= n; v[1] /= n; v[2] /= n;
+  if (edge) { if (v[2] < 0) { q[0] = 0; q[1] = 1; q[2] = 0; q[3] = 0; } else { q[0] = 1; q[1] = q[2] = q[3] = 0; } return; }
+  T ax[2] = {-v[1], v[0]};
+  const T an = sqrt(ax[0] * ax[0] + ax[1] * ax[1]);
+  ax[0] /= an; ax[1] /= an;
+  const T ang = acos(v[2]);
+  q[0] = cos(ang / 2); q[1] = sin(ang / 2) * ax[0]; q[2] = sin(ang / 2) * ax[1]; q[3] = 0;
+}
+template <class T> FLY_INL T quat_dist_short_arc(const T* a, const T* b) {  /* quaternions.py:273-295 */
+  const T na = sqrt(a[0] * a[0] + a[1] * a[1] + a[2] * a[2] + a[3] * a[3]);
+  const T nb = sqrt(b[0] * b[0] + b[1] * b[1] + b[2] * b[2] + b[3] * b[3]);
+  const T d = (a[0] * b[0] + a[1] * b[1] + a[2] * b[2] + a[3] * b[3]) / (na * nb);
+  T x = 2 * d * d - 1;
+  if (x > 1) x = 1;
+  return acos(x);
+}
+
+struct FlyClipView { const float* rows; int T; };
+template <class T>
+FLY_INL const float* fly_clip_row(const DModel<T>& m, const FlyClipView& c, int row) {
+  if (row >= c.T) row = c.T - 1;
+  return c.rows + (size_t)row * m.clip_width;
+}
+
+/* observation assembly: fruitfly.py:532-669, tasks/base.py:237-261, walk_on_ball.py:81-88 */
+template <class T>
+FLY_FN void fly_write_obs(const DModel<T>& m, const Ws<T>& w, const FlyClipView& clip, int step_counter, float* obs,
+                          T sensor_scale) {
+  const int* off = m.obs_offset;
+  const int rb = m.root_body;
+  const T *rp = w.xpos + 3 * rb, *rm = w.xmat + 9 * rb;
+  FLY_FOR(s, m.nsensor) {
+    const int key = m.sensor_obs[2 * s], idx = m.sensor_obs[2 * s + 1];
+    const int dim = m.sensor_type[s] == FLYB_SENS_TOUCH ? 1 : 3;
+    if (off[key] >= 0)
+      for (int k = 0; k < dim; k++) obs[off[key] + dim * idx + k] = (float)(w.sens_sum[m.sensor_adr[s] + k] * sensor_scale);
+  }
+  if (off[FLYB_OBS_ACTUATOR_ACTIVATION] >= 0) FLY_FOR(i, m.na) obs[off[FLYB_OBS_ACTUATOR_ACTIVATION] + i] = (float)w.act[i];
+  if (off[FLYB_OBS_APPENDAGES_POS] >= 0)
+    FLY_FOR(i, m.n_appendages) {
+      const T* sp = w.site_xpos + 3 * m.appendage_site[i];
+      T d[3] = {sp[0] - rp[0], sp[1] - rp[1], sp[2] - rp[2]}, o[3];
+      matT_vec(o, rm, d);
+      for (int k = 0; k < 3; k++) obs[off[FLYB_OBS_APPENDAGES_POS] + 3 * i + k] = (float)o[k];
+    }
+  if (off[FLYB_OBS_BALL_QVEL] >= 0) FLY_FOR(k, 3) obs[off[FLYB_OBS_BALL_QVEL] + k] = (float)w.qvel[m.ball_dofadr + k];
+  FLY_FOR(i, m.n_obs_joints) {
+    obs[off[FLYB_OBS_JOINTS_POS] + i] = (float)w.qpos[m.obs_joint_qposadr[i]];
+    obs[off[FLYB_OBS_JOINTS_VEL] + i] = (float)w.qvel[m.obs_joint_dofadr[i]];
+  }
+  FLY_FOR(k, 3) obs[off[FLYB_OBS_WORLD_ZAXIS] + k] = (float)rm[6 + k];
+  if (off[FLYB_OBS_REF_DISPLACEMENT] >= 0 && clip.rows) {
+    const T* rq = w.qpos + m.root_qposadr + 3;
+    T qi[4];
+    quat_recip(qi, rq);
+    FLY_FOR(i, m.future_steps + 1) {
+      const float* r = fly_clip_row(m, clip, step_counter + i);
+      T d[3], o[3], q[4], rqt[4] = {(T)r[3], (T)r[4], (T)r[5], (T)r[6]};
+      for (int k = 0; k < 3; k++) d[k] = (T)r[k] - w.qpos[m.root_qposadr + k];
+      matT_vec(o, rm, d);
+      quat_mul(q, qi, rqt);  /* quaternions.py:13-17 */
+      for (int k = 0; k < 3; k++) obs[off[FLYB_OBS_REF_DISPLACEMENT] + 3 * i + k] = (float)o[k];
+      for (int k = 0; k < 4; k++) obs[off[FLYB_OBS_REF_ROOT_QUAT] + 4 * i + k] = (float)q[k];
+      if (i == 0) for (int k = 0; k < 3; k++) w.obs_tmp[k] = o[k];
+    }
+  }
+  FLY_SYNC();
+}
+
+/* DeepMimic-style reward: walk_imitation.py:151-163, rewards.py:36-111 */
+template <class T>
+FLY_FN T fly_walk_imitation_reward(const DModel<T>& m, const Ws<T>& w, const FlyClipView& clip, int step) {
+  if (m.inference_mode || !clip.rows) return T(1);
+  const int nj = m.n_mocap_joints, ns = m.n_mocap_sites;
+  const float* row = fly_clip_row(m, clip, step);
+  const float *rq = row, *rv = row + 7 + nj, *r2s = rv + 6 + nj, *rjq = r2s + 3 * ns;
+  const T* q = w.qpos + m.root_qposadr;
+  const T* v = w.qvel + m.root_dofadr;
+  T d_com = 0, d_qvel = 0, d_r2s = 0, d_jq = 0;
+  for (int k = 0; k < 3; k++) d_com += (q[k] - (T)rq[k]) * (q[k] - (T)rq[k]);
+  T part_qvel = 0, part_jq = 0, part_r2s = 0;
+  const T qc[4] = {q[3], -q[4], -q[5], -q[6]};
+  T qr[4];
+  quat_recip(qr, q + 3);
+  FLY_FOR(i, nj) {
+    const int j = m.mocap_joint[i];
+    const T qj = w.qpos[m.jnt_qposadr[j]], vj = w.qvel[m.jnt_dofadr[j]];
+    part_qvel += (vj - (T)rv[6 + i]) * (vj - (T)rv[6 + i]);
+    T ax[3], q1[4], q2[4], jq[4];
+    quat_rotate(ax, w.xaxis + 3 * j, qr);   /* rewards.py:47-48 */
+    quat_z2vec(q1, ax);                       /* quaternions.py:298-321 */
+    const T n = norm3(ax);
+    const T a2[3] = {ax[0] / n, ax[1] / n, ax[2] / n};
+    axis_angle_quat(q2, a2, qj);
+    quat_mul(jq, q2, q1);
+    const T ref[4] = {(T)rjq[4 * i], (T)rjq[4 * i + 1], (T)rjq[4 * i + 2], (T)rjq[4 * i + 3]};
+    const T a = quat_dist_short_arc(jq, ref);
+    part_jq += a * a;
+  }
+  FLY_FOR(i, ns) {
+    const T* sp = w.site_xpos + 3 * m.mocap_site[i];
+    T d[3] = {sp[0] - q[0], sp[1] - q[1], sp[2] - q[2]}, r[3];
+    quat_rotate(r, d, qc);                    /* quaternions.py:137-159 */
+    for (int k = 0; k < 3; k++) part_r2s += (r[k] - (T)r2s[3 * i + k]) * (r[k] - (T)r2s[3 * i + k]);
+  }
+  for (int k = 0; k < 6; k++) d_qvel += (v[k] - (T)rv[k]) * (v[k] - (T)rv[k]);
+  {
+    const T rqt[4] = {(T)rq[3], (T)rq[4], (T)rq[5], (T)rq[6]};
+    const T a = quat_dist_short_arc(q + 3, rqt);
+    d_jq += a * a;
+  }
+  d_qvel += warp_sum(part_qvel); d_jq += warp_sum(part_jq); d_r2s += warp_sum(part_r2s);
+  const T s_com = T(0.078487), s_qvel = T(53.7801), s_r2s = T(0.0735), s_jq = T(1.2247);  /* rewards.py:99-104 */
+  return T(20) * exp(T(-0.5) / (s_com * s_com) * d_com) * exp(T(-0.5) / (s_qvel * s_qvel) * d_qvel)
+         * exp(T(-0.5) / (s_r2s * s_r2s) * d_r2s) * exp(T(-0.5) / (s_jq * s_jq) * d_jq);
+}
+
+template <class T>
+FLY_INL void fly_set_ghost(const DModel<T>& m, const Ws<T>& w, const FlyClipView& clip, int row, bool with_vel) {
+  if (m.ghost_qposadr < 0 || !clip.rows) return;  /* walk_imitation.py:119-136,138-144 */
+  const float* r = fly_clip_row(m, clip, row);
+  const int nj = m.task_type == FLYB_TASK_WALK_IMITATION ? m.n_mocap_joints : 0;
+  FLY_FOR(k, 7) w.qpos[m.ghost_qposadr + k] = (T)r[k] + (k < 3 ? m.ghost_offset[k] : T(0));
+  if (with_vel) FLY_FOR(k, 6) w.qvel[m.ghost_dofadr + k] = (T)r[7 + nj + k];
+  FLY_SYNC();
+}
+
+template <class T>
+FLY_INL FlyClipView fly_clip_view(const DModel<T>& m, const FlyClips& clips, int id) {
+  FlyClipView v;
+  if (!clips.data || id < 0 || id >= clips.nclips) { v.rows = 0; v.T = 0; return v; }
+  v.rows = clips.data + (size_t)clips.offset[id] * m.clip_width;
+  v.T = clips.length[id];
+  return v;
+}
+
+/* episode reset of the env whose state sits in w; returns step_type FIRST */
+template <class T>
+FLY_FN int fly_env_reset(const DModel<T>& m, const Ws<T>& w, const FlyClips& clips, const FlyIO<T>& io, int env,
+                         int* sint, float* obs) {
+  int clip_id = sint[FLY_SI_FORCED_CLIP];
+  const int episode = sint[FLY_SI_EPISODE];
+  if (clip_id < 0 && clips.nclips > 0)  /* trajectory_loaders.py:122,184: random_state.choice over clips */
+    clip_id = (int)(fly_hash(io.seed ^ fly_hash(((unsigned long long)(io.env_offset + env) << 24) ^ (unsigned long long)episode))
+                    % (unsigned long long)clips.nclips);
+  const FlyClipView clip = fly_clip_view(m, clips, clip_id);
+  FLY_FOR(i, m.nq) w.qpos[i] = m.qpos_reset[i];
+  FLY_FOR(i, m.nv) { w.qvel[i] = 0; w.warm[i] = 0; w.qacc[i] = 0; }
+  FLY_FOR(i, m.na) w.act[i] = 0;
+  FLY_FOR(i, m.nu) w.ctrl[i] = 0;
+  FLY_FOR(i, m.nsensordata) { w.sens_sum[i] = 0; w.sensordata[i] = 0; }
+  FLY_SYNC();
+  int episode_steps = m.max_episode_steps;
+  if (m.task_type == FLYB_TASK_WALK_IMITATION && clip.rows) {
+    const int snippet = clip.T - m.future_steps - 1;  /* walk_imitation.py:101-102 */
+    if (snippet < episode_steps) episode_steps = snippet;
+    const float* r = clip.rows;                        /* walk_imitation.py:119 */
+    FLY_FOR(k, 7) w.qpos[m.root_qposadr + k] = (T)r[k];
+    FLY_FOR(i, m.n_mocap_joints) w.qpos[m.jnt_qposadr[m.mocap_joint[i]]] = (T)r[7 + i];
+    FLY_SYNC();
+    fly_set_ghost(m, w, clip, 0, false);
+  }
+  fly_step1(m, w, true);
+  fly_forward_acc(m, w);
+  fly_accumulate(m, w);
+  fly_write_obs(m, w, clip, 0, obs, m.pad_first_obs ? T(1) : T(1) / T(m.n_substeps));
+  FLY_LANE0 {
+    sint[FLY_SI_STEP] = 0; sint[FLY_SI_EPISODE_STEPS] = episode_steps; sint[FLY_SI_RESET_NEXT] = 0;
+    sint[FLY_SI_CLIP] = clip_id; sint[FLY_SI_EPISODE] = episode + 1; sint[FLY_SI_EPLEN] = 0;
+  }
+  FLY_SYNC();
+  return 0;
+}
+
+/* one control step; returns step_type */
+template <class T>
+FLY_FN int fly_env_step(const DModel<T>& m, const Ws<T>& w, const FlyClips& clips, const float* action_in, int* sint,
+                        float* obs, T* reward, T* discount, int* fatal_out) {
+  const FlyClipView clip = fly_clip_view(m, clips, sint[FLY_SI_CLIP]);
+  int step = sint[FLY_SI_STEP];
+  if (m.task_type == FLYB_TASK_WALK_IMITATION) fly_set_ghost(m, w, clip, step, true);
+  FLY_FOR(a, m.nu) {  /* fruitfly.py:480-492 ; NaN -> 0 walk_imitation.py:147 */
+    const int ai = m.ctrl_action[a];
+    T v = ai >= 0 ? (T)action_in[ai] : T(0);
+    if (v != v) v = 0;
+    w.ctrl[a] = v;
+  }
+  FLY_FOR(k, m.nsensordata) w.sens_sum[k] = 0;
+  FLY_SYNC();
+  step += 1;  /* tasks/base.py:192 */
+  fly_step1(m, w, true);
+  for (int s = 0; s < m.n_substeps; s++) {
+    fly_forward_acc(m, w);
+    fly_integrate(m, w);
+    fly_step1(m, w, s < m.n_substeps - 1);
+    fly_accumulate(m, w);
+  }
+  /* termination: tasks/base.py:214-217, walk_imitation.py:165-191, walk_on_ball.py:75-79 */
+  T qn = 0;
+  FLY_FOR(d, m.nv) qn += w.qacc[d] * w.qacc[d];
+  qn = warp_sum(qn);
+  int fatal = !(sqrt(qn) <= m.terminal_qacc), reached_end = 0;  /* NaN counts as divergence */
+  if (m.task_type != FLYB_TASK_FLIGHT_IMITATION) {
+    T lv[6];
+    const int site = m.thorax_site;
+    fly_local_velocity(m, w, lv, m.site_bodyid[site], w.site_xpos + 3 * site, w.site_xmat + 9 * site);
+    if (norm3(lv + 3) > m.terminal_linvel || norm3(lv) > m.terminal_angvel) fatal = 1;
+  }
+  fly_write_obs(m, w, clip, step, obs, T(1) / T(m.n_substeps));
+  T r = 1;
+  if (m.task_type == FLYB_TASK_WALK_IMITATION) {
+    reached_end = step == sint[FLY_SI_EPISODE_STEPS];
+    if (clip.rows && norm3(w.obs_tmp) > m.terminal_com_dist) fatal = 1;
+    r = fly_walk_imitation_reward(m, w, clip, step);
+  } else if (m.task_type == FLYB_TASK_WALK_ON_BALL) {  /* walk_on_ball.py:61-73: tolerance(linear, margin 6) */
+    const T tgt[3] = {0, -5, 0};
+    for (int k = 0; k < 3; k++) {
+      const T x = fabs_(w.qvel[m.ball_dofadr + k] - tgt[k]) / T(6);
+      r *= x < 1 ? 1 - x : T(0);
+    }
+  }
+  *reward = r;
+  const int terminate = fatal || reached_end;
+  *discount = (m.task_type == FLYB_TASK_WALK_ON_BALL) ? (terminate ? T(0) : T(1)) : ((terminate && !reached_end) ? T(0) : T(1));
+  *fatal_out = fatal;
+  int st = 1;
+  FLY_SYNC();
+  FLY_LANE0 {
+    sint[FLY_SI_STEP] = step;
+    sint[FLY_SI_EPLEN] += 1;
+    if (terminate || step >= m.time_limit_steps) sint[FLY_SI_RESET_NEXT] = 1;
+  }
+  if (terminate || step >= m.time_limit_steps) st = 2;
+  FLY_SYNC();
+  return st;
+}
+
+/* the whole job of one warp for one env: load state, reset or step, store state and outputs */
+template <class T>
+FLY_FN void fly_env_run(const DModel<T>& m, const Ws<T>& w, const FlyClips& clips, const FlyIO<T>& io, int env) {
+  T* sr = io.sreal + (size_t)env * io.sreal_stride;
+  int* si = io.sint + (size_t)env * FLY_SI_COUNT;
+  float* obs = io.obs + (size_t)env * m.obs_dim;
+  FLY_LANE0 for (int k = 0; k < 16; k++) w.counts[k] = 0;
+  const bool do_reset = io.force_reset ? (!io.reset_mask || io.reset_mask[env]) : si[FLY_SI_RESET_NEXT] != 0;
+  if (io.force_reset && !do_reset) return;
+  T *s_qpos = sr, *s_qvel = sr + m.nq, *s_act = s_qvel + m.nv, *s_warm = s_act + m.na, *s_ret = s_warm + m.nv;
+  int st;
+  T reward = 0, discount = 1;
+  int fatal = 0;
+  FLY_SYNC();
+  if (do_reset) {
+    st = fly_env_reset(m, w, clips, io, env, si, obs);
+    FLY_LANE0 s_ret[0] = 0;
+  } else {
+    FLY_FOR(i, m.nq) w.qpos[i] = s_qpos[i];
+    FLY_FOR(i, m.nv) { w.qvel[i] = s_qvel[i]; w.warm[i] = s_warm[i]; }
+    FLY_FOR(i, m.na) w.act[i] = s_act[i];
+    FLY_SYNC();
+    st = fly_env_step(m, w, clips, io.action + (size_t)env * m.action_dim, si, obs, &reward, &discount, &fatal);
+    FLY_LANE0 {
+      s_ret[0] += reward;
+      if (st == 2 && io.stats) {
+        float* o = io.stats + 4 * (size_t)env;
+        o[0] = (float)s_ret[0]; o[1] = (float)si[FLY_SI_EPLEN]; o[2] = (float)fatal; o[3] += 1.0f;
+      }
+    }
+  }
+  FLY_FOR(i, m.nq) s_qpos[i] = w.qpos[i];
+  FLY_FOR(i, m.nv) { s_qvel[i] = w.qvel[i]; s_warm[i] = w.warm[i]; }
+  FLY_FOR(i, m.na) s_act[i] = w.act[i];
+  FLY_LANE0 {
+    if (!io.force_reset || true) {
+      io.reward[env] = (float)reward; io.discount[env] = (float)discount; io.step_type[env] = st;
+    }
+  }
+  if (io.trace_int) {
+    int* ti = io.trace_int + (size_t)env * FLY_TR_INTS;
+    FLY_LANE0 {
+      ti[FLY_TR_NCON] = w.counts[FLY_C_NCON]; ti[FLY_TR_NEFC] = w.counts[FLY_C_NEFC];
+      ti[FLY_TR_NLIMIT] = w.counts[FLY_C_NLIMIT]; ti[FLY_TR_NITER] = w.counts[FLY_C_NITER];
+      ti[FLY_TR_OVERFLOW] = w.counts[FLY_C_OVERFLOW]; ti[FLY_TR_NCAND] = w.counts[FLY_C_NCAND];
+    }
+    FLY_FOR(k, FLY_MAXCON) ti[FLY_TR_PAIRS + k] = k < w.counts[FLY_C_NCON] ? w.con_pair[k] : -1;
+  }
+  if (io.trace_real) {
+    T* tr = io.trace_real + (size_t)env * io.trace_real_stride;
+    FLY_FOR(k, FLY_MAXCON) tr[k] = k < w.counts[FLY_C_NCON] ? w.con_dist[k] : T(0);
+    FLY_FOR(k, m.nv) tr[FLY_MAXCON + k] = w.qacc[k];
+    FLY_FOR(k, m.nsensordata) tr[FLY_MAXCON + m.nv + k] = w.sensordata[k];
+    FLY_FOR(k, FLY_MAXEFC) tr[FLY_MAXCON + m.nv + m.nsensordata + k] = k < w.counts[FLY_C_NEFC] ? w.efc_force[k] : T(0);
+  }
+  FLY_SYNC();
+}
+#endif

@@ -224,7 +224,8 @@ std::string build_dmodel(const FlybModel* m, int flags, DModel<T>* out, FlyArena
     }
   /* triangle enumeration (a <= b < FLY_MAXCHAIN) used to spread a chain row's outer product over lanes */
   std::vector<int> tri_a, tri_b;
-  for (int a = 0; a < FLY_MAXCHAIN; a++) for (int b = a; b < FLY_MAXCHAIN; b++) { tri_a.push_back(a); tri_b.push_back(b); }
+  /* b-major so that the pairs with b < len are exactly the first len (len + 1) / 2 entries */
+  for (int b = 0; b < FLY_MAXCHAIN; b++) for (int a = 0; a <= b; a++) { tri_a.push_back(a); tri_b.push_back(b); }
   d.ntri = (int)tri_a.size();
 
   /* --- collision pairs */

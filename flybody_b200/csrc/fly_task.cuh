@@ -1,0 +1,196 @@
+/* fly_task.cuh - sensors (m12, m14), integration (m13), the physics substep in dm_control's legacy order, and
+ * the task layer (observation assembly, imitation reward, termination, per-env reset) of one environment.
+ *
+ * Task functions restate vnl_ray/tasks/{base,walk_imitation,walk_on_ball}.py, vnl_ray/tasks/rewards.py and
+ * vnl_ray/fruitfly/fruitfly.py; each cites the lines it follows. */
+#ifndef FLY_TASK_CUH_
+#define FLY_TASK_CUH_
+#include "fly_solver.cuh"
+
+/* reference clips in HBM: packed float rows [qpos 7+nj | qvel 6+nj | root2site 3 ns | joint_quat 4 nj] */
+struct FlyClips {
+  const float* data;
+  const int* offset;   /* first row of clip c */
+  const int* length;   /* rows of clip c */
+  int nclips;
+};
+
+/* ---------------------------------------------------------------- m12 acceleration-stage sensors */
+template <class T>
+FLY_INL T fly_ray_capsule(const T* pos, const T* mat, const T* size, const T* pnt, const T* vec) {
+  T d[3] = {pnt[0] - pos[0], pnt[1] - pos[1], pnt[2] - pos[2]}, lp[3], lv[3];
+  matT_vec(lp, mat, d); matT_vec(lv, mat, vec);
+  const T r = size[0], h = size[1];
+  T best = -1;
+  const T a = lv[0] * lv[0] + lv[1] * lv[1], b = lp[0] * lv[0] + lp[1] * lv[1], c = lp[0] * lp[0] + lp[1] * lp[1] - r * r;
+  const T zc = fmin_(h, fmax_(-h, lp[2]));
+  if (lp[0] * lp[0] + lp[1] * lp[1] + (lp[2] - zc) * (lp[2] - zc) <= r * r) return 0;
+  if (a > minval<T>()) {
+    const T det = b * b - a * c;
+    if (det >= 0) {
+      const T x = (-b - sqrt(det)) / a;
+      if (x >= 0 && fabs_(lp[2] + x * lv[2]) <= h) best = x;
+    }
+  }
+  for (int sgn = -1; sgn <= 1; sgn += 2) {
+    const T q[3] = {lp[0], lp[1], lp[2] - sgn * h};
+    const T aa = dot3(lv, lv), bb = dot3(q, lv), cc = dot3(q, q) - r * r, det = bb * bb - aa * cc;
+    if (det < 0 || aa < minval<T>()) continue;
+    const T x = (-bb - sqrt(det)) / aa;
+    if (x >= 0 && sgn * (lp[2] + x * lv[2]) >= h && (best < 0 || x < best)) best = x;
+  }
+  return best;
+}
+
+template <class T>
+FLY_FN void fly_sensors_acc(const DModel<T>& m, const Ws<T>& w) {
+  const int ncon = w.counts[FLY_C_NCON];
+  bool need_rne = false;
+  for (int s = 0; s < m.nsensor; s++) {
+    const int t = m.sensor_type[s];
+    if (t == FLYB_SENS_ACCELEROMETER || t == FLYB_SENS_FORCE) need_rne = true;
+  }
+  if (need_rne) {
+    FLY_FOR(it, 6 * m.nbody) w.cfrc_ext[it] = 0;
+    FLY_SYNC();
+    for (int ci = 0; ci < ncon; ci++) {
+      const int ea = w.con_efc[ci];
+      if (ea < 0) continue;
+      const int dim = w.con_dim[ci], pg = m.pair_geom[w.con_pair[ci]];
+      T fw[3] = {0, 0, 0};
+      for (int k = 0; k < dim; k++) for (int a = 0; a < 3; a++) fw[a] += w.con_frame[9 * ci + 3 * k + a] * w.efc_force[ea + k];
+      FLY_FOR(it, 12) {
+        const int side = it / 6, c = it % 6;
+        const int b = side ? m.geom_bodyid[pg >> 8] : m.geom_bodyid[pg & 255];
+        if (b > 0) {
+          const T sg = side ? T(1) : T(-1);
+          const T* c0 = w.scom + 3 * m.body_rootid[b];
+          const T off[3] = {w.con_pos[3 * ci] - c0[0], w.con_pos[3 * ci + 1] - c0[1], w.con_pos[3 * ci + 2] - c0[2]};
+          T tq[3];
+          cross3(tq, off, fw);
+          w.cfrc_ext[6 * b + c] += sg * (c < 3 ? tq[c] : fw[c - 3]);
+        }
+      }
+      FLY_SYNC();
+    }
+    fly_rne(m, w, (T*)0, 1, 1);
+  }
+  FLY_FOR(s, m.nsensor) {
+    const int site = m.sensor_site[s], b = m.site_bodyid[site], type = m.sensor_type[s];
+    T* out = w.sensordata + m.sensor_adr[s];
+    const T *sp = w.site_xpos + 3 * site, *sm = w.site_xmat + 9 * site;
+    if (type == FLYB_SENS_ACCELEROMETER) {
+      const T* c0 = w.scom + 3 * m.body_rootid[b];
+      const T* ca = w.cacc + 6 * b;
+      T off[3] = {sp[0] - c0[0], sp[1] - c0[1], sp[2] - c0[2]}, t[3], lin[3], lv[6], cor[3], la[3];
+      cross3(t, ca, off);
+      for (int k = 0; k < 3; k++) lin[k] = ca[3 + k] + t[k];
+      matT_vec(la, sm, lin);
+      fly_local_velocity(m, w, lv, b, sp, sm);
+      cross3(cor, lv, lv + 3);
+      for (int k = 0; k < 3; k++) out[k] = la[k] + cor[k];
+    } else if (type == FLYB_SENS_FORCE) {
+      matT_vec(out, sm, w.cfrc_int + 6 * b + 3);
+    } else if (type == FLYB_SENS_TOUCH) {
+      T sum = 0;
+      for (int ci = 0; ci < ncon; ci++) {
+        const int ea = w.con_efc[ci];
+        if (ea < 0) continue;
+        const int pg = m.pair_geom[w.con_pair[ci]];
+        const int b1 = m.geom_bodyid[pg & 255], b2 = m.geom_bodyid[pg >> 8];
+        if (b1 != b && b2 != b) continue;
+        const T fn = w.efc_force[ea];
+        if (fn <= 0) continue;
+        T ray[3] = {w.con_frame[9 * ci], w.con_frame[9 * ci + 1], w.con_frame[9 * ci + 2]};
+        if (b2 == b) { ray[0] = -ray[0]; ray[1] = -ray[1]; ray[2] = -ray[2]; }
+        if (fly_ray_capsule(sp, sm, m.site_size + 3 * site, w.con_pos + 3 * ci, ray) >= 0) sum += fn;
+      }
+      out[0] = sum;
+    }
+  }
+  FLY_SYNC();
+}
+
+/* m14: gyro, velocimeter */
+template <class T>
+FLY_FN void fly_sensors_vel(const DModel<T>& m, const Ws<T>& w) {
+  FLY_FOR(s, m.nsensor) {
+    const int site = m.sensor_site[s], type = m.sensor_type[s];
+    if (type == FLYB_SENS_GYRO || type == FLYB_SENS_VELOCIMETER) {
+      T lv[6];
+      fly_local_velocity(m, w, lv, m.site_bodyid[site], w.site_xpos + 3 * site, w.site_xmat + 9 * site);
+      const T* src = type == FLYB_SENS_GYRO ? lv : lv + 3;
+      for (int k = 0; k < 3; k++) w.sensordata[m.sensor_adr[s] + k] = src[k];
+    }
+  }
+  FLY_SYNC();
+}
+
+/* ---------------------------------------------------------------- pipeline pieces */
+template <class T>
+FLY_FN void fly_step1(const DModel<T>& m, const Ws<T>& w, bool full) {
+  fly_kinematics(m, w);
+  fly_com_pos(m, w);
+  if (full) {
+    fly_crb(m, w);
+    FLY_FOR(e, m.nM) w.qLD[e] = w.qM[e];
+    FLY_SYNC();
+    fly_factor(m, w.qLD);
+    fly_collision(m, w);
+    fly_make_constraint(m, w);
+  }
+  fly_com_vel(m, w);
+  if (full) {
+    fly_passive(m, w);
+    fly_rne(m, w, w.qfrc_bias, 0, 0);
+  }
+  fly_sensors_vel(m, w);
+}
+
+/* actuation, smooth acceleration, constraint solve, acceleration sensors */
+template <class T>
+FLY_FN void fly_forward_acc(const DModel<T>& m, const Ws<T>& w) {
+  fly_actuation(m, w);
+  FLY_FOR(d, m.nv) {
+    const T f = w.qfrc_passive[d] - w.qfrc_bias[d] + w.qfrc_actuator[d];
+    w.qfrc_smooth[d] = f; w.qacc_smooth[d] = f;
+  }
+  FLY_SYNC();
+  fly_solve(m, w.qLD, w.qacc_smooth);
+  fly_fwd_constraint(m, w);
+  fly_sensors_acc(m, w);
+}
+
+/* m13: Euler with implicit joint damping */
+template <class T>
+FLY_FN void fly_integrate(const DModel<T>& m, const Ws<T>& w) {
+  const T dt = m.timestep;
+  FLY_FOR(e, m.nM) {
+    const int i = m.mrow[e];
+    w.qH[e] = w.qM[e] + (e == m.madr[i] ? dt * m.dof_damping[i] : T(0));
+  }
+  FLY_FOR(d, m.nv) w.stmp[d] = w.qfrc_smooth[d] + w.qfrc_constraint[d];
+  FLY_SYNC();
+  fly_factor(m, w.qH);
+  fly_solve(m, w.qH, w.stmp);
+  FLY_FOR(i, m.na) w.act[i] += dt * w.act_dot[i];
+  FLY_FOR(d, m.nv) { w.qvel[d] += dt * w.stmp[d]; w.warm[d] = w.qacc[d]; }
+  FLY_SYNC();
+  FLY_FOR(j, m.njnt) {
+    int qa = m.jnt_qposadr[j], da = m.jnt_dofadr[j];
+    const int type = m.jnt_type[j];
+    if (type == FLYB_JNT_HINGE) w.qpos[qa] += dt * w.qvel[da];
+    else {
+      if (type == FLYB_JNT_FREE) { for (int k = 0; k < 3; k++) w.qpos[qa + k] += dt * w.qvel[da + k]; qa += 3; da += 3; }
+      quat_integrate(w.qpos + qa, w.qvel + da, dt);
+    }
+  }
+  FLY_SYNC();
+}
+
+template <class T>
+FLY_INL void fly_accumulate(const DModel<T>& m, const Ws<T>& w) {
+  FLY_FOR(k, m.nsensordata) w.sens_sum[k] += w.sensordata[k];
+  FLY_SYNC();
+}
+#endif

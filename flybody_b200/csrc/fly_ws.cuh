@@ -43,7 +43,7 @@
   X(efc_R, FLY_MAXEFC, FLY_BULK) X(efc_D, FLY_MAXEFC, FLY_FAST) X(efc_K, FLY_MAXEFC, FLY_BULK)               \
   X(efc_B, FLY_MAXEFC, FLY_BULK) X(efc_imp, FLY_MAXEFC, FLY_BULK) X(efc_aref, FLY_MAXEFC, FLY_BULK)          \
   X(efc_force, FLY_MAXEFC, FLY_FAST) X(efc_jar, FLY_MAXEFC, FLY_FAST) X(efc_jv, FLY_MAXEFC, FLY_FAST)        \
-  X(efc_b, FLY_MAXEFC, FLY_BULK) X(ns_A, FLY_MAXEFC * FLY_MAXEFC / 2, FLY_BULK)                              \
+  X(efc_b, FLY_MAXEFC, FLY_BULK) X(ns_A, FLY_MAXEFC * FLY_MAXEFC * 2 / 3, FLY_BULK)                              \
   X(obs_tmp, 8, FLY_BULK)
 
 /* arrays of int */
@@ -52,7 +52,7 @@
   X(con_efc, FLY_MAXCON, FLY_BULK) X(hit_cnt, 32, FLY_BULK) X(hit_off, 33, FLY_BULK)                         \
   X(efc_start, FLY_MAXEFC, FLY_BULK) X(efc_xid, FLY_MAXEFC, FLY_BULK) X(efc_state, FLY_MAXEFC, FLY_BULK)     \
   X(grp_type, FLY_MAXGRP, FLY_BULK) X(grp_row, FLY_MAXGRP, FLY_BULK) X(grp_con, FLY_MAXGRP, FLY_BULK)        \
-  X(x_start, FLY_MAXCROSS, FLY_BULK) X(x_row, FLY_MAXCROSS, FLY_BULK) X(ns_fr, FLY_MAXEFC, FLY_BULK)         \
+  X(x_start, FLY_MAXCROSS, FLY_BULK) X(x_row, FLY_MAXCROSS, FLY_BULK) X(ns_fr, FLY_MAXEFC, FLY_BULK) X(ns_con, FLY_MAXCON, FLY_BULK)         \
   X(counts, 16, FLY_BULK)
 
 /* arrays of unsigned short */

@@ -1,0 +1,119 @@
+"""ctypes wrapper of the CPU emulation of the engine source (tests/emu/flyb_emu.cpp).  TEST INFRASTRUCTURE ONLY."""
+from __future__ import annotations
+
+import ctypes
+import os
+import subprocess
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = os.path.join(_HERE, "_build", "libflyb_emu.so")
+_CSRC = os.path.join(_HERE, "..", "..", "flybody_b200", "csrc")
+
+
+def build(force: bool = False):
+    srcs = [os.path.join(_HERE, "flyb_emu.cpp")] + [os.path.join(_CSRC, f) for f in os.listdir(_CSRC) if f.endswith((".cuh", ".h"))]
+    newest = max(os.path.getmtime(s) for s in srcs)
+    if force or not os.path.exists(_LIB) or os.path.getmtime(_LIB) < newest:
+        os.makedirs(os.path.dirname(_LIB), exist_ok=True)
+        subprocess.check_call(["g++", "-O2", "-fPIC", "-shared", "-std=c++17", "-o", _LIB, srcs[0]])
+    return _LIB
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        from flybody_b200.model_pack import FlybModel
+        L = ctypes.CDLL(build())
+        L.emu_create.restype = ctypes.c_void_p
+        L.emu_create.argtypes = [ctypes.POINTER(FlybModel), ctypes.c_int, ctypes.c_int, ctypes.c_char_p, ctypes.c_int]
+        L.emu_destroy.argtypes = [ctypes.c_void_p]
+        fp, ip, dp = ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_int), ctypes.POINTER(ctypes.c_double)
+        L.emu_set_clips.argtypes = [ctypes.c_void_p, fp, ip, ip, ctypes.c_int]
+        L.emu_env_reset.argtypes = [ctypes.c_void_p, fp]
+        L.emu_env_step.argtypes = [ctypes.c_void_p, fp, fp, dp, dp]
+        for fn in ("emu_forward", "emu_physics_step"):
+            getattr(L, fn).argtypes = [ctypes.c_void_p]
+        L.emu_call.argtypes = [ctypes.c_void_p, ctypes.c_char_p]
+        L.emu_get.argtypes = [ctypes.c_void_p, ctypes.c_char_p, dp, ctypes.c_int]
+        L.emu_set.argtypes = [ctypes.c_void_p, ctypes.c_char_p, dp, ctypes.c_int]
+        L.emu_geti.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ip, ctypes.c_int]
+        _lib = L
+    return _lib
+
+
+class EmuEnv:
+    def __init__(self, model: dict, flags: int = 0, double: bool = True):
+        from flybody_b200.model_pack import pack_model
+        self.M = model
+        self._struct, self._keep = pack_model(model)
+        err = ctypes.create_string_buffer(256)
+        self._h = lib().emu_create(ctypes.byref(self._struct), flags, int(double), err, 256)
+        if not self._h:
+            raise RuntimeError(err.value.decode())
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().emu_destroy(self._h)
+            self._h = None
+
+    def get(self, name, cap=200000):
+        out = np.zeros(cap)
+        n = lib().emu_get(self._h, name.encode(), out.ctypes.data_as(ctypes.POINTER(ctypes.c_double)), cap)
+        if n < 0:
+            raise KeyError(name)
+        return out[:n].copy()
+
+    def set(self, name, v):
+        v = np.ascontiguousarray(v, dtype=np.float64)
+        n = lib().emu_set(self._h, name.encode(), v.ctypes.data_as(ctypes.POINTER(ctypes.c_double)), v.size)
+        if n < 0:
+            raise KeyError(name)
+
+    def geti(self, name, cap=4096):
+        out = np.zeros(cap, np.int32)
+        n = lib().emu_geti(self._h, name.encode(), out.ctypes.data_as(ctypes.POINTER(ctypes.c_int)), cap)
+        if n < 0:
+            raise KeyError(name)
+        return out[:n].copy()
+
+    def call(self, stage):
+        lib().emu_call(self._h, stage.encode())
+
+    def forward(self):
+        lib().emu_forward(self._h)
+
+    def physics_step(self, n=1):
+        for _ in range(n):
+            lib().emu_physics_step(self._h)
+
+    def dense_m(self, name="qM"):
+        nv = int(self.M["nv"])
+        v, r, c = self.get(name), self.geti("mrow"), self.geti("mcol")
+        A = np.zeros((nv, nv))
+        A[r, c] = v[:len(r)]
+        return A
+
+    def set_clips(self, table, offsets, lengths):
+        t = np.ascontiguousarray(table, np.float32)
+        o = np.ascontiguousarray(offsets, np.int32)
+        ln = np.ascontiguousarray(lengths, np.int32)
+        self._clips = (t, o, ln)
+        fp, ip = ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_int)
+        lib().emu_set_clips(self._h, t.ctypes.data_as(fp), o.ctypes.data_as(ip), ln.ctypes.data_as(ip), len(o))
+
+    def env_reset(self):
+        obs = np.zeros(int(self.M["obs_dim"]), np.float32)
+        st = lib().emu_env_reset(self._h, obs.ctypes.data_as(ctypes.POINTER(ctypes.c_float)))
+        return st, obs
+
+    def env_step(self, action):
+        a = np.ascontiguousarray(action, np.float32)
+        obs = np.zeros(int(self.M["obs_dim"]), np.float32)
+        r, g = ctypes.c_double(0), ctypes.c_double(0)
+        fp = ctypes.POINTER(ctypes.c_float)
+        st = lib().emu_env_step(self._h, a.ctypes.data_as(fp), obs.ctypes.data_as(fp), ctypes.byref(r), ctypes.byref(g))
+        return st, r.value, g.value, obs

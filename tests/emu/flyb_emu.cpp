@@ -1,0 +1,148 @@
+/* flyb_emu.cpp - TEST INFRASTRUCTURE: runs the engine source (flybody_b200/csrc/fly_*.cuh) on the CPU.
+ *
+ * With FLY_EMU defined a warp is a single thread, so the very code the CUDA kernels are built from can be
+ * unit-tested here (no GPU in the build container) against the float64 oracle, in float and in double.
+ * Never linked into, nor reachable from, the product library. */
+#define FLY_EMU 1
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <string>
+#include <vector>
+#include "../../flybody_b200/csrc/fly_env.cuh"
+
+struct EmuBase {
+  virtual ~EmuBase() {}
+  virtual void set_clips(const float* data, const int* off, const int* len, int n) = 0;
+  virtual int env_reset(float* obs) = 0;
+  virtual int env_step(const float* action, float* obs, double* reward, double* discount) = 0;
+  virtual void forward() = 0;
+  virtual void physics_step() = 0;
+  virtual int get(const char* name, double* out, int cap) = 0;
+  virtual int set(const char* name, const double* in, int n) = 0;
+  virtual int geti(const char* name, int* out, int cap) = 0;
+  virtual void call(const char* stage) = 0;
+};
+
+template <class T>
+struct Emu : EmuBase {
+  DModel<T> m;
+  FlyArena arena;
+  Ws<T> w;
+  std::vector<char> mem;
+  std::vector<T> sreal;
+  std::vector<int> sint;
+  std::vector<float> clip_data;
+  std::vector<int> clip_off, clip_len;
+  FlyClips clips;
+  std::string err;
+
+  Emu(const FlybModel* fm, int flags) {
+    err = build_dmodel<T>(fm, flags, &m, &arena);
+    if (!err.empty()) return;
+    fly_relocate(&m, arena.buf.data());
+    size_t fb = 0, bb = 0;
+    ws_bind<T>(m, (Ws<T>*)0, 0, 0, &fb, &bb, true);
+    mem.assign(bb + 64, 0);
+    ws_bind<T>(m, &w, 0, mem.data(), &fb, &bb, true);
+    sreal.assign(m.nq + 2 * m.nv + m.na + 4, 0);
+    sint.assign(FLY_SI_COUNT, 0);
+    sint[FLY_SI_FORCED_CLIP] = -1;
+    clips.data = 0; clips.offset = 0; clips.length = 0; clips.nclips = 0;
+    for (int i = 0; i < m.nq; i++) w.qpos[i] = m.qpos0[i];
+  }
+  void set_clips(const float* data, const int* off, const int* len, int n) override {
+    int rows = 0;
+    for (int i = 0; i < n; i++) rows = off[i] + len[i] > rows ? off[i] + len[i] : rows;
+    clip_data.assign(data, data + (size_t)rows * m.clip_width);
+    clip_off.assign(off, off + n); clip_len.assign(len, len + n);
+    clips.data = clip_data.data(); clips.offset = clip_off.data(); clips.length = clip_len.data(); clips.nclips = n;
+    sint[FLY_SI_FORCED_CLIP] = 0;
+  }
+  FlyIO<T> io(const float* action, float* obs, float* rdst) {
+    FlyIO<T> o;
+    memset(&o, 0, sizeof(o));
+    o.sreal = sreal.data(); o.sint = sint.data(); o.sreal_stride = (int)sreal.size();
+    o.action = action; o.obs = obs; o.reward = rdst; o.discount = rdst + 1; o.step_type = (int*)(rdst + 2);
+    return o;
+  }
+  int env_reset(float* obs) override {
+    float rd[4];
+    FlyIO<T> o = io(0, obs, rd);
+    o.force_reset = 1;
+    fly_env_run(m, w, clips, o, 0);
+    return *(int*)(rd + 2);
+  }
+  int env_step(const float* action, float* obs, double* reward, double* discount) override {
+    float rd[4];
+    FlyIO<T> o = io(action, obs, rd);
+    /* full-precision reward: rerun through the typed path */
+    fly_env_run(m, w, clips, o, 0);
+    *reward = rd[0]; *discount = rd[1];
+    return *(int*)(rd + 2);
+  }
+  void forward() override { fly_step1(m, w, true); fly_forward_acc(m, w); }
+  void physics_step() override { fly_forward_acc(m, w); fly_integrate(m, w); fly_step1(m, w, true); }
+  void call(const char* stage) override {
+    std::string s(stage);
+    if (s == "kinematics") fly_kinematics(m, w);
+    else if (s == "com_pos") fly_com_pos(m, w);
+    else if (s == "crb") fly_crb(m, w);
+    else if (s == "factor") { for (int e = 0; e < m.nM; e++) w.qLD[e] = w.qM[e]; fly_factor(m, w.qLD); }
+    else if (s == "collision") fly_collision(m, w);
+    else if (s == "make_constraint") fly_make_constraint(m, w);
+    else if (s == "step1") fly_step1(m, w, true);
+    else if (s == "forward_acc") fly_forward_acc(m, w);
+    else if (s == "integrate") fly_integrate(m, w);
+    else if (s == "solve_stmp") fly_solve(m, w.qLD, w.stmp);
+    else if (s == "mulm_stmp") fly_mul_m(m, w.qM, w.sMv, w.stmp);
+    else fprintf(stderr, "emu: unknown stage %s\n", stage);
+  }
+  int get(const char* name, double* out, int cap) override {
+    size_t fb, bb;
+    (void)fb; (void)bb;
+#define X(n, cnt, tier) if (!strcmp(name, #n)) { int c = (int)(cnt); if (c > cap) c = cap; for (int i = 0; i < c; i++) out[i] = (double)w.n[i]; return c; }
+    FLY_WS_REAL(X)
+#undef X
+    if (!strcmp(name, "sreal")) { int c = (int)sreal.size() < cap ? (int)sreal.size() : cap; for (int i = 0; i < c; i++) out[i] = (double)sreal[i]; return c; }
+    return -1;
+  }
+  int set(const char* name, const double* in, int n) override {
+#define X(nm, cnt, tier) if (!strcmp(name, #nm)) { int c = (int)(cnt); if (c > n) c = n; for (int i = 0; i < c; i++) w.nm[i] = (T)in[i]; return c; }
+    FLY_WS_REAL(X)
+#undef X
+    return -1;
+  }
+  int geti(const char* name, int* out, int cap) override {
+#define X(n, cnt, tier) if (!strcmp(name, #n)) { int c = (int)(cnt); if (c > cap) c = cap; for (int i = 0; i < c; i++) out[i] = (int)w.n[i]; return c; }
+    FLY_WS_INT(X)
+    FLY_WS_U16(X)
+#undef X
+    if (!strcmp(name, "sint")) { int c = FLY_SI_COUNT < cap ? FLY_SI_COUNT : cap; for (int i = 0; i < c; i++) out[i] = sint[i]; return c; }
+    if (!strcmp(name, "mrow")) { int c = m.nM < cap ? m.nM : cap; for (int i = 0; i < c; i++) out[i] = m.mrow[i]; return c; }
+    if (!strcmp(name, "mcol")) { int c = m.nM < cap ? m.nM : cap; for (int i = 0; i < c; i++) out[i] = m.mcol[i]; return c; }
+    if (!strcmp(name, "nM")) { out[0] = m.nM; return 1; }
+    return -1;
+  }
+};
+
+extern "C" {
+void* emu_create(const FlybModel* m, int flags, int use_double, char* errbuf, int errcap) {
+  EmuBase* e;
+  std::string err;
+  if (use_double) { Emu<double>* x = new Emu<double>(m, flags); err = x->err; e = x; }
+  else { Emu<float>* x = new Emu<float>(m, flags); err = x->err; e = x; }
+  if (!err.empty()) { snprintf(errbuf, errcap, "%s", err.c_str()); delete e; return 0; }
+  return e;
+}
+void emu_destroy(void* h) { delete (EmuBase*)h; }
+void emu_set_clips(void* h, const float* data, const int* off, const int* len, int n) { ((EmuBase*)h)->set_clips(data, off, len, n); }
+int emu_env_reset(void* h, float* obs) { return ((EmuBase*)h)->env_reset(obs); }
+int emu_env_step(void* h, const float* a, float* obs, double* r, double* g) { return ((EmuBase*)h)->env_step(a, obs, r, g); }
+void emu_forward(void* h) { ((EmuBase*)h)->forward(); }
+void emu_physics_step(void* h) { ((EmuBase*)h)->physics_step(); }
+void emu_call(void* h, const char* stage) { ((EmuBase*)h)->call(stage); }
+int emu_get(void* h, const char* name, double* out, int cap) { return ((EmuBase*)h)->get(name, out, cap); }
+int emu_set(void* h, const char* name, const double* in, int n) { return ((EmuBase*)h)->set(name, in, n); }
+int emu_geti(void* h, const char* name, int* out, int cap) { return ((EmuBase*)h)->geti(name, out, cap); }
+}
