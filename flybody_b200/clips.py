@@ -127,3 +127,111 @@ def pack_clips(M: dict, clips: list):
             r[:, 13 + 2 * nj + 3 * ns:] = c["joint_quat"].reshape(T, -1)
         rows.append(r); off.append(n); ln.append(T); n += T
     return np.concatenate(rows), np.array(off, np.int32), np.array(ln, np.int32)
+
+
+# ---------------------------------------------------------------------------- batched (vectorised) generation
+def _bq_mul(a, b):
+    aw, ax, ay, az = a[..., 0], a[..., 1], a[..., 2], a[..., 3]
+    bw, bx, by, bz = b[..., 0], b[..., 1], b[..., 2], b[..., 3]
+    return np.stack([aw * bw - ax * bx - ay * by - az * bz, aw * bx + ax * bw + ay * bz - az * by,
+                     aw * by - ax * bz + ay * bw + az * bx, aw * bz + ax * by - ay * bx + az * bw], axis=-1)
+
+
+def _bq_rot(q, v):
+    """rotate v [...,3] by unit quaternion q [...,4]"""
+    w, u = q[..., :1], q[..., 1:]
+    t = 2.0 * np.cross(u, v)
+    return v + w * t + np.cross(u, t)
+
+
+def batch_walker_features(M: dict, qpos: np.ndarray):
+    """`walker_features` for a batch of full qpos vectors [B, nq] -> root2site [B, n_s, 3], joint_quat [B, n_j, 4].
+    Same arithmetic as rewards.get_walker_features (vnl_ray/tasks/rewards.py:36-60), vectorised over frames."""
+    B, nb = qpos.shape[0], int(M["nbody"])
+    xpos = np.zeros((B, nb, 3))
+    xquat = np.zeros((B, nb, 4)); xquat[..., 0] = 1.0
+    xaxis = np.zeros((B, int(M["njnt"]), 3))
+    for b in range(1, nb):
+        p = int(M["body_parent"][b])
+        pos = xpos[:, p] + _bq_rot(xquat[:, p], np.broadcast_to(M["body_pos"][b], (B, 3)))
+        quat = _bq_mul(xquat[:, p], np.broadcast_to(M["body_quat"][b], (B, 4)))
+        for j in range(int(M["body_jntadr"][b]), int(M["body_jntadr"][b] + M["body_jntnum"][b])):
+            a, t = int(M["jnt_qposadr"][j]), int(M["jnt_type"][j])
+            ax0 = np.broadcast_to(M["jnt_axis"][j], (B, 3))
+            if t == 0:
+                pos = qpos[:, a:a + 3].copy()
+                quat = qpos[:, a + 3:a + 7] / np.linalg.norm(qpos[:, a + 3:a + 7], axis=1, keepdims=True)
+                xaxis[:, j] = _bq_rot(quat, ax0)
+                continue
+            jp = np.broadcast_to(M["jnt_pos"][j], (B, 3))
+            anchor = pos + _bq_rot(quat, jp)
+            xaxis[:, j] = _bq_rot(quat, ax0)
+            if t == 1:
+                ql = qpos[:, a:a + 4] / np.linalg.norm(qpos[:, a:a + 4], axis=1, keepdims=True)
+            else:
+                ang = qpos[:, a] - M["qpos0"][a]
+                ql = np.concatenate([np.cos(ang / 2)[:, None], np.sin(ang / 2)[:, None] * ax0], axis=1)
+            quat = _bq_mul(quat, ql)
+            pos = anchor - _bq_rot(quat, jp)
+        xpos[:, b], xquat[:, b] = pos, quat
+    ra = int(M["root_qposadr"])
+    p = qpos[:, ra:ra + 3]
+    q = qpos[:, ra + 3:ra + 7] / np.linalg.norm(qpos[:, ra + 3:ra + 7], axis=1, keepdims=True)
+    qc = q * np.array([1.0, -1, -1, -1])
+    ns, nj = int(M["n_mocap_sites"]), int(M["n_mocap_joints"])
+    r2s = np.zeros((B, ns, 3))
+    for i, s in enumerate(M["mocap_site"]):
+        b = int(M["site_bodyid"][s])
+        sp = xpos[:, b] + _bq_rot(xquat[:, b], np.broadcast_to(M["site_pos"][s], (B, 3)))
+        r2s[:, i] = _bq_rot(qc, sp - p)
+    jq = np.zeros((B, nj, 4))
+    for i, j in enumerate(M["mocap_joint"]):
+        ax = _bq_rot(qc, xaxis[:, j])
+        ax = ax / np.linalg.norm(ax, axis=1, keepdims=True)
+        ang = qpos[:, int(M["jnt_qposadr"][j])]
+        q2 = np.concatenate([np.cos(ang / 2)[:, None], np.sin(ang / 2)[:, None] * ax], axis=1)
+        # quat_z2vec (quaternions.py:205-252), vectorised incl. the axis-parallel-to-z edge case
+        edge = (ax[:, 0] == 0.0) & (ax[:, 1] == 0.0)
+        rot = np.stack([-ax[:, 1], ax[:, 0]], axis=1)
+        rn = np.linalg.norm(rot, axis=1, keepdims=True)
+        rot = rot / np.where(rn > 0, rn, 1.0)
+        a2 = np.arccos(np.clip(ax[:, 2], -1.0, 1.0))
+        q1 = np.stack([np.cos(a2 / 2), np.sin(a2 / 2) * rot[:, 0], np.sin(a2 / 2) * rot[:, 1], 0 * a2], axis=1)
+        q1[edge & (ax[:, 2] < 0)] = [0.0, 1, 0, 0]
+        q1[edge & (ax[:, 2] >= 0)] = [1.0, 0, 0, 0]
+        jq[:, i] = _bq_mul(q2, q1)
+    return r2s, jq
+
+
+def synthetic_table(M: dict, n_clips: int = 1024, T: int = 600, seed: int = 0, cache: bool = True):
+    """Packed synthetic walking clip table: -> (rows float32 [n T, W], offsets, lengths).
+    Cached under flybody_b200/assets/_cache/ because generation takes a while for 1024 x 600 frames."""
+    import os
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "assets", "_cache",
+                        f"{['walk_on_ball', 'walk_imitation', 'flight_imitation'][int(M['task_type'])]}_{n_clips}x{T}_s{seed}.npz")
+    if cache and os.path.exists(path):
+        d = np.load(path)
+        return d["rows"], d["offsets"], d["lengths"]
+    cl = [synth_walk_clip(M, T=T, seed=seed * 100003 + c, features=False) for c in range(n_clips)]
+    nj = int(M["n_mocap_joints"])
+    full = np.tile(np.asarray(M["qpos_reset"], np.float64), (n_clips * T, 1))
+    allq = np.concatenate([c["qpos"] for c in cl])
+    ra = int(M["root_qposadr"])
+    full[:, ra:ra + 7] = allq[:, :7]
+    for i, j in enumerate(M["mocap_joint"]):
+        full[:, int(M["jnt_qposadr"][j])] = allq[:, 7 + i]
+    r2s = np.zeros((n_clips * T, int(M["n_mocap_sites"]), 3)); jq = np.zeros((n_clips * T, nj, 4))
+    for s in range(0, n_clips * T, 32768):
+        r2s[s:s + 32768], jq[s:s + 32768] = batch_walker_features(M, full[s:s + 32768])
+    for c in range(n_clips):
+        cl[c]["root2site"], cl[c]["joint_quat"] = r2s[c * T:(c + 1) * T], jq[c * T:(c + 1) * T]
+    out = pack_clips(M, cl)
+    if cache:
+        os.makedirs(os.path.dirname(path), exist_ok=True)
+        np.savez(path, rows=out[0], offsets=out[1], lengths=out[2])
+    return out
+
+
+def save_clips(path: str, M: dict, clips: list):
+    rows, off, ln = pack_clips(M, clips)
+    np.savez(path, rows=rows, offsets=off, lengths=ln)

@@ -24,7 +24,7 @@ struct FlyIO {
   int* trace_int;      /* nullable [N, FLY_TR_INTS] */
   T* trace_real;       /* nullable [N, trace_real_stride]: con_dist[MAXCON] | qacc[nv] | sensordata | efc_force[MAXEFC] */
   int trace_real_stride;
-  float* stats;        /* nullable [N, 4] per-env episode stats written at episode end: return, length, fatal, count */
+  float* stats;        /* nullable [N, 4] per-env sums over finished episodes: return, length, fatal, count */
   unsigned long long seed;
   int env_offset;      /* global id of env 0 of this shard */
   int force_reset;     /* 1: reset every env in mask regardless of reset_next */
@@ -317,7 +317,7 @@ FLY_FN void fly_env_run(const DModel<T>& m, const Ws<T>& w, const FlyClips& clip
       s_ret[0] += reward;
       if (st == 2 && io.stats) {
         float* o = io.stats + 4 * (size_t)env;
-        o[0] = (float)s_ret[0]; o[1] = (float)si[FLY_SI_EPLEN]; o[2] = (float)fatal; o[3] += 1.0f;
+        o[0] += (float)s_ret[0]; o[1] += (float)si[FLY_SI_EPLEN]; o[2] += (float)fatal; o[3] += 1.0f;
       }
     }
   }
@@ -325,9 +325,9 @@ FLY_FN void fly_env_run(const DModel<T>& m, const Ws<T>& w, const FlyClips& clip
   FLY_FOR(i, m.nv) { s_qvel[i] = w.qvel[i]; s_warm[i] = w.warm[i]; }
   FLY_FOR(i, m.na) s_act[i] = w.act[i];
   FLY_LANE0 {
-    if (!io.force_reset || true) {
-      io.reward[env] = (float)reward; io.discount[env] = (float)discount; io.step_type[env] = st;
-    }
+    if (io.reward) io.reward[env] = (float)reward;
+    if (io.discount) io.discount[env] = (float)discount;
+    io.step_type[env] = st;
   }
   if (io.trace_int) {
     int* ti = io.trace_int + (size_t)env * FLY_TR_INTS;

@@ -82,7 +82,6 @@ struct DModel {
 #undef X
 };
 
-#ifndef __CUDA_ARCH__
 /* ------------------------------------------------------------------ host: FlybModel -> DModel arena */
 struct FlyArena {
   std::vector<char> buf;
@@ -350,5 +349,4 @@ void fly_relocate(DModel<T>* d, const void* base) {
   FLY_BYTE_FIELDS(X)
 #undef X
 }
-#endif  /* !__CUDA_ARCH__ */
 #endif  /* FLY_MODEL_H_ */

@@ -9,54 +9,53 @@
 #include "fly_model.h"
 #include "fly_math.cuh"
 
-#define FLY_FAST 1
-#define FLY_BULK 0
+/* tier of an array: 0 = always bulk; 1..3 = goes to the fast arena when the launch's `level` is >= the tier */
 #define FLY_NHIT 4   /* most contacts a primitive pair can produce */
 
 /* X(name, element-count expression over `m`, tier) ; arrays of T */
 #define FLY_WS_REAL(X)                                                                                       \
-  X(qpos, m.nq, FLY_FAST) X(qvel, m.nv, FLY_FAST) X(act, m.na, FLY_FAST) X(ctrl, m.nu, FLY_FAST)             \
-  X(warm, m.nv, FLY_FAST) X(qacc, m.nv, FLY_FAST)                                                            \
-  X(xpos, 3 * m.nbody, FLY_FAST) X(xquat, 4 * m.nbody, FLY_FAST) X(xmat, 9 * m.nbody, FLY_FAST)              \
-  X(xipos, 3 * m.nbody, FLY_BULK) X(ximat, 9 * m.nbody, FLY_BULK)                                            \
-  X(xanchor, 3 * m.njnt, FLY_BULK) X(xaxis, 3 * m.njnt, FLY_BULK)                                            \
-  X(geom_xpos, 3 * m.ngeom, FLY_FAST) X(site_xpos, 3 * m.nsite, FLY_BULK) X(site_xmat, 9 * m.nsite, FLY_BULK)\
-  X(scom, 3 * m.nbody, FLY_FAST) X(cinert, 10 * m.nbody, FLY_BULK) X(crb, 10 * m.nbody, FLY_BULK)            \
-  X(cdof, 6 * m.nv, FLY_FAST) X(cdof_dot, 6 * m.nv, FLY_BULK) X(cvel, 6 * m.nbody, FLY_FAST)                 \
-  X(qM, m.nM, FLY_FAST) X(qLD, m.nM, FLY_FAST) X(qH, m.nM, FLY_FAST)                                         \
-  X(act_length, m.nu, FLY_BULK) X(act_force, m.nu, FLY_BULK) X(act_dot, m.na, FLY_BULK)                      \
-  X(qfrc_bias, m.nv, FLY_BULK) X(qfrc_passive, m.nv, FLY_BULK) X(qfrc_actuator, m.nv, FLY_BULK)              \
-  X(qfrc_smooth, m.nv, FLY_FAST) X(qacc_smooth, m.nv, FLY_FAST) X(qfrc_constraint, m.nv, FLY_FAST)           \
-  X(sMa, m.nv, FLY_FAST) X(sgrad, m.nv, FLY_FAST) X(ssearch, m.nv, FLY_FAST) X(sMv, m.nv, FLY_FAST)          \
-  X(stmp, m.nv, FLY_FAST)                                                                                    \
-  X(bodyf, 6 * m.nbody, FLY_BULK) X(boxf, 6 * (m.nfluidbox + m.nfluidgeom), FLY_BULK)                        \
-  X(cacc, 6 * m.nbody, FLY_BULK) X(cfrc_int, 6 * m.nbody, FLY_BULK) X(cfrc_ext, 6 * m.nbody, FLY_BULK)       \
-  X(sensordata, m.nsensordata, FLY_BULK) X(sens_sum, m.nsensordata, FLY_BULK)                                \
-  X(con_dist, FLY_MAXCON, FLY_BULK) X(con_incl, FLY_MAXCON, FLY_BULK) X(con_mu, FLY_MAXCON, FLY_BULK)        \
-  X(con_fric, FLY_MAXCON, FLY_BULK) X(con_pos, 3 * FLY_MAXCON, FLY_BULK) X(con_frame, 9 * FLY_MAXCON, FLY_BULK)\
-  X(con_hc, 9 * FLY_MAXCON, FLY_BULK) X(hit_tmp, 32 * FLY_NHIT * 11, FLY_BULK)                               \
-  X(efc_J, FLY_MAXEFC * FLY_MAXCHAIN, FLY_BULK) X(efc_Y, FLY_MAXEFC * FLY_MAXCHAIN, FLY_BULK)                \
-  X(x_J, FLY_MAXCROSS * FLY_MAXCHAIN, FLY_BULK) X(x_Y, FLY_MAXCROSS * FLY_MAXCHAIN, FLY_BULK)                \
-  X(x_dense, FLY_MAXCROSS * m.nv, FLY_BULK) X(x_S, FLY_MAXCROSS * FLY_MAXCROSS, FLY_BULK)                    \
-  X(x_z, FLY_MAXCROSS, FLY_BULK)                                                                             \
-  X(efc_pos, FLY_MAXEFC, FLY_BULK) X(efc_margin, FLY_MAXEFC, FLY_BULK) X(efc_diag, FLY_MAXEFC, FLY_BULK)     \
-  X(efc_R, FLY_MAXEFC, FLY_BULK) X(efc_D, FLY_MAXEFC, FLY_FAST) X(efc_K, FLY_MAXEFC, FLY_BULK)               \
-  X(efc_B, FLY_MAXEFC, FLY_BULK) X(efc_imp, FLY_MAXEFC, FLY_BULK) X(efc_aref, FLY_MAXEFC, FLY_BULK)          \
-  X(efc_force, FLY_MAXEFC, FLY_FAST) X(efc_jar, FLY_MAXEFC, FLY_FAST) X(efc_jv, FLY_MAXEFC, FLY_FAST)        \
-  X(efc_b, FLY_MAXEFC, FLY_BULK) X(ns_A, FLY_MAXEFC * FLY_MAXEFC * 2 / 3, FLY_BULK)                              \
-  X(obs_tmp, 8, FLY_BULK)
+  X(qpos, m.nq, 1) X(qvel, m.nv, 1) X(act, m.na, 1) X(ctrl, m.nu, 1)             \
+  X(warm, m.nv, 1) X(qacc, m.nv, 1)                                                            \
+  X(xpos, 3 * m.nbody, 2) X(xquat, 4 * m.nbody, 2) X(xmat, 9 * m.nbody, 2)              \
+  X(xipos, 3 * m.nbody, 3) X(ximat, 9 * m.nbody, 0)                                            \
+  X(xanchor, 3 * m.njnt, 0) X(xaxis, 3 * m.njnt, 0)                                            \
+  X(geom_xpos, 3 * m.ngeom, 2) X(site_xpos, 3 * m.nsite, 0) X(site_xmat, 9 * m.nsite, 0)\
+  X(scom, 3 * m.nbody, 2) X(cinert, 10 * m.nbody, 3) X(crb, 10 * m.nbody, 0)            \
+  X(cdof, 6 * m.nv, 2) X(cdof_dot, 6 * m.nv, 3) X(cvel, 6 * m.nbody, 3)                 \
+  X(qM, m.nM, 2) X(qLD, m.nM, 1) X(qH, m.nM, 1)                                         \
+  X(act_length, m.nu, 0) X(act_force, m.nu, 0) X(act_dot, m.na, 0)                      \
+  X(qfrc_bias, m.nv, 0) X(qfrc_passive, m.nv, 0) X(qfrc_actuator, m.nv, 0)              \
+  X(qfrc_smooth, m.nv, 1) X(qacc_smooth, m.nv, 1) X(qfrc_constraint, m.nv, 1)           \
+  X(sMa, m.nv, 1) X(sgrad, m.nv, 1) X(ssearch, m.nv, 1) X(sMv, m.nv, 1)          \
+  X(stmp, m.nv, 1)                                                                                    \
+  X(bodyf, 6 * m.nbody, 0) X(boxf, 6 * (m.nfluidbox + m.nfluidgeom), 0)                        \
+  X(cacc, 6 * m.nbody, 0) X(cfrc_int, 6 * m.nbody, 0) X(cfrc_ext, 6 * m.nbody, 0)       \
+  X(sensordata, m.nsensordata, 0) X(sens_sum, m.nsensordata, 0)                                \
+  X(con_dist, FLY_MAXCON, 0) X(con_incl, FLY_MAXCON, 0) X(con_mu, FLY_MAXCON, 0)        \
+  X(con_fric, FLY_MAXCON, 0) X(con_pos, 3 * FLY_MAXCON, 0) X(con_frame, 9 * FLY_MAXCON, 0)\
+  X(con_hc, 9 * FLY_MAXCON, 0) X(hit_tmp, 32 * FLY_NHIT * 11, 0)                               \
+  X(efc_J, FLY_MAXEFC * FLY_MAXCHAIN, 0) X(efc_Y, FLY_MAXEFC * FLY_MAXCHAIN, 0)                \
+  X(x_J, FLY_MAXCROSS * FLY_MAXCHAIN, 0) X(x_Y, FLY_MAXCROSS * FLY_MAXCHAIN, 0)                \
+  X(x_dense, FLY_MAXCROSS * m.nv, 0) X(x_S, FLY_MAXCROSS * FLY_MAXCROSS, 0)                    \
+  X(x_z, FLY_MAXCROSS, 0)                                                                             \
+  X(efc_pos, FLY_MAXEFC, 0) X(efc_margin, FLY_MAXEFC, 0) X(efc_diag, FLY_MAXEFC, 0)     \
+  X(efc_R, FLY_MAXEFC, 0) X(efc_D, FLY_MAXEFC, 1) X(efc_K, FLY_MAXEFC, 0)               \
+  X(efc_B, FLY_MAXEFC, 0) X(efc_imp, FLY_MAXEFC, 0) X(efc_aref, FLY_MAXEFC, 0)          \
+  X(efc_force, FLY_MAXEFC, 1) X(efc_jar, FLY_MAXEFC, 1) X(efc_jv, FLY_MAXEFC, 1)        \
+  X(efc_b, FLY_MAXEFC, 0) X(ns_A, FLY_MAXEFC * FLY_MAXEFC * 2 / 3, 0)                              \
+  X(obs_tmp, 8, 0)
 
 /* arrays of int */
 #define FLY_WS_INT(X)                                                                                        \
-  X(con_pair, FLY_MAXCON, FLY_BULK) X(con_dim, FLY_MAXCON, FLY_BULK) X(con_excl, FLY_MAXCON, FLY_BULK)       \
-  X(con_efc, FLY_MAXCON, FLY_BULK) X(hit_cnt, 32, FLY_BULK) X(hit_off, 33, FLY_BULK)                         \
-  X(efc_start, FLY_MAXEFC, FLY_BULK) X(efc_xid, FLY_MAXEFC, FLY_BULK) X(efc_state, FLY_MAXEFC, FLY_BULK)     \
-  X(grp_type, FLY_MAXGRP, FLY_BULK) X(grp_row, FLY_MAXGRP, FLY_BULK) X(grp_con, FLY_MAXGRP, FLY_BULK)        \
-  X(x_start, FLY_MAXCROSS, FLY_BULK) X(x_row, FLY_MAXCROSS, FLY_BULK) X(ns_fr, FLY_MAXEFC, FLY_BULK) X(ns_con, FLY_MAXCON, FLY_BULK)         \
-  X(counts, 16, FLY_BULK)
+  X(con_pair, FLY_MAXCON, 0) X(con_dim, FLY_MAXCON, 0) X(con_excl, FLY_MAXCON, 0)       \
+  X(con_efc, FLY_MAXCON, 0) X(hit_cnt, 32, 0) X(hit_off, 33, 0)                         \
+  X(efc_start, FLY_MAXEFC, 0) X(efc_xid, FLY_MAXEFC, 0) X(efc_state, FLY_MAXEFC, 0)     \
+  X(grp_type, FLY_MAXGRP, 0) X(grp_row, FLY_MAXGRP, 0) X(grp_con, FLY_MAXGRP, 0)        \
+  X(x_start, FLY_MAXCROSS, 0) X(x_row, FLY_MAXCROSS, 0) X(ns_fr, FLY_MAXEFC, 0) X(ns_con, FLY_MAXCON, 0)         \
+  X(counts, 16, 0)
 
 /* arrays of unsigned short */
-#define FLY_WS_U16(X) X(cand, FLY_MAXCAND, FLY_BULK) X(lim_item, FLY_MAXEFC, FLY_BULK)
+#define FLY_WS_U16(X) X(cand, FLY_MAXCAND, 0) X(lim_item, FLY_MAXEFC, 0)
 
 /* indices into counts[] */
 enum { FLY_C_NCON = 0, FLY_C_NEFC, FLY_C_NLIMIT, FLY_C_NGRP, FLY_C_NCAND, FLY_C_NITER, FLY_C_OVERFLOW, FLY_C_NCROSS,
@@ -84,12 +83,12 @@ struct Ws {
 /* Carves the two arenas.  Pass null bases to only measure; sizes (bytes, 16-aligned) are returned. */
 template <class T>
 FLY_HD void ws_bind(const DModel<T>& m, Ws<T>* w, char* fast, char* bulk, size_t* fast_bytes, size_t* bulk_bytes,
-                    bool all_bulk) {
+                    int level) {
   size_t off[2] = {0, 0};
   char* base[2] = {bulk, fast};
 #define PLACE(n, cnt, tier, type)                                                    \
   {                                                                                  \
-    int t = all_bulk ? FLY_BULK : (tier);                                            \
+    int t = ((tier) > 0 && (tier) <= level) ? 1 : 0;                                            \
     size_t bytes = (((size_t)(cnt) * sizeof(type)) + 15) & ~(size_t)15;              \
     if (w) w->n = base[t] ? (type*)(base[t] + off[t]) : (type*)0;                    \
     off[t] += bytes;                                                                 \
@@ -104,7 +103,7 @@ FLY_HD void ws_bind(const DModel<T>& m, Ws<T>* w, char* fast, char* bulk, size_t
   FLY_WS_U16(X)
 #undef X
 #undef PLACE
-  if (fast_bytes) *fast_bytes = off[FLY_FAST];
-  if (bulk_bytes) *bulk_bytes = off[FLY_BULK];
+  if (fast_bytes) *fast_bytes = off[1];
+  if (bulk_bytes) *bulk_bytes = off[0];
 }
 #endif

@@ -1,0 +1,386 @@
+/* flyb_cuda.cu - the CUDA engine behind include/flyb.h (sm_100a).
+ *
+ * One persistent warp steps one environment at a time: warps pull env indices from a global counter until
+ * the batch is done, so envs with many contacts do not stall their neighbours.  Each resident warp owns a
+ * slice of shared memory (the hot tiers of the workspace, fly_ws.cuh) and a scratch slot in global memory
+ * that stays hot in L1/L2 because it is indexed by the resident warp, not by the env.  Per-env persistent
+ * state (qpos | qvel | act | qacc_warmstart) is one contiguous row per env in HBM, read and written once per
+ * control step with coalesced lane-strided accesses. */
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <string>
+#include <vector>
+#include "../../include/flyb.h"
+#include "fly_env.cuh"
+
+struct FlybEngine {
+  int device = 0, num_envs = 0, flags = 0, env_offset = 0;
+  unsigned long long seed = 0;
+  DModel<float> m;        /* pointers relocated to device addresses */
+  void* d_arena = nullptr;
+  float* d_sreal = nullptr; int* d_sint = nullptr; int sreal_stride = 0;
+  float* d_stats = nullptr;
+  int* d_trace_int = nullptr; float* d_trace_real = nullptr; int trace_real_stride = 0;
+  char* d_bulk = nullptr; size_t bulk_stride = 0, fast_stride = 0; int bulk_slots = 0;
+  int* d_counter = nullptr;
+  float* d_clip_rows = nullptr; int* d_clip_off = nullptr; int* d_clip_len = nullptr; int n_clips = 0;
+  /* staging for the host-pointer API */
+  float *h_action = nullptr, *h_obs = nullptr, *h_rd = nullptr; int* h_st = nullptr; unsigned char* h_mask = nullptr;
+  float *d_action = nullptr, *d_obs = nullptr, *d_rd = nullptr; int* d_st = nullptr; unsigned char* d_mask = nullptr;
+  cudaStream_t host_stream = nullptr;
+  int smem_level = 2, warps = 4, blocks_per_sm = 0, sm_count = 148, grid = 0;
+  long long launches = 0;
+  std::string err;
+};
+
+static std::string g_create_error;
+
+#define CK(call)                                                                                   \
+  do {                                                                                             \
+    cudaError_t e_ = (call);                                                                       \
+    if (e_ != cudaSuccess) {                                                                       \
+      h->err = std::string(#call) + ": " + cudaGetErrorString(e_);                                 \
+      return 1;                                                                                    \
+    }                                                                                              \
+  } while (0)
+
+struct KArgs {
+  FlyClips clips;
+  FlyIO<float> io;
+  char* bulk;
+  size_t bulk_stride, fast_stride;
+  int* counter;
+  int num_envs, level;
+};
+
+template <int WARPS>
+__global__ void __launch_bounds__(WARPS * 32) fly_step_kernel(const __grid_constant__ DModel<float> m,
+                                                                const __grid_constant__ KArgs a) {
+  extern __shared__ __align__(16) char smem[];
+  __shared__ Ws<float> ws[WARPS];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int slot = blockIdx.x * WARPS + warp;
+  if (lane == 0)
+    ws_bind<float>(m, &ws[warp], smem + warp * a.fast_stride, a.bulk + (size_t)slot * a.bulk_stride, nullptr, nullptr, a.level);
+  __syncwarp();
+  const Ws<float>& w = ws[warp];
+  for (;;) {
+    int env = 0;
+    if (lane == 0) env = atomicAdd(a.counter, 1);
+    env = __shfl_sync(0xffffffffu, env, 0);
+    if (env >= a.num_envs) break;
+    fly_env_run<float>(m, w, a.clips, a.io, env);
+  }
+}
+
+static int launch(FlybEngine* h, const FlyIO<float>& io, cudaStream_t st) {
+  CK(cudaSetDevice(h->device));
+  size_t fb = 0, bb = 0;
+  ws_bind<float>(h->m, nullptr, nullptr, nullptr, &fb, &bb, h->smem_level);
+  h->fast_stride = fb;
+  const int W = h->warps;
+  const size_t smem = fb * W;
+  if (smem > 220 * 1024) { h->err = "shared memory request too large for this smem_level / warps_per_block"; return 1; }
+  void (*kern)(const DModel<float>, const KArgs) = nullptr;
+  switch (W) {
+    case 1: kern = fly_step_kernel<1>; break;
+    case 2: kern = fly_step_kernel<2>; break;
+    case 4: kern = fly_step_kernel<4>; break;
+    case 8: kern = fly_step_kernel<8>; break;
+    default: h->err = "warps_per_block must be 1, 2, 4 or 8"; return 1;
+  }
+  CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int per_sm = 0;
+  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, W * 32, smem));
+  if (per_sm < 1) { h->err = "kernel does not fit on an SM"; return 1; }
+  if (h->blocks_per_sm > 0 && h->blocks_per_sm < per_sm) per_sm = h->blocks_per_sm;
+  int grid = h->sm_count * per_sm;
+  const int need = (h->num_envs + W - 1) / W;
+  if (grid > need) grid = need;
+  if (grid * W > h->bulk_slots) grid = h->bulk_slots / W;
+  h->grid = grid;
+  KArgs a;
+  a.clips.data = h->d_clip_rows; a.clips.offset = h->d_clip_off; a.clips.length = h->d_clip_len; a.clips.nclips = h->n_clips;
+  a.io = io;
+  a.bulk = h->d_bulk; a.bulk_stride = h->bulk_stride; a.fast_stride = fb; a.counter = h->d_counter;
+  a.num_envs = h->num_envs; a.level = h->smem_level;
+  CK(cudaMemsetAsync(h->d_counter, 0, sizeof(int), st));
+  kern<<<grid, W * 32, smem, st>>>(h->m, a);
+  CK(cudaGetLastError());
+  h->launches++;
+  return 0;
+}
+
+static FlyIO<float> make_io(FlybEngine* h, const float* action, float* obs, float* reward, float* discount, int* st) {
+  FlyIO<float> io;
+  memset(&io, 0, sizeof(io));
+  io.sreal = h->d_sreal; io.sint = h->d_sint; io.sreal_stride = h->sreal_stride;
+  io.action = action; io.obs = obs; io.reward = reward; io.discount = discount; io.step_type = st;
+  io.trace_int = h->d_trace_int; io.trace_real = h->d_trace_real; io.trace_real_stride = h->trace_real_stride;
+  io.stats = h->d_stats; io.seed = h->seed; io.env_offset = h->env_offset;
+  return io;
+}
+
+extern "C" {
+
+const char* flyb_last_error(flyb_handle h) { return h ? h->err.c_str() : g_create_error.c_str(); }
+
+int flyb_create(const FlybModel* model, int num_envs, int device, uint64_t seed, int env_offset, int flags,
+                flyb_handle* out) {
+  *out = nullptr;
+  FlybEngine* h = new FlybEngine();
+  auto fail = [&](const std::string& msg) { g_create_error = msg; delete h; return 1; };
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0)
+    return fail("no CUDA device: this library has no CPU fallback");
+  if (device < 0 || device >= ndev) return fail("bad device index");
+  if (num_envs <= 0) return fail("num_envs must be positive");
+  if (cudaSetDevice(device) != cudaSuccess) return fail("cudaSetDevice failed");
+  h->device = device; h->num_envs = num_envs; h->flags = flags; h->seed = seed; h->env_offset = env_offset;
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return fail("cudaGetDeviceProperties failed");
+  h->sm_count = prop.multiProcessorCount;
+  FlyArena arena;
+  std::string e = build_dmodel<float>(model, flags & 0xffff, &h->m, &arena);
+  if (!e.empty()) return fail(e);
+#define CKC(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(std::string(#call) + ": " + cudaGetErrorString(e_)); } while (0)
+  CKC(cudaMalloc(&h->d_arena, arena.buf.size()));
+  CKC(cudaMemcpy(h->d_arena, arena.buf.data(), arena.buf.size(), cudaMemcpyHostToDevice));
+  fly_relocate(&h->m, h->d_arena);
+  const DModel<float>& m = h->m;
+  const size_t N = (size_t)num_envs;
+  h->sreal_stride = ((m.nq + 2 * m.nv + m.na + 1) + 3) & ~3;
+  CKC(cudaMalloc(&h->d_sreal, N * h->sreal_stride * sizeof(float)));
+  CKC(cudaMemset(h->d_sreal, 0, N * h->sreal_stride * sizeof(float)));
+  CKC(cudaMalloc(&h->d_sint, N * FLY_SI_COUNT * sizeof(int)));
+  {
+    std::vector<int> si(N * FLY_SI_COUNT, 0);
+    for (size_t i = 0; i < N; i++) { si[i * FLY_SI_COUNT + FLY_SI_FORCED_CLIP] = -1; si[i * FLY_SI_COUNT + FLY_SI_RESET_NEXT] = 1; }
+    CKC(cudaMemcpy(h->d_sint, si.data(), si.size() * sizeof(int), cudaMemcpyHostToDevice));
+  }
+  CKC(cudaMalloc(&h->d_stats, N * 4 * sizeof(float)));
+  CKC(cudaMemset(h->d_stats, 0, N * 4 * sizeof(float)));
+  if (flags & FLYB_FLAG_TRACE) {
+    h->trace_real_stride = FLY_MAXCON + m.nv + m.nsensordata + FLY_MAXEFC;
+    CKC(cudaMalloc(&h->d_trace_int, N * FLY_TR_INTS * sizeof(int)));
+    CKC(cudaMalloc(&h->d_trace_real, N * h->trace_real_stride * sizeof(float)));
+    CKC(cudaMemset(h->d_trace_int, 0, N * FLY_TR_INTS * sizeof(int)));
+    CKC(cudaMemset(h->d_trace_real, 0, N * h->trace_real_stride * sizeof(float)));
+  }
+  /* scratch slots: one per resident warp, sized for the all-bulk layout so any smem_level fits */
+  size_t fb = 0, bb = 0;
+  ws_bind<float>(m, nullptr, nullptr, nullptr, &fb, &bb, 0);
+  h->bulk_stride = (bb + 255) & ~(size_t)255;
+  h->bulk_slots = h->sm_count * 32;
+  if ((size_t)h->bulk_slots > N + 8) h->bulk_slots = (int)((N + 7) & ~(size_t)7);
+  CKC(cudaMalloc(&h->d_bulk, (size_t)h->bulk_slots * h->bulk_stride));
+  CKC(cudaMemset(h->d_bulk, 0, (size_t)h->bulk_slots * h->bulk_stride));
+  CKC(cudaMalloc(&h->d_counter, sizeof(int)));
+  /* staging */
+  CKC(cudaStreamCreateWithFlags(&h->host_stream, cudaStreamNonBlocking));
+  CKC(cudaMallocHost(&h->h_action, N * m.action_dim * sizeof(float)));
+  CKC(cudaMallocHost(&h->h_obs, N * m.obs_dim * sizeof(float)));
+  CKC(cudaMallocHost(&h->h_rd, N * 2 * sizeof(float)));
+  CKC(cudaMallocHost(&h->h_st, N * sizeof(int)));
+  CKC(cudaMallocHost(&h->h_mask, N));
+  CKC(cudaMalloc(&h->d_action, N * m.action_dim * sizeof(float)));
+  CKC(cudaMalloc(&h->d_obs, N * m.obs_dim * sizeof(float)));
+  CKC(cudaMalloc(&h->d_rd, N * 2 * sizeof(float)));
+  CKC(cudaMalloc(&h->d_st, N * sizeof(int)));
+  CKC(cudaMalloc(&h->d_mask, N));
+  CKC(cudaMemset(h->d_action, 0, N * m.action_dim * sizeof(float)));
+#undef CKC
+  const char* lv = getenv("FLYB_SMEM_LEVEL");
+  if (lv) h->smem_level = atoi(lv);
+  const char* wp = getenv("FLYB_WARPS");
+  if (wp) h->warps = atoi(wp);
+  *out = h;
+  return 0;
+}
+
+void flyb_destroy(flyb_handle h) {
+  if (!h) return;
+  cudaSetDevice(h->device);
+  cudaDeviceSynchronize();
+  cudaFree(h->d_arena); cudaFree(h->d_sreal); cudaFree(h->d_sint); cudaFree(h->d_stats); cudaFree(h->d_trace_int);
+  cudaFree(h->d_trace_real); cudaFree(h->d_bulk); cudaFree(h->d_counter); cudaFree(h->d_clip_rows);
+  cudaFree(h->d_clip_off); cudaFree(h->d_clip_len); cudaFree(h->d_action); cudaFree(h->d_obs); cudaFree(h->d_rd);
+  cudaFree(h->d_st); cudaFree(h->d_mask);
+  cudaFreeHost(h->h_action); cudaFreeHost(h->h_obs); cudaFreeHost(h->h_rd); cudaFreeHost(h->h_st); cudaFreeHost(h->h_mask);
+  if (h->host_stream) cudaStreamDestroy(h->host_stream);
+  delete h;
+}
+
+int64_t flyb_info(flyb_handle h, int what) {
+  switch (what) {
+    case FLYB_INFO_NUM_ENVS: return h->num_envs;
+    case FLYB_INFO_OBS_DIM: return h->m.obs_dim;
+    case FLYB_INFO_ACTION_DIM: return h->m.action_dim;
+    case FLYB_INFO_NQ: return h->m.nq;
+    case FLYB_INFO_NV: return h->m.nv;
+    case FLYB_INFO_NA: return h->m.na;
+    case FLYB_INFO_TRACE_INTS: return FLY_TR_INTS;
+    case FLYB_INFO_TRACE_REALS: return h->trace_real_stride;
+    case FLYB_INFO_LAUNCHES: return h->launches;
+    case FLYB_INFO_SMEM_BYTES: return (int64_t)(h->fast_stride * h->warps);
+    case FLYB_INFO_BULK_BYTES: return (int64_t)h->bulk_stride;
+    case FLYB_INFO_GRID: return h->grid;
+    case FLYB_INFO_MAXCON: return FLY_MAXCON;
+    case FLYB_INFO_MAXEFC: return FLY_MAXEFC;
+    case FLYB_INFO_STATE_INTS: return FLY_SI_COUNT;
+    case FLYB_INFO_WARPS_PER_BLOCK: return h->warps;
+    case FLYB_INFO_SMEM_LEVEL: return h->smem_level;
+  }
+  return -1;
+}
+
+int flyb_configure(flyb_handle h, int smem_level, int warps_per_block, int blocks_per_sm) {
+  if (smem_level < 0 || smem_level > 3) { h->err = "smem_level must be 0..3"; return 1; }
+  if (warps_per_block != 1 && warps_per_block != 2 && warps_per_block != 4 && warps_per_block != 8) {
+    h->err = "warps_per_block must be 1, 2, 4 or 8"; return 1;
+  }
+  h->smem_level = smem_level; h->warps = warps_per_block; h->blocks_per_sm = blocks_per_sm;
+  return 0;
+}
+
+int flyb_load_clips(flyb_handle h, const float* rows, const int32_t* offsets, const int32_t* lengths, int n_clips) {
+  CK(cudaSetDevice(h->device));
+  if (n_clips <= 0) { h->err = "n_clips must be positive"; return 1; }
+  size_t nrows = 0;
+  for (int i = 0; i < n_clips; i++) {
+    if (lengths[i] <= 0 || offsets[i] < 0) { h->err = "bad clip offsets/lengths"; return 1; }
+    size_t e = (size_t)offsets[i] + lengths[i];
+    if (e > nrows) nrows = e;
+  }
+  cudaFree(h->d_clip_rows); cudaFree(h->d_clip_off); cudaFree(h->d_clip_len);
+  h->d_clip_rows = nullptr; h->d_clip_off = nullptr; h->d_clip_len = nullptr; h->n_clips = 0;
+  CK(cudaMalloc(&h->d_clip_rows, nrows * h->m.clip_width * sizeof(float)));
+  CK(cudaMalloc(&h->d_clip_off, n_clips * sizeof(int)));
+  CK(cudaMalloc(&h->d_clip_len, n_clips * sizeof(int)));
+  CK(cudaMemcpy(h->d_clip_rows, rows, nrows * h->m.clip_width * sizeof(float), cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(h->d_clip_off, offsets, n_clips * sizeof(int), cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(h->d_clip_len, lengths, n_clips * sizeof(int), cudaMemcpyHostToDevice));
+  h->n_clips = n_clips;
+  return 0;
+}
+
+int flyb_set_clip_ids(flyb_handle h, const int32_t* ids) {
+  CK(cudaSetDevice(h->device));
+  CK(cudaDeviceSynchronize());
+  std::vector<int> si((size_t)h->num_envs * FLY_SI_COUNT);
+  CK(cudaMemcpy(si.data(), h->d_sint, si.size() * sizeof(int), cudaMemcpyDeviceToHost));
+  for (int i = 0; i < h->num_envs; i++) si[(size_t)i * FLY_SI_COUNT + FLY_SI_FORCED_CLIP] = ids ? ids[i] : -1;
+  CK(cudaMemcpy(h->d_sint, si.data(), si.size() * sizeof(int), cudaMemcpyHostToDevice));
+  return 0;
+}
+
+int flyb_reset(flyb_handle h, const uint8_t* mask, float* obs, int32_t* step_type, void* stream) {
+  FlyIO<float> io = make_io(h, nullptr, obs, nullptr, nullptr, step_type);
+  io.force_reset = 1; io.reset_mask = mask;
+  return launch(h, io, (cudaStream_t)stream);
+}
+
+int flyb_step(flyb_handle h, const float* action, float* obs, float* reward, float* discount, int32_t* step_type,
+              void* stream) {
+  FlyIO<float> io = make_io(h, action, obs, reward, discount, step_type);
+  return launch(h, io, (cudaStream_t)stream);
+}
+
+int flyb_reset_host(flyb_handle h, const uint8_t* mask, float* obs, int32_t* step_type) {
+  CK(cudaSetDevice(h->device));
+  const size_t N = h->num_envs;
+  cudaStream_t s = h->host_stream;
+  if (mask) { memcpy(h->h_mask, mask, N); CK(cudaMemcpyAsync(h->d_mask, h->h_mask, N, cudaMemcpyHostToDevice, s)); }
+  if (flyb_reset(h, mask ? h->d_mask : nullptr, h->d_obs, h->d_st, s)) return 1;
+  CK(cudaMemcpyAsync(h->h_obs, h->d_obs, N * h->m.obs_dim * sizeof(float), cudaMemcpyDeviceToHost, s));
+  CK(cudaMemcpyAsync(h->h_st, h->d_st, N * sizeof(int), cudaMemcpyDeviceToHost, s));
+  CK(cudaStreamSynchronize(s));
+  for (size_t i = 0; i < N; i++) {
+    if (mask && !mask[i]) continue;
+    if (obs) memcpy(obs + i * h->m.obs_dim, h->h_obs + i * h->m.obs_dim, h->m.obs_dim * sizeof(float));
+    if (step_type) step_type[i] = h->h_st[i];
+  }
+  return 0;
+}
+
+int flyb_step_host(flyb_handle h, const float* action, float* obs, float* reward, float* discount, int32_t* step_type) {
+  CK(cudaSetDevice(h->device));
+  const size_t N = h->num_envs;
+  cudaStream_t s = h->host_stream;
+  memcpy(h->h_action, action, N * h->m.action_dim * sizeof(float));
+  CK(cudaMemcpyAsync(h->d_action, h->h_action, N * h->m.action_dim * sizeof(float), cudaMemcpyHostToDevice, s));
+  if (flyb_step(h, h->d_action, h->d_obs, h->d_rd, h->d_rd + N, h->d_st, s)) return 1;
+  CK(cudaMemcpyAsync(h->h_obs, h->d_obs, N * h->m.obs_dim * sizeof(float), cudaMemcpyDeviceToHost, s));
+  CK(cudaMemcpyAsync(h->h_rd, h->d_rd, 2 * N * sizeof(float), cudaMemcpyDeviceToHost, s));
+  CK(cudaMemcpyAsync(h->h_st, h->d_st, N * sizeof(int), cudaMemcpyDeviceToHost, s));
+  CK(cudaStreamSynchronize(s));
+  if (obs) memcpy(obs, h->h_obs, N * h->m.obs_dim * sizeof(float));
+  if (reward) memcpy(reward, h->h_rd, N * sizeof(float));
+  if (discount) memcpy(discount, h->h_rd + N, N * sizeof(float));
+  if (step_type) memcpy(step_type, h->h_st, N * sizeof(int));
+  return 0;
+}
+
+int flyb_get_state(flyb_handle h, float* qpos, float* qvel, float* act, float* warm, int32_t* ints) {
+  CK(cudaSetDevice(h->device));
+  CK(cudaDeviceSynchronize());
+  const DModel<float>& m = h->m;
+  const size_t N = h->num_envs, S = h->sreal_stride;
+  std::vector<float> sr(N * S);
+  CK(cudaMemcpy(sr.data(), h->d_sreal, sr.size() * sizeof(float), cudaMemcpyDeviceToHost));
+  for (size_t i = 0; i < N; i++) {
+    const float* r = sr.data() + i * S;
+    if (qpos) memcpy(qpos + i * m.nq, r, m.nq * sizeof(float));
+    if (qvel) memcpy(qvel + i * m.nv, r + m.nq, m.nv * sizeof(float));
+    if (act && m.na) memcpy(act + i * m.na, r + m.nq + m.nv, m.na * sizeof(float));
+    if (warm) memcpy(warm + i * m.nv, r + m.nq + m.nv + m.na, m.nv * sizeof(float));
+  }
+  if (ints) CK(cudaMemcpy(ints, h->d_sint, N * FLY_SI_COUNT * sizeof(int), cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+int flyb_set_state(flyb_handle h, const float* qpos, const float* qvel, const float* act, const float* warm,
+                   const int32_t* ints) {
+  CK(cudaSetDevice(h->device));
+  CK(cudaDeviceSynchronize());
+  const DModel<float>& m = h->m;
+  const size_t N = h->num_envs, S = h->sreal_stride;
+  std::vector<float> sr(N * S);
+  CK(cudaMemcpy(sr.data(), h->d_sreal, sr.size() * sizeof(float), cudaMemcpyDeviceToHost));
+  for (size_t i = 0; i < N; i++) {
+    float* r = sr.data() + i * S;
+    if (qpos) memcpy(r, qpos + i * m.nq, m.nq * sizeof(float));
+    if (qvel) memcpy(r + m.nq, qvel + i * m.nv, m.nv * sizeof(float));
+    if (act && m.na) memcpy(r + m.nq + m.nv, act + i * m.na, m.na * sizeof(float));
+    if (warm) memcpy(r + m.nq + m.nv + m.na, warm + i * m.nv, m.nv * sizeof(float));
+  }
+  CK(cudaMemcpy(h->d_sreal, sr.data(), sr.size() * sizeof(float), cudaMemcpyHostToDevice));
+  if (ints) CK(cudaMemcpy(h->d_sint, ints, N * FLY_SI_COUNT * sizeof(int), cudaMemcpyHostToDevice));
+  return 0;
+}
+
+int flyb_get_trace(flyb_handle h, int32_t* ints, float* reals) {
+  if (!h->d_trace_int) { h->err = "create the engine with FLYB_FLAG_TRACE to record traces"; return 1; }
+  CK(cudaSetDevice(h->device));
+  CK(cudaDeviceSynchronize());
+  const size_t N = h->num_envs;
+  if (ints) CK(cudaMemcpy(ints, h->d_trace_int, N * FLY_TR_INTS * sizeof(int), cudaMemcpyDeviceToHost));
+  if (reals) CK(cudaMemcpy(reals, h->d_trace_real, N * h->trace_real_stride * sizeof(float), cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+int flyb_episode_stats(flyb_handle h, double* out4) {
+  CK(cudaSetDevice(h->device));
+  CK(cudaDeviceSynchronize());
+  const size_t N = h->num_envs;
+  std::vector<float> s(N * 4);
+  CK(cudaMemcpy(s.data(), h->d_stats, s.size() * sizeof(float), cudaMemcpyDeviceToHost));
+  CK(cudaMemset(h->d_stats, 0, s.size() * sizeof(float)));
+  for (int k = 0; k < 4; k++) out4[k] = 0;
+  for (size_t i = 0; i < N; i++) for (int k = 0; k < 4; k++) out4[k] += s[i * 4 + k];
+  return 0;
+}
+
+}  /* extern "C" */

@@ -1,0 +1,180 @@
+"""ctypes binding of libflyb.so (include/flyb.h): the only way the Python host layer reaches the GPU.
+
+There is no CPU fallback.  If the library has not been built (`python -c "import __graft_entry__ as g; g.build()"`)
+or no CUDA device is present, constructing an engine raises."""
+from __future__ import annotations
+
+import ctypes
+import os
+import subprocess
+import numpy as np
+
+from .model_pack import FlybModel, pack_model
+
+_DIR = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_DIR, "libflyb.so")
+CSRC = os.path.join(_DIR, "csrc")
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "--expt-extended-lambda",
+              "-Xcompiler", "-fPIC", "-shared"]
+
+FLAG_NOCONTACT, FLAG_NOLIMIT, FLAG_NOFLUID, FLAG_NONOSLIP, FLAG_NOACTUATION, FLAG_NOWARMSTART = 1, 2, 4, 8, 16, 32
+FLAG_TRACE = 1 << 16
+(INFO_NUM_ENVS, INFO_OBS_DIM, INFO_ACTION_DIM, INFO_NQ, INFO_NV, INFO_NA, INFO_TRACE_INTS, INFO_TRACE_REALS,
+ INFO_LAUNCHES, INFO_SMEM_BYTES, INFO_BULK_BYTES, INFO_GRID, INFO_MAXCON, INFO_MAXEFC, INFO_STATE_INTS,
+ INFO_WARPS_PER_BLOCK, INFO_SMEM_LEVEL) = range(17)
+
+EXPORTS = ["flyb_create", "flyb_destroy", "flyb_last_error", "flyb_info", "flyb_configure", "flyb_load_clips",
+           "flyb_set_clip_ids", "flyb_reset", "flyb_step", "flyb_reset_host", "flyb_step_host", "flyb_get_state",
+           "flyb_set_state", "flyb_get_trace", "flyb_episode_stats"]
+
+
+def build_library(force: bool = False, verbose: bool = False) -> str:
+    """nvcc-compiles flybody_b200/csrc/flyb_cuda.cu for sm_100a into flybody_b200/libflyb.so (in-tree)."""
+    srcs = [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC))] + [os.path.join(_DIR, "..", "include", f) for f in ("flyb.h", "flyb_model.h")]
+    newest = max(os.path.getmtime(s) for s in srcs)
+    if not force and os.path.exists(LIB_PATH) and os.path.getmtime(LIB_PATH) >= newest:
+        return LIB_PATH
+    cmd = ["nvcc"] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB_PATH, os.path.join(CSRC, "flyb_cuda.cu")]
+    subprocess.check_call(cmd)
+    return LIB_PATH
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(f"{LIB_PATH} is missing: build it with __graft_entry__.build() (nvcc, sm_100a). "
+                               "There is no CPU fallback.")
+        L = ctypes.CDLL(LIB_PATH)
+        vp, c_i, fp = ctypes.c_void_p, ctypes.c_int, ctypes.POINTER(ctypes.c_float)
+        ip, u8p, dp = ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_uint8), ctypes.POINTER(ctypes.c_double)
+        L.flyb_create.argtypes = [ctypes.POINTER(FlybModel), c_i, c_i, ctypes.c_uint64, c_i, c_i, ctypes.POINTER(vp)]
+        L.flyb_destroy.argtypes = [vp]
+        L.flyb_destroy.restype = None
+        L.flyb_last_error.argtypes = [vp]
+        L.flyb_last_error.restype = ctypes.c_char_p
+        L.flyb_info.argtypes = [vp, c_i]
+        L.flyb_info.restype = ctypes.c_int64
+        L.flyb_configure.argtypes = [vp, c_i, c_i, c_i]
+        L.flyb_load_clips.argtypes = [vp, fp, ip, ip, c_i]
+        L.flyb_set_clip_ids.argtypes = [vp, ip]
+        # device-pointer entry points take raw addresses (torch tensor.data_ptr()) and a raw cudaStream_t
+        L.flyb_reset.argtypes = [vp, vp, vp, vp, vp]
+        L.flyb_step.argtypes = [vp, vp, vp, vp, vp, vp, vp]
+        L.flyb_reset_host.argtypes = [vp, u8p, fp, ip]
+        L.flyb_step_host.argtypes = [vp, fp, fp, fp, fp, ip]
+        L.flyb_get_state.argtypes = [vp, fp, fp, fp, fp, ip]
+        L.flyb_set_state.argtypes = [vp, fp, fp, fp, fp, ip]
+        L.flyb_get_trace.argtypes = [vp, ip, fp]
+        L.flyb_episode_stats.argtypes = [vp, dp]
+        _lib = L
+    return _lib
+
+
+def _fp(a):
+    return a.ctypes.data_as(ctypes.POINTER(ctypes.c_float)) if a is not None else None
+
+
+def _ip(a):
+    return a.ctypes.data_as(ctypes.POINTER(ctypes.c_int32)) if a is not None else None
+
+
+class Engine:
+    """One libflyb handle: `num_envs` environments of one compiled task model on one GPU."""
+
+    def __init__(self, model: dict, num_envs: int, device: int = 0, seed: int = 0, env_offset: int = 0, flags: int = 0):
+        self.M = model
+        self._struct, self._keep = pack_model(model)
+        h = ctypes.c_void_p()
+        L = lib()
+        if L.flyb_create(ctypes.byref(self._struct), int(num_envs), int(device), int(seed) & (2**64 - 1), int(env_offset),
+                         int(flags), ctypes.byref(h)):
+            raise RuntimeError("flyb_create: " + L.flyb_last_error(None).decode())
+        self._h = h
+        self.num_envs, self.device, self.flags = int(num_envs), int(device), int(flags)
+        self.obs_dim, self.action_dim = int(self.info(INFO_OBS_DIM)), int(self.info(INFO_ACTION_DIM))
+        self.nq, self.nv, self.na = (int(self.info(k)) for k in (INFO_NQ, INFO_NV, INFO_NA))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().flyb_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def _ck(self, rc):
+        if rc:
+            raise RuntimeError(lib().flyb_last_error(self._h).decode())
+
+    def info(self, what: int) -> int:
+        return int(lib().flyb_info(self._h, what))
+
+    def configure(self, smem_level: int, warps_per_block: int, blocks_per_sm: int = 0):
+        self._ck(lib().flyb_configure(self._h, smem_level, warps_per_block, blocks_per_sm))
+
+    def load_clips(self, rows, offsets, lengths):
+        rows = np.ascontiguousarray(rows, np.float32)
+        offsets = np.ascontiguousarray(offsets, np.int32)
+        lengths = np.ascontiguousarray(lengths, np.int32)
+        self._ck(lib().flyb_load_clips(self._h, _fp(rows), _ip(offsets), _ip(lengths), len(offsets)))
+        self.n_clips = len(offsets)
+
+    def set_clip_ids(self, ids):
+        ids = None if ids is None else np.ascontiguousarray(ids, np.int32)
+        self._ck(lib().flyb_set_clip_ids(self._h, _ip(ids)))
+
+    # ---- device-pointer calls (raw addresses)
+    def reset_ptr(self, mask_ptr, obs_ptr, step_type_ptr, stream=0):
+        self._ck(lib().flyb_reset(self._h, mask_ptr, obs_ptr, step_type_ptr, stream))
+
+    def step_ptr(self, action_ptr, obs_ptr, reward_ptr, discount_ptr, step_type_ptr, stream=0):
+        self._ck(lib().flyb_step(self._h, action_ptr, obs_ptr, reward_ptr, discount_ptr, step_type_ptr, stream))
+
+    # ---- host (numpy) calls
+    def reset_host(self, mask=None):
+        N = self.num_envs
+        obs, st = np.zeros((N, self.obs_dim), np.float32), np.zeros(N, np.int32)
+        m = None if mask is None else np.ascontiguousarray(mask, np.uint8)
+        self._ck(lib().flyb_reset_host(self._h, m.ctypes.data_as(ctypes.POINTER(ctypes.c_uint8)) if m is not None else None,
+                                       _fp(obs), _ip(st)))
+        return st, obs
+
+    def step_host(self, action, out=None):
+        N = self.num_envs
+        a = np.ascontiguousarray(action, np.float32).reshape(N, self.action_dim)
+        if out is None:
+            out = (np.zeros((N, self.obs_dim), np.float32), np.zeros(N, np.float32), np.zeros(N, np.float32), np.zeros(N, np.int32))
+        obs, r, g, st = out
+        self._ck(lib().flyb_step_host(self._h, _fp(a), _fp(obs), _fp(r), _fp(g), _ip(st)))
+        return st, r, g, obs
+
+    def get_state(self):
+        N = self.num_envs
+        q, v = np.zeros((N, self.nq), np.float32), np.zeros((N, self.nv), np.float32)
+        a, w = np.zeros((N, max(self.na, 1)), np.float32), np.zeros((N, self.nv), np.float32)
+        si = np.zeros((N, int(self.info(INFO_STATE_INTS))), np.int32)
+        self._ck(lib().flyb_get_state(self._h, _fp(q), _fp(v), _fp(a), _fp(w), _ip(si)))
+        return dict(qpos=q, qvel=v, act=a[:, :self.na], warm=w, ints=si)
+
+    def set_state(self, qpos=None, qvel=None, act=None, warm=None, ints=None):
+        c = lambda x, dt: None if x is None else np.ascontiguousarray(x, dt)
+        q, v, a, w, si = c(qpos, np.float32), c(qvel, np.float32), c(act, np.float32), c(warm, np.float32), c(ints, np.int32)
+        self._ck(lib().flyb_set_state(self._h, _fp(q), _fp(v), _fp(a), _fp(w), _ip(si)))
+
+    def get_trace(self):
+        N = self.num_envs
+        ti = np.zeros((N, int(self.info(INFO_TRACE_INTS))), np.int32)
+        tr = np.zeros((N, int(self.info(INFO_TRACE_REALS))), np.float32)
+        self._ck(lib().flyb_get_trace(self._h, _ip(ti), _fp(tr)))
+        mc, nv, ns = int(self.info(INFO_MAXCON)), self.nv, int(self.M["nsensordata"])
+        return dict(ncon=ti[:, 0], nefc=ti[:, 1], nlimit=ti[:, 2], niter=ti[:, 3], overflow=ti[:, 4], ncand=ti[:, 5],
+                    pairs=ti[:, 8:], dist=tr[:, :mc], qacc=tr[:, mc:mc + nv], sensordata=tr[:, mc + nv:mc + nv + ns],
+                    efc_force=tr[:, mc + nv + ns:])
+
+    def episode_stats(self):
+        out = np.zeros(4, np.float64)
+        self._ck(lib().flyb_episode_stats(self._h, out.ctypes.data_as(ctypes.POINTER(ctypes.c_double))))
+        return dict(return_sum=out[0], length_sum=out[1], fatal=out[2], episodes=out[3])

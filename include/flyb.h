@@ -1,0 +1,95 @@
+/* flyb.h - C ABI of the B200 batched fruit-fly environment engine (libflyb.so).
+ *
+ * What it replaces.  The reference has no FFI of its own for this path: `env.step(action)` /
+ * `env.reset()` of the objects returned by vnl_ray/fly_envs.py:29-157 reach the MuJoCo C library through
+ * dm_control (`composer.Environment.step` -> `mjcf.Physics.step` -> `mj_step2`/`mj_step1`) one environment
+ * and one Python call at a time.  This library is the boundary a maintainer would bind instead (ctypes stub
+ * in INTEGRATION.md): N environments are stepped by one call, state stays resident in HBM.
+ *
+ *   flyb_create      <- fly_envs.walk_on_ball / walk_imitation / flight_imitation constructors
+ *                       (fly_envs.py:29,75,125) + composer.Environment.__init__ (fly_envs.py:67-72,117-122,152-157)
+ *   flyb_load_clips  <- HDF5WalkingTrajectoryLoader / HDF5FlightTrajectoryLoader (tasks/trajectory_loaders.py:10-223)
+ *   flyb_reset       <- composer.Environment.reset (task hooks walk_imitation.py:91-136)
+ *   flyb_step        <- composer.Environment.step (walk_imitation.py:138-191, tasks/base.py:190-217,
+ *                       fruitfly/fruitfly.py:480-492,532-669, tasks/rewards.py:9-111)
+ *   flyb_step_host   <- the same call as the reference makes it: numpy (host) action in, host TimeStep out
+ *   flyb_get_state / flyb_set_state <- physics.data.qpos/qvel/act/qacc_warmstart access (tasks/base.py:216,
+ *                       walk_imitation.py:119-123)
+ *
+ * Conventions.  All functions return 0 on success, non-zero on error (message: flyb_last_error).  Nothing
+ * throws across the ABI.  Physics divergence is not an error: it ends the episode (step_type LAST, discount
+ * 0), as vnl_ray/tasks/base.py:214-217 and dm_control's PhysicsError handling do.  The caller owns every I/O
+ * buffer; the library owns the model constants, clip table and per-env state.  One handle per GPU and
+ * process; calls on one handle must be serialised by the caller; work is enqueued on the given CUDA stream
+ * (cudaStream_t passed as void*, NULL = default stream) without hidden synchronisation, except the *_host
+ * calls, which synchronise that stream before returning.  There is no CPU fallback: without a CUDA device
+ * flyb_create fails. */
+#ifndef FLYB_H_
+#define FLYB_H_
+#include <stdint.h>
+#include "flyb_model.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct FlybEngine* flyb_handle;
+
+enum { FLYB_STEP_FIRST = 0, FLYB_STEP_MID = 1, FLYB_STEP_LAST = 2 };
+/* flags for flyb_create (tests switch stages off to isolate them) */
+enum { FLYB_FLAG_NOCONTACT = 1, FLYB_FLAG_NOLIMIT = 2, FLYB_FLAG_NOFLUID = 4, FLYB_FLAG_NONOSLIP = 8,
+       FLYB_FLAG_NOACTUATION = 16, FLYB_FLAG_NOWARMSTART = 32, FLYB_FLAG_TRACE = 1 << 16 };
+/* flyb_info selectors */
+enum { FLYB_INFO_NUM_ENVS = 0, FLYB_INFO_OBS_DIM, FLYB_INFO_ACTION_DIM, FLYB_INFO_NQ, FLYB_INFO_NV, FLYB_INFO_NA,
+       FLYB_INFO_TRACE_INTS, FLYB_INFO_TRACE_REALS, FLYB_INFO_LAUNCHES, FLYB_INFO_SMEM_BYTES, FLYB_INFO_BULK_BYTES,
+       FLYB_INFO_GRID, FLYB_INFO_MAXCON, FLYB_INFO_MAXEFC, FLYB_INFO_STATE_INTS, FLYB_INFO_WARPS_PER_BLOCK,
+       FLYB_INFO_SMEM_LEVEL };
+
+/* Compiles `model` for the device and allocates state for num_envs environments on CUDA device `device`.
+ * env_offset is the global index of this shard's first env (multi-GPU: rank * num_envs); it only enters the
+ * counter-based RNG that picks clips, so results do not depend on how envs are sharded. */
+int flyb_create(const FlybModel* model, int num_envs, int device, uint64_t seed, int env_offset, int flags,
+                flyb_handle* out);
+void flyb_destroy(flyb_handle h);
+const char* flyb_last_error(flyb_handle h);  /* h may be NULL: error of the last failed flyb_create */
+int64_t flyb_info(flyb_handle h, int what);
+
+/* Tuning knobs: smem_level 0..3 (how many workspace tiers live in shared memory), warps per block (1..8),
+ * blocks per SM (0 = as many as fit).  Takes effect at the next launch. */
+int flyb_configure(flyb_handle h, int smem_level, int warps_per_block, int blocks_per_sm);
+
+/* Reference clips (host pointers): rows of clip_width floats, [qpos 7+nj | qvel 6+nj | root2site 3ns | joint_quat 4nj]
+ * (walk_imitation) or [qpos 7 | qvel 6] (flight_imitation); clip c occupies rows offsets[c] .. offsets[c]+lengths[c]-1. */
+int flyb_load_clips(flyb_handle h, const float* rows, const int32_t* offsets, const int32_t* lengths, int n_clips);
+/* Per-env clip choice for the next resets (host pointer, num_envs entries; -1 = counter-based random). NULL = all random. */
+int flyb_set_clip_ids(flyb_handle h, const int32_t* ids);
+
+/* Device-pointer API.  mask: NULL (all envs) or num_envs bytes, non-zero = reset that env.
+ * Outputs of envs not reset are left untouched.  obs [N, obs_dim] float32, step_type [N] int32. */
+int flyb_reset(flyb_handle h, const uint8_t* mask, float* obs, int32_t* step_type, void* stream);
+/* One control step (n_substeps physics steps) of every env.  An env whose previous step returned LAST is
+ * reset instead (step_type FIRST, reward 0, discount 1): dm_env auto-reset semantics, per env. */
+int flyb_step(flyb_handle h, const float* action, float* obs, float* reward, float* discount, int32_t* step_type,
+              void* stream);
+
+/* Host-pointer API (what a numpy caller uses): copies through pinned staging buffers, synchronises. */
+int flyb_reset_host(flyb_handle h, const uint8_t* mask, float* obs, int32_t* step_type);
+int flyb_step_host(flyb_handle h, const float* action, float* obs, float* reward, float* discount, int32_t* step_type);
+
+/* State access (host pointers, any may be NULL).  qpos [N,nq] qvel [N,nv] act [N,na] qacc_warmstart [N,nv]
+ * ints [N, FLYB_INFO_STATE_INTS]: step, episode_steps, reset_next, clip, episode, forced_clip, episode_len, - */
+int flyb_get_state(flyb_handle h, float* qpos, float* qvel, float* act, float* warm, int32_t* ints);
+int flyb_set_state(flyb_handle h, const float* qpos, const float* qvel, const float* act, const float* warm,
+                   const int32_t* ints);
+/* Trace of the last launch (needs FLYB_FLAG_TRACE; host pointers, may be NULL).
+ * ints [N, TRACE_INTS]: ncon, nefc, nlimit, solver iterations, overflow bits, candidates, -, -, contact pair ids.
+ * reals [N, TRACE_REALS]: contact dist [MAXCON] | qacc [nv] | sensordata | efc_force [MAXEFC]. */
+int flyb_get_trace(flyb_handle h, int32_t* ints, float* reals);
+/* Episode statistics summed over this shard's envs since the last call (host, 4 doubles):
+ * sum of returns, sum of lengths, fatal terminations, finished episodes. */
+int flyb_episode_stats(flyb_handle h, double* out4);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

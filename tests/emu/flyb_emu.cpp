@@ -42,9 +42,9 @@ struct Emu : EmuBase {
     if (!err.empty()) return;
     fly_relocate(&m, arena.buf.data());
     size_t fb = 0, bb = 0;
-    ws_bind<T>(m, (Ws<T>*)0, 0, 0, &fb, &bb, true);
+    ws_bind<T>(m, (Ws<T>*)0, 0, 0, &fb, &bb, 0);
     mem.assign(bb + 64, 0);
-    ws_bind<T>(m, &w, 0, mem.data(), &fb, &bb, true);
+    ws_bind<T>(m, &w, 0, mem.data(), &fb, &bb, 0);
     sreal.assign(m.nq + 2 * m.nv + m.na + 4, 0);
     sint.assign(FLY_SI_COUNT, 0);
     sint[FLY_SI_FORCED_CLIP] = -1;
