@@ -1,0 +1,93 @@
+"""Generates tests/golden/*.npz by running the importable pure-numpy pieces of the REFERENCE
+(/root/reference/vnl_ray/{quaternions.py,tasks/rewards.py}) on states produced by the float64 oracle.
+Run in the build container only (needs /root/reference); the fixtures are committed and travel to the GPU box.
+
+What the fixtures pin:
+  walk_reward.npz  - per control step of a seeded walk_imitation rollout: the reward that
+                     rewards.reward_factors_deep_mimic(get_walker_features-equivalent, get_reference_features, weights=(20,1,1,1))
+                     returns, and the ref_displacement / ref_root_quat observations computed with the reference's
+                     quaternions.get_dquat_local, from the oracle's qpos / qvel / site_xpos / xaxis at that step.
+  quaternions.npz  - input/output pairs of the reference quaternion helpers the task layer restates.
+"""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, "/root/reference")
+import numpy as np
+
+from vnl_ray import quaternions as Q                      # reference code
+from vnl_ray.tasks import rewards as R                    # reference code
+from flybody_b200 import clips as C
+from flybody_b200.compile_fly import load_model
+from flybody_b200.model_pack import asset_path
+from oracle.oracle import OracleEnv
+
+OUT = os.path.join(ROOT, "tests", "golden")
+
+
+def walk_reward(n_steps=40, seed=0, T=120):
+    M = load_model(asset_path("walk_imitation"))
+    clip = C.synth_walk_clip(M, T=T, seed=seed)
+    rows, off, ln = C.pack_clips(M, [clip])
+    r = rows.astype(np.float64)   # the engine stores clips in float32; the oracle gets the same rounded values
+    nj, ns = int(M["n_mocap_joints"]), int(M["n_mocap_sites"])
+    ref = dict(qpos=r[:, :7 + nj], qvel=r[:, 7 + nj:13 + 2 * nj], root2site=r[:, 13 + 2 * nj:13 + 2 * nj + 3 * ns].reshape(-1, ns, 3),
+               joint_quat=r[:, 13 + 2 * nj + 3 * ns:].reshape(-1, nj, 4))
+    o = OracleEnv(M)
+    o.set_clip(ref["qpos"], ref["qvel"], ref["root2site"], ref["joint_quat"])
+    o.env_reset()
+    rng = np.random.RandomState(seed)
+    F = int(M["future_steps"]) + 1
+    ra, rd = int(M["root_qposadr"]), int(M["root_dofadr"])
+    actions, rewards, ref_disp, ref_quat, oracle_rewards = [], [], [], [], []
+    for k in range(n_steps):
+        a = rng.uniform(M["action_min"], M["action_max"]).astype(np.float32)
+        st, orew, og, oobs = o.env_step(a.astype(np.float64))
+        step = k + 1
+        qpos, qvel = o.d("qpos").copy(), o.d("qvel").copy()
+        jq = [int(M["jnt_qposadr"][j]) for j in M["mocap_joint"]]
+        jd = [int(M["jnt_dofadr"][j]) for j in M["mocap_joint"]]
+        mq = np.concatenate([qpos[ra:ra + 7], qpos[jq]])          # physics.bind(mocap_joints).qpos
+        mv = np.concatenate([qvel[rd:rd + 6], qvel[jd]])
+        sites = o.d("site_xpos").reshape(-1, 3)[np.asarray(M["mocap_site"])]
+        xaxis1 = o.d("xaxis").reshape(-1, 3)[np.asarray(M["mocap_joint"])]
+        # rewards.get_walker_features, lines 39-60, with physics.bind(...) replaced by the arrays above
+        root2site = Q.get_egocentric_vec(mq[:3], sites, mq[3:7])
+        root_quat = mq[3:7]
+        xaxis1 = Q.rotate_vec_with_quat(xaxis1, Q.reciprocal_quat(root_quat))
+        joint_quat = np.vstack((root_quat, Q.joint_orientation_quat(xaxis1, mq[7:])))
+        walker_ft = {"com": mq[:3], "qvel": mv, "root2site": root2site, "joint_quat": joint_quat}
+        reference_ft = R.get_reference_features(ref, step)
+        rew = float(np.prod(R.reward_factors_deep_mimic(walker_ft, reference_ft, weights=(20, 1, 1, 1))))
+        # tasks/base.py:237-261
+        xmat = o.d("xmat").reshape(-1, 3, 3)[int(M["root_body"])]
+        ref_pos = ref["qpos"][step:step + F, :3]
+        disp = (ref_pos - qpos[ra:ra + 3]) @ xmat
+        dq = Q.get_dquat_local(qpos[ra + 3:ra + 7], ref["qpos"][step:step + F, 3:7])
+        actions.append(a); rewards.append(rew); ref_disp.append(disp); ref_quat.append(dq); oracle_rewards.append(orew)
+        if st == 2:
+            break
+    np.savez(os.path.join(OUT, "walk_reward.npz"), seed=seed, T=T, actions=np.array(actions), reward=np.array(rewards),
+             ref_displacement=np.array(ref_disp), ref_root_quat=np.array(ref_quat))
+    print("walk_reward: steps", len(rewards), "max |oracle - reference| reward", np.abs(np.array(rewards) - np.array(oracle_rewards)).max())
+
+
+def quaternion_vectors(seed=1):
+    rng = np.random.RandomState(seed)
+    q1, q2 = rng.normal(size=(64, 4)), rng.normal(size=(64, 4))
+    v = rng.normal(size=(64, 3))
+    v[:4] = [[0, 0, 1.0], [0, 0, -1.0], [0, 0, 2.5], [1e-30, 0, 1.0]]   # quat_z2vec edge cases
+    ang = rng.uniform(-3, 3, 64)
+    np.savez(os.path.join(OUT, "quaternions.npz"), q1=q1, q2=q2, v=v, ang=ang,
+             mult=Q.mult_quat(q1, q2), recip=Q.reciprocal_quat(q1), rot=Q.rotate_vec_with_quat(v, q1),
+             dquat_local=Q.get_dquat_local(q1, q2), z2vec=Q.quat_z2vec(v), dist=Q.quat_dist_short_arc(q1, q2),
+             joint_quat=Q.joint_orientation_quat(v, ang), egocentric=Q.get_egocentric_vec(v[0], v, q1[0]))
+    print("quaternions: ok")
+
+
+if __name__ == "__main__":
+    os.makedirs(OUT, exist_ok=True)
+    walk_reward()
+    quaternion_vectors()
