@@ -1,0 +1,273 @@
+"""bench.py - fly env-steps/s of walk_imitation (BASELINE.json configs[1]: synthetic reference clips, 16384 envs per B200).
+
+  python bench.py --gpus N --steps K --warmup W            own arm (CUDA engine through the C ABI)
+  python bench.py --impl reference --gpus N ...            the reference's CPU algorithm on the host cores
+
+A "step" is one control step (10 physics substeps) of every env of the shard.  `value` is timed with CUDA events
+on the launching stream with actions already resident in HBM; `e2e` goes through the host-pointer C-ABI call
+(`flyb_step_host`: pinned H2D of the actions, launch, D2H of observations / reward / discount / step_type inside the
+timed region).  Envs shard across ranks with no data-path collective (weak scaling: 16384 envs per GPU); NCCL is
+used for the barrier, the max-over-ranks of the timing and the episode-statistics all-reduce.
+
+The reference's own implementation of the path (MuJoCo C via dm_control) is not installable here (no network, not
+vendored): `--impl reference` and `cpu_baseline` time the float64 CPU restatement in oracle/ (kind "port")."""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+import numpy as np  # noqa: E402
+
+ENVS_PER_GPU = 16384
+ALGO_BYTES = {"walk_imitation": 9984, "walk_on_ball": 4436}   # compulsory fp32 bytes per env-step
+METRIC = "fly env-steps/s (walk_imitation, 16384 envs per GPU, synthetic clips, random actions)"
+
+
+def _peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured"
+    return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    def __init__(self, index: int):
+        self.rows, self.proc = [], None
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(index)],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 6 for i in range(4) if r[2 + i].lower().startswith("active")})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(sm)}
+
+
+def _model_and_clips(n_clips, T):
+    from flybody_b200 import clips as C
+    from flybody_b200.compile_fly import load_model
+    from flybody_b200.model_pack import asset_path
+    M = load_model(asset_path("walk_imitation"))
+    return M, C.synthetic_table(M, n_clips, T, 0)
+
+
+# ------------------------------------------------------------------------------------------------ CPU arms
+def _cpu_worker(args):
+    """`steps` control steps of one oracle env (auto-reset on LAST); returns elapsed seconds."""
+    wid, steps, rows_path = args
+    from flybody_b200.compile_fly import load_model
+    from flybody_b200.model_pack import asset_path
+    from oracle.oracle import OracleEnv
+    M = load_model(asset_path("walk_imitation"))
+    d = np.load(rows_path)
+    rows, off, ln = d["rows"], d["offsets"], d["lengths"]
+    c = wid % len(off)
+    r = rows[off[c]:off[c] + ln[c]].astype(np.float64)
+    nj, ns = int(M["n_mocap_joints"]), int(M["n_mocap_sites"])
+    o = OracleEnv(M)
+    o.set_clip(r[:, :7 + nj], r[:, 7 + nj:13 + 2 * nj], r[:, 13 + 2 * nj:13 + 2 * nj + 3 * ns], r[:, 13 + 2 * nj + 3 * ns:])
+    o.env_reset()
+    rng = np.random.RandomState(wid)
+    acts = rng.uniform(M["action_min"], M["action_max"], (steps, int(M["action_dim"])))
+    t0 = time.perf_counter()
+    for k in range(steps):
+        o.env_step(acts[k])
+    return time.perf_counter() - t0
+
+
+def cpu_throughput(cores: int, steps_per_core: int, table):
+    """env-steps/s of the float64 port on `cores` processes (one env each, same workload)."""
+    import multiprocessing as mp
+    import tempfile
+    from oracle import oracle as O
+    O.build()
+    path = os.path.join(tempfile.gettempdir(), f"flyb_bench_clips_{os.getpid()}.npz")
+    np.savez(path, rows=table[0][:table[2][0] * min(len(table[1]), 8)], offsets=table[1][:8], lengths=table[2][:8])
+    if cores == 1:
+        el = [_cpu_worker((0, steps_per_core, path))]
+    else:
+        with mp.get_context("spawn").Pool(cores) as pool:
+            el = pool.map(_cpu_worker, [(i, steps_per_core, path) for i in range(cores)])
+    os.remove(path)
+    dt = max(el)   # stepping only: process start-up and model load are outside the timed region
+    return cores * steps_per_core / dt, dt
+
+
+def run_reference(args):
+    """The reference arm: the CPU algorithm on all host cores, each step a bounded sample of the workload."""
+    rank = int(os.environ.get("RANK", 0))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    M, table = _model_and_clips(8, 600)
+    per_core = 20   # control steps per core per "step" (about 0.3 s of CPU work per core)
+    for _ in range(args.warmup):
+        cpu_throughput(cores, 5, table)
+    vals, ms = [], []
+    for _ in range(args.steps):
+        v, dt = cpu_throughput(cores, per_core, table)
+        vals.append(v); ms.append(dt * 1e3)
+    v = float(np.mean(vals))
+    sample = f"{cores} oracle envs x {per_core} control steps per step (same model, clips and action distribution)"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": "env-steps/s", "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": float(np.mean(ms)), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "walk_imitation, synthetic reference clips, U(ctrlrange) random actions; CPU port of the reference algorithm (MuJoCo/dm_control not installable here)"},
+        "cpu_baseline": {"value": v, "unit": "env-steps/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def run_gpu(args):
+    import torch
+    import torch.distributed as dist
+    from flybody_b200.engine import Engine, INFO_LAUNCHES, INFO_GRID, INFO_SMEM_BYTES
+    from flybody_b200.sharding import shard_range, reduce_stats
+    rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    N = args.envs
+    lo, hi = shard_range(N * world, rank, world)
+    M, table = _model_and_clips(args.clips, 600)
+    eng = Engine(M, N, local, seed=args.seed, env_offset=lo)
+    eng.load_clips(*table)
+    A, O = eng.action_dim, eng.obs_dim
+    obs = torch.zeros((N, O), device=dev); rew = torch.zeros(N, device=dev); disc = torch.zeros(N, device=dev)
+    st = torch.zeros(N, dtype=torch.int32, device=dev)
+    amin = torch.as_tensor(np.asarray(M["action_min"], np.float32), device=dev)
+    amax = torch.as_tensor(np.asarray(M["action_max"], np.float32), device=dev)
+    gen = torch.Generator(device=dev); gen.manual_seed(1234 + rank)
+    pool = [amin + torch.rand((N, A), device=dev, generator=gen) * (amax - amin) for _ in range(8)]
+    flush = torch.empty(256 * 1024 * 1024 // 4, device=dev)   # > 126 MB L2
+    stream = torch.cuda.current_stream(dev).cuda_stream
+
+    def barrier():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    def gmax(x):
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    eng.reset_ptr(0, obs.data_ptr(), st.data_ptr(), stream)
+    for k in range(args.warmup):
+        eng.step_ptr(pool[k % 8].data_ptr(), obs.data_ptr(), rew.data_ptr(), disc.data_ptr(), st.data_ptr(), stream)
+    # ---- device-resident timing: CUDA events on the launching stream, L2 flushed between timed steps
+    l0 = eng.info(INFO_LAUNCHES)
+    clocks = ClockSampler(local) if rank == 0 else None
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    barrier()
+    for k in range(args.steps):
+        flush.fill_(float(k))
+        ev[k][0].record()
+        eng.step_ptr(pool[(k + args.warmup) % 8].data_ptr(), obs.data_ptr(), rew.data_ptr(), disc.data_ptr(), st.data_ptr(), stream)
+        ev[k][1].record()
+    barrier()
+    kernel_ms = [a.elapsed_time(b) for a, b in ev]
+    total_ms = gmax(sum(kernel_ms))
+    launches = eng.info(INFO_LAUNCHES) - l0
+    value = N * world * args.steps / (total_ms * 1e-3)
+    finite = bool(torch.isfinite(obs).all().item())
+    # ---- end to end through the host-pointer C-ABI call
+    h_act = [p.cpu().numpy() for p in pool]
+    out = (np.zeros((N, O), np.float32), np.zeros(N, np.float32), np.zeros(N, np.float32), np.zeros(N, np.int32))
+    for k in range(2):
+        eng.step_host(h_act[k], out)
+    barrier()
+    t0 = time.perf_counter()
+    for k in range(args.steps):
+        eng.step_host(h_act[k % 8], out)
+    torch.cuda.synchronize(dev)
+    e2e_s = gmax(time.perf_counter() - t0)
+    clk = clocks.stop() if clocks else None
+    e2e = N * world * args.steps / e2e_s
+    stats = reduce_stats(eng.episode_stats(), dev)
+    if rank == 0:
+        peak, how = _peaks()
+        per_launch_s = float(np.mean(kernel_ms)) * 1e-3
+        achieved = ALGO_BYTES["walk_imitation"] * N / per_launch_s / 1e9
+        traffic = None
+        tp = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tp):
+            traffic = json.load(open(tp)).get("dram_bytes_per_launch")
+        cpu_steps = args.cpu_steps
+        cpu_v, cpu_dt = cpu_throughput(1, cpu_steps, table)
+        print(json.dumps({
+            "metric": METRIC, "value": value, "unit": "env-steps/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": {"workload": "walk_imitation (BASELINE.json configs[1]): 16384 envs per GPU, 10 physics substeps per control step, "
+                                   f"{args.clips} synthetic reference clips x 600 steps, U(ctrlrange) random actions, auto-reset",
+                       "envs_per_gpu": N, "global_envs": N * world, "l2": "256 MB buffer written between timed steps",
+                       "grid": eng.info(INFO_GRID), "smem_bytes_per_block": eng.info(INFO_SMEM_BYTES), "outputs_finite": finite},
+            "clocks": clk, "gpu_launches": int(launches),
+            "e2e": {"value": e2e, "unit": "env-steps/s", "h2d_bytes_per_step": N * A * 4, "d2h_bytes_per_step": N * (O + 3) * 4},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                         "peak_source": how, "kernel": "fly_step_kernel", "algorithmic_bytes_per_env_step": ALGO_BYTES["walk_imitation"],
+                         "note": "HBM is the contract roofline; the kernel is FP32-issue/latency bound (DESIGN.md)"},
+            "cpu_baseline": {"value": cpu_v, "unit": "env-steps/s", "cores": 1, "kind": "port",
+                             "sample": f"{cpu_steps} control steps of one env, float64 CPU restatement (oracle/), {cpu_dt:.1f} s"},
+            "episode_stats": stats,
+        }))
+    eng.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="flyb", choices=["flyb", "reference"])
+    ap.add_argument("--envs", type=int, default=ENVS_PER_GPU, help="envs per GPU")
+    ap.add_argument("--clips", type=int, default=64)
+    ap.add_argument("--seed", type=int, default=0)
+    ap.add_argument("--cpu-steps", type=int, default=600)
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "flyb" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_gpu(args)
+
+
+if __name__ == "__main__":
+    main()

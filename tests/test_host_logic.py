@@ -1,0 +1,71 @@
+"""Host-side logic that needs no GPU: observation layout, clip packing, sharding arithmetic, stats reduction (gloo)."""
+import os
+
+import numpy as np
+
+
+def test_observation_layout_matches_survey(models):
+    from flybody_b200.fly_envs import observation_layout
+    lay = observation_layout(models["walk_imitation"])
+    dims = {k: int(np.prod(s)) for k, (o, s) in lay.items()}
+    assert sum(dims.values()) == 741 == int(models["walk_imitation"]["obs_dim"])
+    assert lay["walker/ref_displacement"][1] == (65, 3) and lay["walker/ref_root_quat"][1] == (65, 4)
+    assert list(lay) == sorted(lay)  # dm_control orders observation keys
+    assert sum(int(np.prod(s)) for _, s in observation_layout(models["walk_on_ball"]).values()) == 289
+    assert "walker/ball_qvel" in observation_layout(models["walk_on_ball"])
+    offs = sorted((o, int(np.prod(s))) for o, s in lay.values())
+    assert all(offs[i][0] + offs[i][1] == offs[i + 1][0] for i in range(len(offs) - 1))  # blocks tile the row
+
+
+def test_action_spec_order(models):
+    M = models["walk_imitation"]
+    assert int(M["action_dim"]) == 59 and (M["action_min"][:6] == 0).all() and (M["action_max"][:6] == 1).all()
+    assert sorted(int(i) for i in M["ctrl_action"]) == list(range(59))
+
+
+def test_clip_packing_roundtrip(models):
+    from flybody_b200 import clips as C
+    M = models["walk_imitation"]
+    cl = [C.synth_walk_clip(M, T=20 + 3 * i, seed=i, features=(i == 0)) for i in range(3)]
+    for c in cl[1:]:
+        c["root2site"] = np.zeros((c["qpos"].shape[0], 6, 3)); c["joint_quat"] = np.zeros((c["qpos"].shape[0], 66, 4))
+    rows, off, ln = C.pack_clips(M, cl)
+    assert rows.shape == (20 + 23 + 26, C.clip_row_width(M)) and off.tolist() == [0, 20, 43] and ln.tolist() == [20, 23, 26]
+    np.testing.assert_allclose(rows[off[1]:off[1] + ln[1], :73], cl[1]["qpos"], rtol=1e-6, atol=1e-7)
+    r2s, jq = C.batch_walker_features(M, _full_qpos(M, cl[0]["qpos"]))
+    np.testing.assert_allclose(r2s, cl[0]["root2site"], atol=1e-12)
+    np.testing.assert_allclose(jq, cl[0]["joint_quat"], atol=1e-12)
+
+
+def _full_qpos(M, q):
+    full = np.tile(np.asarray(M["qpos_reset"], np.float64), (q.shape[0], 1))
+    full[:, :7] = q[:, :7]
+    for i, j in enumerate(M["mocap_joint"]):
+        full[:, int(M["jnt_qposadr"][j])] = q[:, 7 + i]
+    return full
+
+
+def _worker(rank, world, port, q):
+    import torch.distributed as dist
+    import torch
+    os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from flybody_b200.sharding import shard_range, reduce_stats
+    lo, hi = shard_range(10, rank, world)
+    stats = dict(return_sum=float(rank + 1), length_sum=10.0 * (rank + 1), fatal=1.0, episodes=2.0)
+    out = reduce_stats(stats, torch.device("cpu"))
+    q.put((rank, lo, hi, out))
+    dist.destroy_process_group()
+
+
+def test_sharding_and_stats_allreduce_world2():
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    ps = [ctx.Process(target=_worker, args=(r, 2, 29512, q)) for r in range(2)]
+    [p.start() for p in ps]
+    res = sorted(q.get(timeout=120) for _ in ps)
+    [p.join() for p in ps]
+    assert (res[0][1], res[0][2]) == (0, 5) and (res[1][1], res[1][2]) == (5, 10)
+    for r in res:
+        assert r[3] == dict(return_sum=3.0, length_sum=30.0, fatal=2.0, episodes=4.0)
