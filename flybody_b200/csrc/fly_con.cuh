@@ -54,7 +54,7 @@ FLY_INL void fly_finish_row(const DModel<T>& m, const Ws<T>& w, int r, const T* 
     K = T(1) / fmax_(minval<T>(), dmax * dmax * sr0 * sr0 * sr1 * sr1);
     B = T(2) / fmax_(minval<T>(), dmax * sr0);
   } else { K = -sr0 / fmax_(minval<T>(), dmax * dmax); B = -sr1 / fmax_(minval<T>(), dmax); }
-  w.efc_K[r] = K; w.efc_B[r] = B; w.efc_imp[r] = imp;
+  w.efc_K0[r] = K; w.efc_B[r] = B; w.efc_imp[r] = imp;
   w.efc_R[r] = fmax_(minval<T>(), (1 - imp) * w.efc_diag[r] / imp);
 }
 
@@ -83,7 +83,7 @@ FLY_FN void fly_make_constraint(const DModel<T>& m, const Ws<T>& w) {
     w.efc_margin[r] = 0;
     w.efc_diag[r] = m.dof_invweight0[d];
     fly_finish_row(m, w, r, m.jnt_solref + 2 * j, m.jnt_solimp + 5 * j);
-    w.grp_type[r] = FLY_CT_LIMIT; w.grp_row[r] = r; w.grp_con[r] = j;
+    w.grp_type[r] = FLY_CT_LIMIT; w.grp_row[r] = r; w.grp_con[r] = j; w.efc_g[r] = r;
   }
   /* contact rows: addresses are assigned in contact order by one lane */
   FLY_LANE0 {
@@ -101,11 +101,12 @@ FLY_FN void fly_make_constraint(const DModel<T>& m, const Ws<T>& w) {
       w.con_efc[ci] = r;
       w.grp_type[ngrp] = dim == 1 ? FLY_CT_CONTACT1 : FLY_CT_ELLIPTIC;
       w.grp_row[ngrp] = r; w.grp_con[ngrp] = ci;
-      ngrp++;
       for (int k = 0; k < dim; k++) {
+        w.efc_g[r + k] = ngrp;
         w.efc_xid[r + k] = cross ? nx : -1;
         if (cross) { w.x_row[nx] = r + k; nx++; }
       }
+      ngrp++;
       r += dim;
     }
     w.counts[FLY_C_NEFC] = r; w.counts[FLY_C_NLIMIT] = nlimit; w.counts[FLY_C_NGRP] = ngrp;
@@ -155,7 +156,7 @@ FLY_FN void fly_make_constraint(const DModel<T>& m, const Ws<T>& w) {
       w.efc_R[r + 1] = w.efc_R[r] / fmax_(minval<T>(), m.impratio);
       for (int k = 2; k < dim; k++) w.efc_R[r + k] = w.efc_R[r + 1];
       w.con_mu[ci] = w.con_fric[ci] * sqrt(w.efc_R[r + 1] / w.efc_R[r]);
-      for (int k = 1; k < dim; k++) { w.efc_K[r + k] = 0; w.efc_B[r + k] = w.efc_B[r]; w.efc_imp[r + k] = w.efc_imp[r]; }
+      for (int k = 1; k < dim; k++) { w.efc_K0[r + k] = 0; w.efc_B[r + k] = w.efc_B[r]; w.efc_imp[r + k] = w.efc_imp[r]; }
     }
   }
   FLY_SYNC();

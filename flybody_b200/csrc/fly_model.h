@@ -19,10 +19,10 @@
 
 #define FLY_MAXCHAIN 24   /* longest dof chain root->leaf in the Hessian tree (walk: 6 + 14 abdomen = 20) */
 #define FLY_MAXCON 64     /* detected contacts per env (gap-band contacts included) */
-#define FLY_MAXEFC 192    /* constraint rows per env */
-#define FLY_MAXGRP 160    /* constraint groups (limit row | condim-1 contact | 3-row elliptic contact) */
+#define FLY_MAXEFC 160    /* constraint rows per env */
+#define FLY_MAXGRP 144    /* constraint groups (limit row | condim-1 contact | 3-row elliptic contact) */
 #define FLY_MAXCAND 256   /* narrow-phase candidates after the bounding-sphere test */
-#define FLY_MAXCROSS 16   /* two-chain (cross-branch) rows kept in the Hessian correction */
+#define FLY_MAXCROSS 24   /* two-chain (cross-branch) contact rows */
 #define FLY_HEAVY 24      /* dofs with more descendants than this are reduced warp-cooperatively */
 
 enum { FLY_OPT_NOCONTACT = 1, FLY_OPT_NOLIMIT = 2, FLY_OPT_NOFLUID = 4, FLY_OPT_NONOSLIP = 8,

@@ -1,61 +1,66 @@
 /* fly_solver.cuh - constraint solve (m11) for one environment: primal Newton with elliptic cones and exact
  * line search, followed by the noslip Gauss-Seidel pass.
  *
- * Same iteration as the float64 oracle (and as MuJoCo's Newton solver), different linear algebra: the
- * Hessian H = M + J^T D J is kept in the TREE-SPARSE layout of M.  A contact row whose support is one dof
- * chain (everything that touches the floor or the ball, and self-contacts along one limb) only adds to
- * entries M already has, so H factorises with the same fill-free L^T D L as M.  The few rows that couple
- * two branches (fly-on-fly contacts) enter through a small Woodbury correction.  The Hessian only steers the
- * search direction; cost and gradient are exact, so the optimum is the oracle's. */
+ * Same Newton iteration as the float64 oracle (and as MuJoCo's Newton solver), but carried out in CONSTRAINT
+ * SPACE.  With M = L^T D L, u = D^1/2 L qacc and y_r = D^-1/2 L^-T J_r^T (a chain-local half solve, so y_r is
+ * as sparse as J_r) the problem reads  min 1/2 |u - u_s|^2 + sum_r s_r(y_r . u - aref_r):  the Hessian is
+ * I + Y^T W Y, identity plus rank nefc, and its inverse needs only the small dense matrix I + W A with
+ * A = Y Y^T = J M^-1 J^T (nefc x nefc, typically ~10-20).  Every iterate is kept as coordinates (theta, c) of
+ * qacc - qacc_smooth = theta (qacc_warmstart - qacc_smooth) + M^-1 J^T c, so one Newton iteration costs two
+ * mat-vecs with A, one small LU solve and the line search - no nv-sized factorisation.  M is factorised once
+ * per physics step.  The search direction equals -H^-1 grad of the primal formulation exactly (push-through
+ * identity); the only deliberate deviation is the norm used to scale the line-search tolerance (see below). */
 #ifndef FLY_SOLVER_CUH_
 #define FLY_SOLVER_CUH_
 #include "fly_con.cuh"
 
 /* forces, states, cone Hessians for the residual `jar`; returns the constraint cost */
+typedef double S;  /* accumulator type of the constraint-space iterate (see FLY_WS_DBL) */
+
 template <class T>
-FLY_INL T fly_update_constraint(const DModel<T>& m, const Ws<T>& w, const T* jar, bool write, bool cone_hess) {
-  T cost = 0;
+FLY_INL S fly_update_constraint(const DModel<T>& m, const Ws<T>& w, const S* jar, bool write, bool cone_hess) {
+  S cost = 0;
   FLY_FOR(g, w.counts[FLY_C_NGRP]) {
     const int r = w.grp_row[g];
     if (w.grp_type[g] != FLY_CT_ELLIPTIC) {
-      const T x = jar[r], D = w.efc_D[r];
-      if (x < 0) { cost += T(0.5) * D * x * x; if (write) { w.efc_force[r] = -D * x; w.efc_state[r] = FLY_ST_QUADRATIC; } }
+      const S x = jar[r], D = w.efc_D[r];
+      if (x < 0) { cost += S(0.5) * D * x * x; if (write) { w.efc_force[r] = (T)(-D * x); w.efc_state[r] = FLY_ST_QUADRATIC; } }
       else if (write) { w.efc_force[r] = 0; w.efc_state[r] = FLY_ST_SATISFIED; }
       continue;
     }
     const int ci = w.grp_con[g];
-    const T mu = w.con_mu[ci], f0 = w.con_fric[ci];
-    const T fr[3] = {mu, f0, f0};
-    T U[3], T2 = 0;
+    const S mu = w.con_mu[ci], f0 = w.con_fric[ci];
+    const S fr[3] = {mu, f0, f0};
+    S U[3], T2 = 0;
     for (int k = 0; k < 3; k++) U[k] = jar[r + k] * fr[k];
     T2 = U[1] * U[1] + U[2] * U[2];
-    const T N = U[0], Tn = sqrt(T2);
+    const S N = U[0], Tn = sqrt(T2);
     if (N >= mu * Tn || (Tn <= 0 && N >= 0)) {
       if (write) for (int k = 0; k < 3; k++) { w.efc_force[r + k] = 0; w.efc_state[r + k] = FLY_ST_SATISFIED; }
     } else if (mu * N + Tn <= 0 || (Tn <= 0 && N < 0)) {
       for (int k = 0; k < 3; k++) {
-        const T D = w.efc_D[r + k], x = jar[r + k];
-        cost += T(0.5) * D * x * x;
-        if (write) { w.efc_force[r + k] = -D * x; w.efc_state[r + k] = FLY_ST_QUADRATIC; }
+        const S D = w.efc_D[r + k], x = jar[r + k];
+        cost += S(0.5) * D * x * x;
+        if (write) { w.efc_force[r + k] = (T)(-D * x); w.efc_state[r + k] = FLY_ST_QUADRATIC; }
       }
     } else {
-      const T Dm = w.efc_D[r] / fmax_(minval<T>(), mu * mu * (1 + mu * mu));
-      const T NT = N - mu * Tn;
-      cost += T(0.5) * Dm * NT * NT;
+      const S Dm = w.efc_D[r] / fmax_(minval<S>(), mu * mu * (1 + mu * mu));
+      const S NT = N - mu * Tn;
+      cost += S(0.5) * Dm * NT * NT;
       if (write) {
-        w.efc_force[r] = -Dm * NT * mu;
-        for (int k = 1; k < 3; k++) w.efc_force[r + k] = Dm * NT * mu / Tn * U[k] * fr[k];
+        w.efc_force[r] = (T)(-Dm * NT * mu);
+        for (int k = 1; k < 3; k++) w.efc_force[r + k] = (T)(Dm * NT * mu / Tn * U[k] * fr[k]);
         for (int k = 0; k < 3; k++) w.efc_state[r + k] = FLY_ST_CONE;
       }
       if (cone_hess) {
         T* h = w.con_hc + 9 * ci;
-        T Hu[9];
+        S Hu[9];
         Hu[0] = 1;
         for (int i = 1; i < 3; i++) Hu[i] = Hu[3 * i] = -mu * U[i] / Tn;
         for (int i = 1; i < 3; i++)
           for (int j = 1; j < 3; j++)
-            Hu[3 * i + j] = mu * N / (Tn * Tn * Tn) * U[i] * U[j] + (i == j ? mu * mu - mu * N / Tn : T(0));
-        for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) h[3 * i + j] = Dm * fr[i] * fr[j] * Hu[3 * i + j];
+            Hu[3 * i + j] = mu * N / (Tn * Tn * Tn) * U[i] * U[j] + (i == j ? mu * mu - mu * N / Tn : S(0));
+        for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) h[3 * i + j] = (T)(Dm * fr[i] * fr[j] * Hu[3 * i + j]);
       }
     }
   }
@@ -64,252 +69,41 @@ FLY_INL T fly_update_constraint(const DModel<T>& m, const Ws<T>& w, const T* jar
   return cost;
 }
 
-/* 1/2 (Ma - qfrc_smooth) . (qacc - qacc_smooth) */
-template <class T>
-FLY_INL T fly_gauss(const DModel<T>& m, const Ws<T>& w) {
-  T s = 0;
-  FLY_FOR(d, m.nv) s += T(0.5) * (w.sMa[d] - w.qfrc_smooth[d]) * (w.qacc[d] - w.qacc_smooth[d]);
-  return warp_sum(s);
-}
-
 /* phi(alpha) along the search direction: value and first two derivatives */
 template <class T>
-FLY_INL void fly_ls_eval(const DModel<T>& m, const Ws<T>& w, T alpha, const T* quad, T* out) {
-  T c = 0, d1 = 0, d2 = 0;
+FLY_INL void fly_ls_eval(const DModel<T>& m, const Ws<T>& w, S alpha, const S* quad, S* out) {
+  S c = 0, d1 = 0, d2 = 0;
   FLY_FOR(g, w.counts[FLY_C_NGRP]) {
     const int r = w.grp_row[g];
     if (w.grp_type[g] != FLY_CT_ELLIPTIC) {
-      const T jv = w.efc_jv[r], x = w.efc_jar[r] + alpha * jv;
-      if (x < 0) { const T D = w.efc_D[r]; c += T(0.5) * D * x * x; d1 += D * x * jv; d2 += D * jv * jv; }
+      const S jv = w.efc_jv[r], x = w.efc_jar[r] + alpha * jv;
+      if (x < 0) { const S D = w.efc_D[r]; c += S(0.5) * D * x * x; d1 += D * x * jv; d2 += D * jv * jv; }
       continue;
     }
     const int ci = w.grp_con[g];
-    const T mu = w.con_mu[ci], f0 = w.con_fric[ci];
-    const T fr[3] = {mu, f0, f0};
-    T x[3], v[3];
+    const S mu = w.con_mu[ci], f0 = w.con_fric[ci];
+    const S fr[3] = {mu, f0, f0};
+    S x[3], v[3];
     for (int k = 0; k < 3; k++) { x[k] = (w.efc_jar[r + k] + alpha * w.efc_jv[r + k]) * fr[k]; v[k] = w.efc_jv[r + k] * fr[k]; }
-    const T T2 = x[1] * x[1] + x[2] * x[2], TV = x[1] * v[1] + x[2] * v[2], VV = v[1] * v[1] + v[2] * v[2];
-    const T N = x[0], Tn = sqrt(T2);
+    const S T2 = x[1] * x[1] + x[2] * x[2], TV = x[1] * v[1] + x[2] * v[2], VV = v[1] * v[1] + v[2] * v[2];
+    const S N = x[0], Tn = sqrt(T2);
     if (N >= mu * Tn || (Tn <= 0 && N >= 0)) {
     } else if (mu * N + Tn <= 0 || (Tn <= 0 && N < 0)) {
       for (int k = 0; k < 3; k++) {
-        const T D = w.efc_D[r + k], jv = w.efc_jv[r + k], xx = w.efc_jar[r + k] + alpha * jv;
-        c += T(0.5) * D * xx * xx; d1 += D * xx * jv; d2 += D * jv * jv;
+        const S D = w.efc_D[r + k], jv = w.efc_jv[r + k], xx = w.efc_jar[r + k] + alpha * jv;
+        c += S(0.5) * D * xx * xx; d1 += D * xx * jv; d2 += D * jv * jv;
       }
     } else {
-      const T Dm = w.efc_D[r] / fmax_(minval<T>(), mu * mu * (1 + mu * mu));
-      const T NT = N - mu * Tn, N1 = v[0], T1 = TV / Tn, Tdd = VV / Tn - T1 * T1 / Tn;
-      const T g1 = N1 - mu * T1;
-      c += T(0.5) * Dm * NT * NT; d1 += Dm * NT * g1; d2 += Dm * (g1 * g1 - NT * mu * Tdd);
+      const S Dm = w.efc_D[r] / fmax_(minval<S>(), mu * mu * (1 + mu * mu));
+      const S NT = N - mu * Tn, N1 = v[0], T1 = TV / Tn, Tdd = VV / Tn - T1 * T1 / Tn;
+      const S g1 = N1 - mu * T1;
+      c += S(0.5) * Dm * NT * NT; d1 += Dm * NT * g1; d2 += Dm * (g1 * g1 - NT * mu * Tdd);
     }
   }
   c = warp_sum(c); d1 = warp_sum(d1); d2 = warp_sum(d2);
   out[0] = c + quad[0] + alpha * quad[1] + alpha * alpha * quad[2];
   out[1] = d1 + quad[1] + 2 * alpha * quad[2];
   out[2] = d2 + 2 * quad[2];
-}
-
-template <class T>
-FLY_FN T fly_line_search(const DModel<T>& m, const Ws<T>& w, T gauss) {
-  T snorm = 0, q1 = 0, q2 = 0;
-  FLY_FOR(d, m.nv) {
-    const T s = w.ssearch[d];
-    snorm += s * s;
-    q1 += s * (w.sMa[d] - w.qfrc_smooth[d]);
-    q2 += T(0.5) * s * w.sMv[d];
-  }
-  snorm = sqrt(warp_sum(snorm)); q1 = warp_sum(q1); q2 = warp_sum(q2);
-  if (snorm < minval<T>()) return 0;
-  const T quad[3] = {gauss, q1, q2};
-  const T gtol = m.tolerance * m.ls_tolerance * snorm * m.meaninertia * T(m.nv > 1 ? m.nv : 1);
-  T p[3], lo = 0, hi = -1, alpha = 0;
-  fly_ls_eval(m, w, T(0), quad, p);
-  if (p[1] >= 0) return 0;
-  for (int it = 0; it < m.opt_ls_iterations; it++) {
-    const T step = (p[2] > minval<T>()) ? -p[1] / p[2] : T(0);
-    T next = alpha + step;
-    if (hi < 0) { if (!(next > lo)) next = alpha > 0 ? 2 * alpha : T(1); }
-    else if (!(next > lo && next < hi)) next = T(0.5) * (lo + hi);
-    alpha = next;
-    fly_ls_eval(m, w, alpha, quad, p);
-    if (fabs_(p[1]) < gtol) break;
-    if (p[1] < 0) lo = alpha; else hi = alpha;
-  }
-  return alpha;
-}
-
-/* H <- M + J^T D J (+ cone blocks) for single-chain rows, in the tree-sparse layout; returns the number of
- * active two-chain rows, listed in x_z-adjacent scratch (w.ns_fr reused as the active list) */
-template <class T>
-FLY_FN int fly_hessian(const DModel<T>& m, const Ws<T>& w) {
-  const int ngrp = w.counts[FLY_C_NGRP], nlimit = w.counts[FLY_C_NLIMIT];
-  FLY_FOR(e, m.nM) w.qH[e] = w.qM[e];
-  FLY_SYNC();
-  FLY_FOR(r, nlimit) if (w.efc_state[r] == FLY_ST_QUADRATIC) w.qH[m.madr[w.efc_start[r]]] += w.efc_D[r];
-  FLY_SYNC();
-  int nact = 0;
-  for (int g = nlimit; g < ngrp; g++) {
-    const int r = w.grp_row[g], st = w.efc_state[r];
-    if (st == FLY_ST_SATISFIED) continue;
-    const int dim = w.grp_type[g] == FLY_CT_ELLIPTIC ? 3 : 1;
-    if (w.efc_xid[r] >= 0) {   /* two-chain rows go to the Woodbury list (diagonal weights) */
-      for (int k = 0; k < dim; k++) {
-        const T wgt = st == FLY_ST_QUADRATIC ? w.efc_D[r + k] : w.con_hc[9 * w.grp_con[g] + 4 * k];
-        if (nact < FLY_MAXCROSS && wgt > 0) {
-          FLY_LANE0 { w.ns_fr[nact] = r + k; w.x_z[nact] = wgt; }
-          nact++;
-        }
-      }
-      continue;
-    }
-    const int s = w.efc_start[r], a = m.madr[s], len = m.hdepth[s] + 1;
-    const T* J = w.efc_J + r * FLY_MAXCHAIN;
-    const T* hc = w.con_hc + 9 * w.grp_con[g];
-    FLY_FOR(e, len * (len + 1) / 2) {
-      const int pa = m.tri_a[e], pb = m.tri_b[e];   /* pa <= pb: row = deeper dof, column = its ancestor */
-      T v;
-      if (dim == 1) v = w.efc_D[r] * J[pa] * J[pb];
-      else if (st == FLY_ST_QUADRATIC)
-        v = w.efc_D[r] * J[pa] * J[pb] + w.efc_D[r + 1] * J[FLY_MAXCHAIN + pa] * J[FLY_MAXCHAIN + pb]
-            + w.efc_D[r + 2] * J[2 * FLY_MAXCHAIN + pa] * J[2 * FLY_MAXCHAIN + pb];
-      else {
-        v = 0;
-        for (int k = 0; k < 3; k++) for (int l = 0; l < 3; l++) v += hc[3 * k + l] * J[k * FLY_MAXCHAIN + pa] * J[l * FLY_MAXCHAIN + pb];
-      }
-      w.qH[m.madr[m.mcol[a + pa]] + (pb - pa)] += v;
-    }
-    FLY_SYNC();
-  }
-  FLY_SYNC();
-  return nact;
-}
-
-/* x <- H^-1 x with H = Ht + sum_c wc Jc^T Jc ; Ht factorised in w.qH ; nact two-chain rows in w.ns_fr / w.x_z */
-template <class T>
-FLY_FN void fly_cross_prepare(const DModel<T>& m, const Ws<T>& w, int nact) {
-  for (int c = 0; c < nact; c++) {
-    const int r = w.ns_fr[c], xid = w.efc_xid[r];
-    T* y = w.x_dense + c * m.nv;
-    FLY_FOR(d, m.nv) y[d] = 0;
-    FLY_SYNC();
-    { const int s = w.efc_start[r], a = m.madr[s]; FLY_FOR(k, m.hdepth[s] + 1) y[m.mcol[a + k]] += w.efc_J[r * FLY_MAXCHAIN + k]; }
-    FLY_SYNC();
-    { const int s = w.x_start[xid], a = m.madr[s]; FLY_FOR(k, m.hdepth[s] + 1) y[m.mcol[a + k]] += w.x_J[xid * FLY_MAXCHAIN + k]; }
-    FLY_SYNC();
-    fly_solve(m, w.qH, y);
-  }
-  FLY_FOR(it, nact * nact) {
-    const int c = it / nact, c2 = it % nact;
-    w.x_S[c * FLY_MAXCROSS + c2] = fly_row_dot(m, w, w.ns_fr[c], w.x_dense + c2 * m.nv) + (c == c2 ? T(1) / w.x_z[c] : T(0));
-  }
-  FLY_SYNC();
-}
-template <class T>
-FLY_FN void fly_cross_apply(const DModel<T>& m, const Ws<T>& w, int nact, T* x) {
-  T* z = w.x_z + FLY_MAXCROSS / 2 * 0;  /* weights stay in x_z; rhs/solution go to obs_tmp-free scratch below */
-  T* rhs = w.efc_b;                      /* efc_b is free during the Newton phase */
-  FLY_FOR(c, nact) rhs[c] = fly_row_dot(m, w, w.ns_fr[c], x);
-  FLY_SYNC();
-  FLY_LANE0 {   /* small dense solve S u = rhs, Gaussian elimination with partial pivoting on a copy */
-    T* S = w.x_Y;  /* FLY_MAXCROSS * FLY_MAXCHAIN >= nact^2 scratch */
-    for (int i = 0; i < nact; i++) for (int j = 0; j < nact; j++) S[i * nact + j] = w.x_S[i * FLY_MAXCROSS + j];
-    for (int k = 0; k < nact; k++) {
-      int piv = k; T best = fabs_(S[k * nact + k]);
-      for (int i = k + 1; i < nact; i++) if (fabs_(S[i * nact + k]) > best) { best = fabs_(S[i * nact + k]); piv = i; }
-      if (piv != k) {
-        for (int j = 0; j < nact; j++) { T t = S[k * nact + j]; S[k * nact + j] = S[piv * nact + j]; S[piv * nact + j] = t; }
-        T t = rhs[k]; rhs[k] = rhs[piv]; rhs[piv] = t;
-      }
-      const T dk = S[k * nact + k];
-      if (fabs_(dk) < minval<T>()) continue;
-      for (int i = k + 1; i < nact; i++) {
-        const T f = S[i * nact + k] / dk;
-        for (int j = k; j < nact; j++) S[i * nact + j] -= f * S[k * nact + j];
-        rhs[i] -= f * rhs[k];
-      }
-    }
-    for (int k = nact - 1; k >= 0; k--) {
-      T s = rhs[k];
-      for (int j = k + 1; j < nact; j++) s -= S[k * nact + j] * rhs[j];
-      const T dk = S[k * nact + k];
-      rhs[k] = fabs_(dk) < minval<T>() ? T(0) : s / dk;
-    }
-  }
-  FLY_SYNC();
-  FLY_FOR(d, m.nv) {
-    T s = 0;
-    for (int c = 0; c < nact; c++) s += rhs[c] * w.x_dense[c * m.nv + d];
-    x[d] -= s;
-  }
-  FLY_SYNC();
-  (void)z;
-}
-
-template <class T>
-FLY_FN void fly_newton(const DModel<T>& m, const Ws<T>& w) {
-  const int nv = m.nv, nefc = w.counts[FLY_C_NEFC];
-  int niter = 0;
-  if (nefc == 0) {
-    FLY_FOR(d, nv) { w.qacc[d] = w.qacc_smooth[d]; w.qfrc_constraint[d] = 0; }
-    FLY_LANE0 w.counts[FLY_C_NITER] = 0;
-    FLY_SYNC();
-    return;
-  }
-  const T scale = T(1) / (m.meaninertia * T(nv > 1 ? nv : 1));
-  /* warm start: the better of qacc_warmstart and qacc_smooth */
-  FLY_FOR(d, nv) w.qacc[d] = w.warm[d];
-  FLY_SYNC();
-  FLY_FOR(r, nefc) w.efc_jar[r] = fly_row_dot(m, w, r, w.qacc) - w.efc_aref[r];
-  FLY_SYNC();
-  fly_mul_m(m, w.qM, w.sMa, w.qacc);
-  T cw = fly_update_constraint(m, w, w.efc_jar, false, false) + fly_gauss(m, w);
-  FLY_FOR(r, nefc) w.efc_jv[r] = fly_row_dot(m, w, r, w.qacc_smooth) - w.efc_aref[r];
-  FLY_SYNC();
-  const T cs = fly_update_constraint(m, w, w.efc_jv, false, false);
-  if ((m.flags & FLY_OPT_NOWARMSTART) || cs < cw) {
-    FLY_FOR(d, nv) w.qacc[d] = w.qacc_smooth[d];
-    FLY_FOR(r, nefc) w.efc_jar[r] = w.efc_jv[r];
-    FLY_SYNC();
-    fly_mul_m(m, w.qM, w.sMa, w.qacc);
-  }
-  T cost = fly_update_constraint(m, w, w.efc_jar, true, true);
-  T gauss = fly_gauss(m, w);
-  cost += gauss;
-  for (int it = 0;; it++) {
-    fly_jt_mul(m, w, w.qfrc_constraint, w.efc_force);
-    T gn = 0;
-    FLY_FOR(d, nv) { const T g = w.sMa[d] - w.qfrc_smooth[d] - w.qfrc_constraint[d]; w.sgrad[d] = g; gn += g * g; }
-    gn = warp_sum(gn);
-    FLY_SYNC();
-    if (it > 0 && scale * sqrt(gn) < m.tolerance) break;
-    if (it >= m.opt_iterations) break;
-    const int nact = fly_hessian(m, w);
-    fly_factor(m, w.qH);
-    FLY_FOR(d, nv) w.ssearch[d] = w.sgrad[d];
-    FLY_SYNC();
-    fly_solve(m, w.qH, w.ssearch);
-    if (nact) { fly_cross_prepare(m, w, nact); fly_cross_apply(m, w, nact, w.ssearch); }
-    FLY_FOR(d, nv) w.ssearch[d] = -w.ssearch[d];
-    FLY_SYNC();
-    fly_mul_m(m, w.qM, w.sMv, w.ssearch);
-    fly_j_mul(m, w, w.efc_jv, w.ssearch);
-    const T alpha = fly_line_search(m, w, gauss);
-    if (alpha == 0) break;
-    FLY_FOR(d, nv) { w.qacc[d] += alpha * w.ssearch[d]; w.sMa[d] += alpha * w.sMv[d]; }
-    FLY_FOR(r, nefc) w.efc_jar[r] += alpha * w.efc_jv[r];
-    FLY_SYNC();
-    const T old = cost;
-    cost = fly_update_constraint(m, w, w.efc_jar, true, true);
-    gauss = fly_gauss(m, w);
-    cost += gauss;
-    niter = it + 1;
-    if (scale * (old - cost) < m.tolerance) {
-      fly_jt_mul(m, w, w.qfrc_constraint, w.efc_force);
-      break;
-    }
-  }
-  FLY_LANE0 w.counts[FLY_C_NITER] = niter;
-  FLY_SYNC();
 }
 
 /* ---------------------------------------------------------------- noslip */
@@ -354,20 +148,81 @@ FLY_INL T fly_part_dot(const DModel<T>& m, int sa, const T* ya, int sb, const T*
   return s;
 }
 
+
+/* exact 1-D Newton line search along (efc_jar, efc_jv); quad = {gauss, q1, q2} of the quadratic part */
 template <class T>
-FLY_FN void fly_noslip(const DModel<T>& m, const Ws<T>& w) {
-  const int nefc = w.counts[FLY_C_NEFC], ngrp = w.counts[FLY_C_NGRP], nlimit = w.counts[FLY_C_NLIMIT];
-  const int nx = w.counts[FLY_C_NCROSSROW];
-  /* elliptic contacts, in contact order */
-  FLY_LANE0 {
-    int n3 = 0;
-    for (int g = nlimit; g < ngrp; g++) if (w.grp_type[g] == FLY_CT_ELLIPTIC) { w.ns_fr[n3] = w.grp_row[g]; w.ns_con[n3] = w.grp_con[g]; n3++; }
-    w.counts[FLY_C_NFR] = n3;
+FLY_FN S fly_line_search(const DModel<T>& m, const Ws<T>& w, const S* quad, S gtol) {
+  S p[3], lo = 0, hi = -1, alpha = 0;
+  fly_ls_eval(m, w, S(0), quad, p);
+  if (p[1] >= 0) return 0;
+  for (int it = 0; it < m.opt_ls_iterations; it++) {
+    const S step = (p[2] > minval<S>()) ? -p[1] / p[2] : S(0);
+    S next = alpha + step;
+    if (hi < 0) { if (!(next > lo)) next = alpha > 0 ? 2 * alpha : S(1); }
+    else if (!(next > lo && next < hi)) next = S(0.5) * (lo + hi);
+    alpha = next;
+    fly_ls_eval(m, w, alpha, quad, p);
+    if (fabs_(p[1]) < gtol) break;
+    if (p[1] < 0) lo = alpha; else hi = alpha;
   }
-  FLY_SYNC();
-  const int n3 = w.counts[FLY_C_NFR];
-  if (!n3) return;
-  /* A = J M^-1 J^T, friction rows only, through chain-local half solves */
+  return alpha;
+}
+
+/* (value, index) arg-max over lanes; ties go to the lowest index so that every lane agrees with a serial scan */
+template <class T>
+FLY_INL void warp_argmax(T& v, int& idx) {
+#ifdef FLY_GPU
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const T ov = __shfl_xor_sync(0xffffffffu, v, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
+    if (ov > v || (ov == v && oi < idx)) { v = ov; idx = oi; }
+  }
+#endif
+}
+
+/* dense n x n solve K x = rhs (in place, rhs <- x), LU with partial pivoting, one matrix row per lane */
+template <class T>
+FLY_FN void fly_lu_solve(T* K, int n, T* rhs) {
+  for (int k = 0; k < n; k++) {
+    T best = -1; int bi = k;
+    FLY_FOR(i, n - k) { const T v = fabs_(K[(k + i) * n + k]); if (v > best) { best = v; bi = k + i; } }
+    warp_argmax(best, bi);
+    if (bi != k) {
+      FLY_FOR(j, n) { const T t = K[k * n + j]; K[k * n + j] = K[bi * n + j]; K[bi * n + j] = t; }
+      FLY_SYNC();
+      FLY_LANE0 { const T t = rhs[k]; rhs[k] = rhs[bi]; rhs[bi] = t; }
+      FLY_SYNC();
+    }
+    const T pk = K[k * n + k];
+    if (fabs_(pk) >= minval<T>()) {
+      const T rk = rhs[k];
+      FLY_FOR(i, n - k - 1) {
+        const int r = k + 1 + i;
+        const T l = K[r * n + k] / pk;
+        if (l != 0) {
+          for (int j = k + 1; j < n; j++) K[r * n + j] -= l * K[k * n + j];
+          rhs[r] -= l * rk;
+        }
+      }
+    }
+    FLY_SYNC();
+  }
+  for (int k = n - 1; k >= 0; k--) {
+    T s = 0;
+    FLY_FOR(j, n - k - 1) s += K[k * n + k + 1 + j] * rhs[k + 1 + j];
+    s = warp_sum(s);
+    const T pk = K[k * n + k];
+    FLY_SYNC();
+    FLY_LANE0 rhs[k] = fabs_(pk) < minval<T>() ? T(0) : (rhs[k] - s) / pk;
+    FLY_SYNC();
+  }
+}
+
+/* Y = D^-1/2 L^-T J^T row by row (chain-local), then A = Y Y^T = J M^-1 J^T.  Needs qLD of this step. */
+template <class T>
+FLY_FN void fly_constraint_prepare(const DModel<T>& m, const Ws<T>& w) {
+  const int nefc = w.counts[FLY_C_NEFC], nx = w.counts[FLY_C_NCROSSROW];
   FLY_FOR(it, nefc + nx) {
     if (it < nefc) {
       const int s = w.efc_start[it], len = m.hdepth[s] + 1;
@@ -382,29 +237,183 @@ FLY_FN void fly_noslip(const DModel<T>& m, const Ws<T>& w) {
     }
   }
   FLY_SYNC();
-  FLY_FOR(it, 2 * n3 * nefc) {
-    const int fi = it / nefc, c = it % nefc, rf = w.ns_fr[fi >> 1] + 1 + (fi & 1);
-    const int sa = w.efc_start[rf], sb = w.efc_start[c], xa = w.efc_xid[rf], xb = w.efc_xid[c];
-    const T *ya = w.efc_Y + rf * FLY_MAXCHAIN, *yb = w.efc_Y + c * FLY_MAXCHAIN;
+  FLY_FOR(it, nefc * nefc) {
+    const int ra = it / nefc, rb = it % nefc;
+    const int sa = w.efc_start[ra], sb = w.efc_start[rb], xa = w.efc_xid[ra], xb = w.efc_xid[rb];
+    const T *ya = w.efc_Y + ra * FLY_MAXCHAIN, *yb = w.efc_Y + rb * FLY_MAXCHAIN;
     T s = fly_part_dot(m, sa, ya, sb, yb);
     if (xa >= 0) s += fly_part_dot(m, w.x_start[xa], w.x_Y + xa * FLY_MAXCHAIN, sb, yb);
     if (xb >= 0) s += fly_part_dot(m, sa, ya, w.x_start[xb], w.x_Y + xb * FLY_MAXCHAIN);
     if (xa >= 0 && xb >= 0) s += fly_part_dot(m, w.x_start[xa], w.x_Y + xa * FLY_MAXCHAIN, w.x_start[xb], w.x_Y + xb * FLY_MAXCHAIN);
-    w.ns_A[it] = s;
+    w.efc_A[it] = s;
   }
-  FLY_FOR(r, nefc) w.efc_b[r] = fly_row_dot(m, w, r, w.qacc_smooth) - w.efc_aref[r];
   FLY_SYNC();
+}
+
+/* out <- A v (dense nefc x nefc) */
+template <class T>
+FLY_INL void fly_a_mul(const Ws<T>& w, int nefc, S* out, const S* v) {
+  FLY_FOR(r, nefc) {
+    const T* a = w.efc_A + r * nefc;
+    S s = 0;
+    for (int k = 0; k < nefc; k++) s += a[k] * v[k];
+    out[r] = s;
+  }
+  FLY_SYNC();
+}
+
+template <class T>
+FLY_FN void fly_newton(const DModel<T>& m, const Ws<T>& w) {
+  const int nv = m.nv, nefc = w.counts[FLY_C_NEFC];
+  int niter = 0;
+  if (nefc == 0) {
+    FLY_FOR(d, nv) { w.qacc[d] = w.qacc_smooth[d]; w.qfrc_constraint[d] = 0; }
+    FLY_LANE0 w.counts[FLY_C_NITER] = 0;
+    FLY_SYNC();
+    return;
+  }
+  const S scale = S(1) / ((S)m.meaninertia * S(nv > 1 ? nv : 1));
+  S *bs = w.efc_b, *b0 = w.efc_b0, *c = w.efc_c, *cp = w.efc_cp, *Ac = w.efc_Ac, *Acp = w.efc_Acp, *h = w.efc_h;
+  S *jar = w.efc_jar, *jv = w.efc_jv;
+  T* f = w.efc_force;
+  T* dvec = w.ssearch;  /* qacc_warmstart - qacc_smooth */
+  T* m0 = w.sMa;        /* M (qacc_warmstart - qacc_smooth) */
+  /* warm start: the better of qacc_warmstart and qacc_smooth */
+  FLY_FOR(d, nv) dvec[d] = w.warm[d] - w.qacc_smooth[d];
+  FLY_SYNC();
+  fly_mul_m(m, w.qM, m0, dvec);
+  S dd = 0;
+  FLY_FOR(d, nv) dd += (S)dvec[d] * (S)m0[d];
+  dd = warp_sum(dd);
+  FLY_FOR(r, nefc) {
+    bs[r] = (S)fly_row_dot(m, w, r, w.qacc_smooth) - (S)w.efc_aref[r];
+    b0[r] = fly_row_dot(m, w, r, dvec);
+    jar[r] = bs[r] + b0[r];
+    c[r] = 0; Ac[r] = 0;
+  }
+  FLY_SYNC();
+  const S cw = fly_update_constraint(m, w, jar, false, false) + S(0.5) * dd;
+  const S cs = fly_update_constraint(m, w, bs, false, false);
+  S theta = ((m.flags & FLY_OPT_NOWARMSTART) || cs < cw) ? S(0) : S(1);
+  if (theta == 0) { FLY_FOR(r, nefc) jar[r] = bs[r]; FLY_SYNC(); }
+  S gauss = S(0.5) * theta * theta * dd;
+  S cost = fly_update_constraint(m, w, jar, true, true) + gauss;
+  for (int it = 0;; it++) {
+    /* gradient in generalized coordinates: theta m0 + J^T (c - f) */
+    FLY_FOR(r, nefc) h[r] = c[r] - f[r];
+    FLY_SYNC();
+    FLY_FOR(r, nefc) w.efc_lam[r] = (T)h[r];
+    FLY_SYNC();
+    fly_jt_mul(m, w, w.sgrad, w.efc_lam);
+    T gn = 0;
+    FLY_FOR(d, nv) { const T g = w.sgrad[d] + (T)theta * m0[d]; gn += g * g; }
+    gn = warp_sum(gn);
+    if (it > 0 && scale * sqrt((S)gn) < m.tolerance) break;
+    if (it >= m.opt_iterations) break;
+    /* h = Y g~ = theta b0 + A (c - f) */
+    fly_a_mul(w, nefc, Acp, h);
+    FLY_FOR(r, nefc) h[r] = theta * b0[r] + Acp[r];
+    FLY_SYNC();
+    /* active rows; K = I + W A on them, rhs = W h */
+    const int na = warp_compact(nefc, [&](int r) -> bool { return w.efc_state[r] != FLY_ST_SATISFIED; }, w.lim_item, FLY_MAXEFC);
+    FLY_SYNC();
+    T* K = w.efc_K;
+    T* lam = w.efc_lam;
+    FLY_FOR(i, na) {
+      const int r = w.lim_item[i], g = w.efc_g[r], r0 = w.grp_row[g];
+      if (w.efc_state[r] == FLY_ST_CONE) {
+        const T* hc = w.con_hc + 9 * w.grp_con[g] + 3 * (r - r0);
+        for (int j = 0; j < na; j++) {
+          const int cj = w.lim_item[j];
+          K[i * na + j] = (i == j ? T(1) : T(0)) + hc[0] * w.efc_A[r0 * nefc + cj] + hc[1] * w.efc_A[(r0 + 1) * nefc + cj]
+                          + hc[2] * w.efc_A[(r0 + 2) * nefc + cj];
+        }
+        lam[i] = (T)(hc[0] * h[r0] + hc[1] * h[r0 + 1] + hc[2] * h[r0 + 2]);
+      } else {
+        const T D = w.efc_D[r];
+        for (int j = 0; j < na; j++) K[i * na + j] = (i == j ? T(1) : T(0)) + D * w.efc_A[r * nefc + w.lim_item[j]];
+        lam[i] = (T)(D * h[r]);
+      }
+    }
+    FLY_SYNC();
+    fly_lu_solve(K, na, lam);
+    /* search direction in (theta, c) coordinates: c_p = f + lambda - c, theta_p = -theta */
+    FLY_FOR(r, nefc) cp[r] = f[r] - c[r];
+    FLY_SYNC();
+    FLY_FOR(i, na) cp[w.lim_item[i]] += lam[i];
+    FLY_SYNC();
+    const S thp = -theta;
+    fly_a_mul(w, nefc, Acp, cp);
+    S s1 = 0, s2 = 0, s3 = 0, s4 = 0;
+    FLY_FOR(r, nefc) {
+      jv[r] = thp * b0[r] + Acp[r];
+      s1 += b0[r] * c[r]; s2 += b0[r] * cp[r]; s3 += cp[r] * Ac[r]; s4 += cp[r] * Acp[r];
+    }
+    s1 = warp_sum(s1); s2 = warp_sum(s2); s3 = warp_sum(s3); s4 = warp_sum(s4);
+    FLY_SYNC();
+    const S q1 = thp * theta * dd + thp * s1 + theta * s2 + s3;
+    const S q2 = S(0.5) * (thp * thp * dd + 2 * thp * s2 + s4);
+    if (!(q2 > 0)) break;
+    /* MuJoCo scales the line-search tolerance with |search|_2; here |search|_M / sqrt(meaninertia) stands in
+       for it (the Euclidean norm would cost one more tree solve per iteration) */
+    const S snorm = sqrt(2 * q2 / (S)m.meaninertia);
+    if (snorm < minval<S>()) break;
+    const S gtol = (S)m.tolerance * (S)m.ls_tolerance * snorm * (S)m.meaninertia * S(nv > 1 ? nv : 1);
+    const S quad[3] = {gauss, q1, q2};
+    const S alpha = fly_line_search(m, w, quad, gtol);
+    if (alpha == 0) break;
+    S g1 = 0, g2 = 0;
+    FLY_FOR(r, nefc) {
+      const S cn = c[r] + alpha * cp[r], acn = Ac[r] + alpha * Acp[r];
+      c[r] = cn; Ac[r] = acn; jar[r] += alpha * jv[r];
+      g1 += b0[r] * cn; g2 += cn * acn;
+    }
+    g1 = warp_sum(g1); g2 = warp_sum(g2);
+    FLY_SYNC();
+    theta += alpha * thp;
+    gauss = S(0.5) * (theta * theta * dd + 2 * theta * g1 + g2);
+    const S old = cost;
+    cost = fly_update_constraint(m, w, jar, true, true) + gauss;
+    niter = it + 1;
+    if (scale * (old - cost) < m.tolerance) break;
+  }
+  fly_jt_mul(m, w, w.qfrc_constraint, f);
+  if ((m.flags & FLY_OPT_NONOSLIP) || m.opt_noslip_iterations <= 0) {
+    /* qacc = qacc_smooth + theta d + M^-1 J^T c (with noslip the caller recomputes qacc from the final forces) */
+    FLY_FOR(r, nefc) w.efc_lam[r] = (T)c[r];
+    FLY_SYNC();
+    fly_jt_mul(m, w, w.stmp, w.efc_lam);
+    fly_solve(m, w.qLD, w.stmp);
+    FLY_FOR(d, nv) w.qacc[d] = w.qacc_smooth[d] + (T)theta * dvec[d] + w.stmp[d];
+    FLY_SYNC();
+  }
+  FLY_LANE0 w.counts[FLY_C_NITER] = niter;
+  FLY_SYNC();
+}
+
+/* noslip: Gauss-Seidel over the friction dimensions with the unregularised A, normal forces held fixed */
+template <class T>
+FLY_FN void fly_noslip(const DModel<T>& m, const Ws<T>& w) {
+  const int nefc = w.counts[FLY_C_NEFC], ngrp = w.counts[FLY_C_NGRP], nlimit = w.counts[FLY_C_NLIMIT];
+  FLY_LANE0 {
+    int n3 = 0;
+    for (int g = nlimit; g < ngrp; g++) if (w.grp_type[g] == FLY_CT_ELLIPTIC) { w.ns_fr[n3] = w.grp_row[g]; w.ns_con[n3] = w.grp_con[g]; n3++; }
+    w.counts[FLY_C_NFR] = n3;
+  }
+  FLY_SYNC();
+  const int n3 = w.counts[FLY_C_NFR];
+  if (!n3) return;
   const T scale = T(1) / (m.meaninertia * T(m.nv > 1 ? m.nv : 1));
   T* f = w.efc_force;
   for (int it = 0; it < m.opt_noslip_iterations; it++) {
     T improvement = 0;
     for (int i = 0; i < n3; i++) {
       const int r0 = w.ns_fr[i];
-      const T *A0 = w.ns_A + (2 * i) * nefc, *A1 = A0 + nefc;
+      const T *A0 = w.efc_A + (r0 + 1) * nefc, *A1 = A0 + nefc;
       T res[2] = {0, 0};
       FLY_FOR(k, nefc) { const T fk = f[k]; res[0] += A0[k] * fk; res[1] += A1[k] * fk; }
-      res[0] = warp_sum(res[0]) + w.efc_b[r0 + 1];
-      res[1] = warp_sum(res[1]) + w.efc_b[r0 + 2];
+      res[0] = warp_sum(res[0]) + (T)w.efc_b[r0 + 1];
+      res[1] = warp_sum(res[1]) + (T)w.efc_b[r0 + 2];
       const T old[2] = {f[r0 + 1], f[r0 + 2]};
       const T Ac[4] = {A0[r0 + 1], A0[r0 + 2], A1[r0 + 1], A1[r0 + 2]};
       const T fn = f[r0];
@@ -441,9 +450,10 @@ FLY_FN void fly_fwd_constraint(const DModel<T>& m, const Ws<T>& w) {
   const int nefc = w.counts[FLY_C_NEFC];
   FLY_FOR(r, nefc) {
     const T vel = fly_row_dot(m, w, r, w.qvel);
-    w.efc_aref[r] = -w.efc_B[r] * vel - w.efc_K[r] * w.efc_imp[r] * (w.efc_pos[r] - w.efc_margin[r]);
+    w.efc_aref[r] = -w.efc_B[r] * vel - w.efc_K0[r] * w.efc_imp[r] * (w.efc_pos[r] - w.efc_margin[r]);
   }
   FLY_SYNC();
+  if (nefc) fly_constraint_prepare(m, w);
   fly_newton(m, w);
   if (nefc && !(m.flags & FLY_OPT_NONOSLIP) && m.opt_noslip_iterations > 0) {
     fly_noslip(m, w);

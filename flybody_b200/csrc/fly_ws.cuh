@@ -26,7 +26,7 @@
   X(act_length, m.nu, 0) X(act_force, m.nu, 0) X(act_dot, m.na, 0)                      \
   X(qfrc_bias, m.nv, 0) X(qfrc_passive, m.nv, 0) X(qfrc_actuator, m.nv, 0)              \
   X(qfrc_smooth, m.nv, 1) X(qacc_smooth, m.nv, 1) X(qfrc_constraint, m.nv, 1)           \
-  X(sMa, m.nv, 1) X(sgrad, m.nv, 1) X(ssearch, m.nv, 1) X(sMv, m.nv, 1)          \
+  X(sMa, m.nv, 1) X(sgrad, m.nv, 1) X(ssearch, m.nv, 1)          \
   X(stmp, m.nv, 1)                                                                                    \
   X(bodyf, 6 * m.nbody, 0) X(boxf, 6 * (m.nfluidbox + m.nfluidgeom), 0)                        \
   X(cacc, 6 * m.nbody, 0) X(cfrc_int, 6 * m.nbody, 0) X(cfrc_ext, 6 * m.nbody, 0)       \
@@ -36,20 +36,27 @@
   X(con_hc, 9 * FLY_MAXCON, 0) X(hit_tmp, 32 * FLY_NHIT * 11, 0)                               \
   X(efc_J, FLY_MAXEFC * FLY_MAXCHAIN, 0) X(efc_Y, FLY_MAXEFC * FLY_MAXCHAIN, 0)                \
   X(x_J, FLY_MAXCROSS * FLY_MAXCHAIN, 0) X(x_Y, FLY_MAXCROSS * FLY_MAXCHAIN, 0)                \
-  X(x_dense, FLY_MAXCROSS * m.nv, 0) X(x_S, FLY_MAXCROSS * FLY_MAXCROSS, 0)                    \
-  X(x_z, FLY_MAXCROSS, 0)                                                                             \
   X(efc_pos, FLY_MAXEFC, 0) X(efc_margin, FLY_MAXEFC, 0) X(efc_diag, FLY_MAXEFC, 0)     \
-  X(efc_R, FLY_MAXEFC, 0) X(efc_D, FLY_MAXEFC, 1) X(efc_K, FLY_MAXEFC, 0)               \
+  X(efc_R, FLY_MAXEFC, 0) X(efc_D, FLY_MAXEFC, 1) X(efc_K0, FLY_MAXEFC, 0)               \
   X(efc_B, FLY_MAXEFC, 0) X(efc_imp, FLY_MAXEFC, 0) X(efc_aref, FLY_MAXEFC, 0)          \
-  X(efc_force, FLY_MAXEFC, 1) X(efc_jar, FLY_MAXEFC, 1) X(efc_jv, FLY_MAXEFC, 1)        \
-  X(efc_b, FLY_MAXEFC, 0) X(ns_A, FLY_MAXEFC * FLY_MAXEFC * 2 / 3, 0)                              \
+  X(efc_force, FLY_MAXEFC, 1)        \
+  X(efc_A, FLY_MAXEFC * FLY_MAXEFC, 0) X(efc_K, FLY_MAXEFC * FLY_MAXEFC, 0)             \
+          \
+  X(efc_lam, FLY_MAXEFC, 0)                              \
   X(obs_tmp, 8, 0)
+
+/* arrays of double: the Newton iterate in constraint space (c, jar = b + A c, ...) cancels to a few parts in 1e4
+ * of its terms, so these nefc-sized vectors are kept in float64 even when T is float */
+#define FLY_WS_DBL(X)                                                                                        \
+  X(efc_jar, FLY_MAXEFC, 1) X(efc_jv, FLY_MAXEFC, 1) X(efc_b, FLY_MAXEFC, 0) X(efc_b0, FLY_MAXEFC, 0)        \
+  X(efc_c, FLY_MAXEFC, 0) X(efc_cp, FLY_MAXEFC, 0) X(efc_Ac, FLY_MAXEFC, 0) X(efc_Acp, FLY_MAXEFC, 0)        \
+  X(efc_h, FLY_MAXEFC, 0)
 
 /* arrays of int */
 #define FLY_WS_INT(X)                                                                                        \
   X(con_pair, FLY_MAXCON, 0) X(con_dim, FLY_MAXCON, 0) X(con_excl, FLY_MAXCON, 0)       \
   X(con_efc, FLY_MAXCON, 0) X(hit_cnt, 32, 0) X(hit_off, 33, 0)                         \
-  X(efc_start, FLY_MAXEFC, 0) X(efc_xid, FLY_MAXEFC, 0) X(efc_state, FLY_MAXEFC, 0)     \
+  X(efc_start, FLY_MAXEFC, 0) X(efc_g, FLY_MAXEFC, 0) X(efc_xid, FLY_MAXEFC, 0) X(efc_state, FLY_MAXEFC, 0)     \
   X(grp_type, FLY_MAXGRP, 0) X(grp_row, FLY_MAXGRP, 0) X(grp_con, FLY_MAXGRP, 0)        \
   X(x_start, FLY_MAXCROSS, 0) X(x_row, FLY_MAXCROSS, 0) X(ns_fr, FLY_MAXEFC, 0) X(ns_con, FLY_MAXCON, 0)         \
   X(counts, 16, 0)
@@ -65,6 +72,9 @@ template <class T>
 struct Ws {
 #define X(n, cnt, tier) T* n;
   FLY_WS_REAL(X)
+#undef X
+#define X(n, cnt, tier) double* n;
+  FLY_WS_DBL(X)
 #undef X
 #define X(n, cnt, tier) int* n;
   FLY_WS_INT(X)
@@ -95,6 +105,9 @@ FLY_HD void ws_bind(const DModel<T>& m, Ws<T>* w, char* fast, char* bulk, size_t
   }
 #define X(n, cnt, tier) PLACE(n, cnt, tier, T)
   FLY_WS_REAL(X)
+#undef X
+#define X(n, cnt, tier) PLACE(n, cnt, tier, double)
+  FLY_WS_DBL(X)
 #undef X
 #define X(n, cnt, tier) PLACE(n, cnt, tier, int)
   FLY_WS_INT(X)

@@ -95,7 +95,6 @@ struct Emu : EmuBase {
     else if (s == "forward_acc") fly_forward_acc(m, w);
     else if (s == "integrate") fly_integrate(m, w);
     else if (s == "solve_stmp") fly_solve(m, w.qLD, w.stmp);
-    else if (s == "mulm_stmp") fly_mul_m(m, w.qM, w.sMv, w.stmp);
     else fprintf(stderr, "emu: unknown stage %s\n", stage);
   }
   int get(const char* name, double* out, int cap) override {
@@ -103,6 +102,7 @@ struct Emu : EmuBase {
     (void)fb; (void)bb;
 #define X(n, cnt, tier) if (!strcmp(name, #n)) { int c = (int)(cnt); if (c > cap) c = cap; for (int i = 0; i < c; i++) out[i] = (double)w.n[i]; return c; }
     FLY_WS_REAL(X)
+    FLY_WS_DBL(X)
 #undef X
     if (!strcmp(name, "sreal")) { int c = (int)sreal.size() < cap ? (int)sreal.size() : cap; for (int i = 0; i < c; i++) out[i] = (double)sreal[i]; return c; }
     return -1;
