@@ -190,84 +190,112 @@ FLY_FN void fly_crb(const DModel<T>& m, const Ws<T>& w) {
   FLY_SYNC();
 }
 
-/* ---------------------------------------------------------------- tree-sparse L^T D L
- * A (layout of qM: row i holds A(i, i), A(i, parent), A(i, grandparent) ...) is factorised in place:
- * afterwards row i holds D_i followed by L(i, ancestor).  Gather form: an entry only reads finished rows
- * of descendants, so each depth level is one parallel phase. */
+/* ---------------------------------------------------------------- tree-sparse L^T D L from a lane program
+ * U (layout of qM: row i holds A(i,i), A(i,parent), A(i,grandparent) ...; nM + 1 elements) is the input matrix and is
+ * overwritten by the unnormalised factor U(i,j) = D_i L(i,j); Lout receives D_i on the diagonal and L(i,ancestor) off
+ * it; invD[i] = 1 / D_i.  Gather form, level by level from the leaves: entry (i,j) needs
+ * A(i,j) - sum_{c in desc(i)} L(c,i) U(c,j).  The host cut those sums into equal chunks and dealt them to the lanes
+ * (fly_model.h); a lane streams its chunk words (coalesced), writes one partial per chunk, then the entries of the
+ * level add their partials up.  No index arithmetic or pointer chasing is left in the loop. */
 template <class T>
-FLY_FN void fly_factor(const DModel<T>& m, T* A) {
-  for (int L = m.ndlevel - 1; L >= 0; L--) {
-    const int adr = m.dlvl_adr[L], n = m.dlvl_adr[L + 1] - adr, nl = m.dlvl_nlight[L], W = L + 1;
-    FLY_FOR(it, nl * W) {
-      const int i = m.dlvl_dof[adr + it / W], k = it % W;
-      T s = A[m.madr[i] + k];
-      for (int q = m.desc_adr[i]; q < m.desc_adr[i + 1]; q++) {
-        const int pk = m.desc[q], c = pk & 255, a = pk >> 8;
-        s -= A[a] * A[m.madr[c]] * A[a + k];
-      }
-      A[m.madr[i] + k] = s;
-    }
-    for (int h = nl; h < n; h++) {  /* heavy dofs: descendants over lanes, one entry at a time */
-      const int i = m.dlvl_dof[adr + h], q0 = m.desc_adr[i], nd = m.desc_adr[i + 1] - q0;
-      for (int k = 0; k < W; k++) {
+FLY_FN void fly_factor(const DModel<T>& m, const Ws<T>& w, T* U, T* Lout, T* invD) {
+  T* part = w.fpart;
+  const int nM = m.nM;
+  FLY_LANE0 { U[nM] = 0; Lout[nM] = 0; }
+  FLY_SYNC();
+  for (int lv = 0; lv < m.ndlevel; lv++) {
+    const int base = m.fprog_lvl[3 * lv], per_lane = m.fprog_lvl[3 * lv + 1];
+    FLY_FOR(l, 32) {
+      for (int q = 0; q < per_lane; q++) {
+        const int* P = m.fprog + base + q * (1 + FLY_FCHUNK) * 32 + l;
+        const int slot = FLY_LDG(P);
         T s = 0;
-        FLY_FOR(q, nd) {
-          const int pk = m.desc[q0 + q], c = pk & 255, a = pk >> 8;
-          s += A[a] * A[m.madr[c]] * A[a + k];
+#pragma unroll
+        for (int t = 0; t < FLY_FCHUNK; t++) {
+          const int op = FLY_LDG(P + (1 + t) * 32);
+          s += Lout[op & 2047] * U[op >> 11];
         }
-        s = warp_sum(s);
-        FLY_SYNC();
-        FLY_LANE0 A[m.madr[i] + k] -= s;
+        if (slot != 65535) part[slot] = s;
       }
     }
     FLY_SYNC();
-    FLY_FOR(it, n * W) {
-      const int i = m.dlvl_dof[adr + it / W], k = it % W;
-      if (k > 0) A[m.madr[i] + k] /= A[m.madr[i]];
+    const int e0 = m.fent_adr[lv], ne = m.fent_adr[lv + 1] - e0;
+    FLY_FOR(e, ne) {
+      const int w0 = FLY_LDG(m.fent + 2 * (e0 + e)), w1 = FLY_LDG(m.fent + 2 * (e0 + e) + 1);
+      const int a = w0 & 2047, ad = (w0 >> 11) & 2047, nch = w0 >> 22, s0 = w1 & 65535, sd = w1 >> 16;
+      T u = U[a], ud = U[ad];
+      for (int k = 0; k < nch; k++) { u -= part[s0 + k]; ud -= part[sd + k]; }
+      Lout[a] = a == ad ? u : u / ud;
+    }
+    FLY_SYNC();
+    FLY_FOR(e, ne) {
+      const int w0 = FLY_LDG(m.fent + 2 * (e0 + e));
+      const int a = w0 & 2047, ad = (w0 >> 11) & 2047;
+      U[a] = a == ad ? Lout[a] : Lout[a] * Lout[ad];
     }
     FLY_SYNC();
   }
+  FLY_FOR(i, m.nv) invD[i] = T(1) / Lout[m.madr[i]];
+  FLY_SYNC();
 }
 
-/* x <- (L^T D L)^-1 x */
+/* x <- (L^T D L)^-1 x.  Every subtree below the trunk (the few dofs with many descendants: the free root, or the ball)
+ * is substituted by ONE lane from a precomputed op stream, with no barrier inside; the trunk itself is reduced across
+ * lanes.  Backward pass (x[j] -= sum_desc L(c,j) x[c]), trunk, then forward pass (y[i] = x[i]/D_i - sum_anc L(i,a) y[a]). */
 template <class T>
-FLY_FN void fly_solve(const DModel<T>& m, const T* LD, T* x) {
-  for (int L = m.ndlevel - 2; L >= 0; L--) {
-    const int adr = m.dlvl_adr[L], n = m.dlvl_adr[L + 1] - adr, nl = m.dlvl_nlight[L];
-    FLY_FOR(k, nl) {
-      const int j = m.dlvl_dof[adr + k];
-      T s = 0;
-      for (int q = m.desc_adr[j]; q < m.desc_adr[j + 1]; q++) {
-        const int pk = m.desc[q];
-        s += LD[pk >> 8] * x[pk & 255];
+FLY_FN void fly_solve(const DModel<T>& m, const Ws<T>& w, const T* LD, const T* invD, T* x) {
+  T* tpart = w.tpart;
+  FLY_FOR(l, 32) {
+    T s = 0;
+    const int* P = m.sprog_b + l;
+    for (int q = 0; q < m.sprog_b_len; q++) {
+      const int op = FLY_LDG(P + q * 32);
+      s += LD[op & 2047] * x[(op >> 11) & 255];
+      const int kind = (op >> 19) & 3;
+      if (kind) {
+        const int tgt = op >> 21;
+        if (kind == 1) x[tgt] -= s; else tpart[tgt * 32 + l] = s;
+        s = 0;
       }
-      x[j] -= s;
     }
-    for (int h = nl; h < n; h++) {
-      const int j = m.dlvl_dof[adr + h], q0 = m.desc_adr[j], nd = m.desc_adr[j + 1] - q0;
-      T s = 0;
-      FLY_FOR(q, nd) {
-        const int pk = m.desc[q0 + q];
-        s += LD[pk >> 8] * x[pk & 255];
-      }
-      s = warp_sum(s);
-      FLY_SYNC();
-      FLY_LANE0 x[j] -= s;
-    }
-    FLY_SYNC();
   }
-  FLY_FOR(i, m.nv) x[i] /= LD[m.madr[i]];
   FLY_SYNC();
-  for (int L = 1; L < m.ndlevel; L++) {
-    const int adr = m.dlvl_adr[L], n = m.dlvl_adr[L + 1] - adr;
-    FLY_FOR(k, n) {
-      const int i = m.dlvl_dof[adr + k], a = m.madr[i];
-      T s = 0;
-      for (int q = 1; q <= L; q++) s += LD[a + q] * x[m.mcol[a + q]];
-      x[i] -= s;
+  for (int t = m.ntrunk - 1; t >= 0; t--) {
+    const int dof = m.trunk_dof[t];
+    T s = 0;
+    FLY_FOR(l, 32) s += tpart[t * 32 + l];
+    s = warp_sum(s);
+    for (int t2 = t + 1; t2 < m.ntrunk; t2++) {
+      const int c = m.trunk_dof[t2];
+      if (dof <= c && c <= m.hsublast[dof]) s += LD[m.madr[c] + m.hdepth[c] - m.hdepth[dof]] * x[c];
     }
     FLY_SYNC();
+    FLY_LANE0 x[dof] -= s;
+    FLY_SYNC();
   }
+  FLY_LANE0 {
+    for (int t = 0; t < m.ntrunk; t++) {
+      const int dof = m.trunk_dof[t], a = m.madr[dof];
+      T y = x[dof] * invD[dof];
+      for (int k = 1; k <= m.hdepth[dof]; k++) y -= LD[a + k] * x[m.mcol[a + k]];
+      x[dof] = y;
+    }
+  }
+  FLY_SYNC();
+  FLY_FOR(l, 32) {
+    T s = 0;
+    const int* P = m.sprog_f + l;
+    for (int q = 0; q < m.sprog_f_len; q++) {
+      const int op = FLY_LDG(P + q * 32);
+      s += LD[op & 2047] * x[(op >> 11) & 255];
+      if ((op >> 19) & 3) {
+        const int tgt = op >> 21;
+        x[tgt] = x[tgt] * invD[tgt] - s;
+        s = 0;
+      }
+    }
+  }
+  FLY_SYNC();
 }
 
 /* r <- M v (tree-sparse symmetric product) */

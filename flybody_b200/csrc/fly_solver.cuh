@@ -383,7 +383,7 @@ FLY_FN void fly_newton(const DModel<T>& m, const Ws<T>& w) {
     FLY_FOR(r, nefc) w.efc_lam[r] = (T)c[r];
     FLY_SYNC();
     fly_jt_mul(m, w, w.stmp, w.efc_lam);
-    fly_solve(m, w.qLD, w.stmp);
+    fly_solve(m, w, w.qLD, w.qDinv, w.stmp);
     FLY_FOR(d, nv) w.qacc[d] = w.qacc_smooth[d] + (T)theta * dvec[d] + w.stmp[d];
     FLY_SYNC();
   }
@@ -460,7 +460,7 @@ FLY_FN void fly_fwd_constraint(const DModel<T>& m, const Ws<T>& w) {
     /* qacc = qacc_smooth + M^-1 J^T f */
     FLY_FOR(d, m.nv) w.stmp[d] = w.qfrc_constraint[d];
     FLY_SYNC();
-    fly_solve(m, w.qLD, w.stmp);
+    fly_solve(m, w, w.qLD, w.qDinv, w.stmp);
     FLY_FOR(d, m.nv) w.qacc[d] = w.qacc_smooth[d] + w.stmp[d];
     FLY_SYNC();
   }

@@ -133,9 +133,9 @@ FLY_FN void fly_step1(const DModel<T>& m, const Ws<T>& w, bool full) {
   fly_com_pos(m, w);
   if (full) {
     fly_crb(m, w);
-    FLY_FOR(e, m.nM) w.qLD[e] = w.qM[e];
+    FLY_FOR(e, m.nM) w.qU[e] = w.qM[e];
     FLY_SYNC();
-    fly_factor(m, w.qLD);
+    fly_factor(m, w, w.qU, w.qLD, w.qDinv);
     fly_collision(m, w);
     fly_make_constraint(m, w);
   }
@@ -156,7 +156,7 @@ FLY_FN void fly_forward_acc(const DModel<T>& m, const Ws<T>& w) {
     w.qfrc_smooth[d] = f; w.qacc_smooth[d] = f;
   }
   FLY_SYNC();
-  fly_solve(m, w.qLD, w.qacc_smooth);
+  fly_solve(m, w, w.qLD, w.qDinv, w.qacc_smooth);
   fly_fwd_constraint(m, w);
   fly_sensors_acc(m, w);
 }
@@ -167,12 +167,12 @@ FLY_FN void fly_integrate(const DModel<T>& m, const Ws<T>& w) {
   const T dt = m.timestep;
   FLY_FOR(e, m.nM) {
     const int i = m.mrow[e];
-    w.qH[e] = w.qM[e] + (e == m.madr[i] ? dt * m.dof_damping[i] : T(0));
+    w.qU[e] = w.qM[e] + (e == m.madr[i] ? dt * m.dof_damping[i] : T(0));
   }
   FLY_FOR(d, m.nv) w.stmp[d] = w.qfrc_smooth[d] + w.qfrc_constraint[d];
   FLY_SYNC();
-  fly_factor(m, w.qH);
-  fly_solve(m, w.qH, w.stmp);
+  fly_factor(m, w, w.qU, w.qH, w.qHinv);
+  fly_solve(m, w, w.qH, w.qHinv, w.stmp);
   FLY_FOR(i, m.na) w.act[i] += dt * w.act_dot[i];
   FLY_FOR(d, m.nv) { w.qvel[d] += dt * w.stmp[d]; w.warm[d] = w.qacc[d]; }
   FLY_SYNC();

@@ -88,13 +88,13 @@ struct Emu : EmuBase {
     if (s == "kinematics") fly_kinematics(m, w);
     else if (s == "com_pos") fly_com_pos(m, w);
     else if (s == "crb") fly_crb(m, w);
-    else if (s == "factor") { for (int e = 0; e < m.nM; e++) w.qLD[e] = w.qM[e]; fly_factor(m, w.qLD); }
+    else if (s == "factor") { for (int e = 0; e < m.nM; e++) w.qU[e] = w.qM[e]; fly_factor(m, w, w.qU, w.qLD, w.qDinv); }
     else if (s == "collision") fly_collision(m, w);
     else if (s == "make_constraint") fly_make_constraint(m, w);
     else if (s == "step1") fly_step1(m, w, true);
     else if (s == "forward_acc") fly_forward_acc(m, w);
     else if (s == "integrate") fly_integrate(m, w);
-    else if (s == "solve_stmp") fly_solve(m, w.qLD, w.stmp);
+    else if (s == "solve_stmp") fly_solve(m, w, w.qLD, w.qDinv, w.stmp);
     else fprintf(stderr, "emu: unknown stage %s\n", stage);
   }
   int get(const char* name, double* out, int cap) override {
