@@ -190,108 +190,212 @@ FLY_FN void fly_crb(const DModel<T>& m, const Ws<T>& w) {
   FLY_SYNC();
 }
 
-/* ---------------------------------------------------------------- tree-sparse L^T D L from a lane program
- * U (layout of qM: row i holds A(i,i), A(i,parent), A(i,grandparent) ...; nM + 1 elements) is the input matrix and is
- * overwritten by the unnormalised factor U(i,j) = D_i L(i,j); Lout receives D_i on the diagonal and L(i,ancestor) off
- * it; invD[i] = 1 / D_i.  Gather form, level by level from the leaves: entry (i,j) needs
- * A(i,j) - sum_{c in desc(i)} L(c,i) U(c,j).  The host cut those sums into equal chunks and dealt them to the lanes
- * (fly_model.h); a lane streams its chunk words (coalesced), writes one partial per chunk, then the entries of the
- * level add their partials up.  No index arithmetic or pointer chasing is left in the loop. */
+/* ---------------------------------------------------------------- tree-sparse L^T D L, branch per lane
+ * dst[0..n) -= t * src[0..n) for two rows of one array.  The loads of a block are issued before its stores (the
+ * compiler cannot prove the rows do not overlap, and a load-FMA-store chain per element would expose the full
+ * shared-memory latency n times). */
 template <class T>
-FLY_FN void fly_factor(const DModel<T>& m, const Ws<T>& w, T* U, T* Lout, T* invD) {
-  T* part = w.fpart;
-  const int nM = m.nM;
-  FLY_LANE0 { U[nM] = 0; Lout[nM] = 0; }
-  FLY_SYNC();
-  for (int lv = 0; lv < m.ndlevel; lv++) {
-    const int base = m.fprog_lvl[3 * lv], per_lane = m.fprog_lvl[3 * lv + 1];
-    FLY_FOR(l, 32) {
-      for (int q = 0; q < per_lane; q++) {
-        const int* P = m.fprog + base + q * (1 + FLY_FCHUNK) * 32 + l;
-        const int slot = FLY_LDG(P);
-        T s = 0;
-#pragma unroll
-        for (int t = 0; t < FLY_FCHUNK; t++) {
-          const int op = FLY_LDG(P + (1 + t) * 32);
-          s += Lout[op & 2047] * U[op >> 11];
+FLY_INL void fly_row_axpy(T* dst, const T* src, T t, int n) {
+  int q = 0;
+  for (; q + 8 <= n; q += 8) {
+    const T s0 = src[q], s1 = src[q + 1], s2 = src[q + 2], s3 = src[q + 3], s4 = src[q + 4], s5 = src[q + 5], s6 = src[q + 6], s7 = src[q + 7];
+    const T d0 = dst[q], d1 = dst[q + 1], d2 = dst[q + 2], d3 = dst[q + 3], d4 = dst[q + 4], d5 = dst[q + 5], d6 = dst[q + 6], d7 = dst[q + 7];
+    dst[q] = d0 - t * s0; dst[q + 1] = d1 - t * s1; dst[q + 2] = d2 - t * s2; dst[q + 3] = d3 - t * s3;
+    dst[q + 4] = d4 - t * s4; dst[q + 5] = d5 - t * s5; dst[q + 6] = d6 - t * s6; dst[q + 7] = d7 - t * s7;
+  }
+  if (q + 4 <= n) {
+    const T s0 = src[q], s1 = src[q + 1], s2 = src[q + 2], s3 = src[q + 3];
+    const T d0 = dst[q], d1 = dst[q + 1], d2 = dst[q + 2], d3 = dst[q + 3];
+    dst[q] = d0 - t * s0; dst[q + 1] = d1 - t * s1; dst[q + 2] = d2 - t * s2; dst[q + 3] = d3 - t * s3;
+    q += 4;
+  }
+  const int r = n - q;
+  if (r > 0) {
+    const T s0 = src[q], s1 = r > 1 ? src[q + 1] : T(0), s2 = r > 2 ? src[q + 2] : T(0);
+    const T d0 = dst[q], d1 = r > 1 ? dst[q + 1] : T(0), d2 = r > 2 ? dst[q + 2] : T(0);
+    dst[q] = d0 - t * s0;
+    if (r > 1) dst[q + 1] = d1 - t * s1;
+    if (r > 2) dst[q + 2] = d2 - t * s2;
+  }
+}
+
+/* In place: LD holds the matrix on entry (layout of qM: row i = A(i,i), A(i,parent), A(i,grandparent) ...) and
+ * D_i on the diagonal / L(i,ancestor) off it on return; invD[i] = 1 / D_i.
+ * Phase 1: each lane eliminates the rows of its own branches, deepest dof first (the row updates stay inside the
+ * branch: no barrier, no index stream).  Phase 2: the branch rows' trunk entries are normalised and their outer
+ * products are summed into the small trunk block (registers + warp reduction).  Phase 3: the trunk block (a chain of
+ * at most FLY_MAXTRUNK dofs) is eliminated in registers by every lane alike. */
+template <class T>
+FLY_FN void fly_factor(const DModel<T>& m, const Ws<T>& w, T* LD, T* invD) {
+  (void)w;
+  FLY_FOR(l, 32) {
+    for (int q = 0; q < m.brow_len; q++) {
+      const int word = FLY_LDG(m.brow_b + q * 32 + l);
+      if (word >= 0) {
+        const int k = word & 255, dk = (word >> 8) & 31, ak = word >> 13, hk = FLY_LDG(m.hdepth + k);
+        const T inv = T(1) / LD[ak];
+        invD[k] = inv;
+        int ai_next = FLY_LDG(m.mdiag + ak + 1);
+        for (int r = 1; r <= dk; r++) {
+          const int ai = ai_next;
+          ai_next = FLY_LDG(m.mdiag + ak + r + 1);
+          const T t = LD[ak + r] * inv;
+          fly_row_axpy(LD + ai, LD + ak + r, t, hk - r + 1);
+          LD[ak + r] = t;
         }
-        if (slot != 65535) part[slot] = s;
       }
     }
-    FLY_SYNC();
-    const int e0 = m.fent_adr[lv], ne = m.fent_adr[lv + 1] - e0;
-    FLY_FOR(e, ne) {
-      const int w0 = FLY_LDG(m.fent + 2 * (e0 + e)), w1 = FLY_LDG(m.fent + 2 * (e0 + e) + 1);
-      const int a = w0 & 2047, ad = (w0 >> 11) & 2047, nch = w0 >> 22, s0 = w1 & 65535, sd = w1 >> 16;
-      T u = U[a], ud = U[ad];
-      for (int k = 0; k < nch; k++) { u -= part[s0 + k]; ud -= part[sd + k]; }
-      Lout[a] = a == ad ? u : u / ud;
-    }
-    FLY_SYNC();
-    FLY_FOR(e, ne) {
-      const int w0 = FLY_LDG(m.fent + 2 * (e0 + e));
-      const int a = w0 & 2047, ad = (w0 >> 11) & 2047;
-      U[a] = a == ad ? Lout[a] : Lout[a] * Lout[ad];
-    }
-    FLY_SYNC();
   }
-  FLY_FOR(i, m.nv) invD[i] = T(1) / Lout[m.madr[i]];
+  FLY_SYNC();
+  const int nt = m.ntrunk;
+  if (nt == 0) return;
+  T acc[FLY_MAXTRUNK * (FLY_MAXTRUNK + 1) / 2];
+#pragma unroll
+  for (int e = 0; e < FLY_MAXTRUNK * (FLY_MAXTRUNK + 1) / 2; e++) acc[e] = 0;
+  FLY_FOR(k, m.nv) {
+    const int dk = FLY_LDG(m.dof_din + k);
+    if (dk >= 0) {
+      const int ak = FLY_LDG(m.madr + k), hk = FLY_LDG(m.hdepth + k), ntk = hk - dk;
+      const T inv = invD[k];
+      T u[FLY_MAXTRUNK];
+#pragma unroll
+      for (int q = 0; q < FLY_MAXTRUNK; q++) u[q] = q < ntk ? LD[ak + hk - q] : T(0);
+#pragma unroll
+      for (int i = 0; i < FLY_MAXTRUNK; i++) {
+        const T li = u[i] * inv;
+        if (i < ntk) LD[ak + hk - i] = li;
+#pragma unroll
+        for (int j = 0; j <= i; j++) acc[i * (i + 1) / 2 + j] += li * u[j];
+      }
+    }
+  }
+  int ta[FLY_MAXTRUNK];
+#pragma unroll
+  for (int i = 0; i < FLY_MAXTRUNK; i++) ta[i] = i < nt ? FLY_LDG(m.madr + FLY_LDG(m.trunk_dof + i)) : 0;
+#pragma unroll
+  for (int i = 0; i < FLY_MAXTRUNK; i++)
+    if (i < nt) {
+#pragma unroll
+      for (int j = 0; j <= i; j++) acc[i * (i + 1) / 2 + j] = LD[ta[i] + i - j] - warp_sum(acc[i * (i + 1) / 2 + j]);
+    }
+#pragma unroll
+  for (int k = FLY_MAXTRUNK - 1; k >= 0; k--)
+    if (k < nt) {
+      const T inv = T(1) / acc[k * (k + 1) / 2 + k];
+#pragma unroll
+      for (int i = k - 1; i >= 0; i--) {
+        const T t = acc[k * (k + 1) / 2 + i] * inv;
+#pragma unroll
+        for (int j = 0; j <= i; j++) acc[i * (i + 1) / 2 + j] -= t * acc[k * (k + 1) / 2 + j];
+        acc[k * (k + 1) / 2 + i] = t;
+      }
+    }
+  FLY_SYNC();
+  FLY_LANE0 {
+#pragma unroll
+    for (int i = 0; i < FLY_MAXTRUNK; i++)
+      if (i < nt) {
+        invD[FLY_LDG(m.trunk_dof + i)] = T(1) / acc[i * (i + 1) / 2 + i];
+#pragma unroll
+        for (int j = 0; j <= i; j++) LD[ta[i] + i - j] = acc[i * (i + 1) / 2 + j];
+      }
+  }
   FLY_SYNC();
 }
 
-/* x <- (L^T D L)^-1 x.  Every subtree below the trunk (the few dofs with many descendants: the free root, or the ball)
- * is substituted by ONE lane from a precomputed op stream, with no barrier inside; the trunk itself is reduced across
- * lanes.  Backward pass (x[j] -= sum_desc L(c,j) x[c]), trunk, then forward pass (y[i] = x[i]/D_i - sum_anc L(i,a) y[a]). */
+/* x <- (L^T D L)^-1 x with the same ownership: branch rows by one lane (backward: scatter of the finished x[c] to
+ * its in-branch ancestors; forward: gather over them), the trunk chain in registers in between. */
 template <class T>
 FLY_FN void fly_solve(const DModel<T>& m, const Ws<T>& w, const T* LD, const T* invD, T* x) {
-  T* tpart = w.tpart;
+  (void)w;
   FLY_FOR(l, 32) {
-    T s = 0;
-    const int* P = m.sprog_b + l;
-    for (int q = 0; q < m.sprog_b_len; q++) {
-      const int op = FLY_LDG(P + q * 32);
-      s += LD[op & 2047] * x[(op >> 11) & 255];
-      const int kind = (op >> 19) & 3;
-      if (kind) {
-        const int tgt = op >> 21;
-        if (kind == 1) x[tgt] -= s; else tpart[tgt * 32 + l] = s;
-        s = 0;
+    for (int q = 0; q < m.brow_len; q++) {
+      const int word = FLY_LDG(m.brow_b + q * 32 + l);
+      if (word >= 0) {
+        const int c = word & 255, dk = (word >> 8) & 31, a = word >> 13;
+        const T xc = x[c];
+        for (int k = 1; k <= dk; k += 4) {
+          const int n = dk - k + 1;
+          const int j0 = FLY_LDG(m.mcol + a + k), j1 = FLY_LDG(m.mcol + a + k + 1), j2 = FLY_LDG(m.mcol + a + k + 2), j3 = FLY_LDG(m.mcol + a + k + 3);
+          const T l0 = LD[a + k], l1 = n > 1 ? LD[a + k + 1] : T(0), l2 = n > 2 ? LD[a + k + 2] : T(0), l3 = n > 3 ? LD[a + k + 3] : T(0);
+          const T v0 = x[j0], v1 = n > 1 ? x[j1] : T(0), v2 = n > 2 ? x[j2] : T(0), v3 = n > 3 ? x[j3] : T(0);
+          x[j0] = v0 - l0 * xc;
+          if (n > 1) x[j1] = v1 - l1 * xc;
+          if (n > 2) x[j2] = v2 - l2 * xc;
+          if (n > 3) x[j3] = v3 - l3 * xc;
+        }
       }
     }
   }
   FLY_SYNC();
-  for (int t = m.ntrunk - 1; t >= 0; t--) {
-    const int dof = m.trunk_dof[t];
-    T s = 0;
-    FLY_FOR(l, 32) s += tpart[t * 32 + l];
-    s = warp_sum(s);
-    for (int t2 = t + 1; t2 < m.ntrunk; t2++) {
-      const int c = m.trunk_dof[t2];
-      if (dof <= c && c <= m.hsublast[dof]) s += LD[m.madr[c] + m.hdepth[c] - m.hdepth[dof]] * x[c];
+  const int nt = m.ntrunk;
+  T y[FLY_MAXTRUNK];
+  if (nt > 0) {
+    T acc[FLY_MAXTRUNK];
+#pragma unroll
+    for (int q = 0; q < FLY_MAXTRUNK; q++) acc[q] = 0;
+    FLY_FOR(c, m.nv) {
+      const int dk = FLY_LDG(m.dof_din + c);
+      if (dk >= 0) {
+        const int a = FLY_LDG(m.madr + c), hk = FLY_LDG(m.hdepth + c), ntc = hk - dk;
+        const T xc = x[c];
+#pragma unroll
+        for (int q = 0; q < FLY_MAXTRUNK; q++) if (q < ntc) acc[q] += LD[a + hk - q] * xc;
+      }
+    }
+    int ta[FLY_MAXTRUNK], td[FLY_MAXTRUNK];
+#pragma unroll
+    for (int i = 0; i < FLY_MAXTRUNK; i++) {
+      td[i] = i < nt ? FLY_LDG(m.trunk_dof + i) : 0;
+      ta[i] = FLY_LDG(m.madr + td[i]);
+    }
+    T xt[FLY_MAXTRUNK];
+#pragma unroll
+    for (int k = FLY_MAXTRUNK - 1; k >= 0; k--) {
+      xt[k] = 0;
+      if (k < nt) {
+        T s = warp_sum(acc[k]);
+#pragma unroll
+        for (int k2 = k + 1; k2 < FLY_MAXTRUNK; k2++) if (k2 < nt) s += LD[ta[k2] + k2 - k] * xt[k2];
+        xt[k] = x[td[k]] - s;
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < FLY_MAXTRUNK; k++) {
+      y[k] = 0;
+      if (k < nt) {
+        T s = 0;
+#pragma unroll
+        for (int k2 = 0; k2 < k; k2++) s += LD[ta[k] + k - k2] * y[k2];
+        y[k] = xt[k] * invD[td[k]] - s;
+      }
     }
     FLY_SYNC();
-    FLY_LANE0 x[dof] -= s;
+    FLY_LANE0 {
+#pragma unroll
+      for (int k = 0; k < FLY_MAXTRUNK; k++) if (k < nt) x[td[k]] = y[k];
+    }
+    FLY_FOR(c, m.nv) {
+      const int dk = FLY_LDG(m.dof_din + c);
+      if (dk >= 0) {
+        const int a = FLY_LDG(m.madr + c), hk = FLY_LDG(m.hdepth + c), ntc = hk - dk;
+        T s = 0;
+#pragma unroll
+        for (int q = 0; q < FLY_MAXTRUNK; q++) if (q < ntc) s += LD[a + hk - q] * y[q];
+        x[c] -= s * LD[a];
+      }
+    }
     FLY_SYNC();
   }
-  FLY_LANE0 {
-    for (int t = 0; t < m.ntrunk; t++) {
-      const int dof = m.trunk_dof[t], a = m.madr[dof];
-      T y = x[dof] * invD[dof];
-      for (int k = 1; k <= m.hdepth[dof]; k++) y -= LD[a + k] * x[m.mcol[a + k]];
-      x[dof] = y;
-    }
-  }
-  FLY_SYNC();
   FLY_FOR(l, 32) {
-    T s = 0;
-    const int* P = m.sprog_f + l;
-    for (int q = 0; q < m.sprog_f_len; q++) {
-      const int op = FLY_LDG(P + q * 32);
-      s += LD[op & 2047] * x[(op >> 11) & 255];
-      if ((op >> 19) & 3) {
-        const int tgt = op >> 21;
-        x[tgt] = x[tgt] * invD[tgt] - s;
-        s = 0;
+    for (int q = 0; q < m.brow_len; q++) {
+      const int word = FLY_LDG(m.brow_f + q * 32 + l);
+      if (word >= 0) {
+        const int i = word & 255, dk = (word >> 8) & 31, a = word >> 13;
+        T s = 0;
+#pragma unroll 4
+        for (int k = 1; k <= dk; k++) s += LD[a + k] * x[FLY_LDG(m.mcol + a + k)];
+        x[i] = x[i] * invD[i] - s;
       }
     }
   }

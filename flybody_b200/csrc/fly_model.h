@@ -15,6 +15,7 @@
 #include <string.h>
 #include <string>
 #include <vector>
+#include <algorithm>
 #include "../../include/flyb_model.h"
 
 #define FLY_MAXCHAIN 24   /* longest dof chain root->leaf in the Hessian tree (walk: 6 + 14 abdomen = 20) */
@@ -24,7 +25,7 @@
 #define FLY_MAXCAND 256   /* narrow-phase candidates after the bounding-sphere test */
 #define FLY_MAXCROSS 24   /* two-chain (cross-branch) contact rows */
 #define FLY_HEAVY 24      /* dofs with more descendants than this are reduced warp-cooperatively */
-#define FLY_FCHUNK 8      /* multiply-adds per chunk of the factorisation lane program */
+#define FLY_MAXTRUNK 8    /* dofs of the trunk chain (held in registers by the factorisation and the solves) */
 
 enum { FLY_OPT_NOCONTACT = 1, FLY_OPT_NOLIMIT = 2, FLY_OPT_NOFLUID = 4, FLY_OPT_NONOSLIP = 8,
        FLY_OPT_NOACTUATION = 16, FLY_OPT_NOWARMSTART = 32 };
@@ -34,9 +35,9 @@ enum { FLY_OPT_NOCONTACT = 1, FLY_OPT_NOLIMIT = 2, FLY_OPT_NOFLUID = 4, FLY_OPT_
   X(body_parent) X(body_rootid) X(body_jntadr) X(body_jntnum) X(body_dofadr) X(body_dofnum)               \
   X(body_lastdof) X(body_kchain) X(lvl_adr) X(lvl_body) X(child_adr) X(child)                              \
   X(jnt_type) X(jnt_qposadr) X(jnt_dofadr) X(jnt_bodyid) X(jnt_limited)                                    \
-  X(dof_bodyid) X(dof_jntid) X(dof_parentid) X(hpar) X(hdepth) X(kdepth) X(hsublast) X(madr) X(mrow) X(mcol)\
+  X(dof_bodyid) X(dof_jntid) X(dof_parentid) X(hpar) X(hdepth) X(kdepth) X(hsublast) X(madr) X(mrow) X(mcol) X(mdiag)\
   X(dlvl_adr) X(dlvl_dof) X(dlvl_nlight) X(heavy_dof) X(desc_adr) X(desc) X(tri_a) X(tri_b)                  \
-  X(fprog) X(fprog_lvl) X(fent) X(fent_adr) X(sprog_b) X(sprog_f) X(trunk_dof)                             \
+  X(brow_b) X(brow_f) X(dof_din) X(trunk_dof)                             \
   X(geom_type) X(geom_bodyid) X(pair_geom) X(pair_condim)                                                  \
   X(site_bodyid) X(tendon_adr) X(tendon_num) X(wrap_dofadr) X(wrap_qposadr)                                \
   X(act_trntype) X(act_trnid) X(act_actadr) X(act_ctrllimited) X(act_forcelimited)                         \
@@ -65,7 +66,7 @@ struct DModel {
   /* sizes */
   int nq, nv, nu, na, nbody, njnt, ngeom, npair, nsite, ntendon, nwrap, nsensor, nsensordata, nfluidbox, nfluidgeom;
   int nM, nlevel, ndlevel, ntri, nheavy;
-  int ntrunk, sprog_b_len, sprog_f_len, fpart_max;
+  int ntrunk, brow_len;
   int opt_iterations, opt_ls_iterations, opt_noslip_iterations, flags;
   /* task */
   int task_type, n_substeps, future_steps, action_dim, obs_dim, max_episode_steps, time_limit_steps;
@@ -224,76 +225,30 @@ std::string build_dmodel(const FlybModel* m, int flags, DModel<T>* out, FlyArena
       while (x != y && x >= 0 && y >= 0) { if (x > y) x = hpar[x]; else y = hpar[y]; }
       ncommon[(size_t)a * nv + b] = (x == y && x >= 0) ? (unsigned char)(hdepth[x] + 1) : 0;
     }
-  /* ---- lane programs (static schedules derived from the sparsity; see fly_dyn.cuh: fly_factor / fly_solve) */
-  if (d.nM >= 2047) return "tree-sparse matrix too large for the packed lane programs";
-  auto eaddr = [&](int row, int col) { return madr[row] + hdepth[row] - hdepth[col]; };  /* entry (row, ancestor col) */
-  /* factor: per level (deepest first) the entries (i, j) need  A(i,j) - sum_{c in desc(i)} L(c,i) U(c,j).  The sums
-     are cut into chunks of FLY_FCHUNK products, chunks are spread over lanes (longest first), each chunk writes a
-     partial into a slot; a second phase adds an entry's slots up and normalises. */
-  std::vector<int> fprog, fprog_lvl(3 * (maxhd + 1), 0), fent, fent_adr(maxhd + 2, 0);
-  int fpart_max = 1;
-  for (int L = maxhd; L >= 0; L--) {
-    struct Chunk { int slot; std::vector<int> ops; };
-    std::vector<Chunk> chunks;
-    fent_adr[maxhd - L] = (int)fent.size() / 2;
-    std::vector<std::pair<int, int> > slot_of_entry;  /* (first slot, count) in entry order */
-    std::vector<int> ent_i, ent_k;
-    for (int i = 0; i < nv; i++) if (hdepth[i] == L)
-      for (int k = 0; k <= L; k++) {
-        int j = mcol[madr[i] + k];
-        int first = (int)chunks.size(), cnt = 0;
-        std::vector<int> ops;
-        for (int c = i + 1; c <= hsublast[i]; c++) ops.push_back(eaddr(c, i) | (eaddr(c, j) << 11));
-        for (size_t q = 0; q < ops.size(); q += FLY_FCHUNK) {
-          Chunk ch; ch.slot = (int)chunks.size();
-          for (size_t t = q; t < ops.size() && t < q + FLY_FCHUNK; t++) ch.ops.push_back(ops[t]);
-          while ((int)ch.ops.size() < FLY_FCHUNK) ch.ops.push_back(d.nM | (d.nM << 11));  /* zero entry */
-          chunks.push_back(ch); cnt++;
-        }
-        slot_of_entry.push_back(std::make_pair(first, cnt));
-        ent_i.push_back(i); ent_k.push_back(k);
-      }
-    /* entry table: word0 = address | diag address << 11 | own chunk count << 22 ; word1 = first slot | diag first slot << 16 */
-    for (size_t e = 0; e < ent_i.size(); e++) {
-      int i = ent_i[e], k = ent_k[e];
-      size_t ediag = e - k;  /* entries of row i are consecutive, k = 0 first */
-      int w0 = (madr[i] + k) | (madr[i] << 11) | (slot_of_entry[e].second << 22);
-      int w1 = slot_of_entry[e].first | (slot_of_entry[ediag].first << 16);
-      if (slot_of_entry[e].second != slot_of_entry[ediag].second) return "internal: chunk count mismatch";
-      fent.push_back(w0); fent.push_back(w1);
-    }
-    int nch = (int)chunks.size();
-    if (nch > fpart_max) fpart_max = nch;
-    if (nch >= 65536) return "too many factor chunks";
-    int per_lane = (nch + 31) / 32;
-    fprog_lvl[3 * (maxhd - L)] = (int)fprog.size();
-    fprog_lvl[3 * (maxhd - L) + 1] = per_lane;
-    fprog_lvl[3 * (maxhd - L) + 2] = L;
-    /* chunks all cost the same, so round-robin is balanced: chunk q of lane l = chunks[q * 32 + l] */
-    for (int q = 0; q < per_lane; q++) {
-      for (int l = 0; l < 32; l++) { int id = q * 32 + l; fprog.push_back(id < nch ? chunks[id].slot : 65535); }
-      for (int t = 0; t < FLY_FCHUNK; t++)
-        for (int l = 0; l < 32; l++) { int id = q * 32 + l; fprog.push_back(id < nch ? chunks[id].ops[t] : (d.nM | (d.nM << 11))); }
-    }
-  }
-  fent_adr[maxhd + 1] = (int)fent.size() / 2;
-  d.fpart_max = fpart_max + 32;
-  /* solve: the trunk (heavy dofs) is handled cooperatively, every other subtree ("branch") by one lane */
+  /* ---- branch schedule of the tree-sparse factorisation and solves (fly_dyn.cuh: fly_factor / fly_solve).
+     Trunk = the dofs with many descendants (free root, or the ball): a chain at the top of the Hessian tree, kept in
+     registers by every lane.  Every other subtree hanging off the trunk is a "branch"; a branch is owned by ONE lane,
+     which walks its rows with no barrier inside.  Row descriptor: dof | in-branch depth << 8 | madr << 13. */
+  if (d.nM >= 2047) return "tree-sparse matrix too large for the packed row descriptors";
   std::vector<int> trunk;
   for (int i = 0; i < nv; i++) if (hsublast[i] - i > FLY_HEAVY) trunk.push_back(i);
-  for (size_t t = 0; t < trunk.size(); t++) if (hpar[trunk[t]] >= 0 && !(hsublast[hpar[trunk[t]]] - hpar[trunk[t]] > FLY_HEAVY)) return "trunk dofs must be closed under ancestors";
-  if (trunk.size() > 8) return "more than 8 trunk dofs";
+  if ((int)trunk.size() > FLY_MAXTRUNK) return "more than FLY_MAXTRUNK trunk dofs";
+  for (size_t t = 0; t < trunk.size(); t++)
+    if (hpar[trunk[t]] != (t ? trunk[t - 1] : -1) || hdepth[trunk[t]] != (int)t) return "trunk dofs must form a chain from the root";
   d.ntrunk = (int)trunk.size();
   std::vector<char> is_trunk(nv, 0);
   for (size_t t = 0; t < trunk.size(); t++) is_trunk[trunk[t]] = 1;
+  std::vector<int> dof_din(nv, -1);
+  for (int i = 0; i < nv; i++) if (!is_trunk[i]) dof_din[i] = (hpar[i] < 0 || is_trunk[hpar[i]]) ? 0 : dof_din[hpar[i]] + 1;
   struct Branch { int root; long cost; };
   std::vector<Branch> branches;
-  for (int i = 0; i < nv; i++) if (!is_trunk[i] && (hpar[i] < 0 || is_trunk[hpar[i]])) {
-    long cost = 0;
-    for (int c = i; c <= hsublast[i]; c++) cost += hdepth[c] + 1;
-    Branch b; b.root = i; b.cost = cost; branches.push_back(b);
+  for (int i = 0; i < nv; i++) if (!is_trunk[i] && dof_din[i] == 0) {
+    long cost = 0;  /* multiply-adds of the factorisation inside the branch */
+    for (int c = i; c <= hsublast[i]; c++)
+      for (int a = hpar[c]; a >= 0 && !is_trunk[a]; a = hpar[a]) cost += hdepth[a] + 1;
+    Branch b; b.root = i; b.cost = cost + 1; branches.push_back(b);
   }
-  std::vector<std::vector<int> > lane_br(32);
+  std::vector<std::vector<int> > lane_rows(32);
   {
     std::vector<long> load(32, 0);
     std::vector<int> order(branches.size());
@@ -301,56 +256,22 @@ std::string build_dmodel(const FlybModel* m, int flags, DModel<T>* out, FlyArena
     for (size_t a = 0; a < order.size(); a++) for (size_t b = a + 1; b < order.size(); b++) if (branches[order[b]].cost > branches[order[a]].cost) std::swap(order[a], order[b]);
     for (size_t a = 0; a < order.size(); a++) {
       int best = 0; for (int l = 1; l < 32; l++) if (load[l] < load[best]) best = l;
-      lane_br[best].push_back(order[a]); load[best] += branches[order[a]].cost;
+      int root = branches[order[a]].root;
+      for (int c = root; c <= hsublast[root]; c++) lane_rows[best].push_back(c);
+      load[best] += branches[order[a]].cost;
     }
   }
-  /* op word: L address (11) | x index (8) << 11 | kind (2) << 19 | target (8) << 21 ; kind 1: x[target] -= s (backward) or
-     y[target] = x[target] invD - s (forward); kind 2: trunk partial slot `target` of this lane = s */
-  auto trunk_index = [&](int dof) { for (size_t t = 0; t < trunk.size(); t++) if (trunk[t] == dof) return (int)t; return -1; };
-  std::vector<std::vector<int> > sb(32), sf(32);
+  size_t brow_len = 0;
+  for (int l = 0; l < 32; l++) { std::sort(lane_rows[l].begin(), lane_rows[l].end()); if (lane_rows[l].size() > brow_len) brow_len = lane_rows[l].size(); }
+  std::vector<int> brow_f(brow_len * 32 + 1, -1), brow_b(brow_len * 32 + 1, -1);
   for (int l = 0; l < 32; l++) {
-    for (size_t bi = 0; bi < lane_br[l].size(); bi++) {
-      int root = branches[lane_br[l][bi]].root;
-      for (int j = hsublast[root]; j >= root; j--) {  /* backward: descendants first */
-        std::vector<int> ops;
-        for (int c = j + 1; c <= hsublast[j]; c++) ops.push_back(eaddr(c, j) | (c << 11));
-        if (ops.empty()) ops.push_back(d.nM | (0 << 11));
-        ops.back() |= (1 << 19) | (j << 21);
-        sb[l].insert(sb[l].end(), ops.begin(), ops.end());
-      }
-    }
-    /* trunk partials: slot t accumulates over ALL branches of the lane */
-    for (size_t t = 0; t < trunk.size(); t++) {
-      std::vector<int> ops;
-      for (size_t bi = 0; bi < lane_br[l].size(); bi++) {
-        int root = branches[lane_br[l][bi]].root;
-        if (!(trunk[t] <= root && root <= hsublast[trunk[t]])) continue;
-        for (int c = root; c <= hsublast[root]; c++) ops.push_back(eaddr(c, trunk[t]) | (c << 11));
-      }
-      if (ops.empty()) ops.push_back(d.nM | (0 << 11));
-      ops.back() |= (2 << 19) | ((int)t << 21);
-      sb[l].insert(sb[l].end(), ops.begin(), ops.end());
-    }
-    for (size_t bi = 0; bi < lane_br[l].size(); bi++) {
-      int root = branches[lane_br[l][bi]].root;
-      for (int i = root; i <= hsublast[root]; i++) {  /* forward: ancestors first */
-        std::vector<int> ops;
-        for (int k = 1; k <= hdepth[i]; k++) ops.push_back((madr[i] + k) | (mcol[madr[i] + k] << 11));
-        if (ops.empty()) ops.push_back(d.nM | (0 << 11));
-        ops.back() |= (1 << 19) | (i << 21);
-        sf[l].insert(sf[l].end(), ops.begin(), ops.end());
-      }
+    size_t n = lane_rows[l].size();
+    for (size_t q = 0; q < n; q++) {
+      int i = lane_rows[l][q], word = i | (dof_din[i] << 8) | (madr[i] << 13);
+      brow_f[q * 32 + l] = word; brow_b[(n - 1 - q) * 32 + l] = word;
     }
   }
-  (void)trunk_index;
-  size_t lb = 0, lf = 0;
-  for (int l = 0; l < 32; l++) { if (sb[l].size() > lb) lb = sb[l].size(); if (sf[l].size() > lf) lf = sf[l].size(); }
-  std::vector<int> sprog_b(lb * 32, d.nM), sprog_f(lf * 32, d.nM);
-  for (int l = 0; l < 32; l++) {
-    for (size_t q = 0; q < sb[l].size(); q++) sprog_b[q * 32 + l] = sb[l][q];
-    for (size_t q = 0; q < sf[l].size(); q++) sprog_f[q * 32 + l] = sf[l][q];
-  }
-  d.sprog_b_len = (int)lb; d.sprog_f_len = (int)lf;
+  d.brow_len = (int)brow_len;
 
   /* triangle enumeration (a <= b < FLY_MAXCHAIN) used to spread a chain row's outer product over lanes */
   std::vector<int> tri_a, tri_b;
@@ -413,10 +334,14 @@ std::string build_dmodel(const FlybModel* m, int flags, DModel<T>* out, FlyArena
   d.dof_parentid = puti(vi(m->dof_parentid, nv));
   d.hpar = puti(hpar); d.hdepth = puti(hdepth); d.kdepth = puti(kdepth); d.hsublast = puti(hsublast);
   d.heavy_dof = puti(heavy_dof);
-  d.fprog = puti(fprog); d.fprog_lvl = puti(fprog_lvl); d.fent = puti(fent); d.fent_adr = puti(fent_adr);
-  d.sprog_b = puti(sprog_b); d.sprog_f = puti(sprog_f); d.trunk_dof = puti(trunk);
+  d.brow_b = puti(brow_b); d.brow_f = puti(brow_f); d.dof_din = puti(dof_din); d.trunk_dof = puti(trunk);
   d.ncommon = (const unsigned char*)(uintptr_t)arena->put(ncommon.data(), ncommon.size());
-  d.madr = puti(madr); d.mrow = puti(mrow); d.mcol = puti(mcol);
+  {
+    std::vector<int> mdiag(mcol.size() + 4, 0), mcolp(mcol);
+    for (size_t e = 0; e < mcol.size(); e++) mdiag[e] = madr[mcol[e]];  /* address of the diagonal of entry e's column */
+    mcolp.resize(mcol.size() + 4, 0);
+    d.madr = puti(madr); d.mrow = puti(mrow); d.mcol = puti(mcolp); d.mdiag = puti(mdiag);
+  }
   d.dlvl_adr = puti(dlvl_adr); d.dlvl_dof = puti(dlvl_dof); d.dlvl_nlight = puti(dlvl_nlight);
   d.desc_adr = puti(desc_adr); d.desc = puti(desc); d.tri_a = puti(tri_a); d.tri_b = puti(tri_b);
   d.geom_type = puti(vi(m->geom_type, m->ngeom)); d.geom_bodyid = puti(vi(m->geom_bodyid, m->ngeom));

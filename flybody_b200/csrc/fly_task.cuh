@@ -133,9 +133,9 @@ FLY_FN void fly_step1(const DModel<T>& m, const Ws<T>& w, bool full) {
   fly_com_pos(m, w);
   if (full) {
     fly_crb(m, w);
-    FLY_FOR(e, m.nM) w.qU[e] = w.qM[e];
+    FLY_FOR(e, m.nM) w.qLD[e] = w.qM[e];
     FLY_SYNC();
-    fly_factor(m, w, w.qU, w.qLD, w.qDinv);
+    fly_factor(m, w, w.qLD, w.qDinv);
     fly_collision(m, w);
     fly_make_constraint(m, w);
   }
@@ -167,11 +167,11 @@ FLY_FN void fly_integrate(const DModel<T>& m, const Ws<T>& w) {
   const T dt = m.timestep;
   FLY_FOR(e, m.nM) {
     const int i = m.mrow[e];
-    w.qU[e] = w.qM[e] + (e == m.madr[i] ? dt * m.dof_damping[i] : T(0));
+    w.qH[e] = w.qM[e] + (e == m.madr[i] ? dt * m.dof_damping[i] : T(0));
   }
   FLY_FOR(d, m.nv) w.stmp[d] = w.qfrc_smooth[d] + w.qfrc_constraint[d];
   FLY_SYNC();
-  fly_factor(m, w, w.qU, w.qH, w.qHinv);
+  fly_factor(m, w, w.qH, w.qHinv);
   fly_solve(m, w, w.qH, w.qHinv, w.stmp);
   FLY_FOR(i, m.na) w.act[i] += dt * w.act_dot[i];
   FLY_FOR(d, m.nv) { w.qvel[d] += dt * w.stmp[d]; w.warm[d] = w.qacc[d]; }

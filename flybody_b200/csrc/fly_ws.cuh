@@ -22,8 +22,8 @@
   X(geom_xpos, 3 * m.ngeom, 2) X(site_xpos, 3 * m.nsite, 0) X(site_xmat, 9 * m.nsite, 0)\
   X(scom, 3 * m.nbody, 2) X(cinert, 10 * m.nbody, 3) X(crb, 10 * m.nbody, 0)            \
   X(cdof, 6 * m.nv, 2) X(cdof_dot, 6 * m.nv, 3) X(cvel, 6 * m.nbody, 3)                 \
-  X(qM, m.nM + 1, 2) X(qLD, m.nM + 1, 1) X(qH, m.nM + 1, 1) X(qU, m.nM + 1, 1)                    \
-  X(qDinv, m.nv, 1) X(qHinv, m.nv, 1) X(fpart, m.fpart_max, 1) X(tpart, 8 * 32, 1)                                         \
+  X(qM, m.nM + 1, 2) X(qLD, m.nM + 1, 1) X(qH, m.nM + 1, 1)                    \
+  X(qDinv, m.nv, 1) X(qHinv, m.nv, 1)                                         \
   X(act_length, m.nu, 0) X(act_force, m.nu, 0) X(act_dot, m.na, 0)                      \
   X(qfrc_bias, m.nv, 0) X(qfrc_passive, m.nv, 0) X(qfrc_actuator, m.nv, 0)              \
   X(qfrc_smooth, m.nv, 1) X(qacc_smooth, m.nv, 1) X(qfrc_constraint, m.nv, 1)           \

@@ -88,7 +88,7 @@ struct Emu : EmuBase {
     if (s == "kinematics") fly_kinematics(m, w);
     else if (s == "com_pos") fly_com_pos(m, w);
     else if (s == "crb") fly_crb(m, w);
-    else if (s == "factor") { for (int e = 0; e < m.nM; e++) w.qU[e] = w.qM[e]; fly_factor(m, w, w.qU, w.qLD, w.qDinv); }
+    else if (s == "factor") { for (int e = 0; e < m.nM; e++) w.qLD[e] = w.qM[e]; fly_factor(m, w, w.qLD, w.qDinv); }
     else if (s == "collision") fly_collision(m, w);
     else if (s == "make_constraint") fly_make_constraint(m, w);
     else if (s == "step1") fly_step1(m, w, true);
