@@ -191,198 +191,216 @@ FLY_FN void fly_crb(const DModel<T>& m, const Ws<T>& w) {
 }
 
 /* ---------------------------------------------------------------- tree-sparse L^T D L, branch per lane
- * dst[0..n) -= t * src[0..n) for two rows of one array.  The loads of a block are issued before its stores (the
- * compiler cannot prove the rows do not overlap, and a load-FMA-store chain per element would expose the full
- * shared-memory latency n times). */
-template <class T>
-FLY_INL void fly_row_axpy(T* dst, const T* src, T t, int n) {
+ * NS matrices of the same sparsity are processed together (M and M + dt*damping share every index and branch, so
+ * the second one rides along in the shadow of the first one's memory latency).
+ *
+ * LD[s][ai..ai+n) -= t[s] * LD[s][as..as+n) for two rows of one array.  The loads of a block are issued before its
+ * stores: the compiler cannot prove the rows do not overlap, and a load-FMA-store chain per element would expose the
+ * full shared-memory latency n times. */
+template <class T, int NS>
+FLY_INL void fly_row_axpy(T* const* LD, int ai, int as, const T* t, int n) {
   int q = 0;
-  for (; q + 8 <= n; q += 8) {
-    const T s0 = src[q], s1 = src[q + 1], s2 = src[q + 2], s3 = src[q + 3], s4 = src[q + 4], s5 = src[q + 5], s6 = src[q + 6], s7 = src[q + 7];
-    const T d0 = dst[q], d1 = dst[q + 1], d2 = dst[q + 2], d3 = dst[q + 3], d4 = dst[q + 4], d5 = dst[q + 5], d6 = dst[q + 6], d7 = dst[q + 7];
-    dst[q] = d0 - t * s0; dst[q + 1] = d1 - t * s1; dst[q + 2] = d2 - t * s2; dst[q + 3] = d3 - t * s3;
-    dst[q + 4] = d4 - t * s4; dst[q + 5] = d5 - t * s5; dst[q + 6] = d6 - t * s6; dst[q + 7] = d7 - t * s7;
-  }
-  if (q + 4 <= n) {
-    const T s0 = src[q], s1 = src[q + 1], s2 = src[q + 2], s3 = src[q + 3];
-    const T d0 = dst[q], d1 = dst[q + 1], d2 = dst[q + 2], d3 = dst[q + 3];
-    dst[q] = d0 - t * s0; dst[q + 1] = d1 - t * s1; dst[q + 2] = d2 - t * s2; dst[q + 3] = d3 - t * s3;
-    q += 4;
+  for (; q + 4 <= n; q += 4) {
+    T sv[NS][4], dv[NS][4];
+#pragma unroll
+    for (int s = 0; s < NS; s++)
+#pragma unroll
+      for (int e = 0; e < 4; e++) { sv[s][e] = LD[s][as + q + e]; dv[s][e] = LD[s][ai + q + e]; }
+#pragma unroll
+    for (int s = 0; s < NS; s++)
+#pragma unroll
+      for (int e = 0; e < 4; e++) LD[s][ai + q + e] = dv[s][e] - t[s] * sv[s][e];
   }
   const int r = n - q;
   if (r > 0) {
-    const T s0 = src[q], s1 = r > 1 ? src[q + 1] : T(0), s2 = r > 2 ? src[q + 2] : T(0);
-    const T d0 = dst[q], d1 = r > 1 ? dst[q + 1] : T(0), d2 = r > 2 ? dst[q + 2] : T(0);
-    dst[q] = d0 - t * s0;
-    if (r > 1) dst[q + 1] = d1 - t * s1;
-    if (r > 2) dst[q + 2] = d2 - t * s2;
+    T sv[NS][3], dv[NS][3];
+#pragma unroll
+    for (int s = 0; s < NS; s++)
+#pragma unroll
+      for (int e = 0; e < 3; e++) { sv[s][e] = e < r ? LD[s][as + q + e] : T(0); dv[s][e] = e < r ? LD[s][ai + q + e] : T(0); }
+#pragma unroll
+    for (int s = 0; s < NS; s++)
+#pragma unroll
+      for (int e = 0; e < 3; e++) if (e < r) LD[s][ai + q + e] = dv[s][e] - t[s] * sv[s][e];
   }
 }
 
-/* In place: LD holds the matrix on entry (layout of qM: row i = A(i,i), A(i,parent), A(i,grandparent) ...) and
- * D_i on the diagonal / L(i,ancestor) off it on return; invD[i] = 1 / D_i.
+/* In place: LD[s] holds a matrix on entry (layout of qM: row i = A(i,i), A(i,parent), A(i,grandparent) ...) and
+ * D_i on the diagonal / L(i,ancestor) off it on return; invD[s][i] = 1 / D_i.
  * Phase 1: each lane eliminates the rows of its own branches, deepest dof first (the row updates stay inside the
- * branch: no barrier, no index stream).  Phase 2: the branch rows' trunk entries are normalised and their outer
- * products are summed into the small trunk block (registers + warp reduction).  Phase 3: the trunk block (a chain of
- * at most FLY_MAXTRUNK dofs) is eliminated in registers by every lane alike. */
-template <class T>
-FLY_FN void fly_factor(const DModel<T>& m, const Ws<T>& w, T* LD, T* invD) {
-  (void)w;
+ * branch: no barrier, no index stream).  Phase 2: one lane per entry of the small trunk block sums the outer products
+ * of the branch rows' trunk entries into it, then those entries are normalised.  Phase 3: the trunk chain (at most
+ * FLY_MAXTRUNK dofs) is eliminated with one lane per entry. */
+template <class T, int NS>
+FLY_FN void fly_factor(const DModel<T>& m, T* const* LD, T* const* invD) {
   FLY_FOR(l, 32) {
     for (int q = 0; q < m.brow_len; q++) {
       const int word = FLY_LDG(m.brow_b + q * 32 + l);
       if (word >= 0) {
         const int k = word & 255, dk = (word >> 8) & 31, ak = word >> 13, hk = FLY_LDG(m.hdepth + k);
-        const T inv = T(1) / LD[ak];
-        invD[k] = inv;
+        T inv[NS];
+#pragma unroll
+        for (int s = 0; s < NS; s++) { inv[s] = T(1) / LD[s][ak]; invD[s][k] = inv[s]; }
         int ai_next = FLY_LDG(m.mdiag + ak + 1);
         for (int r = 1; r <= dk; r++) {
           const int ai = ai_next;
           ai_next = FLY_LDG(m.mdiag + ak + r + 1);
-          const T t = LD[ak + r] * inv;
-          fly_row_axpy(LD + ai, LD + ak + r, t, hk - r + 1);
-          LD[ak + r] = t;
+          T t[NS];
+#pragma unroll
+          for (int s = 0; s < NS; s++) t[s] = LD[s][ak + r] * inv[s];
+          fly_row_axpy<T, NS>(LD, ai, ak + r, t, hk - r + 1);
+#pragma unroll
+          for (int s = 0; s < NS; s++) LD[s][ak + r] = t[s];
         }
       }
     }
   }
   FLY_SYNC();
-  const int nt = m.ntrunk;
+  const int nt = m.ntrunk, nb = m.nv - nt;
   if (nt == 0) return;
-  T acc[FLY_MAXTRUNK * (FLY_MAXTRUNK + 1) / 2];
+  FLY_FOR(p, nt * (nt + 1) / 2) {
+    const int j = FLY_LDG(m.tri_a + p), i = FLY_LDG(m.tri_b + p);
+    T acc[NS];
 #pragma unroll
-  for (int e = 0; e < FLY_MAXTRUNK * (FLY_MAXTRUNK + 1) / 2; e++) acc[e] = 0;
-  FLY_FOR(k, m.nv) {
-    const int dk = FLY_LDG(m.dof_din + k);
-    if (dk >= 0) {
-      const int ak = FLY_LDG(m.madr + k), hk = FLY_LDG(m.hdepth + k), ntk = hk - dk;
-      const T inv = invD[k];
-      T u[FLY_MAXTRUNK];
+    for (int s = 0; s < NS; s++) acc[s] = 0;
+#pragma unroll 2
+    for (int e = 0; e < nb; e++) {
+      const int word = FLY_LDG(m.bt_list + e), ae = word & 2047, ntk = (word >> 11) & 15, k = word >> 15;
+      if (i < ntk) {
 #pragma unroll
-      for (int q = 0; q < FLY_MAXTRUNK; q++) u[q] = q < ntk ? LD[ak + hk - q] : T(0);
-#pragma unroll
-      for (int i = 0; i < FLY_MAXTRUNK; i++) {
-        const T li = u[i] * inv;
-        if (i < ntk) LD[ak + hk - i] = li;
-#pragma unroll
-        for (int j = 0; j <= i; j++) acc[i * (i + 1) / 2 + j] += li * u[j];
+        for (int s = 0; s < NS; s++) acc[s] += LD[s][ae - i] * LD[s][ae - j] * invD[s][k];
       }
+    }
+    const int ti = FLY_LDG(m.trunk_adr + i);
+#pragma unroll
+    for (int s = 0; s < NS; s++) LD[s][ti + i - j] -= acc[s];
+  }
+  FLY_SYNC();
+  FLY_FOR(e, nb) {
+    const int word = FLY_LDG(m.bt_list + e), ae = word & 2047, ntk = (word >> 11) & 15, k = word >> 15;
+    for (int q = 0; q < ntk; q++) {
+#pragma unroll
+      for (int s = 0; s < NS; s++) LD[s][ae - q] *= invD[s][k];
     }
   }
-  int ta[FLY_MAXTRUNK];
+  for (int k = nt - 1; k >= 1; k--) {
+    const int ak = FLY_LDG(m.trunk_adr + k);
+    FLY_SYNC();
+    T dinv[NS];
 #pragma unroll
-  for (int i = 0; i < FLY_MAXTRUNK; i++) ta[i] = i < nt ? FLY_LDG(m.madr + FLY_LDG(m.trunk_dof + i)) : 0;
+    for (int s = 0; s < NS; s++) dinv[s] = T(1) / LD[s][ak];
+    FLY_FOR(p, k * (k + 1) / 2) {
+      const int j = FLY_LDG(m.tri_a + p), i = FLY_LDG(m.tri_b + p), ti = FLY_LDG(m.trunk_adr + i);
 #pragma unroll
-  for (int i = 0; i < FLY_MAXTRUNK; i++)
-    if (i < nt) {
-#pragma unroll
-      for (int j = 0; j <= i; j++) acc[i * (i + 1) / 2 + j] = LD[ta[i] + i - j] - warp_sum(acc[i * (i + 1) / 2 + j]);
+      for (int s = 0; s < NS; s++) LD[s][ti + i - j] -= LD[s][ak + k - i] * LD[s][ak + k - j] * dinv[s];
     }
+    FLY_SYNC();
+    FLY_FOR(i, k) {
 #pragma unroll
-  for (int k = FLY_MAXTRUNK - 1; k >= 0; k--)
-    if (k < nt) {
-      const T inv = T(1) / acc[k * (k + 1) / 2 + k];
-#pragma unroll
-      for (int i = k - 1; i >= 0; i--) {
-        const T t = acc[k * (k + 1) / 2 + i] * inv;
-#pragma unroll
-        for (int j = 0; j <= i; j++) acc[i * (i + 1) / 2 + j] -= t * acc[k * (k + 1) / 2 + j];
-        acc[k * (k + 1) / 2 + i] = t;
-      }
+      for (int s = 0; s < NS; s++) LD[s][ak + k - i] *= dinv[s];
     }
+  }
   FLY_SYNC();
-  FLY_LANE0 {
+  FLY_FOR(i, nt) {
 #pragma unroll
-    for (int i = 0; i < FLY_MAXTRUNK; i++)
-      if (i < nt) {
-        invD[FLY_LDG(m.trunk_dof + i)] = T(1) / acc[i * (i + 1) / 2 + i];
-#pragma unroll
-        for (int j = 0; j <= i; j++) LD[ta[i] + i - j] = acc[i * (i + 1) / 2 + j];
-      }
+    for (int s = 0; s < NS; s++) invD[s][FLY_LDG(m.trunk_dof + i)] = T(1) / LD[s][FLY_LDG(m.trunk_adr + i)];
   }
   FLY_SYNC();
 }
 
-/* x <- (L^T D L)^-1 x with the same ownership: branch rows by one lane (backward: scatter of the finished x[c] to
- * its in-branch ancestors; forward: gather over them), the trunk chain in registers in between. */
-template <class T>
-FLY_FN void fly_solve(const DModel<T>& m, const Ws<T>& w, const T* LD, const T* invD, T* x) {
-  (void)w;
+/* x[s] <- (L^T D L)[s]^-1 x[s] with the same ownership: branch rows by one lane (backward: scatter of the finished
+ * x[c] to its in-branch ancestors; forward: gather over them), the trunk chain in registers in between. */
+template <class T, int NS>
+FLY_FN void fly_solve(const DModel<T>& m, const T* const* LD, const T* const* invD, T* const* x) {
   FLY_FOR(l, 32) {
     for (int q = 0; q < m.brow_len; q++) {
       const int word = FLY_LDG(m.brow_b + q * 32 + l);
       if (word >= 0) {
         const int c = word & 255, dk = (word >> 8) & 31, a = word >> 13;
-        const T xc = x[c];
+        T xc[NS];
+#pragma unroll
+        for (int s = 0; s < NS; s++) xc[s] = x[s][c];
         for (int k = 1; k <= dk; k += 4) {
           const int n = dk - k + 1;
-          const int j0 = FLY_LDG(m.mcol + a + k), j1 = FLY_LDG(m.mcol + a + k + 1), j2 = FLY_LDG(m.mcol + a + k + 2), j3 = FLY_LDG(m.mcol + a + k + 3);
-          const T l0 = LD[a + k], l1 = n > 1 ? LD[a + k + 1] : T(0), l2 = n > 2 ? LD[a + k + 2] : T(0), l3 = n > 3 ? LD[a + k + 3] : T(0);
-          const T v0 = x[j0], v1 = n > 1 ? x[j1] : T(0), v2 = n > 2 ? x[j2] : T(0), v3 = n > 3 ? x[j3] : T(0);
-          x[j0] = v0 - l0 * xc;
-          if (n > 1) x[j1] = v1 - l1 * xc;
-          if (n > 2) x[j2] = v2 - l2 * xc;
-          if (n > 3) x[j3] = v3 - l3 * xc;
+          int j[4];
+          T lv[NS][4], v[NS][4];
+#pragma unroll
+          for (int e = 0; e < 4; e++) j[e] = FLY_LDG(m.mcol + a + k + e);
+#pragma unroll
+          for (int s = 0; s < NS; s++)
+#pragma unroll
+            for (int e = 0; e < 4; e++) { lv[s][e] = e < n ? LD[s][a + k + e] : T(0); v[s][e] = e < n ? x[s][j[e]] : T(0); }
+#pragma unroll
+          for (int s = 0; s < NS; s++)
+#pragma unroll
+            for (int e = 0; e < 4; e++) if (e < n) x[s][j[e]] = v[s][e] - lv[s][e] * xc[s];
         }
       }
     }
   }
   FLY_SYNC();
-  const int nt = m.ntrunk;
-  T y[FLY_MAXTRUNK];
+  const int nt = m.ntrunk, nb = m.nv - nt;
   if (nt > 0) {
-    T acc[FLY_MAXTRUNK];
+    T acc[NS][FLY_MAXTRUNK], y[NS][FLY_MAXTRUNK];
 #pragma unroll
-    for (int q = 0; q < FLY_MAXTRUNK; q++) acc[q] = 0;
-    FLY_FOR(c, m.nv) {
-      const int dk = FLY_LDG(m.dof_din + c);
-      if (dk >= 0) {
-        const int a = FLY_LDG(m.madr + c), hk = FLY_LDG(m.hdepth + c), ntc = hk - dk;
-        const T xc = x[c];
+    for (int s = 0; s < NS; s++)
 #pragma unroll
-        for (int q = 0; q < FLY_MAXTRUNK; q++) if (q < ntc) acc[q] += LD[a + hk - q] * xc;
+      for (int q = 0; q < FLY_MAXTRUNK; q++) acc[s][q] = 0;
+    FLY_FOR(e, nb) {
+      const int word = FLY_LDG(m.bt_list + e), ae = word & 2047, ntk = (word >> 11) & 15, c = word >> 15;
+#pragma unroll
+      for (int s = 0; s < NS; s++) {
+        const T xc = x[s][c];
+#pragma unroll
+        for (int q = 0; q < FLY_MAXTRUNK; q++) if (q < ntk) acc[s][q] += LD[s][ae - q] * xc;
       }
     }
     int ta[FLY_MAXTRUNK], td[FLY_MAXTRUNK];
 #pragma unroll
     for (int i = 0; i < FLY_MAXTRUNK; i++) {
       td[i] = i < nt ? FLY_LDG(m.trunk_dof + i) : 0;
-      ta[i] = FLY_LDG(m.madr + td[i]);
+      ta[i] = i < nt ? FLY_LDG(m.trunk_adr + i) : 0;
     }
-    T xt[FLY_MAXTRUNK];
 #pragma unroll
-    for (int k = FLY_MAXTRUNK - 1; k >= 0; k--) {
-      xt[k] = 0;
-      if (k < nt) {
-        T s = warp_sum(acc[k]);
+    for (int s = 0; s < NS; s++) {
+      T xt[FLY_MAXTRUNK];
 #pragma unroll
-        for (int k2 = k + 1; k2 < FLY_MAXTRUNK; k2++) if (k2 < nt) s += LD[ta[k2] + k2 - k] * xt[k2];
-        xt[k] = x[td[k]] - s;
+      for (int k = FLY_MAXTRUNK - 1; k >= 0; k--) {
+        xt[k] = 0;
+        if (k < nt) {
+          T sum = warp_sum(acc[s][k]);
+#pragma unroll
+          for (int k2 = k + 1; k2 < FLY_MAXTRUNK; k2++) if (k2 < nt) sum += LD[s][ta[k2] + k2 - k] * xt[k2];
+          xt[k] = x[s][td[k]] - sum;
+        }
       }
-    }
 #pragma unroll
-    for (int k = 0; k < FLY_MAXTRUNK; k++) {
-      y[k] = 0;
-      if (k < nt) {
-        T s = 0;
+      for (int k = 0; k < FLY_MAXTRUNK; k++) {
+        y[s][k] = 0;
+        if (k < nt) {
+          T sum = 0;
 #pragma unroll
-        for (int k2 = 0; k2 < k; k2++) s += LD[ta[k] + k - k2] * y[k2];
-        y[k] = xt[k] * invD[td[k]] - s;
+          for (int k2 = 0; k2 < k; k2++) sum += LD[s][ta[k] + k - k2] * y[s][k2];
+          y[s][k] = xt[k] * invD[s][td[k]] - sum;
+        }
       }
     }
     FLY_SYNC();
     FLY_LANE0 {
 #pragma unroll
-      for (int k = 0; k < FLY_MAXTRUNK; k++) if (k < nt) x[td[k]] = y[k];
-    }
-    FLY_FOR(c, m.nv) {
-      const int dk = FLY_LDG(m.dof_din + c);
-      if (dk >= 0) {
-        const int a = FLY_LDG(m.madr + c), hk = FLY_LDG(m.hdepth + c), ntc = hk - dk;
-        T s = 0;
+      for (int s = 0; s < NS; s++)
 #pragma unroll
-        for (int q = 0; q < FLY_MAXTRUNK; q++) if (q < ntc) s += LD[a + hk - q] * y[q];
-        x[c] -= s * LD[a];
+        for (int k = 0; k < FLY_MAXTRUNK; k++) if (k < nt) x[s][td[k]] = y[s][k];
+    }
+    FLY_FOR(e, nb) {
+      const int word = FLY_LDG(m.bt_list + e), ae = word & 2047, ntk = (word >> 11) & 15, c = word >> 15;
+      const int a = FLY_LDG(m.madr + c);
+#pragma unroll
+      for (int s = 0; s < NS; s++) {
+        T sum = 0;
+#pragma unroll
+        for (int q = 0; q < FLY_MAXTRUNK; q++) if (q < ntk) sum += LD[s][ae - q] * y[s][q];
+        x[s][c] -= sum * LD[s][a];
       }
     }
     FLY_SYNC();
@@ -392,10 +410,17 @@ FLY_FN void fly_solve(const DModel<T>& m, const Ws<T>& w, const T* LD, const T* 
       const int word = FLY_LDG(m.brow_f + q * 32 + l);
       if (word >= 0) {
         const int i = word & 255, dk = (word >> 8) & 31, a = word >> 13;
-        T s = 0;
+        T sum[NS];
+#pragma unroll
+        for (int s = 0; s < NS; s++) sum[s] = 0;
 #pragma unroll 4
-        for (int k = 1; k <= dk; k++) s += LD[a + k] * x[FLY_LDG(m.mcol + a + k)];
-        x[i] = x[i] * invD[i] - s;
+        for (int k = 1; k <= dk; k++) {
+          const int j = FLY_LDG(m.mcol + a + k);
+#pragma unroll
+          for (int s = 0; s < NS; s++) sum[s] += LD[s][a + k] * x[s][j];
+        }
+#pragma unroll
+        for (int s = 0; s < NS; s++) x[s][i] = x[s][i] * invD[s][i] - sum[s];
       }
     }
   }

@@ -189,138 +189,126 @@ FLY_INL FlyClipView fly_clip_view(const DModel<T>& m, const FlyClips& clips, int
   return v;
 }
 
-/* episode reset of the env whose state sits in w; returns step_type FIRST */
-template <class T>
-FLY_FN int fly_env_reset(const DModel<T>& m, const Ws<T>& w, const FlyClips& clips, const FlyIO<T>& io, int env,
-                         int* sint, float* obs) {
-  int clip_id = sint[FLY_SI_FORCED_CLIP];
-  const int episode = sint[FLY_SI_EPISODE];
-  if (clip_id < 0 && clips.nclips > 0)  /* trajectory_loaders.py:122,184: random_state.choice over clips */
-    clip_id = (int)(fly_hash(io.seed ^ fly_hash(((unsigned long long)(io.env_offset + env) << 24) ^ (unsigned long long)episode))
-                    % (unsigned long long)clips.nclips);
-  const FlyClipView clip = fly_clip_view(m, clips, clip_id);
-  FLY_FOR(i, m.nq) w.qpos[i] = m.qpos_reset[i];
-  FLY_FOR(i, m.nv) { w.qvel[i] = 0; w.warm[i] = 0; w.qacc[i] = 0; }
-  FLY_FOR(i, m.na) w.act[i] = 0;
-  FLY_FOR(i, m.nu) w.ctrl[i] = 0;
-  FLY_FOR(i, m.nsensordata) { w.sens_sum[i] = 0; w.sensordata[i] = 0; }
-  FLY_SYNC();
-  int episode_steps = m.max_episode_steps;
-  if (m.task_type == FLYB_TASK_WALK_IMITATION && clip.rows) {
-    const int snippet = clip.T - m.future_steps - 1;  /* walk_imitation.py:101-102 */
-    if (snippet < episode_steps) episode_steps = snippet;
-    const float* r = clip.rows;                        /* walk_imitation.py:119 */
-    FLY_FOR(k, 7) w.qpos[m.root_qposadr + k] = (T)r[k];
-    FLY_FOR(i, m.n_mocap_joints) w.qpos[m.jnt_qposadr[m.mocap_joint[i]]] = (T)r[7 + i];
-    FLY_SYNC();
-    fly_set_ghost(m, w, clip, 0, false);
-  }
-  fly_step1(m, w, true);
-  fly_forward_acc(m, w);
-  fly_accumulate(m, w);
-  fly_write_obs(m, w, clip, 0, obs, m.pad_first_obs ? T(1) : T(1) / T(m.n_substeps));
-  FLY_LANE0 {
-    sint[FLY_SI_STEP] = 0; sint[FLY_SI_EPISODE_STEPS] = episode_steps; sint[FLY_SI_RESET_NEXT] = 0;
-    sint[FLY_SI_CLIP] = clip_id; sint[FLY_SI_EPISODE] = episode + 1; sint[FLY_SI_EPLEN] = 0;
-  }
-  FLY_SYNC();
-  return 0;
-}
-
-/* one control step; returns step_type */
-template <class T>
-FLY_FN int fly_env_step(const DModel<T>& m, const Ws<T>& w, const FlyClips& clips, const float* action_in, int* sint,
-                        float* obs, T* reward, T* discount, int* fatal_out) {
-  const FlyClipView clip = fly_clip_view(m, clips, sint[FLY_SI_CLIP]);
-  int step = sint[FLY_SI_STEP];
-  if (m.task_type == FLYB_TASK_WALK_IMITATION) fly_set_ghost(m, w, clip, step, true);
-  FLY_FOR(a, m.nu) {  /* fruitfly.py:480-492 ; NaN -> 0 walk_imitation.py:147 */
-    const int ai = m.ctrl_action[a];
-    T v = ai >= 0 ? (T)action_in[ai] : T(0);
-    if (v != v) v = 0;
-    w.ctrl[a] = v;
-  }
-  FLY_FOR(k, m.nsensordata) w.sens_sum[k] = 0;
-  FLY_SYNC();
-  step += 1;  /* tasks/base.py:192 */
-  fly_step1(m, w, true);
-  for (int s = 0; s < m.n_substeps; s++) {
-    fly_forward_acc(m, w);
-    fly_integrate(m, w);
-    fly_step1(m, w, s < m.n_substeps - 1);
-    fly_accumulate(m, w);
-  }
-  /* termination: tasks/base.py:214-217, walk_imitation.py:165-191, walk_on_ball.py:75-79 */
-  T qn = 0;
-  FLY_FOR(d, m.nv) qn += w.qacc[d] * w.qacc[d];
-  qn = warp_sum(qn);
-  int fatal = !(sqrt(qn) <= m.terminal_qacc), reached_end = 0;  /* NaN counts as divergence */
-  if (m.task_type != FLYB_TASK_FLIGHT_IMITATION) {
-    T lv[6];
-    const int site = m.thorax_site;
-    fly_local_velocity(m, w, lv, m.site_bodyid[site], w.site_xpos + 3 * site, w.site_xmat + 9 * site);
-    if (norm3(lv + 3) > m.terminal_linvel || norm3(lv) > m.terminal_angvel) fatal = 1;
-  }
-  fly_write_obs(m, w, clip, step, obs, T(1) / T(m.n_substeps));
-  T r = 1;
-  if (m.task_type == FLYB_TASK_WALK_IMITATION) {
-    reached_end = step == sint[FLY_SI_EPISODE_STEPS];
-    if (clip.rows && norm3(w.obs_tmp) > m.terminal_com_dist) fatal = 1;
-    r = fly_walk_imitation_reward(m, w, clip, step);
-  } else if (m.task_type == FLYB_TASK_WALK_ON_BALL) {  /* walk_on_ball.py:61-73: tolerance(linear, margin 6) */
-    const T tgt[3] = {0, -5, 0};
-    for (int k = 0; k < 3; k++) {
-      const T x = fabs_(w.qvel[m.ball_dofadr + k] - tgt[k]) / T(6);
-      r *= x < 1 ? 1 - x : T(0);
-    }
-  }
-  *reward = r;
-  const int terminate = fatal || reached_end;
-  *discount = (m.task_type == FLYB_TASK_WALK_ON_BALL) ? (terminate ? T(0) : T(1)) : ((terminate && !reached_end) ? T(0) : T(1));
-  *fatal_out = fatal;
-  int st = 1;
-  FLY_SYNC();
-  FLY_LANE0 {
-    sint[FLY_SI_STEP] = step;
-    sint[FLY_SI_EPLEN] += 1;
-    if (terminate || step >= m.time_limit_steps) sint[FLY_SI_RESET_NEXT] = 1;
-  }
-  if (terminate || step >= m.time_limit_steps) st = 2;
-  FLY_SYNC();
-  return st;
-}
-
-/* the whole job of one warp for one env: load state, reset or step, store state and outputs */
+/* The whole job of one warp for one env and one call: load the state, reset the episode OR advance it by one control
+ * step, store state and outputs.  Reset and step share one pass through the pipeline (each stage has a single call
+ * site, so that the fully inlined kernel holds one copy of it):
+ *   reset: step1, forward_acc                                 (mj_forward of the initial state)
+ *   step : step1, n_substeps x [forward_acc, integrate, step1] (dm_control's legacy order: mj_step2 then mj_step1) */
 template <class T>
 FLY_FN void fly_env_run(const DModel<T>& m, const Ws<T>& w, const FlyClips& clips, const FlyIO<T>& io, int env) {
+  if (env < 0) { fly_block_pad(fly_nb_control_step(m)); return; }  /* idle warp of a block that still has work */
   T* sr = io.sreal + (size_t)env * io.sreal_stride;
-  int* si = io.sint + (size_t)env * FLY_SI_COUNT;
+  int* sint = io.sint + (size_t)env * FLY_SI_COUNT;
   float* obs = io.obs + (size_t)env * m.obs_dim;
   FLY_LANE0 for (int k = 0; k < 16; k++) w.counts[k] = 0;
-  const bool do_reset = io.force_reset ? (!io.reset_mask || io.reset_mask[env]) : si[FLY_SI_RESET_NEXT] != 0;
-  if (io.force_reset && !do_reset) return;
+  const bool do_reset = io.force_reset ? (!io.reset_mask || io.reset_mask[env]) : sint[FLY_SI_RESET_NEXT] != 0;
+  if (io.force_reset && !do_reset) { fly_block_pad(fly_nb_control_step(m)); return; }
   T *s_qpos = sr, *s_qvel = sr + m.nq, *s_act = s_qvel + m.nv, *s_warm = s_act + m.na, *s_ret = s_warm + m.nv;
-  int st;
-  T reward = 0, discount = 1;
-  int fatal = 0;
   FLY_SYNC();
+  int clip_id, step = 0, episode_steps = m.max_episode_steps;
+  const int episode = sint[FLY_SI_EPISODE];
+  FlyClipView clip;
   if (do_reset) {
-    st = fly_env_reset(m, w, clips, io, env, si, obs);
-    FLY_LANE0 s_ret[0] = 0;
+    clip_id = sint[FLY_SI_FORCED_CLIP];
+    if (clip_id < 0 && clips.nclips > 0)  /* trajectory_loaders.py:122,184: random_state.choice over clips */
+      clip_id = (int)(fly_hash(io.seed ^ fly_hash(((unsigned long long)(io.env_offset + env) << 24) ^ (unsigned long long)episode))
+                      % (unsigned long long)clips.nclips);
+    clip = fly_clip_view(m, clips, clip_id);
+    FLY_FOR(i, m.nq) w.qpos[i] = m.qpos_reset[i];
+    FLY_FOR(i, m.nv) { w.qvel[i] = 0; w.warm[i] = 0; w.qacc[i] = 0; }
+    FLY_FOR(i, m.na) w.act[i] = 0;
+    FLY_FOR(i, m.nu) w.ctrl[i] = 0;
+    FLY_FOR(i, m.nsensordata) { w.sens_sum[i] = 0; w.sensordata[i] = 0; }
+    FLY_SYNC();
+    if (m.task_type == FLYB_TASK_WALK_IMITATION && clip.rows) {
+      const int snippet = clip.T - m.future_steps - 1;  /* walk_imitation.py:101-102 */
+      if (snippet < episode_steps) episode_steps = snippet;
+      const float* r = clip.rows;                        /* walk_imitation.py:119 */
+      FLY_FOR(k, 7) w.qpos[m.root_qposadr + k] = (T)r[k];
+      FLY_FOR(i, m.n_mocap_joints) w.qpos[m.jnt_qposadr[m.mocap_joint[i]]] = (T)r[7 + i];
+      FLY_SYNC();
+    }
   } else {
     FLY_FOR(i, m.nq) w.qpos[i] = s_qpos[i];
     FLY_FOR(i, m.nv) { w.qvel[i] = s_qvel[i]; w.warm[i] = s_warm[i]; }
     FLY_FOR(i, m.na) w.act[i] = s_act[i];
+    const float* action_in = io.action + (size_t)env * m.action_dim;
+    FLY_FOR(a, m.nu) {  /* fruitfly.py:480-492 ; NaN -> 0 walk_imitation.py:147 */
+      const int ai = m.ctrl_action[a];
+      T v = ai >= 0 ? (T)action_in[ai] : T(0);
+      if (v != v) v = 0;
+      w.ctrl[a] = v;
+    }
+    FLY_FOR(k, m.nsensordata) w.sens_sum[k] = 0;
+    clip_id = sint[FLY_SI_CLIP];
+    clip = fly_clip_view(m, clips, clip_id);
+    step = sint[FLY_SI_STEP];
+    episode_steps = sint[FLY_SI_EPISODE_STEPS];
     FLY_SYNC();
-    st = fly_env_step(m, w, clips, io.action + (size_t)env * m.action_dim, si, obs, &reward, &discount, &fatal);
+  }
+  if (m.task_type == FLYB_TASK_WALK_IMITATION && (clip.rows || !do_reset)) fly_set_ghost(m, w, clip, step, !do_reset);
+  if (!do_reset) step += 1;  /* tasks/base.py:192 */
+  const int nsub = do_reset ? 0 : m.n_substeps;
+  for (int it = 0;; it++) {
+    fly_step1(m, w, it == 0 || it < nsub);
+    if (it > 0) fly_accumulate(m, w);
+    if (it == nsub && !do_reset) break;
+    fly_forward_acc(m, w);
+    if (do_reset) { fly_accumulate(m, w); break; }
+    fly_integrate(m, w);
+  }
+  if (do_reset) fly_block_pad(fly_nb_control_step(m) - FLY_NB_STEP1 - FLY_NB_FWD);
+  int st = 0, fatal = 0;
+  T reward = 0, discount = 1;
+  fly_write_obs(m, w, clip, step, obs, (do_reset && m.pad_first_obs) ? T(1) : T(1) / T(m.n_substeps));
+  if (do_reset) {
     FLY_LANE0 {
+      sint[FLY_SI_STEP] = 0; sint[FLY_SI_EPISODE_STEPS] = episode_steps; sint[FLY_SI_RESET_NEXT] = 0;
+      sint[FLY_SI_CLIP] = clip_id; sint[FLY_SI_EPISODE] = episode + 1; sint[FLY_SI_EPLEN] = 0;
+      s_ret[0] = 0;
+    }
+  } else {
+    /* termination: tasks/base.py:214-217, walk_imitation.py:165-191, walk_on_ball.py:75-79 */
+    T qn = 0;
+    FLY_FOR(d, m.nv) qn += w.qacc[d] * w.qacc[d];
+    qn = warp_sum(qn);
+    int reached_end = 0;
+    fatal = !(sqrt(qn) <= m.terminal_qacc);  /* NaN counts as divergence */
+    if (m.task_type != FLYB_TASK_FLIGHT_IMITATION) {
+      T lv[6];
+      const int site = m.thorax_site;
+      fly_local_velocity(m, w, lv, m.site_bodyid[site], w.site_xpos + 3 * site, w.site_xmat + 9 * site);
+      if (norm3(lv + 3) > m.terminal_linvel || norm3(lv) > m.terminal_angvel) fatal = 1;
+    }
+    T r = 1;
+    if (m.task_type == FLYB_TASK_WALK_IMITATION) {
+      reached_end = step == episode_steps;
+      if (clip.rows && norm3(w.obs_tmp) > m.terminal_com_dist) fatal = 1;
+      r = fly_walk_imitation_reward(m, w, clip, step);
+    } else if (m.task_type == FLYB_TASK_WALK_ON_BALL) {  /* walk_on_ball.py:61-73: tolerance(linear, margin 6) */
+      const T tgt[3] = {0, -5, 0};
+      for (int k = 0; k < 3; k++) {
+        const T x = fabs_(w.qvel[m.ball_dofadr + k] - tgt[k]) / T(6);
+        r *= x < 1 ? 1 - x : T(0);
+      }
+    }
+    reward = r;
+    const int terminate = fatal || reached_end;
+    discount = (m.task_type == FLYB_TASK_WALK_ON_BALL) ? (terminate ? T(0) : T(1)) : ((terminate && !reached_end) ? T(0) : T(1));
+    st = (terminate || step >= m.time_limit_steps) ? 2 : 1;
+    FLY_SYNC();
+    FLY_LANE0 {
+      sint[FLY_SI_STEP] = step;
+      sint[FLY_SI_EPLEN] += 1;
+      if (st == 2) sint[FLY_SI_RESET_NEXT] = 1;
       s_ret[0] += reward;
       if (st == 2 && io.stats) {
         float* o = io.stats + 4 * (size_t)env;
-        o[0] += (float)s_ret[0]; o[1] += (float)si[FLY_SI_EPLEN]; o[2] += (float)fatal; o[3] += 1.0f;
+        o[0] += (float)s_ret[0]; o[1] += (float)sint[FLY_SI_EPLEN]; o[2] += (float)fatal; o[3] += 1.0f;
       }
     }
   }
+  FLY_SYNC();
   FLY_FOR(i, m.nq) s_qpos[i] = w.qpos[i];
   FLY_FOR(i, m.nv) { s_qvel[i] = w.qvel[i]; s_warm[i] = w.warm[i]; }
   FLY_FOR(i, m.na) s_act[i] = w.act[i];

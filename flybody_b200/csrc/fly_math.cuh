@@ -15,11 +15,14 @@
 
 #if defined(__CUDACC__) && !defined(FLY_EMU)
 #define FLY_GPU 1
-#define FLY_FN __device__ __noinline__
+#define FLY_FN __device__ __forceinline__
 #define FLY_INL __device__ __forceinline__
 #define FLY_LANE() ((int)(threadIdx.x & 31))
 #define FLY_FOR(i, n) for (int i = FLY_LANE(); i < (n); i += 32)
 #define FLY_SYNC() __syncwarp()
+/* block-wide rendezvous of the warps of a block (each steps its own env): keeps them in the same stage so that
+ * instruction fetches and model-table lines are shared in the SM's caches.  Every warp must pass the same number. */
+#define FLY_BLOCK_SYNC() __syncthreads()
 #define FLY_LANE0 if (FLY_LANE() == 0)
 #define FLY_LDG(p) __ldg(p)
 template <class T> FLY_INL T warp_sum(T v) {
@@ -58,6 +61,7 @@ template <class P> FLY_INL int warp_compact(int n, P pred, unsigned short* out, 
 #define FLY_LANE() 0
 #define FLY_FOR(i, n) for (int i = 0; i < (n); i++)
 #define FLY_SYNC()
+#define FLY_BLOCK_SYNC()
 #define FLY_LANE0
 #define FLY_LDG(p) (*(p))
 template <class T> FLY_INL T warp_sum(T v) { return v; }

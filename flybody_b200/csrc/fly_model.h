@@ -37,7 +37,7 @@ enum { FLY_OPT_NOCONTACT = 1, FLY_OPT_NOLIMIT = 2, FLY_OPT_NOFLUID = 4, FLY_OPT_
   X(jnt_type) X(jnt_qposadr) X(jnt_dofadr) X(jnt_bodyid) X(jnt_limited)                                    \
   X(dof_bodyid) X(dof_jntid) X(dof_parentid) X(hpar) X(hdepth) X(kdepth) X(hsublast) X(madr) X(mrow) X(mcol) X(mdiag)\
   X(dlvl_adr) X(dlvl_dof) X(dlvl_nlight) X(heavy_dof) X(desc_adr) X(desc) X(tri_a) X(tri_b)                  \
-  X(brow_b) X(brow_f) X(dof_din) X(trunk_dof)                             \
+  X(brow_b) X(brow_f) X(dof_din) X(trunk_dof) X(trunk_adr) X(bt_list)                             \
   X(geom_type) X(geom_bodyid) X(pair_geom) X(pair_condim)                                                  \
   X(site_bodyid) X(tendon_adr) X(tendon_num) X(wrap_dofadr) X(wrap_qposadr)                                \
   X(act_trntype) X(act_trnid) X(act_actadr) X(act_ctrllimited) X(act_forcelimited)                         \
@@ -272,6 +272,11 @@ std::string build_dmodel(const FlybModel* m, int flags, DModel<T>* out, FlyArena
     }
   }
   d.brow_len = (int)brow_len;
+  /* non-trunk dofs: address of the LAST entry of the row (the one towards trunk dof 0) | trunk ancestors << 11 | dof << 15 */
+  std::vector<int> bt_list, trunk_adr;
+  for (int i = 0; i < nv; i++) if (!is_trunk[i]) bt_list.push_back((madr[i] + hdepth[i]) | ((hdepth[i] - dof_din[i]) << 11) | (i << 15));
+  for (size_t t = 0; t < trunk.size(); t++) trunk_adr.push_back(madr[trunk[t]]);
+  bt_list.push_back(0); trunk_adr.push_back(0);
 
   /* triangle enumeration (a <= b < FLY_MAXCHAIN) used to spread a chain row's outer product over lanes */
   std::vector<int> tri_a, tri_b;
@@ -335,6 +340,7 @@ std::string build_dmodel(const FlybModel* m, int flags, DModel<T>* out, FlyArena
   d.hpar = puti(hpar); d.hdepth = puti(hdepth); d.kdepth = puti(kdepth); d.hsublast = puti(hsublast);
   d.heavy_dof = puti(heavy_dof);
   d.brow_b = puti(brow_b); d.brow_f = puti(brow_f); d.dof_din = puti(dof_din); d.trunk_dof = puti(trunk);
+  d.trunk_adr = puti(trunk_adr); d.bt_list = puti(bt_list);
   d.ncommon = (const unsigned char*)(uintptr_t)arena->put(ncommon.data(), ncommon.size());
   {
     std::vector<int> mdiag(mcol.size() + 4, 0), mcolp(mcol);

@@ -267,7 +267,7 @@ FLY_FN void fly_newton(const DModel<T>& m, const Ws<T>& w) {
   const int nv = m.nv, nefc = w.counts[FLY_C_NEFC];
   int niter = 0;
   if (nefc == 0) {
-    FLY_FOR(d, nv) { w.qacc[d] = w.qacc_smooth[d]; w.qfrc_constraint[d] = 0; }
+    FLY_FOR(d, nv) { w.qfrc_constraint[d] = 0; w.stmp[d] = 0; w.sgrad[d] = 0; }
     FLY_LANE0 w.counts[FLY_C_NITER] = 0;
     FLY_SYNC();
     return;
@@ -377,16 +377,13 @@ FLY_FN void fly_newton(const DModel<T>& m, const Ws<T>& w) {
     niter = it + 1;
     if (scale * (old - cost) < m.tolerance) break;
   }
+  /* the iterate is qacc = qacc_smooth + theta d + M^-1 J^T c: leave J^T c in stmp and theta d in sgrad for the caller's
+     solve (with noslip the caller recomputes qacc from the final forces instead) */
+  FLY_FOR(r, nefc) w.efc_lam[r] = (T)c[r];
+  FLY_FOR(d, nv) w.sgrad[d] = (T)theta * dvec[d];
+  FLY_SYNC();
+  fly_jt_mul(m, w, w.stmp, w.efc_lam);
   fly_jt_mul(m, w, w.qfrc_constraint, f);
-  if ((m.flags & FLY_OPT_NONOSLIP) || m.opt_noslip_iterations <= 0) {
-    /* qacc = qacc_smooth + theta d + M^-1 J^T c (with noslip the caller recomputes qacc from the final forces) */
-    FLY_FOR(r, nefc) w.efc_lam[r] = (T)c[r];
-    FLY_SYNC();
-    fly_jt_mul(m, w, w.stmp, w.efc_lam);
-    fly_solve(m, w, w.qLD, w.qDinv, w.stmp);
-    FLY_FOR(d, nv) w.qacc[d] = w.qacc_smooth[d] + (T)theta * dvec[d] + w.stmp[d];
-    FLY_SYNC();
-  }
   FLY_LANE0 w.counts[FLY_C_NITER] = niter;
   FLY_SYNC();
 }
@@ -458,11 +455,20 @@ FLY_FN void fly_fwd_constraint(const DModel<T>& m, const Ws<T>& w) {
   if (nefc && !(m.flags & FLY_OPT_NONOSLIP) && m.opt_noslip_iterations > 0) {
     fly_noslip(m, w);
     /* qacc = qacc_smooth + M^-1 J^T f */
-    FLY_FOR(d, m.nv) w.stmp[d] = w.qfrc_constraint[d];
-    FLY_SYNC();
-    fly_solve(m, w, w.qLD, w.qDinv, w.stmp);
-    FLY_FOR(d, m.nv) w.qacc[d] = w.qacc_smooth[d] + w.stmp[d];
+    FLY_FOR(d, m.nv) { w.stmp[d] = w.qfrc_constraint[d]; w.sgrad[d] = 0; }
     FLY_SYNC();
   }
+  /* Two solves with one walk over the tree: M^-1 stmp for qacc, and the implicit-damping solve of the Euler step
+     (m13), (M + dt B)^-1 (qfrc_smooth + qfrc_constraint), whose right-hand side is final here as well. */
+  FLY_FOR(d, m.nv) w.sMa[d] = w.qfrc_smooth[d] + w.qfrc_constraint[d];
+  FLY_SYNC();
+  {
+    const T* LD[2] = {w.qLD, w.qH};
+    const T* iv[2] = {w.qDinv, w.qHinv};
+    T* x[2] = {w.stmp, w.sMa};
+    fly_solve<T, 2>(m, LD, iv, x);
+  }
+  FLY_FOR(d, m.nv) w.qacc[d] = w.qacc_smooth[d] + w.sgrad[d] + w.stmp[d];
+  FLY_SYNC();
 }
 #endif

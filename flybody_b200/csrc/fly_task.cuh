@@ -126,19 +126,47 @@ FLY_FN void fly_sensors_vel(const DModel<T>& m, const Ws<T>& w) {
   FLY_SYNC();
 }
 
-/* ---------------------------------------------------------------- pipeline pieces */
+/* ---------------------------------------------------------------- pipeline pieces
+ * Block rendezvous points (FLY_BLOCK_SYNC): 3 in fly_step1, 3 in fly_forward_acc, 1 in fly_integrate.  A warp that
+ * does less than a full control step (reset, masked or idle) makes the difference up with fly_block_pad. */
+#define FLY_NB_STEP1 3
+#define FLY_NB_FWD 3
+#define FLY_NB_INT 1
+template <class T>
+FLY_INL int fly_nb_control_step(const DModel<T>& m) {
+  return (1 + m.n_substeps) * FLY_NB_STEP1 + m.n_substeps * (FLY_NB_FWD + FLY_NB_INT);
+}
+FLY_INL void fly_block_pad(int n) {
+  for (int k = 0; k < n; k++) FLY_BLOCK_SYNC();
+}
+
 template <class T>
 FLY_FN void fly_step1(const DModel<T>& m, const Ws<T>& w, bool full) {
+  FLY_BLOCK_SYNC();
   fly_kinematics(m, w);
   fly_com_pos(m, w);
   if (full) {
     fly_crb(m, w);
-    FLY_FOR(e, m.nM) w.qLD[e] = w.qM[e];
-    FLY_SYNC();
-    fly_factor(m, w, w.qLD, w.qDinv);
+    {  /* M and M + dt * damping (the matrix of the implicit-damping Euler step, m13) are factorised together */
+      const T dt = m.timestep;
+      FLY_FOR(e, m.nM) {
+        const int i = m.mrow[e];
+        const T v = w.qM[e];
+        w.qLD[e] = v;
+        w.qH[e] = v + (e == m.madr[i] ? dt * m.dof_damping[i] : T(0));
+      }
+      FLY_SYNC();
+      T* LD[2] = {w.qLD, w.qH};
+      T* iv[2] = {w.qDinv, w.qHinv};
+      fly_factor<T, 2>(m, LD, iv);
+    }
+  }
+  FLY_BLOCK_SYNC();
+  if (full) {
     fly_collision(m, w);
     fly_make_constraint(m, w);
   }
+  FLY_BLOCK_SYNC();
   fly_com_vel(m, w);
   if (full) {
     fly_passive(m, w);
@@ -150,14 +178,22 @@ FLY_FN void fly_step1(const DModel<T>& m, const Ws<T>& w, bool full) {
 /* actuation, smooth acceleration, constraint solve, acceleration sensors */
 template <class T>
 FLY_FN void fly_forward_acc(const DModel<T>& m, const Ws<T>& w) {
+  FLY_BLOCK_SYNC();
   fly_actuation(m, w);
   FLY_FOR(d, m.nv) {
     const T f = w.qfrc_passive[d] - w.qfrc_bias[d] + w.qfrc_actuator[d];
     w.qfrc_smooth[d] = f; w.qacc_smooth[d] = f;
   }
   FLY_SYNC();
-  fly_solve(m, w, w.qLD, w.qDinv, w.qacc_smooth);
+  {
+    const T* LD[1] = {w.qLD};
+    const T* iv[1] = {w.qDinv};
+    T* x[1] = {w.qacc_smooth};
+    fly_solve<T, 1>(m, LD, iv, x);
+  }
+  FLY_BLOCK_SYNC();
   fly_fwd_constraint(m, w);
+  FLY_BLOCK_SYNC();
   fly_sensors_acc(m, w);
 }
 
@@ -165,16 +201,10 @@ FLY_FN void fly_forward_acc(const DModel<T>& m, const Ws<T>& w) {
 template <class T>
 FLY_FN void fly_integrate(const DModel<T>& m, const Ws<T>& w) {
   const T dt = m.timestep;
-  FLY_FOR(e, m.nM) {
-    const int i = m.mrow[e];
-    w.qH[e] = w.qM[e] + (e == m.madr[i] ? dt * m.dof_damping[i] : T(0));
-  }
-  FLY_FOR(d, m.nv) w.stmp[d] = w.qfrc_smooth[d] + w.qfrc_constraint[d];
-  FLY_SYNC();
-  fly_factor(m, w, w.qH, w.qHinv);
-  fly_solve(m, w, w.qH, w.qHinv, w.stmp);
+  FLY_BLOCK_SYNC();
+  /* sMa = (M + dt B)^-1 (qfrc_smooth + qfrc_constraint), solved together with qacc in fly_fwd_constraint */
   FLY_FOR(i, m.na) w.act[i] += dt * w.act_dot[i];
-  FLY_FOR(d, m.nv) { w.qvel[d] += dt * w.stmp[d]; w.warm[d] = w.qacc[d]; }
+  FLY_FOR(d, m.nv) { w.qvel[d] += dt * w.sMa[d]; w.warm[d] = w.qacc[d]; }
   FLY_SYNC();
   FLY_FOR(j, m.njnt) {
     int qa = m.jnt_qposadr[j], da = m.jnt_dofadr[j];

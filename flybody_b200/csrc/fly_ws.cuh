@@ -120,4 +120,59 @@ FLY_HD void ws_bind(const DModel<T>& m, Ws<T>* w, char* fast, char* bulk, size_t
   if (fast_bytes) *fast_bytes = off[1];
   if (bulk_bytes) *bulk_bytes = off[0];
 }
+
+/* Byte offset of every array inside its arena.  The host fills it once per launch configuration (ws_layout) and
+ * passes it as a kernel parameter; each thread then forms its pointers as arena base + constant-bank offset
+ * (ws_attach), with the arena of every array fixed at compile time by LEVEL so that the compiler can tell shared
+ * from global addresses. */
+struct WsOff {
+#define X(n, cnt, tier) unsigned n;
+  FLY_WS_REAL(X) FLY_WS_DBL(X) FLY_WS_INT(X) FLY_WS_U16(X)
+#undef X
+};
+
+template <class T>
+inline void ws_layout(const DModel<T>& m, int level, WsOff* o, size_t* fast_bytes, size_t* bulk_bytes) {
+  size_t off[2] = {0, 0};
+#define PLACE(n, cnt, tier, type)                                          \
+  {                                                                        \
+    int t = ((tier) > 0 && (tier) <= level) ? 1 : 0;                       \
+    size_t bytes = (((size_t)(cnt) * sizeof(type)) + 15) & ~(size_t)15;    \
+    o->n = (unsigned)off[t];                                               \
+    off[t] += bytes;                                                       \
+  }
+#define X(n, cnt, tier) PLACE(n, cnt, tier, T)
+  FLY_WS_REAL(X)
+#undef X
+#define X(n, cnt, tier) PLACE(n, cnt, tier, double)
+  FLY_WS_DBL(X)
+#undef X
+#define X(n, cnt, tier) PLACE(n, cnt, tier, int)
+  FLY_WS_INT(X)
+#undef X
+#define X(n, cnt, tier) PLACE(n, cnt, tier, unsigned short)
+  FLY_WS_U16(X)
+#undef X
+#undef PLACE
+  if (fast_bytes) *fast_bytes = off[1];
+  if (bulk_bytes) *bulk_bytes = off[0];
+}
+
+#if defined(FLY_GPU)
+template <class T, int LEVEL>
+FLY_INL void ws_attach(Ws<T>& w, const WsOff& o, char* fast, char* bulk) {
+#define X(n, cnt, tier) w.n = (T*)((((tier) > 0 && (tier) <= LEVEL) ? fast : bulk) + o.n);
+  FLY_WS_REAL(X)
+#undef X
+#define X(n, cnt, tier) w.n = (double*)((((tier) > 0 && (tier) <= LEVEL) ? fast : bulk) + o.n);
+  FLY_WS_DBL(X)
+#undef X
+#define X(n, cnt, tier) w.n = (int*)((((tier) > 0 && (tier) <= LEVEL) ? fast : bulk) + o.n);
+  FLY_WS_INT(X)
+#undef X
+#define X(n, cnt, tier) w.n = (unsigned short*)((((tier) > 0 && (tier) <= LEVEL) ? fast : bulk) + o.n);
+  FLY_WS_U16(X)
+#undef X
+}
+#endif
 #endif

@@ -55,42 +55,50 @@ struct KArgs {
   int num_envs, level;
 };
 
-template <int WARPS>
+template <int WARPS, int LEVEL>
 __global__ void __launch_bounds__(WARPS * 32) fly_step_kernel(const __grid_constant__ DModel<float> m,
-                                                                const __grid_constant__ KArgs a) {
+                                                                const __grid_constant__ KArgs a,
+                                                                const __grid_constant__ WsOff off) {
   extern __shared__ __align__(16) char smem[];
-  __shared__ Ws<float> ws[WARPS];
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  __shared__ int s_base;
+  const int warp = threadIdx.x >> 5;
   const int slot = blockIdx.x * WARPS + warp;
-  if (lane == 0)
-    ws_bind<float>(m, &ws[warp], smem + warp * a.fast_stride, a.bulk + (size_t)slot * a.bulk_stride, nullptr, nullptr, a.level);
-  __syncwarp();
-  const Ws<float>& w = ws[warp];
-  for (;;) {
-    int env = 0;
-    if (lane == 0) env = atomicAdd(a.counter, 1);
-    env = __shfl_sync(0xffffffffu, env, 0);
-    if (env >= a.num_envs) break;
-    fly_env_run<float>(m, w, a.clips, a.io, env);
+  /* every thread keeps its warp's array pointers as (arena base + constant offset): registers / immediates, with the
+     address space of each array known to the compiler */
+  Ws<float> w;
+  ws_attach<float, LEVEL>(w, off, smem + warp * a.fast_stride, a.bulk + (size_t)slot * a.bulk_stride);
+  for (;;) {  /* the block takes WARPS consecutive envs at a time and its warps step them stage by stage together */
+    __syncthreads();
+    if (threadIdx.x == 0) s_base = atomicAdd(a.counter, WARPS);
+    __syncthreads();
+    const int env = s_base + warp;
+    if (s_base >= a.num_envs) break;
+    fly_env_run<float>(m, w, a.clips, a.io, env < a.num_envs ? env : -1);
   }
+}
+
+/* compiled (warps per block, shared-memory level) combinations */
+#define FLY_KERNEL_CONFIGS(X) X(4, 2) X(6, 2) X(8, 1) X(4, 3)
+typedef void (*FlyKernel)(const DModel<float>, const KArgs, const WsOff);
+static FlyKernel pick_kernel(int warps, int level) {
+#define X(W, L) if (warps == W && level == L) return fly_step_kernel<W, L>;
+  FLY_KERNEL_CONFIGS(X)
+#undef X
+  return nullptr;
 }
 
 static int launch(FlybEngine* h, const FlyIO<float>& io, cudaStream_t st) {
   CK(cudaSetDevice(h->device));
   size_t fb = 0, bb = 0;
-  ws_bind<float>(h->m, nullptr, nullptr, nullptr, &fb, &bb, h->smem_level);
+  WsOff off;
+  ws_layout<float>(h->m, h->smem_level, &off, &fb, &bb);
   h->fast_stride = fb;
   const int W = h->warps;
   const size_t smem = fb * W;
   if (smem > 220 * 1024) { h->err = "shared memory request too large for this smem_level / warps_per_block"; return 1; }
-  void (*kern)(const DModel<float>, const KArgs) = nullptr;
-  switch (W) {
-    case 1: kern = fly_step_kernel<1>; break;
-    case 2: kern = fly_step_kernel<2>; break;
-    case 4: kern = fly_step_kernel<4>; break;
-    case 8: kern = fly_step_kernel<8>; break;
-    default: h->err = "warps_per_block must be 1, 2, 4 or 8"; return 1;
-  }
+  if (bb > h->bulk_stride) { h->err = "internal: bulk slot too small"; return 1; }
+  FlyKernel kern = pick_kernel(W, h->smem_level);
+  if (!kern) { h->err = "this (warps_per_block, smem_level) pair is not compiled in; see FLY_KERNEL_CONFIGS"; return 1; }
   CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int per_sm = 0;
   CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, W * 32, smem));
@@ -107,7 +115,7 @@ static int launch(FlybEngine* h, const FlyIO<float>& io, cudaStream_t st) {
   a.bulk = h->d_bulk; a.bulk_stride = h->bulk_stride; a.fast_stride = fb; a.counter = h->d_counter;
   a.num_envs = h->num_envs; a.level = h->smem_level;
   CK(cudaMemsetAsync(h->d_counter, 0, sizeof(int), st));
-  kern<<<grid, W * 32, smem, st>>>(h->m, a);
+  kern<<<grid, W * 32, smem, st>>>(h->m, a, off);
   CK(cudaGetLastError());
   h->launches++;
   return 0;

@@ -88,13 +88,17 @@ struct Emu : EmuBase {
     if (s == "kinematics") fly_kinematics(m, w);
     else if (s == "com_pos") fly_com_pos(m, w);
     else if (s == "crb") fly_crb(m, w);
-    else if (s == "factor") { for (int e = 0; e < m.nM; e++) w.qLD[e] = w.qM[e]; fly_factor(m, w, w.qLD, w.qDinv); }
+    else if (s == "factor") {
+      for (int e = 0; e < m.nM; e++) { w.qLD[e] = w.qM[e]; w.qH[e] = w.qM[e] + (e == m.madr[m.mrow[e]] ? m.timestep * m.dof_damping[m.mrow[e]] : T(0)); }
+      T* LD[2] = {w.qLD, w.qH}; T* iv[2] = {w.qDinv, w.qHinv};
+      fly_factor<T, 2>(m, LD, iv);
+    }
     else if (s == "collision") fly_collision(m, w);
     else if (s == "make_constraint") fly_make_constraint(m, w);
     else if (s == "step1") fly_step1(m, w, true);
     else if (s == "forward_acc") fly_forward_acc(m, w);
     else if (s == "integrate") fly_integrate(m, w);
-    else if (s == "solve_stmp") fly_solve(m, w, w.qLD, w.qDinv, w.stmp);
+    else if (s == "solve_stmp") { const T* LD[1] = {w.qLD}; const T* iv[1] = {w.qDinv}; T* x[1] = {w.stmp}; fly_solve<T, 1>(m, LD, iv, x); }
     else fprintf(stderr, "emu: unknown stage %s\n", stage);
   }
   int get(const char* name, double* out, int cap) override {
