@@ -9,25 +9,26 @@
 #include "fly_model.h"
 #include "fly_math.cuh"
 
-/* tier of an array: 0 = always bulk; 1..3 = goes to the fast arena when the launch's `level` is >= the tier */
+/* tier of an array: 0 = always bulk; 1..4 = goes to the fast arena when the launch's `level` is >= the tier
+ * (1: the two factorisations and the vectors their solves run on; 2: state and solver vectors; 3, 4: kinematics) */
 #define FLY_NHIT 4   /* most contacts a primitive pair can produce */
 
 /* X(name, element-count expression over `m`, tier) ; arrays of T */
 #define FLY_WS_REAL(X)                                                                                       \
-  X(qpos, m.nq, 1) X(qvel, m.nv, 1) X(act, m.na, 1) X(ctrl, m.nu, 1)             \
-  X(warm, m.nv, 1) X(qacc, m.nv, 1)                                                            \
-  X(xpos, 3 * m.nbody, 2) X(xquat, 4 * m.nbody, 2) X(xmat, 9 * m.nbody, 2)              \
-  X(xipos, 3 * m.nbody, 3) X(ximat, 9 * m.nbody, 0)                                            \
+  X(qpos, m.nq, 2) X(qvel, m.nv, 2) X(act, m.na, 2) X(ctrl, m.nu, 2)             \
+  X(warm, m.nv, 2) X(qacc, m.nv, 2)                                                            \
+  X(xpos, 3 * m.nbody, 3) X(xquat, 4 * m.nbody, 3) X(xmat, 9 * m.nbody, 3)              \
+  X(xipos, 3 * m.nbody, 4) X(ximat, 9 * m.nbody, 0)                                            \
   X(xanchor, 3 * m.njnt, 0) X(xaxis, 3 * m.njnt, 0)                                            \
-  X(geom_xpos, 3 * m.ngeom, 2) X(site_xpos, 3 * m.nsite, 0) X(site_xmat, 9 * m.nsite, 0)\
-  X(scom, 3 * m.nbody, 2) X(cinert, 10 * m.nbody, 3) X(crb, 10 * m.nbody, 0)            \
-  X(cdof, 6 * m.nv, 2) X(cdof_dot, 6 * m.nv, 3) X(cvel, 6 * m.nbody, 3)                 \
-  X(qM, m.nM + 1, 2) X(qLD, m.nM + 1, 1) X(qH, m.nM + 1, 1)                    \
+  X(geom_xpos, 3 * m.ngeom, 3) X(site_xpos, 3 * m.nsite, 0) X(site_xmat, 9 * m.nsite, 0)\
+  X(scom, 3 * m.nbody, 3) X(cinert, 10 * m.nbody, 4) X(crb, 10 * m.nbody, 0)            \
+  X(cdof, 6 * m.nv, 3) X(cdof_dot, 6 * m.nv, 4) X(cvel, 6 * m.nbody, 4)                 \
+  X(qM, m.nM + 1, 3) X(qLD, m.nM + 1, 1) X(qH, m.nM + 1, 1)                    \
   X(qDinv, m.nv, 1) X(qHinv, m.nv, 1)                                         \
   X(act_length, m.nu, 0) X(act_force, m.nu, 0) X(act_dot, m.na, 0)                      \
   X(qfrc_bias, m.nv, 0) X(qfrc_passive, m.nv, 0) X(qfrc_actuator, m.nv, 0)              \
-  X(qfrc_smooth, m.nv, 1) X(qacc_smooth, m.nv, 1) X(qfrc_constraint, m.nv, 1)           \
-  X(sMa, m.nv, 1) X(sgrad, m.nv, 1) X(ssearch, m.nv, 1)          \
+  X(qfrc_smooth, m.nv, 2) X(qacc_smooth, m.nv, 1) X(qfrc_constraint, m.nv, 2)           \
+  X(sMa, m.nv, 1) X(sgrad, m.nv, 2) X(ssearch, m.nv, 2)          \
   X(stmp, m.nv, 1)                                                                                    \
   X(bodyf, 6 * m.nbody, 0) X(boxf, 6 * (m.nfluidbox + m.nfluidgeom), 0)                        \
   X(cacc, 6 * m.nbody, 0) X(cfrc_int, 6 * m.nbody, 0) X(cfrc_ext, 6 * m.nbody, 0)       \
@@ -38,9 +39,9 @@
   X(efc_J, FLY_MAXEFC * FLY_MAXCHAIN, 0) X(efc_Y, FLY_MAXEFC * FLY_MAXCHAIN, 0)                \
   X(x_J, FLY_MAXCROSS * FLY_MAXCHAIN, 0) X(x_Y, FLY_MAXCROSS * FLY_MAXCHAIN, 0)                \
   X(efc_pos, FLY_MAXEFC, 0) X(efc_margin, FLY_MAXEFC, 0) X(efc_diag, FLY_MAXEFC, 0)     \
-  X(efc_R, FLY_MAXEFC, 0) X(efc_D, FLY_MAXEFC, 1) X(efc_K0, FLY_MAXEFC, 0)               \
+  X(efc_R, FLY_MAXEFC, 0) X(efc_D, FLY_MAXEFC, 2) X(efc_K0, FLY_MAXEFC, 0)               \
   X(efc_B, FLY_MAXEFC, 0) X(efc_imp, FLY_MAXEFC, 0) X(efc_aref, FLY_MAXEFC, 0)          \
-  X(efc_force, FLY_MAXEFC, 1)        \
+  X(efc_force, FLY_MAXEFC, 2)        \
   X(efc_A, FLY_MAXEFC * FLY_MAXEFC, 0) X(efc_K, FLY_MAXEFC * FLY_MAXEFC, 0)             \
           \
   X(efc_lam, FLY_MAXEFC, 0)                              \
@@ -49,7 +50,7 @@
 /* arrays of double: the Newton iterate in constraint space (c, jar = b + A c, ...) cancels to a few parts in 1e4
  * of its terms, so these nefc-sized vectors are kept in float64 even when T is float */
 #define FLY_WS_DBL(X)                                                                                        \
-  X(efc_jar, FLY_MAXEFC, 1) X(efc_jv, FLY_MAXEFC, 1) X(efc_b, FLY_MAXEFC, 0) X(efc_b0, FLY_MAXEFC, 0)        \
+  X(efc_jar, FLY_MAXEFC, 2) X(efc_jv, FLY_MAXEFC, 2) X(efc_b, FLY_MAXEFC, 0) X(efc_b0, FLY_MAXEFC, 0)        \
   X(efc_c, FLY_MAXEFC, 0) X(efc_cp, FLY_MAXEFC, 0) X(efc_Ac, FLY_MAXEFC, 0) X(efc_Acp, FLY_MAXEFC, 0)        \
   X(efc_h, FLY_MAXEFC, 0)
 

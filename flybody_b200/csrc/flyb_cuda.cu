@@ -30,7 +30,7 @@ struct FlybEngine {
   float *h_action = nullptr, *h_obs = nullptr, *h_rd = nullptr; int* h_st = nullptr; unsigned char* h_mask = nullptr;
   float *d_action = nullptr, *d_obs = nullptr, *d_rd = nullptr; int* d_st = nullptr; unsigned char* d_mask = nullptr;
   cudaStream_t host_stream = nullptr;
-  int smem_level = 2, warps = 4, blocks_per_sm = 0, sm_count = 148, grid = 0;
+  int smem_level = 1, warps = 16, blocks_per_sm = 0, sm_count = 148, grid = 0;
   long long launches = 0;
   std::string err;
 };
@@ -56,7 +56,7 @@ struct KArgs {
 };
 
 template <int WARPS, int LEVEL>
-__global__ void __launch_bounds__(WARPS * 32) fly_step_kernel(const __grid_constant__ DModel<float> m,
+__global__ void __launch_bounds__(WARPS * 32, 1) fly_step_kernel(const __grid_constant__ DModel<float> m,
                                                                 const __grid_constant__ KArgs a,
                                                                 const __grid_constant__ WsOff off) {
   extern __shared__ __align__(16) char smem[];
@@ -78,7 +78,7 @@ __global__ void __launch_bounds__(WARPS * 32) fly_step_kernel(const __grid_const
 }
 
 /* compiled (warps per block, shared-memory level) combinations */
-#define FLY_KERNEL_CONFIGS(X) X(4, 2) X(6, 2) X(8, 1) X(4, 3)
+#define FLY_KERNEL_CONFIGS(X) X(16, 1) X(12, 1) X(10, 2) X(8, 2) X(6, 3)
 typedef void (*FlyKernel)(const DModel<float>, const KArgs, const WsOff);
 static FlyKernel pick_kernel(int warps, int level) {
 #define X(W, L) if (warps == W && level == L) return fly_step_kernel<W, L>;
@@ -245,9 +245,9 @@ int64_t flyb_info(flyb_handle h, int what) {
 }
 
 int flyb_configure(flyb_handle h, int smem_level, int warps_per_block, int blocks_per_sm) {
-  if (smem_level < 0 || smem_level > 3) { h->err = "smem_level must be 0..3"; return 1; }
-  if (warps_per_block != 1 && warps_per_block != 2 && warps_per_block != 4 && warps_per_block != 8) {
-    h->err = "warps_per_block must be 1, 2, 4 or 8"; return 1;
+  if (smem_level < 0 || smem_level > 4) { h->err = "smem_level must be 0..4"; return 1; }
+  if (!pick_kernel(warps_per_block, smem_level)) {
+    h->err = "this (smem_level, warps_per_block) pair is not compiled in; see FLY_KERNEL_CONFIGS in flyb_cuda.cu"; return 1;
   }
   h->smem_level = smem_level; h->warps = warps_per_block; h->blocks_per_sm = blocks_per_sm;
   return 0;

@@ -54,7 +54,7 @@ void flyb_destroy(flyb_handle h);
 const char* flyb_last_error(flyb_handle h);  /* h may be NULL: error of the last failed flyb_create */
 int64_t flyb_info(flyb_handle h, int what);
 
-/* Tuning knobs: smem_level 0..3 (how many workspace tiers live in shared memory), warps per block (1..8),
+/* Tuning knobs: smem_level 0..4 (how many workspace tiers live in shared memory) and warps per block; only the pairs
  * blocks per SM (0 = as many as fit).  Takes effect at the next launch. */
 int flyb_configure(flyb_handle h, int smem_level, int warps_per_block, int blocks_per_sm);
 
