@@ -235,3 +235,49 @@ def synthetic_table(M: dict, n_clips: int = 1024, T: int = 600, seed: int = 0, c
 def save_clips(path: str, M: dict, clips: list):
     rows, off, ln = pack_clips(M, clips)
     np.savez(path, rows=rows, offsets=off, lengths=ln)
+
+
+# ---------------------------------------------------------------------------- flight reference clips
+_COM_OFFSET = np.array([-0.03697732, 0.00029205, -0.0142447])  # task_utils.py:187,209: CoM in thorax coordinates
+
+
+def com2root(com, quat):
+    """Root-joint position from CoM position and orientation, batched (task_utils.py:194-213)."""
+    return np.asarray(com, np.float64) + _bq_rot(np.asarray(quat, np.float64), np.broadcast_to(-_COM_OFFSET, np.shape(com)))
+
+
+def root2com(root_qpos):
+    """Inverse of com2root for one pose (task_utils.py:174-191)."""
+    root_qpos = np.asarray(root_qpos, np.float64)
+    return root_qpos[:3] + _bq_rot(root_qpos[3:7][None], _COM_OFFSET[None])[0]
+
+
+def flight_clip_from_com(com_qpos, com_qvel):
+    """(com_qpos [T,7], com_qvel [T,6]) as stored in the flight dataset -> clip dict with the ROOT pose:
+    xy re-origin (trajectory_loaders.py:130) then com2root (flight_imitation.py:101-103)."""
+    q = np.array(com_qpos, np.float64)
+    q[:, :2] -= q[0, :2]
+    return dict(qpos=np.concatenate([com2root(q[:, :3], q[:, 3:7]), q[:, 3:7]], axis=1), qvel=np.array(com_qvel, np.float64))
+
+
+def synth_flight_clip(T: int = 3006, seed: int = 0, dt: float = 2e-4):
+    """Synthetic CoM clip: hover with slow drift (|v| <= 30 cm/s) and yaw saccades."""
+    rng = np.random.RandomState(seed)
+    t = np.arange(T) * dt
+    vel = np.zeros((T, 3))
+    for k in range(3):
+        for _ in range(3):
+            vel[:, k] += rng.uniform(-5, 5) * np.sin(2 * np.pi * rng.uniform(1, 8) * t + rng.uniform(0, 2 * np.pi))
+    pos = np.cumsum(vel, axis=0) * dt
+    pos -= pos[0]
+    pos[:, 2] += 1.5 + rng.uniform(-0.2, 0.2)
+    yaw_rate = sum(rng.uniform(-6, 6) * np.sin(2 * np.pi * rng.uniform(1, 6) * t + rng.uniform(0, 2 * np.pi)) for _ in range(2))
+    yaw = np.cumsum(yaw_rate) * dt + rng.uniform(-np.pi, np.pi)
+    quat = np.stack([np.cos(yaw / 2), np.zeros(T), np.zeros(T), np.sin(yaw / 2)], axis=1)
+    ang = np.stack([np.zeros(T), np.zeros(T), yaw_rate], axis=1)
+    return flight_clip_from_com(np.concatenate([pos, quat], axis=1), np.concatenate([vel, ang], axis=1))
+
+
+def synthetic_flight_table(M: dict, n_clips: int = 64, T: int = 3006, seed: int = 0):
+    """Packed synthetic flight clip table -> (rows float32 [n T, 13], offsets, lengths)."""
+    return pack_clips(M, [synth_flight_clip(T=T, seed=seed * 100003 + c) for c in range(n_clips)])

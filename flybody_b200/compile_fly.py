@@ -867,7 +867,7 @@ def task_tables(M: dict, ts: TaskSpec) -> dict:
     M["task_type"] = _TASK_TYPE[ts.task]
     M["n_substeps"], M["future_steps"] = ts.n_substeps, ts.future_steps
     M["control_dt"], M["time_limit"] = ts.control_dt, ts.time_limit
-    M["max_episode_steps"] = int(round(ts.time_limit / ts.control_dt)) + 1  # walk_imitation.py:60
+    M["max_episode_steps"] = int(round(ts.time_limit / ts.control_dt)) + (0 if ts.task == "flight_imitation" else 1)  # walk_imitation.py:60 ; flight_imitation.py:107
     # composer.Environment ends the episode when physics.time() >= time_limit; time is the float64 running sum of
     # the physics timestep, so the first control step at which that holds is found by the same accumulation.
     t, k = 0.0, 0

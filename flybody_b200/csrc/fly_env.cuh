@@ -6,7 +6,7 @@
 
 /* per-env persistent integers */
 enum { FLY_SI_STEP = 0, FLY_SI_EPISODE_STEPS, FLY_SI_RESET_NEXT, FLY_SI_CLIP, FLY_SI_EPISODE, FLY_SI_FORCED_CLIP,
-       FLY_SI_EPLEN, FLY_SI_COUNT = 8 };
+       FLY_SI_EPLEN, FLY_SI_WB_STEP, FLY_SI_WB_FIDX, FLY_SI_WB_FREQ_LO, FLY_SI_WB_FREQ_HI, FLY_SI_COUNT = 12 };
 /* per-env trace integers (optional debug output) */
 enum { FLY_TR_NCON = 0, FLY_TR_NEFC, FLY_TR_NLIMIT, FLY_TR_NITER, FLY_TR_OVERFLOW, FLY_TR_NCAND, FLY_TR_PAIRS = 8,
        FLY_TR_INTS = 8 + FLY_MAXCON };
@@ -29,6 +29,7 @@ struct FlyIO {
   int env_offset;      /* global id of env 0 of this shard */
   int force_reset;     /* 1: reset every env in mask regardless of reset_next */
   const unsigned char* reset_mask; /* nullable */
+  const double* wbpg_phase;        /* nullable [N]: initial wing-beat phase to use at reset instead of the hashed draw */
 };
 
 FLY_INL unsigned long long fly_hash(unsigned long long x) {  /* splitmix64 finaliser */
@@ -116,7 +117,7 @@ FLY_FN void fly_write_obs(const DModel<T>& m, const Ws<T>& w, const FlyClipView&
       quat_mul(q, qi, rqt);  /* quaternions.py:13-17 */
       for (int k = 0; k < 3; k++) obs[off[FLYB_OBS_REF_DISPLACEMENT] + 3 * i + k] = (float)o[k];
       for (int k = 0; k < 4; k++) obs[off[FLYB_OBS_REF_ROOT_QUAT] + 4 * i + k] = (float)q[k];
-      if (i == 0) for (int k = 0; k < 3; k++) w.obs_tmp[k] = o[k];
+      if (i == 0) { for (int k = 0; k < 3; k++) w.obs_tmp[k] = o[k]; for (int k = 0; k < 4; k++) w.obs_tmp[4 + k] = q[k]; }
     }
   }
   FLY_SYNC();
@@ -189,13 +190,68 @@ FLY_INL FlyClipView fly_clip_view(const DModel<T>& m, const FlyClips& clips, int
   return v;
 }
 
+/* ---- wing-beat pattern generator (tasks/pattern_generators.py:121-191), per-env state in sint[FLY_SI_WB_*].
+ * All of it in float64 with numpy's first-minimum argmin, so the table step and frequency index are bit-identical to
+ * the reference's for the same float32 action. */
+FLY_INL void fly_put_double(int* lo_hi, double v) {
+  unsigned long long b;
+  memcpy(&b, &v, 8);
+  lo_hi[0] = (int)(unsigned)(b & 0xffffffffull); lo_hi[1] = (int)(unsigned)(b >> 32);
+}
+FLY_INL double fly_get_double(const int* lo_hi) {
+  const unsigned long long b = (unsigned long long)(unsigned)lo_hi[0] | ((unsigned long long)(unsigned)lo_hi[1] << 32);
+  double v;
+  memcpy(&v, &b, 8);
+  return v;
+}
+/* separately rounded multiply / add: nvcc would otherwise contract a*b + c*d into an FMA, which differs from numpy's
+ * result in the last bit and, accumulated in the low-pass state, would eventually pick another table row */
+FLY_INL double fly_mul_rn(double a, double b) {
+#ifdef FLY_GPU
+  return __dmul_rn(a, b);
+#else
+  return a * b;
+#endif
+}
+FLY_INL double fly_add_rn(double a, double b) {
+#ifdef FLY_GPU
+  return __dadd_rn(a, b);
+#else
+  return a + b;
+#endif
+}
+FLY_INL int fly_wbpg_nearest_freq(const FlyWbpg& wb, double f) {
+  double bv = 1e300; int bi = 0x7fffffff;
+  FLY_FOR(i, wb.nfreq) { const double d = fabs(wb.beat_freqs[i] - f); if (d < bv) { bv = d; bi = i; } }
+  warp_argmin(bv, bi);
+  return bi;
+}
+/* row of frequency table `fidx` whose phase (optionally modulo 1) is nearest to `target` */
+FLY_INL int fly_wbpg_seek(const FlyWbpg& wb, int fidx, double target, bool mod1) {
+  const int o = wb.offsets[fidx], n = wb.offsets[fidx + 1] - o;
+  double bv = 1e300; int bi = 0x7fffffff;
+  FLY_FOR(i, n) {
+    const double ph = mod1 ? fmod(wb.phase[o + i], 1.0) : wb.phase[o + i];
+    const double d = fabs(target - ph);
+    if (d < bv) { bv = d; bi = i; }
+  }
+  warp_argmin(bv, bi);
+  return bi;
+}
+/* uniform [0,1) initial phase of (env, episode): the counter-based stand-in for random_state.uniform() (flight_imitation.py:137) */
+FLY_INL double fly_wbpg_phase0(unsigned long long seed, int global_env, int episode) {
+  const unsigned long long h = fly_hash(seed ^ fly_hash((((unsigned long long)global_env << 24) ^ (unsigned long long)episode) + 0x51ED270B7ull));
+  return (double)(h >> 11) * (1.0 / 9007199254740992.0);
+}
+
 /* The whole job of one warp for one env and one call: load the state, reset the episode OR advance it by one control
  * step, store state and outputs.  Reset and step share one pass through the pipeline (each stage has a single call
  * site, so that the fully inlined kernel holds one copy of it):
  *   reset: step1, forward_acc                                 (mj_forward of the initial state)
  *   step : step1, n_substeps x [forward_acc, integrate, step1] (dm_control's legacy order: mj_step2 then mj_step1) */
 template <class T>
-FLY_FN void fly_env_run(const DModel<T>& m, const Ws<T>& w, const FlyClips& clips, const FlyIO<T>& io, int env) {
+FLY_FN void fly_env_run(const DModel<T>& m, const Ws<T>& w, const FlyClips& clips, const FlyWbpg& wb, const FlyIO<T>& io,
+                        int env) {
   if (env < 0) { fly_block_pad(fly_nb_control_step(m)); return; }  /* idle warp of a block that still has work */
   T* sr = io.sreal + (size_t)env * io.sreal_stride;
   int* sint = io.sint + (size_t)env * FLY_SI_COUNT;
@@ -228,6 +284,26 @@ FLY_FN void fly_env_run(const DModel<T>& m, const Ws<T>& w, const FlyClips& clip
       FLY_FOR(i, m.n_mocap_joints) w.qpos[m.jnt_qposadr[m.mocap_joint[i]]] = (T)r[7 + i];
       FLY_SYNC();
     }
+    if (m.task_type == FLYB_TASK_FLIGHT_IMITATION && clip.rows) {
+      /* flight_imitation.py:106-108: traj_timesteps = min(T, round(time_limit / control_dt)) - (future_steps + 1) */
+      episode_steps = (clip.T < m.max_episode_steps ? clip.T : m.max_episode_steps) - (m.future_steps + 1);
+      const float* r = clip.rows;
+      FLY_FOR(k, 7) w.qpos[m.root_qposadr + k] = (T)r[k];        /* :138 walker.set_pose */
+      FLY_FOR(k, 3) w.qvel[m.root_dofadr + k] = (T)r[7 + k];     /* :145-147 linear velocity only */
+      if (wb.nfreq > 0) {                                        /* :135-143 wbpg.reset(initial_phase, return_qvel) */
+        const double phase0 = io.wbpg_phase ? io.wbpg_phase[env] : fly_wbpg_phase0(io.seed, io.env_offset + env, episode);
+        const int fidx = fly_wbpg_nearest_freq(wb, wb.base_freq);
+        const int ws = fly_wbpg_seek(wb, fidx, phase0, false);
+        const double* row = wb.traj + (size_t)(wb.offsets[fidx] + ws) * 6;
+        FLY_FOR(k, 6) {
+          const int j = m.wing_joint[k];
+          w.qpos[m.jnt_qposadr[j]] = (T)row[k];
+          w.qvel[m.jnt_dofadr[j]] = (T)((row[6 + k] - row[k]) / wb.dt_ctrl);
+        }
+        FLY_LANE0 { sint[FLY_SI_WB_STEP] = ws; sint[FLY_SI_WB_FIDX] = fidx; fly_put_double(sint + FLY_SI_WB_FREQ_LO, wb.base_freq); }
+      }
+      FLY_SYNC();
+    }
   } else {
     FLY_FOR(i, m.nq) w.qpos[i] = s_qpos[i];
     FLY_FOR(i, m.nv) { w.qvel[i] = s_qvel[i]; w.warm[i] = s_warm[i]; }
@@ -240,13 +316,44 @@ FLY_FN void fly_env_run(const DModel<T>& m, const Ws<T>& w, const FlyClips& clip
       w.ctrl[a] = v;
     }
     FLY_FOR(k, m.nsensordata) w.sens_sum[k] = 0;
+    if (m.task_type == FLYB_TASK_FLIGHT_IMITATION && wb.nfreq > 0 && m.user_action >= 0) {
+      /* flight_imitation.py:149-159: requested beat frequency from the user action, generator step, and the wing
+         position targets turned into force commands: action[wings] += target - wing qpos */
+      float au = action_in[m.user_action];
+      if (au != au) au = 0;
+      /* float32 like the reference with a float32 action under numpy >= 2 (flybody_b200/wbpg.py: requested_freq) */
+#ifdef FLY_GPU
+      const float reqf = __fmul_rn((float)wb.base_freq, __fadd_rn(1.0f, __fmul_rn((float)wb.rel_range, au)));  /* no FMA contraction */
+#else
+      const float reqf = (float)wb.base_freq * (1.0f + (float)wb.rel_range * au);
+#endif
+      const double req = (double)reqf;
+      int fidx = sint[FLY_SI_WB_FIDX], ws = sint[FLY_SI_WB_STEP];
+      double cf = fly_get_double(sint + FLY_SI_WB_FREQ_LO);
+      const int o = wb.offsets[fidx], n = wb.offsets[fidx + 1] - o;
+      ws = (ws + 1) % n;
+      cf = wb.rate == 0.0 ? req : fly_add_rn(fly_mul_rn(cf, wb.rate), fly_mul_rn(req, 1 - wb.rate));
+      const int nf = fly_wbpg_nearest_freq(wb, cf);
+      if (nf != fidx) {
+        ws = fly_wbpg_seek(wb, nf, fmod(wb.phase[o + ws], 1.0), true);
+        fidx = nf;
+      }
+      const double* row = wb.traj + (size_t)(wb.offsets[fidx] + ws) * 6;
+      FLY_SYNC();
+      FLY_FOR(k, 6) {
+        const T delta = (T)(row[k] - (double)w.qpos[m.jnt_qposadr[m.wing_joint[k]]]);
+        for (int a = 0; a < m.nu; a++) if (m.ctrl_action[a] == m.wing_action[k]) w.ctrl[a] += delta;
+      }
+      FLY_SYNC();
+      FLY_LANE0 { sint[FLY_SI_WB_STEP] = ws; sint[FLY_SI_WB_FIDX] = fidx; fly_put_double(sint + FLY_SI_WB_FREQ_LO, cf); }
+    }
     clip_id = sint[FLY_SI_CLIP];
     clip = fly_clip_view(m, clips, clip_id);
     step = sint[FLY_SI_STEP];
     episode_steps = sint[FLY_SI_EPISODE_STEPS];
     FLY_SYNC();
   }
-  if (m.task_type == FLYB_TASK_WALK_IMITATION && (clip.rows || !do_reset)) fly_set_ghost(m, w, clip, step, !do_reset);
+  if (m.task_type != FLYB_TASK_WALK_ON_BALL) fly_set_ghost(m, w, clip, step, !do_reset);  /* no-op without ghost or clip */
   if (!do_reset) step += 1;  /* tasks/base.py:192 */
   const int nsub = do_reset ? 0 : m.n_substeps;
   for (int it = 0;; it++) {
@@ -285,6 +392,26 @@ FLY_FN void fly_env_run(const DModel<T>& m, const Ws<T>& w, const FlyClips& clip
       reached_end = step == episode_steps;
       if (clip.rows && norm3(w.obs_tmp) > m.terminal_com_dist) fatal = 1;
       r = fly_walk_imitation_reward(m, w, clip, step);
+    } else if (m.task_type == FLYB_TASK_FLIGHT_IMITATION) {  /* flight_imitation.py:169-209 */
+      reached_end = step == episode_steps;
+      if (w.site_xpos[3 * m.thorax_site + 2] < m.terminal_height) fatal = 1;
+      if (clip.rows) {
+        if (norm3(w.obs_tmp) > m.terminal_com_dist) fatal = 1;
+        if (m.ghost_body >= 0) {
+          /* CoM term: ghost CoM = root2com(ghost pose read back from the physics) vs subtree CoM of the fly; orientation
+             term: short-arc angle of ref_root_quat[0]; both linear tolerances (margin 0.4 cm / pi) */
+          const T coff[3] = {T(-0.03697732), T(0.00029205), T(-0.0142447)};  /* task_utils.py:187 */
+          T og[3], d[3];
+          quat_rotate(og, coff, w.xquat + 4 * m.ghost_body);
+          for (int k = 0; k < 3; k++) d[k] = w.xpos[3 * m.ghost_body + k] + og[k] - w.scom[3 * m.root_body + k];
+          const T x = norm3(d) / T(0.4);
+          /* quat_dist_short_arc([1,0,0,0], q) = arccos(2 (q0/|q|)^2 - 1) (quaternions.py:273-295) evaluated as
+             2 atan2(|q_vec|, |q0|): the same angle, but well conditioned near 0 where fp32 arccos loses half its digits */
+          const T* qd = w.obs_tmp + 4;
+          const T th = 2 * atan2(norm3(qd + 1), fabs_(qd[0])) / T(3.14159265358979323846);
+          r = (x < 1 ? 1 - x : T(0)) * (th < 1 ? 1 - th : T(0));
+        }
+      }
     } else if (m.task_type == FLYB_TASK_WALK_ON_BALL) {  /* walk_on_ball.py:61-73: tolerance(linear, margin 6) */
       const T tgt[3] = {0, -5, 0};
       for (int k = 0; k < 3; k++) {

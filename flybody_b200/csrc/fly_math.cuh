@@ -40,6 +40,15 @@ FLY_INL int warp_sum_i(int v) {
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
   return v;
 }
+/* all-reduce of (value, index) pairs to the smallest value, lowest index on ties (numpy.argmin) */
+FLY_INL void warp_argmin(double& v, int& i) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const double ov = __shfl_xor_sync(0xffffffffu, v, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, i, o);
+    if (ov < v || (ov == v && oi < i)) { v = ov; i = oi; }
+  }
+}
 /* ordered stream compaction of the items i in [0,n) with pred(i): writes their indices to out[], in order */
 template <class P> FLY_INL int warp_compact(int n, P pred, unsigned short* out, int maxout) {
   int cnt = 0;
@@ -67,6 +76,7 @@ template <class P> FLY_INL int warp_compact(int n, P pred, unsigned short* out, 
 template <class T> FLY_INL T warp_sum(T v) { return v; }
 template <class T> FLY_INL T warp_max(T v) { return v; }
 FLY_INL int warp_sum_i(int v) { return v; }
+FLY_INL void warp_argmin(double& v, int& i) { (void)v; (void)i; }
 template <class P> FLY_INL int warp_compact(int n, P pred, unsigned short* out, int maxout) {
   int cnt = 0;
   for (int i = 0; i < n; i++)

@@ -70,7 +70,7 @@ struct DModel {
   int opt_iterations, opt_ls_iterations, opt_noslip_iterations, flags;
   /* task */
   int task_type, n_substeps, future_steps, action_dim, obs_dim, max_episode_steps, time_limit_steps;
-  int root_body, root_qposadr, root_dofadr, ghost_qposadr, ghost_dofadr, ball_dofadr, thorax_site;
+  int root_body, root_qposadr, root_dofadr, ghost_qposadr, ghost_dofadr, ghost_body, ball_dofadr, thorax_site;
   int n_obs_joints, n_appendages, n_mocap_joints, n_mocap_sites, user_action, pad_first_obs, inference_mode;
   int clip_width;
   T timestep, density, viscosity, tolerance, ls_tolerance, noslip_tolerance, impratio, meaninertia;
@@ -119,6 +119,8 @@ std::string build_dmodel(const FlybModel* m, int flags, DModel<T>* out, FlyArena
   CP(inference_mode)
 #undef CP
   d.flags = flags;
+  d.ghost_body = -1;
+  for (int j = 0; j < m->njnt; j++) if (m->ghost_qposadr >= 0 && m->jnt_qposadr[j] == m->ghost_qposadr) d.ghost_body = m->jnt_bodyid[j];
   d.timestep = (T)m->opt_timestep; d.density = (T)m->opt_density; d.viscosity = (T)m->opt_viscosity;
   d.tolerance = (T)m->opt_tolerance; d.ls_tolerance = (T)m->opt_ls_tolerance;
   d.noslip_tolerance = (T)m->opt_noslip_tolerance; d.impratio = (T)m->opt_impratio;

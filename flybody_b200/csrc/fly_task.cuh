@@ -15,6 +15,16 @@ struct FlyClips {
   int nclips;
 };
 
+/* wing-beat pattern generator tables in HBM (flybody_b200/wbpg.py; float64 so that table indices match the reference) */
+struct FlyWbpg {
+  int nfreq;                /* 0: no generator loaded */
+  const double* beat_freqs; /* [nfreq] */
+  const int* offsets;       /* [nfreq + 1] */
+  const double* traj;       /* [rows, 6] */
+  const double* phase;      /* [rows] */
+  double base_freq, rel_range, rate, dt_ctrl;
+};
+
 /* ---------------------------------------------------------------- m12 acceleration-stage sensors */
 template <class T>
 FLY_INL T fly_ray_capsule(const T* pos, const T* mat, const T* size, const T* pnt, const T* vec) {

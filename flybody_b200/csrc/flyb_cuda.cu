@@ -26,6 +26,8 @@ struct FlybEngine {
   char* d_bulk = nullptr; size_t bulk_stride = 0, fast_stride = 0; int bulk_slots = 0;
   int* d_counter = nullptr;
   float* d_clip_rows = nullptr; int* d_clip_off = nullptr; int* d_clip_len = nullptr; int n_clips = 0;
+  FlyWbpg wb = {};        /* device pointers; nfreq 0 until flyb_load_wbpg */
+  void* d_wbpg = nullptr; double* d_wbpg_phase = nullptr;
   /* staging for the host-pointer API */
   float *h_action = nullptr, *h_obs = nullptr, *h_rd = nullptr; int* h_st = nullptr; unsigned char* h_mask = nullptr;
   float *d_action = nullptr, *d_obs = nullptr, *d_rd = nullptr; int* d_st = nullptr; unsigned char* d_mask = nullptr;
@@ -48,6 +50,7 @@ static std::string g_create_error;
 
 struct KArgs {
   FlyClips clips;
+  FlyWbpg wb;
   FlyIO<float> io;
   char* bulk;
   size_t bulk_stride, fast_stride;
@@ -73,7 +76,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) fly_step_kernel(const __grid_co
     __syncthreads();
     const int env = s_base + warp;
     if (s_base >= a.num_envs) break;
-    fly_env_run<float>(m, w, a.clips, a.io, env < a.num_envs ? env : -1);
+    fly_env_run<float>(m, w, a.clips, a.wb, a.io, env < a.num_envs ? env : -1);
   }
 }
 
@@ -112,6 +115,7 @@ static int launch(FlybEngine* h, const FlyIO<float>& io, cudaStream_t st) {
   KArgs a;
   a.clips.data = h->d_clip_rows; a.clips.offset = h->d_clip_off; a.clips.length = h->d_clip_len; a.clips.nclips = h->n_clips;
   a.io = io;
+  a.wb = h->wb;
   a.bulk = h->d_bulk; a.bulk_stride = h->bulk_stride; a.fast_stride = fb; a.counter = h->d_counter;
   a.num_envs = h->num_envs; a.level = h->smem_level;
   CK(cudaMemsetAsync(h->d_counter, 0, sizeof(int), st));
@@ -128,6 +132,7 @@ static FlyIO<float> make_io(FlybEngine* h, const float* action, float* obs, floa
   io.action = action; io.obs = obs; io.reward = reward; io.discount = discount; io.step_type = st;
   io.trace_int = h->d_trace_int; io.trace_real = h->d_trace_real; io.trace_real_stride = h->trace_real_stride;
   io.stats = h->d_stats; io.seed = h->seed; io.env_offset = h->env_offset;
+  io.wbpg_phase = h->d_wbpg_phase;
   return io;
 }
 
@@ -182,7 +187,7 @@ int flyb_create(const FlybModel* model, int num_envs, int device, uint64_t seed,
   ws_bind<float>(m, nullptr, nullptr, nullptr, &fb, &bb, 0);
   h->bulk_stride = (bb + 255) & ~(size_t)255;
   h->bulk_slots = h->sm_count * 32;
-  if ((size_t)h->bulk_slots > N + 8) h->bulk_slots = (int)((N + 7) & ~(size_t)7);
+  if ((size_t)h->bulk_slots > N + 32) h->bulk_slots = (int)((N + 31) & ~(size_t)31);  /* whole blocks of up to 32 warps */
   CKC(cudaMalloc(&h->d_bulk, (size_t)h->bulk_slots * h->bulk_stride));
   CKC(cudaMemset(h->d_bulk, 0, (size_t)h->bulk_slots * h->bulk_stride));
   CKC(cudaMalloc(&h->d_counter, sizeof(int)));
@@ -214,6 +219,7 @@ void flyb_destroy(flyb_handle h) {
   cudaDeviceSynchronize();
   cudaFree(h->d_arena); cudaFree(h->d_sreal); cudaFree(h->d_sint); cudaFree(h->d_stats); cudaFree(h->d_trace_int);
   cudaFree(h->d_trace_real); cudaFree(h->d_bulk); cudaFree(h->d_counter); cudaFree(h->d_clip_rows);
+  cudaFree(h->d_wbpg); cudaFree(h->d_wbpg_phase);
   cudaFree(h->d_clip_off); cudaFree(h->d_clip_len); cudaFree(h->d_action); cudaFree(h->d_obs); cudaFree(h->d_rd);
   cudaFree(h->d_st); cudaFree(h->d_mask);
   cudaFreeHost(h->h_action); cudaFreeHost(h->h_obs); cudaFreeHost(h->h_rd); cudaFreeHost(h->h_st); cudaFreeHost(h->h_mask);
@@ -271,6 +277,40 @@ int flyb_load_clips(flyb_handle h, const float* rows, const int32_t* offsets, co
   CK(cudaMemcpy(h->d_clip_off, offsets, n_clips * sizeof(int), cudaMemcpyHostToDevice));
   CK(cudaMemcpy(h->d_clip_len, lengths, n_clips * sizeof(int), cudaMemcpyHostToDevice));
   h->n_clips = n_clips;
+  return 0;
+}
+
+int flyb_load_wbpg(flyb_handle h, const double* beat_freqs, const int32_t* offsets, const double* traj, const double* phase,
+                   int n_freqs, double base_freq, double rel_freq_range, double rate, double dt_ctrl) {
+  CK(cudaSetDevice(h->device));
+  if (h->m.task_type != FLYB_TASK_FLIGHT_IMITATION) { h->err = "the wing-beat pattern generator belongs to flight_imitation"; return 1; }
+  if (n_freqs <= 0 || offsets[0] != 0) { h->err = "bad wing-beat tables"; return 1; }
+  for (int f = 0; f < n_freqs; f++)
+    if (offsets[f + 1] - offsets[f] < 2) { h->err = "every wing-beat table needs at least two rows"; return 1; }
+  const size_t rows = (size_t)offsets[n_freqs];
+  /* one allocation: freqs | phase | traj (+1 padding row: reset reads row step+1) | offsets */
+  const size_t b_freq = (size_t)n_freqs * 8, b_phase = rows * 8, b_traj = (rows + 1) * 6 * 8, b_off = (size_t)(n_freqs + 1) * 4;
+  cudaFree(h->d_wbpg); h->d_wbpg = nullptr; h->wb.nfreq = 0;
+  CK(cudaMalloc(&h->d_wbpg, b_freq + b_phase + b_traj + b_off));
+  CK(cudaMemset(h->d_wbpg, 0, b_freq + b_phase + b_traj + b_off));
+  char* base = (char*)h->d_wbpg;
+  CK(cudaMemcpy(base, beat_freqs, b_freq, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(base + b_freq, phase, b_phase, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(base + b_freq + b_phase, traj, rows * 6 * 8, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(base + b_freq + b_phase + b_traj, offsets, b_off, cudaMemcpyHostToDevice));
+  h->wb.beat_freqs = (const double*)base; h->wb.phase = (const double*)(base + b_freq);
+  h->wb.traj = (const double*)(base + b_freq + b_phase); h->wb.offsets = (const int*)(base + b_freq + b_phase + b_traj);
+  h->wb.base_freq = base_freq; h->wb.rel_range = rel_freq_range; h->wb.rate = rate; h->wb.dt_ctrl = dt_ctrl;
+  h->wb.nfreq = n_freqs;
+  return 0;
+}
+
+int flyb_set_wbpg_phase(flyb_handle h, const double* phase) {
+  CK(cudaSetDevice(h->device));
+  CK(cudaDeviceSynchronize());
+  if (!phase) { cudaFree(h->d_wbpg_phase); h->d_wbpg_phase = nullptr; return 0; }
+  if (!h->d_wbpg_phase) CK(cudaMalloc(&h->d_wbpg_phase, (size_t)h->num_envs * sizeof(double)));
+  CK(cudaMemcpy(h->d_wbpg_phase, phase, (size_t)h->num_envs * sizeof(double), cudaMemcpyHostToDevice));
   return 0;
 }
 

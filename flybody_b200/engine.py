@@ -25,7 +25,7 @@ FLAG_TRACE = 1 << 16
 
 EXPORTS = ["flyb_create", "flyb_destroy", "flyb_last_error", "flyb_info", "flyb_configure", "flyb_load_clips",
            "flyb_set_clip_ids", "flyb_reset", "flyb_step", "flyb_reset_host", "flyb_step_host", "flyb_get_state",
-           "flyb_set_state", "flyb_get_trace", "flyb_episode_stats"]
+           "flyb_set_state", "flyb_get_trace", "flyb_episode_stats", "flyb_load_wbpg", "flyb_set_wbpg_phase"]
 
 
 def build_library(force: bool = False, verbose: bool = False) -> str:
@@ -70,6 +70,8 @@ def lib():
         L.flyb_set_state.argtypes = [vp, fp, fp, fp, fp, ip]
         L.flyb_get_trace.argtypes = [vp, ip, fp]
         L.flyb_episode_stats.argtypes = [vp, dp]
+        L.flyb_load_wbpg.argtypes = [vp, dp, ip, dp, dp, c_i, ctypes.c_double, ctypes.c_double, ctypes.c_double, ctypes.c_double]
+        L.flyb_set_wbpg_phase.argtypes = [vp, dp]
         _lib = L
     return _lib
 
@@ -121,6 +123,24 @@ class Engine:
         lengths = np.ascontiguousarray(lengths, np.int32)
         self._ck(lib().flyb_load_clips(self._h, _fp(rows), _ip(offsets), _ip(lengths), len(offsets)))
         self.n_clips = len(offsets)
+
+    def load_wbpg(self, tables):
+        """tables: dict from flybody_b200.wbpg.build_tables (flight_imitation only)."""
+        dp = ctypes.POINTER(ctypes.c_double)
+        f = np.ascontiguousarray(tables["beat_freqs"], np.float64); o = np.ascontiguousarray(tables["offsets"], np.int32)
+        t = np.ascontiguousarray(tables["traj"], np.float64); p = np.ascontiguousarray(tables["phase"], np.float64)
+        self._ck(lib().flyb_load_wbpg(self._h, f.ctypes.data_as(dp), _ip(o), t.ctypes.data_as(dp), p.ctypes.data_as(dp), len(f),
+                                      float(tables["base_freq"]), float(tables["rel_freq_range"]), float(tables["rate"]),
+                                      float(tables["dt_ctrl"])))
+
+    def set_wbpg_phase(self, phase):
+        """Per-env initial wing-beat phase for the next resets (None = hashed draw)."""
+        if phase is None:
+            self._ck(lib().flyb_set_wbpg_phase(self._h, None))
+        else:
+            p = np.ascontiguousarray(phase, np.float64)
+            assert p.shape == (self.num_envs,)
+            self._ck(lib().flyb_set_wbpg_phase(self._h, p.ctypes.data_as(ctypes.POINTER(ctypes.c_double))))
 
     def set_clip_ids(self, ids):
         ids = None if ids is None else np.ascontiguousarray(ids, np.int32)

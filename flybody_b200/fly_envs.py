@@ -63,7 +63,7 @@ class BatchedFlyEnv:
     """`num_envs` fruit-fly environments stepped by one CUDA launch per control step."""
 
     def __init__(self, task: str, model: dict, num_envs: int, device=0, seed: int = 0, env_offset: int = 0,
-                 clips=None, trace: bool = False, canonical_actions: bool = False):
+                 clips=None, trace: bool = False, canonical_actions: bool = False, wbpg=None):
         import torch
         if not torch.cuda.is_available():
             raise RuntimeError("flybody_b200 needs a CUDA device (there is no CPU fallback)")
@@ -74,6 +74,8 @@ class BatchedFlyEnv:
         self.engine = Engine(model, num_envs, dev.index or 0, seed, env_offset, FLAG_TRACE if trace else 0)
         if clips is not None:
             self.engine.load_clips(*clips)
+        if wbpg is not None:
+            self.engine.load_wbpg(wbpg)
         N, O, A = self.num_envs, self.engine.obs_dim, self.engine.action_dim
         self._obs = torch.zeros((N, O), dtype=torch.float32, device=dev)
         self._reward = torch.zeros(N, dtype=torch.float32, device=dev)
@@ -183,8 +185,31 @@ def walk_imitation(ref_path=None, random_state=None, terminal_com_dist: float = 
 
 def flight_imitation(wpg_pattern_path=None, ref_path=None, random_state=None, terminal_com_dist: float = 2.0,
                      num_envs: int = 1, device=0, seed: int | None = None, **kw) -> BatchedFlyEnv:
-    """Fly tracking a flying reference (`vnl_ray/fly_envs.py:29-72`).  Not built yet (scope table)."""
-    raise NotImplementedError("flight_imitation: the wing-beat pattern generator and flight task layer are not built yet")
+    """Fly tracking a flying reference with the wing-beat pattern generator (`vnl_ray/fly_envs.py:29-72`).
+
+    wpg_pattern_path: `.npy` with one wing-beat cycle `(timesteps, 3)` (yaw, roll, pitch) as the reference takes it, an
+    array of that shape, or 'synthetic' (SURVEY.md section 8d, config 3).  ref_path: `.npz` of packed flight clips
+    (`clips.save_clips`), a list of clip dicts from `clips.flight_clip_from_com`, or 'synthetic:<n_clips>:<T>:<seed>'."""
+    from . import wbpg as _wbpg
+    M = load_model(asset_path("flight_imitation"))
+    M["terminal_com_dist"] = float(terminal_com_dist)
+    if wpg_pattern_path is None or (isinstance(wpg_pattern_path, str) and wpg_pattern_path == "synthetic"):
+        base = _wbpg.synthetic_base_pattern()
+    elif isinstance(wpg_pattern_path, str):
+        base = np.load(wpg_pattern_path)
+    else:
+        base = np.asarray(wpg_pattern_path)
+    if isinstance(ref_path, str) and ref_path.startswith("synthetic"):
+        parts = ref_path.split(":")
+        n, T, cs = (int(parts[1]) if len(parts) > 1 else 16), (int(parts[2]) if len(parts) > 2 else 3006), \
+            (int(parts[3]) if len(parts) > 3 else 0)
+        clips = _clips.synthetic_flight_table(M, n, T, cs)
+    else:
+        clips = _load_clips_arg(M, ref_path)
+    if clips is None:
+        raise ValueError("flight_imitation needs reference clips (ref_path), as the reference does")
+    return BatchedFlyEnv("flight_imitation", M, num_envs, device, _seed(random_state, seed), clips=clips,
+                         wbpg=_wbpg.build_tables(base), **kw)
 
 
 def _seed(random_state, seed):

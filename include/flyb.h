@@ -61,6 +61,16 @@ int flyb_configure(flyb_handle h, int smem_level, int warps_per_block, int block
 /* Reference clips (host pointers): rows of clip_width floats, [qpos 7+nj | qvel 6+nj | root2site 3ns | joint_quat 4nj]
  * (walk_imitation) or [qpos 7 | qvel 6] (flight_imitation); clip c occupies rows offsets[c] .. offsets[c]+lengths[c]-1. */
 int flyb_load_clips(flyb_handle h, const float* rows, const int32_t* offsets, const int32_t* lengths, int n_clips);
+/* Wing-beat pattern generator tables for flight_imitation (host pointers, float64): what the reference's
+ * WingBeatPatternGenerator.__init__ builds (vnl_ray/tasks/pattern_generators.py:18-119; host builder: flybody_b200/wbpg.py):
+ * beat_freqs [n_freqs], offsets [n_freqs+1] (first row of each frequency), traj [rows, 6], phase [rows]; rate is the
+ * per-control-step low-pass factor exp(-dt_ctrl / ctrl_filter) (0 = no filter).  reset/step of the generator
+ * (pattern_generators.py:121-191) then run inside the kernel, per env. */
+int flyb_load_wbpg(flyb_handle h, const double* beat_freqs, const int32_t* offsets, const double* traj, const double* phase,
+                   int n_freqs, double base_freq, double rel_freq_range, double rate, double dt_ctrl);
+/* Initial wing-beat phase in [0,1) per env for the following resets (host pointer, num_envs doubles) - the value the
+ * reference draws with random_state.uniform() (flight_imitation.py:137).  NULL = counter-based hash of (seed, env, episode). */
+int flyb_set_wbpg_phase(flyb_handle h, const double* phase);
 /* Per-env clip choice for the next resets (host pointer, num_envs entries; -1 = counter-based random). NULL = all random. */
 int flyb_set_clip_ids(flyb_handle h, const int32_t* ids);
 

@@ -42,7 +42,9 @@ struct FlyoEnv {
   FlyoClip clip;
   int has_clip, step_counter, episode_steps, reset_next, nsub_done;
   double *sens_sum, *prev_action;
-  double wbpg_dummy;
+  FlyoWbpg wb;
+  int has_wbpg, wb_step, wb_fidx;
+  double wb_freq, init_phase;
 };
 
 /* ---------------------------------------------------------------- small math */
@@ -1442,6 +1444,47 @@ void flyo_set_option(FlyoEnv* e, const char* name, double v) {
 
 /* ---------------------------------------------------------------- task layer (stubs filled below) */
 void flyo_set_clip(FlyoEnv* e, const FlyoClip* clip) { e->clip = *clip; e->has_clip = 1; }
+void flyo_set_wbpg(FlyoEnv* e, const FlyoWbpg* w) { e->wb = *w; e->has_wbpg = 1; }
+void flyo_set_initial_phase(FlyoEnv* e, double phase) { e->init_phase = phase; }
+void flyo_wbpg_state(const FlyoEnv* e, int* step, int* freq_idx, double* ctrl_freq) {
+  *step = e->wb_step; *freq_idx = e->wb_fidx; *ctrl_freq = e->wb_freq;
+}
+
+/* ---- wing-beat pattern generator state machine: tasks/pattern_generators.py:121-191 (numpy argmin = first minimum) */
+static int wbpg_nearest_freq(const FlyoWbpg* w, double f) {
+  int best = 0;
+  double bd = fabs(w->beat_freqs[0] - f);
+  for (int i = 1; i < w->nfreq; i++) { double d = fabs(w->beat_freqs[i] - f); if (d < bd) { bd = d; best = i; } }
+  return best;
+}
+static void wbpg_reset(FlyoEnv* e, double phase0, double* ang, double* vel) {  /* :121-157 */
+  const FlyoWbpg* w = &e->wb;
+  e->wb_freq = w->base_freq;
+  e->wb_fidx = wbpg_nearest_freq(w, e->wb_freq);
+  int o = w->offsets[e->wb_fidx], n = w->offsets[e->wb_fidx + 1] - o, best = 0;
+  double bd = fabs(phase0 - w->phase[o]);
+  for (int i = 1; i < n; i++) { double d = fabs(phase0 - w->phase[o + i]); if (d < bd) { bd = d; best = i; } }
+  e->wb_step = best;
+  for (int k = 0; k < 6; k++) {
+    ang[k] = w->traj[(size_t)(o + best) * 6 + k];
+    vel[k] = (w->traj[(size_t)(o + best + 1) * 6 + k] - ang[k]) / w->dt_ctrl;
+  }
+}
+static void wbpg_step(FlyoEnv* e, double ctrl_freq, double* ang) {  /* :159-191 */
+  const FlyoWbpg* w = &e->wb;
+  int o = w->offsets[e->wb_fidx], n = w->offsets[e->wb_fidx + 1] - o;
+  e->wb_step = (e->wb_step + 1) % n;
+  e->wb_freq = w->rate == 0.0 ? ctrl_freq : e->wb_freq * w->rate + ctrl_freq * (1 - w->rate);
+  int nf = wbpg_nearest_freq(w, e->wb_freq);
+  if (nf != e->wb_fidx) {
+    double cur = fmod(w->phase[o + e->wb_step], 1.0);
+    int o2 = w->offsets[nf], n2 = w->offsets[nf + 1] - o2, best = 0;
+    double bd = fabs(cur - fmod(w->phase[o2], 1.0));
+    for (int i = 1; i < n2; i++) { double d = fabs(cur - fmod(w->phase[o2 + i], 1.0)); if (d < bd) { bd = d; best = i; } }
+    e->wb_step = best; e->wb_fidx = nf; o = o2;
+  }
+  for (int k = 0; k < 6; k++) ang[k] = w->traj[(size_t)(o + e->wb_step) * 6 + k];
+}
 
 /* quaternion helpers for the task math (vnl_ray/quaternions.py) */
 static void quat_recip(double* r, const double* q) {  /* quaternions.py:88-102 */
@@ -1563,6 +1606,22 @@ static double walk_imitation_reward(FlyoEnv* e, int step) {
          * exp(-0.5 / (s_r2s * s_r2s) * d_r2s) * exp(-0.5 / (s_jq * s_jq) * d_jq);
 }
 
+/* flight_imitation.py:169-196: CoM-distance and root-orientation factors, each a linear tolerance */
+static double flight_imitation_reward(FlyoEnv* e, const double* obs) {
+  const FlybModel* m = e->m;
+  int gb = -1;
+  for (int j = 0; j < m->njnt; j++) if (m->jnt_qposadr[j] == m->ghost_qposadr) gb = m->jnt_bodyid[j];
+  if (gb < 0) return 1.0;
+  const double off[3] = {-0.03697732, 0.00029205, -0.0142447};  /* task_utils.py:174-191 root2com */
+  double og[3], d[3];
+  quat_rotate(og, off, e->xquat + 4 * gb);
+  for (int k = 0; k < 3; k++) d[k] = e->xpos[3 * gb + k] + og[k] - e->subtree_com[3 * m->root_body + k];
+  double x = norm3(d) / 0.4, r = x < 1 ? 1 - x : 0.0;
+  const double one[4] = {1, 0, 0, 0};
+  double th = quat_dist_short_arc(one, obs + m->obs_offset[FLYB_OBS_REF_ROOT_QUAT]) / 3.14159265358979323846;
+  return r * (th < 1 ? 1 - th : 0.0);
+}
+
 static void set_ghost(FlyoEnv* e, int row, int with_vel) {  /* walk_imitation.py:119-136,138-144 */
   const FlybModel* m = e->m;
   if (m->ghost_qposadr < 0 || !e->has_clip) return;
@@ -1595,6 +1654,22 @@ int flyo_env_reset(FlyoEnv* e, double* obs) {
     for (int i = 0; i < m->n_mocap_joints; i++) e->qpos[m->jnt_qposadr[m->mocap_joint[i]]] = r[7 + i];
     set_ghost(e, 0, 0);
   }
+  if (m->task_type == FLYB_TASK_FLIGHT_IMITATION && e->has_clip) {
+    /* flight_imitation.py:106-108: traj_timesteps = min(T, round(time_limit / control_dt)) - (future_steps + 1) */
+    e->episode_steps = (e->clip.T < m->max_episode_steps ? e->clip.T : m->max_episode_steps) - (m->future_steps + 1);
+    set_ghost(e, 0, 0);                                                   /* :131-132 */
+    memcpy(e->qpos + m->root_qposadr, e->clip.qpos, 7 * sizeof(double));  /* :138 walker.set_pose */
+    if (e->has_wbpg) {                                                    /* :135-143 */
+      double ang[6], vel[6];
+      wbpg_reset(e, e->init_phase, ang, vel);
+      for (int k = 0; k < 6; k++) {
+        int j = m->wing_joint[k];
+        e->qpos[m->jnt_qposadr[j]] = ang[k];
+        e->qvel[m->jnt_dofadr[j]] = vel[k];
+      }
+    }
+    memcpy(e->qvel + m->root_dofadr, e->clip.qvel, 3 * sizeof(double));   /* :145-147 linear velocity only */
+  }
   flyo_forward(e);
   accumulate_sensors(e);
   /* composer observation buffers: first sample then zero padding unless pad_with_initial_value */
@@ -1609,6 +1684,18 @@ int flyo_env_step(FlyoEnv* e, const double* action_in, double* obs, double* rewa
   for (int i = 0; i < m->action_dim; i++) action[i] = isnan(action_in[i]) ? 0.0 : action_in[i];  /* walk_imitation.py:147 */
   int step = e->step_counter;                      /* == round(time / control_dt) before stepping */
   if (m->task_type == FLYB_TASK_WALK_IMITATION) set_ghost(e, step, 1);
+  if (m->task_type == FLYB_TASK_FLIGHT_IMITATION) {  /* flight_imitation.py:149-167 */
+    if (e->has_wbpg && m->user_action >= 0) {
+      double ang[6];
+      /* the engine's actions are float32; with a float32 action numpy (>= 2) evaluates base * (1 + rel * act) in float32 */
+      float au = (float)action[m->user_action];
+      float req = (float)e->wb.base_freq * (1.0f + (float)e->wb.rel_range * au);
+      wbpg_step(e, (double)req, ang);
+      for (int k = 0; k < 6; k++)   /* position target -> force command */
+        action[m->wing_action[k]] += ang[k] - e->qpos[m->jnt_qposadr[m->wing_joint[k]]];
+    }
+    set_ghost(e, step, 1);
+  }
   e->step_counter++;                               /* tasks/base.py:192 */
   memcpy(e->prev_action, action, m->action_dim * sizeof(double));
   for (int a = 0; a < m->nu; a++) e->ctrl[a] = m->ctrl_action[a] >= 0 ? action[m->ctrl_action[a]] : 0.0;  /* fruitfly.py:480-492 */
@@ -1634,6 +1721,14 @@ int flyo_env_step(FlyoEnv* e, const double* action_in, double* obs, double* rewa
       if (norm3(d) > m->terminal_com_dist) fatal = 1;
     }
     r = walk_imitation_reward(e, step);
+  } else if (m->task_type == FLYB_TASK_FLIGHT_IMITATION) {
+    reached_end = step == e->episode_steps;          /* flight_imitation.py:198-209 */
+    if (e->site_xpos[3 * m->thorax_site + 2] < m->terminal_height) fatal = 1;
+    if (e->has_clip) {
+      const double* d = obs + m->obs_offset[FLYB_OBS_REF_DISPLACEMENT];
+      if (norm3(d) > m->terminal_com_dist) fatal = 1;
+      r = flight_imitation_reward(e, obs);
+    }
   } else if (m->task_type == FLYB_TASK_WALK_ON_BALL) {   /* walk_on_ball.py:61-73: tolerance(linear, margin 6) */
     const double tgt[3] = {0.0, -5.0, 0.0};
     for (int k = 0; k < 3; k++) {

@@ -38,6 +38,15 @@ typedef struct FlyoClip {  /* one reference clip, row-major float64 */
   const double* joint_quat;/* [T, n_mocap_joints, 4] or NULL */
 } FlyoClip;
 
+typedef struct FlyoWbpg {   /* packed wing-beat pattern generator tables (flybody_b200/wbpg.py), float64 */
+  int nfreq;
+  const double* beat_freqs; /* [nfreq] */
+  const int* offsets;       /* [nfreq + 1] first row of each frequency */
+  const double* traj;       /* [rows, 6] */
+  const double* phase;      /* [rows] */
+  double base_freq, rel_range, rate, dt_ctrl;
+} FlyoWbpg;
+
 typedef struct FlyoEnv FlyoEnv;
 
 FlyoEnv* flyo_create(const FlybModel* m);
@@ -55,6 +64,9 @@ const FlyoContact* flyo_contacts(FlyoEnv* e, int* ncon);
 
 /* task level (composer.Environment semantics) */
 void flyo_set_clip(FlyoEnv* e, const FlyoClip* clip);
+void flyo_set_wbpg(FlyoEnv* e, const FlyoWbpg* w);   /* flight_imitation only */
+void flyo_set_initial_phase(FlyoEnv* e, double phase); /* WBPG phase drawn at the next reset (random_state.uniform()) */
+void flyo_wbpg_state(const FlyoEnv* e, int* step, int* freq_idx, double* ctrl_freq);
 int flyo_env_reset(FlyoEnv* e, double* obs);         /* returns step_type (0 = FIRST) */
 int flyo_env_step(FlyoEnv* e, const double* action, double* obs, double* reward, double* discount);
 

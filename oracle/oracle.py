@@ -31,6 +31,13 @@ class Clip(ctypes.Structure):
                 ("root2site", ctypes.POINTER(ctypes.c_double)), ("joint_quat", ctypes.POINTER(ctypes.c_double))]
 
 
+class Wbpg(ctypes.Structure):
+    _fields_ = [("nfreq", ctypes.c_int), ("beat_freqs", ctypes.POINTER(ctypes.c_double)), ("offsets", ctypes.POINTER(ctypes.c_int)),
+                ("traj", ctypes.POINTER(ctypes.c_double)), ("phase", ctypes.POINTER(ctypes.c_double)),
+                ("base_freq", ctypes.c_double), ("rel_range", ctypes.c_double), ("rate", ctypes.c_double),
+                ("dt_ctrl", ctypes.c_double)]
+
+
 _lib = None
 
 
@@ -53,6 +60,9 @@ def lib():
         L.flyo_contacts.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_int)]
         L.flyo_set_clip.argtypes = [ctypes.c_void_p, ctypes.POINTER(Clip)]
         dp = ctypes.POINTER(ctypes.c_double)
+        L.flyo_set_wbpg.argtypes = [ctypes.c_void_p, ctypes.POINTER(Wbpg)]
+        L.flyo_set_initial_phase.argtypes = [ctypes.c_void_p, ctypes.c_double]
+        L.flyo_wbpg_state.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_int), ctypes.POINTER(ctypes.c_int), dp]
         L.flyo_env_reset.argtypes = [ctypes.c_void_p, dp]
         L.flyo_env_reset.restype = ctypes.c_int
         L.flyo_env_step.argtypes = [ctypes.c_void_p, dp, dp, dp, dp]
@@ -124,6 +134,25 @@ class OracleEnv:
                  joint_quat=arrs[3].ctypes.data_as(dp) if arrs[3] is not None else None)
         self._clip = (c, arrs)
         lib().flyo_set_clip(self._h, ctypes.byref(c))
+
+    def set_wbpg(self, tables):
+        """tables: dict from flybody_b200.wbpg.build_tables"""
+        dp, ip = ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int)
+        arrs = [np.ascontiguousarray(tables["beat_freqs"], np.float64), np.ascontiguousarray(tables["offsets"], np.int32),
+                np.ascontiguousarray(tables["traj"], np.float64), np.ascontiguousarray(tables["phase"], np.float64)]
+        wb = Wbpg(nfreq=len(arrs[0]), beat_freqs=arrs[0].ctypes.data_as(dp), offsets=arrs[1].ctypes.data_as(ip),
+                  traj=arrs[2].ctypes.data_as(dp), phase=arrs[3].ctypes.data_as(dp), base_freq=tables["base_freq"],
+                  rel_range=tables["rel_freq_range"], rate=tables["rate"], dt_ctrl=tables["dt_ctrl"])
+        self._wbpg = (wb, arrs)
+        lib().flyo_set_wbpg(self._h, ctypes.byref(wb))
+
+    def set_initial_phase(self, phase):
+        lib().flyo_set_initial_phase(self._h, float(phase))
+
+    def wbpg_state(self):
+        a, b, c = ctypes.c_int(0), ctypes.c_int(0), ctypes.c_double(0)
+        lib().flyo_wbpg_state(self._h, ctypes.byref(a), ctypes.byref(b), ctypes.byref(c))
+        return a.value, b.value, c.value
 
     def env_reset(self):
         obs = np.zeros(self.M["obs_dim"])

@@ -33,6 +33,9 @@ def lib():
         L.emu_destroy.argtypes = [ctypes.c_void_p]
         fp, ip, dp = ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_int), ctypes.POINTER(ctypes.c_double)
         L.emu_set_clips.argtypes = [ctypes.c_void_p, fp, ip, ip, ctypes.c_int]
+        L.emu_set_wbpg.argtypes = [ctypes.c_void_p, dp, ip, dp, dp, ctypes.c_int, dp]
+        L.emu_set_phase.argtypes = [ctypes.c_void_p, ctypes.c_double]
+        L.emu_wbpg_state.argtypes = [ctypes.c_void_p, ip, ip, dp]
         L.emu_env_reset.argtypes = [ctypes.c_void_p, fp]
         L.emu_env_step.argtypes = [ctypes.c_void_p, fp, fp, dp, dp]
         for fn in ("emu_forward", "emu_physics_step"):
@@ -104,6 +107,22 @@ class EmuEnv:
         self._clips = (t, o, ln)
         fp, ip = ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_int)
         lib().emu_set_clips(self._h, t.ctypes.data_as(fp), o.ctypes.data_as(ip), ln.ctypes.data_as(ip), len(o))
+
+    def set_wbpg(self, tables):
+        dp, ip = ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int)
+        a = [np.ascontiguousarray(tables["beat_freqs"], np.float64), np.ascontiguousarray(tables["offsets"], np.int32),
+             np.ascontiguousarray(tables["traj"], np.float64), np.ascontiguousarray(tables["phase"], np.float64),
+             np.array([tables["base_freq"], tables["rel_freq_range"], tables["rate"], tables["dt_ctrl"]], np.float64)]
+        lib().emu_set_wbpg(self._h, a[0].ctypes.data_as(dp), a[1].ctypes.data_as(ip), a[2].ctypes.data_as(dp),
+                           a[3].ctypes.data_as(dp), len(a[0]), a[4].ctypes.data_as(dp))
+
+    def set_initial_phase(self, phase):
+        lib().emu_set_phase(self._h, float(phase))
+
+    def wbpg_state(self):
+        a, b, c = ctypes.c_int(0), ctypes.c_int(0), ctypes.c_double(0)
+        lib().emu_wbpg_state(self._h, ctypes.byref(a), ctypes.byref(b), ctypes.byref(c))
+        return a.value, b.value, c.value
 
     def env_reset(self):
         obs = np.zeros(int(self.M["obs_dim"]), np.float32)

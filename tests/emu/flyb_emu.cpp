@@ -14,6 +14,9 @@
 struct EmuBase {
   virtual ~EmuBase() {}
   virtual void set_clips(const float* data, const int* off, const int* len, int n) = 0;
+  virtual void set_wbpg(const double* freqs, const int* off, const double* traj, const double* phase, int nf, const double* prm) = 0;
+  virtual void set_phase(double p) = 0;
+  virtual void wbpg_state(int* step, int* fidx, double* freq) = 0;
   virtual int env_reset(float* obs) = 0;
   virtual int env_step(const float* action, float* obs, double* reward, double* discount) = 0;
   virtual void forward() = 0;
@@ -35,6 +38,10 @@ struct Emu : EmuBase {
   std::vector<float> clip_data;
   std::vector<int> clip_off, clip_len;
   FlyClips clips;
+  FlyWbpg wb;
+  std::vector<double> wb_freqs, wb_traj, wb_phase;
+  std::vector<int> wb_off;
+  double phase0 = 0;
   std::string err;
 
   Emu(const FlybModel* fm, int flags) {
@@ -49,6 +56,7 @@ struct Emu : EmuBase {
     sint.assign(FLY_SI_COUNT, 0);
     sint[FLY_SI_FORCED_CLIP] = -1;
     clips.data = 0; clips.offset = 0; clips.length = 0; clips.nclips = 0;
+    memset(&wb, 0, sizeof(wb));
     for (int i = 0; i < m.nq; i++) w.qpos[i] = m.qpos0[i];
   }
   void set_clips(const float* data, const int* off, const int* len, int n) override {
@@ -59,25 +67,38 @@ struct Emu : EmuBase {
     clips.data = clip_data.data(); clips.offset = clip_off.data(); clips.length = clip_len.data(); clips.nclips = n;
     sint[FLY_SI_FORCED_CLIP] = 0;
   }
+  void set_wbpg(const double* freqs, const int* off, const double* traj, const double* phase, int nf, const double* prm) override {
+    const int rows = off[nf];
+    wb_freqs.assign(freqs, freqs + nf); wb_off.assign(off, off + nf + 1);
+    wb_traj.assign(traj, traj + (size_t)rows * 6); wb_traj.resize((size_t)(rows + 1) * 6, 0.0);
+    wb_phase.assign(phase, phase + rows);
+    wb.nfreq = nf; wb.beat_freqs = wb_freqs.data(); wb.offsets = wb_off.data(); wb.traj = wb_traj.data(); wb.phase = wb_phase.data();
+    wb.base_freq = prm[0]; wb.rel_range = prm[1]; wb.rate = prm[2]; wb.dt_ctrl = prm[3];
+  }
+  void set_phase(double p) override { phase0 = p; }
+  void wbpg_state(int* step, int* fidx, double* freq) override {
+    *step = sint[FLY_SI_WB_STEP]; *fidx = sint[FLY_SI_WB_FIDX]; *freq = fly_get_double(sint.data() + FLY_SI_WB_FREQ_LO);
+  }
   FlyIO<T> io(const float* action, float* obs, float* rdst) {
     FlyIO<T> o;
     memset(&o, 0, sizeof(o));
     o.sreal = sreal.data(); o.sint = sint.data(); o.sreal_stride = (int)sreal.size();
     o.action = action; o.obs = obs; o.reward = rdst; o.discount = rdst + 1; o.step_type = (int*)(rdst + 2);
+    o.wbpg_phase = &phase0;
     return o;
   }
   int env_reset(float* obs) override {
     float rd[4];
     FlyIO<T> o = io(0, obs, rd);
     o.force_reset = 1;
-    fly_env_run(m, w, clips, o, 0);
+    fly_env_run(m, w, clips, wb, o, 0);
     return *(int*)(rd + 2);
   }
   int env_step(const float* action, float* obs, double* reward, double* discount) override {
     float rd[4];
     FlyIO<T> o = io(action, obs, rd);
     /* full-precision reward: rerun through the typed path */
-    fly_env_run(m, w, clips, o, 0);
+    fly_env_run(m, w, clips, wb, o, 0);
     *reward = rd[0]; *discount = rd[1];
     return *(int*)(rd + 2);
   }
@@ -141,6 +162,11 @@ void* emu_create(const FlybModel* m, int flags, int use_double, char* errbuf, in
 }
 void emu_destroy(void* h) { delete (EmuBase*)h; }
 void emu_set_clips(void* h, const float* data, const int* off, const int* len, int n) { ((EmuBase*)h)->set_clips(data, off, len, n); }
+void emu_set_wbpg(void* h, const double* freqs, const int* off, const double* traj, const double* phase, int nf, const double* prm) {
+  ((EmuBase*)h)->set_wbpg(freqs, off, traj, phase, nf, prm);
+}
+void emu_set_phase(void* h, double p) { ((EmuBase*)h)->set_phase(p); }
+void emu_wbpg_state(void* h, int* step, int* fidx, double* freq) { ((EmuBase*)h)->wbpg_state(step, fidx, freq); }
 int emu_env_reset(void* h, float* obs) { return ((EmuBase*)h)->env_reset(obs); }
 int emu_env_step(void* h, const float* a, float* obs, double* r, double* g) { return ((EmuBase*)h)->env_step(a, obs, r, g); }
 void emu_forward(void* h) { ((EmuBase*)h)->forward(); }

@@ -150,3 +150,36 @@ def test_walk_on_ball_rollout_matches_oracle(models):
         st, r, g, oobs = o.env_step(a.astype(np.float64)); st2, r2, g2, eobs = e.env_step(a)
         assert st == st2 and g == g2 and abs(r - r2) <= 1e-5
         assert _rel(eobs, oobs) < 5e-4
+
+
+def test_flight_imitation_rollout_matches_oracle(models):
+    """flight task layer: generator indices bit-exact, obs / reward in tolerance."""
+    from flybody_b200 import clips as C, wbpg as W
+    from oracle.oracle import OracleEnv
+    from tests.emu.emu import EmuEnv
+    M = models["flight_imitation"]
+    rows, off, ln = C.pack_clips(M, [C.synth_flight_clip(T=120, seed=5)])
+    r = rows.astype(np.float64)
+    t = W.build_tables(W.synthetic_base_pattern())
+    for double, tol_obs, tol_r in ((True, 2e-7, 1e-6), (False, 5e-4, 1e-5)):
+        o, e = OracleEnv(M), EmuEnv(M, double=double)
+        o.set_clip(r[:, :7], r[:, 7:13]); o.set_wbpg(t); o.set_initial_phase(0.61)
+        e.set_clips(rows, off, ln); e.set_wbpg(t); e.set_initial_phase(0.61)
+        st, oobs = o.env_reset(); st2, eobs = e.env_reset()
+        assert st == st2 == 0 and _rel(eobs, oobs) < tol_obs and o.wbpg_state() == e.wbpg_state()
+        rng = np.random.RandomState(1)
+        user = int(M["user_action"])
+        u = 0.0
+        for k in range(130):
+            a = (0.4 * rng.uniform(M["action_min"], M["action_max"])).astype(np.float32)
+            u = float(np.clip(u + rng.normal(scale=0.3), -1, 1))
+            a[user] = u
+            st, rw, g, oobs = o.env_step(a.astype(np.float64)); st2, rw2, g2, eobs = e.env_step(a)
+            assert st == st2 and g == g2
+            assert o.wbpg_state() == e.wbpg_state(), k          # (table step, frequency index, filtered frequency)
+            assert abs(rw - rw2) <= tol_r * max(1.0, abs(rw))
+            assert _rel(eobs, oobs) < tol_obs
+            if st == 2:
+                break
+        # the clip has 120 rows: the episode ends "well" at step 120 - 6 with discount 1 (flight_imitation.py:106-108,211-220)
+        assert st == 2 and k + 1 == 120 - 6 and g == 1.0

@@ -175,3 +175,74 @@ def test_fly_envs_api_and_large_batch_properties(models):
         env2.step(a)
     assert (env2.flat_observation == first).all()   # counter-based clip choice + deterministic kernels
     env.close(); env2.close()
+
+
+def test_flight_imitation_matches_oracle(models):
+    """flight_imitation through the C ABI: wing-beat generator state bit-exact, obs / reward / termination vs the oracle,
+    envs with different clips and initial phases in one launch."""
+    from flybody_b200 import clips as C, wbpg as W
+    from flybody_b200.engine import Engine, FLAG_TRACE
+    from oracle.oracle import OracleEnv
+    M = models["flight_imitation"]
+    clips = [C.synth_flight_clip(T=90, seed=7), C.synth_flight_clip(T=140, seed=8)]
+    rows, off, ln = C.pack_clips(M, clips)
+    t = W.build_tables(W.synthetic_base_pattern())
+    N = 6
+    clip_ids = np.array([0, 1, 0, 1, 1, 0], np.int32)
+    phases = np.array([0.05, 0.31, 0.5, 0.77, 0.93, 0.05])
+    eng = Engine(M, N, 0, flags=FLAG_TRACE)
+    eng.load_clips(rows, off, ln); eng.load_wbpg(t)
+    eng.set_clip_ids(clip_ids); eng.set_wbpg_phase(phases)
+    orc = []
+    for i in range(N):
+        r = rows[off[clip_ids[i]]:off[clip_ids[i]] + ln[clip_ids[i]]].astype(np.float64)
+        o = OracleEnv(M)
+        o.set_clip(r[:, :7], r[:, 7:13]); o.set_wbpg(t); o.set_initial_phase(phases[i])
+        orc.append(o)
+    st, obs = eng.reset_host()
+    for i in range(N):
+        ost, oobs = orc[i].env_reset()
+        assert st[i] == ost == 0 and _rel(obs[i], oobs) < 2e-5
+    assert (obs[0] == obs[5]).all(), "same clip and phase -> same bits"
+    rng = np.random.RandomState(2)
+    user = int(M["user_action"])
+    done = np.zeros(N, bool)
+    for k in range(100):
+        a = (0.4 * rng.uniform(M["action_min"], M["action_max"], size=(N, int(M["action_dim"])))).astype(np.float32)
+        a[:, user] = np.clip(np.sin(0.3 * k + np.arange(N)) + rng.normal(scale=0.2, size=N), -1, 1)
+        a[5] = a[0]
+        st, r, g, obs = eng.step_host(a)
+        si = eng.get_state()["ints"]
+        for i in range(N):
+            if done[i]:
+                continue
+            ost, orr, og, oobs = orc[i].env_step(a[i].astype(np.float64))
+            assert st[i] == ost and g[i] == og, (k, i)
+            ws, wf, cf = orc[i].wbpg_state()
+            assert (int(si[i, 7]), int(si[i, 8])) == (ws, wf), (k, i)      # FLY_SI_WB_STEP, FLY_SI_WB_FIDX
+            assert np.array([si[i, 9], si[i, 10]], np.int32).view(np.float64)[0] == cf
+            # reward within 1e-5 while the fp32 state has not drifted from the float64 one; 1e-4 later in the rollout
+            # (the CoM-distance factor is 1 - d / 0.4 cm: 4e-6 cm of accumulated position drift is 1e-5 of reward)
+            assert abs(float(r[i]) - orr) <= (1e-5 if k < 20 else 1e-4) * max(1.0, abs(orr))
+            assert _rel(obs[i], oobs) < 5e-4
+            done[i] = ost == 2
+        assert (obs[0] == obs[5]).all()
+        if done.all():
+            break
+    # clip 0 has 90 rows -> good end at step 84; clip 1 has 140 rows -> still running at step 100 unless it crashed
+    assert done[[0, 2, 5]].all()
+    eng.close()
+
+
+def test_fly_envs_flight_imitation_api():
+    import torch
+    from flybody_b200 import fly_envs
+    env = fly_envs.flight_imitation("synthetic", "synthetic:4:400:0", num_envs=64, seed=3)
+    ts = env.reset()
+    assert ts.observation["walker/ref_displacement"].shape == (64, 6, 3) and ts.observation["walker/joints_pos"].shape == (64, 25)
+    assert env.action_spec().shape == (12,)
+    total = torch.zeros(64, device=env.device)
+    for _ in range(20):
+        ts = env.step(torch.zeros((64, 12), device=env.device))
+        total += ts.reward
+    assert torch.isfinite(total).all() and (total > 0).all()

@@ -87,7 +87,39 @@ def quaternion_vectors(seed=1):
     print("quaternions: ok")
 
 
+def wbpg_vectors(seed=2, n_steps=1500):
+    """wbpg.npz - the reference WingBeatPatternGenerator (tasks/pattern_generators.py) run on the synthetic base
+    pattern: table sizes and checksums, and a reset + n_steps trace (requested frequency, table step, frequency index,
+    wing angles) for a frequency command that wanders over the whole range."""
+    import tempfile
+    from vnl_ray.tasks.pattern_generators import WingBeatPatternGenerator   # reference code
+    from flybody_b200 import wbpg as W
+    base = W.synthetic_base_pattern()
+    with tempfile.NamedTemporaryFile(suffix=".npy") as f:
+        np.save(f.name, base)
+        g = WingBeatPatternGenerator(base_pattern_path=f.name)
+    lens = np.array([t["traj"].shape[0] for t in g.traj_ctrl], np.int32)
+    traj_sum = np.array([t["traj"].sum() for t in g.traj_ctrl])
+    phase_sum = np.array([t["phase"].sum() for t in g.traj_ctrl])
+    rng = np.random.RandomState(seed)
+    phase0 = float(rng.uniform())
+    q0, v0 = g.reset(initial_phase=phase0, return_qvel=True)
+    # user action in [-1, 1]: slow random walk with occasional jumps, as float32 like the engine's input
+    act = np.clip(np.cumsum(rng.normal(scale=0.05, size=n_steps)) + (rng.uniform(size=n_steps) < 0.01) * rng.uniform(-1, 1, n_steps), -1, 1).astype(np.float32)
+    steps, fidx, angles, cf = [], [], [], []
+    for k in range(n_steps):
+        freq = g.base_beat_freq * (1 + g.rel_freq_range * act[k])           # flight_imitation.py:153-154
+        a = g.step(ctrl_freq=freq)
+        steps.append(g._step); fidx.append(g._freq_idx); angles.append(a.copy()); cf.append(g._ctrl_freq)
+    np.savez_compressed(os.path.join(OUT, "wbpg.npz"), base=base, lens=lens, traj_sum=traj_sum, phase_sum=phase_sum,
+                        beat_freqs=g.beat_freqs, phase0=phase0, q0=q0, v0=v0, act=act, steps=np.array(steps, np.int32),
+                        freq_idx=np.array(fidx, np.int32), angles=np.array(angles), ctrl_freq=np.array(cf),
+                        row0_f0=g.traj_ctrl[0]["traj"][:4], row0_f200=g.traj_ctrl[200]["traj"][:4])
+    print("wbpg: table rows", int(lens.sum()), "frequency switches", int((np.diff(fidx) != 0).sum()))
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
     walk_reward()
     quaternion_vectors()
+    wbpg_vectors()
