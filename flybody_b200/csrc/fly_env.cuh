@@ -321,13 +321,8 @@ FLY_FN void fly_env_run(const DModel<T>& m, const Ws<T>& w, const FlyClips& clip
          position targets turned into force commands: action[wings] += target - wing qpos */
       float au = action_in[m.user_action];
       if (au != au) au = 0;
-      /* float32 like the reference with a float32 action under numpy >= 2 (flybody_b200/wbpg.py: requested_freq) */
-#ifdef FLY_GPU
-      const float reqf = __fmul_rn((float)wb.base_freq, __fadd_rn(1.0f, __fmul_rn((float)wb.rel_range, au)));  /* no FMA contraction */
-#else
-      const float reqf = (float)wb.base_freq * (1.0f + (float)wb.rel_range * au);
-#endif
-      const double req = (double)reqf;
+      /* float64 from the float32 action, as numpy 1.26.4 (the reference's pin) evaluates it (flybody_b200/wbpg.py) */
+      const double req = fly_mul_rn(wb.base_freq, fly_add_rn(1.0, fly_mul_rn(wb.rel_range, (double)au)));
       int fidx = sint[FLY_SI_WB_FIDX], ws = sint[FLY_SI_WB_STEP];
       double cf = fly_get_double(sint + FLY_SI_WB_FREQ_LO);
       const int o = wb.offsets[fidx], n = wb.offsets[fidx + 1] - o;

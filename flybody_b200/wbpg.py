@@ -70,11 +70,10 @@ def synthetic_base_pattern(n=64):
 
 
 def requested_freq(user_action, base_freq=BASE_FREQ, rel_freq_range=REL_FREQ_RANGE):
-    """flight_imitation.py:151-154 for a float32 action, as numpy >= 2 evaluates it: `base * (1 + rel * act)` stays in
-    float32 (python floats are weak scalars), and only the generator's low-pass promotes it to float64.  The engine's
-    action input is float32, so kernel and oracle do exactly this."""
-    a = np.float32(user_action)
-    return np.float32(base_freq) * (np.float32(1) + np.float32(rel_freq_range) * a)
+    """flight_imitation.py:151-154.  The reference pins numpy==1.26.4 (setup.py), where `base * (1 + rel * act)` with a
+    float32 `act` and python-float constants is evaluated in float64 (legacy value-based promotion; numpy >= 2 would
+    stay in float32).  The engine's action input is float32, so kernel and oracle widen it to float64 first."""
+    return np.float64(base_freq) * (np.float64(1) + np.float64(rel_freq_range) * np.float64(np.float32(user_action)))
 
 
 class WbpgState:

@@ -1687,10 +1687,8 @@ int flyo_env_step(FlyoEnv* e, const double* action_in, double* obs, double* rewa
   if (m->task_type == FLYB_TASK_FLIGHT_IMITATION) {  /* flight_imitation.py:149-167 */
     if (e->has_wbpg && m->user_action >= 0) {
       double ang[6];
-      /* the engine's actions are float32; with a float32 action numpy (>= 2) evaluates base * (1 + rel * act) in float32 */
-      float au = (float)action[m->user_action];
-      float req = (float)e->wb.base_freq * (1.0f + (float)e->wb.rel_range * au);
-      wbpg_step(e, (double)req, ang);
+      /* float64, as numpy 1.26.4 (the reference's pin) evaluates base * (1 + rel * act) for a float32 act */
+      wbpg_step(e, e->wb.base_freq * (1 + e->wb.rel_range * (double)(float)action[m->user_action]), ang);
       for (int k = 0; k < 6; k++)   /* position target -> force command */
         action[m->wing_action[k]] += ang[k] - e->qpos[m->jnt_qposadr[m->wing_joint[k]]];
     }

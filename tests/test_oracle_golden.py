@@ -56,7 +56,7 @@ def test_wbpg_tables_and_state_machine_match_reference_class():
     q0, v0 = s.reset(float(G["phase0"]))
     assert np.array_equal(q0, G["q0"]) and np.array_equal(v0, G["v0"])
     for k, a in enumerate(G["act"]):
-        ang = s.step(t["base_freq"] * (1 + t["rel_freq_range"] * a))
+        ang = s.step(W.requested_freq(a))
         assert (s.step_idx, s.freq_idx) == (int(G["steps"][k]), int(G["freq_idx"][k])), k
         assert np.array_equal(ang, G["angles"][k]) and s.ctrl_freq == G["ctrl_freq"][k]
 

@@ -108,7 +108,9 @@ def wbpg_vectors(seed=2, n_steps=1500):
     act = np.clip(np.cumsum(rng.normal(scale=0.05, size=n_steps)) + (rng.uniform(size=n_steps) < 0.01) * rng.uniform(-1, 1, n_steps), -1, 1).astype(np.float32)
     steps, fidx, angles, cf = [], [], [], []
     for k in range(n_steps):
-        freq = g.base_beat_freq * (1 + g.rel_freq_range * act[k])           # flight_imitation.py:153-154
+        # flight_imitation.py:153-154; float64(act): what the reference's pinned numpy 1.26.4 computes for a float32
+        # action (legacy promotion), independent of the numpy running this script
+        freq = g.base_beat_freq * (1 + g.rel_freq_range * np.float64(act[k]))
         a = g.step(ctrl_freq=freq)
         steps.append(g._step); fidx.append(g._freq_idx); angles.append(a.copy()); cf.append(g._ctrl_freq)
     np.savez_compressed(os.path.join(OUT, "wbpg.npz"), base=base, lens=lens, traj_sum=traj_sum, phase_sum=phase_sum,
