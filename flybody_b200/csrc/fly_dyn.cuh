@@ -16,7 +16,7 @@ FLY_FN void fly_kinematics(const DModel<T>& m, const Ws<T>& w) {
   FLY_LANE0 {
     for (int k = 0; k < 3; k++) { w.xpos[k] = 0; w.xipos[k] = 0; }
     w.xquat[0] = 1; w.xquat[1] = w.xquat[2] = w.xquat[3] = 0;
-    for (int k = 0; k < 9; k++) { w.xmat[k] = (k % 4 == 0) ? T(1) : T(0); w.ximat[k] = w.xmat[k]; }
+    for (int k = 0; k < 9; k++) w.xmat[k] = (k % 4 == 0) ? T(1) : T(0);
   }
   FLY_SYNC();
   for (int L = 1; L <= m.nlevel; L++) {
@@ -54,15 +54,13 @@ FLY_FN void fly_kinematics(const DModel<T>& m, const Ws<T>& w) {
         for (int c = 0; c < 3; c++) pos[c] = anchor[c] - t[c];
       }
       quat_normalize(quat);
-      T mat[9], iq[4];
+      T mat[9];
       quat2mat(mat, quat);
       for (int c = 0; c < 3; c++) w.xpos[3 * b + c] = pos[c];
       for (int c = 0; c < 4; c++) w.xquat[4 * b + c] = quat[c];
       for (int c = 0; c < 9; c++) w.xmat[9 * b + c] = mat[c];
       mat_vec(t, mat, m.body_ipos + 3 * b);
       for (int c = 0; c < 3; c++) w.xipos[3 * b + c] = pos[c] + t[c];
-      quat_mul(iq, quat, m.body_iquat + 4 * b);
-      quat2mat(w.ximat + 9 * b, iq);
     }
     FLY_SYNC();
   }
@@ -120,7 +118,9 @@ FLY_FN void fly_com_pos(const DModel<T>& m, const Ws<T>& w) {
   FLY_SYNC();
   FLY_FOR(bb, m.nbody - 1) {
     const int b = bb + 1;
-    const T* R = w.ximat + 9 * b;
+    T iq[4], R[9];  /* inertial frame orientation (ximat), rebuilt here instead of being stored by the kinematics */
+    quat_mul(iq, w.xquat + 4 * b, m.body_iquat + 4 * b);
+    quat2mat(R, iq);
     const T* I = m.body_inertia + 3 * b;
     const T* c0 = w.scom + 3 * m.body_rootid[b];
     T d[3], mass = m.body_mass[b];
@@ -177,6 +177,7 @@ FLY_FN void fly_crb(const DModel<T>& m, const Ws<T>& w) {
   T* f = w.cdof_dot; /* scratch: cdof_dot is rebuilt later, in the velocity stage */
   FLY_FOR(i, m.nv) inert_vec(f + 6 * i, w.crb + 10 * m.dof_bodyid[i], w.cdof + 6 * i);
   FLY_SYNC();
+  const T dt = m.timestep;
   FLY_FOR(e, m.nM) {
     const int i = m.mrow[e], j = m.mcol[e], k = e - m.madr[i];
     T s = 0;
@@ -185,7 +186,10 @@ FLY_FN void fly_crb(const DModel<T>& m, const Ws<T>& w) {
       s = a[0] * b[0] + a[1] * b[1] + a[2] * b[2] + a[3] * b[3] + a[4] * b[4] + a[5] * b[5];
       if (k == 0) s += m.dof_armature[i];
     }
-    w.qM[e] = s;
+    /* M goes straight into the two arrays that are factorised in place: qLD <- M, qH <- M + dt * damping (the matrix of
+       the implicit-damping Euler step, m13).  M itself is not kept: products with it use the factors (fly_mul_m). */
+    w.qLD[e] = s;
+    w.qH[e] = k == 0 ? s + dt * m.dof_damping[i] : s;
   }
   FLY_SYNC();
 }
@@ -427,17 +431,23 @@ FLY_FN void fly_solve(const DModel<T>& m, const T* const* LD, const T* const* in
   FLY_SYNC();
 }
 
-/* r <- M v (tree-sparse symmetric product) */
+/* r <- M v from the factors, M = L^T D L:  z = D (L v) by a gather along each row, then r = L^T z by a gather over the
+ * descendants (warp-cooperative for the few dofs with many descendants).  z is an nv scratch vector. */
 template <class T>
-FLY_FN void fly_mul_m(const DModel<T>& m, const T* M, T* r, const T* v) {
+FLY_FN void fly_mul_m(const DModel<T>& m, const T* LD, T* r, const T* v, T* z) {
   FLY_FOR(i, m.nv) {
     const int a = m.madr[i], nrow = m.madr[i + 1] - a;
-    T s = 0;
-    for (int q = 0; q < nrow; q++) s += M[a + q] * v[m.mcol[a + q]];
+    T s = v[i];
+    for (int q = 1; q < nrow; q++) s += LD[a + q] * v[m.mcol[a + q]];
+    z[i] = LD[a] * s;
+  }
+  FLY_SYNC();
+  FLY_FOR(i, m.nv) {
+    T s = z[i];
     if (m.hsublast[i] - i <= FLY_HEAVY)
       for (int q = m.desc_adr[i]; q < m.desc_adr[i + 1]; q++) {
         const int pk = m.desc[q];
-        s += M[pk >> 8] * v[pk & 255];
+        s += LD[pk >> 8] * z[pk & 255];
       }
     r[i] = s;
   }
@@ -447,7 +457,7 @@ FLY_FN void fly_mul_m(const DModel<T>& m, const T* M, T* r, const T* v) {
     T s = 0;
     FLY_FOR(q, nd) {
       const int pk = m.desc[q0 + q];
-      s += M[pk >> 8] * v[pk & 255];
+      s += LD[pk >> 8] * z[pk & 255];
     }
     s = warp_sum(s);
     FLY_SYNC();

@@ -13,6 +13,11 @@
 #include <math.h>
 #include <stdint.h>
 
+#ifndef FLY_SYNC_MASK
+#define FLY_SYNC_MASK 0x3ffffu  /* bit per block rendezvous point (fly_task.cuh) */
+#endif
+#define FLY_STAGE_SYNC(bit) do { if (FLY_SYNC_MASK & (1u << (bit))) FLY_BLOCK_SYNC(); } while (0)
+
 #if defined(__CUDACC__) && !defined(FLY_EMU)
 #define FLY_GPU 1
 #define FLY_FN __device__ __forceinline__

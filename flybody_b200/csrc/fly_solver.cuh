@@ -281,7 +281,7 @@ FLY_FN void fly_newton(const DModel<T>& m, const Ws<T>& w) {
   /* warm start: the better of qacc_warmstart and qacc_smooth */
   FLY_FOR(d, nv) dvec[d] = w.warm[d] - w.qacc_smooth[d];
   FLY_SYNC();
-  fly_mul_m(m, w.qM, m0, dvec);
+  fly_mul_m(m, w.qLD, m0, dvec, w.stmp);
   S dd = 0;
   FLY_FOR(d, nv) dd += (S)dvec[d] * (S)m0[d];
   dd = warp_sum(dd);
@@ -451,7 +451,9 @@ FLY_FN void fly_fwd_constraint(const DModel<T>& m, const Ws<T>& w) {
   }
   FLY_SYNC();
   if (nefc) fly_constraint_prepare(m, w);
+  FLY_STAGE_SYNC(15);
   fly_newton(m, w);
+  FLY_STAGE_SYNC(16);
   if (nefc && !(m.flags & FLY_OPT_NONOSLIP) && m.opt_noslip_iterations > 0) {
     fly_noslip(m, w);
     /* qacc = qacc_smooth + M^-1 J^T f */
@@ -462,6 +464,7 @@ FLY_FN void fly_fwd_constraint(const DModel<T>& m, const Ws<T>& w) {
      (m13), (M + dt B)^-1 (qfrc_smooth + qfrc_constraint), whose right-hand side is final here as well. */
   FLY_FOR(d, m.nv) w.sMa[d] = w.qfrc_smooth[d] + w.qfrc_constraint[d];
   FLY_SYNC();
+  FLY_STAGE_SYNC(17);
   {
     const T* LD[2] = {w.qLD, w.qH};
     const T* iv[2] = {w.qDinv, w.qHinv};

@@ -137,11 +137,18 @@ FLY_FN void fly_sensors_vel(const DModel<T>& m, const Ws<T>& w) {
 }
 
 /* ---------------------------------------------------------------- pipeline pieces
- * Block rendezvous points (FLY_BLOCK_SYNC): 3 in fly_step1, 3 in fly_forward_acc, 1 in fly_integrate.  A warp that
- * does less than a full control step (reset, masked or idle) makes the difference up with fly_block_pad. */
-#define FLY_NB_STEP1 3
-#define FLY_NB_FWD 3
-#define FLY_NB_INT 1
+ * Block rendezvous points (FLY_STAGE_SYNC, one bit of FLY_SYNC_MASK each): between all stages of fly_step1 and
+ * fly_forward_acc and before fly_integrate; every warp passes each of them once per call whatever its env does.  A warp
+ * that does less than a full control step (reset, masked or idle) makes the difference up with fly_block_pad.
+ * Measured on B200 (16 warps per SM): without any rendezvous the kernel is 3.4x slower than with seven per substep. */
+/* rendezvous bits: fly_step1 0,7,8,9,1,10,2,11,12,13 (in program order) ; fly_forward_acc 3,14,4,15,16,17,5 ; fly_integrate 6 */
+#define FLY_SYNC_BITS_STEP1 0x3f87u
+#define FLY_SYNC_BITS_FWD 0x3c038u
+#define FLY_SYNC_BITS_INT 0x40u
+FLY_INL constexpr int fly_popc(unsigned x) { return x ? (int)(x & 1u) + fly_popc(x >> 1) : 0; }
+#define FLY_NB_STEP1 fly_popc(FLY_SYNC_MASK & FLY_SYNC_BITS_STEP1)
+#define FLY_NB_FWD fly_popc(FLY_SYNC_MASK & FLY_SYNC_BITS_FWD)
+#define FLY_NB_INT fly_popc(FLY_SYNC_MASK & FLY_SYNC_BITS_INT)
 template <class T>
 FLY_INL int fly_nb_control_step(const DModel<T>& m) {
   return (1 + m.n_substeps) * FLY_NB_STEP1 + m.n_substeps * (FLY_NB_FWD + FLY_NB_INT);
@@ -152,58 +159,54 @@ FLY_INL void fly_block_pad(int n) {
 
 template <class T>
 FLY_FN void fly_step1(const DModel<T>& m, const Ws<T>& w, bool full) {
-  FLY_BLOCK_SYNC();
+  FLY_STAGE_SYNC(0);
   fly_kinematics(m, w);
+  FLY_STAGE_SYNC(7);
   fly_com_pos(m, w);
+  FLY_STAGE_SYNC(8);
+  if (full) fly_crb(m, w);
+  FLY_STAGE_SYNC(9);
   if (full) {
-    fly_crb(m, w);
-    {  /* M and M + dt * damping (the matrix of the implicit-damping Euler step, m13) are factorised together */
-      const T dt = m.timestep;
-      FLY_FOR(e, m.nM) {
-        const int i = m.mrow[e];
-        const T v = w.qM[e];
-        w.qLD[e] = v;
-        w.qH[e] = v + (e == m.madr[i] ? dt * m.dof_damping[i] : T(0));
-      }
-      FLY_SYNC();
+    {  /* M and M + dt * damping (both written by fly_crb) are factorised together */
       T* LD[2] = {w.qLD, w.qH};
       T* iv[2] = {w.qDinv, w.qHinv};
       fly_factor<T, 2>(m, LD, iv);
     }
   }
-  FLY_BLOCK_SYNC();
-  if (full) {
-    fly_collision(m, w);
-    fly_make_constraint(m, w);
-  }
-  FLY_BLOCK_SYNC();
+  FLY_STAGE_SYNC(1);
+  if (full) fly_collision(m, w);
+  FLY_STAGE_SYNC(10);
+  if (full) fly_make_constraint(m, w);
+  FLY_STAGE_SYNC(2);
   fly_com_vel(m, w);
-  if (full) {
-    fly_passive(m, w);
-    fly_rne(m, w, w.qfrc_bias, 0, 0);
-  }
+  FLY_STAGE_SYNC(11);
+  if (full) fly_passive(m, w);
+  FLY_STAGE_SYNC(12);
+  if (full) fly_rne(m, w, w.qfrc_bias, 0, 0);
+  FLY_STAGE_SYNC(13);
   fly_sensors_vel(m, w);
 }
 
 /* actuation, smooth acceleration, constraint solve, acceleration sensors */
 template <class T>
 FLY_FN void fly_forward_acc(const DModel<T>& m, const Ws<T>& w) {
-  FLY_BLOCK_SYNC();
+  FLY_STAGE_SYNC(3);
   fly_actuation(m, w);
   FLY_FOR(d, m.nv) {
     const T f = w.qfrc_passive[d] - w.qfrc_bias[d] + w.qfrc_actuator[d];
     w.qfrc_smooth[d] = f; w.qacc_smooth[d] = f;
   }
   FLY_SYNC();
+  FLY_STAGE_SYNC(14);
   {
     const T* LD[1] = {w.qLD};
     const T* iv[1] = {w.qDinv};
     T* x[1] = {w.qacc_smooth};
     fly_solve<T, 1>(m, LD, iv, x);
   }
-  FLY_BLOCK_SYNC();
+  FLY_STAGE_SYNC(4);
   fly_fwd_constraint(m, w);
-  FLY_BLOCK_SYNC();
+  FLY_STAGE_SYNC(5);
   fly_sensors_acc(m, w);
 }
 
@@ -211,7 +214,7 @@ FLY_FN void fly_forward_acc(const DModel<T>& m, const Ws<T>& w) {
 template <class T>
 FLY_FN void fly_integrate(const DModel<T>& m, const Ws<T>& w) {
   const T dt = m.timestep;
-  FLY_BLOCK_SYNC();
+  FLY_STAGE_SYNC(6);
   /* sMa = (M + dt B)^-1 (qfrc_smooth + qfrc_constraint), solved together with qacc in fly_fwd_constraint */
   FLY_FOR(i, m.na) w.act[i] += dt * w.act_dot[i];
   FLY_FOR(d, m.nv) { w.qvel[d] += dt * w.sMa[d]; w.warm[d] = w.qacc[d]; }

@@ -18,19 +18,19 @@
   X(qpos, m.nq, 2) X(qvel, m.nv, 2) X(act, m.na, 2) X(ctrl, m.nu, 2)             \
   X(warm, m.nv, 2) X(qacc, m.nv, 2)                                                            \
   X(xpos, 3 * m.nbody, 3) X(xquat, 4 * m.nbody, 3) X(xmat, 9 * m.nbody, 3)              \
-  X(xipos, 3 * m.nbody, 4) X(ximat, 9 * m.nbody, 0)                                            \
+  X(xipos, 3 * m.nbody, 4)                                            \
   X(xanchor, 3 * m.njnt, 0) X(xaxis, 3 * m.njnt, 0)                                            \
   X(geom_xpos, 3 * m.ngeom, 3) X(site_xpos, 3 * m.nsite, 0) X(site_xmat, 9 * m.nsite, 0)\
-  X(scom, 3 * m.nbody, 3) X(cinert, 10 * m.nbody, 4) X(crb, 10 * m.nbody, 0)            \
+  X(scom, 3 * m.nbody, 3) X(cinert, 10 * m.nbody, 4) X(crb, 0, 0)            \
   X(cdof, 6 * m.nv, 3) X(cdof_dot, 6 * m.nv, 4) X(cvel, 6 * m.nbody, 4)                 \
-  X(qM, m.nM + 1, 3) X(qLD, m.nM + 1, 1) X(qH, m.nM + 1, 1)                    \
+  X(qLD, m.nM + 1, 1) X(qH, m.nM + 1, 1)                    \
   X(qDinv, m.nv, 1) X(qHinv, m.nv, 1)                                         \
   X(act_length, m.nu, 0) X(act_force, m.nu, 0) X(act_dot, m.na, 0)                      \
   X(qfrc_bias, m.nv, 0) X(qfrc_passive, m.nv, 0) X(qfrc_actuator, m.nv, 0)              \
   X(qfrc_smooth, m.nv, 2) X(qacc_smooth, m.nv, 1) X(qfrc_constraint, m.nv, 2)           \
   X(sMa, m.nv, 1) X(sgrad, m.nv, 2) X(ssearch, m.nv, 2)          \
   X(stmp, m.nv, 1)                                                                                    \
-  X(bodyf, 6 * m.nbody, 0) X(boxf, 6 * (m.nfluidbox + m.nfluidgeom), 0)                        \
+  X(bodyf, 0, 0) X(boxf, 6 * (m.nfluidbox + m.nfluidgeom), 0)                        \
   X(cacc, 6 * m.nbody, 0) X(cfrc_int, 6 * m.nbody, 0) X(cfrc_ext, 6 * m.nbody, 0)       \
   X(sensordata, m.nsensordata, 0) X(sens_sum, m.nsensordata, 0)                                \
   X(con_dist, FLY_MAXCON, 0) X(con_incl, FLY_MAXCON, 0) X(con_mu, FLY_MAXCON, 0)        \
@@ -69,6 +69,13 @@
 /* indices into counts[] */
 enum { FLY_C_NCON = 0, FLY_C_NEFC, FLY_C_NLIMIT, FLY_C_NGRP, FLY_C_NCAND, FLY_C_NITER, FLY_C_OVERFLOW, FLY_C_NCROSS,
        FLY_C_NFR, FLY_C_NCROSSROW };
+
+/* Arrays that only live inside one stage share storage with arrays of another stage (the bulk footprint of all
+ * resident warps has to fit in L2):  crb (CRB pass of step1, 10 per body) lies over cacc + cfrc_int (6 + 6 per body),
+ * bodyf (fly_passive) over cfrc_ext; those three are rebuilt by every RNE pass that uses them. */
+#define FLY_WS_ALIASES(w) \
+  (w).crb = (w).cacc;     \
+  (w).bodyf = (w).cfrc_ext;
 
 template <class T>
 struct Ws {
@@ -118,6 +125,7 @@ FLY_HD void ws_bind(const DModel<T>& m, Ws<T>* w, char* fast, char* bulk, size_t
   FLY_WS_U16(X)
 #undef X
 #undef PLACE
+  if (w) { FLY_WS_ALIASES(*w) }
   if (fast_bytes) *fast_bytes = off[1];
   if (bulk_bytes) *bulk_bytes = off[0];
 }
@@ -174,6 +182,7 @@ FLY_INL void ws_attach(Ws<T>& w, const WsOff& o, char* fast, char* bulk) {
 #define X(n, cnt, tier) w.n = (unsigned short*)((((tier) > 0 && (tier) <= LEVEL) ? fast : bulk) + o.n);
   FLY_WS_U16(X)
 #undef X
+  FLY_WS_ALIASES(w)
 }
 #endif
 #endif

@@ -81,7 +81,11 @@ __global__ void __launch_bounds__(WARPS * 32, 1) fly_step_kernel(const __grid_co
 }
 
 /* compiled (warps per block, shared-memory level) combinations */
-#define FLY_KERNEL_CONFIGS(X) X(16, 1) X(12, 1) X(10, 2) X(8, 2) X(6, 3)
+#ifdef FLY_SINGLE_CONFIG  /* kernel experiments: compile the default pair only */
+#define FLY_KERNEL_CONFIGS(X) X(16, 1)
+#else
+#define FLY_KERNEL_CONFIGS(X) X(16, 1) X(14, 1) X(12, 1) X(8, 2) X(6, 3)
+#endif
 typedef void (*FlyKernel)(const DModel<float>, const KArgs, const WsOff);
 static FlyKernel pick_kernel(int warps, int level) {
 #define X(W, L) if (warps == W && level == L) return fly_step_kernel<W, L>;

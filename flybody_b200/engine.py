@@ -12,7 +12,7 @@ import numpy as np
 from .model_pack import FlybModel, pack_model
 
 _DIR = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_DIR, "libflyb.so")
+LIB_PATH = os.environ.get("FLYB_LIB_PATH", os.path.join(_DIR, "libflyb.so"))  # the override is for kernel experiments (tools/)
 CSRC = os.path.join(_DIR, "csrc")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "--expt-extended-lambda",
               "-Xcompiler", "-fPIC", "-shared"]

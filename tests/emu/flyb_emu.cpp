@@ -110,7 +110,6 @@ struct Emu : EmuBase {
     else if (s == "com_pos") fly_com_pos(m, w);
     else if (s == "crb") fly_crb(m, w);
     else if (s == "factor") {
-      for (int e = 0; e < m.nM; e++) { w.qLD[e] = w.qM[e]; w.qH[e] = w.qM[e] + (e == m.madr[m.mrow[e]] ? m.timestep * m.dof_damping[m.mrow[e]] : T(0)); }
       T* LD[2] = {w.qLD, w.qH}; T* iv[2] = {w.qDinv, w.qHinv};
       fly_factor<T, 2>(m, LD, iv);
     }

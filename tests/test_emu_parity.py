@@ -63,8 +63,10 @@ def test_double_emulation_matches_oracle_stage_by_stage(models, task):
             a, b = e.get(nm), o.d(nm)
             n = min(len(a), len(b))
             assert _rel(a[:n], b[:n]) < 1e-11, (task, trial, nm)
-        assert _rel(e.dense_m("qM"), np.tril(o.d("qM").reshape(nv, nv))) < 1e-13
         assert _rel(e.dense_m("qLD"), np.tril(o.d("qLD").reshape(nv, nv))) < 1e-11
+        e.call("crb")  # fly_crb leaves M in qLD, which is then factorised in place
+        assert _rel(e.dense_m("qLD"), np.tril(o.d("qM").reshape(nv, nv))) < 1e-13
+        e.forward()
         # contact selection: same pairs, same order (bit-exact integer work)
         oc = o.contacts()
         assert e.geti("counts")[0] == len(oc)

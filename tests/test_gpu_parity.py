@@ -134,7 +134,7 @@ def test_results_do_not_depend_on_launch_configuration_or_batch_size(models, wal
     rng = np.random.RandomState(2)
     acts = rng.uniform(M["action_min"], M["action_max"], (3, 300, 59)).astype(np.float32)
     outs = []
-    for (N, lvl, warps) in ((300, 2, 8), (300, 1, 16), (300, 3, 6), (37, 2, 10)):
+    for (N, lvl, warps) in ((300, 2, 8), (300, 1, 16), (300, 3, 6), (37, 1, 14)):
         eng = _engine(M, N)
         eng.configure(lvl, warps)
         eng.load_clips(*walk_clip)
