@@ -237,29 +237,62 @@ FLY_INL void fly_row_axpy(T* const* LD, int ai, int as, const T* t, int n) {
  * FLY_MAXTRUNK dofs) is eliminated with one lane per entry. */
 template <class T, int NS>
 FLY_FN void fly_factor(const DModel<T>& m, T* const* LD, T* const* invD) {
-  FLY_FOR(l, 32) {
-    for (int q = 0; q < m.brow_len; q++) {
-      const int word = FLY_LDG(m.brow_b + q * 32 + l);
+  for (int st = 0; st < m.gsteps; st++) {
+    FLY_FOR(l, 32) {
+      const int word = FLY_LDG(m.gstep_b + st * 32 + l);
       if (word >= 0) {
-        const int k = word & 255, dk = (word >> 8) & 31, ak = word >> 13, hk = FLY_LDG(m.hdepth + k);
+        const int k = word & 255, j = (word >> 8) & 31, g = (word >> 13) & 31, ak = word >> 18;
+        const int hk = FLY_LDG(m.hdepth + k), dk = FLY_LDG(m.dof_din + k);
         T inv[NS];
 #pragma unroll
-        for (int s = 0; s < NS; s++) { inv[s] = T(1) / LD[s][ak]; invD[s][k] = inv[s]; }
+        for (int s = 0; s < NS; s++) inv[s] = T(1) / LD[s][ak];
+        if (j == 0) {
+#pragma unroll
+          for (int s = 0; s < NS; s++) invD[s][k] = inv[s];
+        }
+        /* row k (final: all its descendants are done) updates the rows of its in-branch ancestors; this lane takes
+           the entries mm = j, j + g, ... of each of them */
         int ai_next = FLY_LDG(m.mdiag + ak + 1);
         for (int r = 1; r <= dk; r++) {
-          const int ai = ai_next;
+          const int ai = ai_next, n = hk - r + 1;
           ai_next = FLY_LDG(m.mdiag + ak + r + 1);
           T t[NS];
 #pragma unroll
           for (int s = 0; s < NS; s++) t[s] = LD[s][ak + r] * inv[s];
-          fly_row_axpy<T, NS>(LD, ai, ak + r, t, hk - r + 1);
+          for (int m0 = j; m0 < n; m0 += 4 * g) {
+            T sv[NS][4], dv[NS][4];
 #pragma unroll
-          for (int s = 0; s < NS; s++) LD[s][ak + r] = t[s];
+            for (int s = 0; s < NS; s++)
+#pragma unroll
+              for (int e = 0; e < 4; e++) {
+                const int mm = m0 + e * g;
+                sv[s][e] = mm < n ? LD[s][ak + r + mm] : T(0);
+                dv[s][e] = mm < n ? LD[s][ai + mm] : T(0);
+              }
+#pragma unroll
+            for (int s = 0; s < NS; s++)
+#pragma unroll
+              for (int e = 0; e < 4; e++) {
+                const int mm = m0 + e * g;
+                if (mm < n) LD[s][ai + mm] = dv[s][e] - t[s] * sv[s][e];
+              }
+          }
         }
       }
     }
+    FLY_SYNC();
+    FLY_FOR(l, 32) {  /* normalise row k: U(k, ancestor) -> L(k, ancestor), in-branch part */
+      const int word = FLY_LDG(m.gstep_b + st * 32 + l);
+      if (word >= 0) {
+        const int k = word & 255, j = (word >> 8) & 31, g = (word >> 13) & 31, ak = word >> 18, dk = FLY_LDG(m.dof_din + k);
+        for (int r = 1 + j; r <= dk; r += g) {
+#pragma unroll
+          for (int s = 0; s < NS; s++) LD[s][ak + r] *= invD[s][k];
+        }
+      }
+    }
+    FLY_SYNC();
   }
-  FLY_SYNC();
   const int nt = m.ntrunk, nb = m.nv - nt;
   if (nt == 0) return;
   FLY_FOR(p, nt * (nt + 1) / 2) {
@@ -315,34 +348,24 @@ FLY_FN void fly_factor(const DModel<T>& m, T* const* LD, T* const* invD) {
 /* x[s] <- (L^T D L)[s]^-1 x[s] with the same ownership: branch rows by one lane (backward: scatter of the finished
  * x[c] to its in-branch ancestors; forward: gather over them), the trunk chain in registers in between. */
 template <class T, int NS>
-FLY_FN void fly_solve(const DModel<T>& m, const T* const* LD, const T* const* invD, T* const* x) {
-  FLY_FOR(l, 32) {
-    for (int q = 0; q < m.brow_len; q++) {
-      const int word = FLY_LDG(m.brow_b + q * 32 + l);
+FLY_FN void fly_solve(const DModel<T>& m, const Ws<T>& w, const T* const* LD, const T* const* invD, T* const* x) {
+  for (int st = 0; st < m.gsteps; st++) {
+    FLY_FOR(l, 32) {
+      const int word = FLY_LDG(m.gstep_b + st * 32 + l);
       if (word >= 0) {
-        const int c = word & 255, dk = (word >> 8) & 31, a = word >> 13;
+        const int c = word & 255, j = (word >> 8) & 31, g = (word >> 13) & 31, a = word >> 18, dk = FLY_LDG(m.dof_din + c);
         T xc[NS];
 #pragma unroll
         for (int s = 0; s < NS; s++) xc[s] = x[s][c];
-        for (int k = 1; k <= dk; k += 4) {
-          const int n = dk - k + 1;
-          int j[4];
-          T lv[NS][4], v[NS][4];
+        for (int k = 1 + j; k <= dk; k += g) {
+          const int jx = FLY_LDG(m.mcol + a + k);
 #pragma unroll
-          for (int e = 0; e < 4; e++) j[e] = FLY_LDG(m.mcol + a + k + e);
-#pragma unroll
-          for (int s = 0; s < NS; s++)
-#pragma unroll
-            for (int e = 0; e < 4; e++) { lv[s][e] = e < n ? LD[s][a + k + e] : T(0); v[s][e] = e < n ? x[s][j[e]] : T(0); }
-#pragma unroll
-          for (int s = 0; s < NS; s++)
-#pragma unroll
-            for (int e = 0; e < 4; e++) if (e < n) x[s][j[e]] = v[s][e] - lv[s][e] * xc[s];
+          for (int s = 0; s < NS; s++) x[s][jx] -= LD[s][a + k] * xc[s];
         }
       }
     }
+    FLY_SYNC();
   }
-  FLY_SYNC();
   const int nt = m.ntrunk, nb = m.nv - nt;
   if (nt > 0) {
     T acc[NS][FLY_MAXTRUNK], y[NS][FLY_MAXTRUNK];
@@ -409,26 +432,43 @@ FLY_FN void fly_solve(const DModel<T>& m, const T* const* LD, const T* const* in
     }
     FLY_SYNC();
   }
-  FLY_FOR(l, 32) {
-    for (int q = 0; q < m.brow_len; q++) {
-      const int word = FLY_LDG(m.brow_f + q * 32 + l);
+  for (int st = 0; st < m.gsteps; st++) {
+    FLY_FOR(l, 32) {
+      const int word = FLY_LDG(m.gstep_f + st * 32 + l);
       if (word >= 0) {
-        const int i = word & 255, dk = (word >> 8) & 31, a = word >> 13;
+        const int i = word & 255, j = (word >> 8) & 31, g = (word >> 13) & 31, a = word >> 18, dk = FLY_LDG(m.dof_din + i);
         T sum[NS];
 #pragma unroll
         for (int s = 0; s < NS; s++) sum[s] = 0;
-#pragma unroll 4
-        for (int k = 1; k <= dk; k++) {
-          const int j = FLY_LDG(m.mcol + a + k);
+        for (int k = 1 + j; k <= dk; k += g) {
+          const int jx = FLY_LDG(m.mcol + a + k);
 #pragma unroll
-          for (int s = 0; s < NS; s++) sum[s] += LD[s][a + k] * x[s][j];
+          for (int s = 0; s < NS; s++) sum[s] += LD[s][a + k] * x[s][jx];
         }
+        if (g > 1) {
 #pragma unroll
-        for (int s = 0; s < NS; s++) x[s][i] = x[s][i] * invD[s][i] - sum[s];
+          for (int s = 0; s < NS; s++) w.gpart[s * 32 + l] = sum[s];
+        } else {
+#pragma unroll
+          for (int s = 0; s < NS; s++) x[s][i] = x[s][i] * invD[s][i] - sum[s];
+        }
       }
     }
+    FLY_SYNC();
+    FLY_FOR(l, 32) {
+      const int word = FLY_LDG(m.gstep_f + st * 32 + l);
+      if (word >= 0 && ((word >> 8) & 31) == 0 && ((word >> 13) & 31) > 1) {
+        const int i = word & 255, g = (word >> 13) & 31;
+#pragma unroll
+        for (int s = 0; s < NS; s++) {
+          T tot = 0;
+          for (int q = 0; q < g; q++) tot += w.gpart[s * 32 + l + q];
+          x[s][i] = x[s][i] * invD[s][i] - tot;
+        }
+      }
+    }
+    FLY_SYNC();
   }
-  FLY_SYNC();
 }
 
 /* r <- M v from the factors, M = L^T D L:  z = D (L v) by a gather along each row, then r = L^T z by a gather over the

@@ -37,7 +37,7 @@ enum { FLY_OPT_NOCONTACT = 1, FLY_OPT_NOLIMIT = 2, FLY_OPT_NOFLUID = 4, FLY_OPT_
   X(jnt_type) X(jnt_qposadr) X(jnt_dofadr) X(jnt_bodyid) X(jnt_limited)                                    \
   X(dof_bodyid) X(dof_jntid) X(dof_parentid) X(hpar) X(hdepth) X(kdepth) X(hsublast) X(madr) X(mrow) X(mcol) X(mdiag)\
   X(dlvl_adr) X(dlvl_dof) X(dlvl_nlight) X(heavy_dof) X(desc_adr) X(desc) X(tri_a) X(tri_b)                  \
-  X(brow_b) X(brow_f) X(dof_din) X(trunk_dof) X(trunk_adr) X(bt_list)                             \
+  X(gstep_b) X(gstep_f) X(dof_din) X(trunk_dof) X(trunk_adr) X(bt_list)                             \
   X(geom_type) X(geom_bodyid) X(pair_geom) X(pair_condim)                                                  \
   X(site_bodyid) X(tendon_adr) X(tendon_num) X(wrap_dofadr) X(wrap_qposadr)                                \
   X(act_trntype) X(act_trnid) X(act_actadr) X(act_ctrllimited) X(act_forcelimited)                         \
@@ -66,7 +66,7 @@ struct DModel {
   /* sizes */
   int nq, nv, nu, na, nbody, njnt, ngeom, npair, nsite, ntendon, nwrap, nsensor, nsensordata, nfluidbox, nfluidgeom;
   int nM, nlevel, ndlevel, ntri, nheavy;
-  int ntrunk, brow_len;
+  int ntrunk, gsteps;
   int opt_iterations, opt_ls_iterations, opt_noslip_iterations, flags;
   /* task */
   int task_type, n_substeps, future_steps, action_dim, obs_dim, max_episode_steps, time_limit_steps;
@@ -250,30 +250,65 @@ std::string build_dmodel(const FlybModel* m, int flags, DModel<T>* out, FlyArena
       for (int a = hpar[c]; a >= 0 && !is_trunk[a]; a = hpar[a]) cost += hdepth[a] + 1;
     Branch b; b.root = i; b.cost = cost + 1; branches.push_back(b);
   }
-  std::vector<std::vector<int> > lane_rows(32);
+  /* Lane groups.  The branches are packed into "groups" (a big branch alone, small ones chained); a group owns a set of
+     consecutive lanes and walks its dofs one per step, all groups in step.  Within a step the lanes of a group share the
+     entries of the row being eliminated / substituted.  Step word: dof | lane in group << 8 | group size << 13 |
+     madr << 18, or -1 for an idle lane. */
+  std::vector<std::vector<int> > grp_dofs;   /* dofs of each group, ascending */
+  std::vector<long> grp_cost;
   {
-    std::vector<long> load(32, 0);
     std::vector<int> order(branches.size());
     for (size_t i = 0; i < order.size(); i++) order[i] = (int)i;
     for (size_t a = 0; a < order.size(); a++) for (size_t b = a + 1; b < order.size(); b++) if (branches[order[b]].cost > branches[order[a]].cost) std::swap(order[a], order[b]);
+    size_t max_steps = 1;
+    for (size_t a = 0; a < branches.size(); a++) { size_t n = (size_t)(hsublast[branches[a].root] - branches[a].root + 1); if (n > max_steps) max_steps = n; }
     for (size_t a = 0; a < order.size(); a++) {
-      int best = 0; for (int l = 1; l < 32; l++) if (load[l] < load[best]) best = l;
-      int root = branches[order[a]].root;
-      for (int c = root; c <= hsublast[root]; c++) lane_rows[best].push_back(c);
-      load[best] += branches[order[a]].cost;
+      const Branch& br = branches[order[a]];
+      const size_t n = (size_t)(hsublast[br.root] - br.root + 1);
+      /* a branch longer than half the longest one gets its own group; smaller ones are chained onto the cheapest group
+         that stays within the longest branch's step count (everything is chained once 24 groups exist) */
+      int into = -1;
+      if (n * 2 <= max_steps || grp_dofs.size() >= 24)
+        for (size_t g = 0; g < grp_dofs.size(); g++)
+          if (grp_dofs[g].size() + n <= max_steps && (into < 0 || grp_cost[g] < grp_cost[into])) into = (int)g;
+      if (into < 0) {
+        if (grp_dofs.size() < 32) { grp_dofs.push_back(std::vector<int>()); grp_cost.push_back(0); into = (int)grp_dofs.size() - 1; }
+        else { into = 0; for (size_t g = 1; g < grp_dofs.size(); g++) if (grp_dofs[g].size() < grp_dofs[into].size()) into = (int)g; }
+      }
+      for (int c = br.root; c <= hsublast[br.root]; c++) grp_dofs[into].push_back(c);
+      grp_cost[into] += br.cost;
     }
   }
-  size_t brow_len = 0;
-  for (int l = 0; l < 32; l++) { std::sort(lane_rows[l].begin(), lane_rows[l].end()); if (lane_rows[l].size() > brow_len) brow_len = lane_rows[l].size(); }
-  std::vector<int> brow_f(brow_len * 32 + 1, -1), brow_b(brow_len * 32 + 1, -1);
-  for (int l = 0; l < 32; l++) {
-    size_t n = lane_rows[l].size();
-    for (size_t q = 0; q < n; q++) {
-      int i = lane_rows[l][q], word = i | (dof_din[i] << 8) | (madr[i] << 13);
-      brow_f[q * 32 + l] = word; brow_b[(n - 1 - q) * 32 + l] = word;
+  const int ngrp = (int)grp_dofs.size();
+  std::vector<int> grp_lanes(ngrp, 1);
+  for (int spare = 32 - ngrp; spare > 0; spare--) {  /* remaining lanes go where the per-lane work is largest */
+    int best = 0;
+    for (int g = 1; g < ngrp; g++) if (grp_cost[g] * grp_lanes[best] > grp_cost[best] * grp_lanes[g]) best = g;
+    if (grp_lanes[best] >= 8) {  /* more than 8 lanes on one row does not pay: look for another taker */
+      int alt = -1;
+      for (int g = 0; g < ngrp; g++) if (grp_lanes[g] < 8 && (alt < 0 || grp_cost[g] * grp_lanes[alt] > grp_cost[alt] * grp_lanes[g])) alt = g;
+      if (alt < 0) break;
+      best = alt;
     }
+    grp_lanes[best]++;
   }
-  d.brow_len = (int)brow_len;
+  size_t gsteps = 0;
+  for (int g = 0; g < ngrp; g++) { std::sort(grp_dofs[g].begin(), grp_dofs[g].end()); if (grp_dofs[g].size() > gsteps) gsteps = grp_dofs[g].size(); }
+  std::vector<int> gstep_f(gsteps * 32 + 1, -1), gstep_b(gsteps * 32 + 1, -1);
+  {
+    int lane0 = 0;
+    for (int g = 0; g < ngrp; g++) {
+      const size_t n = grp_dofs[g].size();
+      for (size_t q = 0; q < n; q++)
+        for (int j = 0; j < grp_lanes[g]; j++) {
+          const int i = grp_dofs[g][q], word = i | (j << 8) | (grp_lanes[g] << 13) | (madr[i] << 18);
+          gstep_f[q * 32 + lane0 + j] = word; gstep_b[(n - 1 - q) * 32 + lane0 + j] = word;
+        }
+      lane0 += grp_lanes[g];
+    }
+    if (lane0 > 32) return "internal: lane groups exceed the warp";
+  }
+  d.gsteps = (int)gsteps;
   /* non-trunk dofs: address of the LAST entry of the row (the one towards trunk dof 0) | trunk ancestors << 11 | dof << 15 */
   std::vector<int> bt_list, trunk_adr;
   for (int i = 0; i < nv; i++) if (!is_trunk[i]) bt_list.push_back((madr[i] + hdepth[i]) | ((hdepth[i] - dof_din[i]) << 11) | (i << 15));
@@ -341,7 +376,7 @@ std::string build_dmodel(const FlybModel* m, int flags, DModel<T>* out, FlyArena
   d.dof_parentid = puti(vi(m->dof_parentid, nv));
   d.hpar = puti(hpar); d.hdepth = puti(hdepth); d.kdepth = puti(kdepth); d.hsublast = puti(hsublast);
   d.heavy_dof = puti(heavy_dof);
-  d.brow_b = puti(brow_b); d.brow_f = puti(brow_f); d.dof_din = puti(dof_din); d.trunk_dof = puti(trunk);
+  d.gstep_b = puti(gstep_b); d.gstep_f = puti(gstep_f); d.dof_din = puti(dof_din); d.trunk_dof = puti(trunk);
   d.trunk_adr = puti(trunk_adr); d.bt_list = puti(bt_list);
   d.ncommon = (const unsigned char*)(uintptr_t)arena->put(ncommon.data(), ncommon.size());
   {

@@ -469,7 +469,7 @@ FLY_FN void fly_fwd_constraint(const DModel<T>& m, const Ws<T>& w) {
     const T* LD[2] = {w.qLD, w.qH};
     const T* iv[2] = {w.qDinv, w.qHinv};
     T* x[2] = {w.stmp, w.sMa};
-    fly_solve<T, 2>(m, LD, iv, x);
+    fly_solve<T, 2>(m, w, LD, iv, x);
   }
   FLY_FOR(d, m.nv) w.qacc[d] = w.qacc_smooth[d] + w.sgrad[d] + w.stmp[d];
   FLY_SYNC();

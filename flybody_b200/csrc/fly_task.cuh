@@ -202,7 +202,7 @@ FLY_FN void fly_forward_acc(const DModel<T>& m, const Ws<T>& w) {
     const T* LD[1] = {w.qLD};
     const T* iv[1] = {w.qDinv};
     T* x[1] = {w.qacc_smooth};
-    fly_solve<T, 1>(m, LD, iv, x);
+    fly_solve<T, 1>(m, w, LD, iv, x);
   }
   FLY_STAGE_SYNC(4);
   fly_fwd_constraint(m, w);

@@ -24,7 +24,7 @@
   X(scom, 3 * m.nbody, 3) X(cinert, 10 * m.nbody, 4) X(crb, 0, 0)            \
   X(cdof, 6 * m.nv, 3) X(cdof_dot, 6 * m.nv, 4) X(cvel, 6 * m.nbody, 4)                 \
   X(qLD, m.nM + 1, 1) X(qH, m.nM + 1, 1)                    \
-  X(qDinv, m.nv, 1) X(qHinv, m.nv, 1)                                         \
+  X(qDinv, m.nv, 1) X(qHinv, m.nv, 1) X(gpart, 64, 0)                                         \
   X(act_length, m.nu, 0) X(act_force, m.nu, 0) X(act_dot, m.na, 0)                      \
   X(qfrc_bias, m.nv, 0) X(qfrc_passive, m.nv, 0) X(qfrc_actuator, m.nv, 0)              \
   X(qfrc_smooth, m.nv, 2) X(qacc_smooth, m.nv, 1) X(qfrc_constraint, m.nv, 2)           \

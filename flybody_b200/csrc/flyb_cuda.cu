@@ -25,6 +25,7 @@ struct FlybEngine {
   int* d_trace_int = nullptr; float* d_trace_real = nullptr; int trace_real_stride = 0;
   char* d_bulk = nullptr; size_t bulk_stride = 0, fast_stride = 0; int bulk_slots = 0;
   int* d_counter = nullptr;
+  int *d_work = nullptr, *d_perm = nullptr; int binning = 1;   /* contact-count binning of the env -> block assignment */
   float* d_clip_rows = nullptr; int* d_clip_off = nullptr; int* d_clip_len = nullptr; int n_clips = 0;
   FlyWbpg wb = {};        /* device pointers; nfreq 0 until flyb_load_wbpg */
   void* d_wbpg = nullptr; double* d_wbpg_phase = nullptr;
@@ -55,6 +56,7 @@ struct KArgs {
   char* bulk;
   size_t bulk_stride, fast_stride;
   int* counter;
+  const int* perm;   /* nullable: position in the launch order -> env id */
   int num_envs, level;
 };
 
@@ -74,9 +76,9 @@ __global__ void __launch_bounds__(WARPS * 32, 1) fly_step_kernel(const __grid_co
     __syncthreads();
     if (threadIdx.x == 0) s_base = atomicAdd(a.counter, WARPS);
     __syncthreads();
-    const int env = s_base + warp;
+    const int pos = s_base + warp;
     if (s_base >= a.num_envs) break;
-    fly_env_run<float>(m, w, a.clips, a.wb, a.io, env < a.num_envs ? env : -1);
+    fly_env_run<float>(m, w, a.clips, a.wb, a.io, pos < a.num_envs ? (a.perm ? a.perm[pos] : pos) : -1);
   }
 }
 
@@ -94,6 +96,30 @@ static FlyKernel pick_kernel(int warps, int level) {
   return nullptr;
 }
 
+/* Launch order of the envs for the next step: counting sort by the number of constraint rows of their last solve, heaviest
+ * first.  The warps of a block walk the pipeline in step (FLY_STAGE_SYNC), so a block is as slow as its busiest env; with
+ * envs of similar contact state side by side the wait at the rendezvous after the constraint solve shrinks, and the light
+ * envs end up in the tail of the grid.  Which env a warp steps never changes that env's result. */
+#define FLY_NBINS 64
+__global__ void __launch_bounds__(1024) fly_bin_kernel(const int* __restrict__ work, int* __restrict__ perm, int n) {
+  __shared__ int cnt[FLY_NBINS], start[FLY_NBINS];
+  for (int b = threadIdx.x; b < FLY_NBINS; b += blockDim.x) cnt[b] = 0;
+  __syncthreads();
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    int k = work[i];
+    k = k < 0 ? 0 : (k >= FLY_NBINS ? FLY_NBINS - 1 : k);
+    atomicAdd(&cnt[FLY_NBINS - 1 - k], 1);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) { int s = 0; for (int b = 0; b < FLY_NBINS; b++) { start[b] = s; s += cnt[b]; } }
+  __syncthreads();
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    int k = work[i];
+    k = k < 0 ? 0 : (k >= FLY_NBINS ? FLY_NBINS - 1 : k);
+    perm[atomicAdd(&start[FLY_NBINS - 1 - k], 1)] = i;
+  }
+}
+
 static int launch(FlybEngine* h, const FlyIO<float>& io, cudaStream_t st) {
   CK(cudaSetDevice(h->device));
   size_t fb = 0, bb = 0;
@@ -102,7 +128,7 @@ static int launch(FlybEngine* h, const FlyIO<float>& io, cudaStream_t st) {
   h->fast_stride = fb;
   const int W = h->warps;
   const size_t smem = fb * W;
-  if (smem > 220 * 1024) { h->err = "shared memory request too large for this smem_level / warps_per_block"; return 1; }
+  if (smem > 227 * 1024 - 2048) { h->err = "shared memory request too large for this smem_level / warps_per_block"; return 1; }
   if (bb > h->bulk_stride) { h->err = "internal: bulk slot too small"; return 1; }
   FlyKernel kern = pick_kernel(W, h->smem_level);
   if (!kern) { h->err = "this (warps_per_block, smem_level) pair is not compiled in; see FLY_KERNEL_CONFIGS"; return 1; }
@@ -122,6 +148,13 @@ static int launch(FlybEngine* h, const FlyIO<float>& io, cudaStream_t st) {
   a.wb = h->wb;
   a.bulk = h->d_bulk; a.bulk_stride = h->bulk_stride; a.fast_stride = fb; a.counter = h->d_counter;
   a.num_envs = h->num_envs; a.level = h->smem_level;
+  a.perm = nullptr;
+  a.io.work = h->d_work;
+  if (h->binning && !io.force_reset && h->num_envs > 2 * W) {
+    fly_bin_kernel<<<1, 1024, 0, st>>>(h->d_work, h->d_perm, h->num_envs);
+    a.perm = h->d_perm;
+    h->launches++;
+  }
   CK(cudaMemsetAsync(h->d_counter, 0, sizeof(int), st));
   kern<<<grid, W * 32, smem, st>>>(h->m, a, off);
   CK(cudaGetLastError());
@@ -195,6 +228,10 @@ int flyb_create(const FlybModel* model, int num_envs, int device, uint64_t seed,
   CKC(cudaMalloc(&h->d_bulk, (size_t)h->bulk_slots * h->bulk_stride));
   CKC(cudaMemset(h->d_bulk, 0, (size_t)h->bulk_slots * h->bulk_stride));
   CKC(cudaMalloc(&h->d_counter, sizeof(int)));
+  CKC(cudaMalloc(&h->d_work, N * sizeof(int)));
+  CKC(cudaMalloc(&h->d_perm, N * sizeof(int)));
+  CKC(cudaMemset(h->d_work, 0, N * sizeof(int)));
+  { const char* e = getenv("FLYB_BINNING"); if (e) h->binning = atoi(e); }
   /* staging */
   CKC(cudaStreamCreateWithFlags(&h->host_stream, cudaStreamNonBlocking));
   CKC(cudaMallocHost(&h->h_action, N * m.action_dim * sizeof(float)));
@@ -222,7 +259,7 @@ void flyb_destroy(flyb_handle h) {
   cudaSetDevice(h->device);
   cudaDeviceSynchronize();
   cudaFree(h->d_arena); cudaFree(h->d_sreal); cudaFree(h->d_sint); cudaFree(h->d_stats); cudaFree(h->d_trace_int);
-  cudaFree(h->d_trace_real); cudaFree(h->d_bulk); cudaFree(h->d_counter); cudaFree(h->d_clip_rows);
+  cudaFree(h->d_trace_real); cudaFree(h->d_bulk); cudaFree(h->d_counter); cudaFree(h->d_work); cudaFree(h->d_perm); cudaFree(h->d_clip_rows);
   cudaFree(h->d_wbpg); cudaFree(h->d_wbpg_phase);
   cudaFree(h->d_clip_off); cudaFree(h->d_clip_len); cudaFree(h->d_action); cudaFree(h->d_obs); cudaFree(h->d_rd);
   cudaFree(h->d_st); cudaFree(h->d_mask);

@@ -118,7 +118,7 @@ struct Emu : EmuBase {
     else if (s == "step1") fly_step1(m, w, true);
     else if (s == "forward_acc") fly_forward_acc(m, w);
     else if (s == "integrate") fly_integrate(m, w);
-    else if (s == "solve_stmp") { const T* LD[1] = {w.qLD}; const T* iv[1] = {w.qDinv}; T* x[1] = {w.stmp}; fly_solve<T, 1>(m, LD, iv, x); }
+    else if (s == "solve_stmp") { const T* LD[1] = {w.qLD}; const T* iv[1] = {w.qDinv}; T* x[1] = {w.stmp}; fly_solve<T, 1>(m, w, LD, iv, x); }
     else fprintf(stderr, "emu: unknown stage %s\n", stage);
   }
   int get(const char* name, double* out, int cap) override {
