@@ -30,7 +30,7 @@ struct FlyIO {
   int force_reset;     /* 1: reset every env in mask regardless of reset_next */
   const unsigned char* reset_mask; /* nullable */
   const double* wbpg_phase;        /* nullable [N]: initial wing-beat phase to use at reset instead of the hashed draw */
-  int* work;                       /* nullable [N]: constraint rows of the env's last solve (load-balancing key) */
+  int* work;                       /* nullable [N]: cycles/64 the env spent in its constraint solves this step (load-balancing key) */
 };
 
 FLY_INL unsigned long long fly_hash(unsigned long long x) {  /* splitmix64 finaliser */
@@ -440,7 +440,7 @@ FLY_FN void fly_env_run(const DModel<T>& m, const Ws<T>& w, const FlyClips& clip
     if (io.discount) io.discount[env] = (float)discount;
     io.step_type[env] = st;
   }
-  if (io.work) FLY_LANE0 io.work[env] = w.counts[FLY_C_NEFC];
+  if (io.work) FLY_LANE0 io.work[env] = w.counts[FLY_C_WORK];
   if (io.trace_int) {
     int* ti = io.trace_int + (size_t)env * FLY_TR_INTS;
     FLY_LANE0 {

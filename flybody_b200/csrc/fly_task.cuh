@@ -205,7 +205,15 @@ FLY_FN void fly_forward_acc(const DModel<T>& m, const Ws<T>& w) {
     fly_solve<T, 1>(m, w, LD, iv, x);
   }
   FLY_STAGE_SYNC(4);
+#ifdef FLY_GPU
+  const long long t0 = clock64();
+#endif
   fly_fwd_constraint(m, w);
+#ifdef FLY_GPU
+  /* cycles this env spent in its constraint solve, summed over the control step: the load-balancing key of the next
+     step's launch order (flyb_cuda.cu: fly_bin_kernel) */
+  FLY_LANE0 w.counts[FLY_C_WORK] += (int)((clock64() - t0) >> 6);
+#endif
   FLY_STAGE_SYNC(5);
   fly_sensors_acc(m, w);
 }

@@ -68,7 +68,7 @@
 
 /* indices into counts[] */
 enum { FLY_C_NCON = 0, FLY_C_NEFC, FLY_C_NLIMIT, FLY_C_NGRP, FLY_C_NCAND, FLY_C_NITER, FLY_C_OVERFLOW, FLY_C_NCROSS,
-       FLY_C_NFR, FLY_C_NCROSSROW };
+       FLY_C_NFR, FLY_C_NCROSSROW, FLY_C_WORK };
 
 /* Arrays that only live inside one stage share storage with arrays of another stage (the bulk footprint of all
  * resident warps has to fit in L2):  crb (CRB pass of step1, 10 per body) lies over cacc + cfrc_int (6 + 6 per body),

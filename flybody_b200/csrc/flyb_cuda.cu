@@ -25,7 +25,7 @@ struct FlybEngine {
   int* d_trace_int = nullptr; float* d_trace_real = nullptr; int trace_real_stride = 0;
   char* d_bulk = nullptr; size_t bulk_stride = 0, fast_stride = 0; int bulk_slots = 0;
   int* d_counter = nullptr;
-  int *d_work = nullptr, *d_perm = nullptr; int binning = 1;   /* contact-count binning of the env -> block assignment */
+  int *d_work = nullptr, *d_perm = nullptr; int binning = 0;   /* FLYB_BINNING=1: cost-sorted env -> block assignment (measured: no gain, off) */
   float* d_clip_rows = nullptr; int* d_clip_off = nullptr; int* d_clip_len = nullptr; int n_clips = 0;
   FlyWbpg wb = {};        /* device pointers; nfreq 0 until flyb_load_wbpg */
   void* d_wbpg = nullptr; double* d_wbpg_phase = nullptr;
@@ -96,27 +96,34 @@ static FlyKernel pick_kernel(int warps, int level) {
   return nullptr;
 }
 
-/* Launch order of the envs for the next step: counting sort by the number of constraint rows of their last solve, heaviest
- * first.  The warps of a block walk the pipeline in step (FLY_STAGE_SYNC), so a block is as slow as its busiest env; with
- * envs of similar contact state side by side the wait at the rendezvous after the constraint solve shrinks, and the light
- * envs end up in the tail of the grid.  Which env a warp steps never changes that env's result. */
-#define FLY_NBINS 64
+/* Launch order of the envs for the next step: counting sort by the time their constraint solves took in the last step,
+ * slowest first.  The warps of a block walk the pipeline in step (FLY_STAGE_SYNC), so a block is as slow as its busiest
+ * env; the cost of an env persists from step to step (it follows its contact state), so with envs of similar cost side by
+ * side the wait at the rendezvous after the constraint solve shrinks, and the light envs end up in the tail of the grid.
+ * Keys are linear in cost up to 4x the mean (1024 bins), everything above shares the first bin.  Which warp steps an
+ * env never changes that env's result. */
+#define FLY_NBINS 1024
 __global__ void __launch_bounds__(1024) fly_bin_kernel(const int* __restrict__ work, int* __restrict__ perm, int n) {
   __shared__ int cnt[FLY_NBINS], start[FLY_NBINS];
-  for (int b = threadIdx.x; b < FLY_NBINS; b += blockDim.x) cnt[b] = 0;
+  __shared__ unsigned long long total;
+  if (threadIdx.x == 0) total = 0;
+  cnt[threadIdx.x] = 0;
   __syncthreads();
+  unsigned long long mine = 0;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) mine += (unsigned long long)(work[i] > 0 ? work[i] : 0);
+  atomicAdd(&total, mine);
+  __syncthreads();
+  const unsigned long long mean = total / (unsigned long long)n + 1;
   for (int i = threadIdx.x; i < n; i += blockDim.x) {
-    int k = work[i];
-    k = k < 0 ? 0 : (k >= FLY_NBINS ? FLY_NBINS - 1 : k);
-    atomicAdd(&cnt[FLY_NBINS - 1 - k], 1);
+    const unsigned long long k = (unsigned long long)(work[i] > 0 ? work[i] : 0) * 256ull / mean;
+    atomicAdd(&cnt[FLY_NBINS - 1 - (int)(k < FLY_NBINS ? k : FLY_NBINS - 1)], 1);
   }
   __syncthreads();
   if (threadIdx.x == 0) { int s = 0; for (int b = 0; b < FLY_NBINS; b++) { start[b] = s; s += cnt[b]; } }
   __syncthreads();
   for (int i = threadIdx.x; i < n; i += blockDim.x) {
-    int k = work[i];
-    k = k < 0 ? 0 : (k >= FLY_NBINS ? FLY_NBINS - 1 : k);
-    perm[atomicAdd(&start[FLY_NBINS - 1 - k], 1)] = i;
+    const unsigned long long k = (unsigned long long)(work[i] > 0 ? work[i] : 0) * 256ull / mean;
+    perm[atomicAdd(&start[FLY_NBINS - 1 - (int)(k < FLY_NBINS ? k : FLY_NBINS - 1)], 1)] = i;
   }
 }
 
