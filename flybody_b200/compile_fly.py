@@ -222,7 +222,7 @@ class TaskSpec:
         else:  # fly_envs.py:104-115,144-150, tasks/base.py:343-352
             self.walker = Walker(xml_path, use_legs=True, use_wings=False, joint_filter=0.01, adhesion_filter=0.007)
             self.physics_dt, self.control_dt = 2e-4, 2e-3  # tasks/constants.py:16-17
-            self.time_limit = 2.0 if task == "walk_on_ball" else 10.0
+            self.time_limit = {"walk_on_ball": 2.0, "template": 1.0}.get(task, 10.0)  # fly_envs.py:103,143,213
             self.future_steps = 64 if task == "walk_imitation" else 0
         self.n_substeps = int(round(self.control_dt / self.physics_dt))
         w = self.walker
@@ -849,7 +849,7 @@ def constants(M: dict, ts: TaskSpec) -> dict:
 
 
 # ----------------------------------------------------------------------------
-_TASK_TYPE = {"walk_on_ball": 0, "walk_imitation": 1, "flight_imitation": 2}
+_TASK_TYPE = {"walk_on_ball": 0, "walk_imitation": 1, "flight_imitation": 2, "template": 3}
 _APPENDAGES = ("claw_T1_left", "claw_T1_right", "claw_T2_left", "claw_T2_right", "claw_T3_left",
                "claw_T3_right", "head")  # fruitfly.py:422-446
 _LEG_HINGES_PER_LEG = 11

@@ -377,7 +377,7 @@ FLY_FN void fly_env_run(const DModel<T>& m, const Ws<T>& w, const FlyClips& clip
     qn = warp_sum(qn);
     int reached_end = 0;
     fatal = !(sqrt(qn) <= m.terminal_qacc);  /* NaN counts as divergence */
-    if (m.task_type != FLYB_TASK_FLIGHT_IMITATION) {
+    if (m.task_type == FLYB_TASK_WALK_IMITATION || m.task_type == FLYB_TASK_WALK_ON_BALL) {  /* not flight, not template_task.py:78-83 */
       T lv[6];
       const int site = m.thorax_site;
       fly_local_velocity(m, w, lv, m.site_bodyid[site], w.site_xpos + 3 * site, w.site_xmat + 9 * site);

@@ -212,6 +212,28 @@ def flight_imitation(wpg_pattern_path=None, ref_path=None, random_state=None, te
                          wbpg=_wbpg.build_tables(base), **kw)
 
 
+def template_task(random_state=None, joint_filter: float = 0.01, adhesion_filter: float = 0.007, time_limit: float = 1.0,
+                  mjcb_control=None, observables_options=None, action_corruptor=None, num_envs: int = 1, device=0,
+                  seed: int | None = None, **kw) -> BatchedFlyEnv:
+    """The empty no-op walking task (`vnl_ray/fly_envs.py:209-259`, `tasks/template_task.py`): fly on the floor, reward 1,
+    termination on |qacc| only.  The per-env Python hooks of the reference (`mjcb_control`, `action_corruptor`,
+    `observables_options`) have no batched equivalent and must be None; the actuator filters are compiled into the model."""
+    if mjcb_control is not None or action_corruptor is not None or observables_options is not None:
+        raise NotImplementedError("template_task: Python callbacks / observable options are not supported by the batched engine")
+    if (joint_filter, adhesion_filter) != (0.01, 0.007):
+        raise NotImplementedError("template_task: the actuator filter time constants are fixed at model compile time (0.01, 0.007)")
+    M = load_model(asset_path("template"))
+    if float(time_limit) != 1.0:  # same accumulation as compile_fly.task_tables: first control step with time >= time_limit
+        dt, t, k = float(M["opt_timestep"]), 0.0, 0
+        while t < time_limit:
+            for _ in range(int(M["n_substeps"])):
+                t += dt
+            k += 1
+        M["time_limit_steps"] = k
+        M["max_episode_steps"] = int(round(time_limit / float(M["control_dt"]))) + 1
+    return BatchedFlyEnv("template", M, num_envs, device, _seed(random_state, seed), **kw)
+
+
 def _seed(random_state, seed):
     if seed is not None:
         return int(seed)

@@ -1704,7 +1704,7 @@ int flyo_env_step(FlyoEnv* e, const double* action_in, double* obs, double* rewa
   double qn = 0;
   for (int d = 0; d < m->nv; d++) qn += e->qacc[d] * e->qacc[d];
   int fatal = sqrt(qn) > m->terminal_qacc, reached_end = 0;
-  if (m->task_type != FLYB_TASK_FLIGHT_IMITATION) {
+  if (m->task_type == FLYB_TASK_WALK_IMITATION || m->task_type == FLYB_TASK_WALK_ON_BALL) {  /* not flight, not template_task.py:78-83 */
     double lv[6];
     int site = m->thorax_site;
     local_velocity(e, lv, m->site_bodyid[site], e->site_xpos + 3 * site, e->site_xmat + 9 * site);

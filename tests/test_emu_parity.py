@@ -140,10 +140,12 @@ def test_env_level_rollout_matches_oracle(models, walk_clip):
         assert st == st2 == 0 and r2 == 0 and g2 == 1 and _rel(eobs, oobs) < tol_obs
 
 
-def test_walk_on_ball_rollout_matches_oracle(models):
+@pytest.mark.parametrize("task", ["walk_on_ball", "template"])
+def test_clipless_task_rollout_matches_oracle(models, task):
+    """walk_on_ball (tolerance reward on the ball velocity) and the no-op template task (reward 1, qacc termination only)."""
     from oracle.oracle import OracleEnv
     from tests.emu.emu import EmuEnv
-    M = models["walk_on_ball"]
+    M = models[task]
     o, e = OracleEnv(M), EmuEnv(M, double=False)
     o.env_reset(); e.env_reset()
     rng = np.random.RandomState(0)

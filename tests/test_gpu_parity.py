@@ -38,7 +38,7 @@ def test_library_is_loaded_and_launches():
         assert "libflyb.so" in f.read()
 
 
-@pytest.mark.parametrize("task", ["walk_imitation", "walk_on_ball"])
+@pytest.mark.parametrize("task", ["walk_imitation", "walk_on_ball", "template"])
 def test_reset_and_steps_match_oracle(models, walk_clip, task):
     M = models[task]
     rows = walk_clip[0] if task == "walk_imitation" else None

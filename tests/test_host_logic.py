@@ -13,6 +13,8 @@ def test_observation_layout_matches_survey(models):
     assert list(lay) == sorted(lay)  # dm_control orders observation keys
     assert sum(int(np.prod(s)) for _, s in observation_layout(models["walk_on_ball"]).values()) == 289
     assert "walker/ball_qvel" in observation_layout(models["walk_on_ball"])
+    lay = observation_layout(models["template"])  # Walking base observables only (tasks/base.py:359-364)
+    assert sum(int(np.prod(s)) for _, s in lay.values()) == 286 and "walker/ref_displacement" not in lay and "walker/touch" in lay
     offs = sorted((o, int(np.prod(s))) for o, s in lay.values())
     assert all(offs[i][0] + offs[i][1] == offs[i + 1][0] for i in range(len(offs) - 1))  # blocks tile the row
 
