@@ -71,3 +71,30 @@ def test_sharding_and_stats_allreduce_world2():
     assert (res[0][1], res[0][2]) == (0, 5) and (res[1][1], res[1][2]) == (5, 10)
     for r in res:
         assert r[3] == dict(return_sum=3.0, length_sum=30.0, fatal=2.0, episodes=4.0)
+
+
+def test_hdf5_converter_logic_on_a_dataset_shaped_mapping(models, tmp_path):
+    """tools/convert_hdf5_clips.py reads the flybody dataset layout (trajectory_loaders.py:10-223); h5py is absent here, so
+    the same code is driven with nested dicts of the same shape."""
+    import importlib.util, os
+    from flybody_b200 import clips as C
+    spec = importlib.util.spec_from_file_location("conv", os.path.join(os.path.dirname(__file__), "..", "tools", "convert_hdf5_clips.py"))
+    conv = importlib.util.module_from_spec(spec); spec.loader.exec_module(conv)
+    M = models["walk_imitation"]
+    nj, ns = int(M["n_mocap_joints"]), int(M["n_mocap_sites"])
+    rng = np.random.RandomState(0)
+    def walk(T):
+        return dict(root_qpos=rng.normal(size=(T, 7)) + [3, -2, 0.1, 0, 0, 0, 0], qpos=rng.normal(size=(T, nj)),
+                    root_qvel=rng.normal(size=(T, 6)), qvel=rng.normal(size=(T, nj)),
+                    root2site=rng.normal(size=(T, ns, 3)), joint_quat=rng.normal(size=(T, nj, 4)))
+    f = {"trajectories": {"00001": walk(9), "00000": walk(7)}, "id2name": {"joints": [b"j"] * nj}}
+    cl = conv.walking_clips(f, M)
+    assert [c["qpos"].shape[0] for c in cl] == [7, 9]                       # numeric order of the zero-padded keys
+    assert np.all(cl[0]["qpos"][0, :2] == 0) and cl[0]["qpos"].shape[1] == 7 + nj
+    rows, off, ln = C.pack_clips(M, cl)
+    assert rows.shape == (16, C.clip_row_width(M)) and off.tolist() == [0, 7] and ln.tolist() == [7, 9]
+    com = np.concatenate([rng.normal(size=(5, 3)) + [1, 2, 3], np.tile([1.0, 0, 0, 0], (5, 1))], axis=1)
+    fl = conv.flight_clips({"trajectories": {"0": dict(com_qpos=com, com_qvel=rng.normal(size=(5, 6)))}})
+    # identity orientation: root = com - offset, after the xy origin moved to the first frame
+    assert np.allclose(fl[0]["qpos"][0, :3], [0, 0, com[0, 2]] - C._COM_OFFSET)
+    assert np.allclose(C.root2com(fl[0]["qpos"][2]), com[2, :3] - [com[0, 0], com[0, 1], 0])
