@@ -246,3 +246,41 @@ def test_fly_envs_flight_imitation_api():
         ts = env.step(torch.zeros((64, 12), device=env.device))
         total += ts.reward
     assert torch.isfinite(total).all() and (total > 0).all()
+
+
+def test_sharded_engines_reproduce_the_unsharded_batch(models):
+    """Multi-GPU layout: rank r owns global envs [r N, (r+1) N).  Clip choice and the initial wing-beat
+    phase are counter-based hashes of (seed, global env id, episode), so two half-size engines with env_offset 0 / N/2
+    must produce exactly the bits of one full-size engine - for walking (random clip per env) and for flight (random clip
+    and random phase per env)."""
+    from flybody_b200 import clips as C, wbpg as W
+    from flybody_b200.engine import Engine
+    for task in ("walk_imitation", "flight_imitation"):
+        M = models[task]
+        if task == "walk_imitation":
+            tab = C.synthetic_table(M, 8, 200, 0)
+        else:
+            tab = C.synthetic_flight_table(M, 8, 300, 0)
+        N = 96
+        rng = np.random.RandomState(4)
+        acts = (0.5 * rng.uniform(M["action_min"], M["action_max"], (3, N, int(M["action_dim"])))).astype(np.float32)
+        def run(n, offset):
+            eng = Engine(M, n, 0, seed=11, env_offset=offset)
+            eng.load_clips(*tab)
+            if task == "flight_imitation":
+                eng.load_wbpg(W.build_tables(W.synthetic_base_pattern()))
+            st, obs = eng.reset_host()
+            outs = [obs.copy()]
+            for k in range(3):
+                st, r, g, obs = eng.step_host(acts[k, offset:offset + n])
+                outs.append(np.concatenate([obs, r[:, None], g[:, None]], axis=1))
+            ints = eng.get_state()["ints"].copy()
+            eng.close()
+            return outs, ints
+        full, fi = run(N, 0)
+        a, ai = run(N // 2, 0)
+        b, bi = run(N // 2, N // 2)
+        for k in range(4):
+            assert (np.concatenate([a[k], b[k]]) == full[k]).all(), (task, k)
+        assert (np.concatenate([ai, bi])[:, 3] == fi[:, 3]).all()          # FLY_SI_CLIP: same clip per global env
+        assert len(set(fi[:, 3].tolist())) > 1                              # and not all the same clip
