@@ -95,3 +95,58 @@ def test_friction_cone_is_respected(models):
             assert np.hypot(fr[a + 1], fr[a + 2]) <= c["friction"][0] * fr[a] * (1 + 1e-6) + 1e-9
             n += 1
     assert n > 0
+
+
+def test_momentum_drift_of_internal_forces_vanishes_linearly_with_the_timestep(models):
+    """Free flight with actuators, joint limits, springs and dampers on (all internal forces; contacts and fluid off):
+    gravity changes the linear momentum by exactly m g t and nothing changes the angular momentum about the CoM.  The
+    semi-implicit Euler step keeps that only to first order, so the drift over a fixed time must halve when the
+    timestep halves (a spurious external force - an inconsistent mass matrix, bias force or actuator moment - would give
+    a drift that does not vanish).  Checks CRB / RNE / actuation / limits / implicit damping against one another."""
+    from oracle.oracle import OracleEnv
+    M = models["flight_imitation"]
+    nb, root = int(M["nbody"]), int(M["root_body"])
+    mass, inertia = np.asarray(M["body_mass"]), np.asarray(M["body_inertia"]).reshape(nb, 3)
+    iquat = np.asarray(M["body_iquat"]).reshape(nb, 4)
+    idx = np.where(np.asarray(M["body_rootid"]) == root)[0]      # the fly without the ghost
+    mt = mass[idx].sum()
+    nvw = int(M["ghost_dofadr"])
+
+    def q2m(q):
+        w, x, y, z = q
+        return np.array([[w*w+x*x-y*y-z*z, 2*(x*y-w*z), 2*(x*z+w*y)], [2*(x*y+w*z), w*w-x*x+y*y-z*z, 2*(y*z-w*x)],
+                         [2*(x*z-w*y), 2*(y*z+w*x), w*w-x*x-y*y+z*z]])
+
+    def qmul(a, b):
+        return np.array([a[0]*b[0]-a[1]*b[1]-a[2]*b[2]-a[3]*b[3], a[0]*b[1]+a[1]*b[0]+a[2]*b[3]-a[3]*b[2],
+                         a[0]*b[2]-a[1]*b[3]+a[2]*b[0]+a[3]*b[1], a[0]*b[3]+a[1]*b[2]-a[2]*b[1]+a[3]*b[0]])
+
+    def momentum(o):
+        xipos, cvel, xq = o.d("xipos").reshape(nb, 3), o.d("cvel").reshape(nb, 6), o.d("xquat").reshape(nb, 4)
+        sc = o.d("subtree_com").reshape(nb, 3)[root]
+        c = (xipos[idx] * mass[idx, None]).sum(0) / mt
+        v = {b: cvel[b, 3:] + np.cross(cvel[b, :3], xipos[b] - sc) for b in idx}   # cvel is taken at the root's subtree CoM
+        P = sum(mass[b] * v[b] for b in idx)
+        L = np.zeros(3)
+        for b in idx:
+            R = q2m(qmul(xq[b], iquat[b]))
+            L += mass[b] * np.cross(xipos[b] - c, v[b] - P / mt) + R @ np.diag(inertia[b]) @ R.T @ cvel[b, :3]
+        return P, L
+
+    drift = []
+    for sub in (1, 2, 4):
+        o = OracleEnv(M)
+        o.option("disable_contact", 1); o.option("disable_fluid", 1)
+        o.option("timestep", 5e-5 / sub)
+        rng = np.random.RandomState(0)
+        o.d("qpos")[:] = M["qpos_reset"]; o.d("qpos")[2] += 1.0
+        qv = o.d("qvel"); qv[:] = 0; qv[6:nvw] = rng.normal(scale=20, size=nvw - 6)
+        o.d("ctrl")[:] = rng.uniform(-1, 1, int(M["nu"]))
+        o.forward()
+        P0, L0 = momentum(o)
+        o.step(20 * sub)
+        P1, L1 = momentum(o)
+        dP = P1 - P0 + np.array([0, 0, 981.0 * mt * 20 * 5e-5])
+        drift.append((np.linalg.norm(dP), np.linalg.norm(L1 - L0)))
+    for k in range(2):
+        assert 1.9 < drift[k][0] / drift[k + 1][0] < 2.1 and 1.9 < drift[k][1] / drift[k + 1][1] < 2.1, drift
