@@ -27,7 +27,12 @@
 #define FLY_SYNC() __syncwarp()
 /* block-wide rendezvous of the warps of a block (each steps its own env): keeps them in the same stage so that
  * instruction fetches and model-table lines are shared in the SM's caches.  Every warp must pass the same number. */
+#ifndef FLY_SYNC_GROUP
 #define FLY_BLOCK_SYNC() __syncthreads()
+#else  /* lockstep groups of FLY_SYNC_GROUP warps (named barriers 1..): smaller groups wait less for their slowest env */
+#define FLY_BLOCK_SYNC() \
+  asm volatile("bar.sync %0, %1;" ::"r"(1 + (int)(threadIdx.x >> 5) / FLY_SYNC_GROUP), "n"(FLY_SYNC_GROUP * 32) : "memory")
+#endif
 #define FLY_LANE0 if (FLY_LANE() == 0)
 #define FLY_LDG(p) __ldg(p)
 template <class T> FLY_INL T warp_sum(T v) {

@@ -65,19 +65,27 @@ __global__ void __launch_bounds__(WARPS * 32, 1) fly_step_kernel(const __grid_co
                                                                 const __grid_constant__ KArgs a,
                                                                 const __grid_constant__ WsOff off) {
   extern __shared__ __align__(16) char smem[];
-  __shared__ int s_base;
+#ifdef FLY_SYNC_GROUP
+  constexpr int GW = FLY_SYNC_GROUP;   /* warps of one lockstep group: fetches its own envs, runs on its own barrier */
+#else
+  constexpr int GW = WARPS;
+#endif
+  static_assert(WARPS % GW == 0, "lockstep group must divide the block");
+  __shared__ int s_base[WARPS / GW];
   const int warp = threadIdx.x >> 5;
   const int slot = blockIdx.x * WARPS + warp;
+  const int grp = warp / GW, gwarp = warp % GW;
   /* every thread keeps its warp's array pointers as (arena base + constant offset): registers / immediates, with the
      address space of each array known to the compiler */
   Ws<float> w;
   ws_attach<float, LEVEL>(w, off, smem + warp * a.fast_stride, a.bulk + (size_t)slot * a.bulk_stride);
-  for (;;) {  /* the block takes WARPS consecutive envs at a time and its warps step them stage by stage together */
-    __syncthreads();
-    if (threadIdx.x == 0) s_base = atomicAdd(a.counter, WARPS);
-    __syncthreads();
-    const int pos = s_base + warp;
-    if (s_base >= a.num_envs) break;
+  for (;;) {  /* the group takes GW consecutive envs at a time and its warps step them stage by stage together */
+    FLY_BLOCK_SYNC();
+    if (gwarp == 0 && (threadIdx.x & 31) == 0) s_base[grp] = atomicAdd(a.counter, GW);
+    FLY_BLOCK_SYNC();
+    const int base = s_base[grp];
+    const int pos = base + gwarp;
+    if (base >= a.num_envs) break;
     fly_env_run<float>(m, w, a.clips, a.wb, a.io, pos < a.num_envs ? (a.perm ? a.perm[pos] : pos) : -1);
   }
 }
