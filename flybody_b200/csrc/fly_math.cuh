@@ -22,6 +22,8 @@
 #define FLY_GPU 1
 #define FLY_FN __device__ __forceinline__
 #define FLY_INL __device__ __forceinline__
+#define FLY_MEM __device__ __forceinline__   /* member functions */
+#define FLY_NOINL __device__ __noinline__     /* the few routines that want their own register allocation */
 #define FLY_LANE() ((int)(threadIdx.x & 31))
 #define FLY_FOR(i, n) for (int i = FLY_LANE(); i < (n); i += 32)
 #define FLY_SYNC() __syncwarp()
@@ -74,9 +76,26 @@ template <class P> FLY_INL int warp_compact(int n, P pred, unsigned short* out, 
   __syncwarp();
   return cnt;
 }
+/* ordered in-place filter of list[0..n): keeps the entries with pred(i), returns how many (a kept entry never moves up) */
+template <class P> FLY_INL int warp_filter(int n, P pred, unsigned short* list) {
+  int cnt = 0;
+  const int lane = FLY_LANE();
+  for (int base = 0; base < n; base += 32) {
+    const int i = base + lane;
+    const unsigned short v = i < n ? list[i] : (unsigned short)0;
+    const bool p = i < n && pred(i);
+    const unsigned mask = __ballot_sync(0xffffffffu, p);   /* every lane has read its entry before any lane writes */
+    if (p) list[cnt + __popc(mask & ((1u << lane) - 1u))] = v;
+    cnt += __popc(mask);
+  }
+  __syncwarp();
+  return cnt;
+}
 #else
 #define FLY_FN static
 #define FLY_INL static inline
+#define FLY_MEM inline
+#define FLY_NOINL static
 #define FLY_LANE() 0
 #define FLY_FOR(i, n) for (int i = 0; i < (n); i++)
 #define FLY_SYNC()
@@ -91,6 +110,12 @@ template <class P> FLY_INL int warp_compact(int n, P pred, unsigned short* out, 
   int cnt = 0;
   for (int i = 0; i < n; i++)
     if (pred(i)) { if (cnt < maxout) out[cnt] = (unsigned short)i; cnt++; }
+  return cnt;
+}
+template <class P> FLY_INL int warp_filter(int n, P pred, unsigned short* list) {
+  int cnt = 0;
+  for (int i = 0; i < n; i++)
+    if (pred(i)) list[cnt++] = list[i];
   return cnt;
 }
 #endif

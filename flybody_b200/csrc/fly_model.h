@@ -23,7 +23,7 @@
 #define FLY_MAXEFC 160    /* constraint rows per env */
 #define FLY_MAXGRP 144    /* constraint groups (limit row | condim-1 contact | 3-row elliptic contact) */
 #define FLY_MAXCAND 256   /* narrow-phase candidates after the bounding-sphere test */
-#define FLY_MAXCROSS 24   /* two-chain (cross-branch) contact rows */
+#define FLY_MAXCROSS 64   /* two-chain (cross-branch) contact rows */
 #define FLY_HEAVY 24      /* dofs with more descendants than this are reduced warp-cooperatively */
 #define FLY_MAXTRUNK 8    /* dofs of the trunk chain (held in registers by the factorisation and the solves) */
 

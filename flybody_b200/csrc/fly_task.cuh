@@ -141,7 +141,7 @@ FLY_FN void fly_sensors_vel(const DModel<T>& m, const Ws<T>& w) {
  * fly_forward_acc and before fly_integrate; every warp passes each of them once per call whatever its env does.  A warp
  * that does less than a full control step (reset, masked or idle) makes the difference up with fly_block_pad.
  * Measured on B200 (16 warps per SM): without any rendezvous the kernel is 3.4x slower than with seven per substep. */
-/* rendezvous bits: fly_step1 0,7,8,9,1,10,2,11,12,13 (in program order) ; fly_forward_acc 3,14,4,15,16,17,5 ; fly_integrate 6 */
+/* rendezvous bits: fly_step1 0,7,8,1,9,10,2,11,12,13 (in program order) ; fly_forward_acc 3,14,4,15,16,17,5 ; fly_integrate 6 */
 #define FLY_SYNC_BITS_STEP1 0x3f87u
 #define FLY_SYNC_BITS_FWD 0x3c038u
 #define FLY_SYNC_BITS_INT 0x40u
@@ -164,6 +164,8 @@ FLY_FN void fly_step1(const DModel<T>& m, const Ws<T>& w, bool full) {
   FLY_STAGE_SYNC(7);
   fly_com_pos(m, w);
   FLY_STAGE_SYNC(8);
+  if (full) fly_collision(m, w);  /* before the factorisations: its convex search borrows their storage (qLD | qH) */
+  FLY_STAGE_SYNC(1);
   if (full) fly_crb(m, w);
   FLY_STAGE_SYNC(9);
   if (full) {
@@ -173,8 +175,6 @@ FLY_FN void fly_step1(const DModel<T>& m, const Ws<T>& w, bool full) {
       fly_factor<T, 2>(m, LD, iv);
     }
   }
-  FLY_STAGE_SYNC(1);
-  if (full) fly_collision(m, w);
   FLY_STAGE_SYNC(10);
   if (full) fly_make_constraint(m, w);
   FLY_STAGE_SYNC(2);

@@ -11,7 +11,17 @@
 
 /* tier of an array: 0 = always bulk; 1..4 = goes to the fast arena when the launch's `level` is >= the tier
  * (1: the two factorisations and the vectors their solves run on; 2: state and solver vectors; 3, 4: kinematics) */
+#if defined(__CUDACC__)
+#define FLY_HD __host__ __device__ inline
+#else
+#define FLY_HD inline
+#endif
 #define FLY_NHIT 4   /* most contacts a primitive pair can produce */
+
+/* qLD | qH (adjacent, same tier) double as the warp's portal scratch of the convex narrow phase (fly_col.cuh:
+ * 4 points x 6 float64 x 32 lanes = 6144 B, then two geom poses x 12 words x 32 lanes), which runs while neither
+ * factorisation is live; qLD is padded so that the two together always hold it (2304 words when T is float) */
+FLY_HD int fly_qld_count(int nM) { const int need = 2304 + 8 - (nM + 4); return nM + 1 > need ? nM + 1 : need; }
 
 /* X(name, element-count expression over `m`, tier) ; arrays of T */
 #define FLY_WS_REAL(X)                                                                                       \
@@ -23,7 +33,7 @@
   X(geom_xpos, 3 * m.ngeom, 3) X(site_xpos, 3 * m.nsite, 0) X(site_xmat, 9 * m.nsite, 0)\
   X(scom, 3 * m.nbody, 3) X(cinert, 10 * m.nbody, 4) X(crb, 0, 0)            \
   X(cdof, 6 * m.nv, 3) X(cdof_dot, 6 * m.nv, 4) X(cvel, 6 * m.nbody, 4)                 \
-  X(qLD, m.nM + 1, 1) X(qH, m.nM + 1, 1)                    \
+  X(qLD, fly_qld_count(m.nM), 1) X(qH, m.nM + 1, 1)                    \
   X(qDinv, m.nv, 1) X(qHinv, m.nv, 1) X(gpart, 64, 0)                                         \
   X(act_length, m.nu, 0) X(act_force, m.nu, 0) X(act_dot, m.na, 0)                      \
   X(qfrc_bias, m.nv, 0) X(qfrc_passive, m.nv, 0) X(qfrc_actuator, m.nv, 0)              \
@@ -93,11 +103,6 @@ struct Ws {
 #undef X
 };
 
-#if defined(__CUDACC__)
-#define FLY_HD __host__ __device__ inline
-#else
-#define FLY_HD inline
-#endif
 
 /* Carves the two arenas.  Pass null bases to only measure; sizes (bytes, 16-aligned) are returned. */
 template <class T>

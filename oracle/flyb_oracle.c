@@ -467,6 +467,239 @@ static int hit_sphere_cylinder(Hit* h, const double* c1, double r1, const double
   return hit_sphere_sphere(h, c1, r1, p, 0.0, margin);
 }
 
+/* ---- general convex pairs (MuJoCo mjc_Convex): ellipsoid and cylinder geoms off the plane.
+ * MuJoCo (engine_collision_convex.c, third party, not vendored; the reference leaves the version unpinned, 3.1-3.2 by its
+ * dates) hands these pairs to libccd's Minkowski Portal Refinement (ccdMPRPenetration, libccd src/mpr.c, vendored inside
+ * MuJoCo) with mpr_tolerance 1e-6 and mpr_iterations 50, support functions per geom type, each object inflated by
+ * margin/2, dist = margin - depth, then adjusts the normal from the geom shapes (mjc_fixNormal).  Restated here from the
+ * published algorithm (G. Snethen, "XenoCollide", Game Programming Gems 7; libccd's structure: discoverPortal,
+ * refinePortal, findPenetr, findPos).  "parity unpinned": no MuJoCo build is available to check against; the
+ * known-answer tests compare it with the analytic sphere/capsule/cylinder routines above on degenerate ellipsoids. */
+#define CCD_EPS 2.220446049250313e-16
+#define MPR_TOLERANCE 1e-6
+#define MPR_ITERATIONS 50
+#define MPR_PORTAL_CAP 100  /* guard on libccd's open-ended portal loops (never reached in exact arithmetic) */
+typedef struct { double v[3], v1[3], v2[3]; } Supp;
+typedef struct { int type; const double *pos, *mat, *size; double margin; } CcdObj;
+
+static int ccd_is_zero(double x) { return fabs(x) < CCD_EPS; }
+static int ccd_eq(double a, double b) {
+  double ab = fabs(a - b);
+  if (ab < CCD_EPS) return 1;
+  a = fabs(a); b = fabs(b);
+  return b > a ? ab < CCD_EPS * b : ab < CCD_EPS * a;
+}
+static double sign0(double x) { return x > 0 ? 1.0 : (x < 0 ? -1.0 : 0.0); }
+/* support point of one geom in world direction dir (mjccd_support) */
+static void ccd_support_geom(const CcdObj* o, const double* dir, double* res) {
+  double ld[3], r[3] = {0, 0, 0}, w[3];
+  matT_vec(ld, o->mat, dir);
+  switch (o->type) {
+    case FLYB_GEOM_SPHERE: for (int k = 0; k < 3; k++) r[k] = ld[k] * o->size[0]; break;
+    case FLYB_GEOM_CAPSULE:
+      for (int k = 0; k < 3; k++) r[k] = ld[k] * o->size[0];
+      r[2] += sign0(ld[2]) * o->size[1];
+      break;
+    case FLYB_GEOM_ELLIPSOID: {
+      double t[3] = {ld[0] * o->size[0], ld[1] * o->size[1], ld[2] * o->size[2]};
+      normalize3(t);
+      for (int k = 0; k < 3; k++) r[k] = t[k] * o->size[k];
+      break;
+    }
+    case FLYB_GEOM_CYLINDER: {
+      double t = sqrt(ld[0] * ld[0] + ld[1] * ld[1]);
+      if (t > MINVAL) { double sc = o->size[0] / t; r[0] = ld[0] * sc; r[1] = ld[1] * sc; }
+      r[2] = sign0(ld[2]) * o->size[1];
+      break;
+    }
+    default: break;
+  }
+  mat_vec(w, o->mat, r);
+  for (int k = 0; k < 3; k++) res[k] = w[k] + o->pos[k] + dir[k] * o->margin;
+}
+static void ccd_support(const CcdObj* o1, const CcdObj* o2, const double* dir, Supp* s) {
+  double nd[3] = {-dir[0], -dir[1], -dir[2]};
+  ccd_support_geom(o1, dir, s->v1);
+  ccd_support_geom(o2, nd, s->v2);
+  for (int k = 0; k < 3; k++) s->v[k] = s->v1[k] - s->v2[k];
+}
+static void ccd_normalize(double* v) { double k = 1.0 / norm3(v); v[0] *= k; v[1] *= k; v[2] *= k; }  /* ccdVec3Normalize: scale by 1/len, no guard */
+static void portal_dir(const Supp* P, double* dir) {
+  double a[3], b[3];
+  for (int k = 0; k < 3; k++) { a[k] = P[2].v[k] - P[1].v[k]; b[k] = P[3].v[k] - P[1].v[k]; }
+  cross3(dir, a, b);
+  ccd_normalize(dir);
+}
+static int portal_reach_tolerance(const Supp* P, const Supp* v4, const double* dir) {
+  double dv1 = dot3(P[1].v, dir), dv2 = dot3(P[2].v, dir), dv3 = dot3(P[3].v, dir), dv4 = dot3(v4->v, dir);
+  double d = fmin(fmin(dv4 - dv1, dv4 - dv2), dv4 - dv3);
+  return ccd_eq(d, MPR_TOLERANCE) || d < MPR_TOLERANCE;
+}
+static void expand_portal(Supp* P, const Supp* v4) {
+  double v4v0[3];
+  cross3(v4v0, v4->v, P[0].v);
+  if (dot3(P[1].v, v4v0) > 0) {
+    if (dot3(P[2].v, v4v0) > 0) P[1] = *v4; else P[3] = *v4;
+  } else {
+    if (dot3(P[3].v, v4v0) > 0) P[2] = *v4; else P[1] = *v4;
+  }
+}
+static double point_seg_dist2(const double* x0, const double* b, double* wit) {  /* P = origin */
+  double d[3] = {b[0] - x0[0], b[1] - x0[1], b[2] - x0[2]};
+  double t = -dot3(x0, d) / dot3(d, d);
+  if (t < 0 || ccd_is_zero(t)) { memcpy(wit, x0, 24); }
+  else if (t > 1 || ccd_eq(t, 1)) { memcpy(wit, b, 24); }
+  else for (int k = 0; k < 3; k++) wit[k] = x0[k] + t * d[k];
+  return dot3(wit, wit);
+}
+static double origin_tri_dist2(const double* x0, const double* B, const double* C, double* wit) {  /* ccdVec3PointTriDist2 */
+  double d1[3], d2[3];
+  for (int k = 0; k < 3; k++) { d1[k] = B[k] - x0[k]; d2[k] = C[k] - x0[k]; }
+  double v = dot3(d1, d1), w = dot3(d2, d2), p = dot3(x0, d1), q = dot3(x0, d2), r = dot3(d1, d2);
+  double s = (q * r - w * p) / (w * v - r * r), t = (-s * r - q) / w;
+  if ((ccd_is_zero(s) || s > 0) && (ccd_eq(s, 1) || s < 1) && (ccd_is_zero(t) || t > 0) && (ccd_eq(t, 1) || t < 1) &&
+      (ccd_eq(t + s, 1) || t + s < 1)) {
+    for (int k = 0; k < 3; k++) wit[k] = x0[k] + s * d1[k] + t * d2[k];
+    return dot3(wit, wit);
+  }
+  double w2[3], dist = point_seg_dist2(x0, B, wit), d;
+  d = point_seg_dist2(x0, C, w2); if (d < dist) { dist = d; memcpy(wit, w2, 24); }
+  d = point_seg_dist2(B, C, w2);  if (d < dist) { dist = d; memcpy(wit, w2, 24); }
+  return dist;
+}
+/* returns 0 and (depth, dir, pos) when the inflated objects intersect, -1 otherwise (ccdMPRPenetration) */
+static int mpr_penetration(const CcdObj* o1, const CcdObj* o2, double* depth, double* pdir, double* pos) {
+  Supp P[4], v4;
+  double dir[3], va[3], vb[3], dot;
+  /* discoverPortal */
+  for (int k = 0; k < 3; k++) { P[0].v1[k] = o1->pos[k]; P[0].v2[k] = o2->pos[k]; P[0].v[k] = o1->pos[k] - o2->pos[k]; }
+  if (ccd_eq(P[0].v[0], 0) && ccd_eq(P[0].v[1], 0) && ccd_eq(P[0].v[2], 0)) P[0].v[0] += CCD_EPS * 10;
+  for (int k = 0; k < 3; k++) dir[k] = -P[0].v[k];
+  ccd_normalize(dir);
+  ccd_support(o1, o2, dir, &P[1]);
+  dot = dot3(P[1].v, dir);
+  if (ccd_is_zero(dot) || dot < 0) return -1;
+  cross3(dir, P[0].v, P[1].v);
+  if (ccd_is_zero(dot3(dir, dir))) {
+    if (ccd_eq(P[1].v[0], 0) && ccd_eq(P[1].v[1], 0) && ccd_eq(P[1].v[2], 0)) {  /* findPenetrTouch: normal undefined */
+      *depth = 0; pdir[0] = pdir[1] = pdir[2] = 0;
+    } else {                                                                       /* findPenetrSegment */
+      *depth = norm3(P[1].v);
+      memcpy(pdir, P[1].v, 24); ccd_normalize(pdir);
+    }
+    for (int k = 0; k < 3; k++) pos[k] = 0.5 * (P[1].v1[k] + P[1].v2[k]);
+    return 0;
+  }
+  ccd_normalize(dir);
+  ccd_support(o1, o2, dir, &P[2]);
+  dot = dot3(P[2].v, dir);
+  if (ccd_is_zero(dot) || dot < 0) return -1;
+  for (int k = 0; k < 3; k++) { va[k] = P[1].v[k] - P[0].v[k]; vb[k] = P[2].v[k] - P[0].v[k]; }
+  cross3(dir, va, vb);
+  ccd_normalize(dir);
+  if (dot3(dir, P[0].v) > 0) { Supp t = P[1]; P[1] = P[2]; P[2] = t; dir[0] = -dir[0]; dir[1] = -dir[1]; dir[2] = -dir[2]; }
+  for (int guard = 0;; guard++) {
+    if (guard > MPR_PORTAL_CAP) return -1;
+    ccd_support(o1, o2, dir, &P[3]);
+    dot = dot3(P[3].v, dir);
+    if (ccd_is_zero(dot) || dot < 0) return -1;
+    int cont = 0;
+    cross3(va, P[1].v, P[3].v);
+    dot = dot3(va, P[0].v);
+    if (dot < 0 && !ccd_is_zero(dot)) { P[2] = P[3]; cont = 1; }
+    if (!cont) {
+      cross3(va, P[3].v, P[2].v);
+      dot = dot3(va, P[0].v);
+      if (dot < 0 && !ccd_is_zero(dot)) { P[1] = P[3]; cont = 1; }
+    }
+    if (!cont) break;
+    for (int k = 0; k < 3; k++) { va[k] = P[1].v[k] - P[0].v[k]; vb[k] = P[2].v[k] - P[0].v[k]; }
+    cross3(dir, va, vb);
+    ccd_normalize(dir);
+  }
+  /* refinePortal */
+  for (int guard = 0;; guard++) {
+    if (guard > MPR_PORTAL_CAP) return -1;
+    portal_dir(P, dir);
+    dot = dot3(dir, P[1].v);
+    if (ccd_is_zero(dot) || dot > 0) break;  /* portal encapsulates the origin */
+    ccd_support(o1, o2, dir, &v4);
+    dot = dot3(v4.v, dir);
+    if (!(ccd_is_zero(dot) || dot > 0) || portal_reach_tolerance(P, &v4, dir)) return -1;
+    expand_portal(P, &v4);
+  }
+  /* findPenetr */
+  for (unsigned long it = 0;; it++) {
+    portal_dir(P, dir);
+    ccd_support(o1, o2, dir, &v4);
+    if (portal_reach_tolerance(P, &v4, dir) || it > MPR_ITERATIONS) {
+      *depth = sqrt(origin_tri_dist2(P[1].v, P[2].v, P[3].v, pdir));
+      if (ccd_is_zero(pdir[0]) && ccd_is_zero(pdir[1]) && ccd_is_zero(pdir[2])) memcpy(pdir, dir, 24);  /* origin on the portal */
+      ccd_normalize(pdir);
+      /* findPos: barycentric coordinates of the origin in the portal tetrahedron */
+      double b[4], vec[3], sum;
+      portal_dir(P, dir);
+      cross3(vec, P[1].v, P[2].v); b[0] = dot3(vec, P[3].v);
+      cross3(vec, P[3].v, P[2].v); b[1] = dot3(vec, P[0].v);
+      cross3(vec, P[0].v, P[1].v); b[2] = dot3(vec, P[3].v);
+      cross3(vec, P[2].v, P[1].v); b[3] = dot3(vec, P[0].v);
+      sum = b[0] + b[1] + b[2] + b[3];
+      if (ccd_is_zero(sum) || sum < 0) {
+        b[0] = 0;
+        cross3(vec, P[2].v, P[3].v); b[1] = dot3(vec, dir);
+        cross3(vec, P[3].v, P[1].v); b[2] = dot3(vec, dir);
+        cross3(vec, P[1].v, P[2].v); b[3] = dot3(vec, dir);
+        sum = b[1] + b[2] + b[3];
+      }
+      for (int k = 0; k < 3; k++) {
+        double p1 = 0, p2 = 0;
+        for (int i = 0; i < 4; i++) { p1 += b[i] * P[i].v1[k]; p2 += b[i] * P[i].v2[k]; }
+        pos[k] = 0.5 * (p1 + p2) / sum;
+      }
+      return 0;
+    }
+    expand_portal(P, &v4);
+  }
+}
+/* mjc_fixNormal: normal of a smooth geom at the contact point, from its shape; n is the MPR direction on entry */
+static void convex_geom_normal(const CcdObj* o, const double* cpos, double* n) {
+  double dif[3] = {cpos[0] - o->pos[0], cpos[1] - o->pos[1], cpos[2] - o->pos[2]}, p[3], nl[3];
+  matT_vec(p, o->mat, dif);
+  matT_vec(nl, o->mat, n);
+  switch (o->type) {
+    case FLYB_GEOM_SPHERE: memcpy(nl, p, 24); break;
+    case FLYB_GEOM_CAPSULE:
+      nl[0] = p[0]; nl[1] = p[1];
+      nl[2] = p[2] < -o->size[1] ? p[2] + o->size[1] : (p[2] > o->size[1] ? p[2] - o->size[1] : 0.0);
+      break;
+    case FLYB_GEOM_ELLIPSOID: for (int k = 0; k < 3; k++) nl[k] = p[k] / (o->size[k] * o->size[k]); break;
+    case FLYB_GEOM_CYLINDER: {
+      double dside = fabs(sqrt(p[0] * p[0] + p[1] * p[1]) - o->size[0]), dcap = fabs(fabs(p[2]) - o->size[1]);
+      if (dside < 0.5 * dcap) { nl[0] = p[0]; nl[1] = p[1]; nl[2] = 0; }
+      else if (dcap < 0.5 * dside) { nl[0] = 0; nl[1] = 0; nl[2] = p[2]; }
+      break;
+    }
+    default: break;
+  }
+  normalize3(nl);
+  mat_vec(n, o->mat, nl);
+}
+static int hit_convex(Hit* h, int t1, const double* c1, const double* m1, const double* s1, int t2, const double* c2,
+                      const double* m2, const double* s2, double margin) {
+  CcdObj o1 = {t1, c1, m1, s1, 0.5 * margin}, o2 = {t2, c2, m2, s2, 0.5 * margin};
+  double depth, dir[3], pos[3];
+  if (mpr_penetration(&o1, &o2, &depth, dir, pos) != 0) return 0;
+  if (dir[0] == 0 && dir[1] == 0 && dir[2] == 0) return 0;  /* touching contact without a normal */
+  double n1[3] = {dir[0], dir[1], dir[2]}, n2[3] = {-dir[0], -dir[1], -dir[2]};
+  convex_geom_normal(&o1, pos, n1);
+  convex_geom_normal(&o2, pos, n2);
+  for (int k = 0; k < 3; k++) h->n[k] = n1[k] - n2[k];
+  normalize3(h->n);
+  h->dist = margin - depth; h->has_t = 0;
+  memcpy(h->pos, pos, 24);
+  return 1;
+}
+
 /* world-frame translational Jacobian row of a point fixed to body b, projected on direction dir:
    out[d] += sign * dir . (cdof_lin[d] + cdof_ang[d] x (point - subtree_com[root])) for every dof d above b */
 static void add_jac_dir(FlyoEnv* e, double* out, int b, const double* point, const double* dir, double sign) {
@@ -480,6 +713,38 @@ static void add_jac_dir(FlyoEnv* e, double* out, int b, const double* point, con
     cross3(t, cd, off);
     out[d] += sign * (dir[0] * (cd[3] + t[0]) + dir[1] * (cd[4] + t[1]) + dir[2] * (cd[5] + t[2]));
   }
+}
+
+/* narrow phase of one geom pair (t1 <= t2 in MuJoCo's type order); the collision driver and the unit tests share it */
+static int narrow_pair(Hit* h, int t1, const double* c1, const double* m1, const double* s1, int t2, const double* c2,
+                       const double* m2, const double* s2, double margin) {
+  if (t1 == FLYB_GEOM_PLANE) {
+    double pn[3] = {m1[2], m1[5], m1[8]};
+    if (t2 == FLYB_GEOM_SPHERE) return hit_plane_sphere(h, c1, pn, c2, s2[0], margin);
+    if (t2 == FLYB_GEOM_CAPSULE) return hit_plane_capsule(h, c1, pn, c2, m2, s2, margin);
+    if (t2 == FLYB_GEOM_ELLIPSOID) return hit_plane_ellipsoid(h, c1, pn, c2, m2, s2, margin);
+    if (t2 == FLYB_GEOM_CYLINDER) return hit_plane_cylinder(h, c1, pn, c2, m2, s2, margin);
+    return 0;
+  }
+  if (t1 == FLYB_GEOM_SPHERE) {
+    if (t2 == FLYB_GEOM_SPHERE) return hit_sphere_sphere(h, c1, s1[0], c2, s2[0], margin);
+    if (t2 == FLYB_GEOM_CAPSULE) return hit_sphere_capsule(h, c1, s1[0], c2, m2, s2, margin);
+    if (t2 == FLYB_GEOM_CYLINDER) return hit_sphere_cylinder(h, c1, s1[0], c2, m2, s2, margin);
+  }
+  if (t1 == FLYB_GEOM_CAPSULE && t2 == FLYB_GEOM_CAPSULE) return hit_capsule_capsule(h, c1, m1, s1, c2, m2, s2, margin);
+  return hit_convex(h, t1, c1, m1, s1, t2, c2, m2, s2, margin);  /* every pair type without an analytic routine */
+}
+/* test hook: out = [n, then per hit: dist, pos(3), normal(3)]; force_convex routes the pair through the MPR path */
+int flyo_narrow_pair(int t1, const double* c1, const double* m1, const double* s1, int t2, const double* c2,
+                     const double* m2, const double* s2, double margin, int force_convex, double* out) {
+  Hit h[4];
+  int n = force_convex ? hit_convex(h, t1, c1, m1, s1, t2, c2, m2, s2, margin)
+                       : narrow_pair(h, t1, c1, m1, s1, t2, c2, m2, s2, margin);
+  for (int i = 0; i < n; i++) {
+    out[7 * i] = h[i].dist;
+    for (int k = 0; k < 3; k++) { out[7 * i + 1 + k] = h[i].pos[k]; out[7 * i + 4 + k] = h[i].n[k]; }
+  }
+  return n;
 }
 
 static void collision(FlyoEnv* e) {
@@ -502,21 +767,7 @@ static void collision(FlyoEnv* e) {
       if (dot3(d, d) > bound * bound) continue;
     }
     Hit h[4];
-    int n = 0;
-    if (t1 == FLYB_GEOM_PLANE) {
-      double pn[3] = {m1[2], m1[5], m1[8]};
-      if (t2 == FLYB_GEOM_SPHERE) n = hit_plane_sphere(h, c1, pn, c2, s2[0], margin);
-      else if (t2 == FLYB_GEOM_CAPSULE) n = hit_plane_capsule(h, c1, pn, c2, m2, s2, margin);
-      else if (t2 == FLYB_GEOM_ELLIPSOID) n = hit_plane_ellipsoid(h, c1, pn, c2, m2, s2, margin);
-      else if (t2 == FLYB_GEOM_CYLINDER) n = hit_plane_cylinder(h, c1, pn, c2, m2, s2, margin);
-    } else if (t1 == FLYB_GEOM_SPHERE) {
-      if (t2 == FLYB_GEOM_SPHERE) n = hit_sphere_sphere(h, c1, s1[0], c2, s2[0], margin);
-      else if (t2 == FLYB_GEOM_CAPSULE) n = hit_sphere_capsule(h, c1, s1[0], c2, m2, s2, margin);
-      else if (t2 == FLYB_GEOM_CYLINDER) n = hit_sphere_cylinder(h, c1, s1[0], c2, m2, s2, margin);
-    } else if (t1 == FLYB_GEOM_CAPSULE && t2 == FLYB_GEOM_CAPSULE) {
-      n = hit_capsule_capsule(h, c1, m1, s1, c2, m2, s2, margin);
-    }
-    /* ellipsoid/cylinder pairs off the plane need a general convex routine: not built yet */
+    const int n = narrow_pair(h, t1, c1, m1, s1, t2, c2, m2, s2, margin);
     for (int i = 0; i < n && e->ncon < FLYO_MAXCON; i++) {
       FlyoContact* c = e->con + e->ncon++;
       c->pair = p; c->geom1 = g1; c->geom2 = g2; c->dim = m->pair_condim[p];

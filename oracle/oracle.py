@@ -67,6 +67,8 @@ def lib():
         L.flyo_env_reset.restype = ctypes.c_int
         L.flyo_env_step.argtypes = [ctypes.c_void_p, dp, dp, dp, dp]
         L.flyo_env_step.restype = ctypes.c_int
+        L.flyo_narrow_pair.argtypes = [ctypes.c_int, dp, dp, dp, ctypes.c_int, dp, dp, dp, ctypes.c_double, ctypes.c_int, dp]
+        L.flyo_narrow_pair.restype = ctypes.c_int
         _lib = L
     return _lib
 
@@ -166,3 +168,18 @@ class OracleEnv:
         r, g = ctypes.c_double(0), ctypes.c_double(0)
         st = lib().flyo_env_step(self._h, a.ctypes.data_as(dp), obs.ctypes.data_as(dp), ctypes.byref(r), ctypes.byref(g))
         return st, r.value, g.value, obs
+
+
+GEOM_PLANE, GEOM_SPHERE, GEOM_CAPSULE, GEOM_ELLIPSOID, GEOM_CYLINDER = 0, 2, 3, 4, 5
+
+
+def narrow_pair(t1, pos1, mat1, size1, t2, pos2, mat2, size2, margin=0.0, force_convex=False):
+    """Narrow phase of one primitive pair (geom type, world position, 3x3 world orientation, size) in the oracle.
+    Returns a list of (dist, pos[3], normal[3]); force_convex sends the pair through the MPR routine whatever its types."""
+    a = [np.ascontiguousarray(x, np.float64).reshape(-1) for x in (pos1, mat1, size1, pos2, mat2, size2)]
+    out = np.zeros(28)
+    dp = ctypes.POINTER(ctypes.c_double)
+    P = [x.ctypes.data_as(dp) for x in a]
+    n = lib().flyo_narrow_pair(int(t1), P[0], P[1], P[2], int(t2), P[3], P[4], P[5], float(margin), int(force_convex),
+                               out.ctypes.data_as(dp))
+    return [(out[7 * i], out[7 * i + 1:7 * i + 4].copy(), out[7 * i + 4:7 * i + 7].copy()) for i in range(n)]
