@@ -1,0 +1,225 @@
+"""Batched actor side of the DMPO loop: policy inference, n-step transition assembly and the environment loop, all on
+the GPU the environments live on (BASELINE.json configs[3]).
+
+The reference runs `num_actors` (90, `config/train_config_fly.yaml:8`) Ray processes, each stepping ONE dm_control env
+through `acme.EnvironmentLoop` with a `DelayedFeedForwardActor` (`vnl_ray/agents/actors.py:21-101`) whose adder is acme's
+`NStepTransitionAdder(n_step, discount)` (`agents/ray_distributed_dmpo.py:514-521`; n_step 50, `train_dmpo_ray.py:236`).
+Here one process steps N environments per call (`fly_envs.BatchedFlyEnv`) and these classes are the same three roles with a
+leading batch dimension:
+
+  LayerNormMLPPolicy        the policy network of `agents/network_factory.py:73-101` (batch_concat -> LayerNormMLP ->
+                            MultivariateNormalDiagHead), torch, random init (no checkpoints here)
+  BatchedFeedForwardActor   select_action / observe_first / observe / update with the reference actor's action_delay and
+                            observation_callback arguments
+  NStepTransitionAdder      acme's n-step transitions (o_t, a_t, R, D, o_{t+n}) per env, with the shrinking-horizon flush
+                            at episode end, assembled from ring buffers on the device and shipped to a `sink` callable in
+                            batches (the stand-in for the reverb client, which is not installed here)
+  BatchedEnvironmentLoop    acme.EnvironmentLoop over a batched, auto-resetting environment
+
+acme / sonnet / reverb are third-party and absent: their semantics are restated (acme adders/reverb/transition.py, acme
+tf/networks), not imported, and the restatement of the adder is tested against a per-env list implementation
+(tests/test_actors.py).  The learner, replay and variable server stay out of scope."""
+from __future__ import annotations
+
+import math
+from typing import Callable, Optional
+
+import torch
+from torch import nn
+
+FIRST, MID, LAST = 0, 1, 2
+
+
+def batch_concat(observation) -> torch.Tensor:
+    """acme tf2_utils.batch_concat: flatten every leaf to [N, -1] and concatenate, leaves in sorted-key order."""
+    if isinstance(observation, torch.Tensor):
+        return observation.reshape(observation.shape[0], -1)
+    return torch.cat([observation[k].reshape(observation[k].shape[0], -1) for k in sorted(observation)], dim=1)
+
+
+class LayerNormMLPPolicy(nn.Module):
+    """Linear -> LayerNorm -> tanh -> (Linear -> ELU)* (acme LayerNormMLP, activate_final=True), then a diagonal Gaussian
+    head: mean = Linear, scale = softplus(Linear) * init_scale / softplus(0) + min_scale (MultivariateNormalDiagHead)."""
+
+    def __init__(self, obs_dim: int, action_dim: int, layer_sizes=(512, 512, 512, 512), min_scale: float = 1e-6,
+                 tanh_mean: bool = False, init_scale: float = 0.7, fixed_scale: bool = False):
+        super().__init__()
+        sizes = list(layer_sizes)
+        self.first = nn.Linear(obs_dim, sizes[0])
+        self.norm = nn.LayerNorm(sizes[0])
+        self.rest = nn.ModuleList([nn.Linear(a, b) for a, b in zip(sizes[:-1], sizes[1:])])
+        self.mean = nn.Linear(sizes[-1], action_dim)
+        self.scale = nn.Linear(sizes[-1], action_dim)
+        self.min_scale, self.tanh_mean, self.init_scale, self.fixed_scale = min_scale, tanh_mean, init_scale, fixed_scale
+        for lin in [self.first, *self.rest]:
+            nn.init.trunc_normal_(lin.weight, std=1.0 / math.sqrt(lin.in_features))
+            nn.init.zeros_(lin.bias)
+        for lin in (self.mean, self.scale):   # VarianceScaling(1e-4): a near-zero head, as acme initialises it
+            nn.init.normal_(lin.weight, std=math.sqrt(1e-4 / lin.in_features))
+            nn.init.zeros_(lin.bias)
+
+    def forward(self, observation):
+        x = torch.tanh(self.norm(self.first(batch_concat(observation))))
+        for lin in self.rest:
+            x = nn.functional.elu(lin(x))
+        mean = self.mean(x)
+        if self.tanh_mean:
+            mean = torch.tanh(mean)
+        if self.fixed_scale:
+            scale = torch.full_like(mean, self.init_scale)
+        else:
+            scale = nn.functional.softplus(self.scale(x)) * (self.init_scale / math.log(2.0)) + self.min_scale
+        return mean, scale
+
+    @torch.no_grad()
+    def sample(self, observation, generator: Optional[torch.Generator] = None) -> torch.Tensor:
+        mean, scale = self(observation)
+        eps = torch.randn(mean.shape, device=mean.device, dtype=mean.dtype, generator=generator)
+        return mean + scale * eps
+
+
+class NStepTransitionAdder:
+    """acme's NStepTransitionAdder for N environments at once.
+
+    For the step sequence (o_0, a_0, r_0, d_0, o_1, ...) of one episode it emits, for every start s,
+        (o_s, a_s, R = sum_{k<h} (prod_{j<k} discount * d_{s+j}) r_{s+k}, D = discount^(h-1) prod_{k<h} d_{s+k}, o_{s+h})
+    with h = n_step once n_step steps are available, and h = n_step-1 .. 1 for the last starts when the episode ends
+    (acme `_write` / `_write_last`; the final factor of `discount` is left to the learner, as in acme).
+    Ring buffers live on `device`; every call ships the transitions it completed to `sink(dict)` as one batch."""
+
+    def __init__(self, num_envs: int, obs_dim: int, action_dim: int, n_step: int, discount: float, device="cuda",
+                 sink: Optional[Callable[[dict], None]] = None):
+        self.N, self.n, self.gamma = int(num_envs), int(n_step), float(discount)
+        dev = torch.device(device)
+        self.obs = torch.zeros((self.N, self.n + 1, obs_dim), device=dev)
+        self.act = torch.zeros((self.N, self.n, action_dim), device=dev)
+        self.rew = torch.zeros((self.N, self.n), device=dev)
+        self.disc = torch.ones((self.N, self.n), device=dev)
+        self.count = torch.zeros(self.N, dtype=torch.long, device=dev)   # transitions added to the running episode
+        self.started = torch.zeros(self.N, dtype=torch.bool, device=dev)
+        self._k = torch.arange(self.n, device=dev)
+        self._env = torch.arange(self.N, device=dev)
+        self.sink = sink
+        self.num_written = 0
+
+    def reset(self):
+        self.count.zero_(); self.started.zero_()
+
+    def add_first(self, timestep, mask: Optional[torch.Tensor] = None):
+        """Start of an episode for the envs in `mask` (default: those whose step_type is FIRST)."""
+        obs = batch_concat(timestep.observation)
+        m = (timestep.step_type == FIRST) if mask is None else mask
+        e = self._env[m]
+        self.count[e] = 0
+        self.started[e] = True
+        self.obs[e, 0] = obs[e]
+
+    def _returns(self, env, start, horizon):
+        """n-step return and discount of the transitions (env[i], start[i]) over horizon[i] <= n steps."""
+        idx = (start[:, None] + self._k[None, :]) % self.n
+        live = self._k[None, :] < horizon[:, None]
+        r = torch.gather(self.rew[env], 1, idx)
+        d = torch.where(live, torch.gather(self.disc[env], 1, idx), torch.ones((), device=r.device))
+        g = torch.where(live, torch.full_like(d, self.gamma), torch.ones((), device=r.device))
+        run = torch.cumprod(g * d, dim=1)
+        before = torch.cat([torch.ones_like(run[:, :1]), run[:, :-1]], dim=1)     # prod_{j<k} discount * d_j
+        R = (torch.where(live, r, torch.zeros((), device=r.device)) * before).sum(1)
+        D = run[:, -1] / self.gamma                                                # discount^(h-1) * prod d
+        return R, D
+
+    def add(self, action: torch.Tensor, next_timestep):
+        """Append (a_t, r_t, d_t, o_{t+1}) for every env that is inside an episode; envs whose `next_timestep` is FIRST
+        (auto-reset inside env.step) start a new episode instead and their action is ignored, as the env ignored it."""
+        st = next_timestep.step_type
+        first = st == FIRST
+        if bool(first.any()):
+            self.add_first(next_timestep, first)
+        live = self.started & ~first
+        obs = batch_concat(next_timestep.observation)
+        e = self._env[live]
+        c = self.count[e]
+        self.act[e, c % self.n] = action[e]
+        self.rew[e, c % self.n] = next_timestep.reward[e]
+        self.disc[e, c % self.n] = next_timestep.discount[e]
+        self.obs[e, (c + 1) % (self.n + 1)] = obs[e]
+        self.count[e] = c + 1
+        c = self.count
+        # full-horizon transition of every env that has n steps behind it
+        env = self._env[live & (c >= self.n)]
+        start = c[env] - self.n
+        hor = torch.full_like(start, self.n)
+        # shrinking-horizon flush of the envs whose episode just ended
+        last = self._env[live & (st == LAST)]
+        if last.numel():
+            j = torch.arange(1, self.n, device=last.device)
+            s = c[last][:, None] - self.n + j[None, :]                             # starts count-n+1 .. count-1
+            ok = s >= 0
+            env = torch.cat([env, last[:, None].expand(-1, self.n - 1)[ok]])
+            start = torch.cat([start, s[ok]])
+            hor = torch.cat([hor, (self.n - j)[None, :].expand(last.numel(), -1)[ok]])
+        if env.numel() == 0:
+            return 0
+        R, D = self._returns(env, start, hor)
+        batch = {"observation": self.obs[env, start % (self.n + 1)], "action": self.act[env, start % self.n], "reward": R,
+                 "discount": D, "next_observation": self.obs[env, (start + hor) % (self.n + 1)], "env": env, "start": start}
+        self.num_written += int(env.numel())
+        if self.sink is not None:
+            self.sink(batch)
+        return int(env.numel())
+
+
+class BatchedFeedForwardActor:
+    """`DelayedFeedForwardActor` (`vnl_ray/agents/actors.py:21-101`) over a batch of environments."""
+
+    def __init__(self, policy_network: LayerNormMLPPolicy, adder: Optional[NStepTransitionAdder] = None, variable_client=None,
+                 action_delay: Optional[int] = None, observation_callback: Optional[Callable] = None,
+                 generator: Optional[torch.Generator] = None):
+        self._policy_network, self._adder, self._variable_client = policy_network, adder, variable_client
+        self._action_delay, self._observation_callback, self._generator = action_delay, observation_callback, generator
+        self._action_queue = [] if action_delay is not None else None
+
+    def select_action(self, observation) -> torch.Tensor:
+        if self._observation_callback is not None:
+            observation = self._observation_callback(observation)
+        action = self._policy_network.sample(observation, self._generator)
+        if self._action_delay is not None:                     # actors.py:81-88: zeros while the queue fills
+            self._action_queue.append(action)
+            action = 0 * action if len(self._action_queue) <= self._action_delay else self._action_queue.pop(0)
+        return action
+
+    def observe_first(self, timestep):
+        if self._adder:
+            self._adder.add_first(timestep)
+
+    def observe(self, action, next_timestep):
+        if self._adder:
+            self._adder.add(action, next_timestep)
+
+    def update(self, wait: bool = False):
+        if self._variable_client:
+            self._variable_client.update(wait)
+
+
+class BatchedEnvironmentLoop:
+    """acme.EnvironmentLoop for a batched environment that resets finished envs inside `step` (fly_envs.BatchedFlyEnv)."""
+
+    def __init__(self, environment, actor: BatchedFeedForwardActor):
+        self._environment, self._actor = environment, actor
+        self._timestep = None
+        self.steps = 0
+
+    def run(self, num_steps: int):
+        """`num_steps` batched control steps; returns (env-steps taken, sum of rewards) as python numbers."""
+        env, actor = self._environment, self._actor
+        if self._timestep is None:
+            self._timestep = env.reset()
+            actor.observe_first(self._timestep)
+        reward_sum = torch.zeros((), device=self._timestep.step_type.device, dtype=torch.float64)
+        for _ in range(num_steps):
+            action = actor.select_action(self._timestep.observation)
+            self._timestep = env.step(action)
+            actor.observe(action, self._timestep)
+            actor.update()
+            reward_sum += self._timestep.reward.sum()
+            self.steps += 1
+        return num_steps * int(self._timestep.step_type.shape[0]), float(reward_sum)
