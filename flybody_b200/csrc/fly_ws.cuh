@@ -21,7 +21,7 @@
 /* qLD | qH (adjacent, same tier) double as the warp's portal scratch of the convex narrow phase (fly_col.cuh:
  * 4 points x 6 float64 x 32 lanes = 6144 B, then two geom poses x 12 words x 32 lanes), which runs while neither
  * factorisation is live; qLD is padded so that the two together always hold it (2304 words when T is float) */
-FLY_HD int fly_qld_count(int nM) { const int need = 2304 + 8 - (nM + 4); return nM + 1 > need ? nM + 1 : need; }
+FLY_HD constexpr int fly_qld_count(int nM) { const int need = 2304 + 8 - (nM + 4); return nM + 1 > need ? nM + 1 : need; }
 
 /* X(name, element-count expression over `m`, tier) ; arrays of T */
 #define FLY_WS_REAL(X)                                                                                       \
@@ -170,6 +170,46 @@ inline void ws_layout(const DModel<T>& m, int level, WsOff* o, size_t* fast_byte
 #undef PLACE
   if (fast_bytes) *fast_bytes = off[1];
   if (bulk_bytes) *bulk_bytes = off[0];
+}
+
+/* The sizes the layout depends on.  For the shipped task models they are known when the library is compiled
+ * (fly_dims_gen.h), and the step kernel instantiated for such a model takes its offsets from ws_layout_c at compile time:
+ * every array address is then arena base + immediate (measured on the generic kernel: 10.6 % of all executed instructions
+ * only added a constant-bank offset to an arena base). */
+struct WsDims { int nq, nv, na, nu, nbody, njnt, ngeom, nsite, nM, nsensordata, nfluidbox, nfluidgeom; };
+template <class M> inline WsDims ws_dims_of(const M& m) {
+  return WsDims{m.nq, m.nv, m.na, m.nu, m.nbody, m.njnt, m.ngeom, m.nsite, m.nM, m.nsensordata, m.nfluidbox, m.nfluidgeom};
+}
+inline bool ws_dims_equal(const WsDims& a, const WsDims& b) {
+  return a.nq == b.nq && a.nv == b.nv && a.na == b.na && a.nu == b.nu && a.nbody == b.nbody && a.njnt == b.njnt &&
+         a.ngeom == b.ngeom && a.nsite == b.nsite && a.nM == b.nM && a.nsensordata == b.nsensordata &&
+         a.nfluidbox == b.nfluidbox && a.nfluidgeom == b.nfluidgeom;
+}
+template <class T>
+FLY_HD constexpr WsOff ws_layout_c(const WsDims m, int level) {
+  WsOff o{};
+  size_t off[2] = {0, 0};
+#define PLACE(n, cnt, tier, type)                                          \
+  {                                                                        \
+    int t = ((tier) > 0 && (tier) <= level) ? 1 : 0;                       \
+    size_t bytes = (((size_t)(cnt) * sizeof(type)) + 15) & ~(size_t)15;    \
+    o.n = (unsigned)off[t];                                                \
+    off[t] += bytes;                                                       \
+  }
+#define X(n, cnt, tier) PLACE(n, cnt, tier, T)
+  FLY_WS_REAL(X)
+#undef X
+#define X(n, cnt, tier) PLACE(n, cnt, tier, double)
+  FLY_WS_DBL(X)
+#undef X
+#define X(n, cnt, tier) PLACE(n, cnt, tier, int)
+  FLY_WS_INT(X)
+#undef X
+#define X(n, cnt, tier) PLACE(n, cnt, tier, unsigned short)
+  FLY_WS_U16(X)
+#undef X
+#undef PLACE
+  return o;
 }
 
 #if defined(FLY_GPU)

@@ -13,7 +13,7 @@
 #include <string>
 #include <vector>
 #include "../../include/flyb.h"
-#include "fly_env.cuh"
+#include "fly_kernel.cuh"
 
 struct FlybEngine {
   int device = 0, num_envs = 0, flags = 0, env_offset = 0;
@@ -34,6 +34,7 @@ struct FlybEngine {
   float *d_action = nullptr, *d_obs = nullptr, *d_rd = nullptr; int* d_st = nullptr; unsigned char* d_mask = nullptr;
   cudaStream_t host_stream = nullptr;
   int smem_level = 1, warps = 16, blocks_per_sm = 0, sm_count = 148, grid = 0;
+  int spec = -1, no_spec = 0;   /* index of the model-specialised kernel in use (-1: generic); FLYB_NO_SPEC=1 forces generic */
   long long launches = 0;
   std::string err;
 };
@@ -49,56 +50,27 @@ static std::string g_create_error;
     }                                                                                              \
   } while (0)
 
-struct KArgs {
-  FlyClips clips;
-  FlyWbpg wb;
-  FlyIO<float> io;
-  char* bulk;
-  size_t bulk_stride, fast_stride;
-  int* counter;
-  const int* perm;   /* nullable: position in the launch order -> env id */
-  int num_envs, level;
-};
-
-template <int WARPS, int LEVEL>
-__global__ void __launch_bounds__(WARPS * 32, 1) fly_step_kernel(const __grid_constant__ DModel<float> m,
-                                                                const __grid_constant__ KArgs a,
-                                                                const __grid_constant__ WsOff off) {
-  extern __shared__ __align__(16) char smem[];
-#ifdef FLY_SYNC_GROUP
-  constexpr int GW = FLY_SYNC_GROUP;   /* warps of one lockstep group: fetches its own envs, runs on its own barrier */
-#else
-  constexpr int GW = WARPS;
-#endif
-  static_assert(WARPS % GW == 0, "lockstep group must divide the block");
-  __shared__ int s_base[WARPS / GW];
-  const int warp = threadIdx.x >> 5;
-  const int slot = blockIdx.x * WARPS + warp;
-  const int grp = warp / GW, gwarp = warp % GW;
-  /* every thread keeps its warp's array pointers as (arena base + constant offset): registers / immediates, with the
-     address space of each array known to the compiler */
-  Ws<float> w;
-  ws_attach<float, LEVEL>(w, off, smem + warp * a.fast_stride, a.bulk + (size_t)slot * a.bulk_stride);
-  for (;;) {  /* the group takes GW consecutive envs at a time and its warps step them stage by stage together */
-    FLY_BLOCK_SYNC();
-    if (gwarp == 0 && (threadIdx.x & 31) == 0) s_base[grp] = atomicAdd(a.counter, GW);
-    FLY_BLOCK_SYNC();
-    const int base = s_base[grp];
-    const int pos = base + gwarp;
-    if (base >= a.num_envs) break;
-    fly_env_run<float>(m, w, a.clips, a.wb, a.io, pos < a.num_envs ? (a.perm ? a.perm[pos] : pos) : -1);
-  }
+/* the kernels live in their own translation units (flyb_kern.cu); each exports one getter */
+#define X(W, L) extern "C" const void* flyb_kernel_##W##_##L##_g();
+FLY_KERNEL_CONFIGS(X)
+#undef X
+#define X(i, ...) extern "C" const void* flyb_kernel_16_1_s##i();
+FLY_SPEC_MODELS(X)
+#undef X
+static int spec_of(const DModel<float>& m) {
+  const WsDims d = ws_dims_of(m);
+#define X(i, ...) { const WsDims t = {__VA_ARGS__}; if (ws_dims_equal(d, t)) return i; }
+  FLY_SPEC_MODELS(X)
+#undef X
+  return -1;
 }
-
-/* compiled (warps per block, shared-memory level) combinations */
-#ifdef FLY_SINGLE_CONFIG  /* kernel experiments: compile the default pair only */
-#define FLY_KERNEL_CONFIGS(X) X(16, 1)
-#else
-#define FLY_KERNEL_CONFIGS(X) X(16, 1) X(14, 1) X(12, 1) X(8, 2) X(6, 3)
-#endif
-typedef void (*FlyKernel)(const DModel<float>, const KArgs, const WsOff);
-static FlyKernel pick_kernel(int warps, int level) {
-#define X(W, L) if (warps == W && level == L) return fly_step_kernel<W, L>;
+static const void* pick_kernel(int warps, int level, int spec = -1) {
+  if (warps == FLY_SPEC_WARPS && level == FLY_SPEC_LEVEL) {
+#define X(i, ...) if (spec == i) return flyb_kernel_16_1_s##i();
+    FLY_SPEC_MODELS(X)
+#undef X
+  }
+#define X(W, L) if (warps == W && level == L) return flyb_kernel_##W##_##L##_g();
   FLY_KERNEL_CONFIGS(X)
 #undef X
   return nullptr;
@@ -145,7 +117,16 @@ static int launch(FlybEngine* h, const FlyIO<float>& io, cudaStream_t st) {
   const size_t smem = fb * W;
   if (smem > 227 * 1024 - 2048) { h->err = "shared memory request too large for this smem_level / warps_per_block"; return 1; }
   if (bb > h->bulk_stride) { h->err = "internal: bulk slot too small"; return 1; }
-  FlyKernel kern = pick_kernel(W, h->smem_level);
+  const int spec = h->no_spec ? -1 : spec_of(h->m);
+  const void* kern = pick_kernel(W, h->smem_level, spec);
+  h->spec = (W == FLY_SPEC_WARPS && h->smem_level == FLY_SPEC_LEVEL) ? spec : -1;
+  if (h->spec >= 0) {  /* the compile-time layout must be the one the host sized the arenas with */
+    WsOff c = {};
+#define X(i, ...) if (h->spec == i) { const WsDims t = {__VA_ARGS__}; c = ws_layout_c<float>(t, FLY_SPEC_LEVEL); }
+    FLY_SPEC_MODELS(X)
+#undef X
+    if (memcmp(&c, &off, sizeof(WsOff)) != 0) { h->err = "internal: compile-time workspace layout differs from the run-time one"; return 1; }
+  }
   if (!kern) { h->err = "this (warps_per_block, smem_level) pair is not compiled in; see FLY_KERNEL_CONFIGS"; return 1; }
   CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int per_sm = 0;
@@ -171,7 +152,8 @@ static int launch(FlybEngine* h, const FlyIO<float>& io, cudaStream_t st) {
     h->launches++;
   }
   CK(cudaMemsetAsync(h->d_counter, 0, sizeof(int), st));
-  kern<<<grid, W * 32, smem, st>>>(h->m, a, off);
+  void* kargs[3] = {(void*)&h->m, (void*)&a, (void*)&off};
+  CK(cudaLaunchKernel(kern, dim3(grid), dim3(W * 32), kargs, smem, st));
   CK(cudaGetLastError());
   h->launches++;
   return 0;
@@ -263,6 +245,7 @@ int flyb_create(const FlybModel* model, int num_envs, int device, uint64_t seed,
 #undef CKC
   const char* lv = getenv("FLYB_SMEM_LEVEL");
   if (lv) h->smem_level = atoi(lv);
+  { const char* e = getenv("FLYB_NO_SPEC"); if (e) h->no_spec = atoi(e); }
   const char* wp = getenv("FLYB_WARPS");
   if (wp) h->warps = atoi(wp);
   *out = h;
@@ -302,6 +285,7 @@ int64_t flyb_info(flyb_handle h, int what) {
     case FLYB_INFO_STATE_INTS: return FLY_SI_COUNT;
     case FLYB_INFO_WARPS_PER_BLOCK: return h->warps;
     case FLYB_INFO_SMEM_LEVEL: return h->smem_level;
+    case FLYB_INFO_SPEC_KERNEL: return h->spec;
   }
   return -1;
 }
@@ -314,6 +298,8 @@ int flyb_configure(flyb_handle h, int smem_level, int warps_per_block, int block
   h->smem_level = smem_level; h->warps = warps_per_block; h->blocks_per_sm = blocks_per_sm;
   return 0;
 }
+
+int flyb_use_generic_kernel(flyb_handle h, int generic) { h->no_spec = generic != 0; return 0; }
 
 int flyb_load_clips(flyb_handle h, const float* rows, const int32_t* offsets, const int32_t* lengths, int n_clips) {
   CK(cudaSetDevice(h->device));

@@ -21,22 +21,49 @@ FLAG_NOCONTACT, FLAG_NOLIMIT, FLAG_NOFLUID, FLAG_NONOSLIP, FLAG_NOACTUATION, FLA
 FLAG_TRACE = 1 << 16
 (INFO_NUM_ENVS, INFO_OBS_DIM, INFO_ACTION_DIM, INFO_NQ, INFO_NV, INFO_NA, INFO_TRACE_INTS, INFO_TRACE_REALS,
  INFO_LAUNCHES, INFO_SMEM_BYTES, INFO_BULK_BYTES, INFO_GRID, INFO_MAXCON, INFO_MAXEFC, INFO_STATE_INTS,
- INFO_WARPS_PER_BLOCK, INFO_SMEM_LEVEL) = range(17)
+ INFO_WARPS_PER_BLOCK, INFO_SMEM_LEVEL, INFO_SPEC_KERNEL) = range(18)
 
 EXPORTS = ["flyb_create", "flyb_destroy", "flyb_last_error", "flyb_info", "flyb_configure", "flyb_load_clips",
            "flyb_set_clip_ids", "flyb_reset", "flyb_step", "flyb_reset_host", "flyb_step_host", "flyb_get_state",
-           "flyb_set_state", "flyb_get_trace", "flyb_episode_stats", "flyb_load_wbpg", "flyb_set_wbpg_phase"]
+           "flyb_set_state", "flyb_get_trace", "flyb_episode_stats", "flyb_load_wbpg", "flyb_set_wbpg_phase",
+           "flyb_use_generic_kernel"]
+
+
+KERNEL_CONFIGS = [(16, 1), (14, 1), (12, 1), (8, 2), (6, 3)]   # generic kernels (csrc/fly_kernel.cuh: FLY_KERNEL_CONFIGS)
+N_SPEC_MODELS = 4                                                # csrc/fly_dims_gen.h: FLY_SPEC_COUNT
+
+
+def compile_library(out_path: str, extra_flags=(), verbose: bool = False) -> str:
+    """nvcc (sm_100a, -lineinfo): flyb_cuda.cu plus one translation unit per step-kernel instantiation (flyb_kern.cu), the
+    compiles running in parallel, linked into `out_path`."""
+    import tempfile
+    from concurrent.futures import ThreadPoolExecutor
+    flags = [f for f in NVCC_FLAGS if f != "-shared"] + list(extra_flags) + (["-Xptxas", "-v"] if verbose else [])
+    units = [("flyb_cuda", "flyb_cuda.cu", [])]
+    for w, l in KERNEL_CONFIGS:
+        units.append((f"k_{w}_{l}_g", "flyb_kern.cu", [f"-DFLY_TU_WARPS={w}", f"-DFLY_TU_LEVEL={l}", "-DFLY_TU_SPEC=-1",
+                                                         f"-DFLY_TU_NAME=flyb_kernel_{w}_{l}_g"]))
+    for i in range(N_SPEC_MODELS):
+        units.append((f"k_16_1_s{i}", "flyb_kern.cu", ["-DFLY_TU_WARPS=16", "-DFLY_TU_LEVEL=1", f"-DFLY_TU_SPEC={i}",
+                                                        f"-DFLY_TU_NAME=flyb_kernel_16_1_s{i}"]))
+    with tempfile.TemporaryDirectory() as tmp:
+        def one(u):
+            obj = os.path.join(tmp, u[0] + ".o")
+            subprocess.check_call(["nvcc"] + flags + u[2] + ["-c", "-o", obj, os.path.join(CSRC, u[1])])
+            return obj
+        with ThreadPoolExecutor(max_workers=max(1, min(len(units), os.cpu_count() or 1))) as ex:
+            objs = list(ex.map(one, units))
+        subprocess.check_call(["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", out_path] + objs)
+    return out_path
 
 
 def build_library(force: bool = False, verbose: bool = False) -> str:
-    """nvcc-compiles flybody_b200/csrc/flyb_cuda.cu for sm_100a into flybody_b200/libflyb.so (in-tree)."""
+    """Builds flybody_b200/libflyb.so (in-tree) when a source is newer than it."""
     srcs = [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC))] + [os.path.join(_DIR, "..", "include", f) for f in ("flyb.h", "flyb_model.h")]
     newest = max(os.path.getmtime(s) for s in srcs)
     if not force and os.path.exists(LIB_PATH) and os.path.getmtime(LIB_PATH) >= newest:
         return LIB_PATH
-    cmd = ["nvcc"] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB_PATH, os.path.join(CSRC, "flyb_cuda.cu")]
-    subprocess.check_call(cmd)
-    return LIB_PATH
+    return compile_library(LIB_PATH, verbose=verbose)
 
 
 _lib = None
@@ -59,6 +86,7 @@ def lib():
         L.flyb_info.argtypes = [vp, c_i]
         L.flyb_info.restype = ctypes.c_int64
         L.flyb_configure.argtypes = [vp, c_i, c_i, c_i]
+        L.flyb_use_generic_kernel.argtypes = [vp, c_i]
         L.flyb_load_clips.argtypes = [vp, fp, ip, ip, c_i]
         L.flyb_set_clip_ids.argtypes = [vp, ip]
         # device-pointer entry points take raw addresses (torch tensor.data_ptr()) and a raw cudaStream_t
@@ -116,6 +144,9 @@ class Engine:
 
     def configure(self, smem_level: int, warps_per_block: int, blocks_per_sm: int = 0):
         self._ck(lib().flyb_configure(self._h, smem_level, warps_per_block, blocks_per_sm))
+
+    def use_generic_kernel(self, generic: bool = True):
+        self._ck(lib().flyb_use_generic_kernel(self._h, int(generic)))
 
     def load_clips(self, rows, offsets, lengths):
         rows = np.ascontiguousarray(rows, np.float32)

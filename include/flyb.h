@@ -43,7 +43,8 @@ enum { FLYB_FLAG_NOCONTACT = 1, FLYB_FLAG_NOLIMIT = 2, FLYB_FLAG_NOFLUID = 4, FL
 enum { FLYB_INFO_NUM_ENVS = 0, FLYB_INFO_OBS_DIM, FLYB_INFO_ACTION_DIM, FLYB_INFO_NQ, FLYB_INFO_NV, FLYB_INFO_NA,
        FLYB_INFO_TRACE_INTS, FLYB_INFO_TRACE_REALS, FLYB_INFO_LAUNCHES, FLYB_INFO_SMEM_BYTES, FLYB_INFO_BULK_BYTES,
        FLYB_INFO_GRID, FLYB_INFO_MAXCON, FLYB_INFO_MAXEFC, FLYB_INFO_STATE_INTS, FLYB_INFO_WARPS_PER_BLOCK,
-       FLYB_INFO_SMEM_LEVEL };
+       FLYB_INFO_SMEM_LEVEL,
+       FLYB_INFO_SPEC_KERNEL /* after a launch: index of the model-specialised step kernel in use, -1 = generic */ };
 
 /* Compiles `model` for the device and allocates state for num_envs environments on CUDA device `device`.
  * env_offset is the global index of this shard's first env (multi-GPU: rank * num_envs); it only enters the
@@ -57,6 +58,10 @@ int64_t flyb_info(flyb_handle h, int what);
 /* Tuning knobs: smem_level 0..4 (how many workspace tiers live in shared memory) and warps per block; only the pairs
  * blocks per SM (0 = as many as fit).  Takes effect at the next launch. */
 int flyb_configure(flyb_handle h, int smem_level, int warps_per_block, int blocks_per_sm);
+/* The default configuration runs a step kernel compiled for the model's array sizes when the model is one of the shipped task
+ * models (workspace offsets are immediates: 25 % faster); generic != 0 forces the any-model kernel.  The two agree to float32
+ * rounding, not bit for bit (the compiler contracts multiply-adds differently in the two instantiations). */
+int flyb_use_generic_kernel(flyb_handle h, int generic);
 
 /* Reference clips (host pointers): rows of clip_width floats, [qpos 7+nj | qvel 6+nj | root2site 3ns | joint_quat 4nj]
  * (walk_imitation) or [qpos 7 | qvel 6] (flight_imitation); clip c occupies rows offsets[c] .. offsets[c]+lengths[c]-1. */

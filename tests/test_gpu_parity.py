@@ -137,23 +137,33 @@ def test_auto_reset_nan_actions_and_masked_reset(models, walk_clip):
 
 
 def test_results_do_not_depend_on_launch_configuration_or_batch_size(models, walk_clip):
+    """The generic kernel gives the same bits whatever the launch configuration and batch size.  The default configuration
+    runs the kernel compiled for this model's sizes (compile-time workspace layout): same algorithm, other multiply-add
+    contractions, so it agrees to float32 rounding only - and must be the one selected for a shipped model."""
+    from flybody_b200.engine import INFO_SPEC_KERNEL
     M = models["walk_imitation"]
     rng = np.random.RandomState(2)
     acts = rng.uniform(M["action_min"], M["action_max"], (3, 300, 59)).astype(np.float32)
     outs = []
-    for (N, lvl, warps) in ((300, 2, 8), (300, 1, 16), (300, 3, 6), (37, 1, 14)):
+    for (N, lvl, warps, generic) in ((300, 2, 8, 1), (300, 1, 16, 1), (300, 3, 6, 1), (37, 1, 14, 1), (300, 1, 16, 0), (41, 1, 16, 0)):
         eng = _engine(M, N)
         eng.configure(lvl, warps)
+        eng.use_generic_kernel(bool(generic))
         eng.load_clips(*walk_clip)
         eng.set_clip_ids(np.zeros(N, np.int32))
         eng.reset_host()
         for k in range(3):
             st, r, g, obs = eng.step_host(acts[k, :N])
+        assert (eng.info(INFO_SPEC_KERNEL) >= 0) == (not generic)
         outs.append((obs.copy(), r.copy()))
         eng.close()
-    for o, r in outs[1:]:
+    for o, r in outs[1:4]:
         n = o.shape[0]
         assert (o == outs[0][0][:n]).all() and (r == outs[0][1][:n]).all()
+    so, sr = outs[4]
+    assert (outs[5][0] == so[:41]).all() and (outs[5][1] == sr[:41]).all()      # specialised kernel: batch-size independent
+    scale = np.abs(outs[0][0]).max(axis=0) + 1e-6
+    assert (np.abs(so - outs[0][0]) / scale).max() < 2e-5 and np.abs(sr - outs[0][1]).max() < 2e-5 * 20
 
 
 def test_fly_envs_api_and_large_batch_properties(models):

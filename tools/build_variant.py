@@ -1,4 +1,4 @@
-"""Kernel experiments: build flybody_b200/_exp/libflyb_<name>.so with extra -D flags (default (16,1) config only).
+"""Kernel experiments: build flybody_b200/_exp/libflyb_<name>.so with extra -D flags (all kernel configurations, compiled in parallel).
    usage: python tools/build_variant.py <name> [-DFLAG ...]   ; run with FLYB_LIB_PATH=<that file>"""
 import os, subprocess, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -7,6 +7,4 @@ from flybody_b200 import engine as E
 name, flags = sys.argv[1], sys.argv[2:]
 out = os.path.join(os.path.dirname(E.LIB_PATH), "_exp", f"libflyb_{name}.so")
 os.makedirs(os.path.dirname(out), exist_ok=True)
-cmd = ["nvcc"] + E.NVCC_FLAGS + ["-DFLY_SINGLE_CONFIG"] + flags + ["-o", out, os.path.join(E.CSRC, "flyb_cuda.cu")]
-subprocess.check_call(cmd)
-print(out)
+print(E.compile_library(out, extra_flags=flags))
