@@ -464,13 +464,18 @@ FLY_FN void fly_collision(const DModel<T>& m, const Ws<T>& w) {
     FLY_SYNC();
     return;
   }
-  /* broad phase: bounding spheres (cannot change the result: the narrow phase only reports dist <= margin) */
+  /* broad phase: bounding spheres (cannot change the result: the narrow phase only reports dist <= margin).  The geom
+     centres are staged in the warp's scratch (qLD | qH, free until fly_crb) so that the 2 x npair position reads are
+     shared-memory loads; bit 16 of the pair word says "geom 1 is a plane" (no geom_type lookup on the way) */
+  T* gx = (T*)w.qLD;
+  FLY_FOR(i, 3 * m.ngeom) gx[i] = w.geom_xpos[i];
+  FLY_SYNC();
   int ncand = warp_compact(m.npair, [&](int p) -> bool {
-    const int pg = FLY_LDG(m.pair_geom + p), g1 = pg & 255, g2 = pg >> 8;
-    const T *c1 = w.geom_xpos + 3 * g1, *c2 = w.geom_xpos + 3 * g2;
-    const T d[3] = {c2[0] - c1[0], c2[1] - c1[1], c2[2] - c1[2]};
+    const int pg = FLY_LDG(m.pair_geom + p), g1 = pg & 255, g2 = (pg >> 8) & 255;
     const T bound = FLY_LDG(m.pair_bound + p);
-    if (m.geom_type[g1] == FLYB_GEOM_PLANE) {
+    const T *c1 = gx + 3 * g1, *c2 = gx + 3 * g2;
+    const T d[3] = {c2[0] - c1[0], c2[1] - c1[1], c2[2] - c1[2]};
+    if (pg >> 16) {
       T mat[9];
       fly_geom_xmat(m, w, g1, mat);
       return !(d[0] * mat[2] + d[1] * mat[5] + d[2] * mat[8] > bound);
@@ -485,7 +490,7 @@ FLY_FN void fly_collision(const DModel<T>& m, const Ws<T>& w) {
      float64 search (cannot change the result); the list is compacted in place, order kept. */
   ncand = warp_filter(ncand, [&](int i) -> bool {
     const int p = w.cand[i];
-    const int pg = m.pair_geom[p], g1 = pg & 255, g2 = pg >> 8;
+    const int pg = m.pair_geom[p], g1 = pg & 255, g2 = (pg >> 8) & 255;
     const int t1 = m.geom_type[g1], t2 = m.geom_type[g2];
     if (!fly_pair_is_convex(t1, t2)) return true;
     T m1[9], m2[9], dir[3], nd[3], p1[3], p2[3];
@@ -508,7 +513,7 @@ FLY_FN void fly_collision(const DModel<T>& m, const Ws<T>& w) {
     const int nround = ncand - base < 32 ? ncand - base : 32;
     FLY_FOR(l, nround) {
       const int p = w.cand[base + l];
-      const int pg = m.pair_geom[p], g1 = pg & 255, g2 = pg >> 8;
+      const int pg = m.pair_geom[p], g1 = pg & 255, g2 = (pg >> 8) & 255;
       const int t1 = m.geom_type[g1], t2 = m.geom_type[g2];
       const T *c1 = w.geom_xpos + 3 * g1, *c2 = w.geom_xpos + 3 * g2;
       const T *s1 = m.geom_size + 3 * g1, *s2 = m.geom_size + 3 * g2;

@@ -94,7 +94,7 @@ FLY_FN void fly_make_constraint(const DModel<T>& m, const Ws<T>& w) {
       const int dim = w.con_dim[ci];
       if (r + dim > FLY_MAXEFC || ngrp >= FLY_MAXGRP) { w.counts[FLY_C_OVERFLOW] |= 8; break; }
       const int pg = m.pair_geom[w.con_pair[ci]];
-      const int b1 = m.geom_bodyid[pg & 255], b2 = m.geom_bodyid[pg >> 8];
+      const int b1 = m.geom_bodyid[pg & 255], b2 = m.geom_bodyid[(pg >> 8) & 255];
       const int s1 = b1 > 0 ? m.body_lastdof[b1] : -1, s2 = b2 > 0 ? m.body_lastdof[b2] : -1;
       const bool cross = s1 >= 0 && s2 >= 0 && !fly_is_anc(m, s1, s2) && !fly_is_anc(m, s2, s1);
       if (cross && nx + dim > FLY_MAXCROSS) { w.counts[FLY_C_OVERFLOW] |= 16; continue; }
@@ -120,7 +120,7 @@ FLY_FN void fly_make_constraint(const DModel<T>& m, const Ws<T>& w) {
     if (k < dim) {
       const int r = w.grp_row[g] + k;
       const int pg = m.pair_geom[w.con_pair[ci]];
-      const int b1 = m.geom_bodyid[pg & 255], b2 = m.geom_bodyid[pg >> 8];
+      const int b1 = m.geom_bodyid[pg & 255], b2 = m.geom_bodyid[(pg >> 8) & 255];
       const T *pos = w.con_pos + 3 * ci, *dir = w.con_frame + 9 * ci + 3 * k;
       T* J = w.efc_J + r * FLY_MAXCHAIN;
       const int s1 = b1 > 0 ? m.body_lastdof[b1] : -1, s2 = b2 > 0 ? m.body_lastdof[b2] : -1;
@@ -260,14 +260,14 @@ FLY_FN void fly_actuation(const DModel<T>& m, const Ws<T>& w) {
     int cnt = 0;
     FLY_FOR(ci, ncon) {
       const int pg = m.pair_geom[w.con_pair[ci]];
-      if (m.geom_bodyid[pg & 255] == id || m.geom_bodyid[pg >> 8] == id) cnt++;
+      if (m.geom_bodyid[pg & 255] == id || m.geom_bodyid[(pg >> 8) & 255] == id) cnt++;
     }
     cnt = warp_sum_i(cnt);
     if (!cnt || f == 0) continue;
     const T coef = -gear * f / T(cnt);
     for (int ci = 0; ci < ncon; ci++) {
       const int pg = m.pair_geom[w.con_pair[ci]];
-      const int b1 = m.geom_bodyid[pg & 255], b2 = m.geom_bodyid[pg >> 8];
+      const int b1 = m.geom_bodyid[pg & 255], b2 = m.geom_bodyid[(pg >> 8) & 255];
       if (b1 != id && b2 != id) continue;
       const T *pos = w.con_pos + 3 * ci, *dir = w.con_frame + 9 * ci;
       for (int side = 0; side < 2; side++) {

@@ -61,17 +61,22 @@ FLY_INL void warp_argmin(double& v, int& i) {
     if (ov < v || (ov == v && oi < i)) { v = ov; i = oi; }
   }
 }
-/* ordered stream compaction of the items i in [0,n) with pred(i): writes their indices to out[], in order */
+/* ordered stream compaction of the items i in [0,n) with pred(i): writes their indices to out[], in order.  Four batches
+ * of 32 items are evaluated before their ballots, so that the loads of four independent predicates are in flight together */
 template <class P> FLY_INL int warp_compact(int n, P pred, unsigned short* out, int maxout) {
   int cnt = 0;
   const int lane = FLY_LANE();
-  for (int base = 0; base < n; base += 32) {
-    int i = base + lane;
-    bool p = i < n && pred(i);
-    unsigned mask = __ballot_sync(0xffffffffu, p);
-    int pos = cnt + __popc(mask & ((1u << lane) - 1u));
-    if (p && pos < maxout) out[pos] = (unsigned short)i;
-    cnt += __popc(mask);
+  for (int base = 0; base < n; base += 128) {
+    bool p[4];
+#pragma unroll
+    for (int u = 0; u < 4; u++) { const int i = base + 32 * u + lane; p[u] = i < n && pred(i); }
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      const unsigned mask = __ballot_sync(0xffffffffu, p[u]);
+      const int pos = cnt + __popc(mask & ((1u << lane) - 1u));
+      if (p[u] && pos < maxout) out[pos] = (unsigned short)(base + 32 * u + lane);
+      cnt += __popc(mask);
+    }
   }
   __syncwarp();
   return cnt;

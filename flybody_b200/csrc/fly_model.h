@@ -326,7 +326,7 @@ std::string build_dmodel(const FlybModel* m, int flags, DModel<T>* out, FlyArena
   std::vector<double> pair_bound(m->npair), geom_mat(9 * (size_t)m->ngeom), site_mat(9 * (size_t)m->nsite);
   for (int p = 0; p < m->npair; p++) {
     int g1 = m->pair_geom1[p], g2 = m->pair_geom2[p];
-    pair_geom[p] = g1 | (g2 << 8);
+    pair_geom[p] = g1 | (g2 << 8) | (m->geom_type[g1] == FLYB_GEOM_PLANE ? 1 << 16 : 0);  /* bit 16: geom 1 is a plane */
     if (m->geom_type[g2] == FLYB_GEOM_PLANE) return "plane must be geom1 of a pair";
     pair_bound[p] = (m->geom_type[g1] == FLYB_GEOM_PLANE ? 0.0 : m->geom_rbound[g1]) + m->geom_rbound[g2] + m->pair_margin[p];
   }

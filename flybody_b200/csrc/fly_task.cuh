@@ -71,7 +71,7 @@ FLY_FN void fly_sensors_acc(const DModel<T>& m, const Ws<T>& w) {
       for (int k = 0; k < dim; k++) for (int a = 0; a < 3; a++) fw[a] += w.con_frame[9 * ci + 3 * k + a] * w.efc_force[ea + k];
       FLY_FOR(it, 12) {
         const int side = it / 6, c = it % 6;
-        const int b = side ? m.geom_bodyid[pg >> 8] : m.geom_bodyid[pg & 255];
+        const int b = side ? m.geom_bodyid[(pg >> 8) & 255] : m.geom_bodyid[pg & 255];
         if (b > 0) {
           const T sg = side ? T(1) : T(-1);
           const T* c0 = w.scom + 3 * m.body_rootid[b];
@@ -107,7 +107,7 @@ FLY_FN void fly_sensors_acc(const DModel<T>& m, const Ws<T>& w) {
         const int ea = w.con_efc[ci];
         if (ea < 0) continue;
         const int pg = m.pair_geom[w.con_pair[ci]];
-        const int b1 = m.geom_bodyid[pg & 255], b2 = m.geom_bodyid[pg >> 8];
+        const int b1 = m.geom_bodyid[pg & 255], b2 = m.geom_bodyid[(pg >> 8) & 255];
         if (b1 != b && b2 != b) continue;
         const T fn = w.efc_force[ea];
         if (fn <= 0) continue;

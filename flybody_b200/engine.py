@@ -48,8 +48,11 @@ def compile_library(out_path: str, extra_flags=(), verbose: bool = False) -> str
                                                         f"-DFLY_TU_NAME=flyb_kernel_16_1_s{i}"]))
     with tempfile.TemporaryDirectory() as tmp:
         def one(u):
-            obj = os.path.join(tmp, u[0] + ".o")
-            subprocess.check_call(["nvcc"] + flags + u[2] + ["-c", "-o", obj, os.path.join(CSRC, u[1])])
+            # a stub source per unit so that every embedded cubin has a name of its own (cuobjdump -xelf, ncu tooling)
+            src, obj = os.path.join(tmp, u[0] + ".cu"), os.path.join(tmp, u[0] + ".o")
+            with open(src, "w") as f:
+                f.write('#include "%s"\n' % os.path.join(CSRC, u[1]))
+            subprocess.check_call(["nvcc"] + flags + u[2] + ["-I", CSRC, "-c", "-o", obj, src])
             return obj
         with ThreadPoolExecutor(max_workers=max(1, min(len(units), os.cpu_count() or 1))) as ex:
             objs = list(ex.map(one, units))

@@ -10,8 +10,12 @@ rep = sys.argv[1]
 kname = sys.argv[2] if len(sys.argv) > 2 else "fly_step_kernelILi16ELi1E"
 tmp = tempfile.mkdtemp()
 subprocess.check_call(["cuobjdump", "-xelf", "all", os.path.join(ROOT, "flybody_b200", "libflyb.so")], cwd=tmp, stdout=subprocess.DEVNULL)
-cubin = [f for f in os.listdir(tmp) if f.endswith(".cubin")][0]
-dis = subprocess.run(["nvdisasm", "--print-line-info-inline", cubin], cwd=tmp, capture_output=True, text=True).stdout.splitlines()
+dis = []   # every kernel instantiation sits in a cubin of its own: take the one that holds the kernel asked for
+for cubin in sorted(f for f in os.listdir(tmp) if f.endswith(".cubin")):
+    syms = subprocess.run(["cuobjdump", "-elf", cubin], cwd=tmp, capture_output=True, text=True).stdout
+    if kname in syms:
+        dis = subprocess.run(["nvdisasm", "--print-line-info-inline", cubin], cwd=tmp, capture_output=True, text=True).stdout.splitlines()
+        break
 addr2line, inside, cur = {}, False, None
 for ln in dis:
     if ln.startswith(".text."):
