@@ -395,21 +395,32 @@ int flyb_reset_host(flyb_handle h, const uint8_t* mask, float* obs, int32_t* ste
   return 0;
 }
 
+/* page-locked host memory (cudaHostAlloc / cudaHostRegister, e.g. a pinned torch tensor) can be the DMA target itself */
+static bool is_pinned(const void* p) {
+  cudaPointerAttributes at;
+  if (!p || cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return false; }
+  return at.type == cudaMemoryTypeHost;
+}
+
 int flyb_step_host(flyb_handle h, const float* action, float* obs, float* reward, float* discount, int32_t* step_type) {
   CK(cudaSetDevice(h->device));
-  const size_t N = h->num_envs;
+  const size_t N = h->num_envs, A = h->m.action_dim, O = h->m.obs_dim;
   cudaStream_t s = h->host_stream;
-  memcpy(h->h_action, action, N * h->m.action_dim * sizeof(float));
-  CK(cudaMemcpyAsync(h->d_action, h->h_action, N * h->m.action_dim * sizeof(float), cudaMemcpyHostToDevice, s));
+  /* pageable caller buffers go through the library's pinned staging buffers (one extra host copy each way); page-locked
+     ones are copied to and from directly */
+  const bool pa = is_pinned(action), po = is_pinned(obs), pr = is_pinned(reward), pd = is_pinned(discount), ps = is_pinned(step_type);
+  if (!pa) memcpy(h->h_action, action, N * A * sizeof(float));
+  CK(cudaMemcpyAsync(h->d_action, pa ? action : h->h_action, N * A * sizeof(float), cudaMemcpyHostToDevice, s));
   if (flyb_step(h, h->d_action, h->d_obs, h->d_rd, h->d_rd + N, h->d_st, s)) return 1;
-  CK(cudaMemcpyAsync(h->h_obs, h->d_obs, N * h->m.obs_dim * sizeof(float), cudaMemcpyDeviceToHost, s));
-  CK(cudaMemcpyAsync(h->h_rd, h->d_rd, 2 * N * sizeof(float), cudaMemcpyDeviceToHost, s));
-  CK(cudaMemcpyAsync(h->h_st, h->d_st, N * sizeof(int), cudaMemcpyDeviceToHost, s));
+  if (obs) CK(cudaMemcpyAsync(po ? obs : h->h_obs, h->d_obs, N * O * sizeof(float), cudaMemcpyDeviceToHost, s));
+  if (reward) CK(cudaMemcpyAsync(pr ? reward : h->h_rd, h->d_rd, N * sizeof(float), cudaMemcpyDeviceToHost, s));
+  if (discount) CK(cudaMemcpyAsync(pd ? discount : h->h_rd + N, h->d_rd + N, N * sizeof(float), cudaMemcpyDeviceToHost, s));
+  if (step_type) CK(cudaMemcpyAsync(ps ? step_type : h->h_st, h->d_st, N * sizeof(int), cudaMemcpyDeviceToHost, s));
   CK(cudaStreamSynchronize(s));
-  if (obs) memcpy(obs, h->h_obs, N * h->m.obs_dim * sizeof(float));
-  if (reward) memcpy(reward, h->h_rd, N * sizeof(float));
-  if (discount) memcpy(discount, h->h_rd + N, N * sizeof(float));
-  if (step_type) memcpy(step_type, h->h_st, N * sizeof(int));
+  if (obs && !po) memcpy(obs, h->h_obs, N * O * sizeof(float));
+  if (reward && !pr) memcpy(reward, h->h_rd, N * sizeof(float));
+  if (discount && !pd) memcpy(discount, h->h_rd + N, N * sizeof(float));
+  if (step_type && !ps) memcpy(step_type, h->h_st, N * sizeof(int));
   return 0;
 }
 

@@ -89,6 +89,7 @@ int flyb_step(flyb_handle h, const float* action, float* obs, float* reward, flo
 
 /* Host-pointer API (what a numpy caller uses): copies through pinned staging buffers, synchronises. */
 int flyb_reset_host(flyb_handle h, const uint8_t* mask, float* obs, int32_t* step_type);
+/* Host-pointer variants: page-locked caller buffers are DMA targets themselves, pageable ones are staged. */
 int flyb_step_host(flyb_handle h, const float* action, float* obs, float* reward, float* discount, int32_t* step_type);
 
 /* State access (host pointers, any may be NULL).  qpos [N,nq] qvel [N,nv] act [N,na] qacc_warmstart [N,nv]

@@ -304,3 +304,31 @@ def test_sharded_engines_reproduce_the_unsharded_batch(models):
             assert (np.concatenate([a[k], b[k]]) == full[k]).all(), (task, k)
         assert (np.concatenate([ai, bi])[:, 3] == fi[:, 3]).all()          # FLY_SI_CLIP: same clip per global env
         assert len(set(fi[:, 3].tolist())) > 1                              # and not all the same clip
+
+
+def test_host_call_with_page_locked_buffers_matches_pageable(models, walk_clip):
+    """flyb_step_host copies straight to and from page-locked caller memory and stages pageable memory: same results."""
+    import torch
+    M = models["walk_imitation"]
+    N = 33
+    rng = np.random.RandomState(9)
+    acts = rng.uniform(M["action_min"], M["action_max"], (4, N, 59)).astype(np.float32)
+    res = []
+    for pinned in (False, True):
+        eng = _engine(M, N)
+        eng.load_clips(*walk_clip)
+        eng.set_clip_ids(np.zeros(N, np.int32))
+        eng.reset_host()
+        if pinned:
+            keep = (torch.zeros((N, eng.obs_dim)).pin_memory(), torch.zeros(N).pin_memory(), torch.zeros(N).pin_memory(),
+                    torch.zeros(N, dtype=torch.int32).pin_memory(), torch.zeros((N, 59)).pin_memory())
+            out, a_buf = tuple(t.numpy() for t in keep[:4]), keep[4].numpy()
+        else:
+            out, a_buf = None, np.zeros((N, 59), np.float32)
+        for k in range(4):
+            a_buf[:] = acts[k]
+            st, r, g, obs = eng.step_host(a_buf, out)
+        res.append((obs.copy(), r.copy(), g.copy(), st.copy()))
+        eng.close()
+    for x, y in zip(*res):
+        assert (x == y).all()
