@@ -468,7 +468,7 @@ FLY_FN void fly_collision(const DModel<T>& m, const Ws<T>& w) {
      centres are staged in the warp's scratch (qLD | qH, free until fly_crb) so that the 2 x npair position reads are
      shared-memory loads; bit 16 of the pair word says "geom 1 is a plane" (no geom_type lookup on the way) */
   T* gx = (T*)w.qLD;
-  FLY_FOR(i, 3 * m.ngeom) gx[i] = w.geom_xpos[i];
+  FLY_FOR(i, 3 * FLY_DIM(m, ngeom)) gx[i] = w.geom_xpos[i];
   FLY_SYNC();
   int ncand = warp_compact(m.npair, [&](int p) -> bool {
     const int pg = FLY_LDG(m.pair_geom + p), g1 = pg & 255, g2 = (pg >> 8) & 255;

@@ -64,7 +64,7 @@ FLY_FN void fly_make_constraint(const DModel<T>& m, const Ws<T>& w) {
   /* joint limits: item 2j + side, lower side first; ordered compaction keeps the oracle's row order */
   int nlimit = 0;
   if (!(m.flags & FLY_OPT_NOLIMIT)) {
-    nlimit = warp_compact(2 * m.njnt, [&](int it) -> bool {
+    nlimit = warp_compact(2 * FLY_DIM(m, njnt), [&](int it) -> bool {
       const int j = it >> 1, side = (it & 1) ? 1 : -1;
       if (!m.jnt_limited[j] || m.jnt_type[j] != FLYB_JNT_HINGE) return false;
       return side * (m.jnt_range[2 * j + (it & 1)] - w.qpos[m.jnt_qposadr[j]]) < 0;
@@ -192,7 +192,7 @@ FLY_INL void fly_j_mul(const DModel<T>& m, const Ws<T>& w, T* out, const T* v) {
 template <class T>
 FLY_FN void fly_jt_mul(const DModel<T>& m, const Ws<T>& w, T* out, const T* f) {
   const int nefc = w.counts[FLY_C_NEFC], nlimit = w.counts[FLY_C_NLIMIT];
-  FLY_FOR(d, m.nv) out[d] = 0;
+  FLY_FOR(d, FLY_DIM(m, nv)) out[d] = 0;
   FLY_SYNC();
   FLY_FOR(r, nlimit) out[w.efc_start[r]] += w.efc_J[r * FLY_MAXCHAIN] * f[r];
   FLY_SYNC();
@@ -214,7 +214,7 @@ FLY_FN void fly_jt_mul(const DModel<T>& m, const Ws<T>& w, T* out, const T* f) {
 /* ---------------------------------------------------------------- m3 + m9 transmission and actuation */
 template <class T>
 FLY_FN void fly_actuation(const DModel<T>& m, const Ws<T>& w) {
-  FLY_FOR(a, m.nu) {
+  FLY_FOR(a, FLY_DIM(m, nu)) {
     const int id = m.act_trnid[a], trn = m.act_trntype[a];
     const T gear = m.act_gear[a];
     T len = 0, vel = 0;
@@ -240,13 +240,13 @@ FLY_FN void fly_actuation(const DModel<T>& m, const Ws<T>& w) {
     if (m.flags & FLY_OPT_NOACTUATION) f = 0;
     w.act_force[a] = f;
   }
-  FLY_FOR(d, m.nv) w.qfrc_actuator[d] = 0;
+  FLY_FOR(d, FLY_DIM(m, nv)) w.qfrc_actuator[d] = 0;
   FLY_SYNC();
-  FLY_FOR(a, m.nu)
+  FLY_FOR(a, FLY_DIM(m, nu))
     if (m.act_trntype[a] == FLYB_TRN_JOINT) w.qfrc_actuator[m.jnt_dofadr[m.act_trnid[a]]] += m.act_gear[a] * w.act_force[a];
   FLY_SYNC();
   const int ncon = w.counts[FLY_C_NCON];
-  for (int a = 0; a < m.nu; a++) {
+  for (int a = 0; a < FLY_DIM(m, nu); a++) {
     const int trn = m.act_trntype[a], id = m.act_trnid[a];
     if (trn == FLYB_TRN_JOINT) continue;
     const T f = w.act_force[a], gear = m.act_gear[a];

@@ -64,13 +64,13 @@ FLY_FN void fly_kinematics(const DModel<T>& m, const Ws<T>& w) {
     }
     FLY_SYNC();
   }
-  FLY_FOR(g, m.ngeom) {
+  FLY_FOR(g, FLY_DIM(m, ngeom)) {
     const int b = m.geom_bodyid[g];
     T t[3];
     mat_vec(t, w.xmat + 9 * b, m.geom_pos + 3 * g);
     for (int c = 0; c < 3; c++) w.geom_xpos[3 * g + c] = w.xpos[3 * b + c] + t[c];
   }
-  FLY_FOR(s, m.nsite) {
+  FLY_FOR(s, FLY_DIM(m, nsite)) {
     const int b = m.site_bodyid[s];
     T t[3];
     mat_vec(t, w.xmat + 9 * b, m.site_pos + 3 * s);
@@ -107,16 +107,16 @@ FLY_INL void fly_tree_upsweep(const DModel<T>& m, T* acc, int K) {
 /* ---------------------------------------------------------------- m2 comPos */
 template <class T>
 FLY_FN void fly_com_pos(const DModel<T>& m, const Ws<T>& w) {
-  FLY_FOR(it, 3 * m.nbody) w.scom[it] = m.body_mass[it / 3] * w.xipos[it];
+  FLY_FOR(it, 3 * FLY_DIM(m, nbody)) w.scom[it] = m.body_mass[it / 3] * w.xipos[it];
   FLY_SYNC();
   fly_tree_upsweep(m, w.scom, 3);
-  FLY_FOR(it, 3 * m.nbody) {
+  FLY_FOR(it, 3 * FLY_DIM(m, nbody)) {
     const int b = it / 3;
     const T sm = m.body_subtreemass[b];
     w.scom[it] = sm < minval<T>() ? w.xipos[it] : w.scom[it] / sm;
   }
   FLY_SYNC();
-  FLY_FOR(bb, m.nbody - 1) {
+  FLY_FOR(bb, FLY_DIM(m, nbody) - 1) {
     const int b = bb + 1;
     T iq[4], R[9];  /* inertial frame orientation (ximat), rebuilt here instead of being stored by the kinematics */
     quat_mul(iq, w.xquat + 4 * b, m.body_iquat + 4 * b);
@@ -137,7 +137,7 @@ FLY_FN void fly_com_pos(const DModel<T>& m, const Ws<T>& w) {
     for (int e = 0; e < 6; e++) ci[e] = W[e];
     ci[6] = mass * d[0]; ci[7] = mass * d[1]; ci[8] = mass * d[2]; ci[9] = mass;
   }
-  FLY_FOR(j, m.njnt) {
+  FLY_FOR(j, FLY_DIM(m, njnt)) {
     const int b = m.jnt_bodyid[j];
     int da = m.jnt_dofadr[j];
     const T* c0 = w.scom + 3 * m.body_rootid[b];
@@ -171,14 +171,14 @@ FLY_FN void fly_com_pos(const DModel<T>& m, const Ws<T>& w) {
 /* ---------------------------------------------------------------- m4 CRB -> tree-sparse M */
 template <class T>
 FLY_FN void fly_crb(const DModel<T>& m, const Ws<T>& w) {
-  FLY_FOR(it, 10 * m.nbody) w.crb[it] = it < 10 ? T(0) : w.cinert[it];
+  FLY_FOR(it, 10 * FLY_DIM(m, nbody)) w.crb[it] = it < 10 ? T(0) : w.cinert[it];
   FLY_SYNC();
   fly_tree_upsweep(m, w.crb, 10);
   T* f = w.cdof_dot; /* scratch: cdof_dot is rebuilt later, in the velocity stage */
-  FLY_FOR(i, m.nv) inert_vec(f + 6 * i, w.crb + 10 * m.dof_bodyid[i], w.cdof + 6 * i);
+  FLY_FOR(i, FLY_DIM(m, nv)) inert_vec(f + 6 * i, w.crb + 10 * m.dof_bodyid[i], w.cdof + 6 * i);
   FLY_SYNC();
   const T dt = m.timestep;
-  FLY_FOR(e, m.nM) {
+  FLY_FOR(e, FLY_DIM(m, nM)) {
     const int i = m.mrow[e], j = m.mcol[e], k = e - m.madr[i];
     T s = 0;
     if (k <= m.kdepth[i]) {
@@ -293,7 +293,7 @@ FLY_FN void fly_factor(const DModel<T>& m, T* const* LD, T* const* invD) {
     }
     FLY_SYNC();
   }
-  const int nt = m.ntrunk, nb = m.nv - nt;
+  const int nt = m.ntrunk, nb = FLY_DIM(m, nv) - nt;
   if (nt == 0) return;
   FLY_FOR(p, nt * (nt + 1) / 2) {
     const int j = FLY_LDG(m.tri_a + p), i = FLY_LDG(m.tri_b + p);
@@ -366,7 +366,7 @@ FLY_FN void fly_solve(const DModel<T>& m, const Ws<T>& w, const T* const* LD, co
     }
     FLY_SYNC();
   }
-  const int nt = m.ntrunk, nb = m.nv - nt;
+  const int nt = m.ntrunk, nb = FLY_DIM(m, nv) - nt;
   if (nt > 0) {
     T acc[NS][FLY_MAXTRUNK], y[NS][FLY_MAXTRUNK];
 #pragma unroll
@@ -475,14 +475,14 @@ FLY_FN void fly_solve(const DModel<T>& m, const Ws<T>& w, const T* const* LD, co
  * descendants (warp-cooperative for the few dofs with many descendants).  z is an nv scratch vector. */
 template <class T>
 FLY_FN void fly_mul_m(const DModel<T>& m, const T* LD, T* r, const T* v, T* z) {
-  FLY_FOR(i, m.nv) {
+  FLY_FOR(i, FLY_DIM(m, nv)) {
     const int a = m.madr[i], nrow = m.madr[i + 1] - a;
     T s = v[i];
     for (int q = 1; q < nrow; q++) s += LD[a + q] * v[m.mcol[a + q]];
     z[i] = LD[a] * s;
   }
   FLY_SYNC();
-  FLY_FOR(i, m.nv) {
+  FLY_FOR(i, FLY_DIM(m, nv)) {
     T s = z[i];
     if (m.hsublast[i] - i <= FLY_HEAVY)
       for (int q = m.desc_adr[i]; q < m.desc_adr[i + 1]; q++) {
@@ -552,7 +552,7 @@ template <class T> FLY_INL T pow4(T x) { T y = x * x; return y * y; }
 
 template <class T>
 FLY_FN void fly_passive(const DModel<T>& m, const Ws<T>& w) {
-  FLY_FOR(d, m.nv) {
+  FLY_FOR(d, FLY_DIM(m, nv)) {
     T f = -m.dof_damping[d] * w.qvel[d];
     const int j = m.dof_jntid[d];
     if (m.jnt_type[j] == FLYB_JNT_HINGE) {
@@ -564,7 +564,7 @@ FLY_FN void fly_passive(const DModel<T>& m, const Ws<T>& w) {
   FLY_SYNC();
   if (m.flags & FLY_OPT_NOFLUID) return;
   const T rho = m.density, beta = m.viscosity, PI = T(FLY_PI);
-  const int nbox = m.nfluidbox, nel = nbox + m.nfluidgeom;
+  const int nbox = FLY_DIM(m, nfluidbox), nel = nbox + FLY_DIM(m, nfluidgeom);
   /* phase 1: each fluid element -> world-frame spatial force [torque; force] about its tree's CoM */
   FLY_FOR(i, nel) {
     const bool isbox = i < nbox;
@@ -646,16 +646,16 @@ FLY_FN void fly_passive(const DModel<T>& m, const Ws<T>& w) {
   }
   FLY_SYNC();
   /* phase 2: sum per body, then toward the root; qfrc[d] = cdof[d] . F(subtree of d's body) */
-  FLY_FOR(it, 6 * m.nbody) {
+  FLY_FOR(it, 6 * FLY_DIM(m, nbody)) {
     const int b = it / 6, c = it % 6;
     T s = 0;
     for (int q = m.body_fbox_adr[b]; q < m.body_fbox_adr[b + 1]; q++) s += w.boxf[6 * m.body_fbox[q] + c];
-    for (int g = 0; g < m.nfluidgeom; g++) if (m.fgeom_bodyid[g] == b) s += w.boxf[6 * (nbox + g) + c];
+    for (int g = 0; g < FLY_DIM(m, nfluidgeom); g++) if (m.fgeom_bodyid[g] == b) s += w.boxf[6 * (nbox + g) + c];
     w.bodyf[it] = s;
   }
   FLY_SYNC();
   fly_tree_upsweep(m, w.bodyf, 6);
-  FLY_FOR(d, m.nv) {
+  FLY_FOR(d, FLY_DIM(m, nv)) {
     const T *cd = w.cdof + 6 * d, *F = w.bodyf + 6 * m.dof_bodyid[d];
     w.qfrc_passive[d] += cd[0] * F[0] + cd[1] * F[1] + cd[2] * F[2] + cd[3] * F[3] + cd[4] * F[4] + cd[5] * F[5];
   }
@@ -693,7 +693,7 @@ FLY_FN void fly_rne(const DModel<T>& m, const Ws<T>& w, T* result, int flg_acc, 
   }
   fly_tree_upsweep(m, w.cfrc_int, 6);
   if (result) {
-    FLY_FOR(d, m.nv) {
+    FLY_FOR(d, FLY_DIM(m, nv)) {
       const T *cd = w.cdof + 6 * d, *F = w.cfrc_int + 6 * m.dof_bodyid[d];
       result[d] = cd[0] * F[0] + cd[1] * F[1] + cd[2] * F[2] + cd[3] * F[3] + cd[4] * F[4] + cd[5] * F[5];
     }

@@ -92,7 +92,7 @@ FLY_FN void fly_write_obs(const DModel<T>& m, const Ws<T>& w, const FlyClipView&
     if (off[key] >= 0)
       for (int k = 0; k < dim; k++) obs[off[key] + dim * idx + k] = (float)(w.sens_sum[m.sensor_adr[s] + k] * sensor_scale);
   }
-  if (off[FLYB_OBS_ACTUATOR_ACTIVATION] >= 0) FLY_FOR(i, m.na) obs[off[FLYB_OBS_ACTUATOR_ACTIVATION] + i] = (float)w.act[i];
+  if (off[FLYB_OBS_ACTUATOR_ACTIVATION] >= 0) FLY_FOR(i, FLY_DIM(m, na)) obs[off[FLYB_OBS_ACTUATOR_ACTIVATION] + i] = (float)w.act[i];
   if (off[FLYB_OBS_APPENDAGES_POS] >= 0)
     FLY_FOR(i, m.n_appendages) {
       const T* sp = w.site_xpos + 3 * m.appendage_site[i];
@@ -260,7 +260,7 @@ FLY_FN void fly_env_run(const DModel<T>& m, const Ws<T>& w, const FlyClips& clip
   FLY_LANE0 for (int k = 0; k < 16; k++) w.counts[k] = 0;
   const bool do_reset = io.force_reset ? (!io.reset_mask || io.reset_mask[env]) : sint[FLY_SI_RESET_NEXT] != 0;
   if (io.force_reset && !do_reset) { fly_block_pad(fly_nb_control_step(m)); return; }
-  T *s_qpos = sr, *s_qvel = sr + m.nq, *s_act = s_qvel + m.nv, *s_warm = s_act + m.na, *s_ret = s_warm + m.nv;
+  T *s_qpos = sr, *s_qvel = sr + FLY_DIM(m, nq), *s_act = s_qvel + FLY_DIM(m, nv), *s_warm = s_act + FLY_DIM(m, na), *s_ret = s_warm + FLY_DIM(m, nv);
   FLY_SYNC();
   int clip_id, step = 0, episode_steps = m.max_episode_steps;
   const int episode = sint[FLY_SI_EPISODE];
@@ -271,11 +271,11 @@ FLY_FN void fly_env_run(const DModel<T>& m, const Ws<T>& w, const FlyClips& clip
       clip_id = (int)(fly_hash(io.seed ^ fly_hash(((unsigned long long)(io.env_offset + env) << 24) ^ (unsigned long long)episode))
                       % (unsigned long long)clips.nclips);
     clip = fly_clip_view(m, clips, clip_id);
-    FLY_FOR(i, m.nq) w.qpos[i] = m.qpos_reset[i];
-    FLY_FOR(i, m.nv) { w.qvel[i] = 0; w.warm[i] = 0; w.qacc[i] = 0; }
-    FLY_FOR(i, m.na) w.act[i] = 0;
-    FLY_FOR(i, m.nu) w.ctrl[i] = 0;
-    FLY_FOR(i, m.nsensordata) { w.sens_sum[i] = 0; w.sensordata[i] = 0; }
+    FLY_FOR(i, FLY_DIM(m, nq)) w.qpos[i] = m.qpos_reset[i];
+    FLY_FOR(i, FLY_DIM(m, nv)) { w.qvel[i] = 0; w.warm[i] = 0; w.qacc[i] = 0; }
+    FLY_FOR(i, FLY_DIM(m, na)) w.act[i] = 0;
+    FLY_FOR(i, FLY_DIM(m, nu)) w.ctrl[i] = 0;
+    FLY_FOR(i, FLY_DIM(m, nsensordata)) { w.sens_sum[i] = 0; w.sensordata[i] = 0; }
     FLY_SYNC();
     if (m.task_type == FLYB_TASK_WALK_IMITATION && clip.rows) {
       const int snippet = clip.T - m.future_steps - 1;  /* walk_imitation.py:101-102 */
@@ -306,17 +306,17 @@ FLY_FN void fly_env_run(const DModel<T>& m, const Ws<T>& w, const FlyClips& clip
       FLY_SYNC();
     }
   } else {
-    FLY_FOR(i, m.nq) w.qpos[i] = s_qpos[i];
-    FLY_FOR(i, m.nv) { w.qvel[i] = s_qvel[i]; w.warm[i] = s_warm[i]; }
-    FLY_FOR(i, m.na) w.act[i] = s_act[i];
+    FLY_FOR(i, FLY_DIM(m, nq)) w.qpos[i] = s_qpos[i];
+    FLY_FOR(i, FLY_DIM(m, nv)) { w.qvel[i] = s_qvel[i]; w.warm[i] = s_warm[i]; }
+    FLY_FOR(i, FLY_DIM(m, na)) w.act[i] = s_act[i];
     const float* action_in = io.action + (size_t)env * m.action_dim;
-    FLY_FOR(a, m.nu) {  /* fruitfly.py:480-492 ; NaN -> 0 walk_imitation.py:147 */
+    FLY_FOR(a, FLY_DIM(m, nu)) {  /* fruitfly.py:480-492 ; NaN -> 0 walk_imitation.py:147 */
       const int ai = m.ctrl_action[a];
       T v = ai >= 0 ? (T)action_in[ai] : T(0);
       if (v != v) v = 0;
       w.ctrl[a] = v;
     }
-    FLY_FOR(k, m.nsensordata) w.sens_sum[k] = 0;
+    FLY_FOR(k, FLY_DIM(m, nsensordata)) w.sens_sum[k] = 0;
     if (m.task_type == FLYB_TASK_FLIGHT_IMITATION && wb.nfreq > 0 && m.user_action >= 0) {
       /* flight_imitation.py:149-159: requested beat frequency from the user action, generator step, and the wing
          position targets turned into force commands: action[wings] += target - wing qpos */
@@ -338,7 +338,7 @@ FLY_FN void fly_env_run(const DModel<T>& m, const Ws<T>& w, const FlyClips& clip
       FLY_SYNC();
       FLY_FOR(k, 6) {
         const T delta = (T)(row[k] - (double)w.qpos[m.jnt_qposadr[m.wing_joint[k]]]);
-        for (int a = 0; a < m.nu; a++) if (m.ctrl_action[a] == m.wing_action[k]) w.ctrl[a] += delta;
+        for (int a = 0; a < FLY_DIM(m, nu); a++) if (m.ctrl_action[a] == m.wing_action[k]) w.ctrl[a] += delta;
       }
       FLY_SYNC();
       FLY_LANE0 { sint[FLY_SI_WB_STEP] = ws; sint[FLY_SI_WB_FIDX] = fidx; fly_put_double(sint + FLY_SI_WB_FREQ_LO, cf); }
@@ -373,7 +373,7 @@ FLY_FN void fly_env_run(const DModel<T>& m, const Ws<T>& w, const FlyClips& clip
   } else {
     /* termination: tasks/base.py:214-217, walk_imitation.py:165-191, walk_on_ball.py:75-79 */
     T qn = 0;
-    FLY_FOR(d, m.nv) qn += w.qacc[d] * w.qacc[d];
+    FLY_FOR(d, FLY_DIM(m, nv)) qn += w.qacc[d] * w.qacc[d];
     qn = warp_sum(qn);
     int reached_end = 0;
     fatal = !(sqrt(qn) <= m.terminal_qacc);  /* NaN counts as divergence */
@@ -432,9 +432,9 @@ FLY_FN void fly_env_run(const DModel<T>& m, const Ws<T>& w, const FlyClips& clip
     }
   }
   FLY_SYNC();
-  FLY_FOR(i, m.nq) s_qpos[i] = w.qpos[i];
-  FLY_FOR(i, m.nv) { s_qvel[i] = w.qvel[i]; s_warm[i] = w.warm[i]; }
-  FLY_FOR(i, m.na) s_act[i] = w.act[i];
+  FLY_FOR(i, FLY_DIM(m, nq)) s_qpos[i] = w.qpos[i];
+  FLY_FOR(i, FLY_DIM(m, nv)) { s_qvel[i] = w.qvel[i]; s_warm[i] = w.warm[i]; }
+  FLY_FOR(i, FLY_DIM(m, na)) s_act[i] = w.act[i];
   FLY_LANE0 {
     if (io.reward) io.reward[env] = (float)reward;
     if (io.discount) io.discount[env] = (float)discount;
@@ -453,9 +453,9 @@ FLY_FN void fly_env_run(const DModel<T>& m, const Ws<T>& w, const FlyClips& clip
   if (io.trace_real) {
     T* tr = io.trace_real + (size_t)env * io.trace_real_stride;
     FLY_FOR(k, FLY_MAXCON) tr[k] = k < w.counts[FLY_C_NCON] ? w.con_dist[k] : T(0);
-    FLY_FOR(k, m.nv) tr[FLY_MAXCON + k] = w.qacc[k];
-    FLY_FOR(k, m.nsensordata) tr[FLY_MAXCON + m.nv + k] = w.sensordata[k];
-    FLY_FOR(k, FLY_MAXEFC) tr[FLY_MAXCON + m.nv + m.nsensordata + k] = k < w.counts[FLY_C_NEFC] ? w.efc_force[k] : T(0);
+    FLY_FOR(k, FLY_DIM(m, nv)) tr[FLY_MAXCON + k] = w.qacc[k];
+    FLY_FOR(k, FLY_DIM(m, nsensordata)) tr[FLY_MAXCON + FLY_DIM(m, nv) + k] = w.sensordata[k];
+    FLY_FOR(k, FLY_MAXEFC) tr[FLY_MAXCON + FLY_DIM(m, nv) + FLY_DIM(m, nsensordata) + k] = k < w.counts[FLY_C_NEFC] ? w.efc_force[k] : T(0);
   }
   FLY_SYNC();
 }

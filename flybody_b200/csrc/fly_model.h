@@ -18,6 +18,13 @@
 #include <algorithm>
 #include "../../include/flyb_model.h"
 
+/* Array sizes of the model as the engine source reads them.  In a translation unit compiled for one shipped task model
+ * (flyb_kern.cu with FLY_TU_SPEC >= 0) they are that model's compile-time constants: loop bounds the compiler can unroll
+ * and schedule across; everywhere else they are the fields of the DModel. */
+#ifndef FLY_DIM
+#define FLY_DIM(m, f) ((m).f)
+#endif
+
 #define FLY_MAXCHAIN 24   /* longest dof chain root->leaf in the Hessian tree (walk: 6 + 14 abdomen = 20) */
 #define FLY_MAXCON 64     /* detected contacts per env (gap-band contacts included) */
 #define FLY_MAXEFC 160    /* constraint rows per env */

@@ -141,7 +141,7 @@ FLY_INL void fly_half_solve(const DModel<T>& m, const T* LD, int s, T* x) {
 }
 template <class T>
 FLY_INL T fly_part_dot(const DModel<T>& m, int sa, const T* ya, int sb, const T* yb) {
-  const int nc = m.ncommon[sa * m.nv + sb];
+  const int nc = m.ncommon[sa * FLY_DIM(m, nv) + sb];
   const T *pa = ya + (m.hdepth[sa] + 1 - nc), *pb = yb + (m.hdepth[sb] + 1 - nc);
   T s = 0;
   for (int t = 0; t < nc; t++) s += pa[t] * pb[t];
@@ -264,7 +264,7 @@ FLY_INL void fly_a_mul(const Ws<T>& w, int nefc, S* out, const S* v) {
 
 template <class T>
 FLY_FN void fly_newton(const DModel<T>& m, const Ws<T>& w) {
-  const int nv = m.nv, nefc = w.counts[FLY_C_NEFC];
+  const int nv = FLY_DIM(m, nv), nefc = w.counts[FLY_C_NEFC];
   int niter = 0;
   if (nefc == 0) {
     FLY_FOR(d, nv) { w.qfrc_constraint[d] = 0; w.stmp[d] = 0; w.sgrad[d] = 0; }
@@ -400,7 +400,7 @@ FLY_FN void fly_noslip(const DModel<T>& m, const Ws<T>& w) {
   FLY_SYNC();
   const int n3 = w.counts[FLY_C_NFR];
   if (!n3) return;
-  const T scale = T(1) / (m.meaninertia * T(m.nv > 1 ? m.nv : 1));
+  const T scale = T(1) / (m.meaninertia * T(FLY_DIM(m, nv) > 1 ? FLY_DIM(m, nv) : 1));
   T* f = w.efc_force;
   for (int it = 0; it < m.opt_noslip_iterations; it++) {
     T improvement = 0;
@@ -457,12 +457,12 @@ FLY_FN void fly_fwd_constraint(const DModel<T>& m, const Ws<T>& w) {
   if (nefc && !(m.flags & FLY_OPT_NONOSLIP) && m.opt_noslip_iterations > 0) {
     fly_noslip(m, w);
     /* qacc = qacc_smooth + M^-1 J^T f */
-    FLY_FOR(d, m.nv) { w.stmp[d] = w.qfrc_constraint[d]; w.sgrad[d] = 0; }
+    FLY_FOR(d, FLY_DIM(m, nv)) { w.stmp[d] = w.qfrc_constraint[d]; w.sgrad[d] = 0; }
     FLY_SYNC();
   }
   /* Two solves with one walk over the tree: M^-1 stmp for qacc, and the implicit-damping solve of the Euler step
      (m13), (M + dt B)^-1 (qfrc_smooth + qfrc_constraint), whose right-hand side is final here as well. */
-  FLY_FOR(d, m.nv) w.sMa[d] = w.qfrc_smooth[d] + w.qfrc_constraint[d];
+  FLY_FOR(d, FLY_DIM(m, nv)) w.sMa[d] = w.qfrc_smooth[d] + w.qfrc_constraint[d];
   FLY_SYNC();
   FLY_STAGE_SYNC(17);
   {
@@ -471,7 +471,7 @@ FLY_FN void fly_fwd_constraint(const DModel<T>& m, const Ws<T>& w) {
     T* x[2] = {w.stmp, w.sMa};
     fly_solve<T, 2>(m, w, LD, iv, x);
   }
-  FLY_FOR(d, m.nv) w.qacc[d] = w.qacc_smooth[d] + w.sgrad[d] + w.stmp[d];
+  FLY_FOR(d, FLY_DIM(m, nv)) w.qacc[d] = w.qacc_smooth[d] + w.sgrad[d] + w.stmp[d];
   FLY_SYNC();
 }
 #endif

@@ -61,7 +61,7 @@ FLY_FN void fly_sensors_acc(const DModel<T>& m, const Ws<T>& w) {
     if (t == FLYB_SENS_ACCELEROMETER || t == FLYB_SENS_FORCE) need_rne = true;
   }
   if (need_rne) {
-    FLY_FOR(it, 6 * m.nbody) w.cfrc_ext[it] = 0;
+    FLY_FOR(it, 6 * FLY_DIM(m, nbody)) w.cfrc_ext[it] = 0;
     FLY_SYNC();
     for (int ci = 0; ci < ncon; ci++) {
       const int ea = w.con_efc[ci];
@@ -192,7 +192,7 @@ template <class T>
 FLY_FN void fly_forward_acc(const DModel<T>& m, const Ws<T>& w) {
   FLY_STAGE_SYNC(3);
   fly_actuation(m, w);
-  FLY_FOR(d, m.nv) {
+  FLY_FOR(d, FLY_DIM(m, nv)) {
     const T f = w.qfrc_passive[d] - w.qfrc_bias[d] + w.qfrc_actuator[d];
     w.qfrc_smooth[d] = f; w.qacc_smooth[d] = f;
   }
@@ -224,10 +224,10 @@ FLY_FN void fly_integrate(const DModel<T>& m, const Ws<T>& w) {
   const T dt = m.timestep;
   FLY_STAGE_SYNC(6);
   /* sMa = (M + dt B)^-1 (qfrc_smooth + qfrc_constraint), solved together with qacc in fly_fwd_constraint */
-  FLY_FOR(i, m.na) w.act[i] += dt * w.act_dot[i];
-  FLY_FOR(d, m.nv) { w.qvel[d] += dt * w.sMa[d]; w.warm[d] = w.qacc[d]; }
+  FLY_FOR(i, FLY_DIM(m, na)) w.act[i] += dt * w.act_dot[i];
+  FLY_FOR(d, FLY_DIM(m, nv)) { w.qvel[d] += dt * w.sMa[d]; w.warm[d] = w.qacc[d]; }
   FLY_SYNC();
-  FLY_FOR(j, m.njnt) {
+  FLY_FOR(j, FLY_DIM(m, njnt)) {
     int qa = m.jnt_qposadr[j], da = m.jnt_dofadr[j];
     const int type = m.jnt_type[j];
     if (type == FLYB_JNT_HINGE) w.qpos[qa] += dt * w.qvel[da];
@@ -241,7 +241,7 @@ FLY_FN void fly_integrate(const DModel<T>& m, const Ws<T>& w) {
 
 template <class T>
 FLY_INL void fly_accumulate(const DModel<T>& m, const Ws<T>& w) {
-  FLY_FOR(k, m.nsensordata) w.sens_sum[k] += w.sensordata[k];
+  FLY_FOR(k, FLY_DIM(m, nsensordata)) w.sens_sum[k] += w.sensordata[k];
   FLY_SYNC();
 }
 #endif

@@ -1,4 +1,17 @@
 /* flyb_kern.cu - one instantiation of the step kernel per translation unit (see fly_kernel.cuh).
  * Compiled with -DFLY_TU_WARPS=.. -DFLY_TU_LEVEL=.. -DFLY_TU_SPEC=.. -DFLY_TU_NAME=flyb_kernel_<W>_<L>_<g|sN>. */
+#include "fly_dims_gen.h"
+#if FLY_TU_SPEC >= 0 && !defined(FLY_NO_CONST_DIMS)
+/* this unit's model: its array sizes as constants (fly_model.h: FLY_DIM) */
+template <int S> struct FlyDimsOf;
+#define X(i, a, b, c, d, e, f, g, h, k, l, p, q)                                                          \
+  template <> struct FlyDimsOf<i> {                                                                       \
+    static constexpr int nq = a, nv = b, na = c, nu = d, nbody = e, njnt = f, ngeom = g, nsite = h, nM = k, \
+                         nsensordata = l, nfluidbox = p, nfluidgeom = q;                                  \
+  };
+FLY_SPEC_MODELS(X)
+#undef X
+#define FLY_DIM(m, f) (FlyDimsOf<FLY_TU_SPEC>::f)
+#endif
 #include "fly_kernel.cuh"
 extern "C" const void* FLY_TU_NAME() { return (const void*)fly_step_kernel<FLY_TU_WARPS, FLY_TU_LEVEL, FLY_TU_SPEC>; }
