@@ -27,6 +27,9 @@
 #define FLY_LANE() ((int)(threadIdx.x & 31))
 #define FLY_FOR(i, n) for (int i = FLY_LANE(); i < (n); i += 32)
 #define FLY_SYNC() __syncwarp()
+/* 2-D work items over a 4 x 8 lane tile: rows i in [0,n) across lane / 8, columns j in [j0,n) across lane % 8 */
+#define FLY_FOR_ROW(i, n) for (int i = FLY_LANE() >> 3; i < (n); i += 4)
+#define FLY_FOR_COL(j, j0, n) for (int j = (j0) + (FLY_LANE() & 7); j < (n); j += 8)
 /* block-wide rendezvous of the warps of a block (each steps its own env): keeps them in the same stage so that
  * instruction fetches and model-table lines are shared in the SM's caches.  Every warp must pass the same number. */
 #ifndef FLY_SYNC_GROUP
@@ -103,6 +106,8 @@ template <class P> FLY_INL int warp_filter(int n, P pred, unsigned short* list) 
 #define FLY_NOINL static
 #define FLY_LANE() 0
 #define FLY_FOR(i, n) for (int i = 0; i < (n); i++)
+#define FLY_FOR_ROW(i, n) for (int i = 0; i < (n); i++)
+#define FLY_FOR_COL(j, j0, n) for (int j = (j0); j < (n); j++)
 #define FLY_SYNC()
 #define FLY_BLOCK_SYNC()
 #define FLY_LANE0

@@ -196,14 +196,21 @@ FLY_FN void fly_lu_solve(T* K, int n, T* rhs) {
     }
     const T pk = K[k * n + k];
     if (fabs_(pk) >= minval<T>()) {
+      /* multipliers into column k, then the trailing block as a 4 x 8 lane tile (rows x columns: consecutive lanes on
+         consecutive columns; one row per lane made every access a stride-n gather and left n - k lanes busy) */
+      const int nr = n - k - 1;
       const T rk = rhs[k];
-      FLY_FOR(i, n - k - 1) {
+      FLY_FOR(i, nr) {
         const int r = k + 1 + i;
         const T l = K[r * n + k] / pk;
-        if (l != 0) {
-          for (int j = k + 1; j < n; j++) K[r * n + j] -= l * K[k * n + j];
-          rhs[r] -= l * rk;
-        }
+        K[r * n + k] = l;
+        rhs[r] -= l * rk;
+      }
+      FLY_SYNC();
+      FLY_FOR_ROW(i, nr) {
+        const int r = k + 1 + i;
+        const T l = K[r * n + k];
+        FLY_FOR_COL(j, k + 1, n) K[r * n + j] -= l * K[k * n + j];
       }
     }
     FLY_SYNC();
