@@ -246,9 +246,9 @@ FLY_FN void fly_actuation(const DModel<T>& m, const Ws<T>& w) {
     if (m.act_trntype[a] == FLYB_TRN_JOINT) w.qfrc_actuator[m.jnt_dofadr[m.act_trnid[a]]] += m.act_gear[a] * w.act_force[a];
   FLY_SYNC();
   const int ncon = w.counts[FLY_C_NCON];
-  for (int a = 0; a < FLY_DIM(m, nu); a++) {
+  for (int oa = 0; oa < m.nact_other; oa++) {  /* tendon and adhesion actuators, in actuator order */
+    const int a = m.act_other[oa];
     const int trn = m.act_trntype[a], id = m.act_trnid[a];
-    if (trn == FLYB_TRN_JOINT) continue;
     const T f = w.act_force[a], gear = m.act_gear[a];
     if (trn == FLYB_TRN_TENDON) {
       const int q0 = m.tendon_adr[id];

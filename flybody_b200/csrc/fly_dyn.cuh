@@ -509,30 +509,39 @@ FLY_FN void fly_mul_m(const DModel<T>& m, const T* LD, T* r, const T* v, T* z) {
 /* ---------------------------------------------------------------- m7 comVel */
 template <class T>
 FLY_FN void fly_com_vel(const DModel<T>& m, const Ws<T>& w) {
-  FLY_LANE0 for (int c = 0; c < 6; c++) w.cvel[c] = 0;
-  FLY_SYNC();
-  for (int L = 1; L <= m.nlevel; L++) {
-    const int adr = m.lvl_adr[L], n = m.lvl_adr[L + 1] - adr;
-    FLY_FOR(k, n) {
-      const int b = m.lvl_body[adr + k];
-      T v[6];
-      for (int c = 0; c < 6; c++) v[c] = w.cvel[6 * m.body_parent[b] + c];
-      const int j0 = m.body_jntadr[b], j1 = j0 + m.body_jntnum[b];
-      for (int j = j0; j < j1; j++) {
-        int d = m.jnt_dofadr[j], nd = 1;
-        const int type = m.jnt_type[j];
-        if (type == FLYB_JNT_FREE) {
-          for (int c = 0; c < 18; c++) w.cdof_dot[6 * d + c] = 0;
-          for (int q = 0; q < 3; q++) for (int c = 0; c < 6; c++) v[c] += w.cdof[6 * (d + q) + c] * w.qvel[d + q];
-          d += 3; nd = 3;
-        } else if (type == FLYB_JNT_BALL) nd = 3;
-        for (int q = 0; q < nd; q++) cross_motion(w.cdof_dot + 6 * (d + q), v, w.cdof + 6 * (d + q));
-        for (int q = 0; q < nd; q++) for (int c = 0; c < 6; c++) v[c] += w.cdof[6 * (d + q) + c] * w.qvel[d + q];
-      }
-      for (int c = 0; c < 6; c++) w.cvel[6 * b + c] = v[c];
+  /* cvel of a body = sum of cdof * qvel over its kinematic dof chain, cdof_dot of a dof = (velocity accumulated before its
+     joint) x cdof.  Each lane walks the chain of its own dof / body from the root down - the additions a recursion over
+     the body levels would make, in its order, so the bits are the same - instead of nlevel dependent rounds of a few
+     bodies each. */
+  FLY_FOR(d, FLY_DIM(m, nv)) {
+    const int j = m.dof_jntid[d], type = m.jnt_type[j], d0 = m.jnt_dofadr[j];
+    T* out = w.cdof_dot + 6 * d;
+    if (type == FLYB_JNT_FREE && d < d0 + 3) { for (int c = 0; c < 6; c++) out[c] = 0; continue; }
+    /* chain entries (leaf first) that belong to this joint and do not count: a ball's three dofs and a free joint's
+       three rotations all see the velocity before them */
+    const int skip = type == FLYB_JNT_FREE ? d - d0 - 2 : d - d0 + 1;
+    const int a = m.madr[d];
+    T v[6] = {0, 0, 0, 0, 0, 0};
+    for (int k = m.kdepth[d]; k >= skip; k--) {
+      const int e = m.mcol[a + k];
+      const T qv = w.qvel[e];
+      for (int c = 0; c < 6; c++) v[c] += w.cdof[6 * e + c] * qv;
     }
-    FLY_SYNC();
+    cross_motion(out, v, w.cdof + 6 * d);
   }
+  FLY_FOR(b, FLY_DIM(m, nbody)) {
+    T v[6] = {0, 0, 0, 0, 0, 0};
+    if (b > 0) {
+      const int d = m.body_lastdof[b], a = m.madr[d];
+      for (int k = m.kdepth[d]; k >= 0; k--) {
+        const int e = m.mcol[a + k];
+        const T qv = w.qvel[e];
+        for (int c = 0; c < 6; c++) v[c] += w.cdof[6 * e + c] * qv;
+      }
+    }
+    for (int c = 0; c < 6; c++) w.cvel[6 * b + c] = v[c];
+  }
+  FLY_SYNC();
 }
 
 /* 6D velocity [ang; lin] of a frame (pos, mat) rigidly attached to body b, expressed in that frame */

@@ -47,7 +47,7 @@ enum { FLY_OPT_NOCONTACT = 1, FLY_OPT_NOLIMIT = 2, FLY_OPT_NOFLUID = 4, FLY_OPT_
   X(gstep_b) X(gstep_f) X(dof_din) X(trunk_dof) X(trunk_adr) X(bt_list)                             \
   X(geom_type) X(geom_bodyid) X(pair_geom) X(pair_condim)                                                  \
   X(site_bodyid) X(tendon_adr) X(tendon_num) X(wrap_dofadr) X(wrap_qposadr)                                \
-  X(act_trntype) X(act_trnid) X(act_actadr) X(act_ctrllimited) X(act_forcelimited)                         \
+  X(act_trntype) X(act_trnid) X(act_actadr) X(act_ctrllimited) X(act_forcelimited) X(act_other)            \
   X(sensor_type) X(sensor_site) X(sensor_adr) X(sensor_obs)                                                \
   X(fbox_bodyid) X(body_fbox_adr) X(body_fbox) X(fgeom_bodyid)                                             \
   X(ctrl_action) X(obs_joint_qposadr) X(obs_joint_dofadr) X(appendage_site) X(mocap_joint) X(mocap_site)   \
@@ -73,6 +73,7 @@ struct DModel {
   /* sizes */
   int nq, nv, nu, na, nbody, njnt, ngeom, npair, nsite, ntendon, nwrap, nsensor, nsensordata, nfluidbox, nfluidgeom;
   int nM, nlevel, ndlevel, ntri, nheavy;
+  int nact_other;  /* actuators whose transmission is not a joint (tendon, adhesion body): act_other[] lists them */
   int ntrunk, gsteps;
   int opt_iterations, opt_ls_iterations, opt_noslip_iterations, flags;
   /* task */
@@ -400,6 +401,13 @@ std::string build_dmodel(const FlybModel* m, int flags, DModel<T>* out, FlyArena
   d.tendon_adr = puti(vi(m->tendon_adr, m->ntendon)); d.tendon_num = puti(vi(m->tendon_num, m->ntendon));
   d.wrap_dofadr = puti(vi(m->wrap_dofadr, m->nwrap)); d.wrap_qposadr = puti(vi(m->wrap_qposadr, m->nwrap));
   d.act_trntype = puti(vi(m->act_trntype, m->nu)); d.act_trnid = puti(vi(m->act_trnid, m->nu));
+  {
+    std::vector<int> other;
+    for (int a = 0; a < m->nu; a++) if (m->act_trntype[a] != FLYB_TRN_JOINT) other.push_back(a);
+    d.nact_other = (int)other.size();
+    if (other.empty()) other.push_back(0);
+    d.act_other = puti(other);
+  }
   d.act_actadr = puti(vi(m->act_actadr, m->nu)); d.act_ctrllimited = puti(vi(m->act_ctrllimited, m->nu));
   d.act_forcelimited = puti(vi(m->act_forcelimited, m->nu));
   d.sensor_type = puti(vi(m->sensor_type, m->nsensor)); d.sensor_site = puti(vi(m->sensor_site, m->nsensor));
