@@ -470,7 +470,7 @@ FLY_FN void fly_collision(const DModel<T>& m, const Ws<T>& w) {
   T* gx = (T*)w.qLD;
   FLY_FOR(i, 3 * FLY_DIM(m, ngeom)) gx[i] = w.geom_xpos[i];
   FLY_SYNC();
-  int ncand = warp_compact(m.npair, [&](int p) -> bool {
+  int ncand = warp_compact(FLY_DIM(m, npair), [&](int p) -> bool {
     const int pg = FLY_LDG(m.pair_geom + p), g1 = pg & 255, g2 = (pg >> 8) & 255;
     const T bound = FLY_LDG(m.pair_bound + p);
     const T *c1 = gx + 3 * g1, *c2 = gx + 3 * g2;

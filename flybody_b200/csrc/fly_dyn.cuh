@@ -19,7 +19,7 @@ FLY_FN void fly_kinematics(const DModel<T>& m, const Ws<T>& w) {
     for (int k = 0; k < 9; k++) w.xmat[k] = (k % 4 == 0) ? T(1) : T(0);
   }
   FLY_SYNC();
-  for (int L = 1; L <= m.nlevel; L++) {
+  for (int L = 1; L <= FLY_DIM(m, nlevel); L++) {
     const int adr = m.lvl_adr[L], n = m.lvl_adr[L + 1] - adr;
     FLY_FOR(k, n) {
       const int b = m.lvl_body[adr + k], p = m.body_parent[b];
@@ -89,7 +89,7 @@ FLY_INL void fly_geom_xmat(const DModel<T>& m, const Ws<T>& w, int g, T* mat) {
 /* acc[b] (K numbers per body) <- acc[b] + sum over children, for every non-world body, leaves first */
 template <class T>
 FLY_INL void fly_tree_upsweep(const DModel<T>& m, T* acc, int K) {
-  for (int L = m.nlevel - 1; L >= 1; L--) {
+  for (int L = FLY_DIM(m, nlevel) - 1; L >= 1; L--) {
     const int adr = m.lvl_adr[L], n = m.lvl_adr[L + 1] - adr;
     FLY_FOR(it, n * K) {
       const int b = m.lvl_body[adr + it / K], c = it % K;
@@ -237,7 +237,7 @@ FLY_INL void fly_row_axpy(T* const* LD, int ai, int as, const T* t, int n) {
  * FLY_MAXTRUNK dofs) is eliminated with one lane per entry. */
 template <class T, int NS>
 FLY_FN void fly_factor(const DModel<T>& m, T* const* LD, T* const* invD) {
-  for (int st = 0; st < m.gsteps; st++) {
+  for (int st = 0; st < FLY_DIM(m, gsteps); st++) {
     FLY_FOR(l, 32) {
       const int word = FLY_LDG(m.gstep_b + st * 32 + l);
       if (word >= 0) {
@@ -293,7 +293,7 @@ FLY_FN void fly_factor(const DModel<T>& m, T* const* LD, T* const* invD) {
     }
     FLY_SYNC();
   }
-  const int nt = m.ntrunk, nb = FLY_DIM(m, nv) - nt;
+  const int nt = FLY_DIM(m, ntrunk), nb = FLY_DIM(m, nv) - nt;
   if (nt == 0) return;
   FLY_FOR(p, nt * (nt + 1) / 2) {
     const int j = FLY_LDG(m.tri_a + p), i = FLY_LDG(m.tri_b + p);
@@ -349,7 +349,7 @@ FLY_FN void fly_factor(const DModel<T>& m, T* const* LD, T* const* invD) {
  * x[c] to its in-branch ancestors; forward: gather over them), the trunk chain in registers in between. */
 template <class T, int NS>
 FLY_FN void fly_solve(const DModel<T>& m, const Ws<T>& w, const T* const* LD, const T* const* invD, T* const* x) {
-  for (int st = 0; st < m.gsteps; st++) {
+  for (int st = 0; st < FLY_DIM(m, gsteps); st++) {
     FLY_FOR(l, 32) {
       const int word = FLY_LDG(m.gstep_b + st * 32 + l);
       if (word >= 0) {
@@ -366,7 +366,7 @@ FLY_FN void fly_solve(const DModel<T>& m, const Ws<T>& w, const T* const* LD, co
     }
     FLY_SYNC();
   }
-  const int nt = m.ntrunk, nb = FLY_DIM(m, nv) - nt;
+  const int nt = FLY_DIM(m, ntrunk), nb = FLY_DIM(m, nv) - nt;
   if (nt > 0) {
     T acc[NS][FLY_MAXTRUNK], y[NS][FLY_MAXTRUNK];
 #pragma unroll
@@ -432,7 +432,7 @@ FLY_FN void fly_solve(const DModel<T>& m, const Ws<T>& w, const T* const* LD, co
     }
     FLY_SYNC();
   }
-  for (int st = 0; st < m.gsteps; st++) {
+  for (int st = 0; st < FLY_DIM(m, gsteps); st++) {
     FLY_FOR(l, 32) {
       const int word = FLY_LDG(m.gstep_f + st * 32 + l);
       if (word >= 0) {
@@ -680,7 +680,7 @@ FLY_FN void fly_rne(const DModel<T>& m, const Ws<T>& w, T* result, int flg_acc, 
     for (int c = 0; c < 6; c++) w.cfrc_int[c] = 0;
   }
   FLY_SYNC();
-  for (int L = 1; L <= m.nlevel; L++) {
+  for (int L = 1; L <= FLY_DIM(m, nlevel); L++) {
     const int adr = m.lvl_adr[L], n = m.lvl_adr[L + 1] - adr;
     FLY_FOR(k, n) {
       const int b = m.lvl_body[adr + k];

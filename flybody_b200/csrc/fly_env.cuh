@@ -86,7 +86,7 @@ FLY_FN void fly_write_obs(const DModel<T>& m, const Ws<T>& w, const FlyClipView&
   const int* off = m.obs_offset;
   const int rb = m.root_body;
   const T *rp = w.xpos + 3 * rb, *rm = w.xmat + 9 * rb;
-  FLY_FOR(s, m.nsensor) {
+  FLY_FOR(s, FLY_DIM(m, nsensor)) {
     const int key = m.sensor_obs[2 * s], idx = m.sensor_obs[2 * s + 1];
     const int dim = m.sensor_type[s] == FLYB_SENS_TOUCH ? 1 : 3;
     if (off[key] >= 0)

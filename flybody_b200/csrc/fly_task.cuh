@@ -56,7 +56,7 @@ template <class T>
 FLY_FN void fly_sensors_acc(const DModel<T>& m, const Ws<T>& w) {
   const int ncon = w.counts[FLY_C_NCON];
   bool need_rne = false;
-  for (int s = 0; s < m.nsensor; s++) {
+  for (int s = 0; s < FLY_DIM(m, nsensor); s++) {
     const int t = m.sensor_type[s];
     if (t == FLYB_SENS_ACCELEROMETER || t == FLYB_SENS_FORCE) need_rne = true;
   }
@@ -85,7 +85,7 @@ FLY_FN void fly_sensors_acc(const DModel<T>& m, const Ws<T>& w) {
     }
     fly_rne(m, w, (T*)0, 1, 1);
   }
-  FLY_FOR(s, m.nsensor) {
+  FLY_FOR(s, FLY_DIM(m, nsensor)) {
     const int site = m.sensor_site[s], b = m.site_bodyid[site], type = m.sensor_type[s];
     T* out = w.sensordata + m.sensor_adr[s];
     const T *sp = w.site_xpos + 3 * site, *sm = w.site_xmat + 9 * site;
@@ -124,7 +124,7 @@ FLY_FN void fly_sensors_acc(const DModel<T>& m, const Ws<T>& w) {
 /* m14: gyro, velocimeter */
 template <class T>
 FLY_FN void fly_sensors_vel(const DModel<T>& m, const Ws<T>& w) {
-  FLY_FOR(s, m.nsensor) {
+  FLY_FOR(s, FLY_DIM(m, nsensor)) {
     const int site = m.sensor_site[s], type = m.sensor_type[s];
     if (type == FLYB_SENS_GYRO || type == FLYB_SENS_VELOCIMETER) {
       T lv[6];

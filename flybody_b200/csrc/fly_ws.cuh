@@ -176,14 +176,19 @@ inline void ws_layout(const DModel<T>& m, int level, WsOff* o, size_t* fast_byte
  * (fly_dims_gen.h), and the step kernel instantiated for such a model takes its offsets from ws_layout_c at compile time:
  * every array address is then arena base + immediate (measured on the generic kernel: 10.6 % of all executed instructions
  * only added a constant-bank offset to an arena base). */
-struct WsDims { int nq, nv, na, nu, nbody, njnt, ngeom, nsite, nM, nsensordata, nfluidbox, nfluidgeom; };
+struct WsDims {
+  int nq, nv, na, nu, nbody, njnt, ngeom, nsite, nM, nsensordata, nfluidbox, nfluidgeom;  /* the layout depends on these */
+  int npair, nsensor, ntrunk, gsteps, nlevel;  /* further loop bounds the per-model kernels read as constants (FLY_DIM) */
+};
 template <class M> inline WsDims ws_dims_of(const M& m) {
-  return WsDims{m.nq, m.nv, m.na, m.nu, m.nbody, m.njnt, m.ngeom, m.nsite, m.nM, m.nsensordata, m.nfluidbox, m.nfluidgeom};
+  return WsDims{m.nq, m.nv, m.na, m.nu, m.nbody, m.njnt, m.ngeom, m.nsite, m.nM, m.nsensordata, m.nfluidbox, m.nfluidgeom,
+                m.npair, m.nsensor, m.ntrunk, m.gsteps, m.nlevel};
 }
 inline bool ws_dims_equal(const WsDims& a, const WsDims& b) {
   return a.nq == b.nq && a.nv == b.nv && a.na == b.na && a.nu == b.nu && a.nbody == b.nbody && a.njnt == b.njnt &&
          a.ngeom == b.ngeom && a.nsite == b.nsite && a.nM == b.nM && a.nsensordata == b.nsensordata &&
-         a.nfluidbox == b.nfluidbox && a.nfluidgeom == b.nfluidgeom;
+         a.nfluidbox == b.nfluidbox && a.nfluidgeom == b.nfluidgeom && a.npair == b.npair && a.nsensor == b.nsensor &&
+         a.ntrunk == b.ntrunk && a.gsteps == b.gsteps && a.nlevel == b.nlevel;
 }
 template <class T>
 FLY_HD constexpr WsOff ws_layout_c(const WsDims m, int level) {

@@ -146,6 +146,9 @@ struct Emu : EmuBase {
     if (!strcmp(name, "mrow")) { int c = m.nM < cap ? m.nM : cap; for (int i = 0; i < c; i++) out[i] = m.mrow[i]; return c; }
     if (!strcmp(name, "mcol")) { int c = m.nM < cap ? m.nM : cap; for (int i = 0; i < c; i++) out[i] = m.mcol[i]; return c; }
     if (!strcmp(name, "nM")) { out[0] = m.nM; return 1; }
+    if (!strcmp(name, "ntrunk")) { out[0] = m.ntrunk; return 1; }
+    if (!strcmp(name, "gsteps")) { out[0] = m.gsteps; return 1; }
+    if (!strcmp(name, "nlevel")) { out[0] = m.nlevel; return 1; }
     return -1;
   }
 };
