@@ -117,6 +117,12 @@ static int launch(FlybEngine* h, const FlyIO<float>& io, cudaStream_t st) {
   const size_t smem = fb * W;
   if (smem > 227 * 1024 - 2048) { h->err = "shared memory request too large for this smem_level / warps_per_block"; return 1; }
   if (bb > h->bulk_stride) { h->err = "internal: bulk slot too small"; return 1; }
+  {  /* the convex narrow phase borrows qLD | qH as one scratch block (fly_col.cuh): they must be adjacent and large enough */
+    const size_t need = FLY_PORTAL_WORDS * sizeof(double) + FLY_GEOM_WORDS * sizeof(float);
+    if (off.qH < off.qLD || (size_t)(off.qH - off.qLD) + (size_t)(h->m.nM + 1) * sizeof(float) < need) {
+      h->err = "internal: qLD | qH cannot hold the convex narrow phase's scratch"; return 1;
+    }
+  }
   const int spec = h->no_spec ? -1 : spec_of(h->m);
   const void* kern = pick_kernel(W, h->smem_level, spec);
   h->spec = (W == FLY_SPEC_WARPS && h->smem_level == FLY_SPEC_LEVEL) ? spec : -1;
