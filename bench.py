@@ -260,6 +260,9 @@ def run_gpu(args):
 
 
 def main():
+    # stdout carries ONE JSON line: NCCL prints its version banner to stdout at NCCL_DEBUG=VERSION (set on some boxes)
+    if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+        os.environ["NCCL_DEBUG"] = "WARN"
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
