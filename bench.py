@@ -30,6 +30,16 @@ ALGO_BYTES = {"walk_imitation": 9984, "walk_on_ball": 4436}   # SURVEY.md 8(d): 
 METRIC = "fly env-steps/s (walk_imitation, 16384 envs per GPU, synthetic clips, random actions)"
 
 
+_REAL_STDOUT = None
+
+
+def _emit(obj):
+    """The one JSON line, on the process's original stdout."""
+    sys.stdout.flush()
+    line = (json.dumps(obj) + "\n").encode()
+    os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, line)
+
+
 def _peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -138,14 +148,14 @@ def run_reference(args):
         vals.append(v); ms.append(dt * 1e3)
     v = float(np.mean(vals))
     sample = f"{cores} oracle envs x {per_core} control steps per step (same model, clips and action distribution)"
-    print(json.dumps({
+    _emit({
         "impl": "reference", "metric": METRIC, "value": v, "unit": "env-steps/s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": float(np.mean(ms)), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
         "config": {"workload": "walk_imitation, synthetic reference clips, U(ctrlrange) random actions; CPU port of the reference algorithm (MuJoCo/dm_control not installable here)"},
         "cpu_baseline": {"value": v, "unit": "env-steps/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    }))
+    })
 
 
 def run_gpu(args):
@@ -237,7 +247,7 @@ def run_gpu(args):
             traffic = json.load(open(tp)).get("dram_bytes_per_launch")
         cpu_steps = args.cpu_steps
         cpu_v, cpu_dt = cpu_throughput(1, cpu_steps, table)
-        print(json.dumps({
+        _emit({
             "metric": METRIC, "value": value, "unit": "env-steps/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
@@ -253,16 +263,19 @@ def run_gpu(args):
             "cpu_baseline": {"value": cpu_v, "unit": "env-steps/s", "cores": 1, "kind": "port",
                              "sample": f"{cpu_steps} control steps of one env, float64 CPU restatement (oracle/), {cpu_dt:.1f} s"},
             "episode_stats": stats,
-        }))
+        })
     eng.close()
     if world > 1:
         dist.destroy_process_group()
 
 
 def main():
-    # stdout carries ONE JSON line: NCCL prints its version banner to stdout at NCCL_DEBUG=VERSION (set on some boxes)
-    if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
-        os.environ["NCCL_DEBUG"] = "WARN"
+    # stdout carries ONE JSON line.  Libraries write there too (NCCL prints a version banner to fd 1 at communicator
+    # creation on the GPU boxes), so fd 1 points at stderr while the benchmark runs and _emit() writes to the real one.
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
