@@ -326,21 +326,28 @@ FLY_FN void fly_newton(const DModel<T>& m, const Ws<T>& w) {
     FLY_SYNC();
     T* K = w.efc_K;
     T* lam = w.efc_lam;
+    /* rows across lane / 8, columns across lane % 8 (consecutive lanes on consecutive columns of K and A) */
+    FLY_FOR_ROW(i, na) {
+      const int r = w.lim_item[i], g = w.efc_g[r], r0 = w.grp_row[g];
+      if (w.efc_state[r] == FLY_ST_CONE) {
+        const T* hc = w.con_hc + 9 * w.grp_con[g] + 3 * (r - r0);
+        const T h0 = hc[0], h1 = hc[1], h2 = hc[2];
+        FLY_FOR_COL(j, 0, na) {
+          const int cj = w.lim_item[j];
+          K[i * na + j] = (i == j ? T(1) : T(0)) + h0 * w.efc_A[r0 * nefc + cj] + h1 * w.efc_A[(r0 + 1) * nefc + cj]
+                          + h2 * w.efc_A[(r0 + 2) * nefc + cj];
+        }
+      } else {
+        const T D = w.efc_D[r];
+        FLY_FOR_COL(j, 0, na) K[i * na + j] = (i == j ? T(1) : T(0)) + D * w.efc_A[r * nefc + w.lim_item[j]];
+      }
+    }
     FLY_FOR(i, na) {
       const int r = w.lim_item[i], g = w.efc_g[r], r0 = w.grp_row[g];
       if (w.efc_state[r] == FLY_ST_CONE) {
         const T* hc = w.con_hc + 9 * w.grp_con[g] + 3 * (r - r0);
-        for (int j = 0; j < na; j++) {
-          const int cj = w.lim_item[j];
-          K[i * na + j] = (i == j ? T(1) : T(0)) + hc[0] * w.efc_A[r0 * nefc + cj] + hc[1] * w.efc_A[(r0 + 1) * nefc + cj]
-                          + hc[2] * w.efc_A[(r0 + 2) * nefc + cj];
-        }
         lam[i] = (T)(hc[0] * h[r0] + hc[1] * h[r0 + 1] + hc[2] * h[r0 + 2]);
-      } else {
-        const T D = w.efc_D[r];
-        for (int j = 0; j < na; j++) K[i * na + j] = (i == j ? T(1) : T(0)) + D * w.efc_A[r * nefc + w.lim_item[j]];
-        lam[i] = (T)(D * h[r]);
-      }
+      } else lam[i] = (T)(w.efc_D[r] * h[r]);
     }
     FLY_SYNC();
     fly_lu_solve(K, na, lam);
