@@ -161,7 +161,7 @@ def run_reference(args):
 def run_gpu(args):
     import torch
     import torch.distributed as dist
-    from flybody_b200.engine import Engine, INFO_LAUNCHES, INFO_GRID, INFO_SMEM_BYTES
+    from flybody_b200.engine import Engine, INFO_LAUNCHES, INFO_GRID, INFO_SMEM_BYTES, INFO_SPEC_KERNEL
     from flybody_b200.sharding import shard_range, reduce_stats
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     local = int(os.environ.get("LOCAL_RANK", 0))
@@ -254,7 +254,9 @@ def run_gpu(args):
             "config": {"workload": "walk_imitation (BASELINE.json configs[1]): 16384 envs per GPU, 10 physics substeps per control step, "
                                    f"{args.clips} synthetic reference clips x 600 steps, U(ctrlrange) random actions, auto-reset",
                        "envs_per_gpu": N, "global_envs": N * world, "l2": "256 MB buffer written between timed steps",
-                       "grid": eng.info(INFO_GRID), "smem_bytes_per_block": eng.info(INFO_SMEM_BYTES), "outputs_finite": finite},
+                       "grid": eng.info(INFO_GRID), "smem_bytes_per_block": eng.info(INFO_SMEM_BYTES), "outputs_finite": finite,
+                       "step_kernel": ("compiled for this task model (index %d of csrc/fly_dims_gen.h)" % eng.info(INFO_SPEC_KERNEL))
+                       if eng.info(INFO_SPEC_KERNEL) >= 0 else "generic"},
             "clocks": clk, "gpu_launches": int(launches),
             "e2e": {"value": e2e, "unit": "env-steps/s", "h2d_bytes_per_step": N * A * 4, "d2h_bytes_per_step": N * (O + 3) * 4},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
