@@ -14,7 +14,11 @@
 #include <stdint.h>
 
 #ifndef FLY_SYNC_MASK
-#define FLY_SYNC_MASK 0x3ffffu  /* bit per block rendezvous point (fly_task.cuh) */
+/* bit per block rendezvous point (fly_task.cuh).  All eighteen except the four between the constraint solve and the next
+ * collision pass (5: before the acceleration sensors, 6: integration, 0: kinematics, 7: subtree CoM): warps that finish
+ * their solve early run those short stages instead of waiting (measured 60.2 -> 59.7 ms per step; fewer points cost more:
+ * profiles/r1_summary.md) */
+#define FLY_SYNC_MASK 0x3ff1eu
 #endif
 #define FLY_STAGE_SYNC(bit) do { if (FLY_SYNC_MASK & (1u << (bit))) FLY_BLOCK_SYNC(); } while (0)
 
