@@ -98,3 +98,22 @@ def test_hdf5_converter_logic_on_a_dataset_shaped_mapping(models, tmp_path):
     # identity orientation: root = com - offset, after the xy origin moved to the first frame
     assert np.allclose(fl[0]["qpos"][0, :3], [0, 0, com[0, 2]] - C._COM_OFFSET)
     assert np.allclose(C.root2com(fl[0]["qpos"][2]), com[2, :3] - [com[0, 0], com[0, 1], 0])
+
+
+def test_generated_model_sizes_match_the_shipped_assets(models):
+    """csrc/fly_dims_gen.h (tools/gen_dims.py) drives the per-model step kernels: a stale table would silently send a shipped
+    model to the generic kernel (25 % slower).  Every row must equal the sizes of its asset, derived ones included."""
+    import os, re
+    from tests.emu.emu import EmuEnv
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    text = open(os.path.join(root, "flybody_b200", "csrc", "fly_dims_gen.h")).read()
+    fields = re.search(r"X\(index, ([^)]*)\)", text).group(1).replace(" ", "").split(",")
+    rows = {m.group(2): [int(x) for x in m.group(1).split(",")[1:]]
+            for m in re.finditer(r"X\(([\d, ]+)\) /\* (\w+) \*/", text)}
+    assert set(rows) == {"walk_imitation", "walk_on_ball", "template", "flight_imitation"}
+    for task, vals in rows.items():
+        M = models[task]
+        e = EmuEnv(M, double=False)
+        for k, v in zip(fields, vals):
+            have = int(e.geti(k)[0]) if k in ("nM", "ntrunk", "gsteps", "nlevel") else int(M[k])
+            assert have == v, (task, k, have, v)
