@@ -36,6 +36,7 @@ struct FlybEngine {
   int smem_level = 1, warps = 16, blocks_per_sm = 0, sm_count = 148, grid = 0;
   int spec = -1, no_spec = 0;   /* index of the model-specialised kernel in use (-1: generic); FLYB_NO_SPEC=1 forces generic */
   long long launches = 0;
+  unsigned char* noalloc_scratch = nullptr;   /* device address of g_noalloc_scratch on h->device (flyb_step_noalloc) */
   std::string err;
 };
 
@@ -107,7 +108,34 @@ __global__ void __launch_bounds__(1024) fly_bin_kernel(const int* __restrict__ w
   }
 }
 
-static int launch(FlybEngine* h, const FlyIO<float>& io, cudaStream_t st) {
+/* ---- scratch of flyb_step_noalloc (include/flyb.h): the step kernel's per-warp workspace slots and its work counter in
+ * a file-scope array instead of the cudaMalloc'ed d_bulk / d_counter, for callers that must not allocate.  Every GPU that
+ * loads the library holds these FLYB_NOALLOC_SCRATCH_BYTES until exit.  Layout: [0, 256) the work counter (cleared by
+ * every call), then workspace slots of bulk_stride bytes each.  All calls on a device share the array: two flyb_step_noalloc
+ * calls that overlap on the GPU (different streams, different handles) race on it.
+ * In host code the name g_noalloc_scratch is only a handle for the runtime; the device address comes from
+ * cudaGetSymbolAddress, resolved once per device by noalloc_scratch_of() with that device current. */
+static __device__ __align__(256) unsigned char g_noalloc_scratch[FLYB_NOALLOC_SCRATCH_BYTES];
+#define FLYB_NOALLOC_HEADER 256
+#define FLYB_MAX_DEVICES 64
+static unsigned char* g_noalloc_ptr[FLYB_MAX_DEVICES];   /* device address of the array on each device, 0 = not resolved yet */
+
+/* call with `device` current; returns the device address of the scratch array or null (message in *err) */
+static unsigned char* noalloc_scratch_of(int device, std::string* err) {
+  if (device < 0 || device >= FLYB_MAX_DEVICES) { *err = "device index beyond FLYB_MAX_DEVICES"; return nullptr; }
+  if (!g_noalloc_ptr[device]) {
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+    if (e != cudaSuccess || !p) { *err = std::string("cudaGetSymbolAddress(g_noalloc_scratch): ") + cudaGetErrorString(e); return nullptr; }
+    g_noalloc_ptr[device] = (unsigned char*)p;
+  }
+  return g_noalloc_ptr[device];
+}
+
+/* where a launch takes its scratch from: null = the handle's own cudaMalloc'ed buffers */
+struct LaunchScratch { char* bulk; int slots; int* counter; };
+
+static int launch(FlybEngine* h, const FlyIO<float>& io, cudaStream_t st, const LaunchScratch* sc = nullptr) {
   CK(cudaSetDevice(h->device));
   size_t fb = 0, bb = 0;
   WsOff off;
@@ -142,22 +170,25 @@ static int launch(FlybEngine* h, const FlyIO<float>& io, cudaStream_t st) {
   int grid = h->sm_count * per_sm;
   const int need = (h->num_envs + W - 1) / W;
   if (grid > need) grid = need;
-  if (grid * W > h->bulk_slots) grid = h->bulk_slots / W;
+  const int slots = sc ? sc->slots : h->bulk_slots;
+  if (grid * W > slots) grid = slots / W;
+  if (grid < 1) { h->err = "scratch too small for one block of this launch configuration"; return 1; }
   h->grid = grid;
   KArgs a;
   a.clips.data = h->d_clip_rows; a.clips.offset = h->d_clip_off; a.clips.length = h->d_clip_len; a.clips.nclips = h->n_clips;
   a.io = io;
   a.wb = h->wb;
-  a.bulk = h->d_bulk; a.bulk_stride = h->bulk_stride; a.fast_stride = fb; a.counter = h->d_counter;
+  a.bulk = sc ? sc->bulk : h->d_bulk; a.bulk_stride = h->bulk_stride; a.fast_stride = fb;
+  a.counter = sc ? sc->counter : h->d_counter;
   a.num_envs = h->num_envs; a.level = h->smem_level;
   a.perm = nullptr;
   a.io.work = h->d_work;
-  if (h->binning && !io.force_reset && h->num_envs > 2 * W) {
+  if (h->binning && !sc && !io.force_reset && h->num_envs > 2 * W) {
     fly_bin_kernel<<<1, 1024, 0, st>>>(h->d_work, h->d_perm, h->num_envs);
     a.perm = h->d_perm;
     h->launches++;
   }
-  CK(cudaMemsetAsync(h->d_counter, 0, sizeof(int), st));
+  CK(cudaMemsetAsync(a.counter, 0, sizeof(int), st));
   void* kargs[3] = {(void*)&h->m, (void*)&a, (void*)&off};
   CK(cudaLaunchKernel(kern, dim3(grid), dim3(W * 32), kargs, smem, st));
   CK(cudaGetLastError());
@@ -195,6 +226,11 @@ int flyb_create(const FlybModel* model, int num_envs, int device, uint64_t seed,
   cudaDeviceProp prop;
   if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return fail("cudaGetDeviceProperties failed");
   h->sm_count = prop.multiProcessorCount;
+  {  /* set-up of flyb_step_noalloc: device address of the static scratch, once per device, with that device current */
+    std::string e;
+    h->noalloc_scratch = noalloc_scratch_of(device, &e);
+    if (!h->noalloc_scratch) return fail(e);
+  }
   FlyArena arena;
   std::string e = build_dmodel<float>(model, flags & 0xffff, &h->m, &arena);
   if (!e.empty()) return fail(e);
@@ -382,6 +418,32 @@ int flyb_step(flyb_handle h, const float* action, float* obs, float* reward, flo
               void* stream) {
   FlyIO<float> io = make_io(h, action, obs, reward, discount, step_type);
   return launch(h, io, (cudaStream_t)stream);
+}
+
+int flyb_step_noalloc(flyb_handle h, const float* action, float* obs, float* reward, float* discount, int32_t* step_type,
+                      void* stream) {
+  /* no cudaMalloc / cudaFree / allocating library call on this path: the workspace slots and the work counter live in
+     g_noalloc_scratch (address resolved at flyb_create); launch() only sets a function attribute, queries occupancy,
+     clears the counter (cudaMemsetAsync) and launches */
+  if (h->num_envs > FLYB_NOALLOC_MAX_ENVS) {
+    h->err = "flyb_step_noalloc: num_envs " + std::to_string(h->num_envs) + " exceeds FLYB_NOALLOC_MAX_ENVS (" +
+             std::to_string(FLYB_NOALLOC_MAX_ENVS) + "); use flyb_step";
+    return 1;
+  }
+  if (!h->noalloc_scratch) { h->err = "flyb_step_noalloc: static scratch was not resolved at flyb_create"; return 1; }
+  const size_t room = (size_t)FLYB_NOALLOC_SCRATCH_BYTES - FLYB_NOALLOC_HEADER;
+  const int slots = (int)(room / h->bulk_stride);
+  if (slots < h->warps) {
+    h->err = "flyb_step_noalloc: the workspace of one block (" + std::to_string((size_t)h->warps * h->bulk_stride) +
+             " bytes) exceeds FLYB_NOALLOC_SCRATCH_BYTES (" + std::to_string((size_t)FLYB_NOALLOC_SCRATCH_BYTES) + ")";
+    return 1;
+  }
+  LaunchScratch sc;
+  sc.counter = (int*)h->noalloc_scratch;
+  sc.bulk = (char*)h->noalloc_scratch + FLYB_NOALLOC_HEADER;
+  sc.slots = slots;
+  FlyIO<float> io = make_io(h, action, obs, reward, discount, step_type);
+  return launch(h, io, (cudaStream_t)stream, &sc);
 }
 
 int flyb_reset_host(flyb_handle h, const uint8_t* mask, float* obs, int32_t* step_type) {

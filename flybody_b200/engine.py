@@ -26,7 +26,7 @@ FLAG_TRACE = 1 << 16
 EXPORTS = ["flyb_create", "flyb_destroy", "flyb_last_error", "flyb_info", "flyb_configure", "flyb_load_clips",
            "flyb_set_clip_ids", "flyb_reset", "flyb_step", "flyb_reset_host", "flyb_step_host", "flyb_get_state",
            "flyb_set_state", "flyb_get_trace", "flyb_episode_stats", "flyb_load_wbpg", "flyb_set_wbpg_phase",
-           "flyb_use_generic_kernel"]
+           "flyb_use_generic_kernel", "flyb_step_noalloc"]
 
 
 KERNEL_CONFIGS = [(16, 1), (14, 1), (12, 1), (8, 2), (6, 3)]   # generic kernels (csrc/fly_kernel.cuh: FLY_KERNEL_CONFIGS)
@@ -95,6 +95,7 @@ def lib():
         # device-pointer entry points take raw addresses (torch tensor.data_ptr()) and a raw cudaStream_t
         L.flyb_reset.argtypes = [vp, vp, vp, vp, vp]
         L.flyb_step.argtypes = [vp, vp, vp, vp, vp, vp, vp]
+        L.flyb_step_noalloc.argtypes = [vp, vp, vp, vp, vp, vp, vp]
         L.flyb_reset_host.argtypes = [vp, u8p, fp, ip]
         L.flyb_step_host.argtypes = [vp, fp, fp, fp, fp, ip]
         L.flyb_get_state.argtypes = [vp, fp, fp, fp, fp, ip]
@@ -186,6 +187,10 @@ class Engine:
 
     def step_ptr(self, action_ptr, obs_ptr, reward_ptr, discount_ptr, step_type_ptr, stream=0):
         self._ck(lib().flyb_step(self._h, action_ptr, obs_ptr, reward_ptr, discount_ptr, step_type_ptr, stream))
+
+    def step_noalloc_ptr(self, action_ptr, obs_ptr, reward_ptr, discount_ptr, step_type_ptr, stream=0):
+        """flyb_step with the kernel's scratch in the library's static device array: the call allocates nothing (flyb.h)."""
+        self._ck(lib().flyb_step_noalloc(self._h, action_ptr, obs_ptr, reward_ptr, discount_ptr, step_type_ptr, stream))
 
     # ---- host (numpy) calls
     def reset_host(self, mask=None):

@@ -87,6 +87,24 @@ int flyb_reset(flyb_handle h, const uint8_t* mask, float* obs, int32_t* step_typ
 int flyb_step(flyb_handle h, const float* action, float* obs, float* reward, float* discount, int32_t* step_type,
               void* stream);
 
+/* flyb_step for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid allocation).  No counterpart in the reference.  Same arguments,
+ * results and stream semantics as flyb_step (device pointers, caller-owned inputs and outputs), but the step kernel's
+ * scratch memory - the per-warp workspace slots and the work counter, which flyb_step keeps in buffers that flyb_create
+ * cudaMalloc'ed - lives in a file-scope `static __device__` array of FLYB_NOALLOC_SCRATCH_BYTES inside the library (every
+ * GPU that loads the library holds it until exit; its device address is resolved with cudaGetSymbolAddress at flyb_create).
+ * The call itself allocates nothing: no cudaMalloc, cudaFree or allocating library routine.
+ * Limits: handles with more than FLYB_NOALLOC_MAX_ENVS environments, or whose one-block workspace does not fit the array,
+ * are rejected with an error (flyb_last_error).  The array holds few workspace slots, so fewer blocks run than under
+ * flyb_step: this entry point is for small batches.
+ * Sharing: every call on a device uses the same array, which keeps the previous call's contents; the work counter is
+ * cleared by each call (the workspace needs no clearing: every stage writes what it reads).  Calls that overlap on the
+ * GPU - two streams, or two handles on one device - race on the array; serialise them. */
+#define FLYB_NOALLOC_SCRATCH_BYTES (16u << 20)
+#define FLYB_NOALLOC_MAX_ENVS 1024
+int flyb_step_noalloc(flyb_handle h, const float* action, float* obs, float* reward, float* discount, int32_t* step_type,
+                      void* stream);
+
 /* Host-pointer API (what a numpy caller uses): copies through pinned staging buffers, synchronises. */
 int flyb_reset_host(flyb_handle h, const uint8_t* mask, float* obs, int32_t* step_type);
 /* Host-pointer variants: page-locked caller buffers are DMA targets themselves, pageable ones are staged. */
