@@ -189,11 +189,11 @@ template <class T> struct Supp { T v[3], v1[3]; };  /* Minkowski-difference poin
 /* The portal (centre point + three vertices) of one lane's search lives in a scratch array shared by the warp, element e of
  * lane l at [e * 32 + l]: the vertices are replaced through a computed index, which in thread-local arrays means local
  * memory; in shared memory it is an LDS.  The geoms' poses follow it in the same scratch (FLY_GEOM_WORDS). */
-#define FLY_PORTAL_WORDS (4 * 6 * 32)   /* float64 words of portal scratch per warp */
-#define FLY_GEOM_WORDS (24 * 32)        /* working-precision words after it: pos1 mat1 pos2 mat2 per lane */
+#define FLY_PORTAL_WORDS (4 * 6 * FLY_NL)   /* float64 words of portal scratch per warp */
+#define FLY_GEOM_WORDS (24 * FLY_NL)        /* working-precision words after it: pos1 mat1 pos2 mat2 per lane */
 template <class T> struct Portal {
   T* s;
-  FLY_MEM T& at(int i, int e) const { return s[(i * 6 + e) * 32]; }
+  FLY_MEM T& at(int i, int e) const { return s[(i * 6 + e) * FLY_NL]; }
   FLY_MEM void get_v(int i, T* o) const { o[0] = at(i, 0); o[1] = at(i, 1); o[2] = at(i, 2); }
   FLY_MEM void get_v1(int i, T* o) const { o[0] = at(i, 3); o[1] = at(i, 4); o[2] = at(i, 5); }
   FLY_MEM void set(int i, const Supp<T>& p) const { for (int k = 0; k < 3; k++) { at(i, k) = p.v[k]; at(i, 3 + k) = p.v1[k]; } }
@@ -508,9 +508,9 @@ FLY_FN void fly_collision(const DModel<T>& m, const Ws<T>& w) {
     return !(reach < T(-1e-4));
   }, w.cand);
   FLY_SYNC();
-  /* narrow phase, 32 candidates per round; hits are appended in candidate order */
-  for (int base = 0; base < ncand; base += 32) {
-    const int nround = ncand - base < 32 ? ncand - base : 32;
+  /* narrow phase, FLY_NL candidates per round; hits are appended in candidate order */
+  for (int base = 0; base < ncand; base += FLY_NL) {
+    const int nround = ncand - base < FLY_NL ? ncand - base : FLY_NL;
     FLY_FOR(l, nround) {
       const int p = w.cand[base + l];
       const int pg = m.pair_geom[p], g1 = pg & 255, g2 = (pg >> 8) & 255;
@@ -548,10 +548,10 @@ FLY_FN void fly_collision(const DModel<T>& m, const Ws<T>& w) {
         /* this lane's slice of the warp scratch: portal (float64) | pos1 mat1 pos2 mat2 (working precision) */
         const Portal<double> P = {(double*)w.qLD + FLY_LANE()};  /* qLD | qH: not live between fly_com_pos and fly_crb */
         T* gs = (T*)((double*)w.qLD + FLY_PORTAL_WORDS) + FLY_LANE();
-        for (int k = 0; k < 3; k++) { gs[k * 32] = c1[k]; gs[(12 + k) * 32] = c2[k]; }
-        for (int k = 0; k < 9; k++) { gs[(3 + k) * 32] = m1[k]; gs[(15 + k) * 32] = m2[k]; }
-        const CcdObj<double, T> o1 = {t1, gs, gs + 3 * 32, s1, 32, 0.5 * (double)margin};
-        const CcdObj<double, T> o2 = {t2, gs + 12 * 32, gs + 15 * 32, s2, 32, 0.5 * (double)margin};
+        for (int k = 0; k < 3; k++) { gs[k * FLY_NL] = c1[k]; gs[(12 + k) * FLY_NL] = c2[k]; }
+        for (int k = 0; k < 9; k++) { gs[(3 + k) * FLY_NL] = m1[k]; gs[(15 + k) * FLY_NL] = m2[k]; }
+        const CcdObj<double, T> o1 = {t1, gs, gs + 3 * FLY_NL, s1, FLY_NL, 0.5 * (double)margin};
+        const CcdObj<double, T> o2 = {t2, gs + 12 * FLY_NL, gs + 15 * FLY_NL, s2, FLY_NL, 0.5 * (double)margin};
         Hit<double> hd;
 #ifdef FLY_MPR_SKIP  /* kernel experiment: everything but the search itself */
         n = 0;
@@ -578,10 +578,10 @@ FLY_FN void fly_collision(const DModel<T>& m, const Ws<T>& w) {
     FLY_LANE0 {
       int s = 0;
       for (int l = 0; l < nround; l++) { w.hit_off[l] = s; s += w.hit_cnt[l]; }
-      w.hit_off[32] = s;
+      w.hit_off[FLY_NL] = s;
     }
     FLY_SYNC();
-    const int total = w.hit_off[32];
+    const int total = w.hit_off[FLY_NL];
     FLY_FOR(l, nround) {
       const int p = w.cand[base + l], n = w.hit_cnt[l];
       for (int i = 0; i < n; i++) {

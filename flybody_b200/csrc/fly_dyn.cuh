@@ -238,8 +238,8 @@ FLY_INL void fly_row_axpy(T* const* LD, int ai, int as, const T* t, int n) {
 template <class T, int NS>
 FLY_FN void fly_factor(const DModel<T>& m, T* const* LD, T* const* invD) {
   for (int st = 0; st < FLY_DIM(m, gsteps); st++) {
-    FLY_FOR(l, 32) {
-      const int word = FLY_LDG(m.gstep_b + st * 32 + l);
+    FLY_FOR(l, FLY_NL) {
+      const int word = FLY_LDG(m.gstep_b + st * FLY_NL + l);
       if (word >= 0) {
         const int k = word & 255, j = (word >> 8) & 31, g = (word >> 13) & 31, ak = word >> 18;
         const int hk = FLY_LDG(m.hdepth + k), dk = FLY_LDG(m.dof_din + k);
@@ -281,8 +281,8 @@ FLY_FN void fly_factor(const DModel<T>& m, T* const* LD, T* const* invD) {
       }
     }
     FLY_SYNC();
-    FLY_FOR(l, 32) {  /* normalise row k: U(k, ancestor) -> L(k, ancestor), in-branch part */
-      const int word = FLY_LDG(m.gstep_b + st * 32 + l);
+    FLY_FOR(l, FLY_NL) {  /* normalise row k: U(k, ancestor) -> L(k, ancestor), in-branch part */
+      const int word = FLY_LDG(m.gstep_b + st * FLY_NL + l);
       if (word >= 0) {
         const int k = word & 255, j = (word >> 8) & 31, g = (word >> 13) & 31, ak = word >> 18, dk = FLY_LDG(m.dof_din + k);
         for (int r = 1 + j; r <= dk; r += g) {
@@ -350,8 +350,8 @@ FLY_FN void fly_factor(const DModel<T>& m, T* const* LD, T* const* invD) {
 template <class T, int NS>
 FLY_FN void fly_solve(const DModel<T>& m, const Ws<T>& w, const T* const* LD, const T* const* invD, T* const* x) {
   for (int st = 0; st < FLY_DIM(m, gsteps); st++) {
-    FLY_FOR(l, 32) {
-      const int word = FLY_LDG(m.gstep_b + st * 32 + l);
+    FLY_FOR(l, FLY_NL) {
+      const int word = FLY_LDG(m.gstep_b + st * FLY_NL + l);
       if (word >= 0) {
         const int c = word & 255, j = (word >> 8) & 31, g = (word >> 13) & 31, a = word >> 18, dk = FLY_LDG(m.dof_din + c);
         T xc[NS];
@@ -433,8 +433,8 @@ FLY_FN void fly_solve(const DModel<T>& m, const Ws<T>& w, const T* const* LD, co
     FLY_SYNC();
   }
   for (int st = 0; st < FLY_DIM(m, gsteps); st++) {
-    FLY_FOR(l, 32) {
-      const int word = FLY_LDG(m.gstep_f + st * 32 + l);
+    FLY_FOR(l, FLY_NL) {
+      const int word = FLY_LDG(m.gstep_f + st * FLY_NL + l);
       if (word >= 0) {
         const int i = word & 255, j = (word >> 8) & 31, g = (word >> 13) & 31, a = word >> 18, dk = FLY_LDG(m.dof_din + i);
         T sum[NS];
@@ -447,7 +447,7 @@ FLY_FN void fly_solve(const DModel<T>& m, const Ws<T>& w, const T* const* LD, co
         }
         if (g > 1) {
 #pragma unroll
-          for (int s = 0; s < NS; s++) w.gpart[s * 32 + l] = sum[s];
+          for (int s = 0; s < NS; s++) w.gpart[s * FLY_NL + l] = sum[s];
         } else {
 #pragma unroll
           for (int s = 0; s < NS; s++) x[s][i] = x[s][i] * invD[s][i] - sum[s];
@@ -455,14 +455,14 @@ FLY_FN void fly_solve(const DModel<T>& m, const Ws<T>& w, const T* const* LD, co
       }
     }
     FLY_SYNC();
-    FLY_FOR(l, 32) {
-      const int word = FLY_LDG(m.gstep_f + st * 32 + l);
+    FLY_FOR(l, FLY_NL) {
+      const int word = FLY_LDG(m.gstep_f + st * FLY_NL + l);
       if (word >= 0 && ((word >> 8) & 31) == 0 && ((word >> 13) & 31) > 1) {
         const int i = word & 255, g = (word >> 13) & 31;
 #pragma unroll
         for (int s = 0; s < NS; s++) {
           T tot = 0;
-          for (int q = 0; q < g; q++) tot += w.gpart[s * 32 + l + q];
+          for (int q = 0; q < g; q++) tot += w.gpart[s * FLY_NL + l + q];
           x[s][i] = x[s][i] * invD[s][i] - tot;
         }
       }

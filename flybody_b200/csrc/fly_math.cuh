@@ -22,85 +22,111 @@
 #endif
 #define FLY_STAGE_SYNC(bit) do { if (FLY_SYNC_MASK & (1u << (bit))) FLY_BLOCK_SYNC(); } while (0)
 
+/* Lanes per environment.  FLY_NL = 32: one warp steps one env.  FLY_NL = 16 (8): a warp steps two (four) envs side by side,
+ * each on its own group of FLY_NL consecutive lanes - the semantics of cooperative_groups::tiled_partition<FLY_NL>: barriers,
+ * shuffles and ballots carry the group's lane mask, so the groups of a warp may run different control flow (different contact
+ * counts, solver iterations) and still share every instruction they execute in common.  Most stages have fewer than 16
+ * independent work items (profiles/r1_by_function_final.txt: 16.0 of 32 lanes active), and the register file, not the lane
+ * count, is what limits the envs resident on an SM: narrower groups put more envs behind the same registers. */
+#ifndef FLY_NL
+#define FLY_NL 32
+#endif
+#define FLY_SUBS (32 / FLY_NL)   /* envs per warp */
+
 #if defined(__CUDACC__) && !defined(FLY_EMU)
 #define FLY_GPU 1
 #define FLY_FN __device__ __forceinline__
 #define FLY_INL __device__ __forceinline__
 #define FLY_MEM __device__ __forceinline__   /* member functions */
 #define FLY_NOINL __device__ __noinline__     /* the few routines that want their own register allocation */
-#define FLY_LANE() ((int)(threadIdx.x & 31))
-#define FLY_FOR(i, n) for (int i = FLY_LANE(); i < (n); i += 32)
-#define FLY_SYNC() __syncwarp()
-/* 2-D work items over a 4 x 8 lane tile: rows i in [0,n) across lane / 8, columns j in [j0,n) across lane % 8 */
-#define FLY_FOR_ROW(i, n) for (int i = FLY_LANE() >> 3; i < (n); i += 4)
+#define FLY_LANE() ((int)(threadIdx.x & (FLY_NL - 1)))
+#if FLY_NL == 32
+#define FLY_SHIFT() 0
+#define FLY_MASK() 0xffffffffu
+#else
+#define FLY_SHIFT() ((int)(threadIdx.x & 31 & ~(FLY_NL - 1)))          /* first lane of this env's group */
+#define FLY_MASK() (((1u << FLY_NL) - 1u) << FLY_SHIFT())             /* the group's lanes */
+#endif
+#define FLY_SUB() ((int)((threadIdx.x & 31) / FLY_NL))                 /* which group of the warp */
+#define FLY_FOR(i, n) for (int i = FLY_LANE(); i < (n); i += FLY_NL)
+#define FLY_SYNC() __syncwarp(FLY_MASK())
+/* ballot over the group, bit l = lane l of the group */
+#define FLY_BALLOT(p) ((__ballot_sync(FLY_MASK(), (p)) >> FLY_SHIFT()) & (FLY_NL == 32 ? 0xffffffffu : ((1u << (FLY_NL & 31)) - 1u)))
+/* 2-D work items over a (FLY_NL / 8) x 8 lane tile: rows i in [0,n) across lane / 8, columns j in [j0,n) across lane % 8 */
+#define FLY_FOR_ROW(i, n) for (int i = FLY_LANE() >> 3; i < (n); i += FLY_NL / 8)
 #define FLY_FOR_COL(j, j0, n) for (int j = (j0) + (FLY_LANE() & 7); j < (n); j += 8)
-/* block-wide rendezvous of the warps of a block (each steps its own env): keeps them in the same stage so that
- * instruction fetches and model-table lines are shared in the SM's caches.  Every warp must pass the same number. */
+/* block-wide rendezvous of the warps of a block (each steps its own envs): keeps them in the same stage so that
+ * instruction fetches and model-table lines are shared in the SM's caches.  Every env must pass the same number.
+ * With several envs per warp the groups of a warp may arrive apart: the barrier is the per-thread (non-aligned) form. */
 #ifndef FLY_SYNC_GROUP
+#if FLY_NL == 32
 #define FLY_BLOCK_SYNC() __syncthreads()
+#else
+#define FLY_BLOCK_SYNC() asm volatile("barrier.sync 0;" ::: "memory")
+#endif
 #else  /* lockstep groups of FLY_SYNC_GROUP warps (named barriers 1..): smaller groups wait less for their slowest env */
 #define FLY_BLOCK_SYNC() \
-  asm volatile("bar.sync %0, %1;" ::"r"(1 + (int)(threadIdx.x >> 5) / FLY_SYNC_GROUP), "n"(FLY_SYNC_GROUP * 32) : "memory")
+  asm volatile("barrier.sync %0, %1;" ::"r"(1 + (int)(threadIdx.x >> 5) / FLY_SYNC_GROUP), "n"(FLY_SYNC_GROUP * 32) : "memory")
 #endif
 #define FLY_LANE0 if (FLY_LANE() == 0)
 #define FLY_LDG(p) __ldg(p)
 template <class T> FLY_INL T warp_sum(T v) {
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  for (int o = FLY_NL / 2; o > 0; o >>= 1) v += __shfl_xor_sync(FLY_MASK(), v, o);
   return v;
 }
 template <class T> FLY_INL T warp_max(T v) {
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) { T u = __shfl_xor_sync(0xffffffffu, v, o); v = u > v ? u : v; }
+  for (int o = FLY_NL / 2; o > 0; o >>= 1) { T u = __shfl_xor_sync(FLY_MASK(), v, o); v = u > v ? u : v; }
   return v;
 }
 FLY_INL int warp_sum_i(int v) {
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  for (int o = FLY_NL / 2; o > 0; o >>= 1) v += __shfl_xor_sync(FLY_MASK(), v, o);
   return v;
 }
 /* all-reduce of (value, index) pairs to the smallest value, lowest index on ties (numpy.argmin) */
 FLY_INL void warp_argmin(double& v, int& i) {
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    const double ov = __shfl_xor_sync(0xffffffffu, v, o);
-    const int oi = __shfl_xor_sync(0xffffffffu, i, o);
+  for (int o = FLY_NL / 2; o > 0; o >>= 1) {
+    const double ov = __shfl_xor_sync(FLY_MASK(), v, o);
+    const int oi = __shfl_xor_sync(FLY_MASK(), i, o);
     if (ov < v || (ov == v && oi < i)) { v = ov; i = oi; }
   }
 }
 /* ordered stream compaction of the items i in [0,n) with pred(i): writes their indices to out[], in order.  Four batches
- * of 32 items are evaluated before their ballots, so that the loads of four independent predicates are in flight together */
+ * of FLY_NL items are evaluated before their ballots, so that the loads of four independent predicates are in flight together */
 template <class P> FLY_INL int warp_compact(int n, P pred, unsigned short* out, int maxout) {
   int cnt = 0;
   const int lane = FLY_LANE();
-  for (int base = 0; base < n; base += 128) {
+  for (int base = 0; base < n; base += 4 * FLY_NL) {
     bool p[4];
 #pragma unroll
-    for (int u = 0; u < 4; u++) { const int i = base + 32 * u + lane; p[u] = i < n && pred(i); }
+    for (int u = 0; u < 4; u++) { const int i = base + FLY_NL * u + lane; p[u] = i < n && pred(i); }
 #pragma unroll
     for (int u = 0; u < 4; u++) {
-      const unsigned mask = __ballot_sync(0xffffffffu, p[u]);
+      const unsigned mask = FLY_BALLOT(p[u]);
       const int pos = cnt + __popc(mask & ((1u << lane) - 1u));
-      if (p[u] && pos < maxout) out[pos] = (unsigned short)(base + 32 * u + lane);
+      if (p[u] && pos < maxout) out[pos] = (unsigned short)(base + FLY_NL * u + lane);
       cnt += __popc(mask);
     }
   }
-  __syncwarp();
+  FLY_SYNC();
   return cnt;
 }
 /* ordered in-place filter of list[0..n): keeps the entries with pred(i), returns how many (a kept entry never moves up) */
 template <class P> FLY_INL int warp_filter(int n, P pred, unsigned short* list) {
   int cnt = 0;
   const int lane = FLY_LANE();
-  for (int base = 0; base < n; base += 32) {
+  for (int base = 0; base < n; base += FLY_NL) {
     const int i = base + lane;
     const unsigned short v = i < n ? list[i] : (unsigned short)0;
     const bool p = i < n && pred(i);
-    const unsigned mask = __ballot_sync(0xffffffffu, p);   /* every lane has read its entry before any lane writes */
+    const unsigned mask = FLY_BALLOT(p);   /* every lane has read its entry before any lane writes */
     if (p) list[cnt + __popc(mask & ((1u << lane) - 1u))] = v;
     cnt += __popc(mask);
   }
-  __syncwarp();
+  FLY_SYNC();
   return cnt;
 }
 #else

@@ -115,7 +115,7 @@ static inline void fly_quat2mat(const double* q, double* m) {
 /* Builds the model with pointer fields holding OFFSETS into `arena`; call fly_relocate() with the base
  * address the arena finally lives at (host or device).  Returns "" or an error message. */
 template <class T>
-std::string build_dmodel(const FlybModel* m, int flags, DModel<T>* out, FlyArena* arena) {
+std::string build_dmodel(const FlybModel* m, int flags, DModel<T>* out, FlyArena* arena, int nlanes = 32) {
   DModel<T>& d = *out;
   memset(&d, 0, sizeof(d));
 #define CP(n) d.n = m->n;
@@ -274,13 +274,13 @@ std::string build_dmodel(const FlybModel* m, int flags, DModel<T>* out, FlyArena
       const Branch& br = branches[order[a]];
       const size_t n = (size_t)(hsublast[br.root] - br.root + 1);
       /* a branch longer than half the longest one gets its own group; smaller ones are chained onto the cheapest group
-         that stays within the longest branch's step count (everything is chained once 24 groups exist) */
+         that stays within the longest branch's step count (everything is chained once three quarters of the lanes own a group) */
       int into = -1;
-      if (n * 2 <= max_steps || grp_dofs.size() >= 24)
+      if (n * 2 <= max_steps || (int)grp_dofs.size() >= nlanes * 3 / 4)
         for (size_t g = 0; g < grp_dofs.size(); g++)
           if (grp_dofs[g].size() + n <= max_steps && (into < 0 || grp_cost[g] < grp_cost[into])) into = (int)g;
       if (into < 0) {
-        if (grp_dofs.size() < 32) { grp_dofs.push_back(std::vector<int>()); grp_cost.push_back(0); into = (int)grp_dofs.size() - 1; }
+        if ((int)grp_dofs.size() < nlanes) { grp_dofs.push_back(std::vector<int>()); grp_cost.push_back(0); into = (int)grp_dofs.size() - 1; }
         else { into = 0; for (size_t g = 1; g < grp_dofs.size(); g++) if (grp_dofs[g].size() < grp_dofs[into].size()) into = (int)g; }
       }
       for (int c = br.root; c <= hsublast[br.root]; c++) grp_dofs[into].push_back(c);
@@ -289,7 +289,7 @@ std::string build_dmodel(const FlybModel* m, int flags, DModel<T>* out, FlyArena
   }
   const int ngrp = (int)grp_dofs.size();
   std::vector<int> grp_lanes(ngrp, 1);
-  for (int spare = 32 - ngrp; spare > 0; spare--) {  /* remaining lanes go where the per-lane work is largest */
+  for (int spare = nlanes - ngrp; spare > 0; spare--) {  /* remaining lanes go where the per-lane work is largest */
     int best = 0;
     for (int g = 1; g < ngrp; g++) if (grp_cost[g] * grp_lanes[best] > grp_cost[best] * grp_lanes[g]) best = g;
     if (grp_lanes[best] >= 8) {  /* more than 8 lanes on one row does not pay: look for another taker */
@@ -302,7 +302,7 @@ std::string build_dmodel(const FlybModel* m, int flags, DModel<T>* out, FlyArena
   }
   size_t gsteps = 0;
   for (int g = 0; g < ngrp; g++) { std::sort(grp_dofs[g].begin(), grp_dofs[g].end()); if (grp_dofs[g].size() > gsteps) gsteps = grp_dofs[g].size(); }
-  std::vector<int> gstep_f(gsteps * 32 + 1, -1), gstep_b(gsteps * 32 + 1, -1);
+  std::vector<int> gstep_f(gsteps * nlanes + 1, -1), gstep_b(gsteps * nlanes + 1, -1);
   {
     int lane0 = 0;
     for (int g = 0; g < ngrp; g++) {
@@ -310,11 +310,11 @@ std::string build_dmodel(const FlybModel* m, int flags, DModel<T>* out, FlyArena
       for (size_t q = 0; q < n; q++)
         for (int j = 0; j < grp_lanes[g]; j++) {
           const int i = grp_dofs[g][q], word = i | (j << 8) | (grp_lanes[g] << 13) | (madr[i] << 18);
-          gstep_f[q * 32 + lane0 + j] = word; gstep_b[(n - 1 - q) * 32 + lane0 + j] = word;
+          gstep_f[q * nlanes + lane0 + j] = word; gstep_b[(n - 1 - q) * nlanes + lane0 + j] = word;
         }
       lane0 += grp_lanes[g];
     }
-    if (lane0 > 32) return "internal: lane groups exceed the warp";
+    if (lane0 > nlanes) return "internal: lane groups exceed the lanes of an env";
   }
   d.gsteps = (int)gsteps;
   /* non-trunk dofs: address of the LAST entry of the row (the one towards trunk dof 0) | trunk ancestors << 11 | dof << 15 */

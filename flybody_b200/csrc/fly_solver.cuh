@@ -173,9 +173,9 @@ template <class T>
 FLY_INL void warp_argmax(T& v, int& idx) {
 #ifdef FLY_GPU
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    const T ov = __shfl_xor_sync(0xffffffffu, v, o);
-    const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
+  for (int o = FLY_NL / 2; o > 0; o >>= 1) {
+    const T ov = __shfl_xor_sync(FLY_MASK(), v, o);
+    const int oi = __shfl_xor_sync(FLY_MASK(), idx, o);
     if (ov > v || (ov == v && oi < idx)) { v = ov; idx = oi; }
   }
 #endif

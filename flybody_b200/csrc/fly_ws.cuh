@@ -9,8 +9,9 @@
 #include "fly_model.h"
 #include "fly_math.cuh"
 
-/* tier of an array: 0 = always bulk; 1..4 = goes to the fast arena when the launch's `level` is >= the tier
- * (1: the two factorisations and the vectors their solves run on; 2: state and solver vectors; 3, 4: kinematics) */
+/* tier of an array: 0 = always bulk; 1..5 = goes to the fast arena when the launch's `level` is >= the tier
+ * (1: the factorisation of M and the vectors its solves run on; 2: the factorisation of M + dt B; 3: state and solver
+ * vectors; 4, 5: kinematics) */
 #if defined(__CUDACC__)
 #define FLY_HD __host__ __device__ inline
 #else
@@ -19,26 +20,30 @@
 #define FLY_NHIT 4   /* most contacts a primitive pair can produce */
 
 /* qLD | qH (adjacent, same tier) double as the warp's portal scratch of the convex narrow phase (fly_col.cuh:
- * 4 points x 6 float64 x 32 lanes = 6144 B, then two geom poses x 12 words x 32 lanes), which runs while neither
- * factorisation is live; qLD is padded so that the two together always hold it (2304 words when T is float) */
-FLY_HD constexpr int fly_qld_count(int nM) { const int need = 2304 + 8 - (nM + 4); return nM + 1 > need ? nM + 1 : need; }
+ * 4 points x 6 float64 x nl lanes, then two geom poses x 12 words x nl lanes; nl = lanes per env, FLY_NL of the kernel), which runs while neither
+ * factorisation is live; qLD is padded so that the two together always hold it (72 nl words when T is float) */
+FLY_HD constexpr int fly_qld_count(int nM, int nl) {
+  /* nl <= 16: the scratch (72 nl words) fits qLD alone, so qH may live in another arena; nl = 32: qLD | qH hold it together */
+  const int need = nl <= 16 ? 72 * nl : 72 * nl + 8 - (nM + 4);
+  return nM + 1 > need ? nM + 1 : need;
+}
 
 /* X(name, element-count expression over `m`, tier) ; arrays of T */
 #define FLY_WS_REAL(X)                                                                                       \
-  X(qpos, m.nq, 2) X(qvel, m.nv, 2) X(act, m.na, 2) X(ctrl, m.nu, 2)             \
-  X(warm, m.nv, 2) X(qacc, m.nv, 2)                                                            \
-  X(xpos, 3 * m.nbody, 3) X(xquat, 4 * m.nbody, 3) X(xmat, 9 * m.nbody, 3)              \
-  X(xipos, 3 * m.nbody, 4)                                            \
+  X(qpos, m.nq, 3) X(qvel, m.nv, 3) X(act, m.na, 3) X(ctrl, m.nu, 3)             \
+  X(warm, m.nv, 3) X(qacc, m.nv, 3)                                                            \
+  X(xpos, 3 * m.nbody, 4) X(xquat, 4 * m.nbody, 4) X(xmat, 9 * m.nbody, 4)              \
+  X(xipos, 3 * m.nbody, 5)                                            \
   X(xanchor, 3 * m.njnt, 0) X(xaxis, 3 * m.njnt, 0)                                            \
-  X(geom_xpos, 3 * m.ngeom, 3) X(site_xpos, 3 * m.nsite, 0) X(site_xmat, 9 * m.nsite, 0)\
-  X(scom, 3 * m.nbody, 3) X(cinert, 10 * m.nbody, 4) X(crb, 0, 0)            \
-  X(cdof, 6 * m.nv, 3) X(cdof_dot, 6 * m.nv, 4) X(cvel, 6 * m.nbody, 4)                 \
-  X(qLD, fly_qld_count(m.nM), 1) X(qH, m.nM + 1, 1)                    \
-  X(qDinv, m.nv, 1) X(qHinv, m.nv, 1) X(gpart, 64, 0)                                         \
+  X(geom_xpos, 3 * m.ngeom, 4) X(site_xpos, 3 * m.nsite, 0) X(site_xmat, 9 * m.nsite, 0)\
+  X(scom, 3 * m.nbody, 4) X(cinert, 10 * m.nbody, 5) X(crb, 0, 0)            \
+  X(cdof, 6 * m.nv, 4) X(cdof_dot, 6 * m.nv, 5) X(cvel, 6 * m.nbody, 5)                 \
+  X(qLD, fly_qld_count(m.nM, nl), 1) X(qH, m.nM + 1, 2)                    \
+  X(qDinv, m.nv, 1) X(qHinv, m.nv, 2) X(gpart, 64, 0)                                         \
   X(act_length, m.nu, 0) X(act_force, m.nu, 0) X(act_dot, m.na, 0)                      \
   X(qfrc_bias, m.nv, 0) X(qfrc_passive, m.nv, 0) X(qfrc_actuator, m.nv, 0)              \
-  X(qfrc_smooth, m.nv, 2) X(qacc_smooth, m.nv, 1) X(qfrc_constraint, m.nv, 2)           \
-  X(sMa, m.nv, 1) X(sgrad, m.nv, 2) X(ssearch, m.nv, 2)          \
+  X(qfrc_smooth, m.nv, 3) X(qacc_smooth, m.nv, 1) X(qfrc_constraint, m.nv, 3)           \
+  X(sMa, m.nv, 1) X(sgrad, m.nv, 3) X(ssearch, m.nv, 3)          \
   X(stmp, m.nv, 1)                                                                                    \
   X(bodyf, 0, 0) X(boxf, 6 * (m.nfluidbox + m.nfluidgeom), 0)                        \
   X(cacc, 6 * m.nbody, 0) X(cfrc_int, 6 * m.nbody, 0) X(cfrc_ext, 6 * m.nbody, 0)       \
@@ -49,9 +54,9 @@ FLY_HD constexpr int fly_qld_count(int nM) { const int need = 2304 + 8 - (nM + 4
   X(efc_J, FLY_MAXEFC * FLY_MAXCHAIN, 0) X(efc_Y, FLY_MAXEFC * FLY_MAXCHAIN, 0)                \
   X(x_J, FLY_MAXCROSS * FLY_MAXCHAIN, 0) X(x_Y, FLY_MAXCROSS * FLY_MAXCHAIN, 0)                \
   X(efc_pos, FLY_MAXEFC, 0) X(efc_margin, FLY_MAXEFC, 0) X(efc_diag, FLY_MAXEFC, 0)     \
-  X(efc_R, FLY_MAXEFC, 0) X(efc_D, FLY_MAXEFC, 2) X(efc_K0, FLY_MAXEFC, 0)               \
+  X(efc_R, FLY_MAXEFC, 0) X(efc_D, FLY_MAXEFC, 3) X(efc_K0, FLY_MAXEFC, 0)               \
   X(efc_B, FLY_MAXEFC, 0) X(efc_imp, FLY_MAXEFC, 0) X(efc_aref, FLY_MAXEFC, 0)          \
-  X(efc_force, FLY_MAXEFC, 2)        \
+  X(efc_force, FLY_MAXEFC, 3)        \
   X(efc_A, FLY_MAXEFC * FLY_MAXEFC, 0) X(efc_K, FLY_MAXEFC * FLY_MAXEFC, 0)             \
           \
   X(efc_lam, FLY_MAXEFC, 0)                              \
@@ -60,7 +65,7 @@ FLY_HD constexpr int fly_qld_count(int nM) { const int need = 2304 + 8 - (nM + 4
 /* arrays of double: the Newton iterate in constraint space (c, jar = b + A c, ...) cancels to a few parts in 1e4
  * of its terms, so these nefc-sized vectors are kept in float64 even when T is float */
 #define FLY_WS_DBL(X)                                                                                        \
-  X(efc_jar, FLY_MAXEFC, 2) X(efc_jv, FLY_MAXEFC, 2) X(efc_b, FLY_MAXEFC, 0) X(efc_b0, FLY_MAXEFC, 0)        \
+  X(efc_jar, FLY_MAXEFC, 3) X(efc_jv, FLY_MAXEFC, 3) X(efc_b, FLY_MAXEFC, 0) X(efc_b0, FLY_MAXEFC, 0)        \
   X(efc_c, FLY_MAXEFC, 0) X(efc_cp, FLY_MAXEFC, 0) X(efc_Ac, FLY_MAXEFC, 0) X(efc_Acp, FLY_MAXEFC, 0)        \
   X(efc_h, FLY_MAXEFC, 0)
 
@@ -107,7 +112,7 @@ struct Ws {
 /* Carves the two arenas.  Pass null bases to only measure; sizes (bytes, 16-aligned) are returned. */
 template <class T>
 FLY_HD void ws_bind(const DModel<T>& m, Ws<T>* w, char* fast, char* bulk, size_t* fast_bytes, size_t* bulk_bytes,
-                    int level) {
+                    int level, int nl = 32) {
   size_t off[2] = {0, 0};
   char* base[2] = {bulk, fast};
 #define PLACE(n, cnt, tier, type)                                                    \
@@ -146,7 +151,7 @@ struct WsOff {
 };
 
 template <class T>
-inline void ws_layout(const DModel<T>& m, int level, WsOff* o, size_t* fast_bytes, size_t* bulk_bytes) {
+inline void ws_layout(const DModel<T>& m, int level, WsOff* o, size_t* fast_bytes, size_t* bulk_bytes, int nl = 32) {
   size_t off[2] = {0, 0};
 #define PLACE(n, cnt, tier, type)                                          \
   {                                                                        \
@@ -191,7 +196,7 @@ inline bool ws_dims_equal(const WsDims& a, const WsDims& b) {
          a.ntrunk == b.ntrunk && a.gsteps == b.gsteps && a.nlevel == b.nlevel;
 }
 template <class T>
-FLY_HD constexpr WsOff ws_layout_c(const WsDims m, int level) {
+FLY_HD constexpr WsOff ws_layout_c(const WsDims m, int level, int nl = 32) {
   WsOff o{};
   size_t off[2] = {0, 0};
 #define PLACE(n, cnt, tier, type)                                          \

@@ -33,7 +33,8 @@ struct FlybEngine {
   float *h_action = nullptr, *h_obs = nullptr, *h_rd = nullptr; int* h_st = nullptr; unsigned char* h_mask = nullptr;
   float *d_action = nullptr, *d_obs = nullptr, *d_rd = nullptr; int* d_st = nullptr; unsigned char* d_mask = nullptr;
   cudaStream_t host_stream = nullptr;
-  int smem_level = 1, warps = 16, blocks_per_sm = 0, sm_count = 148, grid = 0;
+  int smem_level = 0, warps = 28, blocks_per_sm = 0, sm_count = 148, grid = 0;
+  int lanes = 32;               /* lanes per env (FLY_NL of the kernels this handle launches): fixed at flyb_create */
   int spec = -1, no_spec = 0;   /* index of the model-specialised kernel in use (-1: generic); FLYB_NO_SPEC=1 forces generic */
   long long launches = 0;
   unsigned char* noalloc_scratch = nullptr;   /* device address of g_noalloc_scratch on h->device (flyb_step_noalloc) */
@@ -51,13 +52,12 @@ static std::string g_create_error;
     }                                                                                              \
   } while (0)
 
-/* the kernels live in their own translation units (flyb_kern.cu); each exports one getter */
-#define X(W, L) extern "C" const void* flyb_kernel_##W##_##L##_g();
-FLY_KERNEL_CONFIGS(X)
-#undef X
-#define X(i, ...) extern "C" const void* flyb_kernel_16_1_s##i();
-FLY_SPEC_MODELS(X)
-#undef X
+/* the kernels live in their own translation units (flyb_kern.cu); each registers itself at load time */
+struct FlyKernelEntry { int lanes, warps, level, spec; const void* fn; };
+static std::vector<FlyKernelEntry>& kernel_registry() { static std::vector<FlyKernelEntry> r; return r; }
+void fly_register_kernel(int lanes, int warps, int level, int spec, const void* fn) {
+  kernel_registry().push_back(FlyKernelEntry{lanes, warps, level, spec, fn});
+}
 static int spec_of(const DModel<float>& m) {
   const WsDims d = ws_dims_of(m);
 #define X(i, ...) { const WsDims t = {__VA_ARGS__}; if (ws_dims_equal(d, t)) return i; }
@@ -65,15 +65,9 @@ static int spec_of(const DModel<float>& m) {
 #undef X
   return -1;
 }
-static const void* pick_kernel(int warps, int level, int spec = -1) {
-  if (warps == FLY_SPEC_WARPS && level == FLY_SPEC_LEVEL) {
-#define X(i, ...) if (spec == i) return flyb_kernel_16_1_s##i();
-    FLY_SPEC_MODELS(X)
-#undef X
-  }
-#define X(W, L) if (warps == W && level == L) return flyb_kernel_##W##_##L##_g();
-  FLY_KERNEL_CONFIGS(X)
-#undef X
+static const void* pick_kernel(int lanes, int warps, int level, int spec) {
+  for (const FlyKernelEntry& e : kernel_registry())
+    if (e.lanes == lanes && e.warps == warps && e.level == level && e.spec == spec) return e.fn;
   return nullptr;
 }
 
@@ -139,39 +133,41 @@ static int launch(FlybEngine* h, const FlyIO<float>& io, cudaStream_t st, const 
   CK(cudaSetDevice(h->device));
   size_t fb = 0, bb = 0;
   WsOff off;
-  ws_layout<float>(h->m, h->smem_level, &off, &fb, &bb);
+  ws_layout<float>(h->m, h->smem_level, &off, &fb, &bb, h->lanes);
   h->fast_stride = fb;
-  const int W = h->warps;
-  const size_t smem = fb * W;
+  const int W = h->warps, EPB = W * (32 / h->lanes);   /* envs per block */
+  const size_t smem = fb * EPB;
   if (smem > 227 * 1024 - 2048) { h->err = "shared memory request too large for this smem_level / warps_per_block"; return 1; }
   if (bb > h->bulk_stride) { h->err = "internal: bulk slot too small"; return 1; }
-  {  /* the convex narrow phase borrows qLD | qH as one scratch block (fly_col.cuh): they must be adjacent and large enough */
-    const size_t need = FLY_PORTAL_WORDS * sizeof(double) + FLY_GEOM_WORDS * sizeof(float);
-    if (off.qH < off.qLD || (size_t)(off.qH - off.qLD) + (size_t)(h->m.nM + 1) * sizeof(float) < need) {
-      h->err = "internal: qLD | qH cannot hold the convex narrow phase's scratch"; return 1;
-    }
+  {  /* the convex narrow phase borrows qLD (| qH when they share an arena) as one scratch block (fly_col.cuh) */
+    const size_t need = (size_t)(4 * 6 * h->lanes) * sizeof(double) + (size_t)(24 * h->lanes) * sizeof(float);
+    const bool alone = (size_t)fly_qld_count(h->m.nM, h->lanes) * sizeof(float) >= need;
+    const bool together = (h->smem_level == 0 || h->smem_level >= 2) && off.qH >= off.qLD &&
+                          (size_t)(off.qH - off.qLD) + (size_t)(h->m.nM + 1) * sizeof(float) >= need;
+    if (!alone && !together) { h->err = "this smem_level leaves no room for the convex narrow phase's scratch (32 lanes per env need smem_level 0 or >= 2)"; return 1; }
   }
-  const int spec = h->no_spec ? -1 : spec_of(h->m);
-  const void* kern = pick_kernel(W, h->smem_level, spec);
-  h->spec = (W == FLY_SPEC_WARPS && h->smem_level == FLY_SPEC_LEVEL) ? spec : -1;
+  int spec = h->no_spec ? -1 : spec_of(h->m);
+  const void* kern = pick_kernel(h->lanes, W, h->smem_level, spec);
+  if (!kern && spec >= 0) { spec = -1; kern = pick_kernel(h->lanes, W, h->smem_level, -1); }
+  h->spec = spec;
   if (h->spec >= 0) {  /* the compile-time layout must be the one the host sized the arenas with */
     WsOff c = {};
-#define X(i, ...) if (h->spec == i) { const WsDims t = {__VA_ARGS__}; c = ws_layout_c<float>(t, FLY_SPEC_LEVEL); }
+#define X(i, ...) if (h->spec == i) { const WsDims t = {__VA_ARGS__}; c = ws_layout_c<float>(t, h->smem_level, h->lanes); }
     FLY_SPEC_MODELS(X)
 #undef X
     if (memcmp(&c, &off, sizeof(WsOff)) != 0) { h->err = "internal: compile-time workspace layout differs from the run-time one"; return 1; }
   }
-  if (!kern) { h->err = "this (warps_per_block, smem_level) pair is not compiled in; see FLY_KERNEL_CONFIGS"; return 1; }
+  if (!kern) { h->err = "no step kernel compiled for this (lanes, warps_per_block, smem_level); see KERNEL_UNITS in flybody_b200/engine.py"; return 1; }
   CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int per_sm = 0;
   CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, W * 32, smem));
   if (per_sm < 1) { h->err = "kernel does not fit on an SM"; return 1; }
   if (h->blocks_per_sm > 0 && h->blocks_per_sm < per_sm) per_sm = h->blocks_per_sm;
   int grid = h->sm_count * per_sm;
-  const int need = (h->num_envs + W - 1) / W;
+  const int need = (h->num_envs + EPB - 1) / EPB;
   if (grid > need) grid = need;
   const int slots = sc ? sc->slots : h->bulk_slots;
-  if (grid * W > slots) grid = slots / W;
+  if (grid * EPB > slots) grid = slots / EPB;
   if (grid < 1) { h->err = "scratch too small for one block of this launch configuration"; return 1; }
   h->grid = grid;
   KArgs a;
@@ -183,7 +179,7 @@ static int launch(FlybEngine* h, const FlyIO<float>& io, cudaStream_t st, const 
   a.num_envs = h->num_envs; a.level = h->smem_level;
   a.perm = nullptr;
   a.io.work = h->d_work;
-  if (h->binning && !sc && !io.force_reset && h->num_envs > 2 * W) {
+  if (h->binning && !sc && !io.force_reset && h->num_envs > 2 * EPB) {
     fly_bin_kernel<<<1, 1024, 0, st>>>(h->d_work, h->d_perm, h->num_envs);
     a.perm = h->d_perm;
     h->launches++;
@@ -232,7 +228,10 @@ int flyb_create(const FlybModel* model, int num_envs, int device, uint64_t seed,
     if (!h->noalloc_scratch) return fail(e);
   }
   FlyArena arena;
-  std::string e = build_dmodel<float>(model, flags & 0xffff, &h->m, &arena);
+  if (flags & FLYB_FLAG_LANES16) h->lanes = 16;
+  { const char* e = getenv("FLYB_LANES"); if (e) h->lanes = atoi(e); }   /* kernel experiments */
+  if (h->lanes != 32 && h->lanes != 16 && h->lanes != 8) return fail("FLYB_LANES must be 32, 16 or 8");
+  std::string e = build_dmodel<float>(model, flags & 0xffff, &h->m, &arena, h->lanes);
   if (!e.empty()) return fail(e);
 #define CKC(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(std::string(#call) + ": " + cudaGetErrorString(e_)); } while (0)
   CKC(cudaMalloc(&h->d_arena, arena.buf.size()));
@@ -260,10 +259,10 @@ int flyb_create(const FlybModel* model, int num_envs, int device, uint64_t seed,
   }
   /* scratch slots: one per resident warp, sized for the all-bulk layout so any smem_level fits */
   size_t fb = 0, bb = 0;
-  ws_bind<float>(m, nullptr, nullptr, nullptr, &fb, &bb, 0);
+  ws_bind<float>(m, nullptr, nullptr, nullptr, &fb, &bb, 0, h->lanes);
   h->bulk_stride = (bb + 255) & ~(size_t)255;
-  h->bulk_slots = h->sm_count * 32;
-  if ((size_t)h->bulk_slots > N + 32) h->bulk_slots = (int)((N + 31) & ~(size_t)31);  /* whole blocks of up to 32 warps */
+  h->bulk_slots = h->sm_count * 32 * (32 / h->lanes);
+  if ((size_t)h->bulk_slots > N + 128) h->bulk_slots = (int)((N + 127) & ~(size_t)127);  /* whole blocks of up to 128 envs */
   CKC(cudaMalloc(&h->d_bulk, (size_t)h->bulk_slots * h->bulk_stride));
   CKC(cudaMemset(h->d_bulk, 0, (size_t)h->bulk_slots * h->bulk_stride));
   CKC(cudaMalloc(&h->d_counter, sizeof(int)));
@@ -319,7 +318,7 @@ int64_t flyb_info(flyb_handle h, int what) {
     case FLYB_INFO_TRACE_INTS: return FLY_TR_INTS;
     case FLYB_INFO_TRACE_REALS: return h->trace_real_stride;
     case FLYB_INFO_LAUNCHES: return h->launches;
-    case FLYB_INFO_SMEM_BYTES: return (int64_t)(h->fast_stride * h->warps);
+    case FLYB_INFO_SMEM_BYTES: return (int64_t)(h->fast_stride * h->warps * (32 / h->lanes));
     case FLYB_INFO_BULK_BYTES: return (int64_t)h->bulk_stride;
     case FLYB_INFO_GRID: return h->grid;
     case FLYB_INFO_MAXCON: return FLY_MAXCON;
@@ -328,14 +327,15 @@ int64_t flyb_info(flyb_handle h, int what) {
     case FLYB_INFO_WARPS_PER_BLOCK: return h->warps;
     case FLYB_INFO_SMEM_LEVEL: return h->smem_level;
     case FLYB_INFO_SPEC_KERNEL: return h->spec;
+    case FLYB_INFO_LANES: return h->lanes;
   }
   return -1;
 }
 
 int flyb_configure(flyb_handle h, int smem_level, int warps_per_block, int blocks_per_sm) {
-  if (smem_level < 0 || smem_level > 4) { h->err = "smem_level must be 0..4"; return 1; }
-  if (!pick_kernel(warps_per_block, smem_level)) {
-    h->err = "this (smem_level, warps_per_block) pair is not compiled in; see FLY_KERNEL_CONFIGS in flyb_cuda.cu"; return 1;
+  if (smem_level < 0 || smem_level > 5) { h->err = "smem_level must be 0..5"; return 1; }
+  if (!pick_kernel(h->lanes, warps_per_block, smem_level, -1) && !pick_kernel(h->lanes, warps_per_block, smem_level, spec_of(h->m))) {
+    h->err = "no step kernel compiled for this (lanes, warps_per_block, smem_level); see KERNEL_UNITS in flybody_b200/engine.py"; return 1;
   }
   h->smem_level = smem_level; h->warps = warps_per_block; h->blocks_per_sm = blocks_per_sm;
   return 0;
@@ -433,8 +433,8 @@ int flyb_step_noalloc(flyb_handle h, const float* action, float* obs, float* rew
   if (!h->noalloc_scratch) { h->err = "flyb_step_noalloc: static scratch was not resolved at flyb_create"; return 1; }
   const size_t room = (size_t)FLYB_NOALLOC_SCRATCH_BYTES - FLYB_NOALLOC_HEADER;
   const int slots = (int)(room / h->bulk_stride);
-  if (slots < h->warps) {
-    h->err = "flyb_step_noalloc: the workspace of one block (" + std::to_string((size_t)h->warps * h->bulk_stride) +
+  if (slots < h->warps * (32 / h->lanes)) {
+    h->err = "flyb_step_noalloc: the workspace of one block (" + std::to_string((size_t)h->warps * (32 / h->lanes) * h->bulk_stride) +
              " bytes) exceeds FLYB_NOALLOC_SCRATCH_BYTES (" + std::to_string((size_t)FLYB_NOALLOC_SCRATCH_BYTES) + ")";
     return 1;
   }

@@ -19,9 +19,10 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
 
 FLAG_NOCONTACT, FLAG_NOLIMIT, FLAG_NOFLUID, FLAG_NONOSLIP, FLAG_NOACTUATION, FLAG_NOWARMSTART = 1, 2, 4, 8, 16, 32
 FLAG_TRACE = 1 << 16
+FLAG_LANES16 = 1 << 17
 (INFO_NUM_ENVS, INFO_OBS_DIM, INFO_ACTION_DIM, INFO_NQ, INFO_NV, INFO_NA, INFO_TRACE_INTS, INFO_TRACE_REALS,
  INFO_LAUNCHES, INFO_SMEM_BYTES, INFO_BULK_BYTES, INFO_GRID, INFO_MAXCON, INFO_MAXEFC, INFO_STATE_INTS,
- INFO_WARPS_PER_BLOCK, INFO_SMEM_LEVEL, INFO_SPEC_KERNEL) = range(18)
+ INFO_WARPS_PER_BLOCK, INFO_SMEM_LEVEL, INFO_SPEC_KERNEL, INFO_LANES) = range(19)
 
 EXPORTS = ["flyb_create", "flyb_destroy", "flyb_last_error", "flyb_info", "flyb_configure", "flyb_load_clips",
            "flyb_set_clip_ids", "flyb_reset", "flyb_step", "flyb_reset_host", "flyb_step_host", "flyb_get_state",
@@ -29,23 +30,32 @@ EXPORTS = ["flyb_create", "flyb_destroy", "flyb_last_error", "flyb_info", "flyb_
            "flyb_use_generic_kernel", "flyb_step_noalloc"]
 
 
-KERNEL_CONFIGS = [(16, 1), (14, 1), (12, 1), (8, 2), (6, 3)]   # generic kernels (csrc/fly_kernel.cuh: FLY_KERNEL_CONFIGS)
-N_SPEC_MODELS = 4                                                # csrc/fly_dims_gen.h: FLY_SPEC_COUNT
+N_SPEC_MODELS = 4   # csrc/fly_dims_gen.h: FLY_SPEC_COUNT
+# Step-kernel instantiations built into the library: (lanes per env, warps per block, shared-memory level, model index or -1 = any
+# model).  Each is a translation unit of its own (csrc/flyb_kern.cu) that registers its kernel when the library is loaded.
+KERNEL_UNITS = ([(32, 28, 0, i) for i in range(N_SPEC_MODELS)]             # the default: one per shipped task model
+                + [(32, 28, 0, -1), (32, 16, 2, -1), (32, 8, 3, -1)]          # any model; other launch configurations
+                + [(16, 16, 0, -1)])                                          # two envs per warp (FLAG_LANES16)
 
 
-def compile_library(out_path: str, extra_flags=(), verbose: bool = False) -> str:
+def kernel_units():
+    """KERNEL_UNITS, or the subset / extra units named in FLYB_BUILD_UNITS ("lanes:warps:level:spec,...") for kernel experiments."""
+    e = os.environ.get("FLYB_BUILD_UNITS")
+    if not e:
+        return list(KERNEL_UNITS)
+    return [tuple(int(x) for x in u.split(":")) for u in e.split(",") if u]
+
+
+def compile_library(out_path: str, extra_flags=(), verbose: bool = False, units=None) -> str:
     """nvcc (sm_100a, -lineinfo): flyb_cuda.cu plus one translation unit per step-kernel instantiation (flyb_kern.cu), the
     compiles running in parallel, linked into `out_path`."""
     import tempfile
     from concurrent.futures import ThreadPoolExecutor
     flags = [f for f in NVCC_FLAGS if f != "-shared"] + list(extra_flags) + (["-Xptxas", "-v"] if verbose else [])
-    units = [("flyb_cuda", "flyb_cuda.cu", [])]
-    for w, l in KERNEL_CONFIGS:
-        units.append((f"k_{w}_{l}_g", "flyb_kern.cu", [f"-DFLY_TU_WARPS={w}", f"-DFLY_TU_LEVEL={l}", "-DFLY_TU_SPEC=-1",
-                                                         f"-DFLY_TU_NAME=flyb_kernel_{w}_{l}_g"]))
-    for i in range(N_SPEC_MODELS):
-        units.append((f"k_16_1_s{i}", "flyb_kern.cu", ["-DFLY_TU_WARPS=16", "-DFLY_TU_LEVEL=1", f"-DFLY_TU_SPEC={i}",
-                                                        f"-DFLY_TU_NAME=flyb_kernel_16_1_s{i}"]))
+    tus = [("flyb_cuda", "flyb_cuda.cu", [])]
+    for nl, w, l, sp in (units if units is not None else kernel_units()):
+        tus.append((f"k_{nl}_{w}_{l}_{'g' if sp < 0 else 's%d' % sp}", "flyb_kern.cu",
+                    [f"-DFLY_NL={nl}", f"-DFLY_TU_WARPS={w}", f"-DFLY_TU_LEVEL={l}", f"-DFLY_TU_SPEC={sp}"]))
     with tempfile.TemporaryDirectory() as tmp:
         def one(u):
             # a stub source per unit so that every embedded cubin has a name of its own (cuobjdump -xelf, ncu tooling)
@@ -54,8 +64,8 @@ def compile_library(out_path: str, extra_flags=(), verbose: bool = False) -> str
                 f.write('#include "%s"\n' % os.path.join(CSRC, u[1]))
             subprocess.check_call(["nvcc"] + flags + u[2] + ["-I", CSRC, "-c", "-o", obj, src])
             return obj
-        with ThreadPoolExecutor(max_workers=max(1, min(len(units), os.cpu_count() or 1))) as ex:
-            objs = list(ex.map(one, units))
+        with ThreadPoolExecutor(max_workers=max(1, min(len(tus), os.cpu_count() or 1))) as ex:
+            objs = list(ex.map(one, tus))
         subprocess.check_call(["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", out_path] + objs)
     return out_path
 

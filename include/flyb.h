@@ -38,13 +38,15 @@ typedef struct FlybEngine* flyb_handle;
 enum { FLYB_STEP_FIRST = 0, FLYB_STEP_MID = 1, FLYB_STEP_LAST = 2 };
 /* flags for flyb_create (tests switch stages off to isolate them) */
 enum { FLYB_FLAG_NOCONTACT = 1, FLYB_FLAG_NOLIMIT = 2, FLYB_FLAG_NOFLUID = 4, FLYB_FLAG_NONOSLIP = 8,
-       FLYB_FLAG_NOACTUATION = 16, FLYB_FLAG_NOWARMSTART = 32, FLYB_FLAG_TRACE = 1 << 16 };
+       FLYB_FLAG_NOACTUATION = 16, FLYB_FLAG_NOWARMSTART = 32, FLYB_FLAG_TRACE = 1 << 16,
+       FLYB_FLAG_LANES16 = 1 << 17 /* two envs per warp, 16 lanes each (csrc/fly_math.cuh: FLY_NL); default: one env per warp */ };
 /* flyb_info selectors */
 enum { FLYB_INFO_NUM_ENVS = 0, FLYB_INFO_OBS_DIM, FLYB_INFO_ACTION_DIM, FLYB_INFO_NQ, FLYB_INFO_NV, FLYB_INFO_NA,
        FLYB_INFO_TRACE_INTS, FLYB_INFO_TRACE_REALS, FLYB_INFO_LAUNCHES, FLYB_INFO_SMEM_BYTES, FLYB_INFO_BULK_BYTES,
        FLYB_INFO_GRID, FLYB_INFO_MAXCON, FLYB_INFO_MAXEFC, FLYB_INFO_STATE_INTS, FLYB_INFO_WARPS_PER_BLOCK,
        FLYB_INFO_SMEM_LEVEL,
-       FLYB_INFO_SPEC_KERNEL /* after a launch: index of the model-specialised step kernel in use, -1 = generic */ };
+       FLYB_INFO_SPEC_KERNEL /* after a launch: index of the model-specialised step kernel in use, -1 = generic */,
+       FLYB_INFO_LANES /* lanes of a warp that step one env: 32 (one env per warp), 16 or 8 (two / four envs per warp) */ };
 
 /* Compiles `model` for the device and allocates state for num_envs environments on CUDA device `device`.
  * env_offset is the global index of this shard's first env (multi-GPU: rank * num_envs); it only enters the
@@ -55,8 +57,9 @@ void flyb_destroy(flyb_handle h);
 const char* flyb_last_error(flyb_handle h);  /* h may be NULL: error of the last failed flyb_create */
 int64_t flyb_info(flyb_handle h, int what);
 
-/* Tuning knobs: smem_level 0..4 (how many workspace tiers live in shared memory) and warps per block; only the pairs
- * blocks per SM (0 = as many as fit).  Takes effect at the next launch. */
+/* Tuning knobs: smem_level 0..5 (how many workspace tiers live in shared memory, csrc/fly_ws.cuh; default 0: the whole
+ * workspace in per-warp global scratch behind a full-size L1, 28 warps per SM), warps per block (only the combinations built into the library: KERNEL_UNITS in
+ * flybody_b200/engine.py) and blocks per SM (0 = as many as fit).  Takes effect at the next launch. */
 int flyb_configure(flyb_handle h, int smem_level, int warps_per_block, int blocks_per_sm);
 /* The default configuration runs a step kernel compiled for the model's array sizes when the model is one of the shipped task
  * models (workspace offsets are immediates: 25 % faster); generic != 0 forces the any-model kernel.  The two agree to float32

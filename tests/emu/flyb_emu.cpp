@@ -124,6 +124,7 @@ struct Emu : EmuBase {
   int get(const char* name, double* out, int cap) override {
     size_t fb, bb;
     (void)fb; (void)bb;
+    const int nl = 32; (void)nl;   /* lanes per env the workspace was sized for (fly_ws.cuh) */
 #define X(n, cnt, tier) if (!strcmp(name, #n)) { int c = (int)(cnt); if (c > cap) c = cap; for (int i = 0; i < c; i++) out[i] = (double)w.n[i]; return c; }
     FLY_WS_REAL(X)
     FLY_WS_DBL(X)
@@ -132,6 +133,7 @@ struct Emu : EmuBase {
     return -1;
   }
   int set(const char* name, const double* in, int n) override {
+    const int nl = 32; (void)nl;
 #define X(nm, cnt, tier) if (!strcmp(name, #nm)) { int c = (int)(cnt); if (c > n) c = n; for (int i = 0; i < c; i++) w.nm[i] = (T)in[i]; return c; }
     FLY_WS_REAL(X)
 #undef X

@@ -140,13 +140,15 @@ def test_results_do_not_depend_on_launch_configuration_or_batch_size(models, wal
     """The generic kernel gives the same bits whatever the launch configuration and batch size.  The default configuration
     runs the kernel compiled for this model's sizes (compile-time workspace layout): same algorithm, other multiply-add
     contractions, so it agrees to float32 rounding only - and must be the one selected for a shipped model."""
-    from flybody_b200.engine import INFO_SPEC_KERNEL
+    from flybody_b200.engine import INFO_SPEC_KERNEL, INFO_LANES
     M = models["walk_imitation"]
     rng = np.random.RandomState(2)
     acts = rng.uniform(M["action_min"], M["action_max"], (3, 300, 59)).astype(np.float32)
     outs = []
-    for (N, lvl, warps, generic) in ((300, 2, 8, 1), (300, 1, 16, 1), (300, 3, 6, 1), (37, 1, 14, 1), (300, 1, 16, 0), (41, 1, 16, 0)):
-        eng = _engine(M, N)
+    from flybody_b200.engine import FLAG_LANES16
+    for (N, lvl, warps, generic) in ((300, 3, 8, 1), (300, 2, 16, 1), (300, 0, 28, 1), (37, 0, 28, 1), (300, 0, 28, 0), (41, 0, 28, 0),
+                                     (300, 0, 16, 16)):
+        eng = _engine(M, N, flags=FLAG_LANES16 if generic == 16 else 0)
         eng.configure(lvl, warps)
         eng.use_generic_kernel(bool(generic))
         eng.load_clips(*walk_clip)
@@ -155,6 +157,7 @@ def test_results_do_not_depend_on_launch_configuration_or_batch_size(models, wal
         for k in range(3):
             st, r, g, obs = eng.step_host(acts[k, :N])
         assert (eng.info(INFO_SPEC_KERNEL) >= 0) == (not generic)
+        assert eng.info(INFO_LANES) == (16 if generic == 16 else 32)
         outs.append((obs.copy(), r.copy()))
         eng.close()
     for o, r in outs[1:4]:
@@ -164,6 +167,10 @@ def test_results_do_not_depend_on_launch_configuration_or_batch_size(models, wal
     assert (outs[5][0] == so[:41]).all() and (outs[5][1] == sr[:41]).all()      # specialised kernel: batch-size independent
     scale = np.abs(outs[0][0]).max(axis=0) + 1e-6
     assert (np.abs(so - outs[0][0]) / scale).max() < 2e-5 and np.abs(sr - outs[0][1]).max() < 2e-5 * 20
+    # two envs per warp (16 lanes each): same algorithm, other reduction trees (sums over 16 instead of 32 lanes) - float32
+    # rounding again, a little more of it after 30 physics steps (measured 3.5e-5)
+    ho, hr = outs[6]
+    assert (np.abs(ho - outs[0][0]) / scale).max() < 1e-4 and np.abs(hr - outs[0][1]).max() < 1e-4 * 20
 
 
 def test_fly_envs_api_and_large_batch_properties(models):
