@@ -213,7 +213,7 @@ FLY_FN void fly_jt_mul(const DModel<T>& m, const Ws<T>& w, T* out, const T* f) {
 
 /* ---------------------------------------------------------------- m3 + m9 transmission and actuation */
 template <class T>
-FLY_FN void fly_actuation(const DModel<T>& m, const Ws<T>& w) {
+FLY_FN void fly_actuation(const DModel<T>& m, const Ws<T>& w, bool actuate) {
   FLY_FOR(a, FLY_DIM(m, nu)) {
     const int id = m.act_trnid[a], trn = m.act_trntype[a];
     const T gear = m.act_gear[a];
@@ -237,7 +237,7 @@ FLY_FN void fly_actuation(const DModel<T>& m, const Ws<T>& w) {
     }
     T f = m.act_gainprm[a] * input + m.act_biasprm[3 * a] + m.act_biasprm[3 * a + 1] * len + m.act_biasprm[3 * a + 2] * vel;
     if (m.act_forcelimited[a]) f = fmin_(m.act_forcerange[2 * a + 1], fmax_(m.act_forcerange[2 * a], f));
-    if (m.flags & FLY_OPT_NOACTUATION) f = 0;
+    if ((m.flags & FLY_OPT_NOACTUATION) || !actuate) f = 0;   /* mjDSBL_ACTUATION: the forward pass of a reset */
     w.act_force[a] = f;
   }
   FLY_FOR(d, FLY_DIM(m, nv)) w.qfrc_actuator[d] = 0;

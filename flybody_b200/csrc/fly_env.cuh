@@ -8,9 +8,11 @@
 enum { FLY_SI_STEP = 0, FLY_SI_EPISODE_STEPS, FLY_SI_RESET_NEXT, FLY_SI_CLIP, FLY_SI_EPISODE, FLY_SI_FORCED_CLIP,
        FLY_SI_EPLEN, FLY_SI_WB_STEP, FLY_SI_WB_FIDX, FLY_SI_WB_FREQ_LO, FLY_SI_WB_FREQ_HI, FLY_SI_COUNT = 12 };
 /* per-env trace integers (optional debug output) */
-enum { FLY_TR_NCON = 0, FLY_TR_NEFC, FLY_TR_NLIMIT, FLY_TR_NITER, FLY_TR_OVERFLOW, FLY_TR_NCAND, FLY_TR_PAIRS = 8,
-       FLY_TR_INTS = 8 + FLY_MAXCON };
+enum { FLY_TR_NCON = 0, FLY_TR_NEFC, FLY_TR_NLIMIT, FLY_TR_NITER, FLY_TR_OVERFLOW, FLY_TR_NCAND, FLY_TR_NCON0, FLY_TR_PAIRS = 8,
+       FLY_TR_PAIRS0 = 8 + FLY_MAXCON,   /* contact pair list of the state the control step STARTED from (its first collision pass) */
+       FLY_TR_INTS = 8 + 2 * FLY_MAXCON };
 
+#define FLY_NSTAT 8
 template <class T>
 struct FlyIO {
   T* sreal;            /* [N, sreal_stride]: qpos | qvel | act | qacc_warmstart | episode return */
@@ -24,7 +26,8 @@ struct FlyIO {
   int* trace_int;      /* nullable [N, FLY_TR_INTS] */
   T* trace_real;       /* nullable [N, trace_real_stride]: con_dist[MAXCON] | qacc[nv] | sensordata | efc_force[MAXEFC] */
   int trace_real_stride;
-  float* stats;        /* nullable [N, 4] per-env sums over finished episodes: return, length, fatal, count */
+  float* stats;        /* nullable [N, FLY_NSTAT] per-env sums: return, length, fatal, count of finished episodes; control steps with a
+                          capacity overflow (contacts / rows dropped); reset passes; control steps */
   unsigned long long seed;
   int env_offset;      /* global id of env 0 of this shard */
   int force_reset;     /* 1: reset every env in mask regardless of reset_next */
@@ -354,10 +357,21 @@ FLY_FN void fly_env_run(const DModel<T>& m, const Ws<T>& w, const FlyClips& clip
   const int nsub = do_reset ? 0 : m.n_substeps;
   for (int it = 0;; it++) {
     fly_step1(m, w, it == 0 || it < nsub);
+    if (it == 0 && io.trace_int) {
+      int* ti = io.trace_int + (size_t)env * FLY_TR_INTS;
+      FLY_LANE0 ti[FLY_TR_NCON0] = w.counts[FLY_C_NCON];
+      FLY_FOR(k, FLY_MAXCON) ti[FLY_TR_PAIRS0 + k] = k < w.counts[FLY_C_NCON] ? w.con_pair[k] : -1;
+    }
     if (it > 0) fly_accumulate(m, w);
     if (it == nsub && !do_reset) break;
-    fly_forward_acc(m, w);
-    if (do_reset) { fly_accumulate(m, w); break; }
+    /* the forward pass of a reset runs with actuation disabled (dm_control Physics.after_reset) and, like every
+       mj_fwdConstraint, leaves its qacc as the next warm start */
+    fly_forward_acc(m, w, !do_reset);
+    if (do_reset) {
+      FLY_FOR(d, FLY_DIM(m, nv)) w.warm[d] = w.qacc[d];
+      fly_accumulate(m, w);
+      break;
+    }
     fly_integrate(m, w);
   }
   if (do_reset) fly_block_pad(fly_nb_control_step(m) - FLY_NB_STEP1 - FLY_NB_FWD);
@@ -368,7 +382,13 @@ FLY_FN void fly_env_run(const DModel<T>& m, const Ws<T>& w, const FlyClips& clip
     FLY_LANE0 {
       sint[FLY_SI_STEP] = 0; sint[FLY_SI_EPISODE_STEPS] = episode_steps; sint[FLY_SI_RESET_NEXT] = 0;
       sint[FLY_SI_CLIP] = clip_id; sint[FLY_SI_EPISODE] = episode + 1; sint[FLY_SI_EPLEN] = 0;
+      sint[FLY_SI_FORCED_CLIP] = -1;   /* walk_imitation.py:86-89: the forced index holds for the next episode only */
       s_ret[0] = 0;
+      if (io.stats) {
+        float* o = io.stats + FLY_NSTAT * (size_t)env;
+        o[5] += 1.0f;
+        if (w.counts[FLY_C_OVERFLOW]) o[4] += 1.0f;
+      }
     }
   } else {
     /* termination: tasks/base.py:214-217, walk_imitation.py:165-191, walk_on_ball.py:75-79 */
@@ -425,9 +445,11 @@ FLY_FN void fly_env_run(const DModel<T>& m, const Ws<T>& w, const FlyClips& clip
       sint[FLY_SI_EPLEN] += 1;
       if (st == 2) sint[FLY_SI_RESET_NEXT] = 1;
       s_ret[0] += reward;
-      if (st == 2 && io.stats) {
-        float* o = io.stats + 4 * (size_t)env;
-        o[0] += (float)s_ret[0]; o[1] += (float)sint[FLY_SI_EPLEN]; o[2] += (float)fatal; o[3] += 1.0f;
+      if (io.stats) {
+        float* o = io.stats + FLY_NSTAT * (size_t)env;
+        if (st == 2) { o[0] += (float)s_ret[0]; o[1] += (float)sint[FLY_SI_EPLEN]; o[2] += (float)fatal; o[3] += 1.0f; }
+        if (w.counts[FLY_C_OVERFLOW]) o[4] += 1.0f;   /* contacts or constraint rows were dropped somewhere in this control step */
+        o[6] += 1.0f;
       }
     }
   }

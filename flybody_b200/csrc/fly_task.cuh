@@ -189,9 +189,9 @@ FLY_FN void fly_step1(const DModel<T>& m, const Ws<T>& w, bool full) {
 
 /* actuation, smooth acceleration, constraint solve, acceleration sensors */
 template <class T>
-FLY_FN void fly_forward_acc(const DModel<T>& m, const Ws<T>& w) {
+FLY_FN void fly_forward_acc(const DModel<T>& m, const Ws<T>& w, bool actuate = true) {
   FLY_STAGE_SYNC(3);
-  fly_actuation(m, w);
+  fly_actuation(m, w, actuate);
   FLY_FOR(d, FLY_DIM(m, nv)) {
     const T f = w.qfrc_passive[d] - w.qfrc_bias[d] + w.qfrc_actuator[d];
     w.qfrc_smooth[d] = f; w.qacc_smooth[d] = f;

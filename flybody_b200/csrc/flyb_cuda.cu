@@ -33,6 +33,7 @@ struct FlybEngine {
   float *h_action = nullptr, *h_obs = nullptr, *h_rd = nullptr; int* h_st = nullptr; unsigned char* h_mask = nullptr;
   float *d_action = nullptr, *d_obs = nullptr, *d_rd = nullptr; int* d_st = nullptr; unsigned char* d_mask = nullptr;
   cudaStream_t host_stream = nullptr;
+  cudaEvent_t last_launch = nullptr;   /* recorded after every launch on the caller's stream: the *_host calls wait for it */
   int smem_level = 0, warps = 28, blocks_per_sm = 0, sm_count = 148, grid = 0;
   int lanes = 32;               /* lanes per env (FLY_NL of the kernels this handle launches): fixed at flyb_create */
   int spec = -1, no_spec = 0;   /* index of the model-specialised kernel in use (-1: generic); FLYB_NO_SPEC=1 forces generic */
@@ -188,6 +189,7 @@ static int launch(FlybEngine* h, const FlyIO<float>& io, cudaStream_t st, const 
   void* kargs[3] = {(void*)&h->m, (void*)&a, (void*)&off};
   CK(cudaLaunchKernel(kern, dim3(grid), dim3(W * 32), kargs, smem, st));
   CK(cudaGetLastError());
+  if (!sc) CK(cudaEventRecord(h->last_launch, st));   /* (flyb_step_noalloc stays free of anything but the clear and the launch) */
   h->launches++;
   return 0;
 }
@@ -248,8 +250,9 @@ int flyb_create(const FlybModel* model, int num_envs, int device, uint64_t seed,
     for (size_t i = 0; i < N; i++) { si[i * FLY_SI_COUNT + FLY_SI_FORCED_CLIP] = -1; si[i * FLY_SI_COUNT + FLY_SI_RESET_NEXT] = 1; }
     CKC(cudaMemcpy(h->d_sint, si.data(), si.size() * sizeof(int), cudaMemcpyHostToDevice));
   }
-  CKC(cudaMalloc(&h->d_stats, N * 4 * sizeof(float)));
-  CKC(cudaMemset(h->d_stats, 0, N * 4 * sizeof(float)));
+  CKC(cudaMalloc(&h->d_stats, N * FLY_NSTAT * sizeof(float)));
+  CKC(cudaMemset(h->d_stats, 0, N * FLY_NSTAT * sizeof(float)));
+  CKC(cudaEventCreateWithFlags(&h->last_launch, cudaEventDisableTiming));
   if (flags & FLYB_FLAG_TRACE) {
     h->trace_real_stride = FLY_MAXCON + m.nv + m.nsensordata + FLY_MAXEFC;
     CKC(cudaMalloc(&h->d_trace_int, N * FLY_TR_INTS * sizeof(int)));
@@ -304,6 +307,7 @@ void flyb_destroy(flyb_handle h) {
   cudaFree(h->d_st); cudaFree(h->d_mask);
   cudaFreeHost(h->h_action); cudaFreeHost(h->h_obs); cudaFreeHost(h->h_rd); cudaFreeHost(h->h_st); cudaFreeHost(h->h_mask);
   if (h->host_stream) cudaStreamDestroy(h->host_stream);
+  if (h->last_launch) cudaEventDestroy(h->last_launch);
   delete h;
 }
 
@@ -401,6 +405,9 @@ int flyb_set_wbpg_phase(flyb_handle h, const double* phase) {
 int flyb_set_clip_ids(flyb_handle h, const int32_t* ids) {
   CK(cudaSetDevice(h->device));
   CK(cudaDeviceSynchronize());
+  if (ids && h->n_clips > 0)
+    for (int i = 0; i < h->num_envs; i++)
+      if (ids[i] >= h->n_clips) { h->err = "flyb_set_clip_ids: clip id " + std::to_string(ids[i]) + " of env " + std::to_string(i) + " is beyond the loaded table (" + std::to_string(h->n_clips) + " clips)"; return 1; }
   std::vector<int> si((size_t)h->num_envs * FLY_SI_COUNT);
   CK(cudaMemcpy(si.data(), h->d_sint, si.size() * sizeof(int), cudaMemcpyDeviceToHost));
   for (int i = 0; i < h->num_envs; i++) si[(size_t)i * FLY_SI_COUNT + FLY_SI_FORCED_CLIP] = ids ? ids[i] : -1;
@@ -450,6 +457,7 @@ int flyb_reset_host(flyb_handle h, const uint8_t* mask, float* obs, int32_t* ste
   CK(cudaSetDevice(h->device));
   const size_t N = h->num_envs;
   cudaStream_t s = h->host_stream;
+  CK(cudaStreamWaitEvent(s, h->last_launch, 0));   /* a device-pointer call still in flight on the caller's stream goes first */
   if (mask) { memcpy(h->h_mask, mask, N); CK(cudaMemcpyAsync(h->d_mask, h->h_mask, N, cudaMemcpyHostToDevice, s)); }
   if (flyb_reset(h, mask ? h->d_mask : nullptr, h->d_obs, h->d_st, s)) return 1;
   CK(cudaMemcpyAsync(h->h_obs, h->d_obs, N * h->m.obs_dim * sizeof(float), cudaMemcpyDeviceToHost, s));
@@ -473,7 +481,9 @@ static bool is_pinned(const void* p) {
 int flyb_step_host(flyb_handle h, const float* action, float* obs, float* reward, float* discount, int32_t* step_type) {
   CK(cudaSetDevice(h->device));
   const size_t N = h->num_envs, A = h->m.action_dim, O = h->m.obs_dim;
+  if (!action) { h->err = "flyb_step_host: action must not be NULL"; return 1; }
   cudaStream_t s = h->host_stream;
+  CK(cudaStreamWaitEvent(s, h->last_launch, 0));   /* a device-pointer call still in flight on the caller's stream goes first */
   /* pageable caller buffers go through the library's pinned staging buffers (one extra host copy each way); page-locked
      ones are copied to and from directly */
   const bool pa = is_pinned(action), po = is_pinned(obs), pr = is_pinned(reward), pd = is_pinned(discount), ps = is_pinned(step_type);
@@ -540,15 +550,15 @@ int flyb_get_trace(flyb_handle h, int32_t* ints, float* reals) {
   return 0;
 }
 
-int flyb_episode_stats(flyb_handle h, double* out4) {
+int flyb_episode_stats(flyb_handle h, double* out8) {
   CK(cudaSetDevice(h->device));
   CK(cudaDeviceSynchronize());
   const size_t N = h->num_envs;
-  std::vector<float> s(N * 4);
+  std::vector<float> s(N * FLY_NSTAT);
   CK(cudaMemcpy(s.data(), h->d_stats, s.size() * sizeof(float), cudaMemcpyDeviceToHost));
   CK(cudaMemset(h->d_stats, 0, s.size() * sizeof(float)));
-  for (int k = 0; k < 4; k++) out4[k] = 0;
-  for (size_t i = 0; i < N; i++) for (int k = 0; k < 4; k++) out4[k] += s[i * 4 + k];
+  for (int k = 0; k < FLY_NSTAT; k++) out8[k] = 0;
+  for (size_t i = 0; i < N; i++) for (int k = 0; k < FLY_NSTAT; k++) out8[k] += s[i * FLY_NSTAT + k];
   return 0;
 }
 

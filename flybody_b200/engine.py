@@ -240,10 +240,11 @@ class Engine:
         self._ck(lib().flyb_get_trace(self._h, _ip(ti), _fp(tr)))
         mc, nv, ns = int(self.info(INFO_MAXCON)), self.nv, int(self.M["nsensordata"])
         return dict(ncon=ti[:, 0], nefc=ti[:, 1], nlimit=ti[:, 2], niter=ti[:, 3], overflow=ti[:, 4], ncand=ti[:, 5],
-                    pairs=ti[:, 8:], dist=tr[:, :mc], qacc=tr[:, mc:mc + nv], sensordata=tr[:, mc + nv:mc + nv + ns],
+                    ncon0=ti[:, 6], pairs=ti[:, 8:8 + mc], pairs0=ti[:, 8 + mc:8 + 2 * mc], dist=tr[:, :mc], qacc=tr[:, mc:mc + nv], sensordata=tr[:, mc + nv:mc + nv + ns],
                     efc_force=tr[:, mc + nv + ns:])
 
     def episode_stats(self):
-        out = np.zeros(4, np.float64)
+        out = np.zeros(8, np.float64)
         self._ck(lib().flyb_episode_stats(self._h, out.ctypes.data_as(ctypes.POINTER(ctypes.c_double))))
-        return dict(return_sum=out[0], length_sum=out[1], fatal=out[2], episodes=out[3])
+        return dict(return_sum=out[0], length_sum=out[1], fatal=out[2], episodes=out[3], overflow_steps=out[4],
+                    resets=out[5], steps=out[6])

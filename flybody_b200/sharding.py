@@ -14,7 +14,7 @@ def reduce_stats(stats: dict, device):
     """Sum the episode statistics over all ranks (NCCL on GPUs, gloo in the CPU tests)."""
     import torch
     import torch.distributed as dist
-    keys = ("return_sum", "length_sum", "fatal", "episodes")
+    keys = tuple(k for k in ("return_sum", "length_sum", "fatal", "episodes", "overflow_steps", "resets", "steps") if k in stats)
     t = torch.tensor([float(stats[k]) for k in keys], dtype=torch.float64, device=device)
     if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
         dist.all_reduce(t, op=dist.ReduceOp.SUM)

@@ -21,8 +21,9 @@
  * 0), as vnl_ray/tasks/base.py:214-217 and dm_control's PhysicsError handling do.  The caller owns every I/O
  * buffer; the library owns the model constants, clip table and per-env state.  One handle per GPU and
  * process; calls on one handle must be serialised by the caller; work is enqueued on the given CUDA stream
- * (cudaStream_t passed as void*, NULL = default stream) without hidden synchronisation, except the *_host
- * calls, which synchronise that stream before returning.  There is no CPU fallback: without a CUDA device
+ * (cudaStream_t passed as void*, NULL = default stream) without hidden synchronisation.  The *_host calls run on a
+ * stream of the library's own, first wait (on the device) for the handle's last device-pointer launch, and synchronise
+ * before returning.  There is no CPU fallback: without a CUDA device
  * flyb_create fails. */
 #ifndef FLYB_H_
 #define FLYB_H_
@@ -79,7 +80,8 @@ int flyb_load_wbpg(flyb_handle h, const double* beat_freqs, const int32_t* offse
 /* Initial wing-beat phase in [0,1) per env for the following resets (host pointer, num_envs doubles) - the value the
  * reference draws with random_state.uniform() (flight_imitation.py:137).  NULL = counter-based hash of (seed, env, episode). */
 int flyb_set_wbpg_phase(flyb_handle h, const double* phase);
-/* Per-env clip choice for the next resets (host pointer, num_envs entries; -1 = counter-based random). NULL = all random. */
+/* Per-env clip choice for each env's NEXT episode only (host pointer, num_envs entries; -1 = counter-based random), as
+ * task.set_next_trajectory_index (walk_imitation.py:86-89).  NULL = all random.  Ids beyond the loaded table are an error. */
 int flyb_set_clip_ids(flyb_handle h, const int32_t* ids);
 
 /* Device-pointer API.  mask: NULL (all envs) or num_envs bytes, non-zero = reset that env.
@@ -119,12 +121,16 @@ int flyb_get_state(flyb_handle h, float* qpos, float* qvel, float* act, float* w
 int flyb_set_state(flyb_handle h, const float* qpos, const float* qvel, const float* act, const float* warm,
                    const int32_t* ints);
 /* Trace of the last launch (needs FLYB_FLAG_TRACE; host pointers, may be NULL).
- * ints [N, TRACE_INTS]: ncon, nefc, nlimit, solver iterations, overflow bits, candidates, -, -, contact pair ids.
+ * ints [N, TRACE_INTS]: ncon, nefc, nlimit, solver iterations, overflow bits, candidates (all of the control step's last full
+ * physics step), ncon0, -, contact pair ids [MAXCON] of that step, contact pair ids [MAXCON] of the state the control step
+ * started from (ncon0 of them; = the reference's contact list after the previous control step).
  * reals [N, TRACE_REALS]: contact dist [MAXCON] | qacc [nv] | sensordata | efc_force [MAXEFC]. */
 int flyb_get_trace(flyb_handle h, int32_t* ints, float* reals);
-/* Episode statistics summed over this shard's envs since the last call (host, 4 doubles):
- * sum of returns, sum of lengths, fatal terminations, finished episodes. */
-int flyb_episode_stats(flyb_handle h, double* out4);
+/* Statistics summed over this shard's envs since the last call (host, 8 doubles): [0] sum of returns, [1] sum of lengths,
+ * [2] fatal terminations, [3] count of the episodes that finished; [4] control steps (or reset passes) in which a capacity was
+ * exceeded and contacts or constraint rows were dropped (FLYB_INFO_MAXCON / MAXEFC; MuJoCo would raise a warning counter:
+ * must be 0 for the physics to be the reference's); [5] reset passes; [6] control steps; [7] unused. */
+int flyb_episode_stats(flyb_handle h, double* out8);
 
 #ifdef __cplusplus
 }

@@ -1768,6 +1768,27 @@ static double quat_dist_short_arc(const double* a, const double* b) {  /* quater
   return acos(x);
 }
 
+/* test hook: the quaternion helpers above on raw inputs, so that the reference-generated fixture (tests/golden/quaternions.npz,
+ * vnl_ray/quaternions.py) checks them directly, edge cases included.  op: 0 reciprocal(a) 1 rotate(v = a, q = b) 2 z2vec(a)
+ * 3 dist_short_arc(a, b) 4 joint_orientation_quat(axis = a, angle = b[0]) 5 get_dquat_local(a, b) 6 get_egocentric_vec(root =
+ * a[0..3), site = a[3..6), root_quat = b) 7 mult(a, b).  Returns the number of doubles written. */
+int flyo_quat_op(int op, const double* a, const double* b, double* out) {
+  switch (op) {
+    case 0: quat_recip(out, a); return 4;
+    case 1: quat_rotate(out, a, b); return 3;
+    case 2: quat_z2vec(out, a); return 4;
+    case 3: out[0] = quat_dist_short_arc(a, b); return 1;
+    case 4: {   /* rewards.py:47-51 as the reward code evaluates it */
+      double q1[4], q2[4], n = norm3(a), a2[3] = {a[0] / n, a[1] / n, a[2] / n};
+      quat_z2vec(q1, a); axis_angle_quat(q2, a2, b[0]); quat_mul(out, q2, q1); return 4;
+    }
+    case 5: { double qi[4]; quat_recip(qi, a); quat_mul(out, qi, b); return 4; }
+    case 6: { double d[3] = {a[3] - a[0], a[4] - a[1], a[5] - a[2]}, qc[4] = {b[0], -b[1], -b[2], -b[3]}; quat_rotate(out, d, qc); return 3; }
+    case 7: quat_mul(out, a, b); return 4;
+  }
+  return 0;
+}
+
 static const double* clip_row(const double* base, int row, int width) { return base + (size_t)row * width; }
 
 /* observation assembly: fruitfly.py:532-669, tasks/base.py:237-261, walk_on_ball.py:81-88 */
@@ -1921,7 +1942,16 @@ int flyo_env_reset(FlyoEnv* e, double* obs) {
     }
     memcpy(e->qvel + m->root_dofadr, e->clip.qvel, 3 * sizeof(double));   /* :145-147 linear velocity only */
   }
-  flyo_forward(e);
+  /* dm_control's Physics.after_reset(), reached when composer's _reset_attempt leaves reset_context(), runs mj_forward with
+     actuation disabled ("we don't yet have meaningful control inputs"): the affine position servos (biasprm 0 -kp) would
+     otherwise pull at the initial pose, and the FIRST observation's accelerometer / force / touch would see it */
+  {
+    const int keep = e->disable_actuation;
+    e->disable_actuation = 1;
+    flyo_forward(e);
+    e->disable_actuation = keep;
+  }
+  memcpy(e->qacc_warmstart, e->qacc, m->nv * sizeof(double));   /* mj_fwdConstraint leaves its result as the next warm start */
   accumulate_sensors(e);
   /* composer observation buffers: first sample then zero padding unless pad_with_initial_value */
   write_obs(e, obs, m->pad_first_obs ? 1.0 : 1.0 / m->n_substeps);

@@ -69,6 +69,8 @@ def lib():
         L.flyo_env_step.restype = ctypes.c_int
         L.flyo_narrow_pair.argtypes = [ctypes.c_int, dp, dp, dp, ctypes.c_int, dp, dp, dp, ctypes.c_double, ctypes.c_int, dp]
         L.flyo_narrow_pair.restype = ctypes.c_int
+        L.flyo_quat_op.argtypes = [ctypes.c_int, dp, dp, dp]
+        L.flyo_quat_op.restype = ctypes.c_int
         _lib = L
     return _lib
 
@@ -183,3 +185,14 @@ def narrow_pair(t1, pos1, mat1, size1, t2, pos2, mat2, size2, margin=0.0, force_
     n = lib().flyo_narrow_pair(int(t1), P[0], P[1], P[2], int(t2), P[3], P[4], P[5], float(margin), int(force_convex),
                                out.ctypes.data_as(dp))
     return [(out[7 * i], out[7 * i + 1:7 * i + 4].copy(), out[7 * i + 4:7 * i + 7].copy()) for i in range(n)]
+
+
+def quat_op(op: int, a, b=None):
+    """The oracle's task-layer quaternion helpers on raw inputs (flyo_quat_op: 0 reciprocal, 1 rotate(v, q), 2 z2vec, 3 short-arc
+    distance, 4 joint_orientation_quat(axis, angle), 5 get_dquat_local, 6 get_egocentric_vec([root, site], quat), 7 mult)."""
+    dp = ctypes.POINTER(ctypes.c_double)
+    a = np.ascontiguousarray(a, np.float64).reshape(-1)
+    b = np.ascontiguousarray(b if b is not None else [0.0], np.float64).reshape(-1)
+    out = np.zeros(4)
+    n = lib().flyo_quat_op(int(op), a.ctypes.data_as(dp), b.ctypes.data_as(dp), out.ctypes.data_as(dp))
+    return out[:n].copy()

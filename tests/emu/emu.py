@@ -44,6 +44,7 @@ def lib():
         L.emu_get.argtypes = [ctypes.c_void_p, ctypes.c_char_p, dp, ctypes.c_int]
         L.emu_set.argtypes = [ctypes.c_void_p, ctypes.c_char_p, dp, ctypes.c_int]
         L.emu_geti.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ip, ctypes.c_int]
+        L.emu_quat_op.argtypes = [ctypes.c_int, ctypes.c_int, dp, dp, dp]
         _lib = L
     return _lib
 
@@ -136,3 +137,15 @@ class EmuEnv:
         fp = ctypes.POINTER(ctypes.c_float)
         st = lib().emu_env_step(self._h, a.ctypes.data_as(fp), obs.ctypes.data_as(fp), ctypes.byref(r), ctypes.byref(g))
         return st, r.value, g.value, obs
+
+
+def quat_op(op: int, a, b=None, double: bool = False):
+    """The engine's task-layer quaternion helpers (csrc/fly_env.cuh) on raw inputs, in float32 or float64 (ops: oracle.quat_op)."""
+    dp = ctypes.POINTER(ctypes.c_double)
+    aa = np.zeros(6); aa[:np.size(a)] = np.asarray(a, np.float64).reshape(-1)
+    bb = np.zeros(4)
+    if b is not None:
+        bb[:np.size(b)] = np.asarray(b, np.float64).reshape(-1)
+    out = np.zeros(4)
+    n = lib().emu_quat_op(int(double), int(op), aa.ctypes.data_as(dp), bb.ctypes.data_as(dp), out.ctypes.data_as(dp))
+    return out[:n].copy()

@@ -155,6 +155,32 @@ struct Emu : EmuBase {
   }
 };
 
+/* test hook: the engine's task-layer quaternion helpers (fly_env.cuh, fly_math.cuh) on raw inputs, in T; ops as flyo_quat_op */
+template <class T> static int quat_op_t(int op, const double* ad, const double* bd, double* out) {
+  T a[6], b[4], o[4] = {0, 0, 0, 0};
+  for (int k = 0; k < 6; k++) a[k] = (T)ad[k];
+  for (int k = 0; k < 4; k++) b[k] = (T)bd[k];
+  int n = 0;
+  switch (op) {
+    case 0: quat_recip(o, a); n = 4; break;
+    case 1: quat_rotate(o, a, b); n = 3; break;
+    case 2: quat_z2vec(o, a); n = 4; break;
+    case 3: o[0] = quat_dist_short_arc(a, b); n = 1; break;
+    case 4: {   /* fly_walk_imitation_reward's joint quaternion */
+      T q1[4], q2[4];
+      quat_z2vec(q1, a);
+      const T nn = norm3(a);
+      const T a2[3] = {a[0] / nn, a[1] / nn, a[2] / nn};
+      axis_angle_quat(q2, a2, b[0]);
+      quat_mul(o, q2, q1); n = 4; break;
+    }
+    case 5: { T qi[4]; quat_recip(qi, a); quat_mul(o, qi, b); n = 4; break; }
+    case 6: { T d[3] = {a[3] - a[0], a[4] - a[1], a[5] - a[2]}, qc[4] = {b[0], -b[1], -b[2], -b[3]}; quat_rotate(o, d, qc); n = 3; break; }
+    case 7: quat_mul(o, a, b); n = 4; break;
+  }
+  for (int k = 0; k < n; k++) out[k] = (double)o[k];
+  return n;
+}
 extern "C" {
 void* emu_create(const FlybModel* m, int flags, int use_double, char* errbuf, int errcap) {
   EmuBase* e;
@@ -165,6 +191,9 @@ void* emu_create(const FlybModel* m, int flags, int use_double, char* errbuf, in
   return e;
 }
 void emu_destroy(void* h) { delete (EmuBase*)h; }
+int emu_quat_op(int use_double, int op, const double* a, const double* b, double* out) {
+  return use_double ? quat_op_t<double>(op, a, b, out) : quat_op_t<float>(op, a, b, out);
+}
 void emu_set_clips(void* h, const float* data, const int* off, const int* len, int n) { ((EmuBase*)h)->set_clips(data, off, len, n); }
 void emu_set_wbpg(void* h, const double* freqs, const int* off, const double* traj, const double* phase, int nf, const double* prm) {
   ((EmuBase*)h)->set_wbpg(freqs, off, traj, phase, nf, prm);

@@ -238,6 +238,7 @@ def test_flight_imitation_matches_oracle(models):
         a = (0.4 * rng.uniform(M["action_min"], M["action_max"], size=(N, int(M["action_dim"])))).astype(np.float32)
         a[:, user] = np.clip(np.sin(0.3 * k + np.arange(N)) + rng.normal(scale=0.2, size=N), -1, 1)
         a[5] = a[0]
+        running05 = not done[0]
         st, r, g, obs = eng.step_host(a)
         si = eng.get_state()["ints"]
         for i in range(N):
@@ -253,7 +254,8 @@ def test_flight_imitation_matches_oracle(models):
             assert abs(float(r[i]) - orr) <= (1e-5 if k < 20 else 1e-4) * max(1.0, abs(orr))
             assert _rel(obs[i], oobs) < 5e-4
             done[i] = ost == 2
-        assert (obs[0] == obs[5]).all()
+        if running05:   # (the forced clip ids hold for one episode: after it envs 0 and 5 draw their own clips)
+            assert (obs[0] == obs[5]).all()
         if done.all():
             break
     # clip 0 has 90 rows -> good end at step 84; clip 1 has 140 rows -> still running at step 100 unless it crashed
