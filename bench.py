@@ -26,8 +26,16 @@ sys.path.insert(0, ROOT)
 import numpy as np  # noqa: E402
 
 ENVS_PER_GPU = 16384
-ALGO_BYTES = {"walk_imitation": 9984, "walk_on_ball": 4436}   # compulsory fp32 bytes per env-step
+ALGO_BYTES = {"walk_imitation": 9984, "walk_on_ball": 4436, "flight_imitation": 1924}   # compulsory fp32 bytes per env-step
 METRIC = "fly env-steps/s (walk_imitation, 16384 envs per GPU, synthetic clips, random actions)"
+
+
+
+
+def workload(clips: int) -> str:
+    """config.workload of both arms (the reference arm times a bounded sample of exactly this workload)."""
+    return ("walk_imitation (BASELINE.json configs[1]): 16384 envs per GPU, 10 physics substeps per control step, "
+            f"{clips} synthetic reference clips x 600 steps, U(ctrlrange) random actions, auto-reset")
 
 
 _REAL_STDOUT = None
@@ -87,7 +95,7 @@ def _model_and_clips(n_clips, T):
     from flybody_b200.compile_fly import load_model
     from flybody_b200.model_pack import asset_path
     M = load_model(asset_path("walk_imitation"))
-    return M, C.synthetic_table(M, n_clips, T, 0)
+    return M, C.synthetic_table(M, n_clips, T, 0, cache=False)   # every rank builds its own copy (about a minute for 1024 clips)
 
 
 # ------------------------------------------------------------------------------------------------ CPU arms
@@ -147,21 +155,75 @@ def run_reference(args):
         v, dt = cpu_throughput(cores, per_core, table)
         vals.append(v); ms.append(dt * 1e3)
     v = float(np.mean(vals))
-    sample = f"{cores} oracle envs x {per_core} control steps per step (same model, clips and action distribution)"
+    sample = (f"{cores} oracle envs (one per host core, clips 0..7 of the same table) x {per_core} control steps per step, same model "
+              "and action distribution; float64 CPU port of the reference algorithm (MuJoCo / dm_control not installable here)")
     _emit({
         "impl": "reference", "metric": METRIC, "value": v, "unit": "env-steps/s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": float(np.mean(ms)), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "walk_imitation, synthetic reference clips, U(ctrlrange) random actions; CPU port of the reference algorithm (MuJoCo/dm_control not installable here)"},
+        "config": {"workload": workload(args.clips), "sample": sample},
         "cpu_baseline": {"value": v, "unit": "env-steps/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     })
 
 
+def _time_steps(torch, eng, dev, acts, steps, warm, flush, out):
+    """`steps` control steps timed with CUDA events on the launching stream after `warm` untimed ones, L2 flushed in between;
+    returns ms per step (list)."""
+    obs, rew, disc, st = out
+    stream = torch.cuda.current_stream(dev).cuda_stream
+    for k in range(warm):
+        eng.step_ptr(acts(k).data_ptr(), obs.data_ptr(), rew.data_ptr(), disc.data_ptr(), st.data_ptr(), stream)
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    torch.cuda.synchronize(dev)
+    for k in range(steps):
+        flush.fill_(float(k))
+        a = acts(warm + k)
+        ev[k][0].record()
+        eng.step_ptr(a.data_ptr(), obs.data_ptr(), rew.data_ptr(), disc.data_ptr(), st.data_ptr(), stream)
+        ev[k][1].record()
+    torch.cuda.synchronize(dev)
+    return [a.elapsed_time(b) for a, b in ev]
+
+
+def _other_task(torch, task, N, dev, local, flush, peak, steps=10, warm=5):
+    """One more task at the same batch size, device-timed like the headline (random actions; flight at 0.3 x ctrlrange so that
+    episodes last, as tools/task_probe.py does)."""
+    from flybody_b200 import clips as C, wbpg as W
+    from flybody_b200.compile_fly import load_model
+    from flybody_b200.engine import Engine
+    from flybody_b200.model_pack import asset_path
+    M = load_model(asset_path(task))
+    eng = Engine(M, N, local, seed=1)
+    scale = 1.0
+    if task == "flight_imitation":
+        eng.load_clips(*C.synthetic_flight_table(M, 64, 3006, 0))
+        eng.load_wbpg(W.build_tables(W.synthetic_base_pattern()))
+        scale = 0.3
+    A, O = eng.action_dim, eng.obs_dim
+    out = (torch.zeros((N, O), device=dev), torch.zeros(N, device=dev), torch.zeros(N, device=dev),
+           torch.zeros(N, dtype=torch.int32, device=dev))
+    amin = torch.as_tensor(np.asarray(M["action_min"], np.float32), device=dev)
+    amax = torch.as_tensor(np.asarray(M["action_max"], np.float32), device=dev)
+    gen = torch.Generator(device=dev); gen.manual_seed(99)
+    pool = [scale * (amin + torch.rand((N, A), device=dev, generator=gen) * (amax - amin)) for _ in range(8)]
+    eng.reset_ptr(0, out[0].data_ptr(), out[3].data_ptr(), torch.cuda.current_stream(dev).cuda_stream)
+    ms = _time_steps(torch, eng, dev, lambda k: pool[k % 8], steps, warm, flush, out)
+    stats = eng.episode_stats()
+    eng.close()
+    t = float(np.mean(ms)) * 1e-3
+    ach = ALGO_BYTES[task] * N / t / 1e9
+    return {"value": N / t, "unit": "env-steps/s", "ms_per_step": t * 1e3, "envs": N, "n_substeps": int(M["n_substeps"]),
+            "algorithmic_bytes_per_env_step": ALGO_BYTES[task], "achieved_gbs": ach, "frac": ach / peak,
+            "actions": "U(ctrlrange)" if scale == 1.0 else f"{scale} x U(ctrlrange)", "overflow_steps": stats["overflow_steps"],
+            "reset_share": stats["resets"] / max(1.0, stats["resets"] + stats["steps"])}
+
+
 def run_gpu(args):
     import torch
     import torch.distributed as dist
-    from flybody_b200.engine import Engine, INFO_LAUNCHES, INFO_GRID, INFO_SMEM_BYTES, INFO_SPEC_KERNEL
+    from flybody_b200.engine import (Engine, INFO_LAUNCHES, INFO_GRID, INFO_SMEM_BYTES, INFO_SPEC_KERNEL, INFO_WARPS_PER_BLOCK,
+                                     fma_peak_tflops)
     from flybody_b200.sharding import shard_range, reduce_stats
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     local = int(os.environ.get("LOCAL_RANK", 0))
@@ -200,6 +262,7 @@ def run_gpu(args):
     for k in range(args.warmup):
         eng.step_ptr(pool[k % 8].data_ptr(), obs.data_ptr(), rew.data_ptr(), disc.data_ptr(), st.data_ptr(), stream)
     # ---- device-resident timing: CUDA events on the launching stream, L2 flushed between timed steps
+    eng.episode_stats()   # counters from here on: the timed steps and the end-to-end leg
     l0 = eng.info(INFO_LAUNCHES)
     clocks = ClockSampler(local) if rank == 0 else None
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
@@ -237,6 +300,47 @@ def run_gpu(args):
     clk = clocks.stop() if clocks else None
     e2e = N * world * args.steps / e2e_s
     stats = reduce_stats(eng.episode_stats(), dev)
+    extras = {}
+    if world == 1 and not args.no_extras:
+        # ---- the other workloads of SURVEY.md 8(d), same process, device-timed like the headline (N = 1 run only)
+        peak0, _ = _peaks()
+        # config 2 (ii): reference-tracking actions - every env is sent the joint angles of its own clip's next row on the
+        # position servos of the mocap joints, other actuators mid-range, + 2 % of the control range of Gaussian noise
+        rows_t = torch.as_tensor(table[0], device=dev)
+        off_t, len_t = torch.as_tensor(table[1], device=dev).long(), torch.as_tensor(table[2], device=dev).long()
+        mocap = {int(j): i for i, j in enumerate(np.asarray(M["mocap_joint"]))}
+        col = np.full(A, -1)
+        for a in range(int(M["nu"])):
+            ai, j = int(M["ctrl_action"][a]), int(M["act_trnid"][a])
+            if ai >= 0 and int(M["act_trntype"][a]) == 0 and j in mocap:
+                col[ai] = 7 + mocap[j]
+        dst = torch.as_tensor(np.nonzero(col >= 0)[0], device=dev)
+        src = torch.as_tensor(col[col >= 0], device=dev)
+        mid = 0.5 * (amin + amax)
+        mask = torch.ones(N, dtype=torch.uint8, device=dev)
+        eng.reset_ptr(mask.data_ptr(), obs.data_ptr(), st.data_ptr(), stream)
+
+        def tracking(k):
+            ints = torch.as_tensor(eng.get_state()["ints"], device=dev).long()
+            row = off_t[ints[:, 3]] + torch.minimum(ints[:, 0] + 1, len_t[ints[:, 3]] - 1)
+            a = mid.repeat(N, 1)
+            a[:, dst] = rows_t[row][:, src]
+            a = a + 0.02 * (amax - amin) * torch.randn((N, A), device=dev, generator=gen)
+            tracking.keep = torch.minimum(torch.maximum(a, amin), amax).contiguous()
+            return tracking.keep
+        eng.episode_stats()
+        ms_t = _time_steps(torch, eng, dev, tracking, 10, 20, flush, (obs, rew, disc, st))
+        ts = eng.episode_stats()
+        tt = float(np.mean(ms_t)) * 1e-3
+        extras["tracking_actions"] = {"value": N / tt, "unit": "env-steps/s", "ms_per_step": tt * 1e3, "envs": N,
+                                      "actions": "clip joint angles of the next row on the position servos + 2 % noise (SURVEY 8d config 2 ii)",
+                                      "mean_reward": float(rew.mean().item()), "episodes_ended": ts["episodes"],
+                                      "overflow_steps": ts["overflow_steps"],
+                                      "frac": ALGO_BYTES["walk_imitation"] * N / tt / 1e9 / peak0}
+        del rows_t
+        for task in ("flight_imitation", "walk_on_ball"):
+            extras[task] = _other_task(torch, task, N, dev, local, flush, peak0)
+        extras["fma_peak_tflops"] = fma_peak_tflops(local)
     if rank == 0:
         peak, how = _peaks()
         per_launch_s = float(np.mean(kernel_ms)) * 1e-3
@@ -246,25 +350,39 @@ def run_gpu(args):
         if os.path.exists(tp):
             traffic = json.load(open(tp)).get("dram_bytes_per_launch")
         cpu_steps = args.cpu_steps
-        cpu_v, cpu_dt = cpu_throughput(1, cpu_steps, table)
+        cores = os.cpu_count() or 1
+        cpu_v, cpu_dt = cpu_throughput(cores, cpu_steps, table)
+        fp32 = None
+        fp = os.path.join(ROOT, "profiles", "r2_fp32.json")
+        if os.path.exists(fp) and "fma_peak_tflops" in extras:
+            flop = float(json.load(open(fp))["fp32_flop_per_env_step"])
+            ach_tf = flop * N / per_launch_s / 1e12
+            fp32 = {"flop_per_env_step": flop, "flop_source": "profiles/r2_fp32.json (ncu smsp__sass_thread_inst_executed_op_f{add,mul,fma} of the kept capture)",
+                    "achieved_tflops": ach_tf, "peak_tflops": extras["fma_peak_tflops"],
+                    "peak_source": "FMA micro-benchmark measured in this run (flyb_fma_peak)", "frac": ach_tf / extras["fma_peak_tflops"]}
+        timed_steps = max(1.0, stats.get("steps", 0.0) + stats.get("resets", 0.0))
         _emit({
             "metric": METRIC, "value": value, "unit": "env-steps/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
-            "config": {"workload": "walk_imitation (BASELINE.json configs[1]): 16384 envs per GPU, 10 physics substeps per control step, "
-                                   f"{args.clips} synthetic reference clips x 600 steps, U(ctrlrange) random actions, auto-reset",
+            "config": {"workload": workload(args.clips), "clip_table_gb": table[0].nbytes / 1e9,
                        "envs_per_gpu": N, "global_envs": N * world, "l2": "256 MB buffer written between timed steps",
-                       "grid": eng.info(INFO_GRID), "smem_bytes_per_block": eng.info(INFO_SMEM_BYTES), "outputs_finite": finite,
+                       "grid": eng.info(INFO_GRID), "warps_per_block": eng.info(INFO_WARPS_PER_BLOCK),
+                       "smem_bytes_per_block": eng.info(INFO_SMEM_BYTES), "outputs_finite": finite,
+                       "overflow_envs": stats.get("overflow_steps"),
+                       "reset_share_of_env_steps": stats.get("resets", 0.0) / timed_steps,
                        "step_kernel": ("compiled for this task model (index %d of csrc/fly_dims_gen.h)" % eng.info(INFO_SPEC_KERNEL))
                        if eng.info(INFO_SPEC_KERNEL) >= 0 else "generic"},
             "clocks": clk, "gpu_launches": int(launches),
             "e2e": {"value": e2e, "unit": "env-steps/s", "h2d_bytes_per_step": N * A * 4, "d2h_bytes_per_step": N * (O + 3) * 4},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                          "peak_source": how, "kernel": "fly_step_kernel", "algorithmic_bytes_per_env_step": ALGO_BYTES["walk_imitation"],
-                         "note": "HBM is the contract roofline; the kernel is FP32-issue/latency bound (DESIGN.md)"},
-            "cpu_baseline": {"value": cpu_v, "unit": "env-steps/s", "cores": 1, "kind": "port",
-                             "sample": f"{cpu_steps} control steps of one env, float64 CPU restatement (oracle/), {cpu_dt:.1f} s"},
+                         "note": "HBM is the contract roofline; the kernel is FP32-issue/latency bound (DESIGN.md)", "fp32": fp32},
+            "cpu_baseline": {"value": cpu_v, "unit": "env-steps/s", "cores": cores, "kind": "port",
+                             "sample": f"{cores} oracle envs (one per host core) x {cpu_steps} control steps, float64 CPU restatement "
+                                       f"(oracle/), same model, clips and action distribution, {cpu_dt:.1f} s"},
             "episode_stats": stats,
+            **{k: v for k, v in extras.items() if k != "fma_peak_tflops"},
         })
     eng.close()
     if world > 1:
@@ -284,9 +402,10 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="flyb", choices=["flyb", "reference"])
     ap.add_argument("--envs", type=int, default=ENVS_PER_GPU, help="envs per GPU")
-    ap.add_argument("--clips", type=int, default=64)
+    ap.add_argument("--clips", type=int, default=1024, help="synthetic reference clips x 600 steps (SURVEY 8d config 2: 1024 = 1.05 GB in HBM)")
+    ap.add_argument("--no-extras", action="store_true", help="skip the tracking-action / flight / ball arms of the N = 1 run")
     ap.add_argument("--seed", type=int, default=0)
-    ap.add_argument("--cpu-steps", type=int, default=600)
+    ap.add_argument("--cpu-steps", type=int, default=400, help="control steps per host core of the cpu_baseline leg")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "flyb" else args.warmup
     if args.impl == "reference":

@@ -103,6 +103,23 @@ __global__ void __launch_bounds__(1024) fly_bin_kernel(const int* __restrict__ w
   }
 }
 
+/* ---- FP32 FMA peak of the device, measured (flyb_fma_peak): every thread runs 16 independent FMA chains; 8 blocks of 256
+ * threads per SM keep the FMA pipes full.  The roofline denominator bench.py quotes FP32-pipe fractions against. */
+__global__ void __launch_bounds__(256) fly_fma_peak_kernel(float* out, int iters) {
+  float a[16];
+#pragma unroll
+  for (int k = 0; k < 16; k++) a[k] = 1.0f + 0.001f * (float)(threadIdx.x + k);
+  const float m = 0.9999f, c = 1e-4f;
+  for (int it = 0; it < iters; it++) {
+#pragma unroll
+    for (int k = 0; k < 16; k++) a[k] = fmaf(a[k], m, c);
+  }
+  float s = 0;
+#pragma unroll
+  for (int k = 0; k < 16; k++) s += a[k];
+  if (s == 12345.678f) out[0] = s;   /* keeps the chains alive without a store on the timed path */
+}
+
 /* ---- scratch of flyb_step_noalloc (include/flyb.h): the step kernel's per-warp workspace slots and its work counter in
  * a file-scope array instead of the cudaMalloc'ed d_bulk / d_counter, for callers that must not allocate.  Every GPU that
  * loads the library holds these FLYB_NOALLOC_SCRATCH_BYTES until exit.  Layout: [0, 256) the work counter (cleared by
@@ -425,6 +442,30 @@ int flyb_step(flyb_handle h, const float* action, float* obs, float* reward, flo
               void* stream) {
   FlyIO<float> io = make_io(h, action, obs, reward, discount, step_type);
   return launch(h, io, (cudaStream_t)stream);
+}
+
+int flyb_fma_peak(int device, double* tflops) {
+  if (cudaSetDevice(device) != cudaSuccess) return 1;
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return 1;
+  float* d = nullptr;
+  if (cudaMalloc(&d, 256) != cudaSuccess) return 1;
+  const int blocks = prop.multiProcessorCount * 8, iters = 1 << 16;
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0); cudaEventCreate(&e1);
+  float best = 1e30f;
+  for (int rep = 0; rep < 5; rep++) {   /* first repetitions warm the clocks; the best of the rest is the peak */
+    cudaEventRecord(e0);
+    fly_fma_peak_kernel<<<blocks, 256>>>(d, iters);
+    cudaEventRecord(e1);
+    if (cudaEventSynchronize(e1) != cudaSuccess) { cudaFree(d); return 1; }
+    float ms = 0;
+    cudaEventElapsedTime(&ms, e0, e1);
+    if (rep >= 2 && ms < best) best = ms;
+  }
+  cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(d);
+  *tflops = 2.0 * 16.0 * (double)iters * 256.0 * (double)blocks / ((double)best * 1e-3) / 1e12;
+  return 0;
 }
 
 int flyb_step_noalloc(flyb_handle h, const float* action, float* obs, float* reward, float* discount, int32_t* step_type,

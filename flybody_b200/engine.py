@@ -27,7 +27,7 @@ FLAG_LANES16 = 1 << 17
 EXPORTS = ["flyb_create", "flyb_destroy", "flyb_last_error", "flyb_info", "flyb_configure", "flyb_load_clips",
            "flyb_set_clip_ids", "flyb_reset", "flyb_step", "flyb_reset_host", "flyb_step_host", "flyb_get_state",
            "flyb_set_state", "flyb_get_trace", "flyb_episode_stats", "flyb_load_wbpg", "flyb_set_wbpg_phase",
-           "flyb_use_generic_kernel", "flyb_step_noalloc"]
+           "flyb_use_generic_kernel", "flyb_step_noalloc", "flyb_fma_peak"]
 
 
 N_SPEC_MODELS = 4   # csrc/fly_dims_gen.h: FLY_SPEC_COUNT
@@ -106,6 +106,7 @@ def lib():
         L.flyb_reset.argtypes = [vp, vp, vp, vp, vp]
         L.flyb_step.argtypes = [vp, vp, vp, vp, vp, vp, vp]
         L.flyb_step_noalloc.argtypes = [vp, vp, vp, vp, vp, vp, vp]
+        L.flyb_fma_peak.argtypes = [c_i, dp]
         L.flyb_reset_host.argtypes = [vp, u8p, fp, ip]
         L.flyb_step_host.argtypes = [vp, fp, fp, fp, fp, ip]
         L.flyb_get_state.argtypes = [vp, fp, fp, fp, fp, ip]
@@ -124,6 +125,14 @@ def _fp(a):
 
 def _ip(a):
     return a.ctypes.data_as(ctypes.POINTER(ctypes.c_int32)) if a is not None else None
+
+
+def fma_peak_tflops(device: int = 0) -> float:
+    """Measured FP32 FMA peak of the device (flyb_fma_peak)."""
+    out = ctypes.c_double(0)
+    if lib().flyb_fma_peak(int(device), ctypes.byref(out)):
+        raise RuntimeError("flyb_fma_peak failed")
+    return out.value
 
 
 class Engine:

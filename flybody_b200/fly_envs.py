@@ -63,7 +63,8 @@ class BatchedFlyEnv:
     """`num_envs` fruit-fly environments stepped by one CUDA launch per control step."""
 
     def __init__(self, task: str, model: dict, num_envs: int, device=0, seed: int = 0, env_offset: int = 0,
-                 clips=None, trace: bool = False, canonical_actions: bool = False, wbpg=None):
+                 clips=None, trace: bool = False, canonical_actions: bool = False, wbpg=None, action_corruptor=None,
+                 observables_options=None):
         import torch
         if not torch.cuda.is_available():
             raise RuntimeError("flybody_b200 needs a CUDA device (there is no CPU fallback)")
@@ -82,6 +83,28 @@ class BatchedFlyEnv:
         self._discount = torch.ones(N, dtype=torch.float32, device=dev)
         self._step_type = torch.zeros(N, dtype=torch.int32, device=dev)
         self._layout = observation_layout(model)
+        # observables_options (tasks/base.py:127: walker.observables.set_options): of dm_control's per-observable options the
+        # batched engine honours `enabled` (a disabled observable is left out of the observation dict and the spec); the kernel
+        # still computes it.  Either {"enabled": ...} for all, or {"walker/<name>" | "<name>": {"enabled": ...}}.
+        if observables_options:
+            per = observables_options if all(isinstance(v, dict) for v in observables_options.values()) else \
+                {k: observables_options for k in self._layout}
+            for key, opts in per.items():
+                unknown = set(opts) - {"enabled"}
+                if unknown:
+                    raise NotImplementedError(f"observables_options: only 'enabled' is supported by the batched engine, got {sorted(unknown)}")
+                full = key if key in self._layout else "walker/" + key
+                if full not in self._layout:
+                    raise KeyError(f"observables_options: no observable {key!r}")
+                if not opts.get("enabled", True):
+                    del self._layout[full]
+        # action_corruptor (tasks/template_task.py:68-70): called on the [num_envs, action_dim] CUDA tensor of real-valued
+        # actions before every control step, as corruptor(action, generator) -> action (generator: a torch.Generator on the
+        # env's device seeded from `seed`, standing in for the reference's random_state)
+        self._corruptor = action_corruptor
+        self._gen = torch.Generator(device=dev)
+        self._gen.manual_seed(int(seed) + 7919 * int(env_offset))
+        self._clip_tables = clips
         self._canonical = bool(canonical_actions)
         self._amin = torch.as_tensor(np.asarray(model["action_min"], np.float32), device=dev)
         self._amax = torch.as_tensor(np.asarray(model["action_max"], np.float32), device=dev)
@@ -108,6 +131,8 @@ class BatchedFlyEnv:
         a = action.to(device=self.device, dtype=self._torch.float32)
         if self._canonical:  # CanonicalSpecWrapper / task_utils.canonical2real (vnl_ray/tasks/task_utils.py:53-76)
             a = self._amin + (a.clamp(-1.0, 1.0) + 1.0) * 0.5 * (self._amax - self._amin)
+        if self._corruptor is not None:
+            a = self._corruptor(a, self._gen).to(device=self.device, dtype=self._torch.float32)
         a = a.contiguous()
         assert a.shape == (self.num_envs, self._A), f"action must be [{self.num_envs}, {self._A}]"
         self.engine.step_ptr(a.data_ptr(), self._obs.data_ptr(), self._reward.data_ptr(), self._discount.data_ptr(),
@@ -140,6 +165,39 @@ class BatchedFlyEnv:
     def set_next_trajectory_index(self, idx):
         """`WalkImitation.set_next_trajectory_index` (walk_imitation.py:86-89), per env or one index for all."""
         ids = np.full(self.num_envs, int(idx), np.int32) if np.isscalar(idx) else np.asarray(idx, np.int32)
+        self.engine.set_clip_ids(ids)
+
+    def set_next_trajectory(self, qpos, qvel, env=None):
+        """`InferenceWalkingTrajectoryLoader.set_next_trajectory` (tasks/trajectory_loaders.py:241-248): a custom centre-of-mass
+        trajectory, qpos (T, 7) and qvel (T, 6), becomes the reference of the next episode - of every env, or of the envs listed
+        in `env`.  Joint and site features of the row are zero (in inference mode the reward is the constant 1,
+        walk_imitation.py:153-154; the ghost, ref_displacement / ref_root_quat and the com-distance termination use the root
+        pose only).  The trajectory is appended to the device clip table."""
+        if self.task_name != "walk_imitation":
+            raise ValueError("set_next_trajectory belongs to walk_imitation")
+        qpos, qvel = np.asarray(qpos, np.float64), np.asarray(qvel, np.float64)
+        if qpos.ndim != 2 or qpos.shape[1] != 7 or qvel.shape != (qpos.shape[0], 6):
+            raise ValueError("qpos must be (T, 7) and qvel (T, 6)")
+        M = self.M
+        nj, ns, T = int(M["n_mocap_joints"]), int(M["n_mocap_sites"]), qpos.shape[0]
+        if T < int(M["future_steps"]) + 2:
+            raise ValueError(f"the trajectory needs at least future_steps + 2 = {int(M['future_steps']) + 2} rows")
+        row = np.zeros((T, (7 + nj) + (6 + nj) + 3 * ns + 4 * nj), np.float32)
+        row[:, :7] = qpos
+        row[:, 7 + nj:13 + nj] = qvel
+        row[:, 13 + 2 * nj + 3 * ns::4] = 1.0            # identity joint quaternions
+        if self._clip_tables is None:
+            rows, off, ln = row, np.zeros(1, np.int32), np.array([T], np.int32)
+        else:
+            r0, o0, l0 = self._clip_tables
+            rows = np.concatenate([r0, row]); off = np.append(o0, len(r0)).astype(np.int32); ln = np.append(l0, T).astype(np.int32)
+        self._clip_tables = (rows, off, ln)
+        self.engine.load_clips(rows, off, ln)
+        ids = np.full(self.num_envs, -1, np.int32)
+        if env is None:
+            ids[:] = len(off) - 1
+        else:
+            ids[np.asarray(env, np.int64)] = len(off) - 1
         self.engine.set_clip_ids(ids)
 
     def episode_stats(self):
@@ -212,17 +270,48 @@ def flight_imitation(wpg_pattern_path=None, ref_path=None, random_state=None, te
                          wbpg=_wbpg.build_tables(base), **kw)
 
 
+class GaussianActionNoise:
+    """An `action_corruptor` (vnl_ray/fly_envs.py:231-233: "add random noise to the action"): zero-mean Gaussian noise with a
+    standard deviation of `std` (scalar or per action dimension), on the device, clipped to the action bounds if given."""
+
+    def __init__(self, std, minimum=None, maximum=None):
+        self.std, self.lo, self.hi = std, minimum, maximum
+
+    def __call__(self, action, generator):
+        import torch
+        std = torch.as_tensor(self.std, dtype=action.dtype, device=action.device)
+        out = action + std * torch.randn(action.shape, dtype=action.dtype, device=action.device, generator=generator)
+        if self.lo is not None:
+            out = torch.maximum(out, torch.as_tensor(self.lo, dtype=action.dtype, device=action.device))
+        if self.hi is not None:
+            out = torch.minimum(out, torch.as_tensor(self.hi, dtype=action.dtype, device=action.device))
+        return out
+
+
 def template_task(random_state=None, joint_filter: float = 0.01, adhesion_filter: float = 0.007, time_limit: float = 1.0,
                   mjcb_control=None, observables_options=None, action_corruptor=None, num_envs: int = 1, device=0,
                   seed: int | None = None, **kw) -> BatchedFlyEnv:
     """The empty no-op walking task (`vnl_ray/fly_envs.py:209-259`, `tasks/template_task.py`): fly on the floor, reward 1,
-    termination on |qacc| only.  The per-env Python hooks of the reference (`mjcb_control`, `action_corruptor`,
-    `observables_options`) have no batched equivalent and must be None; the actuator filters are compiled into the model."""
-    if mjcb_control is not None or action_corruptor is not None or observables_options is not None:
-        raise NotImplementedError("template_task: Python callbacks / observable options are not supported by the batched engine")
-    if (joint_filter, adhesion_filter) != (0.01, 0.007):
-        raise NotImplementedError("template_task: the actuator filter time constants are fixed at model compile time (0.01, 0.007)")
+    termination on |qacc| only.
+
+    joint_filter / adhesion_filter: time constants of the actuator activation filters (fruitfly.py:271-281), run-time model
+    fields here (0 = "filter disabled" would remove the activation states and change the observation layout: not supported).
+    action_corruptor: batched form of the reference's hook, `corruptor(action [N, A] CUDA tensor, torch.Generator) -> action`
+    (e.g. `GaussianActionNoise`).  observables_options: `enabled` only.  mjcb_control: MuJoCo calls it inside every physics
+    step; the control step is one fused kernel launch here, so a per-physics-step Python callback cannot be honoured - use
+    action_corruptor (once per control step, on the device) instead."""
+    if mjcb_control is not None:
+        raise NotImplementedError("template_task: mjcb_control runs inside every physics step; the batched engine fuses the control "
+                                  "step into one launch - pass a per-control-step device hook as action_corruptor instead")
     M = load_model(asset_path("template"))
+    if joint_filter <= 0 or adhesion_filter <= 0:
+        raise NotImplementedError("template_task: a filter time constant of 0 (filter disabled) changes the model's state layout")
+    if (joint_filter, adhesion_filter) != (0.01, 0.007):
+        dyn = np.array(M["act_dynprm"], np.float64)
+        for a, name in enumerate(M["_names_act"]):
+            if int(M["act_actadr"][a]) >= 0:
+                dyn[a] = adhesion_filter if "adhere" in name else joint_filter
+        M["act_dynprm"] = dyn
     if float(time_limit) != 1.0:  # same accumulation as compile_fly.task_tables: first control step with time >= time_limit
         dt, t, k = float(M["opt_timestep"]), 0.0, 0
         while t < time_limit:
@@ -231,7 +320,8 @@ def template_task(random_state=None, joint_filter: float = 0.01, adhesion_filter
             k += 1
         M["time_limit_steps"] = k
         M["max_episode_steps"] = int(round(time_limit / float(M["control_dt"]))) + 1
-    return BatchedFlyEnv("template", M, num_envs, device, _seed(random_state, seed), **kw)
+    return BatchedFlyEnv("template", M, num_envs, device, _seed(random_state, seed), action_corruptor=action_corruptor,
+                         observables_options=observables_options, **kw)
 
 
 def _seed(random_state, seed):

@@ -132,6 +132,10 @@ int flyb_get_trace(flyb_handle h, int32_t* ints, float* reals);
  * must be 0 for the physics to be the reference's); [5] reset passes; [6] control steps; [7] unused. */
 int flyb_episode_stats(flyb_handle h, double* out8);
 
+/* Measurement utility (no reference counterpart): FP32 fused-multiply-add throughput of the device in TFLOP/s, measured with
+ * a register-resident FMA micro-benchmark - the denominator of the FP32-pipe fractions bench.py reports. */
+int flyb_fma_peak(int device, double* tflops);
+
 #ifdef __cplusplus
 }
 #endif

@@ -50,6 +50,9 @@ def test_reset_and_steps_match_oracle(models, walk_clip, task):
     rng = np.random.RandomState(0)
     actions = [rng.uniform(M["action_min"], M["action_max"]).astype(np.float32) for _ in range(12)]
     o, ref = _oracle_rollout(M, rows, actions)
+    from flybody_b200.fly_envs import observation_layout
+    from tests.test_gpu_hetero import _block_errors, STIFF, TOL_STIFF, TOL_KIN
+    layout = observation_layout(M)
     st, obs = eng.reset_host()
     assert (st == 0).all() and _rel(obs[0], ref[0][1]) < 2e-5
     worst = 0.0
@@ -57,8 +60,12 @@ def test_reset_and_steps_match_oracle(models, walk_clip, task):
         st, r, g, obs = eng.step_host(np.tile(a, (N, 1)))
         ost, orr, og, oobs = ref[k + 1]
         assert (st == ost).all() and (g == og).all()
+        # reward: 1e-5 of max(1, |r|) - the walking reward reaches 20, where one float32 ulp is 1.9e-6 and the exponent sums
+        # 264 squared differences; absolute 1e-5 holds wherever |r| <= 1 (ball, flight, template)
         assert abs(float(r[0]) - orr) <= 1e-5 * max(1.0, abs(orr))
-        assert _rel(obs[0], oobs) < 5e-4
+        # every observation block on its own physical scale (tests/test_gpu_hetero.py), a tenth of the rollout bounds
+        for name, e in _block_errors(layout, obs[0], oobs).items():
+            assert e < 0.1 * (TOL_STIFF if name in STIFF else TOL_KIN), (k, name, e)
         assert (obs == obs[0]).all(), "identical envs must produce identical bits"
         worst = max(worst, _rel(obs[0], oobs))
         tr = eng.get_trace()
@@ -85,7 +92,7 @@ def test_one_physics_step_tolerance_and_contact_pairs(models):
     eng.step_host(a)
     s, tr = eng.get_state(), eng.get_trace()
     assert (tr["overflow"] == 0).all()
-    checked = strict = 0
+    checked = strict = over = 0
     for i in range(N):
         o = OracleEnv(M)
         o.d("qpos")[:] = np.float32(qs[i]); o.d("qvel")[:] = np.float32(vs[i]); o.d("act")[:] = np.float32(act[i])
@@ -107,7 +114,9 @@ def test_one_physics_step_tolerance_and_contact_pairs(models):
         strict += not violent
         assert _rel(s["qpos"][i], o.d("qpos")) <= 1e-5, i
         assert _rel(s["qvel"][i], o.d("qvel")) <= tol, (i, float(np.abs(o.d("qacc")).max()))
-    assert checked >= N // 2 and strict >= N // 3
+        over += _rel(s["qvel"][i], o.d("qvel")) > 1e-5
+    print(f"\none physics step, {N} random states: {strict} below 1e6 cm/s^2 held to 1e-5; {over} of the {N - strict} violent ones exceed 1e-5 in qvel")
+    assert checked >= N // 2 and strict >= N // 3 and over <= 6
     eng.close()
 
 
