@@ -11,9 +11,10 @@ leading batch dimension:
                             MultivariateNormalDiagHead), torch, random init (no checkpoints here)
   BatchedFeedForwardActor   select_action / observe_first / observe / update with the reference actor's action_delay and
                             observation_callback arguments
-  NStepTransitionAdder      acme's n-step transitions (o_t, a_t, R, D, o_{t+n}) per env, with the shrinking-horizon flush
-                            at episode end, assembled from ring buffers on the device and shipped to a `sink` callable in
-                            batches (the stand-in for the reverb client, which is not installed here)
+  NStepTransitionAdder      acme's n-step transitions (o_s, a_s, R, D, o_{s+h}) per env - growing horizons at the start of an
+                            episode, full horizon n_step in between, shrinking horizons at its end - assembled from ring
+                            buffers on the device and shipped to a `sink` callable in batches (the stand-in for the reverb
+                            client, which is not installed here)
   BatchedEnvironmentLoop    acme.EnvironmentLoop over a batched, auto-resetting environment
 
 acme / sonnet / reverb are third-party and absent: their semantics are restated (acme adders/reverb/transition.py, acme
@@ -79,16 +80,22 @@ class LayerNormMLPPolicy(nn.Module):
 
 
 class NStepTransitionAdder:
-    """acme's NStepTransitionAdder for N environments at once.
+    """acme's NStepTransitionAdder (dm-acme adders/reverb/transition.py; the reference leaves dm-acme unpinned, this restates
+    the current release) for N environments at once.
 
-    For the step sequence (o_0, a_0, r_0, d_0, o_1, ...) of one episode it emits, for every start s,
+    For the step sequence (o_0, a_0, r_0, d_0, o_1, ...) of one episode acme writes one transition after EVERY step t (t = 1, 2,
+    ... counts the steps taken): from s = max(0, t - n_step) to t, i.e. horizon h = min(t, n_step) - the growing horizons
+    (o_0 -> o_1), (o_0 -> o_2), ... at the start of an episode, then the sliding full horizon (`add`: `_first_idx` only advances
+    once `episode_steps >= n_step`, `_write` runs every step) - and, when the episode ends at t = L, the shrinking horizons from
+    s = max(0, L - n_step) + 1 .. L - 1 to L (`_write_last`).  Each transition is
         (o_s, a_s, R = sum_{k<h} (prod_{j<k} discount * d_{s+j}) r_{s+k}, D = discount^(h-1) prod_{k<h} d_{s+k}, o_{s+h})
-    with h = n_step once n_step steps are available, and h = n_step-1 .. 1 for the last starts when the episode ends
-    (acme `_write` / `_write_last`; the final factor of `discount` is left to the learner, as in acme).
-    Ring buffers live on `device`; every call ships the transitions it completed to `sink(dict)` as one batch."""
+    (`_compute_cumulative_quantities`: the last factor of `discount` is left to the learner).
+    Ring buffers live on `device`.  Every call ships two batches to `sink(dict)`: the per-step transitions as FIXED-SHAPE
+    [N, ...] tensors with a boolean `valid` mask (no host synchronisation), and - only when an episode ended in this call, which
+    costs the call's single device-to-host read - the shrinking-horizon transitions of the ended envs."""
 
     def __init__(self, num_envs: int, obs_dim: int, action_dim: int, n_step: int, discount: float, device="cuda",
-                 sink: Optional[Callable[[dict], None]] = None):
+                 sink: Optional[Callable[[dict], None]] = None, count_on_host: bool = True):
         self.N, self.n, self.gamma = int(num_envs), int(n_step), float(discount)
         dev = torch.device(device)
         self.obs = torch.zeros((self.N, self.n + 1, obs_dim), device=dev)
@@ -100,19 +107,23 @@ class NStepTransitionAdder:
         self._k = torch.arange(self.n, device=dev)
         self._env = torch.arange(self.N, device=dev)
         self.sink = sink
-        self.num_written = 0
+        self.written = torch.zeros((), dtype=torch.long, device=dev)     # transitions shipped so far (device-side counter)
+        self._count_on_host = count_on_host
+
+    @property
+    def num_written(self) -> int:
+        return int(self.written)
 
     def reset(self):
         self.count.zero_(); self.started.zero_()
 
     def add_first(self, timestep, mask: Optional[torch.Tensor] = None):
-        """Start of an episode for the envs in `mask` (default: those whose step_type is FIRST)."""
+        """Start of an episode for the envs in `mask` (default: those whose step_type is FIRST).  Fixed shapes, no sync."""
         obs = batch_concat(timestep.observation)
         m = (timestep.step_type == FIRST) if mask is None else mask
-        e = self._env[m]
-        self.count[e] = 0
-        self.started[e] = True
-        self.obs[e, 0] = obs[e]
+        self.count = torch.where(m, torch.zeros_like(self.count), self.count)
+        self.started = self.started | m
+        self.obs[:, 0] = torch.where(m[:, None], obs, self.obs[:, 0])
 
     def _returns(self, env, start, horizon):
         """n-step return and discount of the transitions (env[i], start[i]) over horizon[i] <= n steps."""
@@ -127,45 +138,55 @@ class NStepTransitionAdder:
         D = run[:, -1] / self.gamma                                                # discount^(h-1) * prod d
         return R, D
 
+    def _batch(self, env, start, hor):
+        R, D = self._returns(env, start, hor)
+        return {"observation": self.obs[env, start % (self.n + 1)], "action": self.act[env, start % self.n], "reward": R,
+                "discount": D, "next_observation": self.obs[env, (start + hor) % (self.n + 1)], "env": env, "start": start,
+                "horizon": hor}
+
     def add(self, action: torch.Tensor, next_timestep):
         """Append (a_t, r_t, d_t, o_{t+1}) for every env that is inside an episode; envs whose `next_timestep` is FIRST
         (auto-reset inside env.step) start a new episode instead and their action is ignored, as the env ignored it."""
         st = next_timestep.step_type
         first = st == FIRST
-        if bool(first.any()):
-            self.add_first(next_timestep, first)
+        self.add_first(next_timestep, first)
         live = self.started & ~first
         obs = batch_concat(next_timestep.observation)
-        e = self._env[live]
-        c = self.count[e]
-        self.act[e, c % self.n] = action[e]
-        self.rew[e, c % self.n] = next_timestep.reward[e]
-        self.disc[e, c % self.n] = next_timestep.discount[e]
-        self.obs[e, (c + 1) % (self.n + 1)] = obs[e]
-        self.count[e] = c + 1
+        e = self._env
         c = self.count
-        # full-horizon transition of every env that has n steps behind it
-        env = self._env[live & (c >= self.n)]
-        start = c[env] - self.n
-        hor = torch.full_like(start, self.n)
-        # shrinking-horizon flush of the envs whose episode just ended
-        last = self._env[live & (st == LAST)]
-        if last.numel():
-            j = torch.arange(1, self.n, device=last.device)
-            s = c[last][:, None] - self.n + j[None, :]                             # starts count-n+1 .. count-1
-            ok = s >= 0
-            env = torch.cat([env, last[:, None].expand(-1, self.n - 1)[ok]])
-            start = torch.cat([start, s[ok]])
-            hor = torch.cat([hor, (self.n - j)[None, :].expand(last.numel(), -1)[ok]])
-        if env.numel() == 0:
-            return 0
-        R, D = self._returns(env, start, hor)
-        batch = {"observation": self.obs[env, start % (self.n + 1)], "action": self.act[env, start % self.n], "reward": R,
-                 "discount": D, "next_observation": self.obs[env, (start + hor) % (self.n + 1)], "env": env, "start": start}
-        self.num_written += int(env.numel())
+        slot, oslot = c % self.n, (c + 1) % (self.n + 1)
+        lv = live[:, None]
+        self.act[e, slot] = torch.where(lv, action, self.act[e, slot])
+        self.rew[e, slot] = torch.where(live, next_timestep.reward, self.rew[e, slot])
+        self.disc[e, slot] = torch.where(live, next_timestep.discount, self.disc[e, slot])
+        self.obs[e, oslot] = torch.where(lv, obs, self.obs[e, oslot])
+        c = torch.where(live, c + 1, c)
+        self.count = c
+        # the transition acme writes after every step: from max(0, t - n) over min(t, n) steps (fixed shape, masked)
+        start = torch.clamp(c - self.n, min=0)
+        hor = torch.clamp(c, max=self.n).clamp(min=1)
+        batch = self._batch(e, start, hor)
+        batch["valid"] = live
+        self.written += live.sum()
         if self.sink is not None:
             self.sink(batch)
-        return int(env.numel())
+        # shrinking-horizon flush of the envs whose episode just ended: starts max(0, L - n) + 1 .. L - 1, all ending at L
+        ended = live & (st == LAST)
+        if not bool(ended.any()):        # the call's one host read
+            return
+        last = e[ended]
+        j = torch.arange(1, self.n, device=last.device)
+        s = c[last][:, None] - self.n + j[None, :]
+        ok = s >= 1
+        env2 = last[:, None].expand(-1, self.n - 1)[ok]
+        start2 = s[ok]
+        hor2 = (self.n - j)[None, :].expand(last.numel(), -1)[ok]
+        if env2.numel():
+            tail = self._batch(env2, start2, hor2)
+            tail["valid"] = torch.ones_like(env2, dtype=torch.bool)
+            self.written += env2.numel()
+            if self.sink is not None:
+                self.sink(tail)
 
 
 class BatchedFeedForwardActor:

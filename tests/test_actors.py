@@ -1,5 +1,7 @@
-"""Host-side logic of the batched actor (flybody_b200/actors.py) on CPU tensors: the n-step adder against a per-env list
-implementation of acme's NStepTransitionAdder semantics, the policy head, action delay and the environment loop."""
+"""The batched actor (flybody_b200/actors.py): the n-step adder against a per-env list implementation of acme's
+NStepTransitionAdder sequence (growing horizons at the start of an episode, the sliding full horizon, shrinking horizons at its
+end), the policy head, action delay and the environment loop - on CPU tensors, and (-m gpu) the same checks on CUDA tensors
+plus the whole actor loop over the real batched environment."""
 import collections
 
 import numpy as np
@@ -43,34 +45,43 @@ class FakeEnv:
         return TimeStep(torch.as_tensor(st), torch.as_tensor(r), torch.as_tensor(d), self._obs())
 
 
-def _reference_transitions(steps, n, gamma):
-    """One episode as [(o, a, r, d, o_next), ...] -> acme's n-step transitions, the plain way."""
-    out = []
+def _reference_transitions(steps, n, gamma, finished=True):
+    """One episode as [(o, a, r, d, o_next), ...] -> the transitions acme's NStepTransitionAdder writes, in its order
+    (adders/reverb/transition.py): after every step t the transition from max(0, t - n) to t; at the end of the episode the
+    shrinking ones from max(0, T - n) + 1 .. T - 1 to T."""
     T = len(steps)
-    starts = list(range(0, T - n + 1)) + [s for s in range(max(0, T - n + 1), T)]
-    for s in starts:
-        h = min(n, T - s)
+    spans = [(max(0, t - n), t) for t in range(1, T + 1)]
+    if finished:
+        spans += [(s, T) for s in range(max(0, T - n) + 1, T)]
+    out = []
+    for s, e in spans:
         R, run = 0.0, 1.0
-        for k in range(h):
-            R += run * steps[s + k][2]
-            run *= gamma * steps[s + k][3]
-        out.append((s, steps[s][0], steps[s][1], R, run / gamma, steps[s + h - 1][4]))
+        for k in range(s, e):
+            R += run * steps[k][2]
+            run *= gamma * steps[k][3]
+        out.append((s, steps[s][0], steps[s][1], R, run / gamma, steps[e - 1][4]))
     return out
 
 
-@pytest.mark.parametrize("n_step", [1, 3, 5])
-def test_nstep_adder_matches_per_env_reference(n_step):
+def _check_adder(n_step, device):
     N, O, Adim, gamma = 9, 6, 4, 0.95
     env = FakeEnv(N, O, seed=n_step)
     got = collections.defaultdict(list)
+    dev = torch.device(device)
+
+    def to(ts):
+        return TimeStep(ts.step_type.to(dev), None if ts.reward is None else ts.reward.to(dev),
+                        None if ts.discount is None else ts.discount.to(dev), {k: v.to(dev) for k, v in ts.observation.items()})
 
     def sink(b):
+        b = {k: v.cpu() for k, v in b.items()}
         for i in range(len(b["env"])):
-            got[int(b["env"][i])].append(tuple(np.asarray(b[k][i]) for k in ("start", "observation", "action", "reward", "discount", "next_observation")))
+            if bool(b["valid"][i]):
+                got[int(b["env"][i])].append(tuple(np.asarray(b[k][i]) for k in ("start", "observation", "action", "reward", "discount", "next_observation")))
 
-    adder = A.NStepTransitionAdder(N, O, Adim, n_step, gamma, device="cpu", sink=sink)
+    adder = A.NStepTransitionAdder(N, O, Adim, n_step, gamma, device=device, sink=sink)
     ts = env.reset()
-    adder.add_first(ts)
+    adder.add_first(to(ts))
     episodes = [[] for _ in range(N)]       # finished + running episodes per env
     cur = [[] for _ in range(N)]
     prev = A.batch_concat(ts.observation).numpy().copy()
@@ -78,7 +89,7 @@ def test_nstep_adder_matches_per_env_reference(n_step):
     for t in range(60):
         a = torch.as_tensor(rng.normal(size=(N, Adim)), dtype=torch.float32)
         ts = env.step(a)
-        adder.add(a, ts)
+        adder.add(a.to(dev), to(ts))
         o = A.batch_concat(ts.observation).numpy()
         for i in range(N):
             if int(ts.step_type[i]) == 0:
@@ -93,11 +104,9 @@ def test_nstep_adder_matches_per_env_reference(n_step):
         want = []
         for ep in episodes[i]:
             want += _reference_transitions(ep, n_step, gamma)
-        # the running episode has only emitted its full-horizon transitions
-        want += [w for w in _reference_transitions(cur[i], n_step, gamma) if w[0] + n_step <= len(cur[i])]
+        want += _reference_transitions(cur[i], n_step, gamma, finished=False)
         have = got[i]
         assert len(have) == len(want), (i, len(have), len(want))
-        # per episode the order is full-horizon transitions as they complete, then the flush: same as the reference list
         for h, w in zip(have, want):
             assert int(h[0]) == w[0]
             np.testing.assert_allclose(h[1], w[1], atol=0); np.testing.assert_allclose(h[2], w[2], atol=0)
@@ -105,6 +114,39 @@ def test_nstep_adder_matches_per_env_reference(n_step):
             np.testing.assert_allclose(h[5], w[5], atol=0)
         total += len(want)
     assert adder.num_written == total and total > 200
+
+
+@pytest.mark.parametrize("n_step", [1, 3, 5])
+def test_nstep_adder_matches_per_env_reference(n_step):
+    _check_adder(n_step, "cpu")
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n_step", [1, 5, 50])
+def test_nstep_adder_matches_per_env_reference_on_cuda(n_step):
+    _check_adder(n_step, "cuda")
+
+
+@pytest.mark.gpu
+def test_actor_loop_over_the_batched_fly_env():
+    """BASELINE.json configs[3]: policy (741 -> 512 x 4 -> 2 x 59), env and n-step adder on one GPU, 256 walk_imitation envs."""
+    from flybody_b200 import fly_envs
+    env = fly_envs.walk_imitation("synthetic:4:200:0", num_envs=256, seed=2)
+    O, Adim = env.flat_observation.shape[1], env.action_spec().shape[0]
+    torch.manual_seed(0)
+    pi = A.LayerNormMLPPolicy(O, Adim).to(env.device)
+    got = {"n": 0, "bad": 0}
+
+    def sink(b):
+        v = b["valid"]
+        got["n"] += int(v.sum())
+        got["bad"] += int((~torch.isfinite(b["reward"][v])).sum()) + int((~torch.isfinite(b["next_observation"][v])).sum())
+    adder = A.NStepTransitionAdder(256, O, Adim, 5, 0.95, device=env.device, sink=sink)
+    loop = A.BatchedEnvironmentLoop(env, A.BatchedFeedForwardActor(pi, adder, generator=torch.Generator(device=env.device).manual_seed(1)))
+    n, rsum = loop.run(40)
+    assert n == 40 * 256 and np.isfinite(rsum) and rsum > 0
+    assert got["n"] == adder.num_written >= 40 * 256 - 256 and got["bad"] == 0
+    env.close()
 
 
 def test_policy_head_and_batch_concat_order():
@@ -129,7 +171,7 @@ def test_action_delay_and_environment_loop():
     env = FakeEnv(N, O, seed=3)
     pi = A.LayerNormMLPPolicy(O, Adim, layer_sizes=(16,))
     seen = []
-    adder = A.NStepTransitionAdder(N, O, Adim, 2, 0.9, device="cpu", sink=lambda b: seen.append(int(len(b["env"]))))
+    adder = A.NStepTransitionAdder(N, O, Adim, 2, 0.9, device="cpu", sink=lambda b: seen.append(int(b["valid"].sum())))
     actor = A.BatchedFeedForwardActor(pi, adder, action_delay=2, generator=torch.Generator().manual_seed(0))
     obs = env.reset().observation
     assert float(actor.select_action(obs).abs().max()) == 0 and float(actor.select_action(obs).abs().max()) == 0

@@ -8,13 +8,14 @@ from flybody_b200.compile_fly import load_model
 from flybody_b200.engine import Engine
 from flybody_b200.model_pack import asset_path
 
-N = int(os.environ.get("N", 2368)); lvl = int(os.environ.get("LEVEL", 2)); warps = int(os.environ.get("WARPS", 4))
+N = int(os.environ.get("N", 4144)); lvl = os.environ.get("LEVEL"); warps = os.environ.get("WARPS")   # default: the library's configuration
 steps = int(os.environ.get("STEPS", 4)); task = os.environ.get("TASK", "walk_imitation")
 M = load_model(asset_path(task))
 eng = Engine(M, N, 0, seed=1)
 if task == "walk_imitation":
     eng.load_clips(*C.synthetic_table(M, 32, 600, 0))
-eng.configure(lvl, warps, int(os.environ.get("BPS", 0)))
+if lvl is not None and warps is not None:
+    eng.configure(int(lvl), int(warps), int(os.environ.get("BPS", 0)))
 dev = torch.device("cuda:0")
 obs = torch.zeros((N, eng.obs_dim), device=dev); r = torch.zeros(N, device=dev); g = torch.zeros(N, device=dev)
 st = torch.zeros(N, dtype=torch.int32, device=dev)
