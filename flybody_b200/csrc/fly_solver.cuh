@@ -53,14 +53,13 @@ FLY_INL S fly_update_constraint(const DModel<T>& m, const Ws<T>& w, const S* jar
         for (int k = 0; k < 3; k++) w.efc_state[r + k] = FLY_ST_CONE;
       }
       if (cone_hess) {
+        /* Hessian block of the cone cost 1/2 Dm (N - mu T)^2 in the rows' own units: Dm F (g g^T + c p p^T) F with F = diag(fr),
+           g = (1, -mu U1/T, -mu U2/T), p = (0, -U2/T, U1/T), c = mu (mu T - N) / T >= 0 in this zone - positive semi-definite of
+           rank 2.  Its factor S (3 x 2, H = S S^T) is what the Newton step needs: columns sqrt(Dm) F g and sqrt(Dm c) F p. */
         T* h = w.con_hc + 9 * ci;
-        S Hu[9];
-        Hu[0] = 1;
-        for (int i = 1; i < 3; i++) Hu[i] = Hu[3 * i] = -mu * U[i] / Tn;
-        for (int i = 1; i < 3; i++)
-          for (int j = 1; j < 3; j++)
-            Hu[3 * i + j] = mu * N / (Tn * Tn * Tn) * U[i] * U[j] + (i == j ? mu * mu - mu * N / Tn : S(0));
-        for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) h[3 * i + j] = (T)(Dm * fr[i] * fr[j] * Hu[3 * i + j]);
+        const S sd = sqrt(Dm), sc = sqrt(Dm * fmax_(S(0), mu * (mu * Tn - N) / Tn));
+        h[0] = (T)(sd * fr[0]); h[1] = (T)(-sd * fr[1] * mu * U[1] / Tn); h[2] = (T)(-sd * fr[2] * mu * U[2] / Tn);
+        h[3] = 0; h[4] = (T)(-sc * fr[1] * U[2] / Tn); h[5] = (T)(sc * fr[2] * U[1] / Tn);
       }
     }
   }
@@ -181,47 +180,42 @@ FLY_INL void warp_argmax(T& v, int& idx) {
 #endif
 }
 
-/* dense n x n solve K x = rhs (in place, rhs <- x), LU with partial pivoting, one matrix row per lane */
+/* dense n x n solve K z = rhs for a symmetric positive definite K (lower triangle given, row-major, destroyed; rhs <- z):
+ * Cholesky K = L L^T without pivoting, the forward substitution folded into the elimination, then the back substitution
+ * column by column.  Two barriers per column going down, one coming back; no pivot search, no shuffles.
+ * scratch: 2 n numbers (1 / L_kk and the intermediate vector y). */
 template <class T>
-FLY_FN void fly_lu_solve(T* K, int n, T* rhs) {
+FLY_FN void fly_chol_solve(T* K, int n, T* rhs, T* scratch) {
+  T *dinv = scratch, *y = scratch + n;
   for (int k = 0; k < n; k++) {
-    T best = -1; int bi = k;
-    FLY_FOR(i, n - k) { const T v = fabs_(K[(k + i) * n + k]); if (v > best) { best = v; bi = k + i; } }
-    warp_argmax(best, bi);
-    if (bi != k) {
-      FLY_FOR(j, n) { const T t = K[k * n + j]; K[k * n + j] = K[bi * n + j]; K[bi * n + j] = t; }
-      FLY_SYNC();
-      FLY_LANE0 { const T t = rhs[k]; rhs[k] = rhs[bi]; rhs[bi] = t; }
-      FLY_SYNC();
-    }
-    const T pk = K[k * n + k];
-    if (fabs_(pk) >= minval<T>()) {
-      /* multipliers into column k, then the trailing block as a 4 x 8 lane tile (rows x columns: consecutive lanes on
-         consecutive columns; one row per lane made every access a stride-n gather and left n - k lanes busy) */
-      const int nr = n - k - 1;
-      const T rk = rhs[k];
-      FLY_FOR(i, nr) {
+    FLY_SYNC();                       /* the trailing update of column k - 1 (or the caller's fill) is visible */
+    const T inv = T(1) / sqrt(fmax_(K[k * n + k], minval<T>()));
+    const T yk = rhs[k] * inv;
+    const int nr = n - k - 1;
+    FLY_FOR(i, nr + 1) {
+      if (i == nr) { dinv[k] = inv; y[k] = yk; }
+      else {
         const int r = k + 1 + i;
-        const T l = K[r * n + k] / pk;
+        const T l = K[r * n + k] * inv;
         K[r * n + k] = l;
-        rhs[r] -= l * rk;
-      }
-      FLY_SYNC();
-      FLY_FOR_ROW(i, nr) {
-        const int r = k + 1 + i;
-        const T l = K[r * n + k];
-        FLY_FOR_COL(j, k + 1, n) K[r * n + j] -= l * K[k * n + j];
+        rhs[r] -= l * yk;
       }
     }
     FLY_SYNC();
+    /* trailing block, lower triangle: rows across lane / 8, columns across lane % 8 */
+    FLY_FOR_ROW(i, nr) {
+      const int r = k + 1 + i;
+      const T l = K[r * n + k];
+      FLY_FOR_COL(j, k + 1, r + 1) K[r * n + j] -= l * K[j * n + k];
+    }
   }
-  for (int k = n - 1; k >= 0; k--) {
-    T s = 0;
-    FLY_FOR(j, n - k - 1) s += K[k * n + k + 1 + j] * rhs[k + 1 + j];
-    s = warp_sum(s);
-    const T pk = K[k * n + k];
-    FLY_SYNC();
-    FLY_LANE0 rhs[k] = fabs_(pk) < minval<T>() ? T(0) : (rhs[k] - s) / pk;
+  FLY_SYNC();
+  for (int k = n - 1; k >= 0; k--) {   /* L^T z = y: z_k = y_k / L_kk, then y_i -= L_ki z_k for i < k (row k is contiguous) */
+    const T zk = y[k] * dinv[k];
+    FLY_FOR(i, k + 1) {
+      if (i == k) rhs[k] = zk;
+      else y[i] -= K[k * n + i] * zk;
+    }
     FLY_SYNC();
   }
 }
@@ -321,40 +315,65 @@ FLY_FN void fly_newton(const DModel<T>& m, const Ws<T>& w) {
     fly_a_mul(w, nefc, Acp, h);
     FLY_FOR(r, nefc) h[r] = theta * b0[r] + Acp[r];
     FLY_SYNC();
-    /* active rows; K = I + W A on them, rhs = W h */
-    const int na = warp_compact(nefc, [&](int r) -> bool { return w.efc_state[r] != FLY_ST_SATISFIED; }, w.lim_item, FLY_MAXEFC);
+    /* Newton step (I + W A) x = W h with W the block-diagonal Hessian of the constraint cost (D_r on quadratic rows, the
+       rank-2 cone block S_c S_c^T on contacts in the cone zone).  With W = S S^T and x = S z this is the symmetric positive
+       definite system (I + S^T A S) z = S^T h: one column of S per quadratic row (a single entry sqrt(D_r)) and two per
+       cone contact - smaller than the row system, Cholesky instead of pivoted LU.  lim_item lists the columns by their
+       first row: a quadratic row, or row r0 / r0 + 1 of a cone contact for its first / second column. */
+    const int nz = warp_compact(nefc, [&](int r) -> bool {
+      const int stt = w.efc_state[r];
+      return stt == FLY_ST_QUADRATIC || (stt == FLY_ST_CONE && r - w.grp_row[w.efc_g[r]] < 2);
+    }, w.lim_item, FLY_MAXEFC);
     FLY_SYNC();
     T* K = w.efc_K;
     T* lam = w.efc_lam;
-    /* rows across lane / 8, columns across lane % 8 (consecutive lanes on consecutive columns of K and A) */
-    FLY_FOR_ROW(i, na) {
-      const int r = w.lim_item[i], g = w.efc_g[r], r0 = w.grp_row[g];
-      if (w.efc_state[r] == FLY_ST_CONE) {
-        const T* hc = w.con_hc + 9 * w.grp_con[g] + 3 * (r - r0);
-        const T h0 = hc[0], h1 = hc[1], h2 = hc[2];
-        FLY_FOR_COL(j, 0, na) {
-          const int cj = w.lim_item[j];
-          K[i * na + j] = (i == j ? T(1) : T(0)) + h0 * w.efc_A[r0 * nefc + cj] + h1 * w.efc_A[(r0 + 1) * nefc + cj]
-                          + h2 * w.efc_A[(r0 + 2) * nefc + cj];
+    /* column a: rows ra .. ra + na - 1 with entries sa[] */
+#define FLY_SCOL(a, ra, na, sa)                                                                          \
+    int ra, na; T sa[3];                                                                                 \
+    {                                                                                                    \
+      const int r_ = w.lim_item[a];                                                                      \
+      if (w.efc_state[r_] == FLY_ST_CONE) {                                                              \
+        const int g_ = w.efc_g[r_], r0_ = w.grp_row[g_];                                                 \
+        const T* hc_ = w.con_hc + 9 * w.grp_con[g_] + 3 * (r_ - r0_);                                    \
+        ra = r0_; na = 3; sa[0] = hc_[0]; sa[1] = hc_[1]; sa[2] = hc_[2];                                \
+      } else { ra = r_; na = 1; sa[0] = sqrt(w.efc_D[r_]); sa[1] = sa[2] = 0; }                          \
+    }
+    FLY_FOR_ROW(a, nz) {
+      FLY_SCOL(a, ra, na, sa)
+      FLY_FOR_COL(b, 0, a + 1) {
+        FLY_SCOL(b, rb, nb, sb)
+        T acc = a == b ? T(1) : T(0);
+        for (int i = 0; i < na; i++) {
+          T t = 0;
+          for (int j = 0; j < nb; j++) t += w.efc_A[(ra + i) * nefc + rb + j] * sb[j];
+          acc += sa[i] * t;
         }
-      } else {
-        const T D = w.efc_D[r];
-        FLY_FOR_COL(j, 0, na) K[i * na + j] = (i == j ? T(1) : T(0)) + D * w.efc_A[r * nefc + w.lim_item[j]];
+        K[a * nz + b] = acc;
       }
     }
-    FLY_FOR(i, na) {
-      const int r = w.lim_item[i], g = w.efc_g[r], r0 = w.grp_row[g];
-      if (w.efc_state[r] == FLY_ST_CONE) {
-        const T* hc = w.con_hc + 9 * w.grp_con[g] + 3 * (r - r0);
-        lam[i] = (T)(hc[0] * h[r0] + hc[1] * h[r0 + 1] + hc[2] * h[r0 + 2]);
-      } else lam[i] = (T)(w.efc_D[r] * h[r]);
+    FLY_FOR(a, nz) {
+      FLY_SCOL(a, ra, na, sa)
+      S t = 0;
+      for (int i = 0; i < na; i++) t += (S)sa[i] * h[ra + i];
+      lam[a] = (T)t;
     }
     FLY_SYNC();
-    fly_lu_solve(K, na, lam);
-    /* search direction in (theta, c) coordinates: c_p = f + lambda - c, theta_p = -theta */
+    fly_chol_solve(K, nz, lam, w.hit_tmp);   /* hit_tmp: scratch of the collision stage, idle here */
+    /* search direction in (theta, c) coordinates: c_p = f + x - c with x = S z, theta_p = -theta */
     FLY_FOR(r, nefc) cp[r] = f[r] - c[r];
     FLY_SYNC();
-    FLY_FOR(i, na) cp[w.lim_item[i]] += lam[i];
+    FLY_FOR(a, nz) {
+      const int r_ = w.lim_item[a];
+      if (w.efc_state[r_] != FLY_ST_CONE) cp[r_] += (S)(sqrt(w.efc_D[r_]) * lam[a]);
+      else {
+        const int g_ = w.efc_g[r_], r0_ = w.grp_row[g_];
+        if (r_ == r0_) {   /* the lane of a contact's first column adds both columns: they share the three rows */
+          const T* hc_ = w.con_hc + 9 * w.grp_con[g_];
+          for (int k = 0; k < 3; k++) cp[r0_ + k] += (S)(hc_[k] * lam[a] + hc_[3 + k] * lam[a + 1]);
+        }
+      }
+    }
+#undef FLY_SCOL
     FLY_SYNC();
     const S thp = -theta;
     fly_a_mul(w, nefc, Acp, cp);
