@@ -465,8 +465,8 @@ FLY_FN void fly_collision(const DModel<T>& m, const Ws<T>& w) {
     return;
   }
   /* broad phase: bounding spheres (cannot change the result: the narrow phase only reports dist <= margin).  The geom
-     centres are staged in the warp's scratch (qLD | qH, free until fly_crb) so that the 2 x npair position reads are
-     shared-memory loads; bit 16 of the pair word says "geom 1 is a plane" (no geom_type lookup on the way) */
+     centres are staged in qLD (free until fly_crb; shared memory when the launch keeps it there) so that the 2 x npair position
+     reads are close; bit 16 of the pair word says "geom 1 is a plane" (no geom_type lookup on the way) */
   T* gx = (T*)w.qLD;
   FLY_FOR(i, 3 * FLY_DIM(m, ngeom)) gx[i] = w.geom_xpos[i];
   FLY_SYNC();
@@ -545,9 +545,9 @@ FLY_FN void fly_collision(const DModel<T>& m, const Ws<T>& w) {
         /* pair types without an analytic routine.  Always in float64: the portal search branches on signs of small
            differences and its contact point is a barycentric estimate on the last portal, so a float32 run takes other
            branches and lands up to a portal width away (measured: normals off by O(1) on the thin wing ellipsoids) */
-        /* this lane's slice of the warp scratch: portal (float64) | pos1 mat1 pos2 mat2 (working precision) */
-        const Portal<double> P = {(double*)w.qLD + FLY_LANE()};  /* qLD | qH: not live between fly_com_pos and fly_crb */
-        T* gs = (T*)((double*)w.qLD + FLY_PORTAL_WORDS) + FLY_LANE();
+        /* this lane's slice of the env's scratch: portal (float64) | pos1 mat1 pos2 mat2 (working precision) */
+        const Portal<double> P = {(double*)w.efc_A + FLY_LANE()};  /* efc_A: dead between the constraint solve and fly_make_constraint */
+        T* gs = (T*)((double*)w.efc_A + FLY_PORTAL_WORDS) + FLY_LANE();
         for (int k = 0; k < 3; k++) { gs[k * FLY_NL] = c1[k]; gs[(12 + k) * FLY_NL] = c2[k]; }
         for (int k = 0; k < 9; k++) { gs[(3 + k) * FLY_NL] = m1[k]; gs[(15 + k) * FLY_NL] = m2[k]; }
         const CcdObj<double, T> o1 = {t1, gs, gs + 3 * FLY_NL, s1, FLY_NL, 0.5 * (double)margin};

@@ -9,9 +9,9 @@
 #include "fly_model.h"
 #include "fly_math.cuh"
 
-/* tier of an array: 0 = always bulk; 1..5 = goes to the fast arena when the launch's `level` is >= the tier
- * (1: the factorisation of M and the vectors its solves run on; 2: the factorisation of M + dt B; 3: state and solver
- * vectors; 4, 5: kinematics) */
+/* tier of an array: 0 = always bulk; 1..6 = goes to the fast arena when the launch's `level` is >= the tier
+ * (1: the factorisation of M; 2: the vectors its solves run on; 3: the factorisation of M + dt B; 4: state and solver
+ * vectors; 5, 6: kinematics).  `nl` (lanes per env) is part of the signatures for arrays sized per lane. */
 #if defined(__CUDACC__)
 #define FLY_HD __host__ __device__ inline
 #else
@@ -19,32 +19,23 @@
 #endif
 #define FLY_NHIT 4   /* most contacts a primitive pair can produce */
 
-/* qLD | qH (adjacent, same tier) double as the warp's portal scratch of the convex narrow phase (fly_col.cuh:
- * 4 points x 6 float64 x nl lanes, then two geom poses x 12 words x nl lanes; nl = lanes per env, FLY_NL of the kernel), which runs while neither
- * factorisation is live; qLD is padded so that the two together always hold it (72 nl words when T is float) */
-FLY_HD constexpr int fly_qld_count(int nM, int nl) {
-  /* nl <= 16: the scratch (72 nl words) fits qLD alone, so qH may live in another arena; nl = 32: qLD | qH hold it together */
-  const int need = nl <= 16 ? 72 * nl : 72 * nl + 8 - (nM + 4);
-  return nM + 1 > need ? nM + 1 : need;
-}
-
 /* X(name, element-count expression over `m`, tier) ; arrays of T */
 #define FLY_WS_REAL(X)                                                                                       \
-  X(qpos, m.nq, 3) X(qvel, m.nv, 3) X(act, m.na, 3) X(ctrl, m.nu, 3)             \
-  X(warm, m.nv, 3) X(qacc, m.nv, 3)                                                            \
-  X(xpos, 3 * m.nbody, 4) X(xquat, 4 * m.nbody, 4) X(xmat, 9 * m.nbody, 4)              \
-  X(xipos, 3 * m.nbody, 5)                                            \
+  X(qpos, m.nq, 4) X(qvel, m.nv, 4) X(act, m.na, 4) X(ctrl, m.nu, 4)             \
+  X(warm, m.nv, 4) X(qacc, m.nv, 4)                                                            \
+  X(xpos, 3 * m.nbody, 5) X(xquat, 4 * m.nbody, 5) X(xmat, 9 * m.nbody, 5)              \
+  X(xipos, 3 * m.nbody, 6)                                            \
   X(xanchor, 3 * m.njnt, 0) X(xaxis, 3 * m.njnt, 0)                                            \
-  X(geom_xpos, 3 * m.ngeom, 4) X(site_xpos, 3 * m.nsite, 0) X(site_xmat, 9 * m.nsite, 0)\
-  X(scom, 3 * m.nbody, 4) X(cinert, 10 * m.nbody, 5) X(crb, 0, 0)            \
-  X(cdof, 6 * m.nv, 4) X(cdof_dot, 6 * m.nv, 5) X(cvel, 6 * m.nbody, 5)                 \
-  X(qLD, fly_qld_count(m.nM, nl), 1) X(qH, m.nM + 1, 2)                    \
-  X(qDinv, m.nv, 1) X(qHinv, m.nv, 2) X(gpart, 64, 0)                                         \
+  X(geom_xpos, 3 * m.ngeom, 5) X(site_xpos, 3 * m.nsite, 0) X(site_xmat, 9 * m.nsite, 0)\
+  X(scom, 3 * m.nbody, 5) X(cinert, 10 * m.nbody, 6) X(crb, 0, 0)            \
+  X(cdof, 6 * m.nv, 5) X(cdof_dot, 6 * m.nv, 6) X(cvel, 6 * m.nbody, 6)                 \
+  X(qLD, m.nM + 1, 1) X(qH, m.nM + 1, 3)                    \
+  X(qDinv, m.nv, 1) X(qHinv, m.nv, 3) X(gpart, 64, 0)                                         \
   X(act_length, m.nu, 0) X(act_force, m.nu, 0) X(act_dot, m.na, 0)                      \
   X(qfrc_bias, m.nv, 0) X(qfrc_passive, m.nv, 0) X(qfrc_actuator, m.nv, 0)              \
-  X(qfrc_smooth, m.nv, 3) X(qacc_smooth, m.nv, 1) X(qfrc_constraint, m.nv, 3)           \
-  X(sMa, m.nv, 1) X(sgrad, m.nv, 3) X(ssearch, m.nv, 3)          \
-  X(stmp, m.nv, 1)                                                                                    \
+  X(qfrc_smooth, m.nv, 4) X(qacc_smooth, m.nv, 2) X(qfrc_constraint, m.nv, 4)           \
+  X(sMa, m.nv, 2) X(sgrad, m.nv, 4) X(ssearch, m.nv, 4)          \
+  X(stmp, m.nv, 2)                                                                                    \
   X(bodyf, 0, 0) X(boxf, 6 * (m.nfluidbox + m.nfluidgeom), 0)                        \
   X(cacc, 6 * m.nbody, 0) X(cfrc_int, 6 * m.nbody, 0) X(cfrc_ext, 6 * m.nbody, 0)       \
   X(sensordata, m.nsensordata, 0) X(sens_sum, m.nsensordata, 0)                                \
@@ -54,9 +45,9 @@ FLY_HD constexpr int fly_qld_count(int nM, int nl) {
   X(efc_J, FLY_MAXEFC * FLY_MAXCHAIN, 0) X(efc_Y, FLY_MAXEFC * FLY_MAXCHAIN, 0)                \
   X(x_J, FLY_MAXCROSS * FLY_MAXCHAIN, 0) X(x_Y, FLY_MAXCROSS * FLY_MAXCHAIN, 0)                \
   X(efc_pos, FLY_MAXEFC, 0) X(efc_margin, FLY_MAXEFC, 0) X(efc_diag, FLY_MAXEFC, 0)     \
-  X(efc_R, FLY_MAXEFC, 0) X(efc_D, FLY_MAXEFC, 3) X(efc_K0, FLY_MAXEFC, 0)               \
+  X(efc_R, FLY_MAXEFC, 0) X(efc_D, FLY_MAXEFC, 4) X(efc_K0, FLY_MAXEFC, 0)               \
   X(efc_B, FLY_MAXEFC, 0) X(efc_imp, FLY_MAXEFC, 0) X(efc_aref, FLY_MAXEFC, 0)          \
-  X(efc_force, FLY_MAXEFC, 3)        \
+  X(efc_force, FLY_MAXEFC, 4)        \
   X(efc_A, FLY_MAXEFC * FLY_MAXEFC, 0) X(efc_K, FLY_MAXEFC * FLY_MAXEFC, 0)             \
           \
   X(efc_lam, FLY_MAXEFC, 0)                              \
@@ -65,7 +56,7 @@ FLY_HD constexpr int fly_qld_count(int nM, int nl) {
 /* arrays of double: the Newton iterate in constraint space (c, jar = b + A c, ...) cancels to a few parts in 1e4
  * of its terms, so these nefc-sized vectors are kept in float64 even when T is float */
 #define FLY_WS_DBL(X)                                                                                        \
-  X(efc_jar, FLY_MAXEFC, 3) X(efc_jv, FLY_MAXEFC, 3) X(efc_b, FLY_MAXEFC, 0) X(efc_b0, FLY_MAXEFC, 0)        \
+  X(efc_jar, FLY_MAXEFC, 4) X(efc_jv, FLY_MAXEFC, 4) X(efc_b, FLY_MAXEFC, 0) X(efc_b0, FLY_MAXEFC, 0)        \
   X(efc_c, FLY_MAXEFC, 0) X(efc_cp, FLY_MAXEFC, 0) X(efc_Ac, FLY_MAXEFC, 0) X(efc_Acp, FLY_MAXEFC, 0)        \
   X(efc_h, FLY_MAXEFC, 0)
 

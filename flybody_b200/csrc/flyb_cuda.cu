@@ -157,13 +157,6 @@ static int launch(FlybEngine* h, const FlyIO<float>& io, cudaStream_t st, const 
   const size_t smem = fb * EPB;
   if (smem > 227 * 1024 - 2048) { h->err = "shared memory request too large for this smem_level / warps_per_block"; return 1; }
   if (bb > h->bulk_stride) { h->err = "internal: bulk slot too small"; return 1; }
-  {  /* the convex narrow phase borrows qLD (| qH when they share an arena) as one scratch block (fly_col.cuh) */
-    const size_t need = (size_t)(4 * 6 * h->lanes) * sizeof(double) + (size_t)(24 * h->lanes) * sizeof(float);
-    const bool alone = (size_t)fly_qld_count(h->m.nM, h->lanes) * sizeof(float) >= need;
-    const bool together = (h->smem_level == 0 || h->smem_level >= 2) && off.qH >= off.qLD &&
-                          (size_t)(off.qH - off.qLD) + (size_t)(h->m.nM + 1) * sizeof(float) >= need;
-    if (!alone && !together) { h->err = "this smem_level leaves no room for the convex narrow phase's scratch (32 lanes per env need smem_level 0 or >= 2)"; return 1; }
-  }
   int spec = h->no_spec ? -1 : spec_of(h->m);
   const void* kern = pick_kernel(h->lanes, W, h->smem_level, spec);
   if (!kern && spec >= 0) { spec = -1; kern = pick_kernel(h->lanes, W, h->smem_level, -1); }
@@ -354,7 +347,7 @@ int64_t flyb_info(flyb_handle h, int what) {
 }
 
 int flyb_configure(flyb_handle h, int smem_level, int warps_per_block, int blocks_per_sm) {
-  if (smem_level < 0 || smem_level > 5) { h->err = "smem_level must be 0..5"; return 1; }
+  if (smem_level < 0 || smem_level > 6) { h->err = "smem_level must be 0..6"; return 1; }
   if (!pick_kernel(h->lanes, warps_per_block, smem_level, -1) && !pick_kernel(h->lanes, warps_per_block, smem_level, spec_of(h->m))) {
     h->err = "no step kernel compiled for this (lanes, warps_per_block, smem_level); see KERNEL_UNITS in flybody_b200/engine.py"; return 1;
   }

@@ -34,7 +34,7 @@ N_SPEC_MODELS = 4   # csrc/fly_dims_gen.h: FLY_SPEC_COUNT
 # Step-kernel instantiations built into the library: (lanes per env, warps per block, shared-memory level, model index or -1 = any
 # model).  Each is a translation unit of its own (csrc/flyb_kern.cu) that registers its kernel when the library is loaded.
 KERNEL_UNITS = ([(32, 28, 0, i) for i in range(N_SPEC_MODELS)]             # the default: one per shipped task model
-                + [(32, 28, 0, -1), (32, 16, 2, -1), (32, 8, 3, -1)]          # any model; other launch configurations
+                + [(32, 28, 0, -1), (32, 16, 3, -1), (32, 8, 4, -1)]          # any model; other launch configurations
                 + [(16, 16, 0, -1)])                                          # two envs per warp (FLAG_LANES16)
 
 

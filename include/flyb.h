@@ -58,7 +58,7 @@ void flyb_destroy(flyb_handle h);
 const char* flyb_last_error(flyb_handle h);  /* h may be NULL: error of the last failed flyb_create */
 int64_t flyb_info(flyb_handle h, int what);
 
-/* Tuning knobs: smem_level 0..5 (how many workspace tiers live in shared memory, csrc/fly_ws.cuh; default 0: the whole
+/* Tuning knobs: smem_level 0..6 (how many workspace tiers live in shared memory, csrc/fly_ws.cuh; default 0: the whole
  * workspace in per-warp global scratch behind a full-size L1, 28 warps per SM), warps per block (only the combinations built into the library: KERNEL_UNITS in
  * flybody_b200/engine.py) and blocks per SM (0 = as many as fit).  Takes effect at the next launch. */
 int flyb_configure(flyb_handle h, int smem_level, int warps_per_block, int blocks_per_sm);

@@ -155,7 +155,7 @@ def test_results_do_not_depend_on_launch_configuration_or_batch_size(models, wal
     acts = rng.uniform(M["action_min"], M["action_max"], (3, 300, 59)).astype(np.float32)
     outs = []
     from flybody_b200.engine import FLAG_LANES16
-    for (N, lvl, warps, generic) in ((300, 3, 8, 1), (300, 2, 16, 1), (300, 0, 28, 1), (37, 0, 28, 1), (300, 0, 28, 0), (41, 0, 28, 0),
+    for (N, lvl, warps, generic) in ((300, 4, 8, 1), (300, 3, 16, 1), (300, 0, 28, 1), (37, 0, 28, 1), (300, 0, 28, 0), (41, 0, 28, 0),
                                      (300, 0, 16, 16)):
         eng = _engine(M, N, flags=FLAG_LANES16 if generic == 16 else 0)
         eng.configure(lvl, warps)
