@@ -124,7 +124,9 @@ class BatchedFlyEnv:
         if mask is not None:
             mask = mask.to(device=self.device, dtype=self._torch.uint8).contiguous()
             mp = mask.data_ptr()
+        self._torch.cuda.nvtx.range_push("flyb.reset")
         self.engine.reset_ptr(mp, self._obs.data_ptr(), self._step_type.data_ptr(), self._stream())
+        self._torch.cuda.nvtx.range_pop()
         return TimeStep(self._step_type, None, None, self._obs_dict())
 
     def step(self, action) -> TimeStep:
@@ -135,8 +137,10 @@ class BatchedFlyEnv:
             a = self._corruptor(a, self._gen).to(device=self.device, dtype=self._torch.float32)
         a = a.contiguous()
         assert a.shape == (self.num_envs, self._A), f"action must be [{self.num_envs}, {self._A}]"
+        self._torch.cuda.nvtx.range_push("flyb.step")     # NVTX range per control step (visible in nsys / ncu timelines)
         self.engine.step_ptr(a.data_ptr(), self._obs.data_ptr(), self._reward.data_ptr(), self._discount.data_ptr(),
                              self._step_type.data_ptr(), self._stream())
+        self._torch.cuda.nvtx.range_pop()
         self._last_action = a  # keep alive until the launch has consumed it
         return TimeStep(self._step_type, self._reward, self._discount, self._obs_dict())
 

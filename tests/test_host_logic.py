@@ -2,6 +2,7 @@
 import os
 
 import numpy as np
+import pytest
 
 
 def test_observation_layout_matches_survey(models):
@@ -117,3 +118,25 @@ def test_generated_model_sizes_match_the_shipped_assets(models):
         for k, v in zip(fields, vals):
             have = int(e.geti(k)[0]) if k in ("nM", "ntrunk", "gsteps", "nlevel") else int(M[k])
             assert have == v, (task, k, have, v)
+
+
+@pytest.mark.parametrize("task", ["walk_on_ball", "walk_imitation", "flight_imitation", "template"])
+def test_shipped_assets_are_what_the_reference_mjcf_compiles_to(task):
+    """flybody_b200/assets/<task>.npz must be bit for bit what compile_fly.compile_task makes of the reference's
+    vnl_ray/fruitfly/assets/fruitfly.xml (fruitfly.py:115-326 + tasks/base.py surgery restated in compile_fly.py).  Skipped
+    where the reference is not mounted (the GPU box)."""
+    import os
+    import numpy as np
+    xml = "/root/reference/vnl_ray/fruitfly/assets/fruitfly.xml"
+    if not os.path.exists(xml):
+        pytest.skip("reference not mounted")
+    from flybody_b200.compile_fly import compile_task, load_model
+    from flybody_b200.model_pack import asset_path
+    fresh, shipped = compile_task(task, xml), load_model(asset_path(task))
+    assert set(fresh) == set(shipped)
+    for k in shipped:
+        a, b = shipped[k], fresh[k]
+        if isinstance(a, (list, tuple, str)):
+            assert list(a) == list(b), k
+        else:
+            assert np.array_equal(np.asarray(a), np.asarray(b)), k
