@@ -87,6 +87,55 @@ def quaternion_vectors(seed=1):
     print("quaternions: ok")
 
 
+def terrain_vectors():
+    """Terrains of the vision-flight arenas from the reference's OWN functions.  vnl_ray/tasks/arenas/hills.py imports
+    dm_control at module level, so its four module-level functions (pure numpy / scipy) are lifted out of the source file
+    with `ast` and executed as they stand; the arenas' `initialize_episode` bodies (hills.py:357-390, 439-452) are replayed
+    here call by call with the same RandomState."""
+    import ast
+    from scipy import ndimage
+    src = open("/root/reference/vnl_ray/tasks/arenas/hills.py").read()
+    tree = ast.parse(src)
+    want = ("pos_to_terrain_idx", "terrain_bowl", "add_sine_bumps", "add_sine_trench")
+    ns = {"np": np, "ndimage": ndimage}
+    for node in tree.body:
+        if isinstance(node, ast.FunctionDef) and node.name in want:
+            exec(compile(ast.Module([node], []), "hills.py", "exec"), ns)
+
+    class _Model:   # what terrain_bowl reads from physics.model (hills.py:160-166: dim 20, grid_density 10)
+        hfield_size = np.array([[20.0, 20.0, 1.0, 0.05]])
+        hfield_nrow = np.array([401])
+        hfield_ncol = np.array([401])
+
+    class _Physics:
+        model = _Model()
+    out = {}
+    for seed in (0, 1):
+        rs = np.random.RandomState(seed)      # SineBumps.initialize_episode
+        bowl = ns["terrain_bowl"](_Physics(), elevation_z=rs.uniform(4.0, 5.0), random_state=rs)
+        size = _Model.hfield_size[0, :2]
+        t = ns["add_sine_bumps"](bowl, size, wavelength=rs.uniform(10.0, 15.0), phase=rs.uniform(0.0, 2 * np.pi), height=rs.uniform(0.5, 1.0))
+        out[f"bumps{seed}_sub"] = t[::8, ::8].copy()
+        out[f"bumps{seed}_stats"] = np.array([t.min(), t.max(), t.mean(), (t ** 2).sum()])
+        rs = np.random.RandomState(seed)      # SineTrench.initialize_episode
+        bowl = ns["terrain_bowl"](_Physics(), elevation_z=rs.uniform(4.0, 5.0), random_state=rs)
+        start_x = rs.uniform(-5.0, -3.0)
+        end_x = start_x + rs.uniform(4.0, 10.0)
+        amplitude = rs.uniform(0.7 / 2, 1.2 / 2)
+        width = 2 * amplitude + 0.604 * rs.uniform(0.5, 1)
+        t, sine = ns["add_sine_trench"](bowl, size, start_x=start_x, end_x=end_x, phase=rs.uniform(0.0, 2 * np.pi),
+                                        wavelength=rs.uniform(5.0, 8.0), amplitude=amplitude, width=width,
+                                        height=rs.uniform(1.3, 1.3), sigma=rs.uniform(0.2, 0.2))
+        out[f"trench{seed}_sub"] = t[::8, ::8].copy()
+        out[f"trench{seed}_stats"] = np.array([t.min(), t.max(), t.mean(), (t ** 2).sum()])
+        out[f"trench{seed}_x"] = np.linspace(start_x, end_x, sine.shape[0])
+        out[f"trench{seed}_y"] = sine
+        out[f"trench{seed}_row"] = t[200].copy()       # the row through the arena's centre: walls and trench floor
+    out["idx"] = np.array([ns["pos_to_terrain_idx"](x, y, size, 401, 401) for x, y in ((-5.0, 0.0), (3.3, -1.2), (19.99, 7.0), (0.04, 0.06))])
+    np.savez_compressed(os.path.join(OUT, "terrain.npz"), **out)
+    print("terrain: ok")
+
+
 def wbpg_vectors(seed=2, n_steps=1500):
     """wbpg.npz - the reference WingBeatPatternGenerator (tasks/pattern_generators.py) run on the synthetic base
     pattern: table sizes and checksums, and a reset + n_steps trace (requested frequency, table step, frequency index,
@@ -124,4 +173,5 @@ if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
     walk_reward()
     quaternion_vectors()
+    terrain_vectors()
     wbpg_vectors()
