@@ -173,6 +173,7 @@ FLY_INL int hit_sphere_cylinder(Hit<T>* h, const T* c1, T r1, const T* c2, const
  * and the normal is rebuilt from the geom shapes at the contact point. */
 /* one geom of a convex pair: arithmetic in T, geometry stored as G (the engine's working precision) with element stride gs
  * (1: plain arrays; 32: the lane-interleaved warp scratch) */
+#define FLY_GEOM_PRISM 100   /* internal geom type: one prism of a height field */
 template <class T, class G> struct CcdObj {
   int type; const G *pos, *mat, *size; int gs; T margin;
   FLY_MEM T p(int k) const { return (T)pos[k * gs]; }
@@ -227,6 +228,13 @@ template <class T, class G> FLY_INL void ccd_support_geom(const CcdObj<T, G>& o,
     const T t = sqrt(ld[0] * ld[0] + ld[1] * ld[1]);
     if (t > minval<T>()) { const T sc = o.s(0) / t; r[0] = ld[0] * sc; r[1] = ld[1] * sc; }
     r[2] = sign0(ld[2]) * o.s(1);
+  } else if (o.type == FLY_GEOM_PRISM) {   /* height-field prism (fly_hfield.cuh): six vertices relative to pos in size[0..18) */
+    T best = T(-1e300);
+    for (int v = 0; v < 6; v++) {
+      const T q0 = o.s(3 * v), q1 = o.s(3 * v + 1), q2 = o.s(3 * v + 2);
+      const T d = q0 * ld[0] + q1 * ld[1] + q2 * ld[2];
+      if (d > best) { best = d; r[0] = q0; r[1] = q1; r[2] = q2; }
+    }
   }
   o.to_world(w, r);
   for (int k = 0; k < 3; k++) res[k] = w[k] + o.p(k) + dir[k] * o.margin;

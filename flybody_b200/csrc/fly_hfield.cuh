@@ -1,0 +1,77 @@
+/* fly_hfield.cuh - height field against a convex geom (terrain of the vision-guided flight tasks,
+ * vnl_ray/tasks/arenas/hills.py; MuJoCo mjc_ConvexHField restated, see oracle/flyb_oracle.c: flyo_narrow_hfield for the notes).
+ *
+ * One query = one geom, handled by ONE lane: the geom is expressed in the height field's frame, the cells under its bounds are
+ * walked as zig-zag strips, every three consecutive strip vertices top a prism (bottom at -base, top raised by the margin) that
+ * goes through the portal refinement of fly_col.cuh as object 1.  Arithmetic in float64, like every convex pair. */
+#ifndef FLY_HFIELD_CUH_
+#define FLY_HFIELD_CUH_
+#include "fly_col.cuh"
+
+struct FlyHfield {
+  const float* data;   /* [nrow, ncol] heights before scaling */
+  int nrow, ncol;
+  double pos[3], mat[9];   /* pose of the height-field geom */
+  double size[4];          /* x half extent, y half extent, elevation scale, base thickness */
+};
+
+/* contacts of geom (type, world pos / mat, size) with the field; out: dist, pos(3), normal(3) per contact; P: this lane's
+ * portal scratch.  Returns the number of contacts written (at most maxcon). */
+FLY_INL int fly_hfield_narrow(const FlyHfield& hf, int type, const double* c2, const double* m2, const double* s2, double margin,
+                              int maxcon, double* out, const Portal<double>& P) {
+  typedef double T;
+  T pos[3], mat[9];
+  {
+    const T d[3] = {c2[0] - hf.pos[0], c2[1] - hf.pos[1], c2[2] - hf.pos[2]};
+    matT_vec(pos, hf.mat, d);
+    for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) mat[3 * i + j] = hf.mat[i] * m2[j] + hf.mat[3 + i] * m2[3 + j] + hf.mat[6 + i] * m2[6 + j];
+  }
+  const CcdObj<T, T> geom = {type, pos, mat, s2, 1, T(0)};
+  T lo[3], hi[3];
+  for (int a = 0; a < 3; a++) {
+    T dir[3] = {0, 0, 0}, p[3];
+    dir[a] = 1; ccd_support_geom(geom, dir, p); hi[a] = p[a];
+    dir[a] = -1; ccd_support_geom(geom, dir, p); lo[a] = p[a];
+  }
+  const T sx = hf.size[0], sy = hf.size[1];
+  if (hi[0] < -sx || lo[0] > sx || hi[1] < -sy || lo[1] > sy || hi[2] < -hf.size[3]) return 0;
+  const T dx = 2 * sx / (hf.ncol - 1), dy = 2 * sy / (hf.nrow - 1);
+  int cmin = (int)floor((lo[0] + sx) / dx), cmax = (int)ceil((hi[0] + sx) / dx);
+  int rmin = (int)floor((lo[1] + sy) / dy), rmax = (int)ceil((hi[1] + sy) / dy);
+  if (cmin < 0) cmin = 0;
+  if (rmin < 0) rmin = 0;
+  if (cmax > hf.ncol - 1) cmax = hf.ncol - 1;
+  if (rmax > hf.nrow - 1) rmax = hf.nrow - 1;
+  const T ident[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
+  int ncon = 0;
+  for (int r = rmin; r < rmax; r++) {
+    T top[3][3] = {{0, 0, 0}, {0, 0, 0}, {0, 0, 0}};   /* the last three strip vertices (shifted before the first is set: start defined) */
+    int nvert = 0;
+    for (int c = cmin; c <= cmax; c++)
+      for (int i = 0; i < 2; i++) {
+        for (int k = 0; k < 3; k++) { top[0][k] = top[1][k]; top[1][k] = top[2][k]; }
+        top[2][0] = dx * c - sx; top[2][1] = dy * (r + i) - sy;
+        top[2][2] = (T)hf.data[(size_t)(r + i) * hf.ncol + c] * hf.size[2] + margin;
+        if (++nvert < 3) continue;
+        if (top[0][2] < lo[2] && top[1][2] < lo[2] && top[2][2] < lo[2]) continue;
+        T cen[3] = {0, 0, 0}, verts[18];
+        for (int v = 0; v < 3; v++) { cen[0] += top[v][0] / 3; cen[1] += top[v][1] / 3; cen[2] += T(0.5) * (top[v][2] - hf.size[3]) / 3; }
+        for (int v = 0; v < 3; v++) {
+          for (int k = 0; k < 2; k++) { verts[3 * v + k] = top[v][k] - cen[k]; verts[9 + 3 * v + k] = top[v][k] - cen[k]; }
+          verts[3 * v + 2] = top[v][2] - cen[2]; verts[9 + 3 * v + 2] = -hf.size[3] - cen[2];
+        }
+        const CcdObj<T, T> prism = {FLY_GEOM_PRISM, cen, ident, verts, 1, T(0)};
+        T depth, dir[3], cp[3];
+        if (!mpr_penetration(prism, geom, P, &depth, dir, cp)) continue;
+        if ((dir[0] == 0 && dir[1] == 0 && dir[2] == 0) || ncon >= maxcon) continue;
+        const T lp[3] = {cp[0] - T(0.5) * margin * dir[0], cp[1] - T(0.5) * margin * dir[1], cp[2] - T(0.5) * margin * dir[2]};
+        T wp[3], wn[3];
+        mat_vec(wp, hf.mat, lp); mat_vec(wn, hf.mat, dir);
+        out[7 * ncon] = margin - depth;
+        for (int k = 0; k < 3; k++) { out[7 * ncon + 1 + k] = wp[k] + hf.pos[k]; out[7 * ncon + 4 + k] = wn[k]; }
+        ncon++;
+      }
+  }
+  return ncon;
+}
+#endif

@@ -14,6 +14,8 @@
 #include <vector>
 #include "../../include/flyb.h"
 #include "fly_kernel.cuh"
+#include "fly_hfield.cuh"
+#include "fly_eyes.cuh"
 
 struct FlybEngine {
   int device = 0, num_envs = 0, flags = 0, env_offset = 0;
@@ -101,6 +103,31 @@ __global__ void __launch_bounds__(1024) fly_bin_kernel(const int* __restrict__ w
     const unsigned long long k = (unsigned long long)(work[i] > 0 ? work[i] : 0) * 256ull / mean;
     perm[atomicAdd(&start[FLY_NBINS - 1 - (int)(k < FLY_NBINS ? k : FLY_NBINS - 1)], 1)] = i;
   }
+}
+
+/* ---- height field against convex geoms, one query per thread (flyb_hfield_contacts: first slice of the vision-guided flight
+ * terrain).  The portal scratch of the convex search is lane-interleaved per warp in shared memory. */
+__global__ void __launch_bounds__(128) fly_hfield_kernel(FlyHfield hf, int nq, const int* __restrict__ types,
+                                                          const double* __restrict__ geoms, int maxcon, double* __restrict__ out) {
+  __shared__ double scratch[4][4 * 6 * 32];
+  const int q = blockIdx.x * blockDim.x + threadIdx.x;
+  const Portal<double> P = {scratch[threadIdx.x >> 5] + (threadIdx.x & 31)};
+  if (q >= nq) return;
+  const double* g = geoms + 16 * (size_t)q;
+  double* o = out + (size_t)q * (1 + 7 * maxcon);
+  o[0] = (double)fly_hfield_narrow(hf, types[q], g, g + 3, g + 12, g[15], maxcon, o + 1, P);
+}
+
+/* ---- eye cameras: one thread per pixel (flyb_render_eyes, csrc/fly_eyes.cuh) */
+__global__ void __launch_bounds__(256) fly_eyes_kernel(FlyScene sc, int ncam, const int* __restrict__ terrain_id,
+                                                        const float* __restrict__ cams, int W, int H, float tanhalf,
+                                                        unsigned char* __restrict__ out) {
+  const size_t p = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= (size_t)ncam * W * H) return;
+  const int cam = (int)(p / ((size_t)W * H)), i = (int)((p / W) % H), j = (int)(p % W);
+  const float* c = cams + 12 * (size_t)cam;
+  const float* h = sc.data + (size_t)terrain_id[cam] * sc.nrow * sc.ncol;
+  eye_pixel<float>(sc, h, c, c + 3, W, H, tanhalf, i, j, out + 3 * p);
 }
 
 /* ---- FP32 FMA peak of the device, measured (flyb_fma_peak): every thread runs 16 independent FMA chains; 8 blocks of 256
@@ -435,6 +462,74 @@ int flyb_step(flyb_handle h, const float* action, float* obs, float* reward, flo
               void* stream) {
   FlyIO<float> io = make_io(h, action, obs, reward, discount, step_type);
   return launch(h, io, (cudaStream_t)stream);
+}
+
+int flyb_hfield_contacts(int device, const float* data, int nrow, int ncol, const double* pose12, const double* size4, int nquery,
+                         const int32_t* types, const double* geoms16, int maxcon, double* out) {
+  auto fail = [&](const std::string& msg) { g_create_error = msg; return 1; };
+  if (nrow < 2 || ncol < 2 || nquery <= 0 || maxcon <= 0) return fail("flyb_hfield_contacts: bad sizes");
+  if (cudaSetDevice(device) != cudaSuccess) return fail("flyb_hfield_contacts: no CUDA device (there is no CPU fallback)");
+  FlyHfield hf;
+  float* d_data = nullptr; int* d_types = nullptr; double *d_geoms = nullptr, *d_out = nullptr;
+  const size_t nd = (size_t)nrow * ncol, no = (size_t)nquery * (1 + 7 * maxcon);
+  cudaError_t e = cudaSuccess;
+#define CKH(call) if (e == cudaSuccess) e = (call)
+  CKH(cudaMalloc(&d_data, nd * sizeof(float)));
+  CKH(cudaMalloc(&d_types, nquery * sizeof(int)));
+  CKH(cudaMalloc(&d_geoms, (size_t)nquery * 16 * sizeof(double)));
+  CKH(cudaMalloc(&d_out, no * sizeof(double)));
+  CKH(cudaMemcpy(d_data, data, nd * sizeof(float), cudaMemcpyHostToDevice));
+  CKH(cudaMemcpy(d_types, types, nquery * sizeof(int), cudaMemcpyHostToDevice));
+  CKH(cudaMemcpy(d_geoms, geoms16, (size_t)nquery * 16 * sizeof(double), cudaMemcpyHostToDevice));
+  CKH(cudaMemset(d_out, 0, no * sizeof(double)));
+  if (e == cudaSuccess) {
+    hf.data = d_data; hf.nrow = nrow; hf.ncol = ncol;
+    for (int k = 0; k < 3; k++) hf.pos[k] = pose12[k];
+    for (int k = 0; k < 9; k++) hf.mat[k] = pose12[3 + k];
+    for (int k = 0; k < 4; k++) hf.size[k] = size4[k];
+    fly_hfield_kernel<<<(nquery + 127) / 128, 128>>>(hf, nquery, d_types, d_geoms, maxcon, d_out);
+    e = cudaGetLastError();
+  }
+  CKH(cudaMemcpy(out, d_out, no * sizeof(double), cudaMemcpyDeviceToHost));
+#undef CKH
+  cudaFree(d_data); cudaFree(d_types); cudaFree(d_geoms); cudaFree(d_out);
+  if (e != cudaSuccess) return fail(std::string("flyb_hfield_contacts: ") + cudaGetErrorString(e));
+  return 0;
+}
+
+int flyb_render_eyes(int device, const float* data, int nterrain, int nrow, int ncol, float half_extent, float z_offset, int ncam,
+                     const int32_t* terrain_id, const float* cams12, int width, int height, float fovy_deg, const float* colors8,
+                     uint8_t* out) {
+  auto fail = [&](const std::string& msg) { g_create_error = msg; return 1; };
+  if (nterrain <= 0 || nrow < 2 || ncol < 2 || ncam <= 0 || width <= 0 || height <= 0) return fail("flyb_render_eyes: bad sizes");
+  for (int i = 0; i < ncam; i++) if (terrain_id[i] < 0 || terrain_id[i] >= nterrain) return fail("flyb_render_eyes: terrain id out of range");
+  if (cudaSetDevice(device) != cudaSuccess) return fail("flyb_render_eyes: no CUDA device (there is no CPU fallback)");
+  float *d_data = nullptr, *d_cams = nullptr; int* d_tid = nullptr; unsigned char* d_out = nullptr;
+  const size_t nd = (size_t)nterrain * nrow * ncol, no = (size_t)ncam * width * height * 3;
+  cudaError_t e = cudaSuccess;
+#define CKH(call) if (e == cudaSuccess) e = (call)
+  CKH(cudaMalloc(&d_data, nd * sizeof(float)));
+  CKH(cudaMalloc(&d_cams, (size_t)ncam * 12 * sizeof(float)));
+  CKH(cudaMalloc(&d_tid, ncam * sizeof(int)));
+  CKH(cudaMalloc(&d_out, no));
+  CKH(cudaMemcpy(d_data, data, nd * sizeof(float), cudaMemcpyHostToDevice));
+  CKH(cudaMemcpy(d_cams, cams12, (size_t)ncam * 12 * sizeof(float), cudaMemcpyHostToDevice));
+  CKH(cudaMemcpy(d_tid, terrain_id, ncam * sizeof(int), cudaMemcpyHostToDevice));
+  if (e == cudaSuccess) {
+    FlyScene sc;
+    sc.data = d_data; sc.nrow = nrow; sc.ncol = ncol; sc.half = half_extent; sc.zoff = z_offset;
+    for (int k = 0; k < 3; k++) { sc.rgb[k] = colors8[k]; sc.sky[k] = colors8[3 + k]; }
+    sc.ambient = colors8[6]; sc.diffuse = colors8[7];
+    const size_t npix = (size_t)ncam * width * height;
+    fly_eyes_kernel<<<(unsigned)((npix + 255) / 256), 256>>>(sc, ncam, d_tid, d_cams, width, height,
+                                                            tanf(0.5f * fovy_deg * 3.14159265358979f / 180.0f), d_out);
+    e = cudaGetLastError();
+  }
+  CKH(cudaMemcpy(out, d_out, no, cudaMemcpyDeviceToHost));
+#undef CKH
+  cudaFree(d_data); cudaFree(d_cams); cudaFree(d_tid); cudaFree(d_out);
+  if (e != cudaSuccess) return fail(std::string("flyb_render_eyes: ") + cudaGetErrorString(e));
+  return 0;
 }
 
 int flyb_fma_peak(int device, double* tflops) {

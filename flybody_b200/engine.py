@@ -27,7 +27,7 @@ FLAG_LANES16 = 1 << 17
 EXPORTS = ["flyb_create", "flyb_destroy", "flyb_last_error", "flyb_info", "flyb_configure", "flyb_load_clips",
            "flyb_set_clip_ids", "flyb_reset", "flyb_step", "flyb_reset_host", "flyb_step_host", "flyb_get_state",
            "flyb_set_state", "flyb_get_trace", "flyb_episode_stats", "flyb_load_wbpg", "flyb_set_wbpg_phase",
-           "flyb_use_generic_kernel", "flyb_step_noalloc", "flyb_fma_peak"]
+           "flyb_use_generic_kernel", "flyb_step_noalloc", "flyb_fma_peak", "flyb_hfield_contacts", "flyb_render_eyes"]
 
 
 N_SPEC_MODELS = 4   # csrc/fly_dims_gen.h: FLY_SPEC_COUNT
@@ -52,7 +52,10 @@ def compile_library(out_path: str, extra_flags=(), verbose: bool = False, units=
     import tempfile
     from concurrent.futures import ThreadPoolExecutor
     flags = [f for f in NVCC_FLAGS if f != "-shared"] + list(extra_flags) + (["-Xptxas", "-v"] if verbose else [])
-    tus = [("flyb_cuda", "flyb_cuda.cu", [])]
+    # flyb_cuda.cu also holds the height-field and eye-camera kernels.  The portal refinement against a prism takes support points
+    # among the vertices of a face whenever its direction is that face's normal: ties decided by the last bit.  Without
+    # multiply-add contraction the float64 device code rounds like the CPU code and picks the same vertex.
+    tus = [("flyb_cuda", "flyb_cuda.cu", ["-fmad=false"])]
     for nl, w, l, sp in (units if units is not None else kernel_units()):
         tus.append((f"k_{nl}_{w}_{l}_{'g' if sp < 0 else 's%d' % sp}", "flyb_kern.cu",
                     [f"-DFLY_NL={nl}", f"-DFLY_TU_WARPS={w}", f"-DFLY_TU_LEVEL={l}", f"-DFLY_TU_SPEC={sp}"]))
@@ -73,6 +76,7 @@ def compile_library(out_path: str, extra_flags=(), verbose: bool = False, units=
 def build_library(force: bool = False, verbose: bool = False) -> str:
     """Builds flybody_b200/libflyb.so (in-tree) when a source is newer than it."""
     srcs = [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC))] + [os.path.join(_DIR, "..", "include", f) for f in ("flyb.h", "flyb_model.h")]
+    srcs.append(os.path.abspath(__file__))   # the build list and the compiler flags live here
     newest = max(os.path.getmtime(s) for s in srcs)
     if not force and os.path.exists(LIB_PATH) and os.path.getmtime(LIB_PATH) >= newest:
         return LIB_PATH
@@ -107,6 +111,8 @@ def lib():
         L.flyb_step.argtypes = [vp, vp, vp, vp, vp, vp, vp]
         L.flyb_step_noalloc.argtypes = [vp, vp, vp, vp, vp, vp, vp]
         L.flyb_fma_peak.argtypes = [c_i, dp]
+        L.flyb_hfield_contacts.argtypes = [c_i, fp, c_i, c_i, dp, dp, c_i, ip, dp, c_i, dp]
+        L.flyb_render_eyes.argtypes = [c_i, fp, c_i, c_i, c_i, ctypes.c_float, ctypes.c_float, c_i, ip, fp, c_i, c_i, ctypes.c_float, fp, u8p]
         L.flyb_reset_host.argtypes = [vp, u8p, fp, ip]
         L.flyb_step_host.argtypes = [vp, fp, fp, fp, fp, ip]
         L.flyb_get_state.argtypes = [vp, fp, fp, fp, fp, ip]
@@ -133,6 +139,54 @@ def fma_peak_tflops(device: int = 0) -> float:
     if lib().flyb_fma_peak(int(device), ctypes.byref(out)):
         raise RuntimeError("flyb_fma_peak failed")
     return out.value
+
+
+def hfield_contacts(data, pose12, size4, types, geoms16, maxcon: int = 16, device: int = 0):
+    """flyb_hfield_contacts: height field `data` [nrow, ncol] against the query geoms on the GPU; returns, per query, a list of
+    (dist, pos[3], normal[3])."""
+    dp = ctypes.POINTER(ctypes.c_double)
+    d = np.ascontiguousarray(data, np.float32)
+    pose, size = np.ascontiguousarray(pose12, np.float64).reshape(12), np.ascontiguousarray(size4, np.float64).reshape(4)
+    t = np.ascontiguousarray(types, np.int32)
+    g = np.ascontiguousarray(geoms16, np.float64).reshape(len(t), 16)
+    out = np.zeros((len(t), 1 + 7 * maxcon))
+    if lib().flyb_hfield_contacts(int(device), _fp(d), d.shape[0], d.shape[1], pose.ctypes.data_as(dp), size.ctypes.data_as(dp), len(t),
+                                  _ip(t), g.ctypes.data_as(dp), int(maxcon), out.ctypes.data_as(dp)):
+        raise RuntimeError(lib().flyb_last_error(None).decode())
+    return [[(o[1 + 7 * i], o[2 + 7 * i:5 + 7 * i].copy(), o[5 + 7 * i:8 + 7 * i].copy()) for i in range(int(o[0]))] for o in out]
+
+
+# eye cameras of the fly in the frame of its head body (vnl_ray/fruitfly/assets/fruitfly.xml:335-336)
+EYE_POS = {"right": (0.0219, 0.0131, 0.0), "left": (-0.0219, 0.0131, 0.0)}
+EYE_QUAT = {"right": (0.474, 0.688, -0.344, -0.429), "left": (0.474, 0.688, 0.344, 0.429)}
+TERRAIN_RGB, HEADLIGHT = (0.2, 0.3, 0.4), (0.4, 0.8)   # hills.py:207,223-225 (aesthetic "default": flat colour)
+
+
+def eye_cameras(head_pos, head_mat):
+    """World poses [2, 12] (right eye, left eye: position, row-major orientation) from the head body's pose."""
+    def q2m(q):
+        w, x, y, z = np.asarray(q, np.float64) / np.linalg.norm(q)
+        return np.array([[w*w+x*x-y*y-z*z, 2*(x*y-w*z), 2*(x*z+w*y)], [2*(x*y+w*z), w*w-x*x+y*y-z*z, 2*(y*z-w*x)],
+                         [2*(x*z-w*y), 2*(y*z+w*x), w*w-x*x-y*y+z*z]])
+    hp, hm = np.asarray(head_pos, np.float64), np.asarray(head_mat, np.float64).reshape(3, 3)
+    return np.stack([np.r_[hp + hm @ np.asarray(EYE_POS[k]), (hm @ q2m(EYE_QUAT[k])).ravel()] for k in ("right", "left")])
+
+
+def render_eyes(heights, terrain_id, cams12, half_extent=20.0, z_offset=-0.01, size=32, fovy=150.0, rgb=TERRAIN_RGB,
+                sky=(0.0, 0.0, 0.0), headlight=HEADLIGHT, device: int = 0):
+    """flyb_render_eyes: uint8 images [ncam, size, size, 3] of the terrains `heights` [nterrain, n, n] seen from `cams12`."""
+    h = np.ascontiguousarray(heights, np.float32)
+    if h.ndim == 2:
+        h = h[None]
+    cams = np.ascontiguousarray(cams12, np.float32).reshape(-1, 12)
+    tid = np.ascontiguousarray(terrain_id, np.int32).reshape(-1)
+    colors = np.ascontiguousarray(list(rgb) + list(sky) + list(headlight), np.float32)
+    out = np.zeros((len(cams), size, size, 3), np.uint8)
+    if lib().flyb_render_eyes(int(device), _fp(h), h.shape[0], h.shape[1], h.shape[2], float(half_extent), float(z_offset), len(cams),
+                              _ip(tid), _fp(cams), size, size, float(fovy), _fp(colors),
+                              out.ctypes.data_as(ctypes.POINTER(ctypes.c_uint8))):
+        raise RuntimeError(lib().flyb_last_error(None).decode())
+    return out
 
 
 class Engine:

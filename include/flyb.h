@@ -132,6 +132,25 @@ int flyb_get_trace(flyb_handle h, int32_t* ints, float* reals);
  * must be 0 for the physics to be the reference's); [5] reset passes; [6] control steps; [7] unused. */
 int flyb_episode_stats(flyb_handle h, double* out8);
 
+/* Height field against convex geoms (host pointers; first slice of the terrain of vision_guided_flight, vnl_ray/fly_envs.py:160-206,
+ * tasks/arenas/hills.py:160-166, 186-221: the `terrain` hfield geom that MuJoCo collides with the fly through mjc_ConvexHField).
+ * data [nrow, ncol] float32 heights (x elevation scale), pose12 = position (3) and row-major orientation (9) of the hfield geom,
+ * size4 = x half extent, y half extent, elevation scale, base thickness.  Query q: types[q] (FLYB_GEOM_SPHERE / CAPSULE /
+ * ELLIPSOID / CYLINDER), geoms16[q] = world position (3), orientation (9), size (3), margin.  out [nquery, 1 + 7 maxcon]:
+ * number of contacts, then dist, position (3), normal (3, field -> geom) of each.  Error text: flyb_last_error(NULL). */
+int flyb_hfield_contacts(int device, const float* data, int nrow, int ncol, const double* pose12, const double* size4, int nquery,
+                         const int32_t* types, const double* geoms16, int maxcon, double* out);
+
+/* The fly's eye cameras as a ray caster over the terrain (host pointers; first slice of the `right_eye` / `left_eye` observables,
+ * vnl_ray/fruitfly/fruitfly.py:676-708 with tasks/vision_flight.py:25-26: 32 x 32 pixels, fovy 150; the reference renders them
+ * through MuJoCo's OpenGL renderer).  data [nterrain, nrow, ncol] heights over [-half_extent, half_extent]^2, the hfield geom
+ * z_offset (-0.01) below the ground plane; camera i looks at terrain terrain_id[i] from cams12[i] = position (3) and row-major
+ * orientation (9; columns = the camera's x (right), y (up), z (backward) axes in the world).  colors8 = terrain rgb, background
+ * rgb, headlight ambient and diffuse.  out [ncam, height, width, 3] uint8.  What is and is not rendered: csrc/fly_eyes.cuh. */
+int flyb_render_eyes(int device, const float* data, int nterrain, int nrow, int ncol, float half_extent, float z_offset, int ncam,
+                     const int32_t* terrain_id, const float* cams12, int width, int height, float fovy_deg, const float* colors8,
+                     uint8_t* out);
+
 /* Measurement utility (no reference counterpart): FP32 fused-multiply-add throughput of the device in TFLOP/s, measured with
  * a register-resident FMA micro-benchmark - the denominator of the FP32-pipe fractions bench.py reports. */
 int flyb_fma_peak(int device, double* tflops);

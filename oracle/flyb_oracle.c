@@ -481,6 +481,7 @@ static int hit_sphere_cylinder(Hit* h, const double* c1, double r1, const double
 #define MPR_PORTAL_CAP 100  /* guard on libccd's open-ended portal loops (never reached in exact arithmetic) */
 typedef struct { double v[3], v1[3], v2[3]; } Supp;
 typedef struct { int type; const double *pos, *mat, *size; double margin; } CcdObj;
+#define GEOM_PRISM 100   /* internal: one prism of a height field (size -> 6 vertices relative to pos) */
 
 static int ccd_is_zero(double x) { return fabs(x) < CCD_EPS; }
 static int ccd_eq(double a, double b) {
@@ -510,6 +511,15 @@ static void ccd_support_geom(const CcdObj* o, const double* dir, double* res) {
       double t = sqrt(ld[0] * ld[0] + ld[1] * ld[1]);
       if (t > MINVAL) { double sc = o->size[0] / t; r[0] = ld[0] * sc; r[1] = ld[1] * sc; }
       r[2] = sign0(ld[2]) * o->size[1];
+      break;
+    }
+    case GEOM_PRISM: {   /* six vertices in size[0..18), given relative to pos: the farthest one */
+      double best = -1e300;
+      for (int v = 0; v < 6; v++) {
+        const double* q = o->size + 3 * v;
+        const double d = q[0] * ld[0] + q[1] * ld[1] + q[2] * ld[2];
+        if (d > best) { best = d; r[0] = q[0]; r[1] = q[1]; r[2] = q[2]; }
+      }
       break;
     }
     default: break;
@@ -745,6 +755,68 @@ int flyo_narrow_pair(int t1, const double* c1, const double* m1, const double* s
     for (int k = 0; k < 3; k++) { out[7 * i + 1 + k] = h[i].pos[k]; out[7 * i + 4 + k] = h[i].n[k]; }
   }
   return n;
+}
+
+/* ---- height field against a convex geom (MuJoCo mjc_ConvexHField, engine_collision_convex.c; third party, restated from the
+ * published description and memory of its structure - "parity unpinned" like the rest of the convex code).
+ * The geom is expressed in the height field's frame; the grid cells under its axis-aligned bounds (taken with its support
+ * function) are walked row by row as a zig-zag strip of vertices (column c of row r, column c of row r + 1, column c + 1 of row
+ * r, ...): every three consecutive strip vertices are the top triangle of a prism whose bottom lies at -base, its top raised by
+ * the margin.  Prisms whose top stays below the geom's lowest point are skipped; the others go through the same portal
+ * refinement as every convex pair (prism as object 1, its centroid as centre).  A penetration of depth d gives a contact with
+ * dist = margin - d, normal = the refinement's direction (prism -> geom), position = its contact point lowered by margin / 2.
+ * hsize: x half extent, y half extent, elevation scale, base thickness; data[r * ncol + c] x hsize[2] is the height at
+ * x = -hsize[0] + c dx, y = -hsize[1] + r dy.  Returns the number of contacts written (at most maxcon): dist, pos(3), normal(3). */
+int flyo_narrow_hfield(const double* hpos, const double* hmat, const double* hsize, int nrow, int ncol, const float* data,
+                       int t2, const double* c2, const double* m2, const double* s2, double margin, int maxcon, double* out) {
+  double pos[3], mat[9], d[3] = {c2[0] - hpos[0], c2[1] - hpos[1], c2[2] - hpos[2]};
+  matT_vec(pos, hmat, d);
+  for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) mat[3 * i + j] = hmat[i] * m2[j] + hmat[3 + i] * m2[3 + j] + hmat[6 + i] * m2[6 + j];
+  const CcdObj geom = {t2, pos, mat, s2, 0.0};
+  /* bounds of the geom in the height field's frame */
+  double lo[3], hi[3];
+  for (int a = 0; a < 3; a++) {
+    double dir[3] = {0, 0, 0}, p[3];
+    dir[a] = 1; ccd_support_geom(&geom, dir, p); hi[a] = p[a];
+    dir[a] = -1; ccd_support_geom(&geom, dir, p); lo[a] = p[a];
+  }
+  const double sx = hsize[0], sy = hsize[1];
+  if (hi[0] < -sx || lo[0] > sx || hi[1] < -sy || lo[1] > sy || hi[2] < -hsize[3]) return 0;
+  const double dx = 2 * sx / (ncol - 1), dy = 2 * sy / (nrow - 1);
+  int cmin = (int)floor((lo[0] + sx) / dx), cmax = (int)ceil((hi[0] + sx) / dx);
+  int rmin = (int)floor((lo[1] + sy) / dy), rmax = (int)ceil((hi[1] + sy) / dy);
+  if (cmin < 0) cmin = 0; if (rmin < 0) rmin = 0;
+  if (cmax > ncol - 1) cmax = ncol - 1; if (rmax > nrow - 1) rmax = nrow - 1;
+  static const double ident[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
+  int ncon = 0;
+  for (int r = rmin; r < rmax; r++) {
+    double top[3][3] = {{0, 0, 0}, {0, 0, 0}, {0, 0, 0}};   /* sliding window over the strip */
+    int nvert = 0;
+    for (int c = cmin; c <= cmax; c++)
+      for (int i = 0; i < 2; i++) {
+        memcpy(top[0], top[1], 24); memcpy(top[1], top[2], 24);
+        top[2][0] = dx * c - sx; top[2][1] = dy * (r + i) - sy;
+        top[2][2] = (double)data[(size_t)(r + i) * ncol + c] * hsize[2] + margin;
+        if (++nvert < 3) continue;
+        if (top[0][2] < lo[2] && top[1][2] < lo[2] && top[2][2] < lo[2]) continue;
+        double cen[3] = {0, 0, 0}, verts[18];
+        for (int v = 0; v < 3; v++) { cen[0] += top[v][0] / 3; cen[1] += top[v][1] / 3; cen[2] += 0.5 * (top[v][2] - hsize[3]) / 3; }
+        for (int v = 0; v < 3; v++) {
+          for (int k = 0; k < 2; k++) { verts[3 * v + k] = top[v][k] - cen[k]; verts[9 + 3 * v + k] = top[v][k] - cen[k]; }
+          verts[3 * v + 2] = top[v][2] - cen[2]; verts[9 + 3 * v + 2] = -hsize[3] - cen[2];
+        }
+        const CcdObj prism = {GEOM_PRISM, cen, ident, verts, 0.0};
+        double depth, dir[3], cp[3];
+        if (mpr_penetration(&prism, &geom, &depth, dir, cp) != 0) continue;
+        if ((dir[0] == 0 && dir[1] == 0 && dir[2] == 0) || ncon >= maxcon) continue;
+        double lp[3] = {cp[0] - 0.5 * margin * dir[0], cp[1] - 0.5 * margin * dir[1], cp[2] - 0.5 * margin * dir[2]}, wp[3], wn[3];
+        mat_vec(wp, hmat, lp); mat_vec(wn, hmat, dir);
+        out[7 * ncon] = margin - depth;
+        for (int k = 0; k < 3; k++) { out[7 * ncon + 1 + k] = wp[k] + hpos[k]; out[7 * ncon + 4 + k] = wn[k]; }
+        ncon++;
+      }
+  }
+  return ncon;
 }
 
 static void collision(FlyoEnv* e) {

@@ -62,6 +62,8 @@ double* flyo_dptr(FlyoEnv* e, const char* name, int* count);
 int* flyo_iptr(FlyoEnv* e, const char* name, int* count);
 const FlyoContact* flyo_contacts(FlyoEnv* e, int* ncon);
 /* narrow phase of one primitive pair (unit tests): out[7*i] = dist, pos(3), normal(3) of hit i; returns the hit count */
+int flyo_narrow_hfield(const double* hpos, const double* hmat, const double* hsize, int nrow, int ncol, const float* data,
+                       int t2, const double* c2, const double* m2, const double* s2, double margin, int maxcon, double* out);
 int flyo_quat_op(int op, const double* a, const double* b, double* out);   /* test hook: task-layer quaternion helpers */
 int flyo_narrow_pair(int t1, const double* c1, const double* m1, const double* s1, int t2, const double* c2,
                      const double* m2, const double* s2, double margin, int force_convex, double* out);

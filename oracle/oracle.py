@@ -69,6 +69,9 @@ def lib():
         L.flyo_env_step.restype = ctypes.c_int
         L.flyo_narrow_pair.argtypes = [ctypes.c_int, dp, dp, dp, ctypes.c_int, dp, dp, dp, ctypes.c_double, ctypes.c_int, dp]
         L.flyo_narrow_pair.restype = ctypes.c_int
+        L.flyo_narrow_hfield.argtypes = [dp, dp, dp, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_float), ctypes.c_int, dp, dp, dp,
+                                         ctypes.c_double, ctypes.c_int, dp]
+        L.flyo_narrow_hfield.restype = ctypes.c_int
         L.flyo_quat_op.argtypes = [ctypes.c_int, dp, dp, dp]
         L.flyo_quat_op.restype = ctypes.c_int
         _lib = L
@@ -196,3 +199,16 @@ def quat_op(op: int, a, b=None):
     out = np.zeros(4)
     n = lib().flyo_quat_op(int(op), a.ctypes.data_as(dp), b.ctypes.data_as(dp), out.ctypes.data_as(dp))
     return out[:n].copy()
+
+
+def narrow_hfield(hpos, hmat, hsize, data, t2, pos2, mat2, size2, margin=0.0, maxcon=16):
+    """Height field (geom pose hpos / hmat, hsize = [x half extent, y half extent, elevation scale, base], data [nrow, ncol]
+    float32) against one convex geom in the oracle: list of (dist, pos[3], normal[3])."""
+    dp = ctypes.POINTER(ctypes.c_double)
+    a = [np.ascontiguousarray(x, np.float64).reshape(-1) for x in (hpos, hmat, hsize, pos2, mat2, size2)]
+    d = np.ascontiguousarray(data, np.float32)
+    out = np.zeros(7 * maxcon)
+    n = lib().flyo_narrow_hfield(a[0].ctypes.data_as(dp), a[1].ctypes.data_as(dp), a[2].ctypes.data_as(dp), d.shape[0], d.shape[1],
+                                 d.ctypes.data_as(ctypes.POINTER(ctypes.c_float)), int(t2), a[3].ctypes.data_as(dp),
+                                 a[4].ctypes.data_as(dp), a[5].ctypes.data_as(dp), float(margin), int(maxcon), out.ctypes.data_as(dp))
+    return [(out[7 * i], out[7 * i + 1:7 * i + 4].copy(), out[7 * i + 4:7 * i + 7].copy()) for i in range(n)]

@@ -45,6 +45,7 @@ def lib():
         L.emu_set.argtypes = [ctypes.c_void_p, ctypes.c_char_p, dp, ctypes.c_int]
         L.emu_geti.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ip, ctypes.c_int]
         L.emu_quat_op.argtypes = [ctypes.c_int, ctypes.c_int, dp, dp, dp]
+        L.emu_hfield_contacts.argtypes = [fp, ctypes.c_int, ctypes.c_int, dp, dp, ctypes.c_int, ip, dp, ctypes.c_int, dp]
         _lib = L
     return _lib
 
@@ -149,3 +150,18 @@ def quat_op(op: int, a, b=None, double: bool = False):
     out = np.zeros(4)
     n = lib().emu_quat_op(int(double), int(op), aa.ctypes.data_as(dp), bb.ctypes.data_as(dp), out.ctypes.data_as(dp))
     return out[:n].copy()
+
+
+def hfield_contacts(data, pose12, size4, types, geoms16, maxcon: int = 16):
+    """The engine's height-field narrow phase (csrc/fly_hfield.cuh) compiled for the CPU; arguments and result as
+    flybody_b200.engine.hfield_contacts."""
+    dp = ctypes.POINTER(ctypes.c_double)
+    d = np.ascontiguousarray(data, np.float32)
+    pose, size = np.ascontiguousarray(pose12, np.float64).reshape(12), np.ascontiguousarray(size4, np.float64).reshape(4)
+    t = np.ascontiguousarray(types, np.int32)
+    g = np.ascontiguousarray(geoms16, np.float64).reshape(len(t), 16)
+    out = np.zeros((len(t), 1 + 7 * maxcon))
+    lib().emu_hfield_contacts(d.ctypes.data_as(ctypes.POINTER(ctypes.c_float)), d.shape[0], d.shape[1], pose.ctypes.data_as(dp),
+                              size.ctypes.data_as(dp), len(t), t.ctypes.data_as(ctypes.POINTER(ctypes.c_int)), g.ctypes.data_as(dp),
+                              int(maxcon), out.ctypes.data_as(dp))
+    return [[(o[1 + 7 * i], o[2 + 7 * i:5 + 7 * i].copy(), o[5 + 7 * i:8 + 7 * i].copy()) for i in range(int(o[0]))] for o in out]

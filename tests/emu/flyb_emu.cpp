@@ -10,6 +10,7 @@
 #include <string>
 #include <vector>
 #include "../../flybody_b200/csrc/fly_env.cuh"
+#include "../../flybody_b200/csrc/fly_hfield.cuh"
 
 struct EmuBase {
   virtual ~EmuBase() {}
@@ -191,6 +192,23 @@ void* emu_create(const FlybModel* m, int flags, int use_double, char* errbuf, in
   return e;
 }
 void emu_destroy(void* h) { delete (EmuBase*)h; }
+/* the engine's height-field narrow phase (csrc/fly_hfield.cuh) on the CPU: same arguments as flyb_hfield_contacts */
+int emu_hfield_contacts(const float* data, int nrow, int ncol, const double* pose12, const double* size4, int nquery,
+                        const int* types, const double* geoms16, int maxcon, double* out) {
+  FlyHfield hf;
+  hf.data = data; hf.nrow = nrow; hf.ncol = ncol;
+  for (int k = 0; k < 3; k++) hf.pos[k] = pose12[k];
+  for (int k = 0; k < 9; k++) hf.mat[k] = pose12[3 + k];
+  for (int k = 0; k < 4; k++) hf.size[k] = size4[k];
+  std::vector<double> scratch(4 * 6 * 32);
+  const Portal<double> P = {scratch.data()};
+  for (int q = 0; q < nquery; q++) {
+    const double* g = geoms16 + 16 * (size_t)q;
+    double* o = out + (size_t)q * (1 + 7 * maxcon);
+    o[0] = (double)fly_hfield_narrow(hf, types[q], g, g + 3, g + 12, g[15], maxcon, o + 1, P);
+  }
+  return 0;
+}
 int emu_quat_op(int use_double, int op, const double* a, const double* b, double* out) {
   return use_double ? quat_op_t<double>(op, a, b, out) : quat_op_t<float>(op, a, b, out);
 }
