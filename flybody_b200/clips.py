@@ -281,3 +281,119 @@ def synth_flight_clip(T: int = 3006, seed: int = 0, dt: float = 2e-4):
 def synthetic_flight_table(M: dict, n_clips: int = 64, T: int = 3006, seed: int = 0):
     """Packed synthetic flight clip table -> (rows float32 [n T, 13], offsets, lengths)."""
     return pack_clips(M, [synth_flight_clip(T=T, seed=seed * 100003 + c) for c in range(n_clips)])
+
+
+# ---------------------------------------------------------------------------- the reference's HDF5 datasets
+def _open_hdf5(path):
+    """h5py where it exists; otherwise the pure-python reader of `hdf5_lite` (same mapping interface)."""
+    try:
+        import h5py
+        return h5py.File(path, "r")
+    except ImportError:
+        from . import hdf5_lite
+        return hdf5_lite.File(path)
+
+
+def _traj_keys(f):
+    return sorted(f["trajectories"].keys(), key=lambda k: int(k))
+
+
+def _decode(names):
+    return [n.decode("utf-8") if isinstance(n, (bytes, np.bytes_)) else str(n) for n in np.asarray(names).tolist()]
+
+
+def hdf5_walking_clips(f, M: dict, max_clips=None, traj_indices=None):
+    """Clip dicts from an open walking dataset (`h5py.File`, `hdf5_lite.File` or a mapping of the same shape), as
+    `HDF5WalkingTrajectoryLoader.get_trajectory` returns them (trajectory_loaders.py:189-215): `qpos = [root_qpos | qpos]`,
+    `qvel = [root_qvel | qvel]`, xy origin moved to the first frame (:206), `root2site`, `joint_quat`.
+
+    The reference takes its mocap joints / sites from the dataset's `id2name` lists (walk_imitation.py:63-71); the compiled model
+    fixes them (`M["mocap_joint"]`, `M["mocap_site"]`), so when `id2name` is present its names are matched to the model's and the
+    dataset's columns are reordered into the model's order; a name the model tracks but the dataset lacks is an error."""
+    nj, ns = int(M["n_mocap_joints"]), int(M["n_mocap_sites"])
+    jsel = ssel = None
+    if "id2name" in f:
+        strip = lambda n: n.split("/", 1)[1] if n.startswith("walker/") else n   # noqa: E731
+        if "joints" in f["id2name"] and "_names_jnt" in M:
+            names = _decode(f["id2name"]["joints"])
+            have = {n: i for i, n in enumerate(names)}
+            want = [strip(M["_names_jnt"][int(j)]) for j in M["mocap_joint"]]
+            if all(n in have for n in want):
+                jsel = np.array([have[n] for n in want], np.int64)
+            elif len(names) != nj:       # unknown names but the right count: taken in the order stored
+                raise ValueError(f"dataset lists {len(names)} joints that do not cover the {nj} joints the compiled model tracks "
+                                 f"(missing e.g. {[n for n in want if n not in have][:3]})")
+        if "sites" in f["id2name"] and "_names_site" in M:
+            names = _decode(f["id2name"]["sites"])
+            have = {n: i for i, n in enumerate(names)}
+            want = [strip(M["_names_site"][int(s)]) for s in M["mocap_site"]]
+            if all(n in have for n in want):
+                ssel = np.array([have[n] for n in want], np.int64)
+            elif len(names) != ns:
+                raise ValueError(f"dataset lists {len(names)} sites that do not cover the {ns} sites the compiled model tracks")
+    keys = _traj_keys(f)
+    if traj_indices is not None:
+        keys = [keys[int(i)] for i in traj_indices]
+    out = []
+    for k in keys[:max_clips]:
+        t = f["trajectories"][k]
+        jq_pos, jq_vel = np.asarray(t["qpos"], np.float64), np.asarray(t["qvel"], np.float64)
+        r2s, jq = np.asarray(t["root2site"], np.float64), np.asarray(t["joint_quat"], np.float64)
+        if jsel is not None:
+            jq_pos, jq_vel, jq = jq_pos[:, jsel], jq_vel[:, jsel], jq[:, jsel]
+        if ssel is not None:
+            r2s = r2s[:, ssel]
+        qpos = np.concatenate([np.asarray(t["root_qpos"], np.float64), jq_pos], axis=1)
+        qvel = np.concatenate([np.asarray(t["root_qvel"], np.float64), jq_vel], axis=1)
+        qpos[:, :2] -= qpos[0, :2]
+        if qpos.shape[1] != 7 + nj or r2s.shape[1:] != (ns, 3) or jq.shape[1:] != (nj, 4):
+            raise ValueError(f"clip {k}: shapes {qpos.shape} {r2s.shape} {jq.shape} do not match the model ({nj} joints, {ns} sites)")
+        out.append(dict(qpos=qpos, qvel=qvel, root2site=r2s, joint_quat=jq))
+    return out
+
+
+def hdf5_flight_clips(f, max_clips=None, traj_indices=None):
+    """Clip dicts from an open flight dataset (`com_qpos`, `com_qvel` per trajectory; trajectory_loaders.py:90-132)."""
+    keys = _traj_keys(f)
+    if traj_indices is not None:
+        keys = [keys[int(i)] for i in traj_indices]
+    return [flight_clip_from_com(np.asarray(f["trajectories"][k]["com_qpos"], np.float64),
+                                 np.asarray(f["trajectories"][k]["com_qvel"], np.float64)) for k in keys[:max_clips]]
+
+
+def load_hdf5_clips(M: dict, path: str, max_clips=None, traj_indices=None):
+    """`ref_path="*.hdf5"` of `fly_envs.walk_imitation` / `flight_imitation`: the reference's dataset file -> packed clip table.
+    Walking or flight is told from the datasets the first trajectory holds."""
+    with _open_hdf5(path) as f:
+        first = f["trajectories"][_traj_keys(f)[0]]
+        if "com_qpos" in first:
+            cl = hdf5_flight_clips(f, max_clips, traj_indices)
+        else:
+            cl = hdf5_walking_clips(f, M, max_clips, traj_indices)
+        dt = float(np.asarray(f["timestep_seconds"][()])) if "timestep_seconds" in f else None
+    if dt is not None and abs(dt - float(M["control_dt"])) > 1e-9 * max(1.0, dt):
+        raise ValueError(f"dataset timestep {dt} s differs from the task's control timestep {float(M['control_dt'])} s")
+    return pack_clips(M, cl)
+
+
+def export_hdf5(path: str, M: dict, clips: list, kind: str = "walking", **write_options):
+    """Write clip dicts in the reference's dataset layout (trajectory_loaders.py:33-35, 90-97, 155-157, 189-223) with
+    `hdf5_lite.write_file`: `trajectories/<zero-padded idx>/…`, `trajectory_lengths`, `timestep_seconds`, `id2name/{joints,sites}`.
+    Flight clips are stored as CoM poses (`root2com`), walking clips as they are (their xy origin is already at the first frame)."""
+    from . import hdf5_lite
+    nz = len(str(len(clips)))
+    traj = {}
+    for i, c in enumerate(clips):
+        if kind == "flight":
+            com = np.stack([root2com(r) for r in c["qpos"]])
+            traj[str(i).zfill(nz)] = dict(com_qpos=np.concatenate([com, c["qpos"][:, 3:7]], axis=1), com_qvel=np.asarray(c["qvel"], np.float64))
+        else:
+            traj[str(i).zfill(nz)] = dict(root_qpos=c["qpos"][:, :7], qpos=c["qpos"][:, 7:], root_qvel=c["qvel"][:, :6], qvel=c["qvel"][:, 6:],
+                                          root2site=c["root2site"], joint_quat=c["joint_quat"])
+    tree = {"trajectories": traj, "trajectory_lengths": np.array([c["qpos"].shape[0] for c in clips], np.int64),
+            "timestep_seconds": np.float64(M["control_dt"])}
+    if kind != "flight":
+        strip = lambda n: n.split("/", 1)[1] if n.startswith("walker/") else n   # noqa: E731
+        tree["id2name"] = {"joints": np.array([strip(M["_names_jnt"][int(j)]).encode() for j in M["mocap_joint"]]),
+                           "sites": np.array([strip(M["_names_site"][int(s)]).encode() for s in M["mocap_site"]])}
+    hdf5_lite.write_file(path, tree, **write_options)

@@ -212,7 +212,9 @@ class BatchedFlyEnv:
 
 
 def _load_clips_arg(M, ref_path):
-    """ref_path: `.npz` written by `clips.save_clips`, a list of clip dicts, or 'synthetic:<n_clips>:<T>:<seed>'."""
+    """ref_path: the reference's HDF5 dataset (`*.hdf5` / `*.h5`, vnl_ray/tasks/trajectory_loaders.py: read with h5py where it
+    exists, else with `hdf5_lite`), a `.npz` written by `clips.save_clips`, a list of clip dicts, or
+    'synthetic:<n_clips>:<T>:<seed>'."""
     if ref_path is None:
         return None
     if isinstance(ref_path, (list, tuple)):
@@ -225,8 +227,11 @@ def _load_clips_arg(M, ref_path):
     if isinstance(ref_path, str) and ref_path.endswith(".npz") and os.path.exists(ref_path):
         d = np.load(ref_path)
         return d["rows"], d["offsets"], d["lengths"]
-    raise ValueError("ref_path must be a clip .npz, a list of clips or 'synthetic:<n>:<T>:<seed>' "
-                     "(the HDF5 dataset of the reference cannot be read here: h5py is not installed)")
+    if isinstance(ref_path, str) and ref_path.lower().endswith((".hdf5", ".h5", ".hdf")):
+        if not os.path.exists(ref_path):
+            raise FileNotFoundError(ref_path)
+        return _clips.load_hdf5_clips(M, ref_path)
+    raise ValueError("ref_path must be the reference's HDF5 dataset, a clip .npz, a list of clips or 'synthetic:<n>:<T>:<seed>'")
 
 
 def walk_on_ball(random_state=None, num_envs: int = 1, device=0, seed: int | None = None, **kw) -> BatchedFlyEnv:

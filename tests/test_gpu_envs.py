@@ -92,3 +92,25 @@ def test_inference_mode_takes_a_custom_trajectory(models):
     with pytest.raises(ValueError):
         env.set_next_trajectory(q[:10], v[:10])
     env.close()
+
+
+def test_walk_imitation_reads_the_reference_hdf5_layout(models, tmp_path):
+    """`walk_imitation(ref_path="*.hdf5")` (vnl_ray/fly_envs.py:75-122 with trajectory_loaders.py:163-223): a dataset in the
+    reference's layout, read without h5py, drives the same rollout as the same clips handed over as a list."""
+    import torch
+    from flybody_b200 import clips as C, fly_envs
+    M = models["walk_imitation"]
+    cl = [C.synth_walk_clip(M, T=100 + i, seed=i) for i in range(4)]
+    p = str(tmp_path / "walk.hdf5")
+    C.export_hdf5(p, M, cl, dataset_options={"qpos": dict(chunks=(50, 66), deflate=2)})
+    outs = []
+    for ref in (p, cl):
+        env = fly_envs.walk_imitation(ref_path=ref, num_envs=8, seed=5)
+        ts = env.reset()
+        a = torch.zeros((8, env.action_spec().shape[0]), device=env.device)
+        for _ in range(3):
+            ts = env.step(a)
+        outs.append((ts.reward.cpu().numpy().copy(), ts.observation["walker/ref_displacement"].cpu().numpy().copy()))
+        env.close()
+    assert np.array_equal(outs[0][0], outs[1][0]) and np.array_equal(outs[0][1], outs[1][1])
+    assert len(set(outs[0][0].tolist())) > 1          # the envs drew different clips
