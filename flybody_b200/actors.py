@@ -8,7 +8,9 @@ Here one process steps N environments per call (`fly_envs.BatchedFlyEnv`) and th
 leading batch dimension:
 
   LayerNormMLPPolicy        the policy network of `agents/network_factory.py:73-101` (batch_concat -> LayerNormMLP ->
-                            MultivariateNormalDiagHead), torch, random init (no checkpoints here)
+                            MultivariateNormalDiagHead), torch, random init (no checkpoints here): owner of the parameters
+                            and fp32 reference
+  FusedPolicy               the same network as one hand-written sm_100a kernel (tcgen05 / TMEM / TMA, `flyb_policy_*`)
   BatchedFeedForwardActor   select_action / observe_first / observe / update with the reference actor's action_delay and
                             observation_callback arguments
   NStepTransitionAdder      acme's n-step transitions (o_s, a_s, R, D, o_{s+h}) per env - growing horizons at the start of an
@@ -77,6 +79,98 @@ class LayerNormMLPPolicy(nn.Module):
         mean, scale = self(observation)
         eps = torch.randn(mean.shape, device=mean.device, dtype=mean.dtype, generator=generator)
         return mean + scale * eps
+
+
+class FusedPolicy:
+    """A `LayerNormMLPPolicy` evaluated by the hand-written sm_100a kernel behind `flyb_policy_*` (include/flyb.h,
+    csrc/flyb_policy.cu): bf16 operands on the tcgen05 tensor cores with fp32 accumulation in tensor memory, TMA-fed weight
+    tiles, LayerNorm / tanh / ELU / softplus epilogues and the Gaussian sample fused into one launch per call (plus the bf16
+    cast of the observations).  The torch module stays the owner of the parameters (a learner / variable client updates it);
+    `refresh()` re-uploads them.  Same interface as the module: `policy(obs) -> (mean, scale)`, `policy.sample(obs, generator)`.
+    No fallback: construction fails without the CUDA library or on a device without tcgen05."""
+
+    def __init__(self, policy: LayerNormMLPPolicy, max_rows: int, device=None):
+        import ctypes
+        from . import engine
+        sizes = [policy.first.out_features] + [lin.out_features for lin in policy.rest]
+        if sizes != [512, 512, 512, 512]:
+            raise ValueError(f"the fused policy kernel is built for layer_sizes (512, 512, 512, 512), got {tuple(sizes)}")
+        self.module = policy
+        dev = torch.device(device) if device is not None else policy.first.weight.device
+        if dev.type != "cuda":
+            raise RuntimeError("FusedPolicy needs the policy on a CUDA device (there is no CPU path)")
+        self.device = dev
+        self.obs_dim, self.act_dim = policy.first.in_features, policy.mean.out_features
+        self.max_rows = int(max_rows)
+        self._L = engine.lib()
+        self._h = ctypes.c_void_p()
+        index = dev.index if dev.index is not None else torch.cuda.current_device()
+        if self._L.flyb_policy_create(index, self.obs_dim, self.act_dim, self.max_rows, ctypes.byref(self._h)):
+            msg = self._L.flyb_policy_last_error(self._h).decode() if self._h else "allocation failed"
+            self._L.flyb_policy_destroy(self._h); self._h = None
+            raise RuntimeError("flyb_policy_create: " + msg)
+        self.refresh()
+
+    def _check(self, rc, what):
+        if rc:
+            raise RuntimeError(f"{what}: {self._L.flyb_policy_last_error(self._h).decode()}")
+
+    def refresh(self):
+        """Upload the module's current parameters (fp32 on the device) into the kernel's bf16 weight buffers."""
+        m = self.module
+        ts = [m.first.weight, m.first.bias, m.norm.weight, m.norm.bias]
+        for lin in m.rest:
+            ts += [lin.weight, lin.bias]
+        ts += [m.mean.weight, m.mean.bias, m.scale.weight, m.scale.bias]
+        ts = [t.detach().to(self.device, torch.float32).contiguous() for t in ts]
+        with torch.cuda.device(self.device):
+            st = torch.cuda.current_stream().cuda_stream
+            self._check(self._L.flyb_policy_set_weights(self._h, *[t.data_ptr() for t in ts], float(m.norm.eps), float(m.init_scale),
+                                                        float(m.min_scale), int(bool(m.tanh_mean)), st), "flyb_policy_set_weights")
+        self._keep = ts   # alive until the copies enqueued above have run
+
+    def _forward(self, observation, eps, want_stats: bool, want_action: bool):
+        obs = batch_concat(observation).to(torch.float32).contiguous()
+        n = obs.shape[0]
+        mean = torch.empty((n, self.act_dim), device=self.device) if want_stats else None
+        scale = torch.empty((n, self.act_dim), device=self.device) if want_stats else None
+        action = torch.empty((n, self.act_dim), device=self.device) if want_action else None
+        ptr = lambda t: t.data_ptr() if t is not None else None   # noqa: E731
+        with torch.cuda.device(self.device):
+            st = torch.cuda.current_stream().cuda_stream
+            self._check(self._L.flyb_policy_forward(self._h, obs.data_ptr(), n, ptr(eps), ptr(mean), ptr(scale), ptr(action), st),
+                        "flyb_policy_forward")
+        return mean, scale, action
+
+    def __call__(self, observation):
+        mean, scale, _ = self._forward(observation, None, True, False)
+        if self.module.fixed_scale:
+            scale = torch.full_like(mean, self.module.init_scale)
+        return mean, scale
+
+    @torch.no_grad()
+    def sample(self, observation, generator: Optional[torch.Generator] = None) -> torch.Tensor:
+        n = next(iter(observation.values())).shape[0] if isinstance(observation, dict) else observation.shape[0]
+        eps = torch.randn((n, self.act_dim), device=self.device, dtype=torch.float32, generator=generator)
+        if self.module.fixed_scale:
+            mean, _, _ = self._forward(observation, None, True, False)
+            return mean + self.module.init_scale * eps
+        return self._forward(observation, eps, False, True)[2]
+
+    @property
+    def launches(self) -> int:
+        return int(self._L.flyb_policy_launches(self._h))
+
+    def close(self):
+        if self._h:
+            self._L.flyb_policy_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 class NStepTransitionAdder:

@@ -1,0 +1,449 @@
+/* flyb_policy.cu - the actor's policy network as ONE fused sm_100a kernel (BASELINE.json configs[3]).
+ *
+ * The network of vnl_ray/agents/network_factory.py:73-101 (acme LayerNormMLP((512, 512, 512, 512), activate_final=True) ->
+ * MultivariateNormalDiagHead):  x = tanh(LayerNorm(W1 obs + b1)); x = elu(Wl x + bl), l = 2..4; mean = Wm x + bm;
+ * scale = softplus(Ws x + bs) * init_scale / ln 2 + min_scale; action = mean + scale * eps.
+ * For 16 384 envs that is 16 384 x (741 x 512 + 3 x 512^2 + 512 x 118) = 26 GFLOP per control step: the one GEMM-shaped piece of
+ * the actor side, so it runs on the 5th-generation tensor cores:
+ *
+ *   - one CTA per 128 observation rows (UMMA M = 128, cta_group::1), 6 warps: warps 0-3 epilogue (one thread per row = one
+ *     TMEM lane), warp 4 TMA producer, warp 5 MMA issuer (one elected thread each);
+ *   - the whole 128 x 512 fp32 layer output lives in TMEM (512 columns), written by tcgen05.mma.kind::f16 (bf16 x bf16 -> fp32,
+ *     N = 256 per instruction), read back by tcgen05.ld.32x32b for bias + LayerNorm + tanh / ELU;
+ *   - activations never leave the SM: the epilogue writes them as bf16 into shared memory in the canonical K-major
+ *     SWIZZLE_128B layout, where the next layer's MMAs read them as the A operand (128 KB: 8 K-chunks of 128 rows x 128 B);
+ *   - weights (bf16, [out, in] row-major = K-major, L2-resident: 2.3 MB) and the first layer's input tiles stream through a
+ *     2-stage TMA pipeline (cp.async.bulk.tensor.2d, SWIZZLE_128B, mbarrier complete_tx), freed by tcgen05.commit.
+ *
+ * Every spin on an mbarrier is bounded (trap after ~2 s) so that a protocol bug cannot hang the device. */
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <new>
+#include <string>
+
+#include "../../include/flyb.h"
+
+namespace {
+
+constexpr int PH = 512;            /* hidden width of every layer */
+constexpr int PKC = 64;            /* bf16 elements per K chunk = one 128-byte swizzle row */
+constexpr int PM = 128;            /* rows per CTA */
+constexpr int PNH = 256;           /* N per MMA instruction */
+constexpr int PSTAGES = 2;
+constexpr int PA_BYTES = PM * PKC * 2;      /* 16 KB: an A tile (128 rows x 64 bf16) */
+constexpr int PB_BYTES = PNH * PKC * 2;     /* 32 KB: a B tile (256 weight rows x 64 bf16) */
+constexpr int PSTAGE_BYTES = PA_BYTES + PB_BYTES;
+constexpr int PACT_BYTES = PM * PH * 2;     /* 128 KB */
+constexpr int PHEAD_N = 128;                /* head output columns: mean at 0.., scale at 64.. */
+constexpr int PSMEM_BYTES = PACT_BYTES + PSTAGES * PSTAGE_BYTES + 1024 /* barriers */ + 1024 /* alignment slack */;
+constexpr int PTHREADS = 192;
+
+struct PolicyParams {
+  const float* b1; const float* ln_g; const float* ln_b;
+  const float* b[3];
+  const float* bm; const float* bs;
+  const float* eps;                /* nullable [N, A] */
+  float* mean; float* scale; float* action;   /* each nullable, [N, A] */
+  int n_rows, act_dim, nk1;        /* nk1: K chunks of the first layer (obs_dim padded to 64) */
+  float ln_eps, scale_mul, min_scale;
+  int tanh_mean;
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t done;
+  const long long t0 = clock64();
+  for (;;) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+    if (done) return;
+    if (clock64() - t0 > 4000000000LL) __trap();   /* ~2 s: a protocol bug must not hang the GPU */
+  }
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int x, int y, uint32_t bar) {
+  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+               ::"r"(dst), "l"(map), "r"(x), "r"(y), "r"(bar) : "memory");
+}
+/* shared-memory matrix descriptor, K-major, SWIZZLE_128B: start >> 4 | LBO (unused) | SBO = 1024 B (8 rows x 128 B) | version 1 */
+__device__ __forceinline__ uint64_t umma_desc(uint32_t addr) {
+  return (uint64_t)((addr & 0x3FFFF) >> 4) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
+}
+/* instruction descriptor of kind::f16: D fp32 (bit 4), A / B bf16 (bits 7, 10), both K-major, N >> 3 at bit 17, M >> 4 at bit 24 */
+__device__ __forceinline__ constexpr uint32_t umma_idesc(int M, int N) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float* v) {
+  uint32_t r[32];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
+        "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]),
+        "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]),
+        "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr) : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 32; i++) v[i] = __uint_as_float(r[i]);
+}
+__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+/* 32 activations of row r, columns [32 c, 32 c + 32), into the A-operand buffer: K chunk c / 2, 16-byte groups swizzled by row */
+__device__ __forceinline__ void store_act32(uint8_t* act, int r, int c, const float* y) {
+  uint8_t* row = act + (c >> 1) * PA_BYTES + r * 128;
+  const int g0 = (c & 1) * 4;
+#pragma unroll
+  for (int g = 0; g < 4; g++) {
+    uint4 q;
+    q.x = pack_bf16(y[8 * g + 0], y[8 * g + 1]); q.y = pack_bf16(y[8 * g + 2], y[8 * g + 3]);
+    q.z = pack_bf16(y[8 * g + 4], y[8 * g + 5]); q.w = pack_bf16(y[8 * g + 6], y[8 * g + 7]);
+    *reinterpret_cast<uint4*>(row + (((g0 + g) ^ (r & 7)) << 4)) = q;
+  }
+}
+
+__global__ void __launch_bounds__(PTHREADS, 1)
+fly_policy_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w1,
+                  const __grid_constant__ CUtensorMap map_w2, const __grid_constant__ CUtensorMap map_w3,
+                  const __grid_constant__ CUtensorMap map_w4, const __grid_constant__ CUtensorMap map_wh,
+                  const __grid_constant__ PolicyParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* act = smem;                                   /* 8 chunks x 16 KB */
+  uint8_t* stage = smem + PACT_BYTES;                    /* PSTAGES x (A 16 KB | B 32 KB) */
+  uint64_t* bars = reinterpret_cast<uint64_t*>(stage + PSTAGES * PSTAGE_BYTES);
+  /* bars: full[PSTAGES], empty[PSTAGES], acc_full, act_ready ; then the TMEM base address */
+  const uint32_t bar_full = smem_u32(bars), bar_empty = smem_u32(bars + PSTAGES);
+  const uint32_t bar_acc = smem_u32(bars + 2 * PSTAGES), bar_act = smem_u32(bars + 2 * PSTAGES + 1);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * PSTAGES + 2);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row0 = blockIdx.x * PM;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < PSTAGES; s++) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, 1); }
+    mbar_init(bar_acc, 1);
+    mbar_init(bar_act, PM);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 4) {   /* the allocating warp also frees: all 512 columns (one CTA per SM: nothing to contend with) */
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem = *tmem_slot;
+
+  /* the item sequence both pipeline ends walk: layer 0: 2 N-halves x nk1 chunks (A + B tiles); layers 1-3: 2 x 8 (B only, A =
+     the activation buffer); layer 4 = the head: 8 chunks of a 128-row B tile */
+  if (warp == 4 && lane == 0) {
+    /* ------------------------------------------------------------------------------------------------ TMA producer */
+    const CUtensorMap* wmap[5] = {&map_w1, &map_w2, &map_w3, &map_w4, &map_wh};
+    int it = 0;
+    for (int l = 0; l < 5; l++) {
+      const int nk = l == 0 ? p.nk1 : PH / PKC, nhalf = l == 4 ? 1 : 2;
+      for (int nh = 0; nh < nhalf; nh++)
+        for (int kc = 0; kc < nk; kc++, it++) {
+          const int s = it % PSTAGES;
+          mbar_wait(bar_empty + 8 * s, ((it / PSTAGES) & 1) ^ 1);
+          const uint32_t a_dst = smem_u32(stage + s * PSTAGE_BYTES), b_dst = a_dst + PA_BYTES;
+          const uint32_t bytes = (l == 0 ? PA_BYTES : 0) + (l == 4 ? PHEAD_N * PKC * 2 : PB_BYTES);
+          mbar_expect_tx(bar_full + 8 * s, bytes);
+          if (l == 0) tma_load_2d(a_dst, &map_x, kc * PKC, row0, bar_full + 8 * s);
+          tma_load_2d(b_dst, wmap[l], kc * PKC, nh * PNH, bar_full + 8 * s);
+        }
+    }
+  } else if (warp == 5 && lane == 0) {
+    /* -------------------------------------------------------------------------------------------------- MMA issuer */
+    int it = 0;
+    for (int l = 0; l < 5; l++) {
+      const int nk = l == 0 ? p.nk1 : PH / PKC, nhalf = l == 4 ? 1 : 2;
+      const uint32_t idesc = l == 4 ? umma_idesc(PM, PHEAD_N) : umma_idesc(PM, PNH);
+      if (l > 0) {   /* the epilogue has drained TMEM and written this layer's A operand */
+        mbar_wait(bar_act, (l - 1) & 1);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      }
+      for (int nh = 0; nh < nhalf; nh++)
+        for (int kc = 0; kc < nk; kc++, it++) {
+          const int s = it % PSTAGES;
+          mbar_wait(bar_full + 8 * s, (it / PSTAGES) & 1);
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          const uint32_t a_base = l == 0 ? smem_u32(stage + s * PSTAGE_BYTES) : smem_u32(act + kc * PA_BYTES);
+          const uint32_t b_base = smem_u32(stage + s * PSTAGE_BYTES) + PA_BYTES;
+#pragma unroll
+          for (int k = 0; k < PKC / 16; k++)   /* UMMA K = 16 bf16 = 32 bytes along the swizzled row */
+            umma_bf16(tmem + nh * PNH, umma_desc(a_base + 32 * k), umma_desc(b_base + 32 * k), idesc, (kc | k) != 0);
+          umma_commit(bar_empty + 8 * s);     /* frees the stage once these MMAs have read it */
+        }
+      umma_commit(bar_acc);                   /* the layer's accumulator is complete */
+    }
+  } else if (warp < 4) {
+    /* ---------------------------------------------------------------------------------------------------- epilogue */
+    const int r = warp * 32 + lane;                        /* row of the tile = TMEM lane */
+    const uint32_t trow = tmem + ((uint32_t)(warp * 32) << 16);
+    float v[32];
+    for (int l = 0; l < 5; l++) {
+      mbar_wait(bar_acc, l & 1);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      if (l == 0) {         /* bias, LayerNorm over the 512 features of the row, tanh */
+        float sum = 0;
+        for (int c = 0; c < PH / 32; c++) {
+          tmem_ld32(trow + 32 * c, v);
+#pragma unroll
+          for (int j = 0; j < 32; j++) sum += v[j] + __ldg(p.b1 + 32 * c + j);
+        }
+        const float mu = sum * (1.0f / PH);
+        float sq = 0;
+        for (int c = 0; c < PH / 32; c++) {
+          tmem_ld32(trow + 32 * c, v);
+#pragma unroll
+          for (int j = 0; j < 32; j++) { const float d = v[j] + __ldg(p.b1 + 32 * c + j) - mu; sq += d * d; }
+        }
+        const float rstd = rsqrtf(sq * (1.0f / PH) + p.ln_eps);
+        for (int c = 0; c < PH / 32; c++) {
+          tmem_ld32(trow + 32 * c, v);
+#pragma unroll
+          for (int j = 0; j < 32; j++) {
+            const int col = 32 * c + j;
+            v[j] = tanhf((v[j] + __ldg(p.b1 + col) - mu) * rstd * __ldg(p.ln_g + col) + __ldg(p.ln_b + col));
+          }
+          store_act32(act, r, c, v);
+        }
+      } else if (l < 4) {   /* bias, ELU */
+        const float* b = p.b[l - 1];
+        for (int c = 0; c < PH / 32; c++) {
+          tmem_ld32(trow + 32 * c, v);
+#pragma unroll
+          for (int j = 0; j < 32; j++) { const float x = v[j] + __ldg(b + 32 * c + j); v[j] = x > 0.f ? x : expm1f(x); }
+          store_act32(act, r, c, v);
+        }
+      } else {              /* heads: mean | scale (columns 64..), sampled action */
+        const int row = row0 + r;
+        float s[32];
+        for (int c = 0; c < 2; c++) {
+          tmem_ld32(trow + 32 * c, v);
+          tmem_ld32(trow + 64 + 32 * c, s);
+          if (row < p.n_rows) {
+#pragma unroll
+            for (int j = 0; j < 32; j++) {
+              const int col = 32 * c + j;
+              if (col < p.act_dim) {
+                float mean = v[j] + __ldg(p.bm + col);
+                if (p.tanh_mean) mean = tanhf(mean);
+                const float x = s[j] + __ldg(p.bs + col);
+                const float sp = x > 20.f ? x : log1pf(expf(x));
+                const float scale = sp * p.scale_mul + p.min_scale;
+                const size_t o = (size_t)row * p.act_dim + col;
+                if (p.mean) p.mean[o] = mean;
+                if (p.scale) p.scale[o] = scale;
+                if (p.action) p.action[o] = mean + scale * (p.eps ? p.eps[o] : 0.f);
+              }
+            }
+          }
+        }
+      }
+      if (l < 4) {
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   /* generic-proxy stores -> visible to the tensor core */
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        mbar_arrive(bar_act);
+      }
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 4) {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512) : "memory");
+  }
+}
+
+/* fp32 [rows, cols] -> bf16 [rows_pad, cols_pad], zero padded (weights once, observations every call) */
+__global__ void fly_policy_cast(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int rows, int cols, int rows_pad,
+                                int cols_pad, int dst_row0) {
+  const size_t n = (size_t)rows_pad * cols_pad;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const int r = (int)(i / cols_pad), c = (int)(i % cols_pad);
+    dst[(size_t)(dst_row0 + r) * cols_pad + c] = __float2bfloat16((r < rows && c < cols) ? src[(size_t)r * cols + c] : 0.f);
+  }
+}
+
+struct Policy {
+  int device = 0, obs_dim = 0, act_dim = 0, k1pad = 0, max_rows = 0;
+  __nv_bfloat16 *w1 = nullptr, *w2 = nullptr, *w3 = nullptr, *w4 = nullptr, *wh = nullptr, *xb = nullptr;
+  float* vec = nullptr;            /* b1 | ln_g | ln_b | b2 | b3 | b4 | bm (64) | bs (64) */
+  CUtensorMap m_w1, m_w2, m_w3, m_w4, m_wh, m_x;
+  int x_rows = -1;
+  float ln_eps = 1e-5f, init_scale = 0.7f, min_scale = 1e-6f;
+  int tanh_mean = 0;
+  long long launches = 0;
+  std::string err;
+};
+
+typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                             const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                             CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeFn encode_fn() {
+  static EncodeFn fn = nullptr;
+  if (!fn) {
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+      fn = (EncodeFn)ptr;
+  }
+  return fn;
+}
+
+/* bf16 [rows, cols] row-major, box = 64 columns x box_rows, 128-byte swizzle */
+bool make_map(CUtensorMap* map, void* base, int rows, int cols, int box_rows) {
+  EncodeFn fn = encode_fn();
+  if (!fn) return false;
+  cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t gstride[1] = {(cuuint64_t)cols * 2};
+  cuuint32_t box[2] = {PKC, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  return fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+            CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+int pfail(Policy* P, const char* what, cudaError_t e = cudaSuccess) {
+  P->err = std::string(what) + (e != cudaSuccess ? std::string(": ") + cudaGetErrorString(e) : std::string());
+  return 1;
+}
+
+#define PCK(call)                                       \
+  do {                                                  \
+    cudaError_t e_ = (call);                            \
+    if (e_ != cudaSuccess) return pfail(P, #call, e_);  \
+  } while (0)
+
+}  // namespace
+
+extern "C" {
+
+int flyb_policy_create(int device, int obs_dim, int act_dim, int max_rows, flyb_policy_handle* out) {
+  if (!out) return 1;
+  *out = nullptr;
+  if (obs_dim < 1 || obs_dim > 4096 || act_dim < 1 || act_dim > 64 || max_rows < 1) return 1;
+  Policy* P = new (std::nothrow) Policy();
+  if (!P) return 1;
+  *out = P;
+  P->device = device; P->obs_dim = obs_dim; P->act_dim = act_dim;
+  P->k1pad = (obs_dim + PKC - 1) / PKC * PKC;
+  P->max_rows = (max_rows + PM - 1) / PM * PM;
+  PCK(cudaSetDevice(device));
+  int cc_major = 0;
+  PCK(cudaDeviceGetAttribute(&cc_major, cudaDevAttrComputeCapabilityMajor, device));
+  if (cc_major != 10) return pfail(P, "flyb_policy needs an sm_100 device (tcgen05 / TMEM)");
+  if (!encode_fn()) return pfail(P, "cuTensorMapEncodeTiled is not available from this driver");
+  PCK(cudaMalloc(&P->w1, (size_t)PH * P->k1pad * 2));
+  PCK(cudaMalloc(&P->w2, (size_t)PH * PH * 2));
+  PCK(cudaMalloc(&P->w3, (size_t)PH * PH * 2));
+  PCK(cudaMalloc(&P->w4, (size_t)PH * PH * 2));
+  PCK(cudaMalloc(&P->wh, (size_t)PHEAD_N * PH * 2));
+  PCK(cudaMalloc(&P->xb, (size_t)P->max_rows * P->k1pad * 2));
+  PCK(cudaMalloc(&P->vec, (size_t)(6 * PH + 128) * sizeof(float)));
+  PCK(cudaMemset(P->vec, 0, (size_t)(6 * PH + 128) * sizeof(float)));
+  PCK(cudaMemset(P->wh, 0, (size_t)PHEAD_N * PH * 2));
+  if (!make_map(&P->m_w1, P->w1, PH, P->k1pad, PNH) || !make_map(&P->m_w2, P->w2, PH, PH, PNH) ||
+      !make_map(&P->m_w3, P->w3, PH, PH, PNH) || !make_map(&P->m_w4, P->w4, PH, PH, PNH) ||
+      !make_map(&P->m_wh, P->wh, PHEAD_N, PH, PHEAD_N))
+    return pfail(P, "cuTensorMapEncodeTiled failed for a weight matrix");
+  PCK(cudaFuncSetAttribute(fly_policy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PSMEM_BYTES));
+  return 0;
+}
+
+void flyb_policy_destroy(flyb_policy_handle h) {
+  Policy* P = (Policy*)h;
+  if (!P) return;
+  cudaSetDevice(P->device);
+  cudaFree(P->w1); cudaFree(P->w2); cudaFree(P->w3); cudaFree(P->w4); cudaFree(P->wh); cudaFree(P->xb); cudaFree(P->vec);
+  delete P;
+}
+
+const char* flyb_policy_last_error(flyb_policy_handle h) { return h ? ((Policy*)h)->err.c_str() : "null handle"; }
+
+long long flyb_policy_launches(flyb_policy_handle h) { return h ? ((Policy*)h)->launches : 0; }
+
+int flyb_policy_set_weights(flyb_policy_handle h, const float* w1, const float* b1, const float* ln_g, const float* ln_b,
+                            const float* w2, const float* b2, const float* w3, const float* b3, const float* w4, const float* b4,
+                            const float* wm, const float* bm, const float* ws, const float* bs, float ln_eps, float init_scale,
+                            float min_scale, int tanh_mean, void* stream) {
+  Policy* P = (Policy*)h;
+  if (!P) return 1;
+  if (!w1 || !b1 || !ln_g || !ln_b || !w2 || !b2 || !w3 || !b3 || !w4 || !b4 || !wm || !bm || !ws || !bs)
+    return pfail(P, "flyb_policy_set_weights: null pointer");
+  cudaStream_t st = (cudaStream_t)stream;
+  PCK(cudaSetDevice(P->device));
+  fly_policy_cast<<<256, 256, 0, st>>>(w1, P->w1, PH, P->obs_dim, PH, P->k1pad, 0);
+  fly_policy_cast<<<256, 256, 0, st>>>(w2, P->w2, PH, PH, PH, PH, 0);
+  fly_policy_cast<<<256, 256, 0, st>>>(w3, P->w3, PH, PH, PH, PH, 0);
+  fly_policy_cast<<<256, 256, 0, st>>>(w4, P->w4, PH, PH, PH, PH, 0);
+  fly_policy_cast<<<64, 256, 0, st>>>(wm, P->wh, P->act_dim, PH, 64, PH, 0);    /* head rows 0..63: mean, 64..127: scale */
+  fly_policy_cast<<<64, 256, 0, st>>>(ws, P->wh, P->act_dim, PH, 64, PH, 64);
+  const float* src[6] = {b1, ln_g, ln_b, b2, b3, b4};
+  for (int i = 0; i < 6; i++) PCK(cudaMemcpyAsync(P->vec + i * PH, src[i], PH * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  PCK(cudaMemcpyAsync(P->vec + 6 * PH, bm, P->act_dim * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  PCK(cudaMemcpyAsync(P->vec + 6 * PH + 64, bs, P->act_dim * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  PCK(cudaGetLastError());
+  P->ln_eps = ln_eps; P->init_scale = init_scale; P->min_scale = min_scale; P->tanh_mean = tanh_mean;
+  P->launches += 6;
+  return 0;
+}
+
+int flyb_policy_forward(flyb_policy_handle h, const float* obs, int n_rows, const float* eps, float* mean, float* scale,
+                        float* action, void* stream) {
+  Policy* P = (Policy*)h;
+  if (!P) return 1;
+  if (!obs || n_rows < 1) return pfail(P, "flyb_policy_forward: no observations");
+  if (n_rows > P->max_rows) return pfail(P, "flyb_policy_forward: more rows than the handle was created for");
+  cudaStream_t st = (cudaStream_t)stream;
+  PCK(cudaSetDevice(P->device));
+  const int rows_pad = (n_rows + PM - 1) / PM * PM;
+  if (P->x_rows != rows_pad) {
+    if (!make_map(&P->m_x, P->xb, rows_pad, P->k1pad, PM)) return pfail(P, "cuTensorMapEncodeTiled failed for the observations");
+    P->x_rows = rows_pad;
+  }
+  fly_policy_cast<<<592, 256, 0, st>>>(obs, P->xb, n_rows, P->obs_dim, rows_pad, P->k1pad, 0);
+  PolicyParams pp;
+  pp.b1 = P->vec; pp.ln_g = P->vec + PH; pp.ln_b = P->vec + 2 * PH;
+  pp.b[0] = P->vec + 3 * PH; pp.b[1] = P->vec + 4 * PH; pp.b[2] = P->vec + 5 * PH;
+  pp.bm = P->vec + 6 * PH; pp.bs = P->vec + 6 * PH + 64;
+  pp.eps = eps; pp.mean = mean; pp.scale = scale; pp.action = action;
+  pp.n_rows = n_rows; pp.act_dim = P->act_dim; pp.nk1 = P->k1pad / PKC;
+  pp.ln_eps = P->ln_eps; pp.scale_mul = P->init_scale / 0.6931471805599453f; pp.min_scale = P->min_scale;
+  pp.tanh_mean = P->tanh_mean;
+  fly_policy_kernel<<<rows_pad / PM, PTHREADS, PSMEM_BYTES, st>>>(P->m_x, P->m_w1, P->m_w2, P->m_w3, P->m_w4, P->m_wh, pp);
+  PCK(cudaGetLastError());
+  P->launches += 2;
+  return 0;
+}
+
+}  // extern "C"

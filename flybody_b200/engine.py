@@ -27,7 +27,9 @@ FLAG_LANES16 = 1 << 17
 EXPORTS = ["flyb_create", "flyb_destroy", "flyb_last_error", "flyb_info", "flyb_configure", "flyb_load_clips",
            "flyb_set_clip_ids", "flyb_reset", "flyb_step", "flyb_reset_host", "flyb_step_host", "flyb_get_state",
            "flyb_set_state", "flyb_get_trace", "flyb_episode_stats", "flyb_load_wbpg", "flyb_set_wbpg_phase",
-           "flyb_use_generic_kernel", "flyb_step_noalloc", "flyb_fma_peak", "flyb_hfield_contacts", "flyb_render_eyes"]
+           "flyb_use_generic_kernel", "flyb_step_noalloc", "flyb_fma_peak", "flyb_hfield_contacts", "flyb_render_eyes",
+           "flyb_policy_create", "flyb_policy_destroy", "flyb_policy_last_error", "flyb_policy_launches",
+           "flyb_policy_set_weights", "flyb_policy_forward"]
 
 
 N_SPEC_MODELS = 4   # csrc/fly_dims_gen.h: FLY_SPEC_COUNT
@@ -55,7 +57,7 @@ def compile_library(out_path: str, extra_flags=(), verbose: bool = False, units=
     # flyb_cuda.cu also holds the height-field and eye-camera kernels.  The portal refinement against a prism takes support points
     # among the vertices of a face whenever its direction is that face's normal: ties decided by the last bit.  Without
     # multiply-add contraction the float64 device code rounds like the CPU code and picks the same vertex.
-    tus = [("flyb_cuda", "flyb_cuda.cu", ["-fmad=false"])]
+    tus = [("flyb_cuda", "flyb_cuda.cu", ["-fmad=false"]), ("flyb_policy", "flyb_policy.cu", [])]
     for nl, w, l, sp in (units if units is not None else kernel_units()):
         tus.append((f"k_{nl}_{w}_{l}_{'g' if sp < 0 else 's%d' % sp}", "flyb_kern.cu",
                     [f"-DFLY_NL={nl}", f"-DFLY_TU_WARPS={w}", f"-DFLY_TU_LEVEL={l}", f"-DFLY_TU_SPEC={sp}"]))
@@ -121,6 +123,15 @@ def lib():
         L.flyb_episode_stats.argtypes = [vp, dp]
         L.flyb_load_wbpg.argtypes = [vp, dp, ip, dp, dp, c_i, ctypes.c_double, ctypes.c_double, ctypes.c_double, ctypes.c_double]
         L.flyb_set_wbpg_phase.argtypes = [vp, dp]
+        L.flyb_policy_create.argtypes = [c_i, c_i, c_i, c_i, ctypes.POINTER(vp)]
+        L.flyb_policy_destroy.argtypes = [vp]
+        L.flyb_policy_destroy.restype = None
+        L.flyb_policy_last_error.argtypes = [vp]
+        L.flyb_policy_last_error.restype = ctypes.c_char_p
+        L.flyb_policy_launches.argtypes = [vp]
+        L.flyb_policy_launches.restype = ctypes.c_longlong
+        L.flyb_policy_set_weights.argtypes = [vp] + [vp] * 14 + [ctypes.c_float, ctypes.c_float, ctypes.c_float, c_i, vp]
+        L.flyb_policy_forward.argtypes = [vp, vp, c_i, vp, vp, vp, vp, vp]
         _lib = L
     return _lib
 

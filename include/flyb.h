@@ -151,6 +151,28 @@ int flyb_render_eyes(int device, const float* data, int nterrain, int nrow, int 
                      const int32_t* terrain_id, const float* cams12, int width, int height, float fovy_deg, const float* colors8,
                      uint8_t* out);
 
+/* The actor's policy network, batched (replaces the per-actor TensorFlow policy call of
+ * vnl_ray/agents/actors.py:59-89 on the network of agents/network_factory.py:73-101: batch_concat -> acme LayerNormMLP((512, 512,
+ * 512, 512), activate_final=True) -> MultivariateNormalDiagHead).  One fused sm_100a kernel per call: bf16 operands, fp32
+ * accumulation in tensor memory (tcgen05.mma), TMA-fed weight tiles, activations resident in shared memory
+ * (csrc/flyb_policy.cu).  All pointers are DEVICE pointers to fp32 (torch parameters / observation tensors); weights are
+ * [out, in] row-major as torch.nn.Linear stores them, wm / ws are the mean and scale heads [act_dim, 512].
+ * forward: obs [n_rows, obs_dim]; eps (nullable) standard-normal noise [n_rows, act_dim]; outputs (each nullable) [n_rows,
+ * act_dim]: mean (tanh'ed when tanh_mean), scale = softplus(.) * init_scale / ln 2 + min_scale, action = mean + scale * eps.
+ * Work is enqueued on `stream`, no synchronisation.  Limits: hidden width 512, 4 layers, act_dim <= 64, obs_dim <= 4096,
+ * n_rows <= max_rows of the handle.  Errors: non-zero return, text from flyb_policy_last_error. */
+typedef void* flyb_policy_handle;
+int flyb_policy_create(int device, int obs_dim, int act_dim, int max_rows, flyb_policy_handle* out);
+void flyb_policy_destroy(flyb_policy_handle h);
+const char* flyb_policy_last_error(flyb_policy_handle h);
+long long flyb_policy_launches(flyb_policy_handle h);   /* kernels launched through this handle so far */
+int flyb_policy_set_weights(flyb_policy_handle h, const float* w1, const float* b1, const float* ln_g, const float* ln_b,
+                            const float* w2, const float* b2, const float* w3, const float* b3, const float* w4, const float* b4,
+                            const float* wm, const float* bm, const float* ws, const float* bs, float ln_eps, float init_scale,
+                            float min_scale, int tanh_mean, void* stream);
+int flyb_policy_forward(flyb_policy_handle h, const float* obs, int n_rows, const float* eps, float* mean, float* scale,
+                        float* action, void* stream);
+
 /* Measurement utility (no reference counterpart): FP32 fused-multiply-add throughput of the device in TFLOP/s, measured with
  * a register-resident FMA micro-benchmark - the denominator of the FP32-pipe fractions bench.py reports. */
 int flyb_fma_peak(int device, double* tflops);
