@@ -219,6 +219,63 @@ def _other_task(torch, task, N, dev, local, flush, peak, steps=10, warm=5):
             "reset_share": stats["resets"] / max(1.0, stats["resets"] + stats["steps"])}
 
 
+def _actor_loop(torch, eng, N, dev, flush, out, amin, amax, env_only_ms, steps=10, warm=5):
+    """config 4 (BASELINE.json configs[3]): the actor side of the DMPO loop on the GPU the environments live on - fused policy
+    kernel (flyb_policy_forward: sample an action from the observations) -> clamp -> step kernel -> n-step adder (n_step 50,
+    discount 0.99: train_dmpo_ray.py:236), device-timed per iteration like the headline; the policy alone is timed beside it."""
+    import collections
+    from flybody_b200 import actors as A
+    obs, rew, disc, st = out
+    TS = collections.namedtuple("TimeStep", ["step_type", "reward", "discount", "observation"])
+    stream = torch.cuda.current_stream(dev).cuda_stream
+    torch.manual_seed(0)
+    pol = A.LayerNormMLPPolicy(obs.shape[1], amin.shape[0]).to(dev)
+    fused = A.FusedPolicy(pol, max_rows=N)
+    adder = A.NStepTransitionAdder(N, obs.shape[1], amin.shape[0], n_step=50, discount=0.99, device=dev, sink=None)
+    gen = torch.Generator(device=dev); gen.manual_seed(5)
+    adder.add_first(TS(st, None, None, obs), torch.ones(N, dtype=torch.bool, device=dev))
+    l0 = fused.launches
+
+    inner = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+
+    def one(k=-1):
+        a = torch.minimum(torch.maximum(fused.sample(obs, gen), amin), amax)
+        if k >= 0:
+            inner[k][0].record()
+        eng.step_ptr(a.data_ptr(), obs.data_ptr(), rew.data_ptr(), disc.data_ptr(), st.data_ptr(), stream)
+        if k >= 0:
+            inner[k][1].record()
+        adder.add(a, TS(st, rew, disc, obs))
+    for _ in range(warm):
+        one()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    torch.cuda.synchronize(dev)
+    for k in range(steps):
+        flush.fill_(float(k))
+        ev[k][0].record(); one(k); ev[k][1].record()
+    torch.cuda.synchronize(dev)
+    ms = float(np.mean([a.elapsed_time(b) for a, b in ev]))
+    env_ms = float(np.mean([a.elapsed_time(b) for a, b in inner]))   # the step kernel inside the loop, under the policy's actions
+    pe = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    for k in range(steps):
+        flush.fill_(float(k))
+        pe[k][0].record(); fused.sample(obs, gen); pe[k][1].record()
+    torch.cuda.synchronize(dev)
+    pms = float(np.mean([a.elapsed_time(b) for a, b in pe]))
+    flop = 2.0 * N * (obs.shape[1] * 512 + 3 * 512 * 512 + 512 * 2 * amin.shape[0])
+    res = {"value": N / (ms * 1e-3), "unit": "env-steps/s", "ms_per_step": ms, "envs": N,
+           "loop": "fused policy kernel (sample) -> clamp -> step kernel -> n-step adder (n_step 50)",
+           "step_kernel_ms_in_loop": env_ms, "ratio_to_env_only": env_ms / ms,
+           "note": "ratio_to_env_only = the step kernel's own time inside this loop / the loop's time per step (the policy's N(0, 0.7) "
+                   "actions keep the flies on their feet: more contacts per step than under U(ctrlrange), headline_ms = %.2f)" % env_only_ms,
+           "policy_ms": pms, "policy_tflops": flop / (pms * 1e-3) / 1e12,
+           "policy_kernel": "fly_policy_kernel (tcgen05.mma kind::f16 bf16 -> fp32 in TMEM, TMA weight tiles; incl. the fp32 -> bf16 cast of "
+                            "the observations and torch.randn for the noise)",
+           "policy_launches_per_step": (fused.launches - l0) / float(warm + 2 * steps), "transitions_written": adder.num_written}
+    fused.close()
+    return res
+
+
 def run_gpu(args):
     import torch
     import torch.distributed as dist
@@ -338,6 +395,7 @@ def run_gpu(args):
                                       "overflow_steps": ts["overflow_steps"],
                                       "frac": ALGO_BYTES["walk_imitation"] * N / tt / 1e9 / peak0}
         del rows_t
+        extras["actor_loop"] = _actor_loop(torch, eng, N, dev, flush, (obs, rew, disc, st), amin, amax, total_ms / args.steps)
         for task in ("flight_imitation", "walk_on_ball"):
             extras[task] = _other_task(torch, task, N, dev, local, flush, peak0)
         extras["fma_peak_tflops"] = fma_peak_tflops(local)

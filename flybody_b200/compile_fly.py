@@ -38,7 +38,7 @@ _ACTION_CLASSES = ("adhesion", "head", "mouth", "antennae", "wings", "abdomen", 
 SPAWN_POS = np.array([0.0, 0.0, 0.1278])  # fruitfly.py:23
 
 MJ_MINVAL = 1e-15
-GEOM_TYPES = {"plane": 0, "sphere": 2, "capsule": 3, "ellipsoid": 4, "cylinder": 5, "box": 6, "mesh": 7}
+GEOM_TYPES = {"plane": 0, "hfield": 1, "sphere": 2, "capsule": 3, "ellipsoid": 4, "cylinder": 5, "box": 6, "mesh": 7}
 JNT_FREE, JNT_BALL, JNT_HINGE = 0, 1, 3
 
 
@@ -210,15 +210,17 @@ class TaskSpec:
     """Composite scene: world body tree + merged element lists + task metadata."""
 
     def __init__(self, task: str, xml_path: str):
-        assert task in ("walk_imitation", "walk_on_ball", "flight_imitation", "template")
+        assert task in ("walk_imitation", "walk_on_ball", "flight_imitation", "template", "vision_flight")
         self.task = task
         self.xml_path = xml_path
-        flight = task == "flight_imitation"
-        if flight:  # fly_envs.py:55-65, tasks/base.py:284-293
+        flight = task in ("flight_imitation", "vision_flight")
+        self.flight, self.vision = flight, task == "vision_flight"
+        self.hfield = None
+        if flight:  # fly_envs.py:55-65, 191-200, tasks/base.py:284-293, tasks/vision_flight.py:49-55
             self.walker = Walker(xml_path, use_legs=False, use_wings=True, joint_filter=0.0,
                                  adhesion_filter=0.007, num_user_actions=1)
             self.physics_dt, self.control_dt = 5e-5, 2e-4  # tasks/constants.py:22-23
-            self.time_limit, self.future_steps = 0.6, 5
+            self.time_limit, self.future_steps = (0.4, 0) if self.vision else (0.6, 5)
         else:  # fly_envs.py:104-115,144-150, tasks/base.py:343-352
             self.walker = Walker(xml_path, use_legs=True, use_wings=False, joint_filter=0.01, adhesion_filter=0.007)
             self.physics_dt, self.control_dt = 2e-4, 2e-3  # tasks/constants.py:16-17
@@ -238,6 +240,13 @@ class TaskSpec:
             ball.joints.append(Joint(name="ball", type="ball"))
             world.children.append(ball)
             ground = ball.geoms[0]
+        elif self.vision:  # tasks/arenas/hills.py:160-221: the `terrain` height field at z = -0.01, then the ground plane
+            dim, density = 20.0, 10
+            n = int((2 * density * dim) // 2) * 2 + 1
+            self.hfield = dict(nrow=n, ncol=n, size=np.array([dim, dim, 1.0, 0.05]))
+            world.geoms.append(Geom(name="terrain", type="hfield", size=np.array([dim, dim, 1.0]), pos=np.array([0.0, 0.0, -0.01])))
+            ground = Geom(name="groundplane", type="plane", size=np.array([dim, dim, 0.5]))
+            world.geoms.append(ground)
         else:  # dm_control floors.Floor: an infinite plane at z=0 with default contact parameters [3P]
             ground = Geom(name="groundplane", type="plane", size=np.array([8.0, 8.0, 0.25]))
             world.geoms.append(ground)
@@ -258,7 +267,8 @@ class TaskSpec:
                 if spec.class_is(g.dclass, "adhesion-collision"):
                     g.friction[0] = 1.0
         else:  # tasks/base.py:296-325
-            ground.contype = ground.conaffinity = 0
+            if not self.vision:   # floor_contacts=False; the vision task keeps them (fly_envs.py:198)
+                ground.contype = ground.conaffinity = 0
             gains = {"yaw": 18.0, "roll": 18.0, "pitch": 18.0}  # tasks/constants.py:31
             for a in spec.actuators:
                 if a.dclass in gains:
@@ -275,6 +285,12 @@ class TaskSpec:
             for c in thorax.children:
                 self.excludes.append(("walker/thorax", c.name))
 
+        if self.vision:
+            # the two eye cameras of the head (fruitfly.xml:335-336) as sites: their world frames are the camera frames
+            # (x right, y up, looking along -z) the ray caster starts from
+            head = spec.find_body("walker/head")
+            head.sites.append(mjcf.Site(name="walker/eye_right", pos=np.array([0.0219, 0.0131, 0.0]), quat=np.array([0.474, 0.688, -0.344, -0.429])))
+            head.sites.append(mjcf.Site(name="walker/eye_left", pos=np.array([-0.0219, 0.0131, 0.0]), quat=np.array([0.474, 0.688, 0.344, 0.429])))
         self.ghost = None
         if task in ("walk_imitation", "flight_imitation"):  # tasks/base.py:141-149
             g = make_ghost(xml_path)
@@ -577,7 +593,8 @@ def _mix_pair(g1: Geom, g2: Geom):
 def _rbound(g: Geom):
     s = g.size
     return {"plane": -1.0, "sphere": s[0], "capsule": s[0] + s[1], "ellipsoid": max(s),
-            "cylinder": np.hypot(s[0], s[1]), "box": np.linalg.norm(s)}[g.type]
+            "cylinder": np.hypot(s[0], s[1]), "box": np.linalg.norm(s),
+            "hfield": float(np.sqrt(s[0] ** 2 + s[1] ** 2 + 25.0))}[g.type]   # covers heights up to 5 (elevation_z_range)
 
 
 def finalize(M: dict, ts: TaskSpec) -> dict:
@@ -849,7 +866,7 @@ def constants(M: dict, ts: TaskSpec) -> dict:
 
 
 # ----------------------------------------------------------------------------
-_TASK_TYPE = {"walk_on_ball": 0, "walk_imitation": 1, "flight_imitation": 2, "template": 3}
+_TASK_TYPE = {"walk_on_ball": 0, "walk_imitation": 1, "flight_imitation": 2, "template": 3, "vision_flight": 4}
 _APPENDAGES = ("claw_T1_left", "claw_T1_right", "claw_T2_left", "claw_T2_right", "claw_T3_left",
                "claw_T3_right", "head")  # fruitfly.py:422-446
 _LEG_HINGES_PER_LEG = 11
@@ -867,7 +884,7 @@ def task_tables(M: dict, ts: TaskSpec) -> dict:
     M["task_type"] = _TASK_TYPE[ts.task]
     M["n_substeps"], M["future_steps"] = ts.n_substeps, ts.future_steps
     M["control_dt"], M["time_limit"] = ts.control_dt, ts.time_limit
-    M["max_episode_steps"] = int(round(ts.time_limit / ts.control_dt)) + (0 if ts.task == "flight_imitation" else 1)  # walk_imitation.py:60 ; flight_imitation.py:107
+    M["max_episode_steps"] = int(round(ts.time_limit / ts.control_dt)) + (0 if ts.flight else 1)  # walk_imitation.py:60 ; flight_imitation.py:107
     # composer.Environment ends the episode when physics.time() >= time_limit; time is the float64 running sum of
     # the physics timestep, so the first control step at which that holds is found by the same accumulation.
     t, k = 0.0, 0
@@ -905,7 +922,7 @@ def task_tables(M: dict, ts: TaskSpec) -> dict:
     M["n_obs_joints"] = len(oj)
     M["obs_joint_qposadr"] = np.array([jq[jid[n]] for n in oj], np.int32)
     M["obs_joint_dofadr"] = np.array([jd[jid[n]] for n in oj], np.int32)
-    walking = ts.task != "flight_imitation"
+    walking = not ts.flight
     app = [sid["walker/" + n] for n in _APPENDAGES] if walking else []
     M["n_appendages"], M["appendage_site"] = len(app), np.array(app, np.int32)
     # mocap joints/sites: the walking dataset's id2name lists are not shipped
@@ -936,6 +953,8 @@ def task_tables(M: dict, ts: TaskSpec) -> dict:
         dims["ball_qvel"] = 3
     if ts.task in ("walk_imitation", "flight_imitation"):
         dims.update(ref_displacement=3 * F, ref_root_quat=4 * F)
+    if ts.vision:   # tasks/vision_flight.py:243-252; the eye images are a separate uint8 output (flyb_render)
+        dims["task_input"] = 2
     off, n = -np.ones(16, np.int32), 0
     for i, k in enumerate(OBS_KEYS):
         if k in dims:
@@ -948,6 +967,22 @@ def task_tables(M: dict, ts: TaskSpec) -> dict:
     M["terminal_com_dist"] = {"walk_imitation": 0.3, "flight_imitation": 2.0}.get(ts.task, 0.0)  # fly_envs.py:33,78
     M["ghost_offset"] = np.zeros(3)
     M["pad_first_obs"], M["inference_mode"] = 0, 0
+    # vision-guided flight (tasks/vision_flight.py:18-63, fly_envs.py:160-206): terrain geom, eye sites, episode draws
+    gn = M["_names_geom"]
+    M["hfield_geom"] = gn.index("terrain") if ts.vision else -1
+    M["hfield_nrow"] = ts.hfield["nrow"] if ts.vision else 0
+    M["hfield_ncol"] = ts.hfield["ncol"] if ts.vision else 0
+    M["hfield_size"] = ts.hfield["size"] if ts.vision else np.zeros(4)
+    M["eye_site"] = np.array([sid["walker/eye_right"], sid["walker/eye_left"]] if ts.vision else [-1, -1], np.int32)
+    up = None
+    if ts.flight:
+        site, _ = w.spec.find_site("walker/hover_up_dir")
+        up = site.quat
+    M["vision_init_quat"] = _neg_quat(up) if ts.vision else np.array([1.0, 0, 0, 0])   # vision_flight.py:131: neg_quat(up_dir)
+    th = np.deg2rad(47.5)                                                              # vision_flight.py:111-112, body pitch
+    M["vision_target_zaxis"] = np.array([np.sin(th), 0.0, np.cos(th)])
+    # target_height_range, target_speed_range, init_pos_x_range, init_pos_y_range (vision_flight.py:28-31)
+    M["vision_ranges"] = np.array([0.5, 0.8, 20.0, 40.0, -5.0, -5.0, 0.0, 0.0])
     # solver options: MuJoCo defaults [3P] + fruitfly.xml:4
     M["opt_iterations"], M["opt_ls_iterations"] = 100, 50
     M["opt_noslip_iterations"] = int(ts.option.get("noslip_iterations", 0))

@@ -464,6 +464,11 @@ FLY_INL bool fly_pair_is_convex(int t1, int t2) {
 }
 
 /* ---------------------------------------------------------------- m5 collision driver */
+#define FLY_MAXHFCON 16   /* contacts kept per geom - height field pair (oracle: FLYO_MAXHFCON) */
+#define FLY_HF_OFF (FLY_PORTAL_WORDS + 24 * FLY_NL)   /* float64 words of efc_A in front of the height-field contact slices */
+template <class T> FLY_INL int fly_hfield_pair(const DModel<T>& m, const Ws<T>& w, const T* c2, const T* m2, const T* s2, int t2,
+                                               double margin, double* out);
+
 template <class T>
 FLY_FN void fly_collision(const DModel<T>& m, const Ws<T>& w) {
   int ncon = 0;
@@ -483,7 +488,8 @@ FLY_FN void fly_collision(const DModel<T>& m, const Ws<T>& w) {
     const T bound = FLY_LDG(m.pair_bound + p);
     const T *c1 = gx + 3 * g1, *c2 = gx + 3 * g2;
     const T d[3] = {c2[0] - c1[0], c2[1] - c1[1], c2[2] - c1[2]};
-    if (pg >> 16) {
+    if (FLY_DIM(m, nhfield) && ((pg >> 17) & 1)) return true;   /* height field: its narrow phase tests the bounds */
+    if ((pg >> 16) & 1) {
       T mat[9];
       fly_geom_xmat(m, w, g1, mat);
       return !(d[0] * mat[2] + d[1] * mat[5] + d[2] * mat[8] > bound);
@@ -500,7 +506,7 @@ FLY_FN void fly_collision(const DModel<T>& m, const Ws<T>& w) {
     const int p = w.cand[i];
     const int pg = m.pair_geom[p], g1 = pg & 255, g2 = (pg >> 8) & 255;
     const int t1 = m.geom_type[g1], t2 = m.geom_type[g2];
-    if (!fly_pair_is_convex(t1, t2)) return true;
+    if (t1 == FLYB_GEOM_HFIELD || !fly_pair_is_convex(t1, t2)) return true;
     T m1[9], m2[9], dir[3], nd[3], p1[3], p2[3];
     fly_geom_xmat(m, w, g1, m1);
     fly_geom_xmat(m, w, g2, m2);
@@ -533,7 +539,12 @@ FLY_FN void fly_collision(const DModel<T>& m, const Ws<T>& w) {
       Hit<T> h[FLY_NHIT];
       int n = 0;
       bool convex = false;
-      if (t1 == FLYB_GEOM_PLANE) {
+      if (FLY_DIM(m, nhfield) && t1 == FLYB_GEOM_HFIELD) {
+        /* terrain of the vision-guided flight task (fly_hfield.cuh): up to FLY_MAXHFCON contacts, kept in this lane's slice of
+           the scratch behind the portal words (float64, like every convex pair) */
+        double* hb = (double*)w.efc_A + FLY_HF_OFF + (size_t)l * (7 * FLY_MAXHFCON);
+        n = fly_hfield_pair(m, w, c2, m2, s2, t2, (double)margin, hb);
+      } else if (t1 == FLYB_GEOM_PLANE) {
         if (t2 == FLYB_GEOM_SPHERE) n = hit_plane_sphere(h, c1, a1, c2, s2[0], margin);
         else if (t2 == FLYB_GEOM_CAPSULE) n = hit_plane_capsule(h, c1, a1, c2, a2, s2, margin);
         else if (t2 == FLYB_GEOM_ELLIPSOID) n = hit_plane_ellipsoid(h, c1, a1, c2, m2, s2, margin);
@@ -575,6 +586,7 @@ FLY_FN void fly_collision(const DModel<T>& m, const Ws<T>& w) {
         }
       }
       w.hit_cnt[l] = n;
+      if (!(FLY_DIM(m, nhfield) && t1 == FLYB_GEOM_HFIELD))
       for (int i = 0; i < n; i++) {
         T* o = w.hit_tmp + (l * FLY_NHIT + i) * 11;
         o[0] = h[i].dist;
@@ -592,10 +604,17 @@ FLY_FN void fly_collision(const DModel<T>& m, const Ws<T>& w) {
     const int total = w.hit_off[FLY_NL];
     FLY_FOR(l, nround) {
       const int p = w.cand[base + l], n = w.hit_cnt[l];
+      const bool hf = FLY_DIM(m, nhfield) && ((m.pair_geom[p] >> 17) & 1);
       for (int i = 0; i < n; i++) {
         const int ci = ncon + w.hit_off[l] + i;
         if (ci >= FLY_MAXCON) break;
-        const T* o = w.hit_tmp + (l * FLY_NHIT + i) * 11;
+        T ob[11];
+        if (hf) {
+          const double* hb = (const double*)w.efc_A + FLY_HF_OFF + (size_t)l * (7 * FLY_MAXHFCON) + 7 * i;
+          for (int k = 0; k < 7; k++) ob[k] = (T)hb[k];
+          ob[7] = ob[8] = ob[9] = ob[10] = 0;
+        }
+        const T* o = hf ? ob : w.hit_tmp + (l * FLY_NHIT + i) * 11;
         w.con_pair[ci] = p;
         w.con_dim[ci] = m.pair_condim[p];
         w.con_dist[ci] = o[0];

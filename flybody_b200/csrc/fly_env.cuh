@@ -3,6 +3,7 @@
 #ifndef FLY_ENV_CUH_
 #define FLY_ENV_CUH_
 #include "fly_task.cuh"
+#include "fly_hfield.cuh"
 
 /* per-env persistent integers */
 enum { FLY_SI_STEP = 0, FLY_SI_EPISODE_STEPS, FLY_SI_RESET_NEXT, FLY_SI_CLIP, FLY_SI_EPISODE, FLY_SI_FORCED_CLIP,
@@ -34,6 +35,8 @@ struct FlyIO {
   const unsigned char* reset_mask; /* nullable */
   const double* wbpg_phase;        /* nullable [N]: initial wing-beat phase to use at reset instead of the hashed draw */
   int* work;                       /* nullable [N]: cycles/64 the env spent in its constraint solves this step (load-balancing key) */
+  float* eyes;                     /* nullable [N, 24]: world frames of the right / left eye camera (vision_flight) */
+  int* eye_terrain;                /* [N] with eyes: index of the env's terrain in the pool */
 };
 
 FLY_INL unsigned long long fly_hash(unsigned long long x) {  /* splitmix64 finaliser */
@@ -248,6 +251,75 @@ FLY_INL double fly_wbpg_phase0(unsigned long long seed, int global_env, int epis
   return (double)(h >> 11) * (1.0 / 9007199254740992.0);
 }
 
+/* ---- vision-guided flight (tasks/vision_flight.py).  The episode's draws - which terrain of the pool, target height, target
+ * speed (vision_flight.py:106-109; arenas/hills.py regenerates the terrain every episode) - are counter-based hashes of (seed,
+ * global env id, episode), recomputed by every control step instead of stored (flybody_b200/fly_envs.py: vision_draws is the
+ * host-side copy). */
+template <class T>
+FLY_INL void fly_vision_draws(const DModel<T>& m, unsigned long long seed, int global_env, int episode, int* terrain, T* height, T* speed) {
+  const unsigned long long h = fly_hash(seed ^ fly_hash((((unsigned long long)global_env << 24) ^ (unsigned long long)episode) + 0x7E44A1ull));
+  *terrain = m.nterrain > 0 ? (int)(h % (unsigned long long)m.nterrain) : 0;
+  const double u1 = (double)(fly_hash(h + 1) >> 11) * (1.0 / 9007199254740992.0);
+  const double u2 = (double)(fly_hash(h + 2) >> 11) * (1.0 / 9007199254740992.0);
+  *height = (T)((double)m.vision_ranges[0] + ((double)m.vision_ranges[1] - (double)m.vision_ranges[0]) * u1);
+  *speed = (T)((double)m.vision_ranges[2] + ((double)m.vision_ranges[3] - (double)m.vision_ranges[2]) * u2);
+}
+/* index of the first minimum of |linspace(lo, hi, n) - x|, as numpy.argmin returns it (vision_flight.py:100-101, 181): only the
+ * grid points next to x can hold it */
+FLY_INL int fly_nearest_linspace(double lo, double hi, int n, double x) {
+  const double step = (hi - lo) / (n - 1);
+  int k = (int)floor((x - lo) / step);
+  int best = 0;
+  double bv = 1e300;
+  for (int i = k - 1; i <= k + 2; i++) {
+    const int j = i < 0 ? 0 : (i > n - 1 ? n - 1 : i);
+    const double a = j == n - 1 ? hi : j * step + lo, d = fabs(a - x);
+    if (d < bv || (d == bv && j < best)) { bv = d; best = j; }
+  }
+  return best;
+}
+template <class T>
+FLY_INL T fly_hfield_height(const DModel<T>& m, int terrain, T x, T y) {  /* get_hfield_height, vision_flight.py:92-104 */
+  if (!m.hf_pool) return T(0);
+  const double half = m.hfield_size[0];
+  const int xi = fly_nearest_linspace(-half, half, m.hfield_ncol, (double)x), yi = fly_nearest_linspace(-half, half, m.hfield_ncol, (double)y);
+  return (T)(m.hfield_size[2] * (double)m.hf_pool[((size_t)terrain * m.hfield_nrow + yi) * m.hfield_ncol + xi]);
+}
+template <class T> FLY_INL T fly_tol_linear(T x, T lo, T hi, T margin) {  /* dm_control rewards.tolerance, "linear", value_at_margin 0 */
+  if (lo <= x && x <= hi) return T(1);
+  if (margin == 0) return T(0);
+  const T d = (x < lo ? lo - x : x - hi) / margin;
+  return d < 1 ? 1 - d : T(0);
+}
+template <class T>
+FLY_FN T fly_vision_reward(const DModel<T>& m, const Ws<T>& w, int terrain, T t_height, T t_speed) {  /* vision_flight.py:157-212 */
+  const T* xpos = w.qpos + m.root_qposadr;
+  const T* vel = w.qvel + m.root_dofadr;
+  const T height = fly_tol_linear(xpos[2] - fly_hfield_height(m, terrain, xpos[0], xpos[1]), t_height, t_height, T(0.15));
+  T center = 1;
+  if (m.trench_meta) {
+    const double* tm = m.trench_meta + 3 * terrain;
+    const int nt = (int)tm[0];
+    if (nt > 1 && tm[1] <= (double)xpos[0] && (double)xpos[0] <= tm[2]) {
+      const int idx = fly_nearest_linspace(tm[1], tm[2], nt, (double)xpos[0]);
+      const T c = (T)m.trench_y[(size_t)terrain * m.trench_stride + idx];
+      center = fly_tol_linear(xpos[1], c, c, T(0.15));
+    }
+  }
+  const T x_speed = vel[0] >= t_speed ? T(1) : fly_tol_linear(vel[0], t_speed, t_speed, T(1.1) * t_speed);
+  const T speed = fly_tol_linear(norm3(vel), t_speed, t_speed, T(1.1) * t_speed);
+  T side = 0;
+  for (int s = 0; s < FLY_DIM(m, nsensor); s++)
+    if (m.sensor_type[s] == FLYB_SENS_VELOCIMETER) side = w.sensordata[m.sensor_adr[s] + 1];
+  const T side_speed = fly_tol_linear(side, T(0), T(0), T(10));
+  const T* zax = w.xmat + 9 * m.root_body + 6;
+  T zd = m.vision_target_zaxis[0] * zax[0] + m.vision_target_zaxis[1] * zax[1] + m.vision_target_zaxis[2] * zax[2];
+  if (zd > 1) zd = 1;
+  if (zd < -1) zd = -1;
+  const T world_zaxis = fly_tol_linear(acos(zd), T(0), T(0), T(FLY_PI));
+  return height * x_speed * speed * side_speed * world_zaxis * center;
+}
+
 /* The whole job of one warp for one env and one call: load the state, reset the episode OR advance it by one control
  * step, store state and outputs.  Reset and step share one pass through the pipeline (each stage has a single call
  * site, so that the fully inlined kernel holds one copy of it):
@@ -264,9 +336,15 @@ FLY_FN void fly_env_run(const DModel<T>& m, const Ws<T>& w, const FlyClips& clip
   const bool do_reset = io.force_reset ? (!io.reset_mask || io.reset_mask[env]) : sint[FLY_SI_RESET_NEXT] != 0;
   if (io.force_reset && !do_reset) { fly_block_pad(fly_nb_control_step(m)); return; }
   T *s_qpos = sr, *s_qvel = sr + FLY_DIM(m, nq), *s_act = s_qvel + FLY_DIM(m, nv), *s_warm = s_act + FLY_DIM(m, na), *s_ret = s_warm + FLY_DIM(m, nv);
+  const int episode = sint[FLY_SI_EPISODE];
+  int terrain = 0;
+  T v_height = 0, v_speed = 0;
+  if (m.task_type == FLYB_TASK_VISION_FLIGHT) {   /* the draws of the episode being started / continued */
+    fly_vision_draws(m, io.seed, io.env_offset + env, do_reset ? episode : episode - 1, &terrain, &v_height, &v_speed);
+    FLY_LANE0 w.counts[FLY_C_TERRAIN] = terrain;
+  }
   FLY_SYNC();
   int clip_id, step = 0, episode_steps = m.max_episode_steps;
-  const int episode = sint[FLY_SI_EPISODE];
   FlyClipView clip;
   if (do_reset) {
     clip_id = sint[FLY_SI_FORCED_CLIP];
@@ -308,6 +386,25 @@ FLY_FN void fly_env_run(const DModel<T>& m, const Ws<T>& w, const FlyClips& clip
       }
       FLY_SYNC();
     }
+    if (m.task_type == FLYB_TASK_VISION_FLIGHT) {   /* vision_flight.py:114-146 */
+      /* init_pos_x / y ranges are single points in the reference's configuration; initialize_qvel is off: the fly starts at rest */
+      const T x0 = m.vision_ranges[4], y0 = m.vision_ranges[6];
+      const T z0 = fly_hfield_height(m, terrain, x0, y0) + v_height;
+      FLY_LANE0 {
+        T* q = w.qpos + m.root_qposadr;
+        q[0] = x0; q[1] = y0; q[2] = z0;
+        for (int k = 0; k < 4; k++) q[3 + k] = m.vision_init_quat[k];
+      }
+      if (wb.nfreq > 0) {                                        /* :125-126, 134: wbpg.reset(initial_phase) -> wing angles */
+        const double phase0 = io.wbpg_phase ? io.wbpg_phase[env] : fly_wbpg_phase0(io.seed, io.env_offset + env, episode);
+        const int fidx = fly_wbpg_nearest_freq(wb, wb.base_freq);
+        const int ws = fly_wbpg_seek(wb, fidx, phase0, false);
+        const double* row = wb.traj + (size_t)(wb.offsets[fidx] + ws) * 6;
+        FLY_FOR(k, 6) w.qpos[m.jnt_qposadr[m.wing_joint[k]]] = (T)row[k];
+        FLY_LANE0 { sint[FLY_SI_WB_STEP] = ws; sint[FLY_SI_WB_FIDX] = fidx; fly_put_double(sint + FLY_SI_WB_FREQ_LO, wb.base_freq); }
+      }
+      FLY_SYNC();
+    }
   } else {
     FLY_FOR(i, FLY_DIM(m, nq)) w.qpos[i] = s_qpos[i];
     FLY_FOR(i, FLY_DIM(m, nv)) { w.qvel[i] = s_qvel[i]; w.warm[i] = s_warm[i]; }
@@ -320,8 +417,8 @@ FLY_FN void fly_env_run(const DModel<T>& m, const Ws<T>& w, const FlyClips& clip
       w.ctrl[a] = v;
     }
     FLY_FOR(k, FLY_DIM(m, nsensordata)) w.sens_sum[k] = 0;
-    if (m.task_type == FLYB_TASK_FLIGHT_IMITATION && wb.nfreq > 0 && m.user_action >= 0) {
-      /* flight_imitation.py:149-159: requested beat frequency from the user action, generator step, and the wing
+    if ((m.task_type == FLYB_TASK_FLIGHT_IMITATION || m.task_type == FLYB_TASK_VISION_FLIGHT) && wb.nfreq > 0 && m.user_action >= 0) {
+      /* flight_imitation.py:149-159, vision_flight.py:148-155: requested beat frequency from the user action, generator step, and the wing
          position targets turned into force commands: action[wings] += target - wing qpos */
       float au = action_in[m.user_action];
       if (au != au) au = 0;
@@ -356,7 +453,10 @@ FLY_FN void fly_env_run(const DModel<T>& m, const Ws<T>& w, const FlyClips& clip
   if (!do_reset) step += 1;  /* tasks/base.py:192 */
   const int nsub = do_reset ? 0 : m.n_substeps;
   for (int it = 0;; it++) {
-    fly_step1(m, w, it == 0 || it < nsub);
+    /* the position stage of the state a control step ends in is the one its successor starts with, so collision, factorisation
+       and constraint rows are left to the successor - except where the task reads the final state's contacts: the vision task
+       ends the episode on an active floor contact (vision_flight.py:214-233) */
+    fly_step1(m, w, it == 0 || it < nsub || m.task_type == FLYB_TASK_VISION_FLIGHT);
     if (it == 0 && io.trace_int) {
       int* ti = io.trace_int + (size_t)env * FLY_TR_INTS;
       FLY_LANE0 ti[FLY_TR_NCON0] = w.counts[FLY_C_NCON];
@@ -378,6 +478,19 @@ FLY_FN void fly_env_run(const DModel<T>& m, const Ws<T>& w, const FlyClips& clip
   int st = 0, fatal = 0;
   T reward = 0, discount = 1;
   fly_write_obs(m, w, clip, step, obs, (do_reset && m.pad_first_obs) ? T(1) : T(1) / T(m.n_substeps));
+  if (m.task_type == FLYB_TASK_VISION_FLIGHT) {
+    if (m.obs_offset[FLYB_OBS_TASK_INPUT] >= 0) FLY_LANE0 {   /* vision_flight.py:243-252 */
+      obs[m.obs_offset[FLYB_OBS_TASK_INPUT]] = (float)v_height; obs[m.obs_offset[FLYB_OBS_TASK_INPUT] + 1] = (float)v_speed;
+    }
+    if (io.eyes) {   /* camera frames of the two eyes for the ray caster (flyb_render): position, row-major orientation */
+      float* eo = io.eyes + (size_t)env * 24;
+      FLY_FOR(k, 24) {
+        const int s = m.eye_site[k / 12], c = k % 12;
+        eo[k] = (float)(c < 3 ? w.site_xpos[3 * s + c] : w.site_xmat[9 * s + c - 3]);
+      }
+      FLY_LANE0 io.eye_terrain[env] = terrain;
+    }
+  }
   if (do_reset) {
     FLY_LANE0 {
       sint[FLY_SI_STEP] = 0; sint[FLY_SI_EPISODE_STEPS] = episode_steps; sint[FLY_SI_RESET_NEXT] = 0;
@@ -434,10 +547,19 @@ FLY_FN void fly_env_run(const DModel<T>& m, const Ws<T>& w, const FlyClips& clip
         const T x = fabs_(w.qvel[m.ball_dofadr + k] - tgt[k]) / T(6);
         r *= x < 1 ? 1 - x : T(0);
       }
+    } else if (m.task_type == FLYB_TASK_VISION_FLIGHT) {  /* vision_flight.py:214-233: an active contact with a world geom is fatal */
+      int touch = 0;
+      FLY_FOR(ci, w.counts[FLY_C_NCON]) {
+        const int pg = m.pair_geom[w.con_pair[ci]];
+        if (w.con_efc[ci] >= 0 && (m.geom_bodyid[pg & 255] == 0 || m.geom_bodyid[(pg >> 8) & 255] == 0)) touch = 1;
+      }
+      if (warp_sum_i(touch) > 0) fatal = 1;
+      r = fly_vision_reward(m, w, terrain, v_height, v_speed);
     }
     reward = r;
     const int terminate = fatal || reached_end;
-    discount = (m.task_type == FLYB_TASK_WALK_ON_BALL) ? (terminate ? T(0) : T(1)) : ((terminate && !reached_end) ? T(0) : T(1));
+    discount = (m.task_type == FLYB_TASK_WALK_ON_BALL || m.task_type == FLYB_TASK_VISION_FLIGHT) ? (terminate ? T(0) : T(1))
+                                                                                               : ((terminate && !reached_end) ? T(0) : T(1));
     st = (terminate || step >= m.time_limit_steps) ? 2 : 1;
     FLY_SYNC();
     FLY_LANE0 {

@@ -74,4 +74,26 @@ FLY_INL int fly_hfield_narrow(const FlyHfield& hf, int type, const double* c2, c
   }
   return ncon;
 }
+
+/* the height-field pair of the step kernel's narrow phase (fly_col.cuh): geom (type t2, pose c2 / m2, size s2) against the
+ * terrain this env flies over - w.counts[FLY_C_TERRAIN] of the pool m.hf_pool; out: dist, pos(3), normal(3) per contact */
+template <class T>
+FLY_INL int fly_hfield_pair(const DModel<T>& m, const Ws<T>& w, const T* c2, const T* m2, const T* s2, int t2, double margin,
+                            double* out) {
+  if (!m.hf_pool) return 0;
+  FlyHfield hf;
+  hf.data = m.hf_pool + (size_t)w.counts[FLY_C_TERRAIN] * m.hfield_nrow * m.hfield_ncol;
+  hf.nrow = m.hfield_nrow; hf.ncol = m.hfield_ncol;
+  const int g = m.hfield_geom;
+  for (int k = 0; k < 3; k++) hf.pos[k] = (double)w.geom_xpos[3 * g + k];
+  T hm[9];
+  fly_geom_xmat(m, w, g, hm);
+  for (int k = 0; k < 9; k++) hf.mat[k] = (double)hm[k];
+  for (int k = 0; k < 4; k++) hf.size[k] = m.hfield_size[k];
+  double c[3], mm[9], sz[3];
+  for (int k = 0; k < 3; k++) { c[k] = (double)c2[k]; sz[k] = (double)s2[k]; }
+  for (int k = 0; k < 9; k++) mm[k] = (double)m2[k];
+  const Portal<double> P = {(double*)w.efc_A + FLY_LANE()};
+  return fly_hfield_narrow(hf, t2, c, mm, sz, margin, FLY_MAXHFCON, out, P);
+}
 #endif

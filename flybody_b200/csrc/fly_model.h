@@ -81,6 +81,14 @@ struct DModel {
   int root_body, root_qposadr, root_dofadr, ghost_qposadr, ghost_dofadr, ghost_body, ball_dofadr, thorax_site;
   int n_obs_joints, n_appendages, n_mocap_joints, n_mocap_sites, user_action, pad_first_obs, inference_mode;
   int clip_width;
+  /* vision-guided flight: the terrain geom (nhfield 0 / 1), its grid, the eye sites; the terrain pool in HBM is attached by the
+     host after build_dmodel (plain device pointers, not part of the arena) */
+  int nhfield, hfield_geom, hfield_nrow, hfield_ncol, eye_site[2], nterrain, trench_stride;
+  double hfield_size[4];
+  T vision_init_quat[4], vision_target_zaxis[3], vision_ranges[8];
+  const float* hf_pool;        /* [nterrain, hfield_nrow, hfield_ncol] heights */
+  const double* trench_meta;   /* [nterrain, 3]: points of the centre line (0: no trench), x of the first, x of the last */
+  const float* trench_y;       /* [nterrain, trench_stride] centre line y */
   T timestep, density, viscosity, tolerance, ls_tolerance, noslip_tolerance, impratio, meaninertia;
   T control_dt, terminal_linvel, terminal_angvel, terminal_com_dist, terminal_qacc, terminal_height;
 #define X(n) const int* n;
@@ -119,6 +127,7 @@ std::string build_dmodel(const FlybModel* m, int flags, DModel<T>* out, FlyArena
   DModel<T>& d = *out;
   memset(&d, 0, sizeof(d));
 #define CP(n) d.n = m->n;
+#define CP2(n) d.n = m->n;
   CP(nq) CP(nv) CP(nu) CP(na) CP(nbody) CP(njnt) CP(ngeom) CP(npair) CP(nsite) CP(ntendon) CP(nwrap) CP(nsensor)
   CP(nsensordata) CP(nfluidbox) CP(nfluidgeom) CP(opt_iterations) CP(opt_ls_iterations) CP(opt_noslip_iterations)
   CP(task_type) CP(n_substeps) CP(future_steps) CP(action_dim) CP(obs_dim) CP(max_episode_steps) CP(time_limit_steps)
@@ -127,6 +136,12 @@ std::string build_dmodel(const FlybModel* m, int flags, DModel<T>* out, FlyArena
   CP(inference_mode)
 #undef CP
   d.flags = flags;
+  CP2(hfield_geom) CP2(hfield_nrow) CP2(hfield_ncol)
+  d.nhfield = m->hfield_geom >= 0 ? 1 : 0;
+  d.eye_site[0] = m->eye_site[0]; d.eye_site[1] = m->eye_site[1];
+  for (int k = 0; k < 4; k++) { d.hfield_size[k] = m->hfield_size[k]; d.vision_init_quat[k] = (T)m->vision_init_quat[k]; }
+  for (int k = 0; k < 3; k++) d.vision_target_zaxis[k] = (T)m->vision_target_zaxis[k];
+  for (int k = 0; k < 8; k++) d.vision_ranges[k] = (T)m->vision_ranges[k];
   d.ghost_body = -1;
   for (int j = 0; j < m->njnt; j++) if (m->ghost_qposadr >= 0 && m->jnt_qposadr[j] == m->ghost_qposadr) d.ghost_body = m->jnt_bodyid[j];
   d.timestep = (T)m->opt_timestep; d.density = (T)m->opt_density; d.viscosity = (T)m->opt_viscosity;
@@ -334,8 +349,10 @@ std::string build_dmodel(const FlybModel* m, int flags, DModel<T>* out, FlyArena
   std::vector<double> pair_bound(m->npair), geom_mat(9 * (size_t)m->ngeom), site_mat(9 * (size_t)m->nsite);
   for (int p = 0; p < m->npair; p++) {
     int g1 = m->pair_geom1[p], g2 = m->pair_geom2[p];
-    pair_geom[p] = g1 | (g2 << 8) | (m->geom_type[g1] == FLYB_GEOM_PLANE ? 1 << 16 : 0);  /* bit 16: geom 1 is a plane */
-    if (m->geom_type[g2] == FLYB_GEOM_PLANE) return "plane must be geom1 of a pair";
+    /* bit 16: geom 1 is a plane; bit 17: geom 1 is the height field (its narrow phase does the bounds test) */
+    pair_geom[p] = g1 | (g2 << 8) | (m->geom_type[g1] == FLYB_GEOM_PLANE ? 1 << 16 : 0) | (m->geom_type[g1] == FLYB_GEOM_HFIELD ? 1 << 17 : 0);
+    if (m->geom_type[g2] == FLYB_GEOM_PLANE || m->geom_type[g2] == FLYB_GEOM_HFIELD) return "plane / height field must be geom1 of a pair";
+    if (m->geom_type[g1] == FLYB_GEOM_HFIELD && g1 != m->hfield_geom) return "one height field per model";
     pair_bound[p] = (m->geom_type[g1] == FLYB_GEOM_PLANE ? 0.0 : m->geom_rbound[g1]) + m->geom_rbound[g2] + m->pair_margin[p];
   }
   for (int g = 0; g < m->ngeom; g++) fly_quat2mat(m->geom_quat + 4 * g, geom_mat.data() + 9 * g);

@@ -74,7 +74,7 @@
 
 /* indices into counts[] */
 enum { FLY_C_NCON = 0, FLY_C_NEFC, FLY_C_NLIMIT, FLY_C_NGRP, FLY_C_NCAND, FLY_C_NITER, FLY_C_OVERFLOW, FLY_C_NCROSS,
-       FLY_C_NFR, FLY_C_NCROSSROW, FLY_C_WORK };
+       FLY_C_NFR, FLY_C_NCROSSROW, FLY_C_WORK, FLY_C_TERRAIN /* index of the env's terrain in the pool */ };
 
 /* Arrays that only live inside one stage share storage with arrays of another stage (the bulk footprint of all
  * resident warps has to fit in L2):  crb (CRB pass of step1, 10 per body) lies over cacc + cfrc_int (6 + 6 per body),
@@ -175,16 +175,17 @@ inline void ws_layout(const DModel<T>& m, int level, WsOff* o, size_t* fast_byte
 struct WsDims {
   int nq, nv, na, nu, nbody, njnt, ngeom, nsite, nM, nsensordata, nfluidbox, nfluidgeom;  /* the layout depends on these */
   int npair, nsensor, ntrunk, gsteps, nlevel;  /* further loop bounds the per-model kernels read as constants (FLY_DIM) */
+  int nhfield;                                 /* 1: the model has a height-field terrain (compiles the prism walk in) */
 };
 template <class M> inline WsDims ws_dims_of(const M& m) {
   return WsDims{m.nq, m.nv, m.na, m.nu, m.nbody, m.njnt, m.ngeom, m.nsite, m.nM, m.nsensordata, m.nfluidbox, m.nfluidgeom,
-                m.npair, m.nsensor, m.ntrunk, m.gsteps, m.nlevel};
+                m.npair, m.nsensor, m.ntrunk, m.gsteps, m.nlevel, m.nhfield};
 }
 inline bool ws_dims_equal(const WsDims& a, const WsDims& b) {
   return a.nq == b.nq && a.nv == b.nv && a.na == b.na && a.nu == b.nu && a.nbody == b.nbody && a.njnt == b.njnt &&
          a.ngeom == b.ngeom && a.nsite == b.nsite && a.nM == b.nM && a.nsensordata == b.nsensordata &&
          a.nfluidbox == b.nfluidbox && a.nfluidgeom == b.nfluidgeom && a.npair == b.npair && a.nsensor == b.nsensor &&
-         a.ntrunk == b.ntrunk && a.gsteps == b.gsteps && a.nlevel == b.nlevel;
+         a.ntrunk == b.ntrunk && a.gsteps == b.gsteps && a.nlevel == b.nlevel && a.nhfield == b.nhfield;
 }
 template <class T>
 FLY_HD constexpr WsOff ws_layout_c(const WsDims m, int level, int nl = 32) {

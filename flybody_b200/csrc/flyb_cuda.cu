@@ -31,6 +31,9 @@ struct FlybEngine {
   float* d_clip_rows = nullptr; int* d_clip_off = nullptr; int* d_clip_len = nullptr; int n_clips = 0;
   FlyWbpg wb = {};        /* device pointers; nfreq 0 until flyb_load_wbpg */
   void* d_wbpg = nullptr; double* d_wbpg_phase = nullptr;
+  /* vision_flight: terrain pool, trench centre lines, and the per-env eye camera frames the step kernel leaves for flyb_render */
+  float* d_hf = nullptr; double* d_trench_meta = nullptr; float* d_trench_y = nullptr;
+  float* d_eyes = nullptr; int* d_eye_terrain = nullptr;
   /* staging for the host-pointer API */
   float *h_action = nullptr, *h_obs = nullptr, *h_rd = nullptr; int* h_st = nullptr; unsigned char* h_mask = nullptr;
   float *d_action = nullptr, *d_obs = nullptr, *d_rd = nullptr; int* d_st = nullptr; unsigned char* d_mask = nullptr;
@@ -127,6 +130,18 @@ __global__ void __launch_bounds__(256) fly_eyes_kernel(FlyScene sc, int ncam, co
   const int cam = (int)(p / ((size_t)W * H)), i = (int)((p / W) % H), j = (int)(p % W);
   const float* c = cams + 12 * (size_t)cam;
   const float* h = sc.data + (size_t)terrain_id[cam] * sc.nrow * sc.ncol;
+  eye_pixel<float>(sc, h, c, c + 3, W, H, tanhalf, i, j, out + 3 * p);
+}
+
+/* the same for the eyes of a handle's envs (flyb_render): camera 2 e + k is eye k of env e, flying over terrain terrain_id[e] */
+__global__ void __launch_bounds__(256) fly_eyes_env_kernel(FlyScene sc, int ncam, const int* __restrict__ terrain_id,
+                                                            const float* __restrict__ cams, int W, int H, float tanhalf,
+                                                            unsigned char* __restrict__ out) {
+  const size_t p = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= (size_t)ncam * W * H) return;
+  const int cam = (int)(p / ((size_t)W * H)), i = (int)((p / W) % H), j = (int)(p % W);
+  const float* c = cams + 12 * (size_t)cam;
+  const float* h = sc.data + (size_t)terrain_id[cam >> 1] * sc.nrow * sc.ncol;
   eye_pixel<float>(sc, h, c, c + 3, W, H, tanhalf, i, j, out + 3 * p);
 }
 
@@ -239,6 +254,7 @@ static FlyIO<float> make_io(FlybEngine* h, const float* action, float* obs, floa
   io.trace_int = h->d_trace_int; io.trace_real = h->d_trace_real; io.trace_real_stride = h->trace_real_stride;
   io.stats = h->d_stats; io.seed = h->seed; io.env_offset = h->env_offset;
   io.wbpg_phase = h->d_wbpg_phase;
+  io.eyes = h->d_eyes; io.eye_terrain = h->d_eye_terrain;
   return io;
 }
 
@@ -340,6 +356,7 @@ void flyb_destroy(flyb_handle h) {
   cudaFree(h->d_arena); cudaFree(h->d_sreal); cudaFree(h->d_sint); cudaFree(h->d_stats); cudaFree(h->d_trace_int);
   cudaFree(h->d_trace_real); cudaFree(h->d_bulk); cudaFree(h->d_counter); cudaFree(h->d_work); cudaFree(h->d_perm); cudaFree(h->d_clip_rows);
   cudaFree(h->d_wbpg); cudaFree(h->d_wbpg_phase);
+  cudaFree(h->d_hf); cudaFree(h->d_trench_meta); cudaFree(h->d_trench_y); cudaFree(h->d_eyes); cudaFree(h->d_eye_terrain);
   cudaFree(h->d_clip_off); cudaFree(h->d_clip_len); cudaFree(h->d_action); cudaFree(h->d_obs); cudaFree(h->d_rd);
   cudaFree(h->d_st); cudaFree(h->d_mask);
   cudaFreeHost(h->h_action); cudaFreeHost(h->h_obs); cudaFreeHost(h->h_rd); cudaFreeHost(h->h_st); cudaFreeHost(h->h_mask);
@@ -408,7 +425,9 @@ int flyb_load_clips(flyb_handle h, const float* rows, const int32_t* offsets, co
 int flyb_load_wbpg(flyb_handle h, const double* beat_freqs, const int32_t* offsets, const double* traj, const double* phase,
                    int n_freqs, double base_freq, double rel_freq_range, double rate, double dt_ctrl) {
   CK(cudaSetDevice(h->device));
-  if (h->m.task_type != FLYB_TASK_FLIGHT_IMITATION) { h->err = "the wing-beat pattern generator belongs to flight_imitation"; return 1; }
+  if (h->m.task_type != FLYB_TASK_FLIGHT_IMITATION && h->m.task_type != FLYB_TASK_VISION_FLIGHT) {
+    h->err = "the wing-beat pattern generator belongs to the flight tasks"; return 1;
+  }
   if (n_freqs <= 0 || offsets[0] != 0) { h->err = "bad wing-beat tables"; return 1; }
   for (int f = 0; f < n_freqs; f++)
     if (offsets[f + 1] - offsets[f] < 2) { h->err = "every wing-beat table needs at least two rows"; return 1; }
@@ -494,6 +513,56 @@ int flyb_hfield_contacts(int device, const float* data, int nrow, int ncol, cons
 #undef CKH
   cudaFree(d_data); cudaFree(d_types); cudaFree(d_geoms); cudaFree(d_out);
   if (e != cudaSuccess) return fail(std::string("flyb_hfield_contacts: ") + cudaGetErrorString(e));
+  return 0;
+}
+
+int flyb_load_terrain(flyb_handle h, const float* heights, int n_terrains, const double* trench_meta, const float* trench_y,
+                      int trench_stride) {
+  CK(cudaSetDevice(h->device));
+  if (h->m.hfield_geom < 0) { h->err = "flyb_load_terrain: the model has no height-field geom (vision_flight only)"; return 1; }
+  if (n_terrains <= 0 || !heights) { h->err = "flyb_load_terrain: no terrains"; return 1; }
+  if ((trench_meta != nullptr) != (trench_y != nullptr) || (trench_meta && trench_stride < 1)) { h->err = "flyb_load_terrain: trench_meta and trench_y go together"; return 1; }
+  if (trench_meta)
+    for (int t = 0; t < n_terrains; t++)
+      if (trench_meta[3 * t] < 0 || trench_meta[3 * t] > trench_stride) { h->err = "flyb_load_terrain: trench centre line longer than trench_stride"; return 1; }
+  cudaFree(h->d_hf); cudaFree(h->d_trench_meta); cudaFree(h->d_trench_y);
+  h->d_hf = nullptr; h->d_trench_meta = nullptr; h->d_trench_y = nullptr;
+  h->m.hf_pool = nullptr; h->m.trench_meta = nullptr; h->m.trench_y = nullptr; h->m.nterrain = 0;
+  const size_t nd = (size_t)n_terrains * h->m.hfield_nrow * h->m.hfield_ncol;
+  CK(cudaMalloc(&h->d_hf, nd * sizeof(float)));
+  CK(cudaMemcpy(h->d_hf, heights, nd * sizeof(float), cudaMemcpyHostToDevice));
+  if (trench_meta) {
+    CK(cudaMalloc(&h->d_trench_meta, (size_t)n_terrains * 3 * sizeof(double)));
+    CK(cudaMalloc(&h->d_trench_y, (size_t)n_terrains * trench_stride * sizeof(float)));
+    CK(cudaMemcpy(h->d_trench_meta, trench_meta, (size_t)n_terrains * 3 * sizeof(double), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(h->d_trench_y, trench_y, (size_t)n_terrains * trench_stride * sizeof(float), cudaMemcpyHostToDevice));
+  }
+  if (!h->d_eyes) {
+    CK(cudaMalloc(&h->d_eyes, (size_t)h->num_envs * 24 * sizeof(float)));
+    CK(cudaMalloc(&h->d_eye_terrain, (size_t)h->num_envs * sizeof(int)));
+    CK(cudaMemset(h->d_eyes, 0, (size_t)h->num_envs * 24 * sizeof(float)));
+    CK(cudaMemset(h->d_eye_terrain, 0, (size_t)h->num_envs * sizeof(int)));
+  }
+  h->m.hf_pool = h->d_hf; h->m.trench_meta = h->d_trench_meta; h->m.trench_y = h->d_trench_y;
+  h->m.nterrain = n_terrains; h->m.trench_stride = trench_stride;
+  return 0;
+}
+
+int flyb_render(flyb_handle h, int width, int height, float fovy_deg, const float* colors8, uint8_t* out, void* stream) {
+  CK(cudaSetDevice(h->device));
+  if (!h->d_hf || !h->d_eyes) { h->err = "flyb_render: no terrain loaded (flyb_load_terrain)"; return 1; }
+  if (width <= 0 || height <= 0 || !out || !colors8) { h->err = "flyb_render: bad arguments"; return 1; }
+  FlyScene sc;
+  sc.data = h->d_hf; sc.nrow = h->m.hfield_nrow; sc.ncol = h->m.hfield_ncol; sc.half = (float)h->m.hfield_size[0];
+  sc.zoff = -0.01f;   /* z of the terrain geom (tasks/arenas/hills.py:190, 215) */
+  for (int k = 0; k < 3; k++) { sc.rgb[k] = colors8[k]; sc.sky[k] = colors8[3 + k]; }
+  sc.ambient = colors8[6]; sc.diffuse = colors8[7];
+  const int ncam = 2 * h->num_envs;
+  const size_t npix = (size_t)ncam * width * height;
+  fly_eyes_env_kernel<<<(unsigned)((npix + 255) / 256), 256, 0, (cudaStream_t)stream>>>(sc, ncam, h->d_eye_terrain, h->d_eyes, width, height,
+                                                                                       tanf(0.5f * fovy_deg * 3.14159265358979f / 180.0f), out);
+  CK(cudaGetLastError());
+  h->launches++;
   return 0;
 }
 

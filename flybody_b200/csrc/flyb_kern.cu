@@ -4,11 +4,11 @@
 #if FLY_TU_SPEC >= 0 && !defined(FLY_NO_CONST_DIMS)
 /* this unit's model: its array sizes as constants (fly_model.h: FLY_DIM) */
 template <int S> struct FlyDimsOf;
-#define X(i, a, b, c, d, e, f, g, h, k, l, p, q, r, s, t, u, v)                                                        \
+#define X(i, a, b, c, d, e, f, g, h, k, l, p, q, r, s, t, u, v, hf)                                                    \
   template <> struct FlyDimsOf<i> {                                                                       \
     static constexpr int nq = a, nv = b, na = c, nu = d, nbody = e, njnt = f, ngeom = g, nsite = h, nM = k, \
                          nsensordata = l, nfluidbox = p, nfluidgeom = q, npair = r, nsensor = s, ntrunk = t,   \
-                         gsteps = u, nlevel = v;                                                          \
+                         gsteps = u, nlevel = v, nhfield = hf;                                            \
   };
 FLY_SPEC_MODELS(X)
 #undef X

@@ -28,11 +28,12 @@ EXPORTS = ["flyb_create", "flyb_destroy", "flyb_last_error", "flyb_info", "flyb_
            "flyb_set_clip_ids", "flyb_reset", "flyb_step", "flyb_reset_host", "flyb_step_host", "flyb_get_state",
            "flyb_set_state", "flyb_get_trace", "flyb_episode_stats", "flyb_load_wbpg", "flyb_set_wbpg_phase",
            "flyb_use_generic_kernel", "flyb_step_noalloc", "flyb_fma_peak", "flyb_hfield_contacts", "flyb_render_eyes",
+           "flyb_load_terrain", "flyb_render",
            "flyb_policy_create", "flyb_policy_destroy", "flyb_policy_last_error", "flyb_policy_launches",
            "flyb_policy_set_weights", "flyb_policy_forward"]
 
 
-N_SPEC_MODELS = 4   # csrc/fly_dims_gen.h: FLY_SPEC_COUNT
+N_SPEC_MODELS = 5   # csrc/fly_dims_gen.h: FLY_SPEC_COUNT
 # Step-kernel instantiations built into the library: (lanes per env, warps per block, shared-memory level, model index or -1 = any
 # model).  Each is a translation unit of its own (csrc/flyb_kern.cu) that registers its kernel when the library is loaded.
 KERNEL_UNITS = ([(32, 28, 0, i) for i in range(N_SPEC_MODELS)]             # the default: one per shipped task model
@@ -123,6 +124,8 @@ def lib():
         L.flyb_episode_stats.argtypes = [vp, dp]
         L.flyb_load_wbpg.argtypes = [vp, dp, ip, dp, dp, c_i, ctypes.c_double, ctypes.c_double, ctypes.c_double, ctypes.c_double]
         L.flyb_set_wbpg_phase.argtypes = [vp, dp]
+        L.flyb_load_terrain.argtypes = [vp, fp, c_i, dp, fp, c_i]
+        L.flyb_render.argtypes = [vp, c_i, c_i, ctypes.c_float, fp, vp, vp]
         L.flyb_policy_create.argtypes = [c_i, c_i, c_i, c_i, ctypes.POINTER(vp)]
         L.flyb_policy_destroy.argtypes = [vp]
         L.flyb_policy_destroy.restype = None
@@ -260,6 +263,20 @@ class Engine:
             p = np.ascontiguousarray(phase, np.float64)
             assert p.shape == (self.num_envs,)
             self._ck(lib().flyb_set_wbpg_phase(self._h, p.ctypes.data_as(ctypes.POINTER(ctypes.c_double))))
+
+    def load_terrain(self, packed):
+        """packed: flybody_b200.terrain.pack_pool(terrain_table(...)) (vision_flight only)."""
+        h, meta, ty = packed["height"], packed["trench_meta"], packed["trench_y"]
+        if h.shape[1:] != (int(self.M["hfield_nrow"]), int(self.M["hfield_ncol"])):
+            raise ValueError(f"terrain grid {h.shape[1:]} does not match the model's height field")
+        self._ck(lib().flyb_load_terrain(self._h, _fp(h), h.shape[0], meta.ctypes.data_as(ctypes.POINTER(ctypes.c_double)) if meta is not None else None,
+                                         _fp(ty) if ty is not None else None, int(packed["trench_stride"])))
+        self.n_terrains = h.shape[0]
+
+    def render_ptr(self, out_ptr, size=32, fovy=150.0, rgb=TERRAIN_RGB, sky=(0.0, 0.0, 0.0), headlight=HEADLIGHT, stream=0):
+        """flyb_render: the eye images of every env after the last reset / step into a device buffer [N, 2, size, size, 3] uint8."""
+        colors = np.ascontiguousarray(list(rgb) + list(sky) + list(headlight), np.float32)
+        self._ck(lib().flyb_render(self._h, int(size), int(size), float(fovy), _fp(colors), out_ptr, stream))
 
     def set_clip_ids(self, ids):
         ids = None if ids is None else np.ascontiguousarray(ids, np.int32)

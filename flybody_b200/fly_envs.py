@@ -49,6 +49,7 @@ def observation_layout(M: dict) -> "collections.OrderedDict[str, tuple[int, tupl
         "ball_qvel": (3,), "force": (3 * int(np.sum(np.asarray(M["sensor_type"]) == 3)),), "gyro": (3,),
         "joints_pos": (int(M["n_obs_joints"]),), "joints_vel": (int(M["n_obs_joints"]),),
         "ref_displacement": (F, 3), "ref_root_quat": (F, 4),
+        "task_input": (2,),
         "touch": (int(np.sum(np.asarray(M["sensor_type"]) == 4)),), "velocimeter": (3,), "world_zaxis": (3,),
     }
     out = collections.OrderedDict()
@@ -64,7 +65,7 @@ class BatchedFlyEnv:
 
     def __init__(self, task: str, model: dict, num_envs: int, device=0, seed: int = 0, env_offset: int = 0,
                  clips=None, trace: bool = False, canonical_actions: bool = False, wbpg=None, action_corruptor=None,
-                 observables_options=None):
+                 observables_options=None, terrain=None, eye_camera_size: int = 32, eye_camera_fovy: float = 150.0):
         import torch
         if not torch.cuda.is_available():
             raise RuntimeError("flybody_b200 needs a CUDA device (there is no CPU fallback)")
@@ -78,6 +79,13 @@ class BatchedFlyEnv:
         if wbpg is not None:
             self.engine.load_wbpg(wbpg)
         N, O, A = self.num_envs, self.engine.obs_dim, self.engine.action_dim
+        # vision_guided_flight: the terrain pool and the two eye images per env (uint8, rendered after every reset / step)
+        self._eyes = None
+        self._seed, self._env_offset = int(seed), int(env_offset)
+        if terrain is not None:
+            self.engine.load_terrain(terrain)
+            self._eye_size, self._eye_fovy = int(eye_camera_size), float(eye_camera_fovy)
+            self._eyes = torch.zeros((N, 2, self._eye_size, self._eye_size, 3), dtype=torch.uint8, device=dev)
         self._obs = torch.zeros((N, O), dtype=torch.float32, device=dev)
         self._reward = torch.zeros(N, dtype=torch.float32, device=dev)
         self._discount = torch.ones(N, dtype=torch.float32, device=dev)
@@ -113,8 +121,13 @@ class BatchedFlyEnv:
     # ---- dm_env API
     def _obs_dict(self):
         N = self.num_envs
-        return collections.OrderedDict(
+        d = collections.OrderedDict(
             (k, self._obs[:, off:off + int(np.prod(shp))].view((N,) + shp)) for k, (off, shp) in self._layout.items())
+        if self._eyes is not None:   # fruitfly.py:676-708: right_eye / left_eye, (size, size, 3) uint8 each
+            self.engine.render_ptr(self._eyes.data_ptr(), self._eye_size, self._eye_fovy, stream=self._stream())
+            d["walker/left_eye"], d["walker/right_eye"] = self._eyes[:, 1], self._eyes[:, 0]
+            d = collections.OrderedDict(sorted(d.items()))
+        return d
 
     def _stream(self):
         return self._torch.cuda.current_stream(self.device).cuda_stream
@@ -152,7 +165,12 @@ class BatchedFlyEnv:
         return BoundedArray((self._A,), np.float32, "action", lo, hi)
 
     def observation_spec(self):
-        return collections.OrderedDict((k, Array(shp, np.float32, k)) for k, (off, shp) in self._layout.items())
+        d = collections.OrderedDict((k, Array(shp, np.float32, k)) for k, (off, shp) in self._layout.items())
+        if self._eyes is not None:
+            for k in ("walker/left_eye", "walker/right_eye"):
+                d[k] = Array((self._eye_size, self._eye_size, 3), np.uint8, k)
+            d = collections.OrderedDict(sorted(d.items()))
+        return d
 
     def reward_spec(self):
         return Array((), np.float32, "reward")
@@ -203,6 +221,17 @@ class BatchedFlyEnv:
         else:
             ids[np.asarray(env, np.int64)] = len(off) - 1
         self.engine.set_clip_ids(ids)
+
+    def vision_targets(self):
+        """(terrain index, target_height, target_speed) of every env's current episode: `task.target_height` / `target_speed`
+        of the reference (tasks/vision_flight.py:235-241), recomputed on the host from the same counter-based draws as the device."""
+        from . import terrain as _terrain
+        if self._eyes is None:
+            raise ValueError("vision_targets belongs to vision_guided_flight")
+        ep = self.engine.get_state()["ints"][:, 4] - 1
+        r = self.M["vision_ranges"]
+        return [_terrain.vision_draws(self._seed, self._env_offset + e, int(max(ep[e], 0)), self.engine.n_terrains, (r[0], r[1]), (r[2], r[3]))
+                for e in range(self.num_envs)]
 
     def episode_stats(self):
         return self.engine.episode_stats()
@@ -277,6 +306,42 @@ def flight_imitation(wpg_pattern_path=None, ref_path=None, random_state=None, te
         raise ValueError("flight_imitation needs reference clips (ref_path), as the reference does")
     return BatchedFlyEnv("flight_imitation", M, num_envs, device, _seed(random_state, seed), clips=clips,
                          wbpg=_wbpg.build_tables(base), **kw)
+
+
+def vision_guided_flight(wpg_pattern_path=None, bumps_or_trench: str = "bumps", random_state=None, num_envs: int = 1, device=0,
+                         seed: int | None = None, n_terrains: int = 16, terrain_seed: int = 0, target_height_range=(0.5, 0.8),
+                         target_speed_range=(20.0, 40.0), init_pos_x_range=(-5.0, -5.0), init_pos_y_range=(0.0, 0.0),
+                         **kwargs_arena) -> BatchedFlyEnv:
+    """Vision-guided flight over `SineBumps` / `SineTrench` terrain (`vnl_ray/fly_envs.py:160-206`, `tasks/vision_flight.py`).
+
+    The reference regenerates its height field on the host at every episode start (`arenas/hills.py:232-258, 328-375, 427-458`);
+    here `n_terrains` terrains are generated once with the reference's draws (`terrain.terrain_table`, `kwargs_arena` = the
+    arena's `dim`, `grid_density` and range arguments) and every (env, episode) flies over one of them.  Observations: the
+    flight observables, `walker/task_input` (target height, target speed) and the two eye cameras `walker/right_eye`,
+    `walker/left_eye` as uint8 [num_envs, 32, 32, 3] tensors, ray-cast on the device (csrc/fly_eyes.cuh says what is drawn).
+    Reward, termination (an active contact with the terrain or the ground plane is fatal) and the wing-beat pattern generator
+    are the reference's; `initialize_qvel` is off as in the reference's constructor.  target_height_range, target_speed_range,
+    init_pos_x_range, init_pos_y_range: the task's constructor arguments (tasks/vision_flight.py:28-31); the start position must
+    be a single point (lo == hi), as it is in the reference's configuration."""
+    from . import terrain as _terrain, wbpg as _wbpg
+    if bumps_or_trench not in ("bumps", "trench"):
+        raise ValueError("Only 'bumps' and 'trench' terrains are supported.")
+    M = load_model(asset_path("vision_flight"))
+    if init_pos_x_range[0] != init_pos_x_range[1] or init_pos_y_range[0] != init_pos_y_range[1]:
+        raise NotImplementedError("vision_guided_flight: init_pos_x_range / init_pos_y_range must be single points (lo == hi)")
+    M["vision_ranges"] = np.array([*target_height_range, *target_speed_range, *init_pos_x_range, *init_pos_y_range], np.float64)
+    dim, density = float(kwargs_arena.get("dim", 20.0)), int(kwargs_arena.get("grid_density", 10))
+    if _terrain.grid_shape(dim, density) != int(M["hfield_nrow"]) or dim != float(M["hfield_size"][0]):
+        raise NotImplementedError("vision_guided_flight: dim / grid_density other than the compiled model's (20, 10) need a recompiled asset")
+    if wpg_pattern_path is None or (isinstance(wpg_pattern_path, str) and wpg_pattern_path == "synthetic"):
+        base = _wbpg.synthetic_base_pattern()
+    elif isinstance(wpg_pattern_path, str):
+        base = np.load(wpg_pattern_path)
+    else:
+        base = np.asarray(wpg_pattern_path)
+    table = _terrain.terrain_table(bumps_or_trench, int(n_terrains), seed=int(terrain_seed), **kwargs_arena)
+    return BatchedFlyEnv("vision_flight", M, num_envs, device, _seed(random_state, seed), wbpg=_wbpg.build_tables(base),
+                         terrain=_terrain.pack_pool(table))
 
 
 class GaussianActionNoise:

@@ -15,11 +15,12 @@ SCALAR_INT = [
     "nsensor", "nsensordata", "nfluidbox", "nfluidgeom",
     "opt_iterations", "opt_ls_iterations", "opt_noslip_iterations",
     # task block
-    "task_type",            # 0 walk_on_ball, 1 walk_imitation, 2 flight_imitation
+    "task_type",            # 0 walk_on_ball, 1 walk_imitation, 2 flight_imitation, 3 template, 4 vision_flight
     "n_substeps", "future_steps", "action_dim", "obs_dim", "max_episode_steps", "time_limit_steps",
     "root_body", "root_qposadr", "root_dofadr", "ghost_qposadr", "ghost_dofadr", "ball_dofadr",
     "thorax_site", "n_obs_joints", "n_appendages", "n_mocap_joints", "n_mocap_sites",
     "user_action", "pad_first_obs", "inference_mode",
+    "hfield_geom", "hfield_nrow", "hfield_ncol",   # vision_flight: the `terrain` geom (-1: none) and its grid
 ]
 
 # scalar double fields
@@ -85,10 +86,15 @@ ARRAYS = [
     ("wing_joint", "i", (6,)), ("wing_action", "i", (6,)),
     ("obs_offset", "i", (16,)),                    # offsets of the observation blocks (OBS_* order), -1 = absent
     ("ghost_offset", "d", (3,)),
+    # vision-guided flight (tasks/vision_flight.py)
+    ("hfield_size", "d", (4,)),                    # x half extent, y half extent, elevation scale, base thickness
+    ("eye_site", "i", (2,)),                       # sites carrying the right / left eye camera frames (-1: none)
+    ("vision_init_quat", "d", (4,)), ("vision_target_zaxis", "d", (3,)),
+    ("vision_ranges", "d", (8,)),                  # target height lo hi, target speed lo hi, init x lo hi, init y lo hi
 ]
 
 # observation blocks, alphabetical by key (`walker/<name>`); index into obs_offset
 OBS_KEYS = [
     "accelerometer", "actuator_activation", "appendages_pos", "ball_qvel", "force", "gyro", "joints_pos",
-    "joints_vel", "ref_displacement", "ref_root_quat", "touch", "velocimeter", "world_zaxis",
+    "joints_vel", "ref_displacement", "ref_root_quat", "task_input", "touch", "velocimeter", "world_zaxis",
 ]

@@ -132,6 +132,22 @@ int flyb_get_trace(flyb_handle h, int32_t* ints, float* reals);
  * must be 0 for the physics to be the reference's); [5] reset passes; [6] control steps; [7] unused. */
 int flyb_episode_stats(flyb_handle h, double* out8);
 
+/* vision_guided_flight (vnl_ray/fly_envs.py:160-206, tasks/vision_flight.py, tasks/arenas/hills.py): the terrain pool of a
+ * handle whose model has a height-field geom.  heights [n_terrains, hfield_nrow, hfield_ncol] float32 (host); for trench
+ * terrains trench_meta [n_terrains, 3] = points of the centre line (0: none), x of its first and of its last point, and
+ * trench_y [n_terrains, trench_stride] its y values (the arena's `trench_specs`, hills.py:377-379); both NULL for bumps.
+ * The reference regenerates its terrain every episode on the host; here every (env, episode) picks one of the pool by a
+ * counter-based hash, the way reference clips are picked.  Collision with the terrain runs inside flyb_step (MuJoCo's
+ * mjc_ConvexHField prism walk, at most 16 contacts per geom); an active contact with the terrain or the ground plane ends
+ * the episode (vision_flight.py:214-233). */
+int flyb_load_terrain(flyb_handle h, const float* heights, int n_terrains, const double* trench_meta, const float* trench_y,
+                      int trench_stride);
+/* The `right_eye` / `left_eye` observables (vnl_ray/fruitfly/fruitfly.py:676-708) of every env after the last flyb_reset /
+ * flyb_step, ray-cast on the device: out [num_envs, 2 (right, left), height, width, 3] uint8 (DEVICE pointer), enqueued on
+ * `stream` (same stream as the step, or ordered after it).  colors8 as flyb_render_eyes.  The reference renders through
+ * MuJoCo's OpenGL renderer (unavailable on this box); what the ray caster draws is stated in csrc/fly_eyes.cuh. */
+int flyb_render(flyb_handle h, int width, int height, float fovy_deg, const float* colors8, uint8_t* out, void* stream);
+
 /* Height field against convex geoms (host pointers; first slice of the terrain of vision_guided_flight, vnl_ray/fly_envs.py:160-206,
  * tasks/arenas/hills.py:160-166, 186-221: the `terrain` hfield geom that MuJoCo collides with the fly through mjc_ConvexHField).
  * data [nrow, ncol] float32 heights (x elevation scale), pose12 = position (3) and row-major orientation (9) of the hfield geom,

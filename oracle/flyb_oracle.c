@@ -45,6 +45,11 @@ struct FlyoEnv {
   FlyoWbpg wb;
   int has_wbpg, wb_step, wb_fidx;
   double wb_freq, init_phase;
+  /* vision-guided flight: the episode's terrain and draws (tasks/vision_flight.py:106-112, arenas/hills.py) */
+  const float* hf_data;
+  int n_trench;
+  const double *trench_x, *trench_y;
+  double target_height, target_speed;
 };
 
 /* ---------------------------------------------------------------- small math */
@@ -834,12 +839,25 @@ static void collision(FlyoEnv* e) {
     if (t1 == FLYB_GEOM_PLANE) {
       double n[3] = {m1[2], m1[5], m1[8]}, d[3] = {c2[0] - c1[0], c2[1] - c1[1], c2[2] - c1[2]};
       if (dot3(d, n) > m->geom_rbound[g2] + margin) continue;
+    } else if (t1 == FLYB_GEOM_HFIELD) {   /* the routine's own bounds test decides */
     } else {
       double d[3] = {c2[0] - c1[0], c2[1] - c1[1], c2[2] - c1[2]}, bound = m->geom_rbound[g1] + m->geom_rbound[g2] + margin;
       if (dot3(d, d) > bound * bound) continue;
     }
-    Hit h[4];
-    const int n = narrow_pair(h, t1, c1, m1, s1, t2, c2, m2, s2, margin);
+    Hit h[FLYO_MAXHFCON];
+    int n;
+    if (t1 == FLYB_GEOM_HFIELD) {
+      /* mjc_ConvexHField keeps up to mjMAXCONPAIR = 50 contacts of one pair; oracle and engine keep FLYO_MAXHFCON = 16
+         (a fly geom of at most 0.1 cm over a 0.1 cm grid touches a handful of prisms; the vision task ends the episode
+         on the first active floor contact, tasks/vision_flight.py:214-232) */
+      double out[7 * FLYO_MAXHFCON];
+      n = e->hf_data ? flyo_narrow_hfield(c1, m1, m->hfield_size, m->hfield_nrow, m->hfield_ncol, e->hf_data, t2, c2, m2, s2,
+                                          margin, FLYO_MAXHFCON, out) : 0;
+      for (int i = 0; i < n; i++) {
+        h[i].dist = out[7 * i]; h[i].has_t = 0;
+        memcpy(h[i].pos, out + 7 * i + 1, 24); memcpy(h[i].n, out + 7 * i + 4, 24);
+      }
+    } else n = narrow_pair(h, t1, c1, m1, s1, t2, c2, m2, s2, margin);
     for (int i = 0; i < n && e->ncon < FLYO_MAXCON; i++) {
       FlyoContact* c = e->con + e->ncon++;
       c->pair = p; c->geom1 = g1; c->geom2 = g2; c->dim = m->pair_condim[p];
@@ -1893,6 +1911,9 @@ static void write_obs(FlyoEnv* e, double* obs, double sensor_scale) {
     obs[off[FLYB_OBS_JOINTS_VEL] + i] = e->qvel[m->obs_joint_dofadr[i]];
   }
   memcpy(obs + off[FLYB_OBS_WORLD_ZAXIS], rm + 6, 3 * sizeof(double));
+  if (off[FLYB_OBS_TASK_INPUT] >= 0) {   /* tasks/vision_flight.py:243-252 */
+    obs[off[FLYB_OBS_TASK_INPUT]] = e->target_height; obs[off[FLYB_OBS_TASK_INPUT] + 1] = e->target_speed;
+  }
   if (off[FLYB_OBS_REF_DISPLACEMENT] >= 0 && e->has_clip) {
     int F = m->future_steps + 1, W = 7 + (m->task_type == FLYB_TASK_WALK_IMITATION ? m->n_mocap_joints : 0);
     const double* rq = e->qpos + m->root_qposadr + 3;
@@ -1966,6 +1987,70 @@ static double flight_imitation_reward(FlyoEnv* e, const double* obs) {
   return r * (th < 1 ? 1 - th : 0.0);
 }
 
+/* ---- vision-guided flight (tasks/vision_flight.py) */
+/* index of the first minimum of |linspace(lo, hi, n) - x| (numpy.argmin of the reference: vision_flight.py:100-101, 181) */
+static int nearest_linspace(double lo, double hi, int n, double x) {
+  const double step = (hi - lo) / (n - 1);
+  int best = 0;
+  double bv = 1e300;
+  for (int i = 0; i < n; i++) {
+    const double a = i == n - 1 ? hi : i * step + lo, d = fabs(a - x);
+    if (d < bv) { bv = d; best = i; }
+  }
+  return best;
+}
+static double hfield_height_at(const FlyoEnv* e, double x, double y) {  /* get_hfield_height, vision_flight.py:92-104 */
+  const FlybModel* m = e->m;
+  if (!e->hf_data) return 0.0;
+  const double half = m->hfield_size[0];
+  const int xi = nearest_linspace(-half, half, m->hfield_ncol, x), yi = nearest_linspace(-half, half, m->hfield_ncol, y);
+  return m->hfield_size[2] * (double)e->hf_data[(size_t)yi * m->hfield_ncol + xi];
+}
+static double tol_linear(double x, double lo, double hi, double margin) {  /* dm_control rewards.tolerance, sigmoid "linear", value_at_margin 0 */
+  if (lo <= x && x <= hi) return 1.0;
+  if (margin == 0) return 0.0;
+  const double d = (x < lo ? lo - x : x - hi) / margin;
+  return fabs(d) < 1 ? 1 - d : 0.0;
+}
+static int vision_floor_contact(const FlyoEnv* e) {  /* check_floor_contact, vision_flight.py:214-227 */
+  const FlybModel* m = e->m;
+  for (int i = 0; i < e->ncon; i++) {
+    const FlyoContact* c = e->con + i;
+    if (c->efc_address < 0) continue;
+    if (m->geom_bodyid[c->geom1] == 0 || m->geom_bodyid[c->geom2] == 0) return 1;
+  }
+  return 0;
+}
+static double vision_reward(FlyoEnv* e) {  /* get_reward_factors, vision_flight.py:157-212 */
+  const FlybModel* m = e->m;
+  const double* xpos = e->qpos + m->root_qposadr;
+  const double* vel = e->qvel + m->root_dofadr;
+  const double height = tol_linear(xpos[2] - hfield_height_at(e, xpos[0], xpos[1]), e->target_height, e->target_height, 0.15);
+  double center = 1.0;
+  if (e->n_trench > 0 && e->trench_x[0] <= xpos[0] && xpos[0] <= e->trench_x[e->n_trench - 1]) {
+    int idx = 0;
+    double bv = 1e300;
+    for (int i = 0; i < e->n_trench; i++) { const double d = fabs(e->trench_x[i] - xpos[0]); if (d < bv) { bv = d; idx = i; } }
+    center = tol_linear(xpos[1], e->trench_y[idx], e->trench_y[idx], 0.15);
+  }
+  const double ts = e->target_speed;
+  const double x_speed = tol_linear(vel[0], ts, INFINITY, 1.1 * ts);
+  const double speed = tol_linear(norm3(vel), ts, ts, 1.1 * ts);
+  double side = 0, zdot = 0;
+  for (int s = 0; s < m->nsensor; s++)
+    if (m->sensor_type[s] == FLYB_SENS_VELOCIMETER) side = e->sensordata[m->sensor_adr[s] + 1];   /* the observable's current value */
+  const double side_speed = tol_linear(side, 0, 0, 10);
+  const double* zax = e->xmat + 9 * m->root_body + 6;   /* world_zaxis observable */
+  for (int k = 0; k < 3; k++) zdot += m->vision_target_zaxis[k] * zax[k];
+  const double world_zaxis = tol_linear(acos(zdot), 0, 0, PI);
+  return height * x_speed * speed * side_speed * world_zaxis * center;
+}
+
+void flyo_set_terrain(FlyoEnv* e, const float* data, int n_trench, const double* trench_x, const double* trench_y) {
+  e->hf_data = data; e->n_trench = n_trench; e->trench_x = trench_x; e->trench_y = trench_y;
+}
+void flyo_set_vision_targets(FlyoEnv* e, double height, double speed) { e->target_height = height; e->target_speed = speed; }
+
 static void set_ghost(FlyoEnv* e, int row, int with_vel) {  /* walk_imitation.py:119-136,138-144 */
   const FlybModel* m = e->m;
   if (m->ghost_qposadr < 0 || !e->has_clip) return;
@@ -2014,6 +2099,19 @@ int flyo_env_reset(FlyoEnv* e, double* obs) {
     }
     memcpy(e->qvel + m->root_dofadr, e->clip.qvel, 3 * sizeof(double));   /* :145-147 linear velocity only */
   }
+  if (m->task_type == FLYB_TASK_VISION_FLIGHT) {   /* vision_flight.py:114-146 */
+    /* init_pos ranges are single points in the reference's configuration (init_pos_x_range (-5, -5), y (0, 0)) */
+    const double x = m->vision_ranges[4], y = m->vision_ranges[6];
+    double* q = e->qpos + m->root_qposadr;
+    q[0] = x; q[1] = y; q[2] = hfield_height_at(e, x, y) + e->target_height;
+    memcpy(q + 3, m->vision_init_quat, 4 * sizeof(double));
+    if (e->has_wbpg) {                               /* :125-126,134: wbpg.reset(initial_phase) -> wing angles only */
+      double ang[6], vel[6];
+      wbpg_reset(e, e->init_phase, ang, vel);
+      for (int k = 0; k < 6; k++) e->qpos[m->jnt_qposadr[m->wing_joint[k]]] = ang[k];
+    }
+    /* initialize_qvel is False (tasks/base.py:51; fly_envs.py:191-200 does not set it): the fly starts at rest */
+  }
   /* dm_control's Physics.after_reset(), reached when composer's _reset_attempt leaves reset_context(), runs mj_forward with
      actuation disabled ("we don't yet have meaningful control inputs"): the affine position servos (biasprm 0 -kp) would
      otherwise pull at the initial pose, and the FIRST observation's accelerometer / force / touch would see it */
@@ -2037,7 +2135,7 @@ int flyo_env_step(FlyoEnv* e, const double* action_in, double* obs, double* rewa
   for (int i = 0; i < m->action_dim; i++) action[i] = isnan(action_in[i]) ? 0.0 : action_in[i];  /* walk_imitation.py:147 */
   int step = e->step_counter;                      /* == round(time / control_dt) before stepping */
   if (m->task_type == FLYB_TASK_WALK_IMITATION) set_ghost(e, step, 1);
-  if (m->task_type == FLYB_TASK_FLIGHT_IMITATION) {  /* flight_imitation.py:149-167 */
+  if (m->task_type == FLYB_TASK_FLIGHT_IMITATION || m->task_type == FLYB_TASK_VISION_FLIGHT) {  /* flight_imitation.py:149-167, vision_flight.py:148-155 */
     if (e->has_wbpg && m->user_action >= 0) {
       double ang[6];
       /* float64, as numpy 1.26.4 (the reference's pin) evaluates base * (1 + rel * act) for a float32 act */
@@ -2086,10 +2184,14 @@ int flyo_env_step(FlyoEnv* e, const double* action_in, double* obs, double* rewa
       double x = fabs(e->qvel[m->ball_dofadr + k] - tgt[k]) / 6.0;
       r *= x < 1 ? 1 - x : 0.0;
     }
+  } else if (m->task_type == FLYB_TASK_VISION_FLIGHT) {  /* vision_flight.py:157-233: floor contacts are fatal */
+    if (vision_floor_contact(e)) fatal = 1;
+    r = vision_reward(e);
   }
   *reward = r;
   int terminate = fatal || reached_end;
-  *discount = (m->task_type == FLYB_TASK_WALK_ON_BALL) ? (terminate ? 0.0 : 1.0) : ((terminate && !reached_end) ? 0.0 : 1.0);
+  *discount = (m->task_type == FLYB_TASK_WALK_ON_BALL || m->task_type == FLYB_TASK_VISION_FLIGHT) ? (terminate ? 0.0 : 1.0)
+                                                                                                  : ((terminate && !reached_end) ? 0.0 : 1.0);
   if (terminate || step >= m->time_limit_steps) { e->reset_next = 1; return 2; }
   return 1;
 }

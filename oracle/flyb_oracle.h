@@ -22,6 +22,7 @@ extern "C" {
 #endif
 
 #define FLYO_MAXCON 160
+#define FLYO_MAXHFCON 16   /* contacts kept per geom - height field pair */
 #define FLYO_MAXEFC 480
 
 typedef struct FlyoContact {
@@ -73,6 +74,9 @@ void flyo_set_clip(FlyoEnv* e, const FlyoClip* clip);
 void flyo_set_wbpg(FlyoEnv* e, const FlyoWbpg* w);   /* flight_imitation only */
 void flyo_set_initial_phase(FlyoEnv* e, double phase); /* WBPG phase drawn at the next reset (random_state.uniform()) */
 void flyo_wbpg_state(const FlyoEnv* e, int* step, int* freq_idx, double* ctrl_freq);
+/* vision_flight: the episode's terrain ([hfield_nrow, hfield_ncol] heights; trench centre line or n_trench = 0) and draws */
+void flyo_set_terrain(FlyoEnv* e, const float* data, int n_trench, const double* trench_x, const double* trench_y);
+void flyo_set_vision_targets(FlyoEnv* e, double height, double speed);
 int flyo_env_reset(FlyoEnv* e, double* obs);         /* returns step_type (0 = FIRST) */
 int flyo_env_step(FlyoEnv* e, const double* action, double* obs, double* reward, double* discount);
 

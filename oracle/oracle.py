@@ -72,6 +72,8 @@ def lib():
         L.flyo_narrow_hfield.argtypes = [dp, dp, dp, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_float), ctypes.c_int, dp, dp, dp,
                                          ctypes.c_double, ctypes.c_int, dp]
         L.flyo_narrow_hfield.restype = ctypes.c_int
+        L.flyo_set_terrain.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_float), ctypes.c_int, dp, dp]
+        L.flyo_set_vision_targets.argtypes = [ctypes.c_void_p, ctypes.c_double, ctypes.c_double]
         L.flyo_quat_op.argtypes = [ctypes.c_int, dp, dp, dp]
         L.flyo_quat_op.restype = ctypes.c_int
         _lib = L
@@ -155,6 +157,18 @@ class OracleEnv:
 
     def set_initial_phase(self, phase):
         lib().flyo_set_initial_phase(self._h, float(phase))
+
+    def set_terrain(self, heights, trench_x=None, trench_y=None):
+        """vision_flight: the episode's height field [nrow, ncol] and, for a trench terrain, its centre line."""
+        dp = ctypes.POINTER(ctypes.c_double)
+        h = np.ascontiguousarray(heights, np.float32)
+        tx = np.ascontiguousarray(trench_x if trench_x is not None else [], np.float64)
+        ty = np.ascontiguousarray(trench_y if trench_y is not None else [], np.float64)
+        self._terrain = (h, tx, ty)
+        lib().flyo_set_terrain(self._h, h.ctypes.data_as(ctypes.POINTER(ctypes.c_float)), len(tx), tx.ctypes.data_as(dp), ty.ctypes.data_as(dp))
+
+    def set_vision_targets(self, height, speed):
+        lib().flyo_set_vision_targets(self._h, float(height), float(speed))
 
     def wbpg_state(self):
         a, b, c = ctypes.c_int(0), ctypes.c_int(0), ctypes.c_double(0)

@@ -16,7 +16,7 @@ def pytest_configure(config):
 def models():
     from flybody_b200.compile_fly import load_model
     from flybody_b200.model_pack import asset_path
-    return {t: load_model(asset_path(t)) for t in ("walk_on_ball", "walk_imitation", "flight_imitation", "template")}
+    return {t: load_model(asset_path(t)) for t in ("walk_on_ball", "walk_imitation", "flight_imitation", "template", "vision_flight")}
 
 
 def clip_arrays(M, rows):

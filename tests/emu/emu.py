@@ -36,6 +36,10 @@ def lib():
         L.emu_set_wbpg.argtypes = [ctypes.c_void_p, dp, ip, dp, dp, ctypes.c_int, dp]
         L.emu_set_phase.argtypes = [ctypes.c_void_p, ctypes.c_double]
         L.emu_wbpg_state.argtypes = [ctypes.c_void_p, ip, ip, dp]
+        L.emu_set_terrain.argtypes = [ctypes.c_void_p, fp, ctypes.c_int, dp, fp, ctypes.c_int]
+        L.emu_set_seed.argtypes = [ctypes.c_void_p, ctypes.c_uint64, ctypes.c_int]
+        L.emu_vision_draws.argtypes = [ctypes.c_void_p, ctypes.c_int, ip, dp, dp]
+        L.emu_eyes.argtypes = [ctypes.c_void_p, fp, ip]
         L.emu_env_reset.argtypes = [ctypes.c_void_p, fp]
         L.emu_env_step.argtypes = [ctypes.c_void_p, fp, fp, dp, dp]
         for fn in ("emu_forward", "emu_physics_step"):
@@ -120,6 +124,27 @@ class EmuEnv:
 
     def set_initial_phase(self, phase):
         lib().emu_set_phase(self._h, float(phase))
+
+    def set_terrain(self, packed):
+        """packed: flybody_b200.terrain.pack_pool(...)"""
+        fp, dp = ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_double)
+        self._terrain = packed
+        h, meta, ty = packed["height"], packed["trench_meta"], packed["trench_y"]
+        lib().emu_set_terrain(self._h, h.ctypes.data_as(fp), h.shape[0], meta.ctypes.data_as(dp) if meta is not None else None,
+                              ty.ctypes.data_as(fp) if ty is not None else None, packed["trench_stride"])
+
+    def set_seed(self, seed, env_offset=0):
+        lib().emu_set_seed(self._h, int(seed), int(env_offset))
+
+    def vision_draws(self, episode):
+        t, h, v = ctypes.c_int(0), ctypes.c_double(0), ctypes.c_double(0)
+        lib().emu_vision_draws(self._h, int(episode), ctypes.byref(t), ctypes.byref(h), ctypes.byref(v))
+        return t.value, h.value, v.value
+
+    def eyes(self):
+        out, t = np.zeros(24, np.float32), ctypes.c_int(0)
+        lib().emu_eyes(self._h, out.ctypes.data_as(ctypes.POINTER(ctypes.c_float)), ctypes.byref(t))
+        return out.reshape(2, 12), t.value
 
     def wbpg_state(self):
         a, b, c = ctypes.c_int(0), ctypes.c_int(0), ctypes.c_double(0)

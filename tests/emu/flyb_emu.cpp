@@ -17,6 +17,10 @@ struct EmuBase {
   virtual void set_clips(const float* data, const int* off, const int* len, int n) = 0;
   virtual void set_wbpg(const double* freqs, const int* off, const double* traj, const double* phase, int nf, const double* prm) = 0;
   virtual void set_phase(double p) = 0;
+  virtual void set_terrain(const float* data, int n, const double* meta, const float* ty, int stride) = 0;
+  virtual void set_seed(unsigned long long seed, int env_offset) = 0;
+  virtual void vision_draws(int episode, int* terrain, double* height, double* speed) = 0;
+  virtual void eyes(float* out24, int* terrain) = 0;
   virtual void wbpg_state(int* step, int* fidx, double* freq) = 0;
   virtual int env_reset(float* obs) = 0;
   virtual int env_step(const float* action, float* obs, double* reward, double* discount) = 0;
@@ -43,6 +47,10 @@ struct Emu : EmuBase {
   std::vector<double> wb_freqs, wb_traj, wb_phase;
   std::vector<int> wb_off;
   double phase0 = 0;
+  std::vector<float> hf, trench_y, eye_out = std::vector<float>(24, 0.f);
+  std::vector<double> trench_meta;
+  unsigned long long seed = 0;
+  int env_offset = 0, eye_terrain = 0;
   std::string err;
 
   Emu(const FlybModel* fm, int flags) {
@@ -77,6 +85,21 @@ struct Emu : EmuBase {
     wb.base_freq = prm[0]; wb.rel_range = prm[1]; wb.rate = prm[2]; wb.dt_ctrl = prm[3];
   }
   void set_phase(double p) override { phase0 = p; }
+  void set_terrain(const float* data, int n, const double* meta, const float* ty, int stride) override {
+    hf.assign(data, data + (size_t)n * m.hfield_nrow * m.hfield_ncol);
+    m.hf_pool = hf.data(); m.nterrain = n; m.trench_meta = 0; m.trench_y = 0; m.trench_stride = stride;
+    if (meta) {
+      trench_meta.assign(meta, meta + 3 * n); trench_y.assign(ty, ty + (size_t)n * stride);
+      m.trench_meta = trench_meta.data(); m.trench_y = trench_y.data();
+    }
+  }
+  void set_seed(unsigned long long s, int off) override { seed = s; env_offset = off; }
+  void vision_draws(int episode, int* terrain, double* height, double* speed) override {
+    T h, v;
+    fly_vision_draws(m, seed, env_offset, episode, terrain, &h, &v);
+    *height = (double)h; *speed = (double)v;
+  }
+  void eyes(float* out24, int* terrain) override { memcpy(out24, eye_out.data(), 24 * sizeof(float)); *terrain = eye_terrain; }
   void wbpg_state(int* step, int* fidx, double* freq) override {
     *step = sint[FLY_SI_WB_STEP]; *fidx = sint[FLY_SI_WB_FIDX]; *freq = fly_get_double(sint.data() + FLY_SI_WB_FREQ_LO);
   }
@@ -86,6 +109,8 @@ struct Emu : EmuBase {
     o.sreal = sreal.data(); o.sint = sint.data(); o.sreal_stride = (int)sreal.size();
     o.action = action; o.obs = obs; o.reward = rdst; o.discount = rdst + 1; o.step_type = (int*)(rdst + 2);
     o.wbpg_phase = &phase0;
+    o.seed = seed; o.env_offset = env_offset;
+    o.eyes = eye_out.data(); o.eye_terrain = &eye_terrain;
     return o;
   }
   int env_reset(float* obs) override {
@@ -217,6 +242,10 @@ void emu_set_wbpg(void* h, const double* freqs, const int* off, const double* tr
   ((EmuBase*)h)->set_wbpg(freqs, off, traj, phase, nf, prm);
 }
 void emu_set_phase(void* h, double p) { ((EmuBase*)h)->set_phase(p); }
+void emu_set_terrain(void* h, const float* data, int n, const double* meta, const float* ty, int stride) { ((EmuBase*)h)->set_terrain(data, n, meta, ty, stride); }
+void emu_set_seed(void* h, unsigned long long seed, int env_offset) { ((EmuBase*)h)->set_seed(seed, env_offset); }
+void emu_vision_draws(void* h, int episode, int* terrain, double* height, double* speed) { ((EmuBase*)h)->vision_draws(episode, terrain, height, speed); }
+void emu_eyes(void* h, float* out24, int* terrain) { ((EmuBase*)h)->eyes(out24, terrain); }
 void emu_wbpg_state(void* h, int* step, int* fidx, double* freq) { ((EmuBase*)h)->wbpg_state(step, fidx, freq); }
 int emu_env_reset(void* h, float* obs) { return ((EmuBase*)h)->env_reset(obs); }
 int emu_env_step(void* h, const float* a, float* obs, double* r, double* g) { return ((EmuBase*)h)->env_step(a, obs, r, g); }

@@ -111,16 +111,16 @@ def test_generated_model_sizes_match_the_shipped_assets(models):
     fields = re.search(r"X\(index, ([^)]*)\)", text).group(1).replace(" ", "").split(",")
     rows = {m.group(2): [int(x) for x in m.group(1).split(",")[1:]]
             for m in re.finditer(r"X\(([\d, ]+)\) /\* (\w+) \*/", text)}
-    assert set(rows) == {"walk_imitation", "walk_on_ball", "template", "flight_imitation"}
+    assert set(rows) == {"walk_imitation", "walk_on_ball", "template", "flight_imitation", "vision_flight"}
     for task, vals in rows.items():
         M = models[task]
         e = EmuEnv(M, double=False)
         for k, v in zip(fields, vals):
-            have = int(e.geti(k)[0]) if k in ("nM", "ntrunk", "gsteps", "nlevel") else int(M[k])
+            have = int(e.geti(k)[0]) if k in ("nM", "ntrunk", "gsteps", "nlevel") else (int(M["hfield_geom"] >= 0) if k == "nhfield" else int(M[k]))
             assert have == v, (task, k, have, v)
 
 
-@pytest.mark.parametrize("task", ["walk_on_ball", "walk_imitation", "flight_imitation", "template"])
+@pytest.mark.parametrize("task", ["walk_on_ball", "walk_imitation", "flight_imitation", "template", "vision_flight"])
 def test_shipped_assets_are_what_the_reference_mjcf_compiles_to(task):
     """flybody_b200/assets/<task>.npz must be bit for bit what compile_fly.compile_task makes of the reference's
     vnl_ray/fruitfly/assets/fruitfly.xml (fruitfly.py:115-326 + tasks/base.py surgery restated in compile_fly.py).  Skipped

@@ -8,7 +8,7 @@ from flybody_b200.compile_fly import compile_task, save_model  # noqa: E402
 
 XML = "/root/reference/vnl_ray/fruitfly/assets/fruitfly.xml"
 OUT = os.path.join(os.path.dirname(__file__), "..", "flybody_b200", "assets")
-for task in ("walk_on_ball", "walk_imitation", "flight_imitation", "template"):
+for task in ("walk_on_ball", "walk_imitation", "flight_imitation", "template", "vision_flight"):
     M = compile_task(task, XML)
     save_model(M, os.path.join(OUT, f"{task}.npz"))
     print(task, {k: M[k] for k in ("nq", "nv", "nu", "na", "nbody", "ngeom", "npair", "obs_dim", "action_dim")})
