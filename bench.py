@@ -26,7 +26,9 @@ sys.path.insert(0, ROOT)
 import numpy as np  # noqa: E402
 
 ENVS_PER_GPU = 16384
-ALGO_BYTES = {"walk_imitation": 9984, "walk_on_ball": 4436, "flight_imitation": 1924}   # compulsory fp32 bytes per env-step
+# compulsory fp32 bytes per env-step; vision_flight (8f rank 4, not in the survey's table): state R+W 2 x (43 + 42 +
+# 42 + 8) x 4 = 1 080, action 48, observations 64 x 4 = 256, two 32 x 32 x 3 uint8 eye images 6 144, reward / discount / type 12
+ALGO_BYTES = {"walk_imitation": 9984, "walk_on_ball": 4436, "flight_imitation": 1924, "vision_flight": 7540}
 METRIC = "fly env-steps/s (walk_imitation, 16384 envs per GPU, synthetic clips, random actions)"
 
 
@@ -167,7 +169,7 @@ def run_reference(args):
     })
 
 
-def _time_steps(torch, eng, dev, acts, steps, warm, flush, out):
+def _time_steps(torch, eng, dev, acts, steps, warm, flush, out, eyes=None):
     """`steps` control steps timed with CUDA events on the launching stream after `warm` untimed ones, L2 flushed in between;
     returns ms per step (list)."""
     obs, rew, disc, st = out
@@ -181,6 +183,8 @@ def _time_steps(torch, eng, dev, acts, steps, warm, flush, out):
         a = acts(warm + k)
         ev[k][0].record()
         eng.step_ptr(a.data_ptr(), obs.data_ptr(), rew.data_ptr(), disc.data_ptr(), st.data_ptr(), stream)
+        if eyes is not None:
+            eng.render_ptr(eyes.data_ptr(), stream=stream)
         ev[k][1].record()
     torch.cuda.synchronize(dev)
     return [a.elapsed_time(b) for a, b in ev]
@@ -196,9 +200,16 @@ def _other_task(torch, task, N, dev, local, flush, peak, steps=10, warm=5):
     M = load_model(asset_path(task))
     eng = Engine(M, N, local, seed=1)
     scale = 1.0
+    eyes = None
     if task == "flight_imitation":
         eng.load_clips(*C.synthetic_flight_table(M, 64, 3006, 0))
         eng.load_wbpg(W.build_tables(W.synthetic_base_pattern()))
+        scale = 0.3
+    if task == "vision_flight":   # 16 trench terrains; the eye images are rendered inside the timed region (flyb_render)
+        from flybody_b200 import terrain as T
+        eng.load_wbpg(W.build_tables(W.synthetic_base_pattern()))
+        eng.load_terrain(T.pack_pool(T.terrain_table("trench", 16, seed=0)))
+        eyes = torch.zeros((N, 2, 32, 32, 3), dtype=torch.uint8, device=dev)
         scale = 0.3
     A, O = eng.action_dim, eng.obs_dim
     out = (torch.zeros((N, O), device=dev), torch.zeros(N, device=dev), torch.zeros(N, device=dev),
@@ -208,7 +219,7 @@ def _other_task(torch, task, N, dev, local, flush, peak, steps=10, warm=5):
     gen = torch.Generator(device=dev); gen.manual_seed(99)
     pool = [scale * (amin + torch.rand((N, A), device=dev, generator=gen) * (amax - amin)) for _ in range(8)]
     eng.reset_ptr(0, out[0].data_ptr(), out[3].data_ptr(), torch.cuda.current_stream(dev).cuda_stream)
-    ms = _time_steps(torch, eng, dev, lambda k: pool[k % 8], steps, warm, flush, out)
+    ms = _time_steps(torch, eng, dev, lambda k: pool[k % 8], steps, warm, flush, out, eyes)
     stats = eng.episode_stats()
     eng.close()
     t = float(np.mean(ms)) * 1e-3
@@ -396,7 +407,7 @@ def run_gpu(args):
                                       "frac": ALGO_BYTES["walk_imitation"] * N / tt / 1e9 / peak0}
         del rows_t
         extras["actor_loop"] = _actor_loop(torch, eng, N, dev, flush, (obs, rew, disc, st), amin, amax, total_ms / args.steps)
-        for task in ("flight_imitation", "walk_on_ball"):
+        for task in ("flight_imitation", "walk_on_ball", "vision_flight"):
             extras[task] = _other_task(torch, task, N, dev, local, flush, peak0)
         extras["fma_peak_tflops"] = fma_peak_tflops(local)
     if rank == 0:

@@ -25,7 +25,14 @@ struct FlyScene {
   float zoff;             /* z of the hfield geom (-0.01) */
   float rgb[3], sky[3];   /* terrain / ground colour, background */
   float ambient, diffuse; /* headlight */
+  /* nullable: per terrain, the largest surface height over each block of FLY_EYE_BLOCK x FLY_EYE_BLOCK cells
+     [nterrain, nbr, nbc] - cells of a block the ray stays above are stepped over without reading their heights */
+  const float* bmax;      /* per terrain: [nbr, nbc] maxima of the 16 x 16 blocks, then [nbr2, nbc2] of the 4 x 4 blocks */
+  int nbr, nbc, nbr2, nbc2;
 };
+#define FLY_EYE_SHIFT 4
+#define FLY_EYE_SHIFT2 2
+#define FLY_EYE_BLOCK (1 << FLY_EYE_SHIFT)
 
 template <class R> FLY_INL R eye_height(const float* h, int ncol, int r, int c, R zoff) {
   const R z = (R)h[(size_t)r * ncol + c] + zoff;
@@ -53,7 +60,8 @@ template <class R> FLY_INL R eye_tri(const R* o, const R* d, const R* a, const R
 }
 
 /* colour of the ray (o, d) in 0..1; fwd: the camera's viewing direction (headlight) */
-template <class R> FLY_INL void eye_trace(const FlyScene& sc, const float* h, const R* o, const R* d, const R* fwd, R* rgb) {
+template <class R> FLY_INL void eye_trace(const FlyScene& sc, const float* h, const R* o, const R* d, const R* fwd, R* rgb,
+                                          const float* bmax = nullptr) {
   const R half = sc.half, cell = 2 * half / (sc.ncol - 1);
   for (int k = 0; k < 3; k++) rgb[k] = sc.sky[k];
   /* clip the ray to the slab |x| <= half, |y| <= half */
@@ -77,7 +85,53 @@ template <class R> FLY_INL void eye_trace(const FlyScene& sc, const float* h, co
   R ty = d[1] != 0 ? ((-half + (r + (sr_ > 0 ? 1 : 0)) * cell) - o[1]) / d[1] : big;
   const R dtx = d[0] != 0 ? cell / (d[0] > 0 ? d[0] : -d[0]) : big, dty = d[1] != 0 ? cell / (d[1] > 0 ? d[1] : -d[1]) : big;
   R tin = t0;
+  const R idx = d[0] != 0 ? 1 / d[0] : big, idy = d[1] != 0 ? 1 / d[1] : big;
+  int blk[2][2] = {{-1, -1}, {-1, -1}};   /* per level: the block found NOT skippable last (its sub-blocks / cells are walked) */
   for (int step = 0; step < 2 * (sc.nrow + sc.ncol); step++) {
+    if (bmax) {
+      /* empty-space skipping, two levels (blocks of 16 x 16 cells, then of 4 x 4): if the ray stays above the highest point of a
+         block until it leaves the block, no cell of the block can pass the height test below, and the walk resumes in the first
+         cell behind the block's far edge */
+      bool jumped = false;
+#pragma unroll
+      for (int lv = 0; lv < 2; lv++) {
+        const int S = lv == 0 ? FLY_EYE_SHIFT : FLY_EYE_SHIFT2;
+        const int br = r >> S, bc = c >> S;
+        if (br == blk[lv][0] && bc == blk[lv][1]) continue;
+        const float* tbl = lv == 0 ? bmax : bmax + sc.nbr * sc.nbc;
+        const int nbc = lv == 0 ? sc.nbc : sc.nbc2;
+        const int ce = sc_ > 0 ? ((bc + 1) << S) : (bc << S);   /* grid line of the far edge */
+        const int re = sr_ > 0 ? ((br + 1) << S) : (br << S);
+        const R txe = d[0] != 0 ? ((-half + (R)ce * cell) - o[0]) * idx : big;
+        const R tye = d[1] != 0 ? ((-half + (R)re * cell) - o[1]) * idy : big;
+        const R te = txe < tye ? txe : tye;
+        const R tz = (te < t1 ? te : t1) * (1 + R(1e-5)) + R(1e-5);
+        const R za = o[2] + tin * d[2], zb = o[2] + tz * d[2];
+        if (!((za < zb ? za : zb) > (R)tbl[br * nbc + bc] + R(1e-4))) { blk[lv][0] = br; blk[lv][1] = bc; continue; }
+        if (te >= t1) return;
+        if (txe < tye) {   /* leaves through a column line: the row follows from y there, kept inside the block's rows */
+          c = sc_ > 0 ? ce : ce - 1;
+          if (c < 0 || c > sc.ncol - 2) return;
+          int rr = (int)floor((o[1] + te * d[1] + half) / cell);
+          const int rlo = br << S, rhi = ((br + 1) << S) - 1;
+          rr = rr < rlo ? rlo : (rr > rhi ? rhi : rr);
+          r = rr > sc.nrow - 2 ? sc.nrow - 2 : rr;
+        } else {
+          r = sr_ > 0 ? re : re - 1;
+          if (r < 0 || r > sc.nrow - 2) return;
+          int cc = (int)floor((o[0] + te * d[0] + half) / cell);
+          const int clo = bc << S, chi = ((bc + 1) << S) - 1;
+          cc = cc < clo ? clo : (cc > chi ? chi : cc);
+          c = cc > sc.ncol - 2 ? sc.ncol - 2 : cc;
+        }
+        tin = te;
+        tx = d[0] != 0 ? ((-half + (c + (sc_ > 0 ? 1 : 0)) * cell) - o[0]) / d[0] : big;
+        ty = d[1] != 0 ? ((-half + (r + (sr_ > 0 ? 1 : 0)) * cell) - o[1]) / d[1] : big;
+        jumped = true;
+        break;
+      }
+      if (jumped) continue;
+    }
     const R tout = tx < ty ? tx : ty;
     const R h00 = eye_height<R>(h, sc.ncol, r, c, sc.zoff), h01 = eye_height<R>(h, sc.ncol, r, c + 1, sc.zoff);
     const R h10 = eye_height<R>(h, sc.ncol, r + 1, c, sc.zoff), h11 = eye_height<R>(h, sc.ncol, r + 1, c + 1, sc.zoff);
@@ -109,12 +163,12 @@ template <class R> FLY_INL void eye_trace(const FlyScene& sc, const float* h, co
 
 /* pixel (i, j) of a camera at pos with orientation mat (row-major, columns = camera axes in the world) */
 template <class R> FLY_INL void eye_pixel(const FlyScene& sc, const float* h, const R* pos, const R* mat, int W, int H, R tanhalf, int i, int j,
-                                          unsigned char* out) {
+                                          unsigned char* out, const float* bmax = nullptr) {
   const R dc[3] = {tanhalf * ((R)W / (R)H) * (2 * ((R)j + R(0.5)) / (R)W - 1), tanhalf * (1 - 2 * ((R)i + R(0.5)) / (R)H), R(-1)};
   R d[3], fwd[3] = {-mat[2], -mat[5], -mat[8]}, rgb[3];
   mat_vec(d, mat, dc);
   normalize3(d);
-  eye_trace<R>(sc, h, pos, d, fwd, rgb);
+  eye_trace<R>(sc, h, pos, d, fwd, rgb, bmax);
   for (int k = 0; k < 3; k++) out[k] = (unsigned char)(int)(rgb[k] * R(255) + R(0.5));
 }
 #endif

@@ -33,7 +33,7 @@ struct FlybEngine {
   void* d_wbpg = nullptr; double* d_wbpg_phase = nullptr;
   /* vision_flight: terrain pool, trench centre lines, and the per-env eye camera frames the step kernel leaves for flyb_render */
   float* d_hf = nullptr; double* d_trench_meta = nullptr; float* d_trench_y = nullptr;
-  float* d_eyes = nullptr; int* d_eye_terrain = nullptr;
+  float* d_eyes = nullptr; int* d_eye_terrain = nullptr; float* d_hf_bmax = nullptr;
   /* staging for the host-pointer API */
   float *h_action = nullptr, *h_obs = nullptr, *h_rd = nullptr; int* h_st = nullptr; unsigned char* h_mask = nullptr;
   float *d_action = nullptr, *d_obs = nullptr, *d_rd = nullptr; int* d_st = nullptr; unsigned char* d_mask = nullptr;
@@ -133,6 +133,19 @@ __global__ void __launch_bounds__(256) fly_eyes_kernel(FlyScene sc, int ncam, co
   eye_pixel<float>(sc, h, c, c + 3, W, H, tanhalf, i, j, out + 3 * p);
 }
 
+/* largest surface height of every FLY_EYE_BLOCK x FLY_EYE_BLOCK block of cells (corner heights as the ray caster reads them) */
+__global__ void fly_eyes_blockmax_kernel(const float* __restrict__ data, int nterrain, int nrow, int ncol, float zoff, int shift, int nbr,
+                                         int nbc, size_t stride, float* __restrict__ bmax) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nterrain * nbr * nbc) return;
+  const int t = i / (nbr * nbc), br = (i / nbc) % nbr, bc = i % nbc, B = 1 << shift;
+  const float* h = data + (size_t)t * nrow * ncol;
+  float mx = 0.f;
+  for (int r = br * B; r <= (br + 1) * B && r < nrow; r++)
+    for (int c = bc * B; c <= (bc + 1) * B && c < ncol; c++) mx = fmaxf(mx, eye_height<float>(h, ncol, r, c, zoff));
+  bmax[(size_t)t * stride + (size_t)br * nbc + bc] = mx;
+}
+
 /* the same for the eyes of a handle's envs (flyb_render): camera 2 e + k is eye k of env e, flying over terrain terrain_id[e] */
 __global__ void __launch_bounds__(256) fly_eyes_env_kernel(FlyScene sc, int ncam, const int* __restrict__ terrain_id,
                                                             const float* __restrict__ cams, int W, int H, float tanhalf,
@@ -141,8 +154,10 @@ __global__ void __launch_bounds__(256) fly_eyes_env_kernel(FlyScene sc, int ncam
   if (p >= (size_t)ncam * W * H) return;
   const int cam = (int)(p / ((size_t)W * H)), i = (int)((p / W) % H), j = (int)(p % W);
   const float* c = cams + 12 * (size_t)cam;
-  const float* h = sc.data + (size_t)terrain_id[cam >> 1] * sc.nrow * sc.ncol;
-  eye_pixel<float>(sc, h, c, c + 3, W, H, tanhalf, i, j, out + 3 * p);
+  const int t = terrain_id[cam >> 1];
+  const float* h = sc.data + (size_t)t * sc.nrow * sc.ncol;
+  eye_pixel<float>(sc, h, c, c + 3, W, H, tanhalf, i, j, out + 3 * p,
+                   sc.bmax ? sc.bmax + (size_t)t * ((size_t)sc.nbr * sc.nbc + (size_t)sc.nbr2 * sc.nbc2) : nullptr);
 }
 
 /* ---- FP32 FMA peak of the device, measured (flyb_fma_peak): every thread runs 16 independent FMA chains; 8 blocks of 256
@@ -356,7 +371,7 @@ void flyb_destroy(flyb_handle h) {
   cudaFree(h->d_arena); cudaFree(h->d_sreal); cudaFree(h->d_sint); cudaFree(h->d_stats); cudaFree(h->d_trace_int);
   cudaFree(h->d_trace_real); cudaFree(h->d_bulk); cudaFree(h->d_counter); cudaFree(h->d_work); cudaFree(h->d_perm); cudaFree(h->d_clip_rows);
   cudaFree(h->d_wbpg); cudaFree(h->d_wbpg_phase);
-  cudaFree(h->d_hf); cudaFree(h->d_trench_meta); cudaFree(h->d_trench_y); cudaFree(h->d_eyes); cudaFree(h->d_eye_terrain);
+  cudaFree(h->d_hf); cudaFree(h->d_trench_meta); cudaFree(h->d_trench_y); cudaFree(h->d_eyes); cudaFree(h->d_eye_terrain); cudaFree(h->d_hf_bmax);
   cudaFree(h->d_clip_off); cudaFree(h->d_clip_len); cudaFree(h->d_action); cudaFree(h->d_obs); cudaFree(h->d_rd);
   cudaFree(h->d_st); cudaFree(h->d_mask);
   cudaFreeHost(h->h_action); cudaFreeHost(h->h_obs); cudaFreeHost(h->h_rd); cudaFreeHost(h->h_st); cudaFreeHost(h->h_mask);
@@ -525,8 +540,8 @@ int flyb_load_terrain(flyb_handle h, const float* heights, int n_terrains, const
   if (trench_meta)
     for (int t = 0; t < n_terrains; t++)
       if (trench_meta[3 * t] < 0 || trench_meta[3 * t] > trench_stride) { h->err = "flyb_load_terrain: trench centre line longer than trench_stride"; return 1; }
-  cudaFree(h->d_hf); cudaFree(h->d_trench_meta); cudaFree(h->d_trench_y);
-  h->d_hf = nullptr; h->d_trench_meta = nullptr; h->d_trench_y = nullptr;
+  cudaFree(h->d_hf); cudaFree(h->d_trench_meta); cudaFree(h->d_trench_y); cudaFree(h->d_hf_bmax);
+  h->d_hf = nullptr; h->d_trench_meta = nullptr; h->d_trench_y = nullptr; h->d_hf_bmax = nullptr;
   h->m.hf_pool = nullptr; h->m.trench_meta = nullptr; h->m.trench_y = nullptr; h->m.nterrain = 0;
   const size_t nd = (size_t)n_terrains * h->m.hfield_nrow * h->m.hfield_ncol;
   CK(cudaMalloc(&h->d_hf, nd * sizeof(float)));
@@ -536,6 +551,19 @@ int flyb_load_terrain(flyb_handle h, const float* heights, int n_terrains, const
     CK(cudaMalloc(&h->d_trench_y, (size_t)n_terrains * trench_stride * sizeof(float)));
     CK(cudaMemcpy(h->d_trench_meta, trench_meta, (size_t)n_terrains * 3 * sizeof(double), cudaMemcpyHostToDevice));
     CK(cudaMemcpy(h->d_trench_y, trench_y, (size_t)n_terrains * trench_stride * sizeof(float), cudaMemcpyHostToDevice));
+  }
+  {  /* block maxima for the eye renderer's empty-space skipping */
+    const int nr = h->m.hfield_nrow - 1, nc = h->m.hfield_ncol - 1;
+    const int nbr = (nr + FLY_EYE_BLOCK - 1) >> FLY_EYE_SHIFT, nbc = (nc + FLY_EYE_BLOCK - 1) >> FLY_EYE_SHIFT;
+    const int nbr2 = (nr + (1 << FLY_EYE_SHIFT2) - 1) >> FLY_EYE_SHIFT2, nbc2 = (nc + (1 << FLY_EYE_SHIFT2) - 1) >> FLY_EYE_SHIFT2;
+    const size_t stride = (size_t)nbr * nbc + (size_t)nbr2 * nbc2;
+    CK(cudaMalloc(&h->d_hf_bmax, (size_t)n_terrains * stride * sizeof(float)));
+    fly_eyes_blockmax_kernel<<<(n_terrains * nbr * nbc + 127) / 128, 128>>>(h->d_hf, n_terrains, h->m.hfield_nrow, h->m.hfield_ncol, -0.01f,
+                                                                          FLY_EYE_SHIFT, nbr, nbc, stride, h->d_hf_bmax);
+    fly_eyes_blockmax_kernel<<<(n_terrains * nbr2 * nbc2 + 127) / 128, 128>>>(h->d_hf, n_terrains, h->m.hfield_nrow, h->m.hfield_ncol, -0.01f,
+                                                                            FLY_EYE_SHIFT2, nbr2, nbc2, stride, h->d_hf_bmax + (size_t)nbr * nbc);
+    CK(cudaGetLastError());
+    CK(cudaDeviceSynchronize());
   }
   if (!h->d_eyes) {
     CK(cudaMalloc(&h->d_eyes, (size_t)h->num_envs * 24 * sizeof(float)));
@@ -555,6 +583,9 @@ int flyb_render(flyb_handle h, int width, int height, float fovy_deg, const floa
   FlyScene sc;
   sc.data = h->d_hf; sc.nrow = h->m.hfield_nrow; sc.ncol = h->m.hfield_ncol; sc.half = (float)h->m.hfield_size[0];
   sc.zoff = -0.01f;   /* z of the terrain geom (tasks/arenas/hills.py:190, 215) */
+  sc.bmax = h->d_hf_bmax;
+  sc.nbr = (h->m.hfield_nrow - 2 + FLY_EYE_BLOCK) >> FLY_EYE_SHIFT; sc.nbc = (h->m.hfield_ncol - 2 + FLY_EYE_BLOCK) >> FLY_EYE_SHIFT;
+  sc.nbr2 = (h->m.hfield_nrow - 2 + (1 << FLY_EYE_SHIFT2)) >> FLY_EYE_SHIFT2; sc.nbc2 = (h->m.hfield_ncol - 2 + (1 << FLY_EYE_SHIFT2)) >> FLY_EYE_SHIFT2;
   for (int k = 0; k < 3; k++) { sc.rgb[k] = colors8[k]; sc.sky[k] = colors8[3 + k]; }
   sc.ambient = colors8[6]; sc.diffuse = colors8[7];
   const int ncam = 2 * h->num_envs;
@@ -589,6 +620,7 @@ int flyb_render_eyes(int device, const float* data, int nterrain, int nrow, int 
     sc.data = d_data; sc.nrow = nrow; sc.ncol = ncol; sc.half = half_extent; sc.zoff = z_offset;
     for (int k = 0; k < 3; k++) { sc.rgb[k] = colors8[k]; sc.sky[k] = colors8[3 + k]; }
     sc.ambient = colors8[6]; sc.diffuse = colors8[7];
+    sc.bmax = nullptr; sc.nbr = sc.nbc = sc.nbr2 = sc.nbc2 = 0;   /* the stand-alone entry point walks every cell (the reference path of the tests) */
     const size_t npix = (size_t)ncam * width * height;
     fly_eyes_kernel<<<(unsigned)((npix + 255) / 256), 256>>>(sc, ncam, d_tid, d_cams, width, height,
                                                             tanf(0.5f * fovy_deg * 3.14159265358979f / 180.0f), d_out);
