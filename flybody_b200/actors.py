@@ -232,11 +232,11 @@ class NStepTransitionAdder:
         D = run[:, -1] / self.gamma                                                # discount^(h-1) * prod d
         return R, D
 
-    def _batch(self, env, start, hor):
+    def _batch(self, env, start, hor, next_obs=None):
         R, D = self._returns(env, start, hor)
         return {"observation": self.obs[env, start % (self.n + 1)], "action": self.act[env, start % self.n], "reward": R,
-                "discount": D, "next_observation": self.obs[env, (start + hor) % (self.n + 1)], "env": env, "start": start,
-                "horizon": hor}
+                "discount": D, "next_observation": self.obs[env, (start + hor) % (self.n + 1)] if next_obs is None else next_obs,
+                "env": env, "start": start, "horizon": hor}
 
     def add(self, action: torch.Tensor, next_timestep):
         """Append (a_t, r_t, d_t, o_{t+1}) for every env that is inside an episode; envs whose `next_timestep` is FIRST
@@ -249,17 +249,18 @@ class NStepTransitionAdder:
         e = self._env
         c = self.count
         slot, oslot = c % self.n, (c + 1) % (self.n + 1)
-        lv = live[:, None]
-        self.act[e, slot] = torch.where(lv, action, self.act[e, slot])
-        self.rew[e, slot] = torch.where(live, next_timestep.reward, self.rew[e, slot])
-        self.disc[e, slot] = torch.where(live, next_timestep.discount, self.disc[e, slot])
-        self.obs[e, oslot] = torch.where(lv, obs, self.obs[e, oslot])
+        # unconditional writes: an env that is not live has count 0 (it was just (re)started, or never started), so these land
+        # in slots 0 / 1, which its first live step overwrites before anything reads them - no gather / select needed
+        self.act[e, slot] = action
+        self.rew[e, slot] = next_timestep.reward
+        self.disc[e, slot] = next_timestep.discount
+        self.obs[e, oslot] = obs
         c = torch.where(live, c + 1, c)
         self.count = c
         # the transition acme writes after every step: from max(0, t - n) over min(t, n) steps (fixed shape, masked)
         start = torch.clamp(c - self.n, min=0)
         hor = torch.clamp(c, max=self.n).clamp(min=1)
-        batch = self._batch(e, start, hor)
+        batch = self._batch(e, start, hor, next_obs=obs)     # the per-step transition ends at the observation just received
         batch["valid"] = live
         self.written += live.sum()
         if self.sink is not None:

@@ -3,11 +3,12 @@
  * The network of vnl_ray/agents/network_factory.py:73-101 (acme LayerNormMLP((512, 512, 512, 512), activate_final=True) ->
  * MultivariateNormalDiagHead):  x = tanh(LayerNorm(W1 obs + b1)); x = elu(Wl x + bl), l = 2..4; mean = Wm x + bm;
  * scale = softplus(Ws x + bs) * init_scale / ln 2 + min_scale; action = mean + scale * eps.
- * For 16 384 envs that is 16 384 x (741 x 512 + 3 x 512^2 + 512 x 118) = 26 GFLOP per control step: the one GEMM-shaped piece of
+ * For 16 384 envs that is 2 x 16 384 x (741 x 512 + 3 x 512^2 + 512 x 118) = 40 GFLOP per control step: the one GEMM-shaped piece of
  * the actor side, so it runs on the 5th-generation tensor cores:
  *
- *   - one CTA per 128 observation rows (UMMA M = 128, cta_group::1), 6 warps: warps 0-3 epilogue (one thread per row = one
- *     TMEM lane), warp 4 TMA producer, warp 5 MMA issuer (one elected thread each);
+ *   - one CTA per 128 observation rows (UMMA M = 128, cta_group::1), 18 warps: warps 0-15 epilogue (a thread per row = TMEM lane
+ *     and quarter of the columns: with 4 warps the epilogue ran at one warp per scheduler and took 85 % of the kernel), warp 16
+ *     TMA producer, warp 17 MMA issuer (one elected thread each);
  *   - the whole 128 x 512 fp32 layer output lives in TMEM (512 columns), written by tcgen05.mma.kind::f16 (bf16 x bf16 -> fp32,
  *     N = 256 per instruction), read back by tcgen05.ld.32x32b for bias + LayerNorm + tanh / ELU;
  *   - activations never leave the SM: the epilogue writes them as bf16 into shared memory in the canonical K-major
@@ -42,7 +43,9 @@ constexpr int PSTAGE_BYTES = PA_BYTES + PB_BYTES;
 constexpr int PACT_BYTES = PM * PH * 2;     /* 128 KB */
 constexpr int PHEAD_N = 128;                /* head output columns: mean at 0.., scale at 64.. */
 constexpr int PSMEM_BYTES = PACT_BYTES + PSTAGES * PSTAGE_BYTES + 1024 /* barriers */ + 1024 /* alignment slack */;
-constexpr int PTHREADS = 192;
+constexpr int PEPI_WARPS = 16;              /* epilogue warps: 4 per quarter of the TMEM lanes, each takes 128 of the 512 columns */
+constexpr int PEPI_THREADS = PEPI_WARPS * 32;
+constexpr int PTHREADS = PEPI_THREADS + 64; /* + TMA producer warp + MMA issuer warp */
 
 struct PolicyParams {
   const float* b1; const float* ln_g; const float* ln_b;
@@ -112,6 +115,14 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float* v) {
 #pragma unroll
   for (int i = 0; i < 32; i++) v[i] = __uint_as_float(r[i]);
 }
+/* activations are rounded to bf16 (8 mantissa bits) right after: the MUFU approximations (tanh.approx, ex2.approx: ~2^-11 relative)
+   are below that rounding */
+__device__ __forceinline__ float fast_tanh(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float fast_elu(float x) { return x > 0.f ? x : __expf(x) - 1.0f; }
 __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
   __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&h);
@@ -149,10 +160,10 @@ fly_policy_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
   if (threadIdx.x == 0) {
     for (int s = 0; s < PSTAGES; s++) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, 1); }
     mbar_init(bar_acc, 1);
-    mbar_init(bar_act, PM);
+    mbar_init(bar_act, PEPI_THREADS);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == 4) {   /* the allocating warp also frees: all 512 columns (one CTA per SM: nothing to contend with) */
+  if (warp == PEPI_WARPS) {   /* the allocating warp also frees: all 512 columns (one CTA per SM: nothing to contend with) */
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
@@ -163,7 +174,7 @@ fly_policy_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
 
   /* the item sequence both pipeline ends walk: layer 0: 2 N-halves x nk1 chunks (A + B tiles); layers 1-3: 2 x 8 (B only, A =
      the activation buffer); layer 4 = the head: 8 chunks of a 128-row B tile */
-  if (warp == 4 && lane == 0) {
+  if (warp == PEPI_WARPS && lane == 0) {
     /* ------------------------------------------------------------------------------------------------ TMA producer */
     const CUtensorMap* wmap[5] = {&map_w1, &map_w2, &map_w3, &map_w4, &map_wh};
     int it = 0;
@@ -180,7 +191,7 @@ fly_policy_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
           tma_load_2d(b_dst, wmap[l], kc * PKC, nh * PNH, bar_full + 8 * s);
         }
     }
-  } else if (warp == 5 && lane == 0) {
+  } else if (warp == PEPI_WARPS + 1 && lane == 0) {
     /* -------------------------------------------------------------------------------------------------- MMA issuer */
     int it = 0;
     for (int l = 0; l < 5; l++) {
@@ -204,67 +215,83 @@ fly_policy_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
         }
       umma_commit(bar_acc);                   /* the layer's accumulator is complete */
     }
-  } else if (warp < 4) {
+  } else if (warp < PEPI_WARPS) {
     /* ---------------------------------------------------------------------------------------------------- epilogue */
-    const int r = warp * 32 + lane;                        /* row of the tile = TMEM lane */
-    const uint32_t trow = tmem + ((uint32_t)(warp * 32) << 16);
+    const int q = warp & 3, cg = warp >> 2;                /* quarter of the TMEM lanes this warp may read; its column group */
+    const int r = q * 32 + lane;                           /* row of the tile = TMEM lane */
+    const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16);
+    const int c0 = cg * (PH / 32 / 4), c1 = c0 + PH / 32 / 4;   /* its chunks of 32 columns */
+    float* red = reinterpret_cast<float*>(act);            /* LayerNorm partial sums [4 column groups][128 rows][2] (act is free then) */
     float v[32];
     for (int l = 0; l < 5; l++) {
       mbar_wait(bar_acc, l & 1);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       if (l == 0) {         /* bias, LayerNorm over the 512 features of the row, tanh */
-        float sum = 0;
-        for (int c = 0; c < PH / 32; c++) {
+        float sum = 0, sq = 0;
+        for (int c = c0; c < c1; c++) {
           tmem_ld32(trow + 32 * c, v);
 #pragma unroll
-          for (int j = 0; j < 32; j++) sum += v[j] + __ldg(p.b1 + 32 * c + j);
+          for (int j4 = 0; j4 < 8; j4++) {
+            const float4 b = __ldg(reinterpret_cast<const float4*>(p.b1 + 32 * c) + j4);
+            const float x0 = v[4 * j4] + b.x, x1 = v[4 * j4 + 1] + b.y, x2 = v[4 * j4 + 2] + b.z, x3 = v[4 * j4 + 3] + b.w;
+            sum += (x0 + x1) + (x2 + x3);
+            sq += (x0 * x0 + x1 * x1) + (x2 * x2 + x3 * x3);
+          }
         }
+        red[(cg * PM + r) * 2] = sum; red[(cg * PM + r) * 2 + 1] = sq;
+        asm volatile("bar.sync 1, %0;" ::"n"(PEPI_THREADS) : "memory");
+        sum = 0; sq = 0;
+#pragma unroll
+        for (int g = 0; g < 4; g++) { sum += red[(g * PM + r) * 2]; sq += red[(g * PM + r) * 2 + 1]; }
+        asm volatile("bar.sync 1, %0;" ::"n"(PEPI_THREADS) : "memory");   /* everyone has read the sums: act may be written */
         const float mu = sum * (1.0f / PH);
-        float sq = 0;
-        for (int c = 0; c < PH / 32; c++) {
+        const float var = fmaxf(sq * (1.0f / PH) - mu * mu, 0.f);
+        const float rstd = rsqrtf(var + p.ln_eps);
+        for (int c = c0; c < c1; c++) {
           tmem_ld32(trow + 32 * c, v);
 #pragma unroll
-          for (int j = 0; j < 32; j++) { const float d = v[j] + __ldg(p.b1 + 32 * c + j) - mu; sq += d * d; }
-        }
-        const float rstd = rsqrtf(sq * (1.0f / PH) + p.ln_eps);
-        for (int c = 0; c < PH / 32; c++) {
-          tmem_ld32(trow + 32 * c, v);
-#pragma unroll
-          for (int j = 0; j < 32; j++) {
-            const int col = 32 * c + j;
-            v[j] = tanhf((v[j] + __ldg(p.b1 + col) - mu) * rstd * __ldg(p.ln_g + col) + __ldg(p.ln_b + col));
+          for (int j4 = 0; j4 < 8; j4++) {
+            const float4 b = __ldg(reinterpret_cast<const float4*>(p.b1 + 32 * c) + j4);
+            const float4 g = __ldg(reinterpret_cast<const float4*>(p.ln_g + 32 * c) + j4);
+            const float4 e = __ldg(reinterpret_cast<const float4*>(p.ln_b + 32 * c) + j4);
+            v[4 * j4 + 0] = fast_tanh((v[4 * j4 + 0] + b.x - mu) * rstd * g.x + e.x);
+            v[4 * j4 + 1] = fast_tanh((v[4 * j4 + 1] + b.y - mu) * rstd * g.y + e.y);
+            v[4 * j4 + 2] = fast_tanh((v[4 * j4 + 2] + b.z - mu) * rstd * g.z + e.z);
+            v[4 * j4 + 3] = fast_tanh((v[4 * j4 + 3] + b.w - mu) * rstd * g.w + e.w);
           }
           store_act32(act, r, c, v);
         }
       } else if (l < 4) {   /* bias, ELU */
-        const float* b = p.b[l - 1];
-        for (int c = 0; c < PH / 32; c++) {
+        const float* bl = p.b[l - 1];
+        for (int c = c0; c < c1; c++) {
           tmem_ld32(trow + 32 * c, v);
 #pragma unroll
-          for (int j = 0; j < 32; j++) { const float x = v[j] + __ldg(b + 32 * c + j); v[j] = x > 0.f ? x : expm1f(x); }
+          for (int j4 = 0; j4 < 8; j4++) {
+            const float4 b = __ldg(reinterpret_cast<const float4*>(bl + 32 * c) + j4);
+            v[4 * j4 + 0] = fast_elu(v[4 * j4 + 0] + b.x); v[4 * j4 + 1] = fast_elu(v[4 * j4 + 1] + b.y);
+            v[4 * j4 + 2] = fast_elu(v[4 * j4 + 2] + b.z); v[4 * j4 + 3] = fast_elu(v[4 * j4 + 3] + b.w);
+          }
           store_act32(act, r, c, v);
         }
-      } else {              /* heads: mean | scale (columns 64..), sampled action */
-        const int row = row0 + r;
+      } else if (cg < 2) {  /* heads: mean | scale (columns 64..), sampled action; two column groups of 32 */
+        const int row = row0 + r, c = cg;
         float s[32];
-        for (int c = 0; c < 2; c++) {
-          tmem_ld32(trow + 32 * c, v);
-          tmem_ld32(trow + 64 + 32 * c, s);
-          if (row < p.n_rows) {
+        tmem_ld32(trow + 32 * c, v);
+        tmem_ld32(trow + 64 + 32 * c, s);
+        if (row < p.n_rows) {
 #pragma unroll
-            for (int j = 0; j < 32; j++) {
-              const int col = 32 * c + j;
-              if (col < p.act_dim) {
-                float mean = v[j] + __ldg(p.bm + col);
-                if (p.tanh_mean) mean = tanhf(mean);
-                const float x = s[j] + __ldg(p.bs + col);
-                const float sp = x > 20.f ? x : log1pf(expf(x));
-                const float scale = sp * p.scale_mul + p.min_scale;
-                const size_t o = (size_t)row * p.act_dim + col;
-                if (p.mean) p.mean[o] = mean;
-                if (p.scale) p.scale[o] = scale;
-                if (p.action) p.action[o] = mean + scale * (p.eps ? p.eps[o] : 0.f);
-              }
+          for (int j = 0; j < 32; j++) {
+            const int col = 32 * c + j;
+            if (col < p.act_dim) {
+              float mean = v[j] + __ldg(p.bm + col);
+              if (p.tanh_mean) mean = tanhf(mean);
+              const float x = s[j] + __ldg(p.bs + col);
+              const float sp = x > 20.f ? x : log1pf(expf(x));
+              const float scale = sp * p.scale_mul + p.min_scale;
+              const size_t o = (size_t)row * p.act_dim + col;
+              if (p.mean) p.mean[o] = mean;
+              if (p.scale) p.scale[o] = scale;
+              if (p.action) p.action[o] = mean + scale * (p.eps ? p.eps[o] : 0.f);
             }
           }
         }
@@ -278,7 +305,7 @@ fly_policy_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
-  if (warp == 4) {
+  if (warp == PEPI_WARPS) {
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512) : "memory");
   }
