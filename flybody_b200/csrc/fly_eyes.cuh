@@ -27,7 +27,7 @@ struct FlyScene {
   float ambient, diffuse; /* headlight */
   /* nullable: per terrain, the largest surface height over each block of FLY_EYE_BLOCK x FLY_EYE_BLOCK cells
      [nterrain, nbr, nbc] - cells of a block the ray stays above are stepped over without reading their heights */
-  const float* bmax;      /* per terrain: [nbr, nbc] maxima of the 16 x 16 blocks, then [nbr2, nbc2] of the 4 x 4 blocks */
+  const float* bmax;      /* per terrain: [nbr, nbc] maxima of the 16 x 16 blocks, [nbr2, nbc2] of the 4 x 4 blocks, the terrain's maximum */
   int nbr, nbc, nbr2, nbc2;
 };
 #define FLY_EYE_SHIFT 4
@@ -59,116 +59,151 @@ template <class R> FLY_INL R eye_tri(const R* o, const R* d, const R* a, const R
   return t;
 }
 
-/* colour of the ray (o, d) in 0..1; fwd: the camera's viewing direction (headlight) */
-template <class R> FLY_INL void eye_trace(const FlyScene& sc, const float* h, const R* o, const R* d, const R* fwd, R* rgb,
-                                          const float* bmax = nullptr) {
-  const R half = sc.half, cell = 2 * half / (sc.ncol - 1);
-  for (int k = 0; k < 3; k++) rgb[k] = sc.sky[k];
-  /* clip the ray to the slab |x| <= half, |y| <= half */
-  R t0 = 0, t1 = R(1e30);
+/* One ray as a state machine: eye_ray_init clips it to the terrain's slab and finds its first cell, eye_ray_step takes one step of
+ * the walk (a jump over a block of cells the ray stays above, or one cell with its height test and two triangles).  eye_trace
+ * loops over the steps; the persistent kernel of flyb_render interleaves the steps of 32 rays per warp and hands a lane its next
+ * ray as soon as its current one ends (rays of one image row take 5 to 200 steps: without that 6 of 32 lanes were busy). */
+template <class R> struct EyeRay {
+  R o[3], d[3], fwd[3];
+  R t1, tin, tx, ty, dtx, dty, idx, idy;
+  int c, r, sc_, sr_, steps;
+  int blk[2][2];   /* per level: the block found NOT skippable last (its sub-blocks / cells are walked) */
+};
+
+/* false: the ray misses the slab |x|, |y| <= half (background) */
+template <class R> FLY_INL bool eye_ray_init(const FlyScene& sc, EyeRay<R>& y) {
+  const R half = sc.half, cell = 2 * half / (sc.ncol - 1), big = R(1e30);
+  const R *o = y.o, *d = y.d;
+  R t0 = 0, t1 = big;
   for (int a = 0; a < 2; a++) {
-    if (d[a] > R(-1e-12) && d[a] < R(1e-12)) { if (o[a] < -half || o[a] > half) return; continue; }
+    if (d[a] > R(-1e-12) && d[a] < R(1e-12)) { if (o[a] < -half || o[a] > half) return false; continue; }
     R ta = (-half - o[a]) / d[a], tb = (half - o[a]) / d[a];
     if (ta > tb) { const R x = ta; ta = tb; tb = x; }
     if (ta > t0) t0 = ta;
     if (tb < t1) t1 = tb;
   }
-  if (t0 >= t1) return;
-  /* cell of the entry point */
-  R px = o[0] + t0 * d[0], py = o[1] + t0 * d[1];
+  if (t0 >= t1) return false;
+  const R px = o[0] + t0 * d[0], py = o[1] + t0 * d[1];
   int c = (int)floor((px + half) / cell), r = (int)floor((py + half) / cell);
   if (c < 0) c = 0; if (c > sc.ncol - 2) c = sc.ncol - 2;
   if (r < 0) r = 0; if (r > sc.nrow - 2) r = sc.nrow - 2;
-  const int sc_ = d[0] > 0 ? 1 : -1, sr_ = d[1] > 0 ? 1 : -1;
-  const R big = R(1e30);
-  R tx = d[0] != 0 ? ((-half + (c + (sc_ > 0 ? 1 : 0)) * cell) - o[0]) / d[0] : big;   /* t of the next column / row boundary */
-  R ty = d[1] != 0 ? ((-half + (r + (sr_ > 0 ? 1 : 0)) * cell) - o[1]) / d[1] : big;
-  const R dtx = d[0] != 0 ? cell / (d[0] > 0 ? d[0] : -d[0]) : big, dty = d[1] != 0 ? cell / (d[1] > 0 ? d[1] : -d[1]) : big;
-  R tin = t0;
-  const R idx = d[0] != 0 ? 1 / d[0] : big, idy = d[1] != 0 ? 1 / d[1] : big;
-  int blk[2][2] = {{-1, -1}, {-1, -1}};   /* per level: the block found NOT skippable last (its sub-blocks / cells are walked) */
-  for (int step = 0; step < 2 * (sc.nrow + sc.ncol); step++) {
-    if (bmax) {
-      /* empty-space skipping, two levels (blocks of 16 x 16 cells, then of 4 x 4): if the ray stays above the highest point of a
-         block until it leaves the block, no cell of the block can pass the height test below, and the walk resumes in the first
-         cell behind the block's far edge */
-      bool jumped = false;
-#pragma unroll
-      for (int lv = 0; lv < 2; lv++) {
-        const int S = lv == 0 ? FLY_EYE_SHIFT : FLY_EYE_SHIFT2;
-        const int br = r >> S, bc = c >> S;
-        if (br == blk[lv][0] && bc == blk[lv][1]) continue;
-        const float* tbl = lv == 0 ? bmax : bmax + sc.nbr * sc.nbc;
-        const int nbc = lv == 0 ? sc.nbc : sc.nbc2;
-        const int ce = sc_ > 0 ? ((bc + 1) << S) : (bc << S);   /* grid line of the far edge */
-        const int re = sr_ > 0 ? ((br + 1) << S) : (br << S);
-        const R txe = d[0] != 0 ? ((-half + (R)ce * cell) - o[0]) * idx : big;
-        const R tye = d[1] != 0 ? ((-half + (R)re * cell) - o[1]) * idy : big;
-        const R te = txe < tye ? txe : tye;
-        const R tz = (te < t1 ? te : t1) * (1 + R(1e-5)) + R(1e-5);
-        const R za = o[2] + tin * d[2], zb = o[2] + tz * d[2];
-        if (!((za < zb ? za : zb) > (R)tbl[br * nbc + bc] + R(1e-4))) { blk[lv][0] = br; blk[lv][1] = bc; continue; }
-        if (te >= t1) return;
-        if (txe < tye) {   /* leaves through a column line: the row follows from y there, kept inside the block's rows */
-          c = sc_ > 0 ? ce : ce - 1;
-          if (c < 0 || c > sc.ncol - 2) return;
-          int rr = (int)floor((o[1] + te * d[1] + half) / cell);
-          const int rlo = br << S, rhi = ((br + 1) << S) - 1;
-          rr = rr < rlo ? rlo : (rr > rhi ? rhi : rr);
-          r = rr > sc.nrow - 2 ? sc.nrow - 2 : rr;
-        } else {
-          r = sr_ > 0 ? re : re - 1;
-          if (r < 0 || r > sc.nrow - 2) return;
-          int cc = (int)floor((o[0] + te * d[0] + half) / cell);
-          const int clo = bc << S, chi = ((bc + 1) << S) - 1;
-          cc = cc < clo ? clo : (cc > chi ? chi : cc);
-          c = cc > sc.ncol - 2 ? sc.ncol - 2 : cc;
-        }
-        tin = te;
-        tx = d[0] != 0 ? ((-half + (c + (sc_ > 0 ? 1 : 0)) * cell) - o[0]) / d[0] : big;
-        ty = d[1] != 0 ? ((-half + (r + (sr_ > 0 ? 1 : 0)) * cell) - o[1]) / d[1] : big;
-        jumped = true;
-        break;
-      }
-      if (jumped) continue;
-    }
-    const R tout = tx < ty ? tx : ty;
-    const R h00 = eye_height<R>(h, sc.ncol, r, c, sc.zoff), h01 = eye_height<R>(h, sc.ncol, r, c + 1, sc.zoff);
-    const R h10 = eye_height<R>(h, sc.ncol, r + 1, c, sc.zoff), h11 = eye_height<R>(h, sc.ncol, r + 1, c + 1, sc.zoff);
-    const R hmax = fmax_(fmax_(h00, h01), fmax_(h10, h11));
-    const R za = o[2] + tin * d[2], zb = o[2] + (tout < t1 ? tout : t1) * d[2];
-    if ((za < zb ? za : zb) <= hmax) {
-      const R x0 = -half + c * cell, y0 = -half + r * cell;
-      const R A[3] = {x0, y0, h00}, B[3] = {x0, y0 + cell, h10}, C[3] = {x0 + cell, y0, h01}, D[3] = {x0 + cell, y0 + cell, h11};
-      R n1[3], n2[3];
-      const R ta = eye_tri(o, d, A, B, C, n1), tb = eye_tri(o, d, B, C, D, n2);
-      R t = -1; const R* n = n1;
-      if (ta > 0 && (tb <= 0 || ta <= tb)) { t = ta; n = n1; }
-      else if (tb > 0) { t = tb; n = n2; }
-      if (t > 0) {
-        R nn[3] = {n[0], n[1], n[2]};
-        normalize3(nn);
-        R lam = -(nn[0] * fwd[0] + nn[1] * fwd[1] + nn[2] * fwd[2]);      /* headlight shines along fwd; surfaces are two-sided */
-        if (lam < 0) lam = -lam;
-        for (int k = 0; k < 3; k++) { const R v = sc.rgb[k] * (sc.ambient + sc.diffuse * lam); rgb[k] = v > 1 ? R(1) : v; }
-        return;
-      }
-    }
-    if (tout >= t1) return;
-    tin = tout;
-    if (tx < ty) { c += sc_; tx += dtx; if (c < 0 || c > sc.ncol - 2) return; }
-    else { r += sr_; ty += dty; if (r < 0 || r > sc.nrow - 2) return; }
-  }
+  y.sc_ = d[0] > 0 ? 1 : -1; y.sr_ = d[1] > 0 ? 1 : -1;
+  y.tx = d[0] != 0 ? ((-half + (c + (y.sc_ > 0 ? 1 : 0)) * cell) - o[0]) / d[0] : big;   /* t of the next column / row boundary */
+  y.ty = d[1] != 0 ? ((-half + (r + (y.sr_ > 0 ? 1 : 0)) * cell) - o[1]) / d[1] : big;
+  y.dtx = d[0] != 0 ? cell / (d[0] > 0 ? d[0] : -d[0]) : big; y.dty = d[1] != 0 ? cell / (d[1] > 0 ? d[1] : -d[1]) : big;
+  y.idx = d[0] != 0 ? 1 / d[0] : big; y.idy = d[1] != 0 ? 1 / d[1] : big;
+  y.c = c; y.r = r; y.t1 = t1; y.tin = t0; y.steps = 0;
+  y.blk[0][0] = y.blk[0][1] = y.blk[1][0] = y.blk[1][1] = -1;
+  return true;
 }
 
-/* pixel (i, j) of a camera at pos with orientation mat (row-major, columns = camera axes in the world) */
+/* one step; returns 0: go on, 1: left the terrain (background), 2: hit (rgb written) */
+template <class R> FLY_INL int eye_ray_step(const FlyScene& sc, const float* h, const float* bmax, EyeRay<R>& y, R* rgb) {
+  const R half = sc.half, cell = 2 * half / (sc.ncol - 1), big = R(1e30);
+  const R *o = y.o, *d = y.d;
+  if (++y.steps > 2 * (sc.nrow + sc.ncol)) return 1;
+  if (bmax) {
+    /* empty-space skipping, two levels (blocks of 16 x 16 cells, then of 4 x 4): if the ray stays above the highest point of a
+       block until it leaves the block, no cell of the block can pass the height test below, and the walk resumes in the first
+       cell behind the block's far edge.  Up to four jumps per step, so that the lanes of a warp reach their next cell test
+       together.  A rising ray above the terrain's highest point is done. */
+    if (d[2] >= 0 && o[2] + y.tin * d[2] > (R)bmax[sc.nbr * sc.nbc + sc.nbr2 * sc.nbc2] + R(1e-4)) return 1;
+    for (int attempt = 0;; attempt++) {
+      int lv = -1;
+      R te = 0, txe = 0, tye = 0;
+      int br = 0, bc = 0, ce = 0, re = 0, S = 0;
+#pragma unroll
+      for (int v = 0; v < 2; v++) {
+        if (lv >= 0) continue;
+        S = v == 0 ? FLY_EYE_SHIFT : FLY_EYE_SHIFT2;
+        br = y.r >> S; bc = y.c >> S;
+        if (br == y.blk[v][0] && bc == y.blk[v][1]) continue;
+        const float* tbl = v == 0 ? bmax : bmax + sc.nbr * sc.nbc;
+        const int nbc = v == 0 ? sc.nbc : sc.nbc2;
+        ce = y.sc_ > 0 ? ((bc + 1) << S) : (bc << S);   /* grid line of the far edge */
+        re = y.sr_ > 0 ? ((br + 1) << S) : (br << S);
+        txe = d[0] != 0 ? ((-half + (R)ce * cell) - o[0]) * y.idx : big;
+        tye = d[1] != 0 ? ((-half + (R)re * cell) - o[1]) * y.idy : big;
+        te = txe < tye ? txe : tye;
+        const R tz = (te < y.t1 ? te : y.t1) * (1 + R(1e-5)) + R(1e-5);
+        const R za = o[2] + y.tin * d[2], zb = o[2] + tz * d[2];
+        if (!((za < zb ? za : zb) > (R)tbl[br * nbc + bc] + R(1e-4))) { y.blk[v][0] = br; y.blk[v][1] = bc; continue; }
+        lv = v;
+      }
+      if (lv < 0) break;           /* both levels need a closer look: test the cell */
+      if (te >= y.t1) return 1;
+      int c, r;
+      if (txe < tye) {   /* leaves through a column line: the row follows from y there, kept inside the block's rows */
+        c = y.sc_ > 0 ? ce : ce - 1;
+        if (c < 0 || c > sc.ncol - 2) return 1;
+        int rr = (int)floor((o[1] + te * d[1] + half) / cell);
+        const int rlo = br << S, rhi = ((br + 1) << S) - 1;
+        rr = rr < rlo ? rlo : (rr > rhi ? rhi : rr);
+        r = rr > sc.nrow - 2 ? sc.nrow - 2 : rr;
+      } else {
+        r = y.sr_ > 0 ? re : re - 1;
+        if (r < 0 || r > sc.nrow - 2) return 1;
+        int cc = (int)floor((o[0] + te * d[0] + half) / cell);
+        const int clo = bc << S, chi = ((bc + 1) << S) - 1;
+        cc = cc < clo ? clo : (cc > chi ? chi : cc);
+        c = cc > sc.ncol - 2 ? sc.ncol - 2 : cc;
+      }
+      y.c = c; y.r = r; y.tin = te;
+      y.tx = d[0] != 0 ? ((-half + (c + (y.sc_ > 0 ? 1 : 0)) * cell) - o[0]) / d[0] : big;
+      y.ty = d[1] != 0 ? ((-half + (r + (y.sr_ > 0 ? 1 : 0)) * cell) - o[1]) / d[1] : big;
+      if (d[2] >= 0 && o[2] + te * d[2] > (R)bmax[sc.nbr * sc.nbc + sc.nbr2 * sc.nbc2] + R(1e-4)) return 1;
+      if (attempt >= 3) return 0;
+    }
+  }
+  const int c = y.c, r = y.r;
+  const R tout = y.tx < y.ty ? y.tx : y.ty;
+  const R h00 = eye_height<R>(h, sc.ncol, r, c, sc.zoff), h01 = eye_height<R>(h, sc.ncol, r, c + 1, sc.zoff);
+  const R h10 = eye_height<R>(h, sc.ncol, r + 1, c, sc.zoff), h11 = eye_height<R>(h, sc.ncol, r + 1, c + 1, sc.zoff);
+  const R hmax = fmax_(fmax_(h00, h01), fmax_(h10, h11));
+  const R za = o[2] + y.tin * d[2], zb = o[2] + (tout < y.t1 ? tout : y.t1) * d[2];
+  if ((za < zb ? za : zb) <= hmax) {
+    const R x0 = -half + c * cell, y0 = -half + r * cell;
+    const R A[3] = {x0, y0, h00}, B[3] = {x0, y0 + cell, h10}, C[3] = {x0 + cell, y0, h01}, D[3] = {x0 + cell, y0 + cell, h11};
+    R n1[3], n2[3];
+    const R ta = eye_tri(o, d, A, B, C, n1), tb = eye_tri(o, d, B, C, D, n2);
+    R t = -1; const R* n = n1;
+    if (ta > 0 && (tb <= 0 || ta <= tb)) { t = ta; n = n1; }
+    else if (tb > 0) { t = tb; n = n2; }
+    if (t > 0) {
+      R nn[3] = {n[0], n[1], n[2]};
+      normalize3(nn);
+      R lam = -(nn[0] * y.fwd[0] + nn[1] * y.fwd[1] + nn[2] * y.fwd[2]);      /* headlight shines along fwd; surfaces are two-sided */
+      if (lam < 0) lam = -lam;
+      for (int k = 0; k < 3; k++) { const R v = sc.rgb[k] * (sc.ambient + sc.diffuse * lam); rgb[k] = v > 1 ? R(1) : v; }
+      return 2;
+    }
+  }
+  if (tout >= y.t1) return 1;
+  y.tin = tout;
+  if (y.tx < y.ty) { y.c += y.sc_; y.tx += y.dtx; if (y.c < 0 || y.c > sc.ncol - 2) return 1; }
+  else { y.r += y.sr_; y.ty += y.dty; if (y.r < 0 || y.r > sc.nrow - 2) return 1; }
+  return 0;
+}
+
+/* direction and headlight axis of pixel (i, j) of a camera at pos with orientation mat (row-major, columns = camera axes in the world) */
+template <class R> FLY_INL void eye_ray_of_pixel(EyeRay<R>& y, const R* pos, const R* mat, int W, int H, R tanhalf, int i, int j) {
+  const R dc[3] = {tanhalf * ((R)W / (R)H) * (2 * ((R)j + R(0.5)) / (R)W - 1), tanhalf * (1 - 2 * ((R)i + R(0.5)) / (R)H), R(-1)};
+  mat_vec(y.d, mat, dc);
+  normalize3(y.d);
+  for (int k = 0; k < 3; k++) { y.o[k] = pos[k]; y.fwd[k] = -mat[3 * k + 2]; }
+}
+FLY_INL void eye_store(unsigned char* out, const float* rgb) {
+  for (int k = 0; k < 3; k++) out[k] = (unsigned char)(int)(rgb[k] * 255.0f + 0.5f);
+}
+
+/* pixel (i, j) of a camera at pos with orientation mat (row-major, columns = camera axes in the world): the whole ray at once */
 template <class R> FLY_INL void eye_pixel(const FlyScene& sc, const float* h, const R* pos, const R* mat, int W, int H, R tanhalf, int i, int j,
                                           unsigned char* out, const float* bmax = nullptr) {
-  const R dc[3] = {tanhalf * ((R)W / (R)H) * (2 * ((R)j + R(0.5)) / (R)W - 1), tanhalf * (1 - 2 * ((R)i + R(0.5)) / (R)H), R(-1)};
-  R d[3], fwd[3] = {-mat[2], -mat[5], -mat[8]}, rgb[3];
-  mat_vec(d, mat, dc);
-  normalize3(d);
-  eye_trace<R>(sc, h, pos, d, fwd, rgb, bmax);
+  EyeRay<R> y;
+  R rgb[3] = {(R)sc.sky[0], (R)sc.sky[1], (R)sc.sky[2]};
+  eye_ray_of_pixel(y, pos, mat, W, H, tanhalf, i, j);
+  if (eye_ray_init(sc, y))
+    while (eye_ray_step(sc, h, bmax, y, rgb) == 0) {}
   for (int k = 0; k < 3; k++) out[k] = (unsigned char)(int)(rgb[k] * R(255) + R(0.5));
 }
 #endif

@@ -33,7 +33,7 @@ struct FlybEngine {
   void* d_wbpg = nullptr; double* d_wbpg_phase = nullptr;
   /* vision_flight: terrain pool, trench centre lines, and the per-env eye camera frames the step kernel leaves for flyb_render */
   float* d_hf = nullptr; double* d_trench_meta = nullptr; float* d_trench_y = nullptr;
-  float* d_eyes = nullptr; int* d_eye_terrain = nullptr; float* d_hf_bmax = nullptr;
+  float* d_eyes = nullptr; int* d_eye_terrain = nullptr; float* d_hf_bmax = nullptr; unsigned* d_eye_counter = nullptr;
   /* staging for the host-pointer API */
   float *h_action = nullptr, *h_obs = nullptr, *h_rd = nullptr; int* h_st = nullptr; unsigned char* h_mask = nullptr;
   float *d_action = nullptr, *d_obs = nullptr, *d_rd = nullptr; int* d_st = nullptr; unsigned char* d_mask = nullptr;
@@ -146,18 +146,49 @@ __global__ void fly_eyes_blockmax_kernel(const float* __restrict__ data, int nte
   bmax[(size_t)t * stride + (size_t)br * nbc + bc] = mx;
 }
 
-/* the same for the eyes of a handle's envs (flyb_render): camera 2 e + k is eye k of env e, flying over terrain terrain_id[e] */
+/* the same for the eyes of a handle's envs (flyb_render): camera 2 e + k is eye k of env e, flying over terrain terrain_id[e].
+ * Persistent: every lane walks one ray a step at a time and takes its next pixel from a global counter as soon as its ray has
+ * ended, so the 32 lanes of a warp stay busy although rays take between 5 and 200 steps. */
 __global__ void __launch_bounds__(256) fly_eyes_env_kernel(FlyScene sc, int ncam, const int* __restrict__ terrain_id,
                                                             const float* __restrict__ cams, int W, int H, float tanhalf,
-                                                            unsigned char* __restrict__ out) {
-  const size_t p = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (p >= (size_t)ncam * W * H) return;
-  const int cam = (int)(p / ((size_t)W * H)), i = (int)((p / W) % H), j = (int)(p % W);
-  const float* c = cams + 12 * (size_t)cam;
-  const int t = terrain_id[cam >> 1];
-  const float* h = sc.data + (size_t)t * sc.nrow * sc.ncol;
-  eye_pixel<float>(sc, h, c, c + 3, W, H, tanhalf, i, j, out + 3 * p,
-                   sc.bmax ? sc.bmax + (size_t)t * ((size_t)sc.nbr * sc.nbc + (size_t)sc.nbr2 * sc.nbc2) : nullptr);
+                                                            unsigned char* __restrict__ out, unsigned* __restrict__ counter) {
+  const unsigned total = (unsigned)ncam * W * H, lane = threadIdx.x & 31;
+  const size_t tstride = (size_t)sc.nbr * sc.nbc + (size_t)sc.nbr2 * sc.nbc2 + 1;
+  EyeRay<float> y;
+  const float *h = nullptr, *bm = nullptr;
+  long long pix = -1;          /* -1: needs a ray, -2: no rays left */
+  for (;;) {
+    const unsigned need = __ballot_sync(0xffffffffu, pix == -1);
+    if (need) {
+      unsigned base = 0;
+      const int leader = __ffs(need) - 1;
+      if ((int)lane == leader) base = atomicAdd(counter, (unsigned)__popc(need));
+      base = __shfl_sync(0xffffffffu, base, leader);
+      if (pix == -1) {
+        const unsigned p = base + __popc(need & ((1u << lane) - 1u));
+        if (p >= total) pix = -2;
+        else {
+          pix = p;
+          const int cam = (int)(p / ((unsigned)W * H)), i = (int)((p / W) % H), j = (int)(p % W);
+          const float* c = cams + 12 * (size_t)cam;
+          const int t = terrain_id[cam >> 1];
+          h = sc.data + (size_t)t * sc.nrow * sc.ncol;
+          bm = sc.bmax ? sc.bmax + (size_t)t * tstride : nullptr;
+          eye_ray_of_pixel(y, c, c + 3, W, H, tanhalf, i, j);
+          if (!eye_ray_init(sc, y)) { eye_store(out + 3 * (size_t)p, sc.sky); pix = -1; }
+        }
+      }
+    }
+    if (__all_sync(0xffffffffu, pix == -2)) break;
+#pragma unroll 1
+    for (int it = 0; it < 4; it++) {   /* a few steps between two looks at the queue */
+      if (pix >= 0) {
+        float rgb[3] = {sc.sky[0], sc.sky[1], sc.sky[2]};
+        const int st = eye_ray_step(sc, h, bm, y, rgb);
+        if (st) { eye_store(out + 3 * (size_t)pix, rgb); pix = -1; }
+      }
+    }
+  }
 }
 
 /* ---- FP32 FMA peak of the device, measured (flyb_fma_peak): every thread runs 16 independent FMA chains; 8 blocks of 256
@@ -371,7 +402,7 @@ void flyb_destroy(flyb_handle h) {
   cudaFree(h->d_arena); cudaFree(h->d_sreal); cudaFree(h->d_sint); cudaFree(h->d_stats); cudaFree(h->d_trace_int);
   cudaFree(h->d_trace_real); cudaFree(h->d_bulk); cudaFree(h->d_counter); cudaFree(h->d_work); cudaFree(h->d_perm); cudaFree(h->d_clip_rows);
   cudaFree(h->d_wbpg); cudaFree(h->d_wbpg_phase);
-  cudaFree(h->d_hf); cudaFree(h->d_trench_meta); cudaFree(h->d_trench_y); cudaFree(h->d_eyes); cudaFree(h->d_eye_terrain); cudaFree(h->d_hf_bmax);
+  cudaFree(h->d_hf); cudaFree(h->d_trench_meta); cudaFree(h->d_trench_y); cudaFree(h->d_eyes); cudaFree(h->d_eye_terrain); cudaFree(h->d_hf_bmax); cudaFree(h->d_eye_counter);
   cudaFree(h->d_clip_off); cudaFree(h->d_clip_len); cudaFree(h->d_action); cudaFree(h->d_obs); cudaFree(h->d_rd);
   cudaFree(h->d_st); cudaFree(h->d_mask);
   cudaFreeHost(h->h_action); cudaFreeHost(h->h_obs); cudaFreeHost(h->h_rd); cudaFreeHost(h->h_st); cudaFreeHost(h->h_mask);
@@ -556,18 +587,21 @@ int flyb_load_terrain(flyb_handle h, const float* heights, int n_terrains, const
     const int nr = h->m.hfield_nrow - 1, nc = h->m.hfield_ncol - 1;
     const int nbr = (nr + FLY_EYE_BLOCK - 1) >> FLY_EYE_SHIFT, nbc = (nc + FLY_EYE_BLOCK - 1) >> FLY_EYE_SHIFT;
     const int nbr2 = (nr + (1 << FLY_EYE_SHIFT2) - 1) >> FLY_EYE_SHIFT2, nbc2 = (nc + (1 << FLY_EYE_SHIFT2) - 1) >> FLY_EYE_SHIFT2;
-    const size_t stride = (size_t)nbr * nbc + (size_t)nbr2 * nbc2;
+    const size_t stride = (size_t)nbr * nbc + (size_t)nbr2 * nbc2 + 1;
     CK(cudaMalloc(&h->d_hf_bmax, (size_t)n_terrains * stride * sizeof(float)));
     fly_eyes_blockmax_kernel<<<(n_terrains * nbr * nbc + 127) / 128, 128>>>(h->d_hf, n_terrains, h->m.hfield_nrow, h->m.hfield_ncol, -0.01f,
                                                                           FLY_EYE_SHIFT, nbr, nbc, stride, h->d_hf_bmax);
     fly_eyes_blockmax_kernel<<<(n_terrains * nbr2 * nbc2 + 127) / 128, 128>>>(h->d_hf, n_terrains, h->m.hfield_nrow, h->m.hfield_ncol, -0.01f,
                                                                             FLY_EYE_SHIFT2, nbr2, nbc2, stride, h->d_hf_bmax + (size_t)nbr * nbc);
+    fly_eyes_blockmax_kernel<<<(n_terrains + 127) / 128, 128>>>(h->d_hf, n_terrains, h->m.hfield_nrow, h->m.hfield_ncol, -0.01f, 30, 1, 1, stride,
+                                                               h->d_hf_bmax + (size_t)nbr * nbc + (size_t)nbr2 * nbc2);   /* one block = the terrain */
     CK(cudaGetLastError());
     CK(cudaDeviceSynchronize());
   }
   if (!h->d_eyes) {
     CK(cudaMalloc(&h->d_eyes, (size_t)h->num_envs * 24 * sizeof(float)));
     CK(cudaMalloc(&h->d_eye_terrain, (size_t)h->num_envs * sizeof(int)));
+    CK(cudaMalloc(&h->d_eye_counter, sizeof(unsigned)));
     CK(cudaMemset(h->d_eyes, 0, (size_t)h->num_envs * 24 * sizeof(float)));
     CK(cudaMemset(h->d_eye_terrain, 0, (size_t)h->num_envs * sizeof(int)));
   }
@@ -590,8 +624,11 @@ int flyb_render(flyb_handle h, int width, int height, float fovy_deg, const floa
   sc.ambient = colors8[6]; sc.diffuse = colors8[7];
   const int ncam = 2 * h->num_envs;
   const size_t npix = (size_t)ncam * width * height;
-  fly_eyes_env_kernel<<<(unsigned)((npix + 255) / 256), 256, 0, (cudaStream_t)stream>>>(sc, ncam, h->d_eye_terrain, h->d_eyes, width, height,
-                                                                                       tanf(0.5f * fovy_deg * 3.14159265358979f / 180.0f), out);
+  unsigned blocks = (unsigned)((npix + 255) / 256), full = (unsigned)h->sm_count * 8u;
+  if (blocks > full) blocks = full;
+  CK(cudaMemsetAsync(h->d_eye_counter, 0, sizeof(unsigned), (cudaStream_t)stream));
+  fly_eyes_env_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(sc, ncam, h->d_eye_terrain, h->d_eyes, width, height,
+                                                               tanf(0.5f * fovy_deg * 3.14159265358979f / 180.0f), out, h->d_eye_counter);
   CK(cudaGetLastError());
   h->launches++;
   return 0;
