@@ -188,6 +188,68 @@ def test_gpu_vision_flight_against_per_env_oracles(models):
 
 
 @pytest.mark.gpu
+def test_gpu_vision_flight_at_the_bench_size(models):
+    """16 384 envs over a pool of 16 trench terrains, 200 control steps with auto-resets (gentle actions, then the wings are driven
+    against the pattern and the flies drop): sampled envs equal their oracles step for step, their episodes end on the floor and
+    restart on other terrains with other targets; no capacity overflow, real images."""
+    import torch
+    from flybody_b200 import fly_envs
+    M = models["vision_flight"]
+    N, seed, NT = 16384, 17, 16
+    env = fly_envs.vision_guided_flight(bumps_or_trench="trench", num_envs=N, seed=seed, n_terrains=NT, terrain_seed=3,
+                                        target_height_range=(0.2, 0.3))
+    M = env.M
+    tab = T.terrain_table("trench", NT, seed=3)
+    wb = W.build_tables(W.synthetic_base_pattern())
+    ts = env.reset()
+    sample = [0, 4143, 4144, 9999, 16383]
+    episode = {e: 0 for e in sample}
+
+    def oracle_of(e):
+        t, h, v = T.vision_draws(seed, e, episode[e], NT, height_range=(0.2, 0.3))
+        o = _oracle_for(M, tab, wb, t, h, v, T.wbpg_phase0(seed, e, episode[e]))
+        return o
+
+    oracles = {e: oracle_of(e) for e in sample}
+    for e in sample:
+        oracles[e].env_reset()
+    gen = torch.Generator(device=env.device); gen.manual_seed(3)
+    lo = torch.as_tensor(np.asarray(M["action_min"], np.float32), device=env.device)
+    hi = torch.as_tensor(np.asarray(M["action_max"], np.float32), device=env.device)
+    restarts = 0
+    since = torch.zeros(N, dtype=torch.int64, device=env.device)       # control steps since the env's last reset
+    wing = torch.as_tensor(np.asarray(M["wing_action"]), device=env.device)
+    for k in range(200):
+        a = 0.3 * (lo + torch.rand((N, lo.shape[0]), device=env.device, generator=gen) * (hi - lo))
+        drop = since >= 5 + (torch.arange(N, device=env.device) % 11)
+        a[drop] = 0.0
+        a[drop[:, None] & torch.isin(torch.arange(lo.shape[0], device=env.device), wing)[None, :]] = -1.0
+        ts = env.step(a)
+        since = torch.where(ts.step_type == 0, torch.zeros_like(since), since + 1)
+        st, r, g = ts.step_type.cpu().numpy(), ts.reward.cpu().numpy(), ts.discount.cpu().numpy()
+        obs, ah = env.flat_observation.cpu().numpy(), a.cpu().numpy()
+        for e in sample:
+            o = oracles[e]
+            ost, orr, og, oobs = o.env_step(ah[e].astype(np.float64))
+            if ost == 0:          # the oracle restarted: new episode, new draws - rebuild it on the new terrain
+                episode[e] += 1
+                restarts += 1
+                o = oracles[e] = oracle_of(e)
+                ost, oobs = o.env_reset()
+                orr, og = 0.0, 1.0
+                assert st[e] == 0
+            assert st[e] == ost, (k, e, st[e], ost)
+            if ost != 0:
+                assert g[e] == og and abs(r[e] - orr) < 5e-4, (k, e, g[e], og, r[e], orr)
+            assert _block_err(M, obs[e], oobs, skip=("accelerometer",)) < 5e-3, (k, e, _block_err(M, obs[e], oobs, skip=("accelerometer",)))
+    stats = env.episode_stats()
+    assert stats["overflow_steps"] == 0 and restarts >= 3, (stats, restarts)
+    eyes = ts.observation["walker/right_eye"]
+    assert eyes.shape == (N, 32, 32, 3) and int(eyes.max()) > 50
+    env.close()
+
+
+@pytest.mark.gpu
 def test_gpu_crash_onto_the_height_field(models):
     """Start over the highest ground of the one terrain in the pool (init_pos_x_range / init_pos_y_range, vision_flight.py:30-31):
     the contacts that end the episodes are the height field's (prism walk inside the step kernel), step for step with the oracle."""
