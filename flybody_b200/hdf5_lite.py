@@ -515,8 +515,32 @@ def _datatype_msg(dt: np.dtype) -> bytes:
     raise Hdf5Unsupported(f"writer: dtype {dt}")
 
 
+def _write_vlen_strings(out: _Out, a: np.ndarray) -> int:
+    """An object array of str / bytes as a variable-length string dataset: elements (length, global-heap address, index) pointing
+    into one global heap collection (spec III.E), the way h5py stores a list of Python strings."""
+    flat = [x.encode("utf-8") if isinstance(x, str) else bytes(x) for x in a.reshape(-1)]
+    body = b""
+    for i, b in enumerate(flat):
+        body += struct.pack("<HHIQ", i + 1, 1, 0, len(b)) + b + bytes(-len(b) % 8)
+    size = max(4096, 16 + len(body) + 16)
+    free = size - 16 - len(body)
+    gcol = out.alloc(size)
+    out.put(gcol, b"GCOL" + struct.pack("<B3xQ", 1, size) + body + struct.pack("<HHIQ", 0, 0, 0, free))
+    elems = b"".join(struct.pack("<IQI", len(b), gcol, i + 1) for i, b in enumerate(flat))
+    addr = out.alloc(max(len(elems), 1))
+    out.put(addr, elems)
+    space = struct.pack("<BBB5x", 1, a.ndim, 0) + struct.pack(f"<{a.ndim}Q", *a.shape)
+    base = struct.pack("<B3BI", 0x10 | 3, 0, 0, 0, 1)                         # base type: one-byte string
+    dtype = struct.pack("<B3BI", 0x10 | 9, 0x01, 0x01, 0, 16) + base          # class 9, type = string, charset UTF-8
+    msgs = [_msg(0x01, space), _msg(0x03, dtype, 1), _msg(0x05, bytes([2, 2, 2, 0])),
+            _msg(0x08, struct.pack("<BBQQ", 3, 1, addr, len(elems)))]
+    return _header(out, msgs)
+
+
 def _write_dataset(out: _Out, a: np.ndarray, chunks: Optional[Tuple[int, ...]], deflate: Optional[int], shuffle: bool) -> int:
     a = np.asarray(a)
+    if a.dtype == object:
+        return _write_vlen_strings(out, a)
     a = a if a.ndim == 0 else np.ascontiguousarray(a)
     if a.dtype.byteorder == ">":
         a = a.astype(a.dtype.newbyteorder("<"))
@@ -629,7 +653,7 @@ def _write_group(out: _Out, tree: dict, opts: dict, leaf_k: int, internal_k: int
 
 
 def write_file(path: str, tree: dict, dataset_options: Optional[dict] = None, leaf_k: int = 4, internal_k: int = 16):
-    """Write `tree` (nested dicts of numpy arrays: int / float / fixed-length byte strings) as an HDF5 file in the library's
+    """Write `tree` (nested dicts of numpy arrays: int / float / fixed-length byte strings / object arrays of str) as an HDF5 file in the library's
     oldest format (superblock 0, old-style groups, version-1 object headers), contiguous unless `dataset_options[name]` gives
     `chunks=(…)`, `deflate=level`, `shuffle=True` for the datasets of that name.  A fixture / export tool: the only HDF5 consumer
     available in this image is the reader above."""

@@ -44,7 +44,7 @@ def test_round_trip_of_every_storage_form(tmp_path):
     tree = {
         "a": {"x": big, "y": rng.normal(size=(5,)).astype(np.float32), "names": np.array([b"coxa_T1_left", b"femur", b""])},
         "scalar": np.float64(2e-3), "lengths": np.arange(11, dtype=np.int64), "u8": np.arange(7, dtype=np.uint8),
-        "many": many, "empty": np.zeros((0, 4)),
+        "many": many, "empty": np.zeros((0, 4)), "vlen": np.array(["coxa_abduct_T1_left", "", "tarsus2_T3_right", "\u00e9"], dtype=object),
         "g": {f"{i:04d}": {"v": np.full((2, 2), float(i))} for i in range(300)},
     }
     p = str(tmp_path / "t.hdf5")
@@ -55,6 +55,7 @@ def test_round_trip_of_every_storage_form(tmp_path):
         assert np.array_equal(f["a"]["x"][()], big) and np.array_equal(f["a/x"][3:9], big[3:9])
         assert f["a"]["y"].dtype == np.float32 and np.array_equal(np.asarray(f["a"]["y"]), tree["a"]["y"])
         assert [s.decode() for s in f["a"]["names"]] == ["coxa_T1_left", "femur", ""]
+        assert [b.decode("utf-8") for b in f["vlen"]] == ["coxa_abduct_T1_left", "", "tarsus2_T3_right", "\u00e9"]   # global-heap strings
         assert f["scalar"][()] == 2e-3 and f["scalar"].shape == ()
         assert np.array_equal(f["lengths"][()], np.arange(11)) and f["lengths"][4] == 4 and len(f["lengths"]) == 11
         assert np.array_equal(f["u8"][()], np.arange(7)) and f["u8"].dtype == np.uint8
