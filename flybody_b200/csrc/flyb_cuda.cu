@@ -146,6 +146,15 @@ __global__ void fly_eyes_blockmax_kernel(const float* __restrict__ data, int nte
   bmax[(size_t)t * stride + (size_t)br * nbc + bc] = mx;
 }
 
+/* the terrain's maximum = the largest of its 16 x 16 block maxima, stored behind the two block tables */
+__global__ void fly_eyes_gmax_kernel(float* __restrict__ bmax, int nterrain, int nb, size_t stride) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= nterrain) return;
+  float mx = 0.f;
+  for (int i = 0; i < nb; i++) mx = fmaxf(mx, bmax[(size_t)t * stride + i]);
+  bmax[(size_t)t * stride + stride - 1] = mx;
+}
+
 /* the same for the eyes of a handle's envs (flyb_render): camera 2 e + k is eye k of env e, flying over terrain terrain_id[e].
  * Persistent: every lane walks one ray a step at a time and takes its next pixel from a global counter as soon as its ray has
  * ended, so the 32 lanes of a warp stay busy although rays take between 5 and 200 steps. */
@@ -593,8 +602,7 @@ int flyb_load_terrain(flyb_handle h, const float* heights, int n_terrains, const
                                                                           FLY_EYE_SHIFT, nbr, nbc, stride, h->d_hf_bmax);
     fly_eyes_blockmax_kernel<<<(n_terrains * nbr2 * nbc2 + 127) / 128, 128>>>(h->d_hf, n_terrains, h->m.hfield_nrow, h->m.hfield_ncol, -0.01f,
                                                                             FLY_EYE_SHIFT2, nbr2, nbc2, stride, h->d_hf_bmax + (size_t)nbr * nbc);
-    fly_eyes_blockmax_kernel<<<(n_terrains + 127) / 128, 128>>>(h->d_hf, n_terrains, h->m.hfield_nrow, h->m.hfield_ncol, -0.01f, 30, 1, 1, stride,
-                                                               h->d_hf_bmax + (size_t)nbr * nbc + (size_t)nbr2 * nbc2);   /* one block = the terrain */
+    fly_eyes_gmax_kernel<<<(n_terrains + 127) / 128, 128>>>(h->d_hf_bmax, n_terrains, nbr * nbc, stride);
     CK(cudaGetLastError());
     CK(cudaDeviceSynchronize());
   }
