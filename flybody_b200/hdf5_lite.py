@@ -23,6 +23,7 @@ The API is the slice of h5py's the loaders use: `File(path)[name]`, `len(group)`
 `dataset[a:b]`, `dataset.shape`, `dataset.dtype`, `np.asarray(dataset)`."""
 from __future__ import annotations
 
+import mmap
 import struct
 import zlib
 from typing import Dict, Iterator, List, Optional, Tuple
@@ -48,8 +49,12 @@ class File:
     def __init__(self, path: str, mode: str = "r"):
         if mode != "r":
             raise ValueError("hdf5_lite.File is read-only; use write_file() to create files")
-        with open(path, "rb") as fh:
-            self._buf = fh.read()
+        # memory-mapped: the walking dataset of the reference (16 252 trajectories) is gigabytes; only what is indexed is paged in
+        self._fh = open(path, "rb")
+        try:
+            self._buf = mmap.mmap(self._fh.fileno(), 0, access=mmap.ACCESS_READ)
+        except ValueError:           # empty file
+            self._buf = b""
         self.filename = path
         self._parse_superblock()
         self._root = Group(self, self._root_header, "/", btree=self._root_btree, heap=self._root_heap)
@@ -102,7 +107,16 @@ class File:
         return self._root.keys()
 
     def close(self):
-        self._buf = b""
+        buf, self._buf = self._buf, b""
+        self._root = None
+        if isinstance(buf, mmap.mmap):
+            try:
+                buf.close()
+            except BufferError:      # numpy views of a dataset are still alive: the map goes when they do
+                pass
+        if getattr(self, "_fh", None) is not None:
+            self._fh.close()
+            self._fh = None
 
     def __enter__(self):
         return self
@@ -170,7 +184,7 @@ class Group:
                     (n,) = struct.unpack_from("<H", b, p + 6)
                     for i in range(n):
                         off, hdr, cache, _r, s0, s1 = struct.unpack_from("<QQIIQQ", b, p + 8 + 40 * i)
-                        end = b.index(b"\x00", seg + off)
+                        end = b.find(b"\x00", seg + off)
                         entries[b[seg + off:end].decode("utf-8")] = (hdr, cache, s0, s1)
                     return
                 if b[p:p + 4] != b"TREE":
