@@ -133,6 +133,63 @@ def test_emulated_engine_matches_the_oracle_through_a_crash(models, kind):
         assert ended
 
 
+def _tolerance(x, bounds, margin):
+    """dm_control.utils.rewards.tolerance(x, bounds, margin, sigmoid="linear", value_at_margin=0) - third party, restated: 1 inside
+    the bounds, falling linearly to 0 at `margin` outside them"""
+    lo, hi = bounds
+    if lo <= x <= hi:
+        return 1.0
+    if margin == 0:
+        return 0.0
+    d = (lo - x if x < lo else x - hi) / margin
+    return 1.0 - d if abs(d) < 1 else 0.0
+
+
+def _reference_reward(M, o, tab, terrain, height, speed):
+    """get_reward_factors of tasks/vision_flight.py:157-212 written out in numpy on the oracle's state"""
+    q, v = o.d("qpos")[int(M["root_qposadr"]):][:7], o.d("qvel")[int(M["root_dofadr"]):][:6]
+    f = [_tolerance(q[2] - T.nearest_height(tab["height"][terrain], (20, 20), q[0], q[1]), (height, height), 0.15)]
+    f.append(_tolerance(v[0], (speed, np.inf), 1.1 * speed))
+    f.append(_tolerance(np.linalg.norm(v[:3]), (speed, speed), 1.1 * speed))
+    vel = [o.d("sensordata")[int(M["sensor_adr"][s]):][:3] for s in range(int(M["nsensor"])) if int(M["sensor_type"][s]) == 2][0]
+    f.append(_tolerance(vel[1], (0, 0), 10))
+    zaxis = o.d("xmat").reshape(-1, 9)[int(M["root_body"])][6:9]
+    th = np.deg2rad(47.5)
+    f.append(_tolerance(np.arccos(np.dot([np.sin(th), 0, np.cos(th)], zaxis)), (0, 0), np.pi))
+    c = 1.0
+    if tab["kind"] == "trench":
+        tx, ty = tab["trench_x"][terrain], tab["trench_y"][terrain]
+        if tx[0] <= q[0] <= tx[-1]:
+            c = _tolerance(q[1], (ty[np.abs(tx - q[0]).argmin()],) * 2, 0.15)
+    f.append(c)
+    return float(np.prod(f)), f
+
+
+@pytest.mark.parametrize("kind", ["trench", "bumps"])
+def test_oracle_reward_is_the_reference_formula(models, kind):
+    """The oracle's C restatement of the six reward factors against the formula read off the reference source, on a flight that
+    crosses the trench's x range (centre-of-trench factor active) at various heights and speeds."""
+    tab = T.terrain_table(kind, 2, seed=5)
+    wb = W.build_tables(W.synthetic_base_pattern())
+    x0 = float(tab["trench_x"][0][3]) if kind == "trench" else -5.0
+    y0 = float(tab["trench_y"][0][3]) + 0.05 if kind == "trench" else 0.0
+    M = _with_start(models["vision_flight"], x0, y0)
+    o = _oracle_for(M, tab, wb, 0, 0.55, 25.0, 0.1)
+    o.env_reset()
+    o.d("qvel")[int(M["root_dofadr"])] = 22.0          # forward, a little below the target speed
+    rng = np.random.RandomState(2)
+    seen_center, nonzero = 0, 0
+    for k in range(120):
+        st, r, g, obs = o.env_step(_actions(M, rng, k, 1000))
+        want, f = _reference_reward(M, o, tab, 0, 0.55, 25.0)
+        assert abs(r - want) < 1e-12, (k, r, want, f)
+        seen_center += f[5] < 1.0
+        nonzero += r > 0
+        if st == 2:
+            break
+    assert nonzero > 10 and (kind != "trench" or seen_center > 5)
+
+
 # ------------------------------------------------------------------------------------------------------------- GPU
 @pytest.mark.gpu
 def test_gpu_vision_flight_against_per_env_oracles(models):
