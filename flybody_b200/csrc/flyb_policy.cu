@@ -14,7 +14,7 @@
  *   - activations never leave the SM: the epilogue writes them as bf16 into shared memory in the canonical K-major
  *     SWIZZLE_128B layout, where the next layer's MMAs read them as the A operand (128 KB: 8 K-chunks of 128 rows x 128 B);
  *   - weights (bf16, [out, in] row-major = K-major, L2-resident: 2.3 MB) and the first layer's input tiles stream through a
- *     2-stage TMA pipeline (cp.async.bulk.tensor.2d, SWIZZLE_128B, mbarrier complete_tx), freed by tcgen05.commit.
+ *     3-stage TMA pipeline (cp.async.bulk.tensor.2d, SWIZZLE_128B, mbarrier complete_tx), freed by tcgen05.commit.
  *
  * Every spin on an mbarrier is bounded (trap after ~2 s) so that a protocol bug cannot hang the device. */
 #include <cuda.h>
@@ -36,10 +36,10 @@ constexpr int PH = 512;            /* hidden width of every layer */
 constexpr int PKC = 64;            /* bf16 elements per K chunk = one 128-byte swizzle row */
 constexpr int PM = 128;            /* rows per CTA */
 constexpr int PNH = 256;           /* N per MMA instruction */
-constexpr int PSTAGES = 2;
+constexpr int PSTAGES = 3;
 constexpr int PA_BYTES = PM * PKC * 2;      /* 16 KB: an A tile (128 rows x 64 bf16) */
 constexpr int PB_BYTES = PNH * PKC * 2;     /* 32 KB: a B tile (256 weight rows x 64 bf16) */
-constexpr int PSTAGE_BYTES = PA_BYTES + PB_BYTES;
+constexpr int PSTAGE_BYTES = PB_BYTES;       /* a stage holds a B tile; the first layer's A tile of the stage lies in the (then unused) activation buffer */
 constexpr int PACT_BYTES = PM * PH * 2;     /* 128 KB */
 constexpr int PHEAD_N = 128;                /* head output columns: mean at 0.., scale at 64.. */
 constexpr int PSMEM_BYTES = PACT_BYTES + PSTAGES * PSTAGE_BYTES + 1024 /* barriers */ + 1024 /* alignment slack */;
@@ -148,7 +148,7 @@ fly_policy_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* act = smem;                                   /* 8 chunks x 16 KB */
-  uint8_t* stage = smem + PACT_BYTES;                    /* PSTAGES x (A 16 KB | B 32 KB) */
+  uint8_t* stage = smem + PACT_BYTES;                    /* PSTAGES x 32 KB B tiles */
   uint64_t* bars = reinterpret_cast<uint64_t*>(stage + PSTAGES * PSTAGE_BYTES);
   /* bars: full[PSTAGES], empty[PSTAGES], acc_full, act_ready ; then the TMEM base address */
   const uint32_t bar_full = smem_u32(bars), bar_empty = smem_u32(bars + PSTAGES);
@@ -184,7 +184,7 @@ fly_policy_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
         for (int kc = 0; kc < nk; kc++, it++) {
           const int s = it % PSTAGES;
           mbar_wait(bar_empty + 8 * s, ((it / PSTAGES) & 1) ^ 1);
-          const uint32_t a_dst = smem_u32(stage + s * PSTAGE_BYTES), b_dst = a_dst + PA_BYTES;
+          const uint32_t a_dst = smem_u32(act + s * PA_BYTES), b_dst = smem_u32(stage + s * PSTAGE_BYTES);
           const uint32_t bytes = (l == 0 ? PA_BYTES : 0) + (l == 4 ? PHEAD_N * PKC * 2 : PB_BYTES);
           mbar_expect_tx(bar_full + 8 * s, bytes);
           if (l == 0) tma_load_2d(a_dst, &map_x, kc * PKC, row0, bar_full + 8 * s);
@@ -206,8 +206,8 @@ fly_policy_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
           const int s = it % PSTAGES;
           mbar_wait(bar_full + 8 * s, (it / PSTAGES) & 1);
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-          const uint32_t a_base = l == 0 ? smem_u32(stage + s * PSTAGE_BYTES) : smem_u32(act + kc * PA_BYTES);
-          const uint32_t b_base = smem_u32(stage + s * PSTAGE_BYTES) + PA_BYTES;
+          const uint32_t a_base = l == 0 ? smem_u32(act + s * PA_BYTES) : smem_u32(act + kc * PA_BYTES);
+          const uint32_t b_base = smem_u32(stage + s * PSTAGE_BYTES);
 #pragma unroll
           for (int k = 0; k < PKC / 16; k++)   /* UMMA K = 16 bf16 = 32 bytes along the swizzled row */
             umma_bf16(tmem + nh * PNH, umma_desc(a_base + 32 * k), umma_desc(b_base + 32 * k), idesc, (kc | k) != 0);
