@@ -1,4 +1,4 @@
-/* fly_eyes.cuh - the fly's two eye cameras as a ray caster over the height-field terrain (first slice;
+/* fly_eyes.cuh - the fly's two eye cameras as a ray caster over the height-field terrain (SURVEY.md 8f rank 4;
  * vnl_ray/fruitfly/fruitfly.py:676-708: MJCFCamera observables of `eye_right` / `eye_left`, 32 x 32 pixels, fovy 150 degrees,
  * tasks/vision_flight.py:25-26,83-84).  The reference renders them with MuJoCo's OpenGL renderer (unavailable on this box); this
  * is the camera and shading arithmetic as plain device code, one thread per pixel:
@@ -9,11 +9,11 @@
  *   everything else is background;
  *   shading: flat colour x (ambient + diffuse max(0, n . l)) with the headlight - the only light the task keeps
  *   (vision_flight.py:66-68; hills.py:223-225 ambient 0.4, diffuse 0.8) - shining along the camera axis, rounded to 8 bits.
- * Not rendered in this slice: the fly's own body (antennae and legs in view), textures and skybox of the "outdoor_natural"
+ * Not rendered: the fly's own body (antennae and legs in view), textures and skybox of the "outdoor_natural"
  * aesthetic (dm_control assets, not available here), specular highlights.
  * The ray walks the grid cell by cell (2-D DDA), skips cells whose corner heights lie below the ray, and intersects the two
- * triangles of the others.  R is float on the device and double in the oracle's restatement (oracle/flyb_oracle.c:
- * flyo_render_eyes). */
+ * triangles of the others; with block maxima (flyb_render) it jumps over blocks of cells it stays above.  R is float on the
+ * device; the oracle is the brute-force float64 renderer oracle/eyes_ref.py (every triangle against every ray). */
 #ifndef FLY_EYES_CUH_
 #define FLY_EYES_CUH_
 #include "fly_math.cuh"

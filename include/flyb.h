@@ -148,7 +148,7 @@ int flyb_load_terrain(flyb_handle h, const float* heights, int n_terrains, const
  * MuJoCo's OpenGL renderer (unavailable on this box); what the ray caster draws is stated in csrc/fly_eyes.cuh. */
 int flyb_render(flyb_handle h, int width, int height, float fovy_deg, const float* colors8, uint8_t* out, void* stream);
 
-/* Height field against convex geoms (host pointers; first slice of the terrain of vision_guided_flight, vnl_ray/fly_envs.py:160-206,
+/* Height field against convex geoms, stand-alone (host pointers; the narrow phase flyb_step runs for the terrain of vision_guided_flight, vnl_ray/fly_envs.py:160-206,
  * tasks/arenas/hills.py:160-166, 186-221: the `terrain` hfield geom that MuJoCo collides with the fly through mjc_ConvexHField).
  * data [nrow, ncol] float32 heights (x elevation scale), pose12 = position (3) and row-major orientation (9) of the hfield geom,
  * size4 = x half extent, y half extent, elevation scale, base thickness.  Query q: types[q] (FLYB_GEOM_SPHERE / CAPSULE /
@@ -157,7 +157,7 @@ int flyb_render(flyb_handle h, int width, int height, float fovy_deg, const floa
 int flyb_hfield_contacts(int device, const float* data, int nrow, int ncol, const double* pose12, const double* size4, int nquery,
                          const int32_t* types, const double* geoms16, int maxcon, double* out);
 
-/* The fly's eye cameras as a ray caster over the terrain (host pointers; first slice of the `right_eye` / `left_eye` observables,
+/* The fly's eye cameras as a ray caster over the terrain, stand-alone (host pointers, every cell walked: the reference path flyb_render is tested against; the `right_eye` / `left_eye` observables,
  * vnl_ray/fruitfly/fruitfly.py:676-708 with tasks/vision_flight.py:25-26: 32 x 32 pixels, fovy 150; the reference renders them
  * through MuJoCo's OpenGL renderer).  data [nterrain, nrow, ncol] heights over [-half_extent, half_extent]^2, the hfield geom
  * z_offset (-0.01) below the ground plane; camera i looks at terrain terrain_id[i] from cams12[i] = position (3) and row-major
