@@ -68,6 +68,7 @@ template <class R> struct EyeRay {
   R t1, tin, tx, ty, dtx, dty, idx, idy;
   int c, r, sc_, sr_, steps;
   int blk[2][2];   /* per level: the block found NOT skippable last (its sub-blocks / cells are walked) */
+  R hc[4];         /* corner heights of the candidate cell (eye_ray_advance -> eye_ray_test) */
 };
 
 /* false: the ray misses the slab |x|, |y| <= half (background) */
@@ -97,8 +98,20 @@ template <class R> FLY_INL bool eye_ray_init(const FlyScene& sc, EyeRay<R>& y) {
   return true;
 }
 
-/* one step; returns 0: go on, 1: left the terrain (background), 2: hit (rgb written) */
-template <class R> FLY_INL int eye_ray_step(const FlyScene& sc, const float* h, const float* bmax, EyeRay<R>& y, R* rgb) {
+/* the DDA step to the neighbouring cell; returns 0: go on, 1: left the terrain */
+template <class R> FLY_INL int eye_ray_next_cell(const FlyScene& sc, EyeRay<R>& y) {
+  const R tout = y.tx < y.ty ? y.tx : y.ty;
+  if (tout >= y.t1) return 1;
+  y.tin = tout;
+  if (y.tx < y.ty) { y.c += y.sc_; y.tx += y.dtx; if (y.c < 0 || y.c > sc.ncol - 2) return 1; }
+  else { y.r += y.sr_; y.ty += y.dty; if (y.r < 0 || y.r > sc.nrow - 2) return 1; }
+  return 0;
+}
+
+/* the walk up to the next cell the ray may hit: jumps over blocks, cells with the height test.  Returns 0: go on, 1: left the
+ * terrain (background), 3: the current cell (y.c, y.r, corner heights in y.hc) passes the height test - eye_ray_test decides.
+ * Split from the triangle tests so that the lanes of a warp can run the expensive part together (flyb_render). */
+template <class R> FLY_INL int eye_ray_advance(const FlyScene& sc, const float* h, const float* bmax, EyeRay<R>& y) {
   const R half = sc.half, cell = 2 * half / (sc.ncol - 1), big = R(1e30);
   const R *o = y.o, *d = y.d;
   if (++y.steps > 2 * (sc.nrow + sc.ncol)) return 1;
@@ -161,28 +174,36 @@ template <class R> FLY_INL int eye_ray_step(const FlyScene& sc, const float* h, 
   const R h10 = eye_height<R>(h, sc.ncol, r + 1, c, sc.zoff), h11 = eye_height<R>(h, sc.ncol, r + 1, c + 1, sc.zoff);
   const R hmax = fmax_(fmax_(h00, h01), fmax_(h10, h11));
   const R za = o[2] + y.tin * d[2], zb = o[2] + (tout < y.t1 ? tout : y.t1) * d[2];
-  if ((za < zb ? za : zb) <= hmax) {
-    const R x0 = -half + c * cell, y0 = -half + r * cell;
-    const R A[3] = {x0, y0, h00}, B[3] = {x0, y0 + cell, h10}, C[3] = {x0 + cell, y0, h01}, D[3] = {x0 + cell, y0 + cell, h11};
-    R n1[3], n2[3];
-    const R ta = eye_tri(o, d, A, B, C, n1), tb = eye_tri(o, d, B, C, D, n2);
-    R t = -1; const R* n = n1;
-    if (ta > 0 && (tb <= 0 || ta <= tb)) { t = ta; n = n1; }
-    else if (tb > 0) { t = tb; n = n2; }
-    if (t > 0) {
-      R nn[3] = {n[0], n[1], n[2]};
-      normalize3(nn);
-      R lam = -(nn[0] * y.fwd[0] + nn[1] * y.fwd[1] + nn[2] * y.fwd[2]);      /* headlight shines along fwd; surfaces are two-sided */
-      if (lam < 0) lam = -lam;
-      for (int k = 0; k < 3; k++) { const R v = sc.rgb[k] * (sc.ambient + sc.diffuse * lam); rgb[k] = v > 1 ? R(1) : v; }
-      return 2;
-    }
+  if ((za < zb ? za : zb) <= hmax) { y.hc[0] = h00; y.hc[1] = h01; y.hc[2] = h10; y.hc[3] = h11; return 3; }
+  return eye_ray_next_cell(sc, y);
+}
+
+/* the two triangles of the candidate cell; returns 2: hit (rgb written), else what eye_ray_next_cell says */
+template <class R> FLY_INL int eye_ray_test(const FlyScene& sc, EyeRay<R>& y, R* rgb) {
+  const R half = sc.half, cell = 2 * half / (sc.ncol - 1);
+  const R *o = y.o, *d = y.d;
+  const R x0 = -half + y.c * cell, y0 = -half + y.r * cell;
+  const R A[3] = {x0, y0, y.hc[0]}, B[3] = {x0, y0 + cell, y.hc[2]}, C[3] = {x0 + cell, y0, y.hc[1]}, D[3] = {x0 + cell, y0 + cell, y.hc[3]};
+  R n1[3], n2[3];
+  const R ta = eye_tri(o, d, A, B, C, n1), tb = eye_tri(o, d, B, C, D, n2);
+  R t = -1; const R* n = n1;
+  if (ta > 0 && (tb <= 0 || ta <= tb)) { t = ta; n = n1; }
+  else if (tb > 0) { t = tb; n = n2; }
+  if (t > 0) {
+    R nn[3] = {n[0], n[1], n[2]};
+    normalize3(nn);
+    R lam = -(nn[0] * y.fwd[0] + nn[1] * y.fwd[1] + nn[2] * y.fwd[2]);      /* headlight shines along fwd; surfaces are two-sided */
+    if (lam < 0) lam = -lam;
+    for (int k = 0; k < 3; k++) { const R v = sc.rgb[k] * (sc.ambient + sc.diffuse * lam); rgb[k] = v > 1 ? R(1) : v; }
+    return 2;
   }
-  if (tout >= y.t1) return 1;
-  y.tin = tout;
-  if (y.tx < y.ty) { y.c += y.sc_; y.tx += y.dtx; if (y.c < 0 || y.c > sc.ncol - 2) return 1; }
-  else { y.r += y.sr_; y.ty += y.dty; if (y.r < 0 || y.r > sc.nrow - 2) return 1; }
-  return 0;
+  return eye_ray_next_cell(sc, y);
+}
+
+/* one step of the whole walk; returns 0: go on, 1: left the terrain (background), 2: hit (rgb written) */
+template <class R> FLY_INL int eye_ray_step(const FlyScene& sc, const float* h, const float* bmax, EyeRay<R>& y, R* rgb) {
+  const int s = eye_ray_advance(sc, h, bmax, y);
+  return s == 3 ? eye_ray_test(sc, y, rgb) : s;
 }
 
 /* direction and headlight axis of pixel (i, j) of a camera at pos with orientation mat (row-major, columns = camera axes in the world) */

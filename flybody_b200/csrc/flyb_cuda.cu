@@ -166,6 +166,7 @@ __global__ void __launch_bounds__(256) fly_eyes_env_kernel(FlyScene sc, int ncam
   EyeRay<float> y;
   const float *h = nullptr, *bm = nullptr;
   long long pix = -1;          /* -1: needs a ray, -2: no rays left */
+  bool cand = false;           /* the ray stands in a cell that passed the height test */
   for (;;) {
     const unsigned need = __ballot_sync(0xffffffffu, pix == -1);
     if (need) {
@@ -189,13 +190,21 @@ __global__ void __launch_bounds__(256) fly_eyes_env_kernel(FlyScene sc, int ncam
       }
     }
     if (__all_sync(0xffffffffu, pix == -2)) break;
+    /* the cheap part of the walk (jumps, height tests) a few times over, then the triangle tests of every lane that has found a
+       candidate cell in one go: the expensive code runs with as many lanes as possible */
 #pragma unroll 1
-    for (int it = 0; it < 4; it++) {   /* a few steps between two looks at the queue */
-      if (pix >= 0) {
-        float rgb[3] = {sc.sky[0], sc.sky[1], sc.sky[2]};
-        const int st = eye_ray_step(sc, h, bm, y, rgb);
-        if (st) { eye_store(out + 3 * (size_t)pix, rgb); pix = -1; }
+    for (int it = 0; it < 4; it++) {
+      if (pix >= 0 && !cand) {
+        const int st = eye_ray_advance(sc, h, bm, y);
+        if (st == 1) { eye_store(out + 3 * (size_t)pix, sc.sky); pix = -1; }
+        cand = st == 3;
       }
+    }
+    if (pix >= 0 && cand) {
+      float rgb[3] = {sc.sky[0], sc.sky[1], sc.sky[2]};
+      const int st = eye_ray_test(sc, y, rgb);
+      cand = false;
+      if (st) { eye_store(out + 3 * (size_t)pix, rgb); pix = -1; }
     }
   }
 }
