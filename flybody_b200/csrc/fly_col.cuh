@@ -467,7 +467,7 @@ FLY_INL bool fly_pair_is_convex(int t1, int t2) {
 #define FLY_MAXHFCON 16   /* contacts kept per geom - height field pair (oracle: FLYO_MAXHFCON) */
 #define FLY_HF_OFF (FLY_PORTAL_WORDS + 24 * FLY_NL)   /* float64 words of efc_A in front of the height-field contact slices */
 template <class T> FLY_INL int fly_hfield_pair(const DModel<T>& m, const Ws<T>& w, const T* c2, const T* m2, const T* s2, int t2,
-                                               double margin, double* out);
+                                               double margin, double* out, int g2id);
 
 template <class T>
 FLY_FN void fly_collision(const DModel<T>& m, const Ws<T>& w) {
@@ -543,7 +543,7 @@ FLY_FN void fly_collision(const DModel<T>& m, const Ws<T>& w) {
         /* terrain of the vision-guided flight task (fly_hfield.cuh): up to FLY_MAXHFCON contacts, kept in this lane's slice of
            the scratch behind the portal words (float64, like every convex pair) */
         double* hb = (double*)w.efc_A + FLY_HF_OFF + (size_t)l * (7 * FLY_MAXHFCON);
-        n = fly_hfield_pair(m, w, c2, m2, s2, t2, (double)margin, hb);
+        n = fly_hfield_pair(m, w, c2, m2, s2, t2, (double)margin, hb, g2);
       } else if (t1 == FLYB_GEOM_PLANE) {
         if (t2 == FLYB_GEOM_SPHERE) n = hit_plane_sphere(h, c1, a1, c2, s2[0], margin);
         else if (t2 == FLYB_GEOM_CAPSULE) n = hit_plane_capsule(h, c1, a1, c2, a2, s2, margin);

@@ -79,12 +79,37 @@ FLY_INL int fly_hfield_narrow(const FlyHfield& hf, int type, const double* c2, c
  * terrain this env flies over - w.counts[FLY_C_TERRAIN] of the pool m.hf_pool; out: dist, pos(3), normal(3) per contact */
 template <class T>
 FLY_INL int fly_hfield_pair(const DModel<T>& m, const Ws<T>& w, const T* c2, const T* m2, const T* s2, int t2, double margin,
-                            double* out) {
+                            double* out, int g2id) {
   if (!m.hf_pool) return 0;
+  const int g = m.hfield_geom;
+  if (m.hf_bmax && m.hfield_size[2] == 1.0) {
+    /* working-precision reject (cannot change the result): the prism tops reach at most the block maximum (+ margin), so a geom
+       whose bounding sphere, margin included, ends above the maxima of the blocks under it has no contact.  The table holds
+       max(height + z of the geom, 0) per block of cells of an axis-aligned field */
+    T hm[9];
+    fly_geom_xmat(m, w, g, hm);
+    if (hm[0] == T(1) && hm[4] == T(1) && hm[8] == T(1) && fabs_(w.geom_xpos[3 * g + 2] + T(0.01)) < T(1e-6)) {   /* the table's frame */
+      const T rb = m.geom_rbound[g2id] + (T)margin + T(1e-5);
+      const T sx = (T)m.hfield_size[0], sy = (T)m.hfield_size[1];
+      const T dx = 2 * sx / (m.hfield_ncol - 1), dy = 2 * sy / (m.hfield_nrow - 1);
+      const T px = c2[0] - w.geom_xpos[3 * g], py = c2[1] - w.geom_xpos[3 * g + 1];
+      int c0 = (int)floor((px - rb + sx) / dx) - 1, c1 = (int)ceil((px + rb + sx) / dx) + 1;
+      int r0 = (int)floor((py - rb + sy) / dy) - 1, r1 = (int)ceil((py + rb + sy) / dy) + 1;
+      if (c1 >= 0 && r1 >= 0 && c0 <= m.hfield_ncol - 1 && r0 <= m.hfield_nrow - 1) {
+        c0 = c0 < 0 ? 0 : c0; r0 = r0 < 0 ? 0 : r0;
+        c1 = c1 > m.hfield_ncol - 2 ? m.hfield_ncol - 2 : c1; r1 = r1 > m.hfield_nrow - 2 ? m.hfield_nrow - 2 : r1;
+        /* the finer of the two tables: blocks of 4 x 4 cells (0.4 cm), behind the [hf_nbr, hf_nbc] table of the 16 x 16 blocks */
+        const float* tb = m.hf_bmax + (size_t)w.counts[FLY_C_TERRAIN] * m.hf_bstride + (size_t)m.hf_nbr * m.hf_nbc;
+        float top = 0.f;
+        for (int br = r0 >> 2; br <= (r1 >> 2); br++)
+          for (int bc = c0 >> 2; bc <= (c1 >> 2); bc++) top = fmax_(top, tb[br * m.hf_nbc2 + bc]);
+        if (c2[2] - rb > (T)top) return 0;
+      }
+    }
+  }
   FlyHfield hf;
   hf.data = m.hf_pool + (size_t)w.counts[FLY_C_TERRAIN] * m.hfield_nrow * m.hfield_ncol;
   hf.nrow = m.hfield_nrow; hf.ncol = m.hfield_ncol;
-  const int g = m.hfield_geom;
   for (int k = 0; k < 3; k++) hf.pos[k] = (double)w.geom_xpos[3 * g + k];
   T hm[9];
   fly_geom_xmat(m, w, g, hm);

@@ -89,6 +89,10 @@ struct DModel {
   const float* hf_pool;        /* [nterrain, hfield_nrow, hfield_ncol] heights */
   const double* trench_meta;   /* [nterrain, 3]: points of the centre line (0: no trench), x of the first, x of the last */
   const float* trench_y;       /* [nterrain, trench_stride] centre line y */
+  const float* hf_bmax;        /* nullable: per terrain, max(height + geom z, 0) over blocks of 16 x 16 cells [hf_nbr, hf_nbc] (the eye
+                                  renderer's table): lets the narrow phase drop a geom that flies above everything under it */
+  int hf_nbr, hf_nbc, hf_nbc2;   /* blocks of 16 x 16 cells; columns of the table of 4 x 4 blocks that follows it */
+  long long hf_bstride;        /* floats per terrain in hf_bmax */
   T timestep, density, viscosity, tolerance, ls_tolerance, noslip_tolerance, impratio, meaninertia;
   T control_dt, terminal_linvel, terminal_angvel, terminal_com_dist, terminal_qacc, terminal_height;
 #define X(n) const int* n;

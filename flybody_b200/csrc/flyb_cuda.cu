@@ -591,7 +591,7 @@ int flyb_load_terrain(flyb_handle h, const float* heights, int n_terrains, const
       if (trench_meta[3 * t] < 0 || trench_meta[3 * t] > trench_stride) { h->err = "flyb_load_terrain: trench centre line longer than trench_stride"; return 1; }
   cudaFree(h->d_hf); cudaFree(h->d_trench_meta); cudaFree(h->d_trench_y); cudaFree(h->d_hf_bmax);
   h->d_hf = nullptr; h->d_trench_meta = nullptr; h->d_trench_y = nullptr; h->d_hf_bmax = nullptr;
-  h->m.hf_pool = nullptr; h->m.trench_meta = nullptr; h->m.trench_y = nullptr; h->m.nterrain = 0;
+  h->m.hf_pool = nullptr; h->m.trench_meta = nullptr; h->m.trench_y = nullptr; h->m.nterrain = 0; h->m.hf_bmax = nullptr;
   const size_t nd = (size_t)n_terrains * h->m.hfield_nrow * h->m.hfield_ncol;
   CK(cudaMalloc(&h->d_hf, nd * sizeof(float)));
   CK(cudaMemcpy(h->d_hf, heights, nd * sizeof(float), cudaMemcpyHostToDevice));
@@ -614,6 +614,7 @@ int flyb_load_terrain(flyb_handle h, const float* heights, int n_terrains, const
     fly_eyes_gmax_kernel<<<(n_terrains + 127) / 128, 128>>>(h->d_hf_bmax, n_terrains, nbr * nbc, stride);
     CK(cudaGetLastError());
     CK(cudaDeviceSynchronize());
+    h->m.hf_bmax = h->d_hf_bmax; h->m.hf_nbr = nbr; h->m.hf_nbc = nbc; h->m.hf_nbc2 = nbc2; h->m.hf_bstride = (long long)stride;
   }
   if (!h->d_eyes) {
     CK(cudaMalloc(&h->d_eyes, (size_t)h->num_envs * 24 * sizeof(float)));

@@ -13,7 +13,9 @@ dev = torch.device("cuda:0")
 M = load_model(asset_path("vision_flight"))
 eng = Engine(M, N, 0, seed=1)
 eng.load_wbpg(W.build_tables(W.synthetic_base_pattern()))
-eng.load_terrain(T.pack_pool(T.terrain_table(kind, 16, seed=0)))
+noterrain = bool(os.environ.get("NOTERRAIN"))     # experiment: what the height-field narrow phase costs (no pool: its pairs return at once)
+if not noterrain:
+    eng.load_terrain(T.pack_pool(T.terrain_table(kind, 16, seed=0)))
 A, O = eng.action_dim, eng.obs_dim
 obs = torch.zeros((N, O), device=dev); rew = torch.zeros(N, device=dev); disc = torch.zeros(N, device=dev)
 st = torch.zeros(N, dtype=torch.int32, device=dev)
@@ -28,7 +30,10 @@ ts, tr = [], []
 for k in range(30):
     a, b, c = ev(), ev(), ev()
     a.record(); eng.step_ptr(pool[k % 8].data_ptr(), obs.data_ptr(), rew.data_ptr(), disc.data_ptr(), st.data_ptr(), s)
-    b.record(); eng.render_ptr(eyes.data_ptr(), stream=s); c.record()
+    b.record()
+    if not noterrain:
+        eng.render_ptr(eyes.data_ptr(), stream=s)
+    c.record()
     torch.cuda.synchronize()
     if k >= 10:
         ts.append(a.elapsed_time(b)); tr.append(b.elapsed_time(c))
