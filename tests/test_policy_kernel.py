@@ -77,6 +77,35 @@ def test_fused_policy_matches_the_torch_module(obs_dim, act_dim, rows):
     fused.close()
 
 
+def test_fused_policy_head_options():
+    """tanh_mean and fixed_scale of the head (network_factory.py:90-98 passes them through to MultivariateNormalDiagHead)."""
+    from flybody_b200 import actors as A
+    torch.manual_seed(3)
+    dev = torch.device("cuda:0")
+    obs = torch.randn((200, 104), device=dev)
+    for kw in (dict(tanh_mean=True), dict(fixed_scale=True, init_scale=0.3), dict(min_scale=0.05, init_scale=1.2)):
+        pol = A.LayerNormMLPPolicy(104, 12, **kw).to(dev)
+        with torch.no_grad():
+            for lin in (pol.mean, pol.scale):
+                lin.weight.normal_(std=2.0 / math.sqrt(512)); lin.bias.normal_(std=0.5)
+        fused = A.FusedPolicy(pol, max_rows=256)
+        with torch.no_grad():
+            mean, scale = fused(obs)
+            m32, s32 = pol(obs)
+        assert float((mean - m32).abs().max()) < 3e-2 * max(1.0, float(m32.abs().max())), kw
+        assert float((scale - s32).abs().max()) < 3e-2 * max(1.0, float(s32.abs().max())), kw
+        if kw.get("tanh_mean"):
+            assert float(mean.abs().max()) <= 1.0
+        if kw.get("fixed_scale"):
+            assert float((scale - 0.3).abs().max()) == 0.0
+        g = torch.Generator(device=dev); g.manual_seed(1)
+        a = fused.sample(obs, g)
+        g.manual_seed(1)
+        eps = torch.randn((200, 12), device=dev, generator=g)
+        assert float((a - (mean + scale * eps)).abs().max()) < 1e-5 * max(1.0, float(a.abs().max())), kw
+        fused.close()
+
+
 def test_actor_loop_with_the_fused_policy():
     """config 4 (BASELINE.json configs[3]): the batched environment loop with the kernel as the actor's policy."""
     from flybody_b200 import actors as A, fly_envs
