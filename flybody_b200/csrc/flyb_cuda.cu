@@ -341,6 +341,7 @@ int flyb_create(const FlybModel* model, int num_envs, int device, uint64_t seed,
   cudaDeviceProp prop;
   if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return fail("cudaGetDeviceProperties failed");
   h->sm_count = prop.multiProcessorCount;
+  { const char* e = getenv("FLYB_SM_LIMIT"); if (e && atoi(e) > 0 && atoi(e) < h->sm_count) h->sm_count = atoi(e); }   /* kernel experiments: blocks on fewer SMs */
   {  /* set-up of flyb_step_noalloc: device address of the static scratch, once per device, with that device current */
     std::string e;
     h->noalloc_scratch = noalloc_scratch_of(device, &e);

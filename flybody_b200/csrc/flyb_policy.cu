@@ -39,6 +39,7 @@ constexpr int PNH = 256;           /* N per MMA instruction */
 constexpr int PSTAGES = 3;
 constexpr int PA_BYTES = PM * PKC * 2;      /* 16 KB: an A tile (128 rows x 64 bf16) */
 constexpr int PB_BYTES = PNH * PKC * 2;     /* 32 KB: a B tile (256 weight rows x 64 bf16) */
+constexpr int PCLUSTER = 2;                 /* CTAs per cluster: each loads 1 / PCLUSTER of a weight tile and multicasts it to all of them */
 constexpr int PSTAGE_BYTES = PB_BYTES;       /* a stage holds a B tile; the first layer's A tile of the stage lies in the (then unused) activation buffer */
 constexpr int PACT_BYTES = PM * PH * 2;     /* 128 KB */
 constexpr int PHEAD_N = 128;                /* head output columns: mean at 0.., scale at 64.. */
@@ -54,6 +55,8 @@ struct PolicyParams {
   const float* eps;                /* nullable [N, A] */
   float* mean; float* scale; float* action;   /* each nullable, [N, A] */
   int n_rows, act_dim, nk1;        /* nk1: K chunks of the first layer (obs_dim padded to 64) */
+  const uint8_t* xb; uint32_t x_row_bytes;       /* the bf16 observations, for the L2 warm-up */
+  const uint8_t* w_ptr[5]; uint32_t w_bytes[5];  /* the bf16 weight matrices, likewise */
   float ln_eps, scale_mul, min_scale;
   int tanh_mean;
 };
@@ -84,6 +87,11 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
   asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
                ::"r"(dst), "l"(map), "r"(x), "r"(y), "r"(bar) : "memory");
 }
+/* the same, delivered to the same shared-memory offset (and signalled on the barrier at the same offset) of every CTA in `mask` */
+__device__ __forceinline__ void tma_load_2d_mc(uint32_t dst, const CUtensorMap* map, int x, int y, uint32_t bar, uint16_t mask) {
+  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%2, %3}], [%4], %5;"
+               ::"r"(dst), "l"(map), "r"(x), "r"(y), "r"(bar), "h"(mask) : "memory");
+}
 /* shared-memory matrix descriptor, K-major, SWIZZLE_128B: start >> 4 | LBO (unused) | SBO = 1024 B (8 rows x 128 B) | version 1 */
 __device__ __forceinline__ uint64_t umma_desc(uint32_t addr) {
   return (uint64_t)((addr & 0x3FFFF) >> 4) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
@@ -99,6 +107,13 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint6
 }
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+/* ... arriving on the barrier at this offset in every CTA of `mask` */
+__device__ __forceinline__ void umma_commit_mc(uint32_t bar, uint16_t mask) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar), "h"(mask) : "memory");
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release;\n\tbarrier.cluster.wait.acquire;" ::: "memory");
 }
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float* v) {
   uint32_t r[32];
@@ -122,45 +137,74 @@ __device__ __forceinline__ float fast_tanh(float x) {
   asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
-__device__ __forceinline__ float fast_elu(float x) { return x > 0.f ? x : __expf(x) - 1.0f; }
+/* ELU without the range handling of __expf (12 instructions and a predicate shuffle per value in the first version): ex2 of a
+   large positive argument is +inf and is not selected */
+__device__ __forceinline__ float fast_elu(float x) {
+  float t;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(x * 1.4426950408889634f));
+  return x > 0.f ? x : t - 1.0f;
+}
 __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
   __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&h);
 }
-/* 32 activations of row r, columns [32 c, 32 c + 32), into the A-operand buffer: K chunk c / 2, 16-byte groups swizzled by row */
-__device__ __forceinline__ void store_act32(uint8_t* act, int r, int c, const float* y) {
-  uint8_t* row = act + (c >> 1) * PA_BYTES + r * 128;
-  const int g0 = (c & 1) * 4;
+/* 32 activations of a row as the four 16-byte groups of the A-operand buffer */
+__device__ __forceinline__ void pack_act32(const float* y, uint4* q) {
 #pragma unroll
   for (int g = 0; g < 4; g++) {
-    uint4 q;
-    q.x = pack_bf16(y[8 * g + 0], y[8 * g + 1]); q.y = pack_bf16(y[8 * g + 2], y[8 * g + 3]);
-    q.z = pack_bf16(y[8 * g + 4], y[8 * g + 5]); q.w = pack_bf16(y[8 * g + 6], y[8 * g + 7]);
-    *reinterpret_cast<uint4*>(row + (((g0 + g) ^ (r & 7)) << 4)) = q;
+    q[g].x = pack_bf16(y[8 * g + 0], y[8 * g + 1]); q[g].y = pack_bf16(y[8 * g + 2], y[8 * g + 3]);
+    q[g].z = pack_bf16(y[8 * g + 4], y[8 * g + 5]); q[g].w = pack_bf16(y[8 * g + 6], y[8 * g + 7]);
   }
 }
+/* ... of row r, columns [32 c, 32 c + 32): K chunk c / 2, 16-byte groups swizzled by row (act_s: shared-space address of the buffer) */
+__device__ __forceinline__ void store_packed32(uint32_t act_s, int r, int c, const uint4* q) {
+  const uint32_t row = act_s + (c >> 1) * PA_BYTES + r * 128;
+  const int g0 = (c & 1) * 4;
+#pragma unroll
+  for (int g = 0; g < 4; g++)
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(row + (((g0 + g) ^ (r & 7)) << 4)), "r"(q[g].x), "r"(q[g].y),
+                 "r"(q[g].z), "r"(q[g].w) : "memory");
+}
 
-__global__ void __launch_bounds__(PTHREADS, 1)
+__device__ __forceinline__ void sts_f32(uint32_t addr, float x) { asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(x) : "memory"); }
+__device__ __forceinline__ float lds_f32(uint32_t addr) {
+  float x;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(x) : "r"(addr) : "memory");
+  return x;
+}
+
+#ifdef FLY_POLICY_PROF   /* kernel experiments: clock64 stamps of two CTAs, read by flyb_policy_prof_dump */
+__device__ long long g_pprof[2][6][6];   /* [5][.]: stamps inside the head epilogue */
+#define PPROF(slot, l, val) do { if (blockIdx.x == 0 || blockIdx.x == 100) g_pprof[blockIdx.x ? 1 : 0][l][slot] = (val); } while (0)
+#else
+#define PPROF(slot, l, val) do { } while (0)
+#endif
+
+__global__ void __cluster_dims__(PCLUSTER, 1, 1) __launch_bounds__(PTHREADS, 1)
 fly_policy_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w1,
                   const __grid_constant__ CUtensorMap map_w2, const __grid_constant__ CUtensorMap map_w3,
                   const __grid_constant__ CUtensorMap map_w4, const __grid_constant__ CUtensorMap map_wh,
                   const __grid_constant__ PolicyParams p) {
   extern __shared__ uint8_t smem_raw[];
+  if (threadIdx.x == PEPI_THREADS + 32) PPROF(4, 5, clock64());
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* act = smem;                                   /* 8 chunks x 16 KB */
   uint8_t* stage = smem + PACT_BYTES;                    /* PSTAGES x 32 KB B tiles */
   uint64_t* bars = reinterpret_cast<uint64_t*>(stage + PSTAGES * PSTAGE_BYTES);
-  /* bars: full[PSTAGES], empty[PSTAGES], acc_full, act_ready ; then the TMEM base address */
+  /* bars: full[PSTAGES], empty[PSTAGES], acc[2] (an N half of the layer is complete), ka (the second half's MMAs are past K chunk 3),
+     epi[2] (the epilogue has drained an N half from TMEM and written its activations) ; then the TMEM base address */
   const uint32_t bar_full = smem_u32(bars), bar_empty = smem_u32(bars + PSTAGES);
-  const uint32_t bar_acc = smem_u32(bars + 2 * PSTAGES), bar_act = smem_u32(bars + 2 * PSTAGES + 1);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * PSTAGES + 2);
+  const uint32_t bar_acc = smem_u32(bars + 2 * PSTAGES), bar_ka = smem_u32(bars + 2 * PSTAGES + 2);
+  const uint32_t bar_epi = smem_u32(bars + 2 * PSTAGES + 3);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * PSTAGES + 5);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row0 = blockIdx.x * PM;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < PSTAGES; s++) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, 1); }
-    mbar_init(bar_acc, 1);
-    mbar_init(bar_act, PEPI_THREADS);
+    for (int s = 0; s < PSTAGES; s++) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, PCLUSTER); }
+    mbar_init(bar_acc, 1); mbar_init(bar_acc + 8, 1);
+    mbar_init(bar_ka, 1);
+    mbar_init(bar_epi, PEPI_THREADS); mbar_init(bar_epi + 8, PEPI_THREADS);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == PEPI_WARPS) {   /* the allocating warp also frees: all 512 columns (one CTA per SM: nothing to contend with) */
@@ -171,9 +215,20 @@ fly_policy_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem = *tmem_slot;
+  /* The CTAs of a cluster walk the weight tiles together: every CTA fetches its 1 / PCLUSTER of the rows of a tile and multicasts
+     them into the same stage of all, so a stage is reloaded once every CTA's MMAs have released it (empty: PCLUSTER arrivals, by
+     multicast commit).  Halves the L2 -> SM traffic per CTA, which bounded the MMA phases. */
+  uint32_t cta_rank;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(cta_rank));
+  constexpr uint16_t kAll = (uint16_t)((1u << PCLUSTER) - 1);
+  cluster_sync_all();   /* the barriers of every CTA are initialised before a peer signals them */
 
-  /* the item sequence both pipeline ends walk: layer 0: 2 N-halves x nk1 chunks (A + B tiles); layers 1-3: 2 x 8 (B only, A =
-     the activation buffer); layer 4 = the head: 8 chunks of a 128-row B tile */
+  /* The item sequence both pipeline ends walk: layer 0: 2 N halves x nk1 chunks (A + B tiles); layers 1-3: 2 x 8 (B only, A =
+     the activation buffer); layer 4 = the head: 8 chunks of a 128-row B tile.
+     MMA and epilogue overlap by halves.  TMEM holds one layer's accumulators (2 halves of 256 columns) and the activation buffer one
+     layer's input, so: the epilogue of half 0 runs while the MMAs of half 1 are issued, and stores into K chunks 0-3 once those
+     MMAs are past them (ka); the next layer's half 0 starts on K chunks 0-3 as soon as the epilogue of half 0 has written them and
+     drained its TMEM columns (epi[0]) - i.e. during the epilogue of half 1 - and goes on to chunks 4-7 after epi[1]. */
   if (warp == PEPI_WARPS && lane == 0) {
     /* ------------------------------------------------------------------------------------------------ TMA producer */
     const CUtensorMap* wmap[5] = {&map_w1, &map_w2, &map_w3, &map_w4, &map_wh};
@@ -186,9 +241,10 @@ fly_policy_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
           mbar_wait(bar_empty + 8 * s, ((it / PSTAGES) & 1) ^ 1);
           const uint32_t a_dst = smem_u32(act + s * PA_BYTES), b_dst = smem_u32(stage + s * PSTAGE_BYTES);
           const uint32_t bytes = (l == 0 ? PA_BYTES : 0) + (l == 4 ? PHEAD_N * PKC * 2 : PB_BYTES);
-          mbar_expect_tx(bar_full + 8 * s, bytes);
+          mbar_expect_tx(bar_full + 8 * s, bytes);   /* (a peer's share may land before this: the transaction count runs negative until then) */
           if (l == 0) tma_load_2d(a_dst, &map_x, kc * PKC, row0, bar_full + 8 * s);
-          tma_load_2d(b_dst, wmap[l], kc * PKC, nh * PNH, bar_full + 8 * s);
+          const int share = (l == 4 ? PHEAD_N : PNH) / PCLUSTER;   /* weight rows this CTA fetches */
+          tma_load_2d_mc(b_dst + cta_rank * share * 128, wmap[l], kc * PKC, nh * PNH + cta_rank * share, bar_full + 8 * s, kAll);
         }
     }
   } else if (warp == PEPI_WARPS + 1 && lane == 0) {
@@ -196,119 +252,214 @@ fly_policy_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
     int it = 0;
     for (int l = 0; l < 5; l++) {
       const int nk = l == 0 ? p.nk1 : PH / PKC, nhalf = l == 4 ? 1 : 2;
+      const int kka = nk - 1 < 3 ? nk - 1 : 3;
       const uint32_t idesc = l == 4 ? umma_idesc(PM, PHEAD_N) : umma_idesc(PM, PNH);
-      if (l > 0) {   /* the epilogue has drained TMEM and written this layer's A operand */
-        mbar_wait(bar_act, (l - 1) & 1);
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-      }
-      for (int nh = 0; nh < nhalf; nh++)
+#ifdef FLY_POLICY_PROF
+      long long wfull = 0;
+#endif
+      PPROF(0, l, clock64());
+      for (int nh = 0; nh < nhalf; nh++) {
         for (int kc = 0; kc < nk; kc++, it++) {
+          if (l > 0 && nh == 0 && (kc == 0 || kc == 4)) {   /* K chunks 0-3 (4-7) of this layer's input are written, TMEM half 0 (1) is drained */
+            mbar_wait(bar_epi + (kc ? 8 : 0), (l - 1) & 1);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          }
           const int s = it % PSTAGES;
+#ifdef FLY_POLICY_PROF
+          const long long tw = clock64();
+#endif
           mbar_wait(bar_full + 8 * s, (it / PSTAGES) & 1);
+#ifdef FLY_POLICY_PROF
+          if (kc == 0 && nh == 0) PPROF(1, l, tw);
+          wfull += clock64() - tw;
+#endif
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
           const uint32_t a_base = l == 0 ? smem_u32(act + s * PA_BYTES) : smem_u32(act + kc * PA_BYTES);
           const uint32_t b_base = smem_u32(stage + s * PSTAGE_BYTES);
 #pragma unroll
           for (int k = 0; k < PKC / 16; k++)   /* UMMA K = 16 bf16 = 32 bytes along the swizzled row */
             umma_bf16(tmem + nh * PNH, umma_desc(a_base + 32 * k), umma_desc(b_base + 32 * k), idesc, (kc | k) != 0);
-          umma_commit(bar_empty + 8 * s);     /* frees the stage once these MMAs have read it */
+          umma_commit_mc(bar_empty + 8 * s, kAll);   /* releases the stage in every CTA of the cluster once these MMAs have read it */
+          if (l < 4 && nh == 1 && kc == kka) umma_commit(bar_ka);
         }
-      umma_commit(bar_acc);                   /* the layer's accumulator is complete */
+        umma_commit(bar_acc + 8 * nh);        /* this half of the layer's accumulator is complete */
+      }
+      PPROF(2, l, wfull); PPROF(3, l, clock64());
     }
   } else if (warp < PEPI_WARPS) {
     /* ---------------------------------------------------------------------------------------------------- epilogue */
     const int q = warp & 3, cg = warp >> 2;                /* quarter of the TMEM lanes this warp may read; its column group */
     const int r = q * 32 + lane;                           /* row of the tile = TMEM lane */
     const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16);
-    const int c0 = cg * (PH / 32 / 4), c1 = c0 + PH / 32 / 4;   /* its chunks of 32 columns */
-    float* red = reinterpret_cast<float*>(act);            /* LayerNorm partial sums [4 column groups][128 rows][2] (act is free then) */
+    const uint32_t act_s = smem_u32(act);
+    /* per N half the thread takes the two 32-column chunks 8 h + 2 cg + {0, 1} of its row, i.e. K chunk 4 h + cg of the next layer */
+    const uint32_t red = act_s + 4 * PA_BYTES;                   /* LayerNorm partial sums [4 column groups][128 rows][2]: K chunk 4 is
+                                                                    neither a staging slot of layer 0's A tiles nor written before the sums are read */
     float v[32];
-    for (int l = 0; l < 5; l++) {
-      mbar_wait(bar_acc, l & 1);
-      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    {   /* L2 warm-up while the first tiles are on their way: the TMA ring holds three tiles, so a tile that misses L2 costs a DRAM
+           round trip per three items.  These warps are idle until the first half of layer 0 is done: they ask for the CTA's own
+           observation rows and for its 1 / gridDim.x of every weight matrix, a line per thread. */
+      const uint8_t* xp = p.xb + (size_t)row0 * p.x_row_bytes;
+      const uint32_t xbytes = PM * p.x_row_bytes;
+      for (uint32_t o = threadIdx.x * 128u; o < xbytes; o += PEPI_THREADS * 128u)
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(xp + o));
+#pragma unroll
+      for (int w = 0; w < 5; w++) {
+        const uint32_t share = ((p.w_bytes[w] + gridDim.x - 1) / gridDim.x + 127u) & ~127u;
+        const uint32_t lo = blockIdx.x * share, hi = lo + share < p.w_bytes[w] ? lo + share : p.w_bytes[w];
+        for (uint32_t o = lo + threadIdx.x * 128u; o < hi; o += PEPI_THREADS * 128u)
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(p.w_ptr[w] + o));
+      }
+    }
+    for (int l = 0; l < 4; l++) {
       if (l == 0) {         /* bias, LayerNorm over the 512 features of the row, tanh */
         float sum = 0, sq = 0;
-        for (int c = c0; c < c1; c++) {
-          tmem_ld32(trow + 32 * c, v);
+        for (int h = 0; h < 2; h++) {
+          mbar_wait(bar_acc + 8 * h, 0);
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          if (threadIdx.x == 0 && h == 0) PPROF(4, l, clock64());
+          for (int j = 0; j < 2; j++) {
+            const int c = 8 * h + 2 * cg + j;
+            tmem_ld32(trow + 32 * c, v);
 #pragma unroll
-          for (int j4 = 0; j4 < 8; j4++) {
-            const float4 b = __ldg(reinterpret_cast<const float4*>(p.b1 + 32 * c) + j4);
-            const float x0 = v[4 * j4] + b.x, x1 = v[4 * j4 + 1] + b.y, x2 = v[4 * j4 + 2] + b.z, x3 = v[4 * j4 + 3] + b.w;
-            sum += (x0 + x1) + (x2 + x3);
-            sq += (x0 * x0 + x1 * x1) + (x2 * x2 + x3 * x3);
+            for (int j4 = 0; j4 < 8; j4++) {
+              const float4 b = __ldg(reinterpret_cast<const float4*>(p.b1 + 32 * c) + j4);
+              const float x0 = v[4 * j4] + b.x, x1 = v[4 * j4 + 1] + b.y, x2 = v[4 * j4 + 2] + b.z, x3 = v[4 * j4 + 3] + b.w;
+              sum += (x0 + x1) + (x2 + x3);
+              sq += (x0 * x0 + x1 * x1) + (x2 * x2 + x3 * x3);
+            }
           }
         }
-        red[(cg * PM + r) * 2] = sum; red[(cg * PM + r) * 2 + 1] = sq;
+        sts_f32(red + (cg * PM + r) * 8, sum); sts_f32(red + (cg * PM + r) * 8 + 4, sq);
         asm volatile("bar.sync 1, %0;" ::"n"(PEPI_THREADS) : "memory");
         sum = 0; sq = 0;
 #pragma unroll
-        for (int g = 0; g < 4; g++) { sum += red[(g * PM + r) * 2]; sq += red[(g * PM + r) * 2 + 1]; }
+        for (int g = 0; g < 4; g++) { sum += lds_f32(red + (g * PM + r) * 8); sq += lds_f32(red + (g * PM + r) * 8 + 4); }
         asm volatile("bar.sync 1, %0;" ::"n"(PEPI_THREADS) : "memory");   /* everyone has read the sums: act may be written */
         const float mu = sum * (1.0f / PH);
         const float var = fmaxf(sq * (1.0f / PH) - mu * mu, 0.f);
         const float rstd = rsqrtf(var + p.ln_eps);
-        for (int c = c0; c < c1; c++) {
-          tmem_ld32(trow + 32 * c, v);
+        mbar_wait(bar_ka, 0);   /* (complete: both halves are; waited on to keep the phase in step) */
+        for (int h = 0; h < 2; h++) {
+          for (int j = 0; j < 2; j++) {
+            const int c = 8 * h + 2 * cg + j;
+            tmem_ld32(trow + 32 * c, v);
 #pragma unroll
-          for (int j4 = 0; j4 < 8; j4++) {
-            const float4 b = __ldg(reinterpret_cast<const float4*>(p.b1 + 32 * c) + j4);
-            const float4 g = __ldg(reinterpret_cast<const float4*>(p.ln_g + 32 * c) + j4);
-            const float4 e = __ldg(reinterpret_cast<const float4*>(p.ln_b + 32 * c) + j4);
-            v[4 * j4 + 0] = fast_tanh((v[4 * j4 + 0] + b.x - mu) * rstd * g.x + e.x);
-            v[4 * j4 + 1] = fast_tanh((v[4 * j4 + 1] + b.y - mu) * rstd * g.y + e.y);
-            v[4 * j4 + 2] = fast_tanh((v[4 * j4 + 2] + b.z - mu) * rstd * g.z + e.z);
-            v[4 * j4 + 3] = fast_tanh((v[4 * j4 + 3] + b.w - mu) * rstd * g.w + e.w);
-          }
-          store_act32(act, r, c, v);
-        }
-      } else if (l < 4) {   /* bias, ELU */
-        const float* bl = p.b[l - 1];
-        for (int c = c0; c < c1; c++) {
-          tmem_ld32(trow + 32 * c, v);
-#pragma unroll
-          for (int j4 = 0; j4 < 8; j4++) {
-            const float4 b = __ldg(reinterpret_cast<const float4*>(bl + 32 * c) + j4);
-            v[4 * j4 + 0] = fast_elu(v[4 * j4 + 0] + b.x); v[4 * j4 + 1] = fast_elu(v[4 * j4 + 1] + b.y);
-            v[4 * j4 + 2] = fast_elu(v[4 * j4 + 2] + b.z); v[4 * j4 + 3] = fast_elu(v[4 * j4 + 3] + b.w);
-          }
-          store_act32(act, r, c, v);
-        }
-      } else if (cg < 2) {  /* heads: mean | scale (columns 64..), sampled action; two column groups of 32 */
-        const int row = row0 + r, c = cg;
-        float s[32];
-        tmem_ld32(trow + 32 * c, v);
-        tmem_ld32(trow + 64 + 32 * c, s);
-        if (row < p.n_rows) {
-#pragma unroll
-          for (int j = 0; j < 32; j++) {
-            const int col = 32 * c + j;
-            if (col < p.act_dim) {
-              float mean = v[j] + __ldg(p.bm + col);
-              if (p.tanh_mean) mean = tanhf(mean);
-              const float x = s[j] + __ldg(p.bs + col);
-              const float sp = x > 20.f ? x : log1pf(expf(x));
-              const float scale = sp * p.scale_mul + p.min_scale;
-              const size_t o = (size_t)row * p.act_dim + col;
-              if (p.mean) p.mean[o] = mean;
-              if (p.scale) p.scale[o] = scale;
-              if (p.action) p.action[o] = mean + scale * (p.eps ? p.eps[o] : 0.f);
+            for (int j4 = 0; j4 < 8; j4++) {
+              const float4 b = __ldg(reinterpret_cast<const float4*>(p.b1 + 32 * c) + j4);
+              const float4 g = __ldg(reinterpret_cast<const float4*>(p.ln_g + 32 * c) + j4);
+              const float4 e = __ldg(reinterpret_cast<const float4*>(p.ln_b + 32 * c) + j4);
+              v[4 * j4 + 0] = fast_tanh((v[4 * j4 + 0] + b.x - mu) * rstd * g.x + e.x);
+              v[4 * j4 + 1] = fast_tanh((v[4 * j4 + 1] + b.y - mu) * rstd * g.y + e.y);
+              v[4 * j4 + 2] = fast_tanh((v[4 * j4 + 2] + b.z - mu) * rstd * g.z + e.z);
+              v[4 * j4 + 3] = fast_tanh((v[4 * j4 + 3] + b.w - mu) * rstd * g.w + e.w);
             }
+            uint4 qq[4];
+            pack_act32(v, qq);
+            store_packed32(act_s, r, c, qq);
           }
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   /* generic-proxy stores -> visible to the tensor core */
+          asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+          mbar_arrive(bar_epi + 8 * h);
+        }
+      } else {              /* bias, ELU */
+        const float* bl = p.b[l - 1];
+        for (int h = 0; h < 2; h++) {
+          mbar_wait(bar_acc + 8 * h, l & 1);
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          if (threadIdx.x == 0 && h == 0) PPROF(4, l, clock64());
+          uint4 qq[2][4];
+#pragma unroll
+          for (int j = 0; j < 2; j++) {
+            const int c = 8 * h + 2 * cg + j;
+            tmem_ld32(trow + 32 * c, v);
+#pragma unroll
+            for (int j4 = 0; j4 < 8; j4++) {
+              const float4 b = __ldg(reinterpret_cast<const float4*>(bl + 32 * c) + j4);
+              v[4 * j4 + 0] = fast_elu(v[4 * j4 + 0] + b.x); v[4 * j4 + 1] = fast_elu(v[4 * j4 + 1] + b.y);
+              v[4 * j4 + 2] = fast_elu(v[4 * j4 + 2] + b.z); v[4 * j4 + 3] = fast_elu(v[4 * j4 + 3] + b.w);
+            }
+            pack_act32(v, qq[j]);
+          }
+          if (h == 0) mbar_wait(bar_ka, l & 1);   /* the MMAs of half 1 have read K chunks 0-3: they may be overwritten */
+#pragma unroll
+          for (int j = 0; j < 2; j++) store_packed32(act_s, r, 8 * h + 2 * cg + j, qq[j]);
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+          asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+          mbar_arrive(bar_epi + 8 * h);
         }
       }
-      if (l < 4) {
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   /* generic-proxy stores -> visible to the tensor core */
-        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-        mbar_arrive(bar_act);
+      if (threadIdx.x == 0) PPROF(5, l, clock64());
+    }
+    {   /* heads: mean (TMEM columns 0..63) | scale (64..127).  Every warp takes 32 columns of one of them; the values go through shared
+           memory (the activation buffer is free: all MMAs are complete) so that the three outputs - a contiguous block of
+           128 x act_dim floats each - leave as coalesced stores */
+      const int rows_here = p.n_rows - row0 < PM ? p.n_rows - row0 : PM;
+      const int valid = rows_here * p.act_dim;
+      const size_t o0 = (size_t)row0 * p.act_dim;
+      constexpr int kPer = PM * 64 / PEPI_THREADS;   /* output elements per thread at most */
+      float ev[kPer];                                /* the noise of this thread's output elements, fetched under the head's MMAs */
+#pragma unroll
+      for (int k = 0; k < kPer; k++) {
+        const int i = threadIdx.x + k * PEPI_THREADS;
+        ev[k] = (p.eps && i < valid) ? __ldg(p.eps + o0 + i) : 0.f;
       }
+      const bool is_scale = cg >= 2;
+      const int c = cg & 1;
+      float bv[32];                                  /* this thread's 32 biases (the vectors are zero-padded to 64) */
+#pragma unroll
+      for (int j4 = 0; j4 < 8; j4++) {
+        const float4 b = __ldg(reinterpret_cast<const float4*>((is_scale ? p.bs : p.bm) + 32 * c) + j4);
+        bv[4 * j4] = b.x; bv[4 * j4 + 1] = b.y; bv[4 * j4 + 2] = b.z; bv[4 * j4 + 3] = b.w;
+      }
+      if (threadIdx.x == 0) PPROF(0, 5, clock64());
+      mbar_wait(bar_acc, 0);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      if (threadIdx.x == 0) PPROF(4, 4, clock64());
+      const uint32_t sm_mean = act_s, sm_scale = act_s + PM * 64 * 4;
+      tmem_ld32(trow + (is_scale ? 64 : 0) + 32 * c, v);
+      if (threadIdx.x == 0) PPROF(1, 5, clock64());
+      if (is_scale) {
+#pragma unroll
+        for (int j = 0; j < 32; j++) {   /* softplus(x) * init_scale / ln 2 + min_scale */
+          const float x = v[j] + bv[j];
+          v[j] = (fmaxf(x, 0.f) + __logf(1.0f + __expf(-fabsf(x)))) * p.scale_mul + p.min_scale;
+        }
+      } else if (p.tanh_mean) {
+#pragma unroll
+        for (int j = 0; j < 32; j++) v[j] = tanhf(v[j] + bv[j]);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; j++) v[j] += bv[j];
+      }
+      const uint32_t dst = (is_scale ? sm_scale : sm_mean) + (uint32_t)(r * p.act_dim + 32 * c) * 4u;
+#pragma unroll
+      for (int j = 0; j < 32; j++)
+        if (32 * c + j < p.act_dim) sts_f32(dst + 4 * j, v[j]);
+      if (threadIdx.x == 0) PPROF(2, 5, clock64());
+      asm volatile("bar.sync 1, %0;" ::"n"(PEPI_THREADS) : "memory");
+      if (threadIdx.x == 0) PPROF(3, 5, clock64());
+#pragma unroll
+      for (int k = 0; k < kPer; k++) {
+        const int i = threadIdx.x + k * PEPI_THREADS;
+        if (i < valid) {
+          const float mean = lds_f32(sm_mean + 4 * i), scale = lds_f32(sm_scale + 4 * i);
+          if (p.mean) p.mean[o0 + i] = mean;
+          if (p.scale) p.scale[o0 + i] = scale;
+          if (p.action) p.action[o0 + i] = mean + scale * ev[k];
+        }
+      }
+      if (threadIdx.x == 0) PPROF(5, 4, clock64());
     }
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
+  cluster_sync_all();   /* no CTA leaves while a peer may still signal its barriers */
   if (warp == PEPI_WARPS) {
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512) : "memory");
   }
+  if (threadIdx.x == PEPI_THREADS + 32) PPROF(5, 5, clock64());
 }
 
 /* fp32 [rows, cols] -> bf16 [rows_pad, cols_pad], zero padded (weights once, observations every call): a block per row, a thread
@@ -389,7 +540,7 @@ int flyb_policy_create(int device, int obs_dim, int act_dim, int max_rows, flyb_
   *out = P;
   P->device = device; P->obs_dim = obs_dim; P->act_dim = act_dim;
   P->k1pad = (obs_dim + PKC - 1) / PKC * PKC;
-  P->max_rows = (max_rows + PM - 1) / PM * PM;
+  P->max_rows = (max_rows + PM * PCLUSTER - 1) / (PM * PCLUSTER) * (PM * PCLUSTER);
   PCK(cudaSetDevice(device));
   int cc_major = 0;
   PCK(cudaDeviceGetAttribute(&cc_major, cudaDevAttrComputeCapabilityMajor, device));
@@ -404,9 +555,9 @@ int flyb_policy_create(int device, int obs_dim, int act_dim, int max_rows, flyb_
   PCK(cudaMalloc(&P->vec, (size_t)(6 * PH + 128) * sizeof(float)));
   PCK(cudaMemset(P->vec, 0, (size_t)(6 * PH + 128) * sizeof(float)));
   PCK(cudaMemset(P->wh, 0, (size_t)PHEAD_N * PH * 2));
-  if (!make_map(&P->m_w1, P->w1, PH, P->k1pad, PNH) || !make_map(&P->m_w2, P->w2, PH, PH, PNH) ||
-      !make_map(&P->m_w3, P->w3, PH, PH, PNH) || !make_map(&P->m_w4, P->w4, PH, PH, PNH) ||
-      !make_map(&P->m_wh, P->wh, PHEAD_N, PH, PHEAD_N))
+  if (!make_map(&P->m_w1, P->w1, PH, P->k1pad, PNH / PCLUSTER) || !make_map(&P->m_w2, P->w2, PH, PH, PNH / PCLUSTER) ||
+      !make_map(&P->m_w3, P->w3, PH, PH, PNH / PCLUSTER) || !make_map(&P->m_w4, P->w4, PH, PH, PNH / PCLUSTER) ||
+      !make_map(&P->m_wh, P->wh, PHEAD_N, PH, PHEAD_N / PCLUSTER))
     return pfail(P, "cuTensorMapEncodeTiled failed for a weight matrix");
   PCK(cudaFuncSetAttribute(fly_policy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PSMEM_BYTES));
   return 0;
@@ -458,7 +609,7 @@ int flyb_policy_forward(flyb_policy_handle h, const float* obs, int n_rows, cons
   if (n_rows > P->max_rows) return pfail(P, "flyb_policy_forward: more rows than the handle was created for");
   cudaStream_t st = (cudaStream_t)stream;
   PCK(cudaSetDevice(P->device));
-  const int rows_pad = (n_rows + PM - 1) / PM * PM;
+  const int rows_pad = (n_rows + PM * PCLUSTER - 1) / (PM * PCLUSTER) * (PM * PCLUSTER);   /* whole clusters; rows beyond n_rows are zero */
   if (P->x_rows != rows_pad) {
     if (!make_map(&P->m_x, P->xb, rows_pad, P->k1pad, PM)) return pfail(P, "cuTensorMapEncodeTiled failed for the observations");
     P->x_rows = rows_pad;
@@ -472,10 +623,31 @@ int flyb_policy_forward(flyb_policy_handle h, const float* obs, int n_rows, cons
   pp.n_rows = n_rows; pp.act_dim = P->act_dim; pp.nk1 = P->k1pad / PKC;
   pp.ln_eps = P->ln_eps; pp.scale_mul = P->init_scale / 0.6931471805599453f; pp.min_scale = P->min_scale;
   pp.tanh_mean = P->tanh_mean;
+  pp.xb = (const uint8_t*)P->xb; pp.x_row_bytes = (uint32_t)P->k1pad * 2;
+  const __nv_bfloat16* wp[5] = {P->w1, P->w2, P->w3, P->w4, P->wh};
+  const uint32_t wb[5] = {(uint32_t)PH * P->k1pad * 2, PH * PH * 2, PH * PH * 2, PH * PH * 2, PHEAD_N * PH * 2};
+  for (int i = 0; i < 5; i++) { pp.w_ptr[i] = (const uint8_t*)wp[i]; pp.w_bytes[i] = wb[i]; }
   fly_policy_kernel<<<rows_pad / PM, PTHREADS, PSMEM_BYTES, st>>>(P->m_x, P->m_w1, P->m_w2, P->m_w3, P->m_w4, P->m_wh, pp);
   PCK(cudaGetLastError());
   P->launches += 2;
   return 0;
 }
+
+#ifdef FLY_POLICY_PROF
+void flyb_policy_prof_dump(void) {
+  long long h[2][6][6];
+  cudaDeviceSynchronize();
+  cudaMemcpyFromSymbol(h, g_pprof, sizeof(h));
+  for (int c = 0; c < 2; c++) {
+    const long long t0 = h[c][0][0];
+    for (int l = 0; l < 5; l++)
+      printf("cta %d layer %d: mma start %lld, first full-wait at %lld, waited on full %lld, issue end %lld | epilogue: acc at %lld, done %lld\n",
+             c ? 100 : 0, l, h[c][l][0] - t0, h[c][l][1] - t0, h[c][l][2], h[c][l][3] - t0, h[c][l][4] - t0, h[c][l][5] - t0);
+    printf("cta %d head epilogue: noise loads issued %lld, TMEM read %lld, staged %lld, past the barrier %lld\n", c ? 100 : 0,
+           h[c][5][0] - t0, h[c][5][1] - t0, h[c][5][2] - t0, h[c][5][3] - t0);
+    printf("cta %d kernel entry %lld, exit %lld\n", c ? 100 : 0, h[c][5][4] - t0, h[c][5][5] - t0);
+  }
+}
+#endif
 
 }  // extern "C"

@@ -31,6 +31,11 @@ with torch.no_grad():
     torch.backends.cuda.matmul.allow_tf32 = True
     t_tf32 = timed(lambda: pol(obs))
 flop = 2.0 * N * (obs_dim * 512 + 3 * 512 * 512 + 512 * 2 * act_dim)
+try:   # a -DFLY_POLICY_PROF build (tools/build_variant.py) carries clock64 stamps of two CTAs
+    from flybody_b200 import engine as _E
+    _E.lib().flyb_policy_prof_dump()
+except AttributeError:
+    pass
 peaks = json.load(open(os.path.join(os.path.dirname(__file__), "..", "MEASURED_PEAKS.json")))
 print(json.dumps({"rows": N, "fused_ms": t_fused, "fused_tflops": flop / t_fused / 1e9, "frac_of_measured_bf16_peak": flop / t_fused / 1e9 / peaks["bf16_tflops"],
                   "torch_fp32_ms": t_torch, "torch_tf32_ms": t_tf32, "gflop": flop / 1e9,
