@@ -36,12 +36,13 @@ constexpr int PH = 512;            /* hidden width of every layer */
 constexpr int PKC = 64;            /* bf16 elements per K chunk = one 128-byte swizzle row */
 constexpr int PM = 128;            /* rows per CTA */
 constexpr int PNH = 256;           /* N per MMA instruction */
-constexpr int PSTAGES = 3;
+constexpr int PSTAGES = 6;
 constexpr int PA_BYTES = PM * PKC * 2;      /* 16 KB: an A tile (128 rows x 64 bf16) */
-constexpr int PB_BYTES = PNH * PKC * 2;     /* 32 KB: a B tile (256 weight rows x 64 bf16) */
-constexpr int PCLUSTER = 2;                 /* CTAs per cluster: each loads 1 / PCLUSTER of a weight tile and multicasts it to all of them */
-constexpr int PSTAGE_BYTES = PB_BYTES;       /* a stage holds a B tile; the first layer's A tile of the stage lies in the (then unused) activation buffer */
+constexpr int PCLUSTER = 2;                 /* a CTA pair (cta_group::2): the MMAs span both CTAs' 128 rows, each CTA holds half of a weight tile */
+constexpr int PB_BYTES = PNH / PCLUSTER * PKC * 2;   /* 16 KB: this CTA's half of a B tile (128 of its 256 weight rows x 64 bf16) */
+constexpr int PSTAGE_BYTES = PB_BYTES;       /* a stage holds that half; the first layer's A tile of the stage lies in the (then unused) activation buffer */
 constexpr int PACT_BYTES = PM * PH * 2;     /* 128 KB */
+static_assert(PSTAGES <= 7, "layer 0 stages its A tiles in K chunks 0 .. PSTAGES - 1 of the activation buffer, chunk 7 holds the LayerNorm sums");
 constexpr int PHEAD_N = 128;                /* head output columns: mean at 0.., scale at 64.. */
 constexpr int PSMEM_BYTES = PACT_BYTES + PSTAGES * PSTAGE_BYTES + 1024 /* barriers */ + 1024 /* alignment slack */;
 constexpr int PEPI_WARPS = 16;              /* epilogue warps: 4 per quarter of the TMEM lanes, each takes 128 of the 512 columns */
@@ -69,48 +70,67 @@ __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
 __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+__device__ __forceinline__ bool mbar_try(uint32_t bar, uint32_t parity) {
   uint32_t done;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+  return done != 0;
+}
+/* (the clock is only read once the first probe has failed: the MMA issuer's waits mostly succeed at once, and its instruction
+   count per MMA is what paces the tensor core) */
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  if (mbar_try(bar, parity)) return;
   const long long t0 = clock64();
-  for (;;) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(done) : "r"(bar), "r"(parity) : "memory");
-    if (done) return;
+  while (!mbar_try(bar, parity))
     if (clock64() - t0 > 4000000000LL) __trap();   /* ~2 s: a protocol bug must not hang the GPU */
-  }
 }
-__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int x, int y, uint32_t bar) {
-  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-               ::"r"(dst), "l"(map), "r"(x), "r"(y), "r"(bar) : "memory");
+/* a 2-D tile load issued by either CTA of a pair, completing on a barrier that may lie in the peer CTA (the leader's: the pair's MMAs are issued there) */
+__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const CUtensorMap* map, int x, int y, uint32_t bar_cluster) {
+  asm volatile("cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+               ::"r"(dst), "l"(map), "r"(x), "r"(y), "r"(bar_cluster) : "memory");
 }
-/* the same, delivered to the same shared-memory offset (and signalled on the barrier at the same offset) of every CTA in `mask` */
-__device__ __forceinline__ void tma_load_2d_mc(uint32_t dst, const CUtensorMap* map, int x, int y, uint32_t bar, uint16_t mask) {
-  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%2, %3}], [%4], %5;"
-               ::"r"(dst), "l"(map), "r"(x), "r"(y), "r"(bar), "h"(mask) : "memory");
+/* shared::cluster address of the same shared-memory offset in CTA `rank` of the cluster */
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar_cluster) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(bar_cluster) : "memory");
+}
+/* wait on a barrier of this CTA that threads of the peer CTA arrive on */
+__device__ __forceinline__ bool mbar_try_cluster(uint32_t bar, uint32_t parity) {
+  uint32_t done;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+  return done != 0;
+}
+__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {
+  if (mbar_try_cluster(bar, parity)) return;
+  const long long t0 = clock64();
+  while (!mbar_try_cluster(bar, parity))
+    if (clock64() - t0 > 4000000000LL) __trap();
 }
 /* shared-memory matrix descriptor, K-major, SWIZZLE_128B: start >> 4 | LBO (unused) | SBO = 1024 B (8 rows x 128 B) | version 1 */
-__device__ __forceinline__ uint64_t umma_desc(uint32_t addr) {
-  return (uint64_t)((addr & 0x3FFFF) >> 4) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
+/* (given the low word, (address & 0x3FFFF) >> 4: 32 bytes further along the swizzled row is + 2) */
+__device__ __forceinline__ uint64_t umma_desc_lo(uint32_t lo) {
+  return (uint64_t)lo | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
 }
 /* instruction descriptor of kind::f16: D fp32 (bit 4), A / B bf16 (bits 7, 10), both K-major, N >> 3 at bit 17, M >> 4 at bit 24 */
 __device__ __forceinline__ constexpr uint32_t umma_idesc(int M, int N) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
+/* issued by the leader CTA of a pair: D (both CTAs' TMEM, 128 lanes each) += A (each CTA's own 128 rows) x B (N split over the CTAs) */
 __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
   asm volatile(
-      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
       ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
+/* arrives on the barrier at this offset in both CTAs of the pair once the MMAs issued so far are complete */
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-}
-/* ... arriving on the barrier at this offset in every CTA of `mask` */
-__device__ __forceinline__ void umma_commit_mc(uint32_t bar, uint16_t mask) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar), "h"(mask) : "memory");
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar), "h"((uint16_t)3) : "memory");
 }
 __device__ __forceinline__ void cluster_sync_all() {
   asm volatile("barrier.cluster.arrive.release;\n\tbarrier.cluster.wait.acquire;" ::: "memory");
@@ -189,7 +209,7 @@ fly_policy_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
   if (threadIdx.x == PEPI_THREADS + 32) PPROF(4, 5, clock64());
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* act = smem;                                   /* 8 chunks x 16 KB */
-  uint8_t* stage = smem + PACT_BYTES;                    /* PSTAGES x 32 KB B tiles */
+  uint8_t* stage = smem + PACT_BYTES;                    /* PSTAGES x 16 KB: this CTA's halves of the B tiles */
   uint64_t* bars = reinterpret_cast<uint64_t*>(stage + PSTAGES * PSTAGE_BYTES);
   /* bars: full[PSTAGES], empty[PSTAGES], acc[2] (an N half of the layer is complete), ka (the second half's MMAs are past K chunk 3),
      epi[2] (the epilogue has drained an N half from TMEM and written its activations) ; then the TMEM base address */
@@ -201,27 +221,30 @@ fly_policy_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
   const int row0 = blockIdx.x * PM;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < PSTAGES; s++) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, PCLUSTER); }
+    for (int s = 0; s < PSTAGES; s++) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, 1); }
     mbar_init(bar_acc, 1); mbar_init(bar_acc + 8, 1);
     mbar_init(bar_ka, 1);
-    mbar_init(bar_epi, PEPI_THREADS); mbar_init(bar_epi + 8, PEPI_THREADS);
+    mbar_init(bar_epi, PCLUSTER * PEPI_WARPS); mbar_init(bar_epi + 8, PCLUSTER * PEPI_WARPS);   /* (the leader's: a lane per epilogue warp of both CTAs) */
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == PEPI_WARPS) {   /* the allocating warp also frees: all 512 columns (one CTA per SM: nothing to contend with) */
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512) : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem = *tmem_slot;
-  /* The CTAs of a cluster walk the weight tiles together: every CTA fetches its 1 / PCLUSTER of the rows of a tile and multicasts
-     them into the same stage of all, so a stage is reloaded once every CTA's MMAs have released it (empty: PCLUSTER arrivals, by
-     multicast commit).  Halves the L2 -> SM traffic per CTA, which bounded the MMA phases. */
+  /* A CTA pair works as one: the leader (rank 0) issues tcgen05.mma.cta_group::2 with M = 256 - each CTA's tensor core takes its own
+     128 rows (its A tiles, its TMEM) and HALF of the weight tile from its own shared memory, the other half comes from the peer.
+     Per MMA a CTA reads 4 + 4 KB of shared memory instead of 4 + 8, and the TMA ring writes half as much: the single-CTA kernel
+     ran its MMAs at 210 cycles each against a floor of 128 with shared memory at ~100 of its 128 B / cycle.  Both CTAs' loads
+     complete on the LEADER's full barriers; the leader's commits arrive on the empty / acc / ka barriers of both; the epilogue
+     warps of both arrive on the leader's epi barriers. */
   uint32_t cta_rank;
   asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(cta_rank));
-  constexpr uint16_t kAll = (uint16_t)((1u << PCLUSTER) - 1);
-  cluster_sync_all();   /* the barriers of every CTA are initialised before a peer signals them */
+  const bool leader = cta_rank == 0;
+  cluster_sync_all();   /* the barriers of both CTAs are initialised before a peer signals them */
 
   /* The item sequence both pipeline ends walk: layer 0: 2 N halves x nk1 chunks (A + B tiles); layers 1-3: 2 x 8 (B only, A =
      the activation buffer); layer 4 = the head: 8 chunks of a 128-row B tile.
@@ -232,55 +255,58 @@ fly_policy_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
   if (warp == PEPI_WARPS && lane == 0) {
     /* ------------------------------------------------------------------------------------------------ TMA producer */
     const CUtensorMap* wmap[5] = {&map_w1, &map_w2, &map_w3, &map_w4, &map_wh};
-    int it = 0;
+    uint32_t s = 0, ph = 1;   /* stage; parity of the empty phase to wait for (a fresh barrier passes parity 1) */
     for (int l = 0; l < 5; l++) {
       const int nk = l == 0 ? p.nk1 : PH / PKC, nhalf = l == 4 ? 1 : 2;
       for (int nh = 0; nh < nhalf; nh++)
-        for (int kc = 0; kc < nk; kc++, it++) {
-          const int s = it % PSTAGES;
-          mbar_wait(bar_empty + 8 * s, ((it / PSTAGES) & 1) ^ 1);
+        for (int kc = 0; kc < nk; kc++) {
+          mbar_wait(bar_empty + 8 * s, ph);
           const uint32_t a_dst = smem_u32(act + s * PA_BYTES), b_dst = smem_u32(stage + s * PSTAGE_BYTES);
-          const uint32_t bytes = (l == 0 ? PA_BYTES : 0) + (l == 4 ? PHEAD_N * PKC * 2 : PB_BYTES);
-          mbar_expect_tx(bar_full + 8 * s, bytes);   /* (a peer's share may land before this: the transaction count runs negative until then) */
-          if (l == 0) tma_load_2d(a_dst, &map_x, kc * PKC, row0, bar_full + 8 * s);
-          const int share = (l == 4 ? PHEAD_N : PNH) / PCLUSTER;   /* weight rows this CTA fetches */
-          tma_load_2d_mc(b_dst + cta_rank * share * 128, wmap[l], kc * PKC, nh * PNH + cta_rank * share, bar_full + 8 * s, kAll);
+          const int share = (l == 4 ? PHEAD_N : PNH) / PCLUSTER;   /* weight rows of the tile this CTA holds */
+          const uint32_t bytes = PCLUSTER * ((l == 0 ? PA_BYTES : 0) + share * PKC * 2);   /* of both CTAs */
+          const uint32_t full = mapa_u32(bar_full + 8 * s, 0);
+          if (leader) mbar_expect_tx(bar_full + 8 * s, bytes);   /* (the peer's bytes may land before this: the transaction count runs negative until then) */
+          if (l == 0) tma_load_2d_pair(a_dst, &map_x, kc * PKC, row0, full);
+          tma_load_2d_pair(b_dst, wmap[l], kc * PKC, nh * PNH + cta_rank * share, full);
+          if (++s == PSTAGES) { s = 0; ph ^= 1; }
         }
     }
-  } else if (warp == PEPI_WARPS + 1 && lane == 0) {
-    /* -------------------------------------------------------------------------------------------------- MMA issuer */
-    int it = 0;
+  } else if (warp == PEPI_WARPS + 1 && lane == 0 && leader) {
+    /* ------------------------------------------------------------------------------- MMA issuer (of the pair: leader only) */
+    uint32_t s = 0, ph = 0;   /* stage and its phase parity */
+    const uint32_t act_lo = (smem_u32(act) & 0x3FFFF) >> 4, stage_lo = (smem_u32(stage) & 0x3FFFF) >> 4;
     for (int l = 0; l < 5; l++) {
       const int nk = l == 0 ? p.nk1 : PH / PKC, nhalf = l == 4 ? 1 : 2;
       const int kka = nk - 1 < 3 ? nk - 1 : 3;
-      const uint32_t idesc = l == 4 ? umma_idesc(PM, PHEAD_N) : umma_idesc(PM, PNH);
+      const uint32_t idesc = l == 4 ? umma_idesc(PCLUSTER * PM, PHEAD_N) : umma_idesc(PCLUSTER * PM, PNH);
 #ifdef FLY_POLICY_PROF
       long long wfull = 0;
 #endif
       PPROF(0, l, clock64());
       for (int nh = 0; nh < nhalf; nh++) {
-        for (int kc = 0; kc < nk; kc++, it++) {
+        const uint32_t d_tmem = tmem + nh * PNH;
+        for (int kc = 0; kc < nk; kc++) {
           if (l > 0 && nh == 0 && (kc == 0 || kc == 4)) {   /* K chunks 0-3 (4-7) of this layer's input are written, TMEM half 0 (1) is drained */
-            mbar_wait(bar_epi + (kc ? 8 : 0), (l - 1) & 1);
+            mbar_wait_cluster(bar_epi + (kc ? 8 : 0), (l - 1) & 1);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
           }
-          const int s = it % PSTAGES;
 #ifdef FLY_POLICY_PROF
           const long long tw = clock64();
 #endif
-          mbar_wait(bar_full + 8 * s, (it / PSTAGES) & 1);
+          mbar_wait(bar_full + 8 * s, ph);
 #ifdef FLY_POLICY_PROF
           if (kc == 0 && nh == 0) PPROF(1, l, tw);
           wfull += clock64() - tw;
 #endif
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-          const uint32_t a_base = l == 0 ? smem_u32(act + s * PA_BYTES) : smem_u32(act + kc * PA_BYTES);
-          const uint32_t b_base = smem_u32(stage + s * PSTAGE_BYTES);
+          const uint32_t a_lo = act_lo + (l == 0 ? s : (uint32_t)kc) * (PA_BYTES >> 4);
+          const uint32_t b_lo = stage_lo + s * (PSTAGE_BYTES >> 4);
 #pragma unroll
           for (int k = 0; k < PKC / 16; k++)   /* UMMA K = 16 bf16 = 32 bytes along the swizzled row */
-            umma_bf16(tmem + nh * PNH, umma_desc(a_base + 32 * k), umma_desc(b_base + 32 * k), idesc, (kc | k) != 0);
-          umma_commit_mc(bar_empty + 8 * s, kAll);   /* releases the stage in every CTA of the cluster once these MMAs have read it */
-          if (l < 4 && nh == 1 && kc == kka) umma_commit(bar_ka);
+            umma_bf16(d_tmem, umma_desc_lo(a_lo + 2 * k), umma_desc_lo(b_lo + 2 * k), idesc, k ? 1u : (uint32_t)kc);
+          umma_commit(bar_empty + 8 * s);     /* releases the stage in both CTAs once these MMAs have read it */
+          if (nh == 1 && kc == kka) umma_commit(bar_ka);
+          if (++s == PSTAGES) { s = 0; ph ^= 1; }
         }
         umma_commit(bar_acc + 8 * nh);        /* this half of the layer's accumulator is complete */
       }
@@ -292,8 +318,9 @@ fly_policy_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
     const int r = q * 32 + lane;                           /* row of the tile = TMEM lane */
     const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16);
     const uint32_t act_s = smem_u32(act);
+    const uint32_t epi_leader = mapa_u32(bar_epi, 0);
     /* per N half the thread takes the two 32-column chunks 8 h + 2 cg + {0, 1} of its row, i.e. K chunk 4 h + cg of the next layer */
-    const uint32_t red = act_s + 4 * PA_BYTES;                   /* LayerNorm partial sums [4 column groups][128 rows][2]: K chunk 4 is
+    const uint32_t red = act_s + 7 * PA_BYTES;                   /* LayerNorm partial sums [4 column groups][128 rows][2]: K chunk 7 is
                                                                     neither a staging slot of layer 0's A tiles nor written before the sums are read */
     float v[32];
     {   /* L2 warm-up while the first tiles are on their way: the TMA ring holds three tiles, so a tile that misses L2 costs a DRAM
@@ -360,7 +387,8 @@ fly_policy_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
           }
           asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   /* generic-proxy stores -> visible to the tensor core */
           asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-          mbar_arrive(bar_epi + 8 * h);
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster(epi_leader + 8 * h);
         }
       } else {              /* bias, ELU */
         const float* bl = p.b[l - 1];
@@ -386,7 +414,8 @@ fly_policy_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
           for (int j = 0; j < 2; j++) store_packed32(act_s, r, 8 * h + 2 * cg + j, qq[j]);
           asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
           asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-          mbar_arrive(bar_epi + 8 * h);
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster(epi_leader + 8 * h);
         }
       }
       if (threadIdx.x == 0) PPROF(5, l, clock64());
@@ -457,7 +486,7 @@ fly_policy_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
   cluster_sync_all();   /* no CTA leaves while a peer may still signal its barriers */
   if (warp == PEPI_WARPS) {
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512) : "memory");
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512) : "memory");
   }
   if (threadIdx.x == PEPI_THREADS + 32) PPROF(5, 5, clock64());
 }
