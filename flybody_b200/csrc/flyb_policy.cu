@@ -6,15 +6,18 @@
  * For 16 384 envs that is 2 x 16 384 x (741 x 512 + 3 x 512^2 + 512 x 118) = 40 GFLOP per control step: the one GEMM-shaped piece of
  * the actor side, so it runs on the 5th-generation tensor cores:
  *
- *   - one CTA per 128 observation rows (UMMA M = 128, cta_group::1), 18 warps: warps 0-15 epilogue (a thread per row = TMEM lane
- *     and quarter of the columns: with 4 warps the epilogue ran at one warp per scheduler and took 85 % of the kernel), warp 16
- *     TMA producer, warp 17 MMA issuer (one elected thread each);
+ *   - a CTA per 128 observation rows, CTAs in PAIRS (cluster of 2, tcgen05.mma.cta_group::2, M = 256): the leader issues the MMAs of
+ *     both; each CTA's tensor core takes its own 128 rows and its own half of the weight tile.  18 warps: warps 0-15 epilogue (a
+ *     thread per row = TMEM lane and quarter of the columns), warp 16 TMA producer, warp 17 MMA issuer (one elected thread each);
  *   - the whole 128 x 512 fp32 layer output lives in TMEM (512 columns), written by tcgen05.mma.kind::f16 (bf16 x bf16 -> fp32,
  *     N = 256 per instruction), read back by tcgen05.ld.32x32b for bias + LayerNorm + tanh / ELU;
  *   - activations never leave the SM: the epilogue writes them as bf16 into shared memory in the canonical K-major
  *     SWIZZLE_128B layout, where the next layer's MMAs read them as the A operand (128 KB: 8 K-chunks of 128 rows x 128 B);
+ *   - MMA and epilogue overlap by N halves: the epilogue of half 0 runs under the MMAs of half 1, the next layer's half 0 starts
+ *     on K chunks 0-3 under the epilogue of half 1;
  *   - weights (bf16, [out, in] row-major = K-major, L2-resident: 2.3 MB) and the first layer's input tiles stream through a
- *     3-stage TMA pipeline (cp.async.bulk.tensor.2d, SWIZZLE_128B, mbarrier complete_tx), freed by tcgen05.commit.
+ *     6-stage TMA pipeline (cp.async.bulk.tensor.2d.cta_group::2, SWIZZLE_128B, complete_tx on the leader's mbarriers), freed by
+ *     tcgen05.commit multicast to both CTAs.
  *
  * Every spin on an mbarrier is bounded (trap after ~2 s) so that a protocol bug cannot hang the device. */
 #include <cuda.h>
@@ -323,8 +326,8 @@ fly_policy_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
     const uint32_t red = act_s + 7 * PA_BYTES;                   /* LayerNorm partial sums [4 column groups][128 rows][2]: K chunk 7 is
                                                                     neither a staging slot of layer 0's A tiles nor written before the sums are read */
     float v[32];
-    {   /* L2 warm-up while the first tiles are on their way: the TMA ring holds three tiles, so a tile that misses L2 costs a DRAM
-           round trip per three items.  These warps are idle until the first half of layer 0 is done: they ask for the CTA's own
+    {   /* L2 warm-up while the first tiles are on their way: the TMA ring holds six tiles, so a tile that misses L2 costs a DRAM
+           round trip per six items.  These warps are idle until the first half of layer 0 is done: they ask for the CTA's own
            observation rows and for its 1 / gridDim.x of every weight matrix, a line per thread. */
       const uint8_t* xp = p.xb + (size_t)row0 * p.x_row_bytes;
       const uint32_t xbytes = PM * p.x_row_bytes;
