@@ -37,6 +37,10 @@ struct FlyIO {
   int* work;                       /* nullable [N]: cycles/64 the env spent in its constraint solves this step (load-balancing key) */
   float* eyes;                     /* nullable [N, 24]: world frames of the right / left eye camera (vision_flight) */
   int* eye_terrain;                /* [N] with eyes: index of the env's terrain in the pool */
+  /* nullable, flyb_step_host: device-visible addresses of page-locked HOST buffers.  A warp copies its env's finished row (and
+     reward, discount, step type) there itself - posted writes over PCIe, under the other envs' steps - so that no device -> host
+     copy is left after the launch */
+  float* host_obs; float* host_reward; float* host_discount; int* host_step_type;
 };
 
 FLY_INL unsigned long long fly_hash(unsigned long long x) {  /* splitmix64 finaliser */
@@ -583,6 +587,13 @@ FLY_FN void fly_env_run(const DModel<T>& m, const Ws<T>& w, const FlyClips& clip
     if (io.reward) io.reward[env] = (float)reward;
     if (io.discount) io.discount[env] = (float)discount;
     io.step_type[env] = st;
+    if (io.host_reward) io.host_reward[env] = (float)reward;
+    if (io.host_discount) io.host_discount[env] = (float)discount;
+    if (io.host_step_type) io.host_step_type[env] = st;
+  }
+  if (io.host_obs) {   /* whole 128-byte segments per warp store: the row was assembled in device memory above */
+    float* ho = io.host_obs + (size_t)env * m.obs_dim;
+    FLY_FOR(i, m.obs_dim) ho[i] = obs[i];
   }
   if (io.work) FLY_LANE0 io.work[env] = w.counts[FLY_C_WORK];
   if (io.trace_int) {

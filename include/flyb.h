@@ -112,7 +112,11 @@ int flyb_step_noalloc(flyb_handle h, const float* action, float* obs, float* rew
 
 /* Host-pointer API (what a numpy caller uses): copies through pinned staging buffers, synchronises. */
 int flyb_reset_host(flyb_handle h, const uint8_t* mask, float* obs, int32_t* step_type);
-/* Host-pointer variants: page-locked caller buffers are DMA targets themselves, pageable ones are staged. */
+/* Host-pointer variants: page-locked caller buffers are read and written directly, pageable ones are staged through the library's
+ * own page-locked buffers.  flyb_step_host copies the actions in, launches, and the kernel itself writes every env's finished
+ * observation row, reward, discount and step type into the (device-visible) host buffers while the other envs are still
+ * stepping: nothing is left to copy when the launch ends.  FLYB_HOST_DIRECT=0 in the environment restores device -> host copies
+ * after the launch. */
 int flyb_step_host(flyb_handle h, const float* action, float* obs, float* reward, float* discount, int32_t* step_type);
 
 /* State access (host pointers, any may be NULL).  qpos [N,nq] qvel [N,nv] act [N,na] qacc_warmstart [N,nv]
