@@ -5,8 +5,8 @@
 
 A "step" is one control step (10 physics substeps) of every env of the shard.  `value` is timed with CUDA events
 on the launching stream with actions already resident in HBM; `e2e` goes through the host-pointer C-ABI call
-(`flyb_step_host`: pinned H2D of the actions, launch, D2H of observations / reward / discount / step_type inside the
-timed region).  Envs shard across ranks with no data-path collective (weak scaling: 16384 envs per GPU); NCCL is
+(`flyb_step_host`: pinned H2D of the actions, launch, observations / reward / discount / step_type written to the pinned host
+buffers - by the kernel itself, row by row as envs finish - inside the timed region).  Envs shard across ranks with no data-path collective (weak scaling: 16384 envs per GPU); NCCL is
 used for the barrier, the max-over-ranks of the timing and the episode-statistics all-reduce.
 
 The reference's own implementation of the path (MuJoCo C via dm_control) is not installable here (no network, not
@@ -347,8 +347,8 @@ def run_gpu(args):
     value = N * world * args.steps / (total_ms * 1e-3)
     finite = bool(torch.isfinite(obs).all().item())
     # ---- end to end through the host-pointer C-ABI call
-    # inputs and outputs in page-locked host memory (the contract's "pinned host memory"): flyb_step_host then copies to and
-    # from the caller's buffers directly; with pageable numpy arrays it stages through its own pinned buffers (one more
+    # inputs and outputs in page-locked host memory (the contract's "pinned host memory"): flyb_step_host then copies the actions
+    # from the caller's buffer and the kernel writes the outputs into the caller's buffers directly; with pageable numpy arrays it stages through its own pinned buffers (one more
     # host copy each way, ~6 ms per step at this size)
     h_pin = [torch.empty((N, A), dtype=torch.float32).pin_memory() for _ in pool]
     for hp, p in zip(h_pin, pool):
