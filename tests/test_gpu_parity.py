@@ -363,3 +363,46 @@ def test_host_call_with_page_locked_buffers_matches_pageable(models, walk_clip):
         eng.close()
     for x, y in zip(*res):
         assert (x == y).all()
+
+
+def test_host_call_direct_writes_match_the_copy_path(models, walk_clip, tmp_path):
+    """flyb_step_host lets the kernel write observation rows, reward, discount and step type into the page-locked host buffers
+    itself; FLYB_HOST_DIRECT=0 (read once per process, so a child process) copies device -> host after the launch instead.
+    Same numbers either way, and the device-pointer call (flyb_step) gives them too."""
+    import os, subprocess, sys
+    from flybody_b200.engine import Engine
+    ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    M = models["walk_imitation"]
+    N = 40
+    rng = np.random.RandomState(11)
+    acts = rng.uniform(M["action_min"], M["action_max"], (3, N, 59)).astype(np.float32)
+    np.save(tmp_path / "acts.npy", acts)
+    np.savez(tmp_path / "clip.npz", *walk_clip)
+    child = f"""
+import sys, numpy as np
+sys.path.insert(0, {ROOT!r})
+from flybody_b200.compile_fly import load_model
+from flybody_b200.model_pack import asset_path
+from flybody_b200.engine import Engine
+M = load_model(asset_path("walk_imitation"))
+acts = np.load({str(tmp_path / "acts.npy")!r})
+clip = np.load({str(tmp_path / "clip.npz")!r})
+eng = Engine(M, {N}, seed=0)
+eng.load_clips(*[clip[k] for k in clip.files])
+eng.set_clip_ids(np.zeros({N}, np.int32))
+eng.reset_host()
+for k in range(3):
+    st, r, g, obs = eng.step_host(acts[k])
+np.savez({str(tmp_path / "out.npz")!r}, obs=obs, r=r, g=g, st=st)
+"""
+    env = dict(os.environ, FLYB_HOST_DIRECT="0")
+    subprocess.check_call([sys.executable, "-c", child], env=env)
+    ref = np.load(tmp_path / "out.npz")
+    eng = Engine(M, N, seed=0)
+    eng.load_clips(*walk_clip)
+    eng.set_clip_ids(np.zeros(N, np.int32))
+    eng.reset_host()
+    for k in range(3):
+        st, r, g, obs = eng.step_host(acts[k])
+    assert (obs == ref["obs"]).all() and (r == ref["r"]).all() and (g == ref["g"]).all() and (st == ref["st"]).all()
+    eng.close()
