@@ -99,22 +99,11 @@ __device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, uint32_t rank) {
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
   return r;
 }
+/* arrival on a barrier of the leader CTA.  Default semantics, as in CUTLASS' ClusterBarrier::arrive(cta_id): the writes it publishes
+   are the thread's own shared-memory stores, already handed to the async proxy by fence.proxy.async; `.release.cluster` puts a
+   MEMBAR.ALL.GPU in front of every arrival (9 % of the kernel's stall samples) */
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar_cluster) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(bar_cluster) : "memory");
-}
-/* wait on a barrier of this CTA that threads of the peer CTA arrive on */
-__device__ __forceinline__ bool mbar_try_cluster(uint32_t bar, uint32_t parity) {
-  uint32_t done;
-  asm volatile(
-      "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-      : "=r"(done) : "r"(bar), "r"(parity) : "memory");
-  return done != 0;
-}
-__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {
-  if (mbar_try_cluster(bar, parity)) return;
-  const long long t0 = clock64();
-  while (!mbar_try_cluster(bar, parity))
-    if (clock64() - t0 > 4000000000LL) __trap();
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(bar_cluster) : "memory");
 }
 /* shared-memory matrix descriptor, K-major, SWIZZLE_128B: start >> 4 | LBO (unused) | SBO = 1024 B (8 rows x 128 B) | version 1 */
 /* (given the low word, (address & 0x3FFFF) >> 4: 32 bytes further along the swizzled row is + 2) */
@@ -290,7 +279,7 @@ fly_policy_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
         const uint32_t d_tmem = tmem + nh * PNH;
         for (int kc = 0; kc < nk; kc++) {
           if (l > 0 && nh == 0 && (kc == 0 || kc == 4)) {   /* K chunks 0-3 (4-7) of this layer's input are written, TMEM half 0 (1) is drained */
-            mbar_wait_cluster(bar_epi + (kc ? 8 : 0), (l - 1) & 1);
+            mbar_wait(bar_epi + (kc ? 8 : 0), (l - 1) & 1);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
           }
 #ifdef FLY_POLICY_PROF
