@@ -142,6 +142,17 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float* v) {
 #pragma unroll
   for (int i = 0; i < 32; i++) v[i] = __uint_as_float(r[i]);
 }
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
+  uint32_t r[16];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
+        "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr) : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 16; i++) v[i] = __uint_as_float(r[i]);
+}
 /* activations are rounded to bf16 (8 mantissa bits) right after: the MUFU approximations (tanh.approx, ex2.approx: ~2^-11 relative)
    are below that rounding */
 __device__ __forceinline__ float fast_tanh(float x) {
@@ -178,6 +189,15 @@ __device__ __forceinline__ void store_packed32(uint32_t act_s, int r, int c, con
                  "r"(q[g].z), "r"(q[g].w) : "memory");
 }
 
+/* 16 activations of row r, columns [64 kc + 16 cg, + 16): 16-byte groups 2 cg, 2 cg + 1 of K chunk kc */
+__device__ __forceinline__ void store_act16(uint32_t act_s, int r, int kc, int cg, const float* y) {
+  const uint32_t row = act_s + kc * PA_BYTES + r * 128;
+#pragma unroll
+  for (int g = 0; g < 2; g++)
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(row + (((2 * cg + g) ^ (r & 7)) << 4)),
+                 "r"(pack_bf16(y[8 * g + 0], y[8 * g + 1])), "r"(pack_bf16(y[8 * g + 2], y[8 * g + 3])),
+                 "r"(pack_bf16(y[8 * g + 4], y[8 * g + 5])), "r"(pack_bf16(y[8 * g + 6], y[8 * g + 7])) : "memory");
+}
 __device__ __forceinline__ void sts_f32(uint32_t addr, float x) { asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(x) : "memory"); }
 __device__ __forceinline__ float lds_f32(uint32_t addr) {
   float x;
@@ -204,11 +224,12 @@ fly_policy_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
   uint8_t* stage = smem + PACT_BYTES;                    /* PSTAGES x 16 KB: this CTA's halves of the B tiles */
   uint64_t* bars = reinterpret_cast<uint64_t*>(stage + PSTAGES * PSTAGE_BYTES);
   /* bars: full[PSTAGES], empty[PSTAGES], acc[2] (an N half of the layer is complete), ka (the second half's MMAs are past K chunk 3),
-     epi[2] (the epilogue has drained an N half from TMEM and written its activations) ; then the TMEM base address */
+     epi[5] (the epilogue has drained half 0 from TMEM and written K chunks 0-3 of the next layer's input | ... K chunk 4 | 5 | 6 | 7 of half 1) ;
+     then the TMEM base address */
   const uint32_t bar_full = smem_u32(bars), bar_empty = smem_u32(bars + PSTAGES);
   const uint32_t bar_acc = smem_u32(bars + 2 * PSTAGES), bar_ka = smem_u32(bars + 2 * PSTAGES + 2);
   const uint32_t bar_epi = smem_u32(bars + 2 * PSTAGES + 3);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * PSTAGES + 5);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * PSTAGES + 8);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row0 = blockIdx.x * PM;
 
@@ -216,7 +237,7 @@ fly_policy_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
     for (int s = 0; s < PSTAGES; s++) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, 1); }
     mbar_init(bar_acc, 1); mbar_init(bar_acc + 8, 1);
     mbar_init(bar_ka, 1);
-    mbar_init(bar_epi, PCLUSTER * PEPI_WARPS); mbar_init(bar_epi + 8, PCLUSTER * PEPI_WARPS);   /* (the leader's: a lane per epilogue warp of both CTAs) */
+    for (int i = 0; i < 5; i++) mbar_init(bar_epi + 8 * i, PCLUSTER * PEPI_WARPS);   /* (the leader's: a lane per epilogue warp of both CTAs) */
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == PEPI_WARPS) {   /* the allocating warp also frees: all 512 columns (one CTA per SM: nothing to contend with) */
@@ -278,8 +299,9 @@ fly_policy_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
       for (int nh = 0; nh < nhalf; nh++) {
         const uint32_t d_tmem = tmem + nh * PNH;
         for (int kc = 0; kc < nk; kc++) {
-          if (l > 0 && nh == 0 && (kc == 0 || kc == 4)) {   /* K chunks 0-3 (4-7) of this layer's input are written, TMEM half 0 (1) is drained */
-            mbar_wait(bar_epi + (kc ? 8 : 0), (l - 1) & 1);
+          if (l > 0 && nh == 0 && (kc == 0 || kc >= 4)) {   /* K chunks 0-3 (chunk kc) of this layer's input are written; TMEM half 0 is
+                                                              drained (half 1: when chunk 7 is, before the MMAs of half 1) */
+            mbar_wait(bar_epi + (kc ? 8 * (kc - 3) : 0), (l - 1) & 1);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
           }
 #ifdef FLY_POLICY_PROF
@@ -359,39 +381,56 @@ fly_policy_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
         const float var = fmaxf(sq * (1.0f / PH) - mu * mu, 0.f);
         const float rstd = rsqrtf(var + p.ln_eps);
         mbar_wait(bar_ka, 0);   /* (complete: both halves are; waited on to keep the phase in step) */
-        for (int h = 0; h < 2; h++) {
-          for (int j = 0; j < 2; j++) {
-            const int c = 8 * h + 2 * cg + j;
-            tmem_ld32(trow + 32 * c, v);
+        for (int j = 0; j < 2; j++) {   /* half 0: K chunk cg of the next layer */
+          const int c = 2 * cg + j;
+          tmem_ld32(trow + 32 * c, v);
 #pragma unroll
-            for (int j4 = 0; j4 < 8; j4++) {
-              const float4 b = __ldg(reinterpret_cast<const float4*>(p.b1 + 32 * c) + j4);
-              const float4 g = __ldg(reinterpret_cast<const float4*>(p.ln_g + 32 * c) + j4);
-              const float4 e = __ldg(reinterpret_cast<const float4*>(p.ln_b + 32 * c) + j4);
-              v[4 * j4 + 0] = fast_tanh((v[4 * j4 + 0] + b.x - mu) * rstd * g.x + e.x);
-              v[4 * j4 + 1] = fast_tanh((v[4 * j4 + 1] + b.y - mu) * rstd * g.y + e.y);
-              v[4 * j4 + 2] = fast_tanh((v[4 * j4 + 2] + b.z - mu) * rstd * g.z + e.z);
-              v[4 * j4 + 3] = fast_tanh((v[4 * j4 + 3] + b.w - mu) * rstd * g.w + e.w);
-            }
-            uint4 qq[4];
-            pack_act32(v, qq);
-            store_packed32(act_s, r, c, qq);
+          for (int j4 = 0; j4 < 8; j4++) {
+            const float4 b = __ldg(reinterpret_cast<const float4*>(p.b1 + 32 * c) + j4);
+            const float4 g = __ldg(reinterpret_cast<const float4*>(p.ln_g + 32 * c) + j4);
+            const float4 e = __ldg(reinterpret_cast<const float4*>(p.ln_b + 32 * c) + j4);
+            v[4 * j4 + 0] = fast_tanh((v[4 * j4 + 0] + b.x - mu) * rstd * g.x + e.x);
+            v[4 * j4 + 1] = fast_tanh((v[4 * j4 + 1] + b.y - mu) * rstd * g.y + e.y);
+            v[4 * j4 + 2] = fast_tanh((v[4 * j4 + 2] + b.z - mu) * rstd * g.z + e.z);
+            v[4 * j4 + 3] = fast_tanh((v[4 * j4 + 3] + b.w - mu) * rstd * g.w + e.w);
           }
-          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   /* generic-proxy stores -> visible to the tensor core */
+          uint4 qq[4];
+          pack_act32(v, qq);
+          store_packed32(act_s, r, c, qq);
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   /* generic-proxy stores -> visible to the tensor core */
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(epi_leader);
+        for (int kc = 4; kc < 8; kc++) {   /* half 1, all warps on one K chunk at a time: the next layer's MMAs follow chunk by chunk */
+          const int c0 = 64 * kc + 16 * cg;
+          tmem_ld16(trow + c0, v);
+#pragma unroll
+          for (int j4 = 0; j4 < 4; j4++) {
+            const float4 b = __ldg(reinterpret_cast<const float4*>(p.b1 + c0) + j4);
+            const float4 g = __ldg(reinterpret_cast<const float4*>(p.ln_g + c0) + j4);
+            const float4 e = __ldg(reinterpret_cast<const float4*>(p.ln_b + c0) + j4);
+            v[4 * j4 + 0] = fast_tanh((v[4 * j4 + 0] + b.x - mu) * rstd * g.x + e.x);
+            v[4 * j4 + 1] = fast_tanh((v[4 * j4 + 1] + b.y - mu) * rstd * g.y + e.y);
+            v[4 * j4 + 2] = fast_tanh((v[4 * j4 + 2] + b.z - mu) * rstd * g.z + e.z);
+            v[4 * j4 + 3] = fast_tanh((v[4 * j4 + 3] + b.w - mu) * rstd * g.w + e.w);
+          }
+          store_act16(act_s, r, kc, cg, v);
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
           asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
           __syncwarp();
-          if (lane == 0) mbar_arrive_cluster(epi_leader + 8 * h);
+          if (lane == 0) mbar_arrive_cluster(epi_leader + 8 * (kc - 3));
         }
       } else {              /* bias, ELU */
         const float* bl = p.b[l - 1];
-        for (int h = 0; h < 2; h++) {
-          mbar_wait(bar_acc + 8 * h, l & 1);
+        {   /* half 0 (under the MMAs of half 1): the thread's 64 columns = K chunk cg of the next layer, held until ka */
+          mbar_wait(bar_acc, l & 1);
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-          if (threadIdx.x == 0 && h == 0) PPROF(4, l, clock64());
+          if (threadIdx.x == 0) PPROF(4, l, clock64());
           uint4 qq[2][4];
 #pragma unroll
           for (int j = 0; j < 2; j++) {
-            const int c = 8 * h + 2 * cg + j;
+            const int c = 2 * cg + j;
             tmem_ld32(trow + 32 * c, v);
 #pragma unroll
             for (int j4 = 0; j4 < 8; j4++) {
@@ -401,13 +440,31 @@ fly_policy_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
             }
             pack_act32(v, qq[j]);
           }
-          if (h == 0) mbar_wait(bar_ka, l & 1);   /* the MMAs of half 1 have read K chunks 0-3: they may be overwritten */
+          mbar_wait(bar_ka, l & 1);   /* the MMAs of half 1 have read K chunks 0-3: they may be overwritten */
 #pragma unroll
-          for (int j = 0; j < 2; j++) store_packed32(act_s, r, 8 * h + 2 * cg + j, qq[j]);
+          for (int j = 0; j < 2; j++) store_packed32(act_s, r, 2 * cg + j, qq[j]);
           asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
           asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
           __syncwarp();
-          if (lane == 0) mbar_arrive_cluster(epi_leader + 8 * h);
+          if (lane == 0) mbar_arrive_cluster(epi_leader);
+        }
+        mbar_wait(bar_acc + 8, l & 1);   /* all of this layer's MMAs are complete */
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        for (int kc = 4; kc < 8; kc++) {   /* half 1 is on the critical path: all warps on one K chunk at a time, the next layer's
+                                              MMAs follow chunk by chunk */
+          const int c0 = 64 * kc + 16 * cg;
+          tmem_ld16(trow + c0, v);
+#pragma unroll
+          for (int j4 = 0; j4 < 4; j4++) {
+            const float4 b = __ldg(reinterpret_cast<const float4*>(bl + c0) + j4);
+            v[4 * j4 + 0] = fast_elu(v[4 * j4 + 0] + b.x); v[4 * j4 + 1] = fast_elu(v[4 * j4 + 1] + b.y);
+            v[4 * j4 + 2] = fast_elu(v[4 * j4 + 2] + b.z); v[4 * j4 + 3] = fast_elu(v[4 * j4 + 3] + b.w);
+          }
+          store_act16(act_s, r, kc, cg, v);
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+          asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster(epi_leader + 8 * (kc - 3));
         }
       }
       if (threadIdx.x == 0) PPROF(5, l, clock64());
