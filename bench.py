@@ -248,6 +248,7 @@ def _actor_loop(torch, eng, N, dev, flush, out, amin, amax, env_only_ms, steps=1
     l0 = fused.launches
 
     inner = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    adder_end = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
 
     def one(k=-1):
         a = torch.minimum(torch.maximum(fused.sample(obs, gen), amin), amax)
@@ -257,6 +258,8 @@ def _actor_loop(torch, eng, N, dev, flush, out, amin, amax, env_only_ms, steps=1
         if k >= 0:
             inner[k][1].record()
         adder.add(a, TS(st, rew, disc, obs))
+        if k >= 0:
+            adder_end[k].record()
     for _ in range(warm):
         one()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
@@ -267,6 +270,7 @@ def _actor_loop(torch, eng, N, dev, flush, out, amin, amax, env_only_ms, steps=1
     torch.cuda.synchronize(dev)
     ms = float(np.mean([a.elapsed_time(b) for a, b in ev]))
     env_ms = float(np.mean([a.elapsed_time(b) for a, b in inner]))   # the step kernel inside the loop, under the policy's actions
+    adder_ms = float(np.mean([inner[k][1].elapsed_time(adder_end[k]) for k in range(steps)]))
     pe = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
     for k in range(steps):
         flush.fill_(float(k))
@@ -279,7 +283,7 @@ def _actor_loop(torch, eng, N, dev, flush, out, amin, amax, env_only_ms, steps=1
            "step_kernel_ms_in_loop": env_ms, "ratio_to_env_only": env_ms / ms,
            "note": "ratio_to_env_only = the step kernel's own time inside this loop / the loop's time per step (the policy's N(0, 0.7) "
                    "actions keep the flies on their feet: more contacts per step than under U(ctrlrange), headline_ms = %.2f)" % env_only_ms,
-           "policy_ms": pms, "policy_tflops": flop / (pms * 1e-3) / 1e12,
+           "adder_ms": adder_ms, "policy_ms": pms, "policy_tflops": flop / (pms * 1e-3) / 1e12,
            "policy_kernel": "fly_policy_kernel (tcgen05.mma kind::f16 bf16 -> fp32 in TMEM, TMA weight tiles; incl. the fp32 -> bf16 cast of "
                             "the observations and torch.randn for the noise)",
            "policy_launches_per_step": (fused.launches - l0) / float(warm + 2 * steps), "transitions_written": adder.num_written}

@@ -27,6 +27,9 @@ from __future__ import annotations
 import math
 from typing import Callable, Optional
 
+import os
+import sys
+
 import torch
 from torch import nn
 
@@ -188,6 +191,8 @@ class NStepTransitionAdder:
     [N, ...] tensors with a boolean `valid` mask (no host synchronisation), and - only when an episode ended in this call, which
     costs the call's single device-to-host read - the shrinking-horizon transitions of the ended envs."""
 
+    _force_torch = os.environ.get("FLYB_ADDER_TORCH") == "1"   # (tools/adder_probe.py: time the torch operations on CUDA tensors as well)
+
     def __init__(self, num_envs: int, obs_dim: int, action_dim: int, n_step: int, discount: float, device="cuda",
                  sink: Optional[Callable[[dict], None]] = None, count_on_host: bool = True):
         self.N, self.n, self.gamma = int(num_envs), int(n_step), float(discount)
@@ -203,6 +208,13 @@ class NStepTransitionAdder:
         self.sink = sink
         self.written = torch.zeros((), dtype=torch.long, device=dev)     # transitions shipped so far (device-side counter)
         self._count_on_host = count_on_host
+        if dev.type == "cuda":
+            # The flush runs only when an episode ends; its first use of torch's indexing / scan kernels costs ~0.1 s of lazy
+            # loading, which would land in some later control step.  Take it here, on an episode of env 0 that is thrown away.
+            ended = torch.zeros(self.N, dtype=torch.bool, device=dev)
+            ended[0] = True
+            self._flush(ended, torch.full((self.N,), self.n + 1, dtype=torch.long, device=dev), ship=False)
+            torch.cuda.synchronize(dev)
 
     @property
     def num_written(self) -> int:
@@ -240,35 +252,45 @@ class NStepTransitionAdder:
 
     def add(self, action: torch.Tensor, next_timestep):
         """Append (a_t, r_t, d_t, o_{t+1}) for every env that is inside an episode; envs whose `next_timestep` is FIRST
-        (auto-reset inside env.step) start a new episode instead and their action is ignored, as the env ignored it."""
+        (auto-reset inside env.step) start a new episode instead and their action is ignored, as the env ignored it.
+        On CUDA tensors the whole step is one kernel (`flyb_adder_step`, csrc/flyb_actor.cu); the torch operations below are the
+        same arithmetic for CPU tensors (and what tests/test_actors.py holds the kernel to)."""
         st = next_timestep.step_type
-        first = st == FIRST
-        self.add_first(next_timestep, first)
-        live = self.started & ~first
         obs = batch_concat(next_timestep.observation)
         e = self._env
-        c = self.count
-        slot, oslot = c % self.n, (c + 1) % (self.n + 1)
-        # unconditional writes: an env that is not live has count 0 (it was just (re)started, or never started), so these land
-        # in slots 0 / 1, which its first live step overwrites before anything reads them - no gather / select needed
-        self.act[e, slot] = action
-        self.rew[e, slot] = next_timestep.reward
-        self.disc[e, slot] = next_timestep.discount
-        self.obs[e, oslot] = obs
-        c = torch.where(live, c + 1, c)
-        self.count = c
-        # the transition acme writes after every step: from max(0, t - n) over min(t, n) steps (fixed shape, masked)
-        start = torch.clamp(c - self.n, min=0)
-        hor = torch.clamp(c, max=self.n).clamp(min=1)
-        batch = self._batch(e, start, hor, next_obs=obs)     # the per-step transition ends at the observation just received
-        batch["valid"] = live
-        self.written += live.sum()
-        if self.sink is not None:
-            self.sink(batch)
-        # shrinking-horizon flush of the envs whose episode just ended: starts max(0, L - n) + 1 .. L - 1, all ending at L
-        ended = live & (st == LAST)
-        if not bool(ended.any()):        # the call's one host read
-            return
+        if self.obs.is_cuda and not self._force_torch:
+            live, c = self._add_cuda(action, next_timestep, obs)
+            if not int(self._any_ended.item()):              # the call's one host read
+                return
+        else:
+            first = st == FIRST
+            self.add_first(next_timestep, first)
+            live = self.started & ~first
+            c = self.count
+            slot, oslot = c % self.n, (c + 1) % (self.n + 1)
+            # unconditional writes: an env that is not live has count 0 (it was just (re)started, or never started), so these land
+            # in slots 0 / 1, which its first live step overwrites before anything reads them - no gather / select needed
+            self.act[e, slot] = action
+            self.rew[e, slot] = next_timestep.reward
+            self.disc[e, slot] = next_timestep.discount
+            self.obs[e, oslot] = obs
+            c = torch.where(live, c + 1, c)
+            self.count = c
+            # the transition acme writes after every step: from max(0, t - n) over min(t, n) steps (fixed shape, masked)
+            start = torch.clamp(c - self.n, min=0)
+            hor = torch.clamp(c, max=self.n).clamp(min=1)
+            batch = self._batch(e, start, hor, next_obs=obs)     # the per-step transition ends at the observation just received
+            batch["valid"] = live
+            self.written += live.sum()
+            if self.sink is not None:
+                self.sink(batch)
+            if not bool((live & (st == LAST)).any()):        # the call's one host read
+                return
+        self._flush(live & (st == LAST), c)
+
+    def _flush(self, ended, c, ship: bool = True):
+        """Shrinking-horizon transitions of the envs whose episode just ended: starts max(0, L - n) + 1 .. L - 1, all ending at L."""
+        e = self._env
         last = e[ended]
         j = torch.arange(1, self.n, device=last.device)
         s = c[last][:, None] - self.n + j[None, :]
@@ -279,9 +301,44 @@ class NStepTransitionAdder:
         if env2.numel():
             tail = self._batch(env2, start2, hor2)
             tail["valid"] = torch.ones_like(env2, dtype=torch.bool)
-            self.written += env2.numel()
-            if self.sink is not None:
-                self.sink(tail)
+            if ship:
+                self.written += env2.numel()
+                if self.sink is not None:
+                    self.sink(tail)
+
+    def _add_cuda(self, action, next_timestep, obs):
+        """One launch: episode starts, ring appends, the per-step transition of every env and the `episode ended somewhere` flag
+        (self._any_ended).  Returns (live, count) for the flush."""
+        from . import engine as _engine
+        import ctypes
+        L = _engine.lib()
+        N, O, A = self.N, self.obs.shape[2], self.act.shape[2]
+        dev = self.obs.device
+        f32 = lambda t: t.to(dtype=torch.float32).contiguous()
+        action, obs = f32(action), f32(obs)
+        reward, disc = f32(next_timestep.reward), f32(next_timestep.discount)
+        st = next_timestep.step_type.to(dtype=torch.int32).contiguous()
+        out_obs = torch.empty((N, O), device=dev); out_act = torch.empty((N, A), device=dev)
+        out_R = torch.empty(N, device=dev); out_D = torch.empty(N, device=dev)
+        valid = torch.empty(N, dtype=torch.bool, device=dev)
+        start = torch.empty(N, dtype=torch.long, device=dev); hor = torch.empty(N, dtype=torch.long, device=dev)
+        if not hasattr(self, "_any_ended"):
+            self._any_ended = torch.zeros(1, dtype=torch.int32, device=dev)
+        vp = ctypes.c_void_p
+        stream = torch.cuda.current_stream(dev).cuda_stream
+        rc = L.flyb_adder_step(dev.index if dev.index is not None else torch.cuda.current_device(), N, O, A, self.n, ctypes.c_float(self.gamma),
+                               vp(self.obs.data_ptr()), vp(self.act.data_ptr()), vp(self.rew.data_ptr()), vp(self.disc.data_ptr()),
+                               vp(self.count.data_ptr()), vp(self.started.data_ptr()), vp(action.data_ptr()), vp(obs.data_ptr()),
+                               vp(reward.data_ptr()), vp(disc.data_ptr()), vp(st.data_ptr()), vp(out_obs.data_ptr()),
+                               vp(out_act.data_ptr()), vp(out_R.data_ptr()), vp(out_D.data_ptr()), vp(valid.data_ptr()),
+                               vp(start.data_ptr()), vp(hor.data_ptr()), vp(self.written.data_ptr()), vp(self._any_ended.data_ptr()),
+                               vp(stream))
+        if rc:
+            raise RuntimeError("flyb_adder_step failed")
+        if self.sink is not None:
+            self.sink({"observation": out_obs, "action": out_act, "reward": out_R, "discount": out_D, "next_observation": obs,
+                       "env": self._env, "start": start, "horizon": hor, "valid": valid})
+        return valid, self.count
 
 
 class BatchedFeedForwardActor:

@@ -30,7 +30,7 @@ EXPORTS = ["flyb_create", "flyb_destroy", "flyb_last_error", "flyb_info", "flyb_
            "flyb_use_generic_kernel", "flyb_step_noalloc", "flyb_fma_peak", "flyb_hfield_contacts", "flyb_render_eyes",
            "flyb_load_terrain", "flyb_render",
            "flyb_policy_create", "flyb_policy_destroy", "flyb_policy_last_error", "flyb_policy_launches",
-           "flyb_policy_set_weights", "flyb_policy_forward"]
+           "flyb_policy_set_weights", "flyb_policy_forward", "flyb_adder_step"]
 
 
 N_SPEC_MODELS = 5   # csrc/fly_dims_gen.h: FLY_SPEC_COUNT
@@ -58,7 +58,7 @@ def compile_library(out_path: str, extra_flags=(), verbose: bool = False, units=
     # flyb_cuda.cu also holds the height-field and eye-camera kernels.  The portal refinement against a prism takes support points
     # among the vertices of a face whenever its direction is that face's normal: ties decided by the last bit.  Without
     # multiply-add contraction the float64 device code rounds like the CPU code and picks the same vertex.
-    tus = [("flyb_cuda", "flyb_cuda.cu", ["-fmad=false"]), ("flyb_policy", "flyb_policy.cu", [])]
+    tus = [("flyb_cuda", "flyb_cuda.cu", ["-fmad=false"]), ("flyb_policy", "flyb_policy.cu", []), ("flyb_actor", "flyb_actor.cu", [])]
     for nl, w, l, sp in (units if units is not None else kernel_units()):
         tus.append((f"k_{nl}_{w}_{l}_{'g' if sp < 0 else 's%d' % sp}", "flyb_kern.cu",
                     [f"-DFLY_NL={nl}", f"-DFLY_TU_WARPS={w}", f"-DFLY_TU_LEVEL={l}", f"-DFLY_TU_SPEC={sp}"]))
@@ -135,6 +135,7 @@ def lib():
         L.flyb_policy_launches.restype = ctypes.c_longlong
         L.flyb_policy_set_weights.argtypes = [vp] + [vp] * 14 + [ctypes.c_float, ctypes.c_float, ctypes.c_float, c_i, vp]
         L.flyb_policy_forward.argtypes = [vp, vp, c_i, vp, vp, vp, vp, vp]
+        L.flyb_adder_step.argtypes = [c_i] * 5 + [ctypes.c_float] + [vp] * 21
         _lib = L
     return _lib
 

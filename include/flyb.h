@@ -193,6 +193,24 @@ int flyb_policy_set_weights(flyb_policy_handle h, const float* w1, const float* 
 int flyb_policy_forward(flyb_policy_handle h, const float* obs, int n_rows, const float* eps, float* mean, float* scale,
                         float* action, void* stream);
 
+/* One step of the actor's n-step transition adder for N environments (replaces the per-environment calls of acme's
+ * NStepTransitionAdder.add that vnl_ray/agents/actors.py:59-89 makes; adder built in vnl_ray/agents/ray_distributed_dmpo.py:268-300).
+ * All pointers are DEVICE buffers owned by the caller (flybody_b200/actors.py: NStepTransitionAdder); the function keeps no state.
+ *   ring_obs [N, n_step + 1, obs_dim], ring_act [N, n_step, action_dim], ring_rew / ring_disc [N, n_step], count [N] int64
+ *   (transitions added to the running episode), started [N] bytes: the rings, updated in place;
+ *   action [N, action_dim], next_obs [N, obs_dim], reward / step_discount [N], step_type [N] int32 (0 FIRST, 1 MID, 2 LAST): the step.
+ *   An env whose step_type is FIRST starts a new episode (its action is ignored, as the env ignored it).
+ *   out_*: the transition acme writes after every step, from s = max(0, t - n_step) over h = min(t, n_step) steps:
+ *   out_obs = o_s, out_act = a_s, out_return = sum_k (prod_{j<k} discount d_{s+j}) r_{s+k}, out_discount = discount^(h-1) prod d,
+ *   out_valid [N] bytes (the env is inside an episode), out_start / out_horizon [N] int64; the transition ends at next_obs.
+ *   written [1] int64 += number of valid transitions; any_ended [1] int32 = 1 when a valid env's step_type is LAST (the caller then
+ *   flushes the shrinking-horizon transitions of those envs).  Enqueued on `stream`; returns non-zero on bad arguments. */
+int flyb_adder_step(int device, int num_envs, int obs_dim, int action_dim, int n_step, float discount, float* ring_obs,
+                    float* ring_act, float* ring_rew, float* ring_disc, int64_t* count, uint8_t* started, const float* action,
+                    const float* next_obs, const float* reward, const float* step_discount, const int32_t* step_type,
+                    float* out_obs, float* out_act, float* out_return, float* out_discount, uint8_t* out_valid, int64_t* out_start,
+                    int64_t* out_horizon, int64_t* written, int32_t* any_ended, void* stream);
+
 /* Measurement utility (no reference counterpart): FP32 fused-multiply-add throughput of the device in TFLOP/s, measured with
  * a register-resident FMA micro-benchmark - the denominator of the FP32-pipe fractions bench.py reports. */
 int flyb_fma_peak(int device, double* tflops);
