@@ -123,3 +123,26 @@ def test_actor_loop_with_the_fused_policy():
     steps, reward = loop.run(6)
     assert steps == 6 * 256 and np.isfinite(reward) and sum(got) >= 5 * 256
     env.close(); fused.close()
+
+
+def test_fused_policy_is_bit_reproducible_at_the_bench_size():
+    """16 384 rows = 64 CTA pairs, 300 calls on the same observations with an L2 flush in between now and then: every call must give
+    the first call's bits.  The kernel has no atomics in its arithmetic, so any difference would be a synchronisation hole in the
+    TMA / MMA / epilogue hand-offs (stale activations, a stage reused too early, an accumulator read before its commit)."""
+    from flybody_b200 import actors as A
+    dev = torch.device("cuda:0")
+    torch.manual_seed(3)
+    pol = A.LayerNormMLPPolicy(741, 59).to(dev)
+    with torch.no_grad():   # heads away from zero so that all five layers matter
+        pol.mean.weight.normal_(std=0.05); pol.scale.weight.normal_(std=0.05)
+    fused = A.FusedPolicy(pol, max_rows=16384)
+    obs = torch.randn((16384, 741), device=dev)
+    flush = torch.empty(192 * 1024 * 1024 // 4, device=dev)
+    mean0, scale0 = [t.clone() for t in fused(obs)]
+    assert torch.isfinite(mean0).all() and torch.isfinite(scale0).all()
+    for k in range(300):
+        if k % 7 == 0:
+            flush.fill_(float(k))
+        mean, scale = fused(obs)
+        assert torch.equal(mean, mean0) and torch.equal(scale, scale0), f"call {k} differs"
+    fused.close()
