@@ -112,7 +112,7 @@ template <class R> FLY_INL int eye_ray_next_cell(const FlyScene& sc, EyeRay<R>& 
  * terrain (background), 3: the current cell (y.c, y.r, corner heights in y.hc) passes the height test - eye_ray_test decides.
  * Split from the triangle tests so that the lanes of a warp can run the expensive part together (flyb_render). */
 template <class R> FLY_INL int eye_ray_advance(const FlyScene& sc, const float* h, const float* bmax, EyeRay<R>& y) {
-  const R half = sc.half, cell = 2 * half / (sc.ncol - 1), big = R(1e30);
+  const R half = sc.half, cell = 2 * half / (sc.ncol - 1), icell = (sc.ncol - 1) / (2 * half), big = R(1e30);
   const R *o = y.o, *d = y.d;
   if (++y.steps > 2 * (sc.nrow + sc.ncol)) return 1;
   if (bmax) {
@@ -149,21 +149,23 @@ template <class R> FLY_INL int eye_ray_advance(const FlyScene& sc, const float* 
       if (txe < tye) {   /* leaves through a column line: the row follows from y there, kept inside the block's rows */
         c = y.sc_ > 0 ? ce : ce - 1;
         if (c < 0 || c > sc.ncol - 2) return 1;
-        int rr = (int)floor((o[1] + te * d[1] + half) / cell);
+        int rr = (int)floor((o[1] + te * d[1] + half) * icell);
         const int rlo = br << S, rhi = ((br + 1) << S) - 1;
         rr = rr < rlo ? rlo : (rr > rhi ? rhi : rr);
         r = rr > sc.nrow - 2 ? sc.nrow - 2 : rr;
       } else {
         r = y.sr_ > 0 ? re : re - 1;
         if (r < 0 || r > sc.nrow - 2) return 1;
-        int cc = (int)floor((o[0] + te * d[0] + half) / cell);
+        int cc = (int)floor((o[0] + te * d[0] + half) * icell);
         const int clo = bc << S, chi = ((bc + 1) << S) - 1;
         cc = cc < clo ? clo : (cc > chi ? chi : cc);
         c = cc > sc.ncol - 2 ? sc.ncol - 2 : cc;
       }
       y.c = c; y.r = r; y.tin = te;
-      y.tx = d[0] != 0 ? ((-half + (c + (y.sc_ > 0 ? 1 : 0)) * cell) - o[0]) / d[0] : big;
-      y.ty = d[1] != 0 ? ((-half + (r + (y.sr_ > 0 ? 1 : 0)) * cell) - o[1]) / d[1] : big;
+      /* (reciprocals instead of divisions in the jump path: an IEEE division is ~10 instructions, and these two lines were 12 % of
+         the renderer's; where the walk resumes differs by an ulp at most, which the cell tests that follow absorb) */
+      y.tx = d[0] != 0 ? ((-half + (c + (y.sc_ > 0 ? 1 : 0)) * cell) - o[0]) * y.idx : big;
+      y.ty = d[1] != 0 ? ((-half + (r + (y.sr_ > 0 ? 1 : 0)) * cell) - o[1]) * y.idy : big;
       if (d[2] >= 0 && o[2] + te * d[2] > (R)bmax[sc.nbr * sc.nbc + sc.nbr2 * sc.nbc2] + R(1e-4)) return 1;
       if (attempt >= 3) return 0;
     }
