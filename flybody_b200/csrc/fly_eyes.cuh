@@ -69,7 +69,11 @@ template <class R> struct EyeRay {
   int c, r, sc_, sr_, steps;
   int blk[2][2];   /* per level: the block found NOT skippable last (its sub-blocks / cells are walked) */
   R hc[4];         /* corner heights of the candidate cell (eye_ray_advance -> eye_ray_test) */
+  R gmax;          /* with block maxima: the terrain's highest point + 1e-4 (eye_ray_set_gmax), above which a rising ray is done */
 };
+template <class R> FLY_INL void eye_ray_set_gmax(const FlyScene& sc, const float* bmax, EyeRay<R>& y) {
+  y.gmax = bmax ? (R)bmax[sc.nbr * sc.nbc + sc.nbr2 * sc.nbc2] + R(1e-4) : R(1e30);
+}
 
 /* false: the ray misses the slab |x|, |y| <= half (background) */
 template <class R> FLY_INL bool eye_ray_init(const FlyScene& sc, EyeRay<R>& y) {
@@ -120,7 +124,7 @@ template <class R> FLY_INL int eye_ray_advance(const FlyScene& sc, const float* 
        block until it leaves the block, no cell of the block can pass the height test below, and the walk resumes in the first
        cell behind the block's far edge.  Up to four jumps per step, so that the lanes of a warp reach their next cell test
        together.  A rising ray above the terrain's highest point is done. */
-    if (d[2] >= 0 && o[2] + y.tin * d[2] > (R)bmax[sc.nbr * sc.nbc + sc.nbr2 * sc.nbc2] + R(1e-4)) return 1;
+    if (d[2] >= 0 && o[2] + y.tin * d[2] > y.gmax) return 1;
     for (int attempt = 0;; attempt++) {
       int lv = -1;
       R te = 0, txe = 0, tye = 0;
@@ -166,7 +170,7 @@ template <class R> FLY_INL int eye_ray_advance(const FlyScene& sc, const float* 
          the renderer's; where the walk resumes differs by an ulp at most, which the cell tests that follow absorb) */
       y.tx = d[0] != 0 ? ((-half + (c + (y.sc_ > 0 ? 1 : 0)) * cell) - o[0]) * y.idx : big;
       y.ty = d[1] != 0 ? ((-half + (r + (y.sr_ > 0 ? 1 : 0)) * cell) - o[1]) * y.idy : big;
-      if (d[2] >= 0 && o[2] + te * d[2] > (R)bmax[sc.nbr * sc.nbc + sc.nbr2 * sc.nbc2] + R(1e-4)) return 1;
+      if (d[2] >= 0 && o[2] + te * d[2] > y.gmax) return 1;
       if (attempt >= 3) return 0;
     }
   }
@@ -225,8 +229,10 @@ template <class R> FLY_INL void eye_pixel(const FlyScene& sc, const float* h, co
   EyeRay<R> y;
   R rgb[3] = {(R)sc.sky[0], (R)sc.sky[1], (R)sc.sky[2]};
   eye_ray_of_pixel(y, pos, mat, W, H, tanhalf, i, j);
-  if (eye_ray_init(sc, y))
+  if (eye_ray_init(sc, y)) {
+    eye_ray_set_gmax(sc, bmax, y);
     while (eye_ray_step(sc, h, bmax, y, rgb) == 0) {}
+  }
   for (int k = 0; k < 3; k++) out[k] = (unsigned char)(int)(rgb[k] * R(255) + R(0.5));
 }
 #endif

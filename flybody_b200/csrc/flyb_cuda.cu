@@ -186,6 +186,7 @@ __global__ void __launch_bounds__(256) fly_eyes_env_kernel(FlyScene sc, int ncam
           bm = sc.bmax ? sc.bmax + (size_t)t * tstride : nullptr;
           eye_ray_of_pixel(y, c, c + 3, W, H, tanhalf, i, j);
           if (!eye_ray_init(sc, y)) { eye_store(out + 3 * (size_t)p, sc.sky); pix = -1; }
+          else eye_ray_set_gmax(sc, bm, y);
         }
       }
     }
