@@ -112,6 +112,11 @@ template <class R> FLY_INL int eye_ray_next_cell(const FlyScene& sc, EyeRay<R>& 
   return 0;
 }
 
+template <class R> FLY_INL bool eye_ray_in_known_blocks(const EyeRay<R>& y) {
+  return (y.r >> FLY_EYE_SHIFT) == y.blk[0][0] && (y.c >> FLY_EYE_SHIFT) == y.blk[0][1] &&
+         (y.r >> FLY_EYE_SHIFT2) == y.blk[1][0] && (y.c >> FLY_EYE_SHIFT2) == y.blk[1][1];
+}
+
 /* the walk up to the next cell the ray may hit: jumps over blocks, cells with the height test.  Returns 0: go on, 1: left the
  * terrain (background), 3: the current cell (y.c, y.r, corner heights in y.hc) passes the height test - eye_ray_test decides.
  * Split from the triangle tests so that the lanes of a warp can run the expensive part together (flyb_render). */
@@ -182,6 +187,74 @@ template <class R> FLY_INL int eye_ray_advance(const FlyScene& sc, const float* 
   const R za = o[2] + y.tin * d[2], zb = o[2] + (tout < y.t1 ? tout : y.t1) * d[2];
   if ((za < zb ? za : zb) <= hmax) { y.hc[0] = h00; y.hc[1] = h01; y.hc[2] = h10; y.hc[3] = h11; return 3; }
   return eye_ray_next_cell(sc, y);
+}
+
+/* The walk as separate moves for a warp that schedules them (flyb_render): eye_ray_jump tries ONE jump over a block the ray stays above -
+ * returns 0: jumped, 1: left the terrain, 2: no block to jump (the cell has to be looked at); eye_ray_cell tests the current cell -
+ * returns 3: candidate (corner heights in y.hc), 1: left the terrain, 0: moved on to the next cell, which still lies in the blocks
+ * found not skippable, 4: moved on and a jump may be possible again. */
+template <class R> FLY_INL int eye_ray_jump(const FlyScene& sc, const float* bmax, EyeRay<R>& y) {
+  const R half = sc.half, cell = 2 * half / (sc.ncol - 1), icell = (sc.ncol - 1) / (2 * half), big = R(1e30);
+  const R *o = y.o, *d = y.d;
+  if (++y.steps > 4 * (sc.nrow + sc.ncol)) return 1;
+  if (d[2] >= 0 && o[2] + y.tin * d[2] > y.gmax) return 1;
+  int lv = -1;
+  R te = 0, txe = 0, tye = 0;
+  int br = 0, bc = 0, ce = 0, re = 0, S = 0;
+#pragma unroll
+  for (int v = 0; v < 2; v++) {
+    if (lv >= 0) continue;
+    S = v == 0 ? FLY_EYE_SHIFT : FLY_EYE_SHIFT2;
+    br = y.r >> S; bc = y.c >> S;
+    if (br == y.blk[v][0] && bc == y.blk[v][1]) continue;
+    const float* tbl = v == 0 ? bmax : bmax + sc.nbr * sc.nbc;
+    const int nbc = v == 0 ? sc.nbc : sc.nbc2;
+    ce = y.sc_ > 0 ? ((bc + 1) << S) : (bc << S);
+    re = y.sr_ > 0 ? ((br + 1) << S) : (br << S);
+    txe = d[0] != 0 ? ((-half + (R)ce * cell) - o[0]) * y.idx : big;
+    tye = d[1] != 0 ? ((-half + (R)re * cell) - o[1]) * y.idy : big;
+    te = txe < tye ? txe : tye;
+    const R tz = (te < y.t1 ? te : y.t1) * (1 + R(1e-5)) + R(1e-5);
+    const R za = o[2] + y.tin * d[2], zb = o[2] + tz * d[2];
+    if (!((za < zb ? za : zb) > (R)tbl[br * nbc + bc] + R(1e-4))) { y.blk[v][0] = br; y.blk[v][1] = bc; continue; }
+    lv = v;
+  }
+  if (lv < 0) return 2;
+  if (te >= y.t1) return 1;
+  int c, r;
+  if (txe < tye) {
+    c = y.sc_ > 0 ? ce : ce - 1;
+    if (c < 0 || c > sc.ncol - 2) return 1;
+    int rr = (int)floor((o[1] + te * d[1] + half) * icell);
+    const int rlo = br << S, rhi = ((br + 1) << S) - 1;
+    rr = rr < rlo ? rlo : (rr > rhi ? rhi : rr);
+    r = rr > sc.nrow - 2 ? sc.nrow - 2 : rr;
+  } else {
+    r = y.sr_ > 0 ? re : re - 1;
+    if (r < 0 || r > sc.nrow - 2) return 1;
+    int cc = (int)floor((o[0] + te * d[0] + half) * icell);
+    const int clo = bc << S, chi = ((bc + 1) << S) - 1;
+    cc = cc < clo ? clo : (cc > chi ? chi : cc);
+    c = cc > sc.ncol - 2 ? sc.ncol - 2 : cc;
+  }
+  y.c = c; y.r = r; y.tin = te;
+  y.tx = d[0] != 0 ? ((-half + (c + (y.sc_ > 0 ? 1 : 0)) * cell) - o[0]) * y.idx : big;
+  y.ty = d[1] != 0 ? ((-half + (r + (y.sr_ > 0 ? 1 : 0)) * cell) - o[1]) * y.idy : big;
+  if (d[2] >= 0 && o[2] + te * d[2] > y.gmax) return 1;
+  return 0;
+}
+template <class R> FLY_INL int eye_ray_cell(const FlyScene& sc, const float* h, EyeRay<R>& y) {
+  const R *o = y.o, *d = y.d;
+  if (++y.steps > 4 * (sc.nrow + sc.ncol)) return 1;
+  const int c = y.c, r = y.r;
+  const R tout = y.tx < y.ty ? y.tx : y.ty;
+  const R h00 = eye_height<R>(h, sc.ncol, r, c, sc.zoff), h01 = eye_height<R>(h, sc.ncol, r, c + 1, sc.zoff);
+  const R h10 = eye_height<R>(h, sc.ncol, r + 1, c, sc.zoff), h11 = eye_height<R>(h, sc.ncol, r + 1, c + 1, sc.zoff);
+  const R hmax = fmax_(fmax_(h00, h01), fmax_(h10, h11));
+  const R za = o[2] + y.tin * d[2], zb = o[2] + (tout < y.t1 ? tout : y.t1) * d[2];
+  if ((za < zb ? za : zb) <= hmax) { y.hc[0] = h00; y.hc[1] = h01; y.hc[2] = h10; y.hc[3] = h11; return 3; }
+  if (eye_ray_next_cell(sc, y)) return 1;
+  return eye_ray_in_known_blocks(y) ? 0 : 4;
 }
 
 /* the two triangles of the candidate cell; returns 2: hit (rgb written), else what eye_ray_next_cell says */
